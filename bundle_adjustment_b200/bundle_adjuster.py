@@ -1,0 +1,214 @@
+"""Drop-in replacement for the reference's ``BundleAdjuster`` (``src/bundle_adjuster.py:16-240``).
+
+Same constructor and ``run(gmap)`` signature, same in-place mutation of ``gmap.keyframes[id].R/.t`` and
+``gmap.map_points[id].position``, same skip / divergence behaviour and the same stdout lines (the
+``LBA Complete`` line is parsed by the reference's ``src/analyze_log.py:42-45``).  The optimisation
+itself - the reference's ``scipy.optimize.least_squares`` call at ``:170-174`` - runs on the GPU through
+``libba_b200.so`` (Levenberg-Marquardt on the Schur complement, same Huber objective).  The private
+helpers keep the reference's names and argument lists so they can be called side by side with the
+reference's in tests.
+
+Flat import, like the reference (``from bundle_adjuster import BundleAdjuster`` with
+``bundle_adjustment_b200`` on ``sys.path``) or ``from bundle_adjustment_b200 import BundleAdjuster``.
+"""
+from __future__ import annotations
+
+import os
+from typing import Dict, List, Optional, Tuple
+
+import numpy as np
+
+from .geometry import matrix_to_rvec, rvec_to_matrix
+from .solver import FlatSolver
+
+
+class BundleAdjuster:
+    """Local bundle adjustment over the most recent window of keyframes, on a B200."""
+
+    def __init__(self, camera_matrix, window_size=5, *, device: int = 0, max_iters: int = 50, ftol: float = 1e-6,
+                 xtol: float = 1e-8, gtol: float = 1e-8, huber_delta: float = 1.0, robust_mode: str = "irls",
+                 verbose: int = 0, lba_steps_dir: Optional[str] = None, solver_options: Optional[dict] = None):
+        # public, mutable attributes exactly as in the reference (src/main.py:83-86 mutates window_size)
+        self.camera_matrix = camera_matrix
+        self.window_size = window_size
+        self.device = device
+        self.solver_options = dict(max_iters=max_iters, ftol=ftol, xtol=xtol, gtol=gtol, huber_delta=huber_delta,
+                                   robust_mode=robust_mode, verbose=verbose)
+        if solver_options:
+            self.solver_options.update(solver_options)
+        # the reference dumps a .pcd after every successful LBA (src/bundle_adjuster.py:187-193) through
+        # Open3D, which is unavailable on this box; set lba_steps_dir to get the same file as ASCII PCD.
+        self.lba_steps_dir = lba_steps_dir
+        self.last_stats: Optional[dict] = None
+        self._solver: Optional[FlatSolver] = None
+
+    # ------------------------------------------------------------------------------------------
+    def _get_solver(self) -> FlatSolver:
+        if self._solver is None:
+            self._solver = FlatSolver(self.device)   # raises without a GPU / built library: no CPU path
+        return self._solver
+
+    def _intrinsics(self):
+        K = np.asarray(self.camera_matrix, dtype=np.float64)
+        return K[0, 0], K[1, 1], K[0, 2], K[1, 2]
+
+    @staticmethod
+    def _index_observations(adjustable_kf_ids, map_point_ids, observations, keypoints_2d, fixed_kf_id=None):
+        """Observation rows -> (obs_cam, obs_pt, obs_uv) in the reference's row order.  Rows whose map
+        point or keyframe is unknown are dropped, as ``_cost_function`` drops them (``:54, 63``)."""
+        kf_idx = {kf_id: i for i, kf_id in enumerate(adjustable_kf_ids)}
+        mp_idx = {mp_id: i for i, mp_id in enumerate(map_point_ids)}
+        cams, pts, uvs = [], [], []
+        for kf_id, mp_id in observations:
+            p = mp_idx.get(mp_id)
+            if p is None:
+                continue
+            c = kf_idx.get(kf_id)
+            if c is None:
+                if fixed_kf_id is not None and kf_id != fixed_kf_id:
+                    continue
+                c = -1
+            cams.append(c)
+            pts.append(p)
+            uvs.append(keypoints_2d[(kf_id, mp_id)])
+        return (np.asarray(cams, dtype=np.int32), np.asarray(pts, dtype=np.int32),
+                np.asarray(uvs, dtype=np.float64).reshape(-1, 2))
+
+    # -- reference-named helpers -----------------------------------------------------------------
+    def _gather_local_data(self, gmap, local_kf_ids: list):
+        """Same contract as the reference's (``:195-218``): sorted unique map point ids of the window,
+        ``(kf_id, mp_id)`` rows in keyframe-major order, and the ``(kf_id, mp_id) -> (u, v)`` dict (a pair
+        listed twice keeps both rows but only the last keypoint)."""
+        seen = set()
+        observations: List[Tuple[int, int]] = []
+        keypoints_2d: Dict[Tuple[int, int], Tuple[float, float]] = {}
+        map_points = gmap.map_points
+        for kf_id in local_kf_ids:
+            kf = gmap.keyframes[kf_id]
+            kps = kf.keypoints
+            for mp_id, kp_idx in kf.observations:
+                if mp_id in map_points:
+                    seen.add(mp_id)
+                    observations.append((kf_id, mp_id))
+                    keypoints_2d[(kf_id, mp_id)] = kps[kp_idx].pt
+        return sorted(seen), observations, keypoints_2d
+
+    def _cost_function(self, params, fixed_kf_pose, fixed_kf_id, adjustable_kf_ids, map_point_ids, observations,
+                       keypoints_2d):
+        """Re-projection residuals (observed - projected, x then y per row) for the parameter vector
+        ``[rvecs | tvecs | points]``; same signature as the reference's (``:24-72``), evaluated by the
+        device residual kernel."""
+        nc, npt = len(adjustable_kf_ids), len(map_point_ids)
+        params = np.asarray(params, dtype=np.float64)
+        fixed_R, fixed_t = fixed_kf_pose
+        obs_cam, obs_pt, obs_uv = self._index_observations(adjustable_kf_ids, map_point_ids, observations,
+                                                           keypoints_2d, fixed_kf_id)
+        if obs_cam.size == 0:
+            return np.array([])
+        fx, fy, cx, cy = self._intrinsics()
+        s = self._get_solver()
+        s.set_problem(fx, fy, cx, cy, params[:3 * nc], params[3 * nc:6 * nc], matrix_to_rvec(fixed_R),
+                      np.asarray(fixed_t, dtype=np.float64).ravel(), params[6 * nc:6 * nc + 3 * npt],
+                      obs_cam, obs_pt, obs_uv)
+        return s.residuals()
+
+    def _prepare_sparsity_matrix(self, num_adj_kfs, num_mps, adj_kf_ids, mp_ids, observations):
+        """0/1 Jacobian structure, shape (2 * n_obs, 6 * n_kfs + 3 * n_mps); same signature as the
+        reference's (``:74-120``).  Built by the device (``ba_sparsity_csr``) and returned as a SciPy CSR
+        matrix whose ``indptr``/``indices`` equal ``reference_matrix.tocsr()``'s.  The GPU solver does not
+        need it; it exists for callers and tests that do."""
+        from scipy.sparse import csr_matrix
+        kp = {o: (0.0, 0.0) for o in observations}
+        obs_cam, obs_pt, obs_uv = self._index_observations(adj_kf_ids, mp_ids, observations, kp, None)
+        if obs_cam.size != len(observations):
+            raise ValueError("observation of a map point outside mp_ids")      # the reference would leave empty rows
+        s = self._get_solver()
+        s.set_problem(1.0, 1.0, 0.0, 0.0, np.zeros((num_adj_kfs, 3)), np.zeros((num_adj_kfs, 3)), np.zeros(3), np.zeros(3),
+                      np.tile([0.0, 0.0, 1.0], (num_mps, 1)), obs_cam, obs_pt, obs_uv)
+        indptr, indices, shape = s.sparsity_csr()
+        return csr_matrix((np.ones(indices.shape[0], dtype=np.int64), indices.astype(np.int32), indptr.astype(np.int32)),
+                          shape=shape)
+
+    def _update_map(self, gmap, optimized_params, adjustable_kf_ids, local_map_point_ids):
+        """Write the optimised vector back (reference ``:220-240``): R from the rotation vector, t as 3x1,
+        positions as 3x1."""
+        nc = len(adjustable_kf_ids)
+        x = np.asarray(optimized_params, dtype=np.float64)
+        rvecs = x[:3 * nc].reshape(nc, 3)
+        tvecs = x[3 * nc:6 * nc].reshape(nc, 3)
+        pts = x[6 * nc:].reshape(len(local_map_point_ids), 3)
+        for i, kf_id in enumerate(adjustable_kf_ids):
+            kf = gmap.keyframes[kf_id]
+            kf.R = rvec_to_matrix(rvecs[i])
+            kf.t = tvecs[i].reshape(3, 1).copy()
+        for i, mp_id in enumerate(local_map_point_ids):
+            gmap.map_points[mp_id].position = pts[i].reshape(3, 1).copy()
+
+    # -- the entry point ---------------------------------------------------------------------------
+    def run(self, gmap):
+        """Run LBA on the most recent window of keyframes (reference ``run``, ``:122-193``)."""
+        print("    --- Running Local Bundle Adjustment ---")
+        self.last_stats = None
+
+        all_kf_ids = sorted(gmap.keyframes.keys())
+        if len(all_kf_ids) < self.window_size:
+            print("    -> LBA Skipped: Not enough keyframes.")
+            return
+
+        local_kf_ids = all_kf_ids[-(self.window_size + 1): -1]      # the newest keyframe is not optimised
+        fixed_kf_id = local_kf_ids[0]
+        adjustable_kf_ids = local_kf_ids[1:]
+        if not adjustable_kf_ids:
+            print("    -> LBA Skipped: No adjustable keyframes.")
+            return
+
+        local_map_point_ids, observations, keypoints_2d = self._gather_local_data(gmap, local_kf_ids)
+        if not local_map_point_ids:
+            print("    -> LBA Skipped: No points in the local window.")
+            return
+
+        rvecs = np.array([matrix_to_rvec(gmap.keyframes[i].R) for i in adjustable_kf_ids]).reshape(-1, 3)
+        tvecs = np.array([np.asarray(gmap.keyframes[i].t, dtype=np.float64).ravel() for i in adjustable_kf_ids]).reshape(-1, 3)
+        pts = np.array([np.asarray(gmap.map_points[i].position, dtype=np.float64).ravel()
+                        for i in local_map_point_ids]).reshape(-1, 3)
+        fixed_kf = gmap.keyframes[fixed_kf_id]
+        obs_cam, obs_pt, obs_uv = self._index_observations(adjustable_kf_ids, local_map_point_ids, observations,
+                                                           keypoints_2d, fixed_kf_id)
+
+        fx, fy, cx, cy = self._intrinsics()
+        solver = self._get_solver()
+        solver.set_problem(fx, fy, cx, cy, rvecs, tvecs, matrix_to_rvec(fixed_kf.R),
+                           np.asarray(fixed_kf.t, dtype=np.float64).ravel(), pts, obs_cam, obs_pt, obs_uv)
+        stats = solver.solve(**self.solver_options)
+        self.last_stats = stats
+
+        # the reference reports and guards on the RAW sum of squares, not the Huber cost (:165, :176-179)
+        initial_cost, final_cost = stats["initial_raw_cost"], stats["final_raw_cost"]
+        if final_cost >= initial_cost:
+            print(f"    -> LBA Diverged! Cost increased from {initial_cost:.2f} to {final_cost:.2f}. Discarding results.")
+            return
+
+        self._update_map(gmap, solver.get_x(), adjustable_kf_ids, local_map_point_ids)
+
+        improvement = 100.0 * (initial_cost - final_cost) / (initial_cost + 1e-8)
+        print(f"    -> LBA Complete. Initial Cost: {initial_cost:.2f}, Final Cost: {final_cost:.2f}, "
+              f"Improvement: {improvement:.2f}%")
+
+        if self.lba_steps_dir is not None:
+            path = os.path.join(self.lba_steps_dir, f"map_after_lba_kf_{fixed_kf_id}.pcd")
+            if _write_pcd(path, gmap):
+                print(f"    -> Saved intermediate map to {path}")
+
+
+def _write_pcd(path: str, gmap) -> bool:
+    """ASCII .pcd of all map points (what the reference saves through Open3D at ``:187-193``)."""
+    pos = [np.asarray(p.position, dtype=np.float64).reshape(3) for p in gmap.map_points.values()]
+    if not pos:
+        return False
+    os.makedirs(os.path.dirname(path) or ".", exist_ok=True)
+    with open(path, "w") as f:
+        f.write("# .PCD v0.7 - Point Cloud Data file format\nVERSION 0.7\nFIELDS x y z\nSIZE 8 8 8\nTYPE F F F\n"
+                f"COUNT 1 1 1\nWIDTH {len(pos)}\nHEIGHT 1\nVIEWPOINT 0 0 0 1 0 0 0\nPOINTS {len(pos)}\nDATA ascii\n")
+        for p in pos:
+            f.write(f"{p[0]:.17g} {p[1]:.17g} {p[2]:.17g}\n")
+    return True

@@ -1,0 +1,855 @@
+// ba_kernels.cuh - hand-written sm_100a kernels of the Levenberg-Marquardt / Schur / PCG loop.
+//
+// Dataflow ("recompute"): no per-observation Jacobian or E block is ever stored.  Every pass streams
+// the 24-byte observation record (u, v, camera, point) and re-derives the 2x3 point Jacobian from the
+// camera pose and the point; the camera Jacobian follows from it algebraically:
+//
+//      x_cam = R (X + w x X + v) + t        (camera increment = world-frame twist (w, v))
+//      Jp    = d r / d X      = -dpi(x_cam) R                       (2x3)
+//      Jc    = d r / d (w, v) = Jp [ -[X]x | I ]                    (2x6)
+//
+// Two observation orders live in HBM:
+//   * point-major  (pm_*): all observations of a point are adjacent.  Per-point sums (V, g_p, the
+//     Schur mat-vec's E^T x) are formed inside one CTA: phase A = one thread per observation writes
+//     its contribution to shared memory, phase B = one thread per point adds them in a fixed order.
+//   * camera-major (cm_*): only observations of adjustable cameras, cut into tiles of <= CM_TILE
+//     observations of ONE camera.  Per-camera sums (U, g_c, Schur right-hand side, preconditioner
+//     blocks, mat-vec result) are block-reduced per tile (warp shuffles + shared memory, fixed tree)
+//     and the few tile partials of a camera are added in tile order by a finishing kernel.
+// No floating-point atomics anywhere: results are bit-reproducible run to run.
+//
+// All loop-carried scalars (damping, costs, PCG alpha/beta, buffer selector, flags) live in the device
+// struct LMState so that the host only enqueues launches and polls a status word.
+#pragma once
+#include "ba_math.cuh"
+
+namespace ba {
+
+constexpr int PM_THREADS = 256;  // point-major CTA; nominal tile = PM_THREADS observations
+constexpr int CM_THREADS = 256;  // camera-major CTA
+constexpr int CM_TILE = 1024;    // observations per camera-major tile (<= 4 per thread)
+constexpr int NSCAL = 16;        // per-iteration scalar slots
+
+// scalar slots (partials are reduced into LMState::scal by k_reduce_scalars)
+enum {
+    // point-side sums (per-rank partial in multi-GPU mode: slots [0, N_PT_SCAL) are all-reduced)
+    S_COST = 0,    // 0.5 * sum rho
+    S_RAW = 1,     // sum r^2
+    S_GDP = 2,     // g_p . dp
+    S_DDP = 3,     // dp^T D_p dp
+    S_DP2 = 4,     // |dp|^2
+    S_XP2 = 5,     // |X|^2
+    S_BAD = 6,     // count of non-finite residuals
+    // camera-side sums (replicated on every rank, never all-reduced)
+    S_GDC = 7,     // g_c . dc
+    S_DDC = 8,     // dc^T D_c dc
+    S_RDC = 9,     // r_pcg . dc
+    S_DC2 = 10,    // |dc|^2
+    S_XC2 = 11,    // |(rvec,t)|^2
+    S_GPMAX = 12,  // max |g_p|   (max-reduced, not summed)
+};
+constexpr int N_PT_SCAL = 7;
+
+struct LMState {
+    double lambda, nu;
+    double cost[2], raw[2];  // per parameter buffer
+    double gmax;             // max |g| at the current point
+    double rz, rz0, pq, alpha, beta;
+    double model, rho, dcost, step_norm, x_norm;
+    double scal[NSCAL];
+    int cur;                 // which parameter buffer is current (0/1); trial = cur ^ 1
+    int status;              // 0 running, > 0 terminated (ba_b200.h)
+    int iter, accepted, rejected;
+    int last_accepted;       // 1 if the last decide() accepted
+    int pcg_done, pcg_iter, pcg_total;
+    int bad;                 // non-finite seen
+};
+
+struct Params {
+    Intr K;
+    double delta;  // Huber threshold
+    int mode;      // robust mode
+    int n_cams;    // adjustable cameras; slot n_cams holds the fixed camera
+    int n_pts, n_obs, n_obs_adj;
+    int pm_tiles, cm_tiles, pm_cap;  // pm_cap = shared-memory slots per contribution row
+    // parameters, double buffered: [2][(n_cams+1)*6] (rvec,t), [2][(n_cams+1)*12] (R,t), [2][n_pts*4]
+    double* cam_rt;
+    double* cam_R;
+    double* pt_X;
+    // per-point normal-equation data
+    double* pt_V;     // [2][n_pts*6]
+    double* pt_g;     // [2][n_pts*4]
+    double* pt_Vinv;  // [n_pts*6]
+    double* pt_h;     // [n_pts*4]  Vinv g_p
+    double* pt_z;     // [n_pts*4]  point-pass output
+    double* pt_D;     // [n_pts*4]  damping diagonal
+    // per-camera data (local coordinates)
+    double* cam_U;     // [n_cams*21]
+    double* cam_g;     // [n_cams*6]
+    double* cam_D;     // [n_cams*6]
+    double* cam_Minv;  // [n_cams*36]
+    double* cam_acc;   // [n_cams*27] tile-summed accumulators (all-reduced in multi-GPU mode)
+    double* v_b;       // [(n_cams+1)*6] right-hand side; the +1 slot (fixed camera) stays zero
+    double* v_x;
+    double* v_r;
+    double* v_p;
+    double* v_q;
+    // observations
+    const double2* o_uv;   // reference order
+    const int2* o_idx;     // (camera slot, point)
+    const double2* pm_uv;  // point-major
+    const int2* pm_idx;
+    const int* pt_off;     // [n_pts+1]
+    const int* pm_tile_pt; // [pm_tiles+1]
+    const double2* cm_uv;  // camera-major (adjustable cameras only)
+    const int* cm_pt;
+    const int4* cm_tile;      // (camera, first obs, count, 0)
+    const int* cam_tile_off;  // [n_cams+1]
+    // partial sums
+    double* cm_partial;  // [cm_tiles*27]
+    double* pm_partial;  // [pm_tiles*NSCAL]
+    double* cam_partial; // [n_cams*NSCAL]
+    LMState* st;
+};
+
+// ---------------------------------------------------------------------------------------------
+// reductions (fixed trees -> deterministic)
+// ---------------------------------------------------------------------------------------------
+BA_D double warp_sum(double v) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_down_sync(0xffffffffu, v, d);
+    return v;
+}
+BA_D double warp_max(double v) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v = fmax(v, __shfl_down_sync(0xffffffffu, v, d));
+    return v;
+}
+
+// Sum N per-thread values over the CTA; thread k < N returns total k in out[k] (shared, N doubles).
+template <int N, int THREADS>
+BA_D void block_sum(double (&v)[N], double* sm /* [THREADS/32 * N] */, double* out /* [N] */) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+        const double s = warp_sum(v[k]);
+        if (lane == 0) sm[w * N + k] = s;
+    }
+    __syncthreads();
+    if (threadIdx.x < N) {
+        double s = 0.0;
+#pragma unroll
+        for (int i = 0; i < THREADS / 32; ++i) s += sm[i * N + threadIdx.x];
+        out[threadIdx.x] = s;
+    }
+}
+
+BA_D void load_cam(const double* __restrict__ base, int slot, double Rt[12]) {
+    const double2* p = reinterpret_cast<const double2*>(base + (size_t)slot * 12);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        const double2 a = __ldg(p + k);
+        Rt[2 * k] = a.x;
+        Rt[2 * k + 1] = a.y;
+    }
+}
+BA_D void load_vec6(const double* __restrict__ base, int slot, double x[6]) {
+    const double2* p = reinterpret_cast<const double2*>(base + (size_t)slot * 6);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double2 a = __ldg(p + k);
+        x[2 * k] = a.x;
+        x[2 * k + 1] = a.y;
+    }
+}
+BA_D void load_pt(const double* __restrict__ base, int p, double X[3]) {
+    const double2* q = reinterpret_cast<const double2*>(base + (size_t)p * 4);
+    const double2 a = __ldg(q), b = __ldg(q + 1);
+    X[0] = a.x; X[1] = a.y; X[2] = b.x;
+}
+BA_D void load_sym3(const double* __restrict__ base, int p, double S[6]) {
+    const double2* q = reinterpret_cast<const double2*>(base + (size_t)p * 6);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double2 a = __ldg(q + k);
+        S[2 * k] = a.x;
+        S[2 * k + 1] = a.y;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// camera preparation: R(rvec) for buffer `which` (0/1 absolute, 2 = current, 3 = trial)
+// ---------------------------------------------------------------------------------------------
+BA_D int resolve_buf(const LMState* st, int which) { return which < 2 ? which : (which == 2 ? st->cur : st->cur ^ 1); }
+
+__global__ void k_cam_prepare(Params P, int which) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c > P.n_cams) return;
+    const int b = resolve_buf(P.st, which);
+    const double* rt = P.cam_rt + (size_t)b * (P.n_cams + 1) * 6 + (size_t)c * 6;
+    double* out = P.cam_R + (size_t)b * (P.n_cams + 1) * 12 + (size_t)c * 12;
+    double R[9];
+    rodrigues(rt, R);
+#pragma unroll
+    for (int k = 0; k < 9; ++k) out[k] = R[k];
+    out[9] = rt[3]; out[10] = rt[4]; out[11] = rt[5];
+}
+
+// ---------------------------------------------------------------------------------------------
+// API kernels, reference observation order
+// ---------------------------------------------------------------------------------------------
+__global__ void k_residuals(Params P, double2* __restrict__ r_out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.n_obs) return;
+    const int b = P.st->cur;
+    const double2 uv = __ldg(P.o_uv + i);
+    const int2 id = __ldg(P.o_idx + i);
+    double Rt[12], X[3];
+    load_cam(P.cam_R + (size_t)b * (P.n_cams + 1) * 12, id.x, Rt);
+    load_pt(P.pt_X + (size_t)b * P.n_pts * 4, id.y, X);
+    double rx, ry;
+    project_residual(Rt, X, uv.x, uv.y, P.K, rx, ry);
+    r_out[i] = make_double2(rx, ry);
+}
+
+// Jacobian blocks in the reference's (rvec, t, X) parameterisation:
+//   d r / d rvec = Jp (-[X]x) Jr(rvec),   d r / d t = Jp R^T = -dpi,   d r / d X = Jp.
+__global__ void k_jacobian_blocks(Params P, double* __restrict__ jc_out, double* __restrict__ jp_out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.n_obs) return;
+    const int b = P.st->cur;
+    const double2 uv = __ldg(P.o_uv + i);
+    const int2 id = __ldg(P.o_idx + i);
+    double Rt[12], X[3];
+    load_cam(P.cam_R + (size_t)b * (P.n_cams + 1) * 12, id.x, Rt);
+    load_pt(P.pt_X + (size_t)b * P.n_pts * 4, id.y, X);
+    ObsLin o;
+    linearize_obs(Rt, X, uv.x, uv.y, P.K, o);
+    double* jp = jp_out + (size_t)i * 6;
+    double* jc = jc_out + (size_t)i * 12;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { jp[k] = o.jx[k]; jp[3 + k] = o.jy[k]; }
+    if (id.x >= P.n_cams) {
+#pragma unroll
+        for (int k = 0; k < 12; ++k) jc[k] = 0.0;
+        return;
+    }
+    const double* rvec = P.cam_rt + (size_t)b * (P.n_cams + 1) * 6 + (size_t)id.x * 6;
+    double Jr[9], ax[3], ay[3];
+    right_jacobian(rvec, Jr);
+    cross3(X, o.jx, ax);  // row of Jp (-[X]x) = (X x j)^T
+    cross3(X, o.jy, ay);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        jc[k] = ax[0] * Jr[k] + ax[1] * Jr[3 + k] + ax[2] * Jr[6 + k];
+        jc[6 + k] = ay[0] * Jr[k] + ay[1] * Jr[3 + k] + ay[2] * Jr[6 + k];
+        // Jp R^T: row . R[k,:]
+        jc[3 + k] = o.jx[0] * Rt[3 * k] + o.jx[1] * Rt[3 * k + 1] + o.jx[2] * Rt[3 * k + 2];
+        jc[9 + k] = o.jy[0] * Rt[3 * k] + o.jy[1] * Rt[3 * k + 1] + o.jy[2] * Rt[3 * k + 2];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// point-major tile helpers
+// ---------------------------------------------------------------------------------------------
+struct PmTile { int p0, p1, o0, n; };
+BA_D PmTile pm_tile(const Params& P) {
+    PmTile t;
+    t.p0 = __ldg(P.pm_tile_pt + blockIdx.x);
+    t.p1 = __ldg(P.pm_tile_pt + blockIdx.x + 1);
+    t.o0 = __ldg(P.pt_off + t.p0);
+    t.n = __ldg(P.pt_off + t.p1) - t.o0;
+    return t;
+}
+
+// K-LINP: linearise at buffer `which` in point-major order.
+//   per point : V_p = sum Jp^T W Jp (6), g_p = sum Jp^T wg r (3)           -> pt_V[b], pt_g[b]
+//   per tile  : 0.5*sum rho, sum r^2, max|g_p|, #bad                       -> pm_partial
+__global__ void __launch_bounds__(PM_THREADS) k_lin_points(Params P, int which) {
+    extern __shared__ double sm[];
+    __shared__ double red[PM_THREADS / 32 * 3];
+    __shared__ double tot[3];
+    const int b = resolve_buf(P.st, which);
+    const PmTile T = pm_tile(P);
+    const int cap = P.pm_cap;
+    const double* camR = P.cam_R + (size_t)b * (P.n_cams + 1) * 12;
+    const double* ptX = P.pt_X + (size_t)b * P.n_pts * 4;
+    double acc[3] = {0.0, 0.0, 0.0};  // cost, raw, bad
+    for (int i = threadIdx.x; i < T.n; i += PM_THREADS) {
+        const double2 uv = __ldg(P.pm_uv + T.o0 + i);
+        const int2 id = __ldg(P.pm_idx + T.o0 + i);
+        double Rt[12], X[3];
+        load_cam(camR, id.x, Rt);
+        load_pt(ptX, id.y, X);
+        ObsLin o;
+        linearize_obs(Rt, X, uv.x, uv.y, P.K, o);
+        double wHx, wgx, r0x, wHy, wgy, r0y;
+        robust_weights(o.rx, P.delta, P.mode, wHx, wgx, r0x);
+        robust_weights(o.ry, P.delta, P.mode, wHy, wgy, r0y);
+        acc[0] += 0.5 * (r0x + r0y);
+        acc[1] += o.rx * o.rx + o.ry * o.ry;
+        if (!(isfinite(o.rx) && isfinite(o.ry))) acc[2] += 1.0;
+        const double ax = wHx * o.jx[0], bx = wHx * o.jx[1], cx = wHx * o.jx[2];
+        const double ay = wHy * o.jy[0], by = wHy * o.jy[1], cy = wHy * o.jy[2];
+        sm[0 * cap + i] = ax * o.jx[0] + ay * o.jy[0];
+        sm[1 * cap + i] = ax * o.jx[1] + ay * o.jy[1];
+        sm[2 * cap + i] = ax * o.jx[2] + ay * o.jy[2];
+        sm[3 * cap + i] = bx * o.jx[1] + by * o.jy[1];
+        sm[4 * cap + i] = bx * o.jx[2] + by * o.jy[2];
+        sm[5 * cap + i] = cx * o.jx[2] + cy * o.jy[2];
+        const double gx = wgx * o.rx, gy = wgy * o.ry;
+        sm[6 * cap + i] = o.jx[0] * gx + o.jy[0] * gy;
+        sm[7 * cap + i] = o.jx[1] * gx + o.jy[1] * gy;
+        sm[8 * cap + i] = o.jx[2] * gx + o.jy[2] * gy;
+    }
+    __syncthreads();
+    double gmax = 0.0;
+    double* V = P.pt_V + (size_t)b * P.n_pts * 6;
+    double* G = P.pt_g + (size_t)b * P.n_pts * 4;
+    for (int j = threadIdx.x; j < T.p1 - T.p0; j += PM_THREADS) {
+        const int p = T.p0 + j;
+        const int a = __ldg(P.pt_off + p) - T.o0, e = __ldg(P.pt_off + p + 1) - T.o0;
+        double s[9];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) s[k] = 0.0;
+        for (int i = a; i < e; ++i) {
+#pragma unroll
+            for (int k = 0; k < 9; ++k) s[k] += sm[k * cap + i];
+        }
+        double2* v2 = reinterpret_cast<double2*>(V + (size_t)p * 6);
+        v2[0] = make_double2(s[0], s[1]); v2[1] = make_double2(s[2], s[3]); v2[2] = make_double2(s[4], s[5]);
+        double2* g2 = reinterpret_cast<double2*>(G + (size_t)p * 4);
+        g2[0] = make_double2(s[6], s[7]); g2[1] = make_double2(s[8], 0.0);
+        gmax = fmax(gmax, fmax(fabs(s[6]), fmax(fabs(s[7]), fabs(s[8]))));
+    }
+    __syncthreads();
+    block_sum<3, PM_THREADS>(acc, red, tot);
+    __syncthreads();
+    // block max of gmax (reuse red)
+    const double wm = warp_max(gmax);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = wm;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double m = 0.0;
+        for (int i = 0; i < PM_THREADS / 32; ++i) m = fmax(m, red[i]);
+        double* out = P.pm_partial + (size_t)blockIdx.x * NSCAL;
+        out[S_COST] = tot[0]; out[S_RAW] = tot[1]; out[S_BAD] = tot[2]; out[S_GPMAX] = m;
+    }
+}
+
+// K-PTPREP: V_d = V + lambda D_p, D_p = clamp(diag V); Vinv = V_d^-1; h = Vinv g_p.
+__global__ void k_point_prepare(Params P, double dmin, double dmax) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P.n_pts) return;
+    const int b = P.st->cur;
+    const double lam = P.st->lambda;
+    double V[6], g[3];
+    load_sym3(P.pt_V + (size_t)b * P.n_pts * 6, p, V);
+    load_pt(P.pt_g + (size_t)b * P.n_pts * 4, p, g);
+    const double d0 = fmin(fmax(V[0], dmin), dmax), d1 = fmin(fmax(V[3], dmin), dmax), d2 = fmin(fmax(V[5], dmin), dmax);
+    V[0] += lam * d0; V[3] += lam * d1; V[5] += lam * d2;
+    double Vi[6], h[3];
+    if (!sym3_inverse(V, Vi)) {  // not SPD (can only come from non-finite input): fall back to the damped diagonal
+        Vi[0] = 1.0 / (lam * d0 + dmin); Vi[3] = 1.0 / (lam * d1 + dmin); Vi[5] = 1.0 / (lam * d2 + dmin);
+        Vi[1] = Vi[2] = Vi[4] = 0.0;
+    }
+    sym3_mulv(Vi, g, h);
+    double2* vo = reinterpret_cast<double2*>(P.pt_Vinv + (size_t)p * 6);
+    vo[0] = make_double2(Vi[0], Vi[1]); vo[1] = make_double2(Vi[2], Vi[3]); vo[2] = make_double2(Vi[4], Vi[5]);
+    double2* ho = reinterpret_cast<double2*>(P.pt_h + (size_t)p * 4);
+    ho[0] = make_double2(h[0], h[1]); ho[1] = make_double2(h[2], 0.0);
+    double2* d = reinterpret_cast<double2*>(P.pt_D + (size_t)p * 4);
+    d[0] = make_double2(d0, d1); d[1] = make_double2(d2, 0.0);
+}
+
+// K-P1 (MODE 0): z_p = Vinv_p * sum_i Jp_i^T W_i Jc_i vec_c         (first half of the Schur mat-vec)
+// K-BACKSUB (MODE 1): dp = -h_p - z_p(x), X_trial = X + dp, plus the step's scalar products.
+template <int MODE>
+__global__ void __launch_bounds__(PM_THREADS) k_point_pass(Params P, const double* __restrict__ vec) {
+    extern __shared__ double sm[];
+    __shared__ double red[PM_THREADS / 32 * 4];
+    __shared__ double tot[4];
+    if (MODE == 0 && P.st->pcg_done) return;
+    const int b = P.st->cur;
+    const PmTile T = pm_tile(P);
+    const int cap = P.pm_cap;
+    const double* camR = P.cam_R + (size_t)b * (P.n_cams + 1) * 12;
+    const double* ptX = P.pt_X + (size_t)b * P.n_pts * 4;
+    for (int i = threadIdx.x; i < T.n; i += PM_THREADS) {
+        const double2 uv = __ldg(P.pm_uv + T.o0 + i);
+        const int2 id = __ldg(P.pm_idx + T.o0 + i);
+        double Rt[12], X[3], x[6];
+        load_cam(camR, id.x, Rt);
+        load_pt(ptX, id.y, X);
+        load_vec6(vec, id.x, x);
+        ObsLin o;
+        linearize_obs(Rt, X, uv.x, uv.y, P.K, o);
+        double wHx, wgx, r0x, wHy, wgy, r0y;
+        robust_weights(o.rx, P.delta, P.mode, wHx, wgx, r0x);
+        robust_weights(o.ry, P.delta, P.mode, wHy, wgy, r0y);
+        // d = w x X + v
+        const double d0 = fma(x[1], X[2], fma(-x[2], X[1], x[3]));
+        const double d1 = fma(x[2], X[0], fma(-x[0], X[2], x[4]));
+        const double d2 = fma(x[0], X[1], fma(-x[1], X[0], x[5]));
+        const double ax = wHx * (o.jx[0] * d0 + o.jx[1] * d1 + o.jx[2] * d2);
+        const double ay = wHy * (o.jy[0] * d0 + o.jy[1] * d1 + o.jy[2] * d2);
+        sm[0 * cap + i] = o.jx[0] * ax + o.jy[0] * ay;
+        sm[1 * cap + i] = o.jx[1] * ax + o.jy[1] * ay;
+        sm[2 * cap + i] = o.jx[2] * ax + o.jy[2] * ay;
+    }
+    __syncthreads();
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};  // g.dp, dp D dp, |dp|^2, |X|^2
+    for (int j = threadIdx.x; j < T.p1 - T.p0; j += PM_THREADS) {
+        const int p = T.p0 + j;
+        const int a = __ldg(P.pt_off + p) - T.o0, e = __ldg(P.pt_off + p + 1) - T.o0;
+        double s[3] = {0.0, 0.0, 0.0};
+        for (int i = a; i < e; ++i) {
+            s[0] += sm[i]; s[1] += sm[cap + i]; s[2] += sm[2 * cap + i];
+        }
+        double Vi[6], z[3];
+        load_sym3(P.pt_Vinv, p, Vi);
+        sym3_mulv(Vi, s, z);
+        if (MODE == 0) {
+            double2* zo = reinterpret_cast<double2*>(P.pt_z + (size_t)p * 4);
+            zo[0] = make_double2(z[0], z[1]); zo[1] = make_double2(z[2], 0.0);
+        } else {
+            double h[3], X[3], g[3], D[3];
+            load_pt(P.pt_h, p, h);
+            load_pt(ptX, p, X);
+            load_pt(P.pt_g + (size_t)b * P.n_pts * 4, p, g);
+            load_pt(P.pt_D, p, D);
+            const double dp0 = -h[0] - z[0], dp1 = -h[1] - z[1], dp2 = -h[2] - z[2];
+            double2* xo = reinterpret_cast<double2*>(P.pt_X + (size_t)(b ^ 1) * P.n_pts * 4 + (size_t)p * 4);
+            xo[0] = make_double2(X[0] + dp0, X[1] + dp1); xo[1] = make_double2(X[2] + dp2, 0.0);
+            acc[0] += g[0] * dp0 + g[1] * dp1 + g[2] * dp2;
+            acc[1] += D[0] * dp0 * dp0 + D[1] * dp1 * dp1 + D[2] * dp2 * dp2;
+            acc[2] += dp0 * dp0 + dp1 * dp1 + dp2 * dp2;
+            acc[3] += X[0] * X[0] + X[1] * X[1] + X[2] * X[2];
+        }
+    }
+    if (MODE == 1) {
+        __syncthreads();
+        block_sum<4, PM_THREADS>(acc, red, tot);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double* out = P.pm_partial + (size_t)blockIdx.x * NSCAL;
+            out[S_GDP] = tot[0]; out[S_DDP] = tot[1]; out[S_DP2] = tot[2]; out[S_XP2] = tot[3];
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// camera-major tile kernels.  KIND 0: U (21) + g_c (6).  KIND 1: Schur right-hand side (6) +
+// preconditioner correction (21).  KIND 2: second half of the Schur mat-vec (6).
+// Accumulator layout: [0..20] symmetric 6x6 upper triangle (sym6), [21..26] 6-vector.  KIND 2 uses [0..5].
+// ---------------------------------------------------------------------------------------------
+template <int KIND>
+struct CmN { static constexpr int value = (KIND == 2) ? 6 : 27; };
+
+template <int KIND>
+__global__ void __launch_bounds__(CM_THREADS) k_camera_pass(Params P, const double* __restrict__ vec, int with_schur_diag) {
+    constexpr int N = CmN<KIND>::value;
+    __shared__ double red[CM_THREADS / 32 * N];
+    __shared__ double tot[N];
+    if (KIND == 2 && P.st->pcg_done) return;
+    const int b = P.st->cur;
+    const int4 tile = __ldg(P.cm_tile + blockIdx.x);
+    const int cam = tile.x, o0 = tile.y, n = tile.z;
+    const double* ptX = P.pt_X + (size_t)b * P.n_pts * 4;
+    double Rt[12], x[6];
+    load_cam(P.cam_R + (size_t)b * (P.n_cams + 1) * 12, cam, Rt);
+    if (KIND == 2) load_vec6(vec, cam, x);
+    double acc[N];
+#pragma unroll
+    for (int k = 0; k < N; ++k) acc[k] = 0.0;
+    for (int i = threadIdx.x; i < n; i += CM_THREADS) {
+        const double2 uv = __ldg(P.cm_uv + o0 + i);
+        const int p = __ldg(P.cm_pt + o0 + i);
+        double X[3];
+        load_pt(ptX, p, X);
+        ObsLin o;
+        linearize_obs(Rt, X, uv.x, uv.y, P.K, o);
+        double wHx, wgx, r0x, wHy, wgy, r0y;
+        robust_weights(o.rx, P.delta, P.mode, wHx, wgx, r0x);
+        robust_weights(o.ry, P.delta, P.mode, wHy, wgy, r0y);
+        if (KIND == 0) {
+            // rows of Jc = (X x j, j)
+            double jcx[6], jcy[6];
+            cross3(X, o.jx, jcx); cross3(X, o.jy, jcy);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { jcx[3 + k] = o.jx[k]; jcy[3 + k] = o.jy[k]; }
+            const double gx = wgx * o.rx, gy = wgy * o.ry;
+            int q = 0;
+#pragma unroll
+            for (int r = 0; r < 6; ++r) {
+                const double sx = wHx * jcx[r], sy = wHy * jcy[r];
+#pragma unroll
+                for (int c = r; c < 6; ++c) { acc[q] += sx * jcx[c] + sy * jcy[c]; ++q; }
+                acc[21 + r] += jcx[r] * gx + jcy[r] * gy;
+            }
+        } else if (KIND == 1) {
+            // W = Jp^T diag(wH) Jp (sym 3x3)
+            double W[6];
+            {
+                const double ax = wHx * o.jx[0], bx = wHx * o.jx[1], cx = wHx * o.jx[2];
+                const double ay = wHy * o.jy[0], by = wHy * o.jy[1], cy = wHy * o.jy[2];
+                W[0] = ax * o.jx[0] + ay * o.jy[0]; W[1] = ax * o.jx[1] + ay * o.jy[1]; W[2] = ax * o.jx[2] + ay * o.jy[2];
+                W[3] = bx * o.jx[1] + by * o.jy[1]; W[4] = bx * o.jx[2] + by * o.jy[2]; W[5] = cx * o.jx[2] + cy * o.jy[2];
+            }
+            double h[3], m[3], xm[3];
+            load_pt(P.pt_h, p, h);
+            sym3_mulv(W, h, m);  // E h = G^T (W h)
+            cross3(X, m, xm);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { acc[21 + k] += xm[k]; acc[24 + k] += m[k]; }
+            if (with_schur_diag) {
+                // T = W Vinv W (sym), correction = G^T T G with G = [-[X]x | I]
+                double Vi[6];
+                load_sym3(P.pt_Vinv, p, Vi);
+                const double Wf[9] = {W[0], W[1], W[2], W[1], W[3], W[4], W[2], W[4], W[5]};
+                double A[9];  // A = Vinv W
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const double col[3] = {Wf[c], Wf[3 + c], Wf[6 + c]};
+                    double r3[3];
+                    sym3_mulv(Vi, col, r3);
+                    A[c] = r3[0]; A[3 + c] = r3[1]; A[6 + c] = r3[2];
+                }
+                double Tm[9];  // T = W A (symmetric)
+#pragma unroll
+                for (int r = 0; r < 3; ++r)
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) Tm[3 * r + c] = Wf[3 * r] * A[c] + Wf[3 * r + 1] * A[3 + c] + Wf[3 * r + 2] * A[6 + c];
+                // C = [X]x T : column c of C = X x T[:,c]
+                double C[9];
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const double tc[3] = {Tm[c], Tm[3 + c], Tm[6 + c]};
+                    double cc[3];
+                    cross3(X, tc, cc);
+                    C[c] = cc[0]; C[3 + c] = cc[1]; C[6 + c] = cc[2];
+                }
+                // top-left = C [X]x^T : row r of result = -(C[r,:] x X)... use (C [X]x^T)[r][c] = (X x C[r,:])[c]
+                // since [X]x^T v = -X x v and (C B^T)[r][c] = sum_k C[r][k] B[c][k] = ([X]x C[r,:]^T)[c] = (X x C[r,:])[c]
+#pragma unroll
+                for (int r = 0; r < 3; ++r) {
+                    const double cr[3] = {C[3 * r], C[3 * r + 1], C[3 * r + 2]};
+                    double tl[3];
+                    cross3(X, cr, tl);
+#pragma unroll
+                    for (int c = r; c < 3; ++c) acc[sym6(r, c)] += tl[c];
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) acc[sym6(r, 3 + c)] += C[3 * r + c];  // top-right = [X]x T
+                }
+#pragma unroll
+                for (int r = 0; r < 3; ++r)
+#pragma unroll
+                    for (int c = r; c < 3; ++c) acc[sym6(3 + r, 3 + c)] += Tm[3 * r + c];
+            }
+        } else {
+            double z[3];
+            load_pt(P.pt_z, p, z);
+            const double d0 = fma(x[1], X[2], fma(-x[2], X[1], x[3]));
+            const double d1 = fma(x[2], X[0], fma(-x[0], X[2], x[4]));
+            const double d2 = fma(x[0], X[1], fma(-x[1], X[0], x[5]));
+            const double bx = wHx * (o.jx[0] * (d0 - z[0]) + o.jx[1] * (d1 - z[1]) + o.jx[2] * (d2 - z[2]));
+            const double by = wHy * (o.jy[0] * (d0 - z[0]) + o.jy[1] * (d1 - z[1]) + o.jy[2] * (d2 - z[2]));
+            double m[3], xm[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) m[k] = o.jx[k] * bx + o.jy[k] * by;
+            cross3(X, m, xm);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { acc[k] += xm[k]; acc[3 + k] += m[k]; }
+        }
+    }
+    block_sum<N, CM_THREADS>(acc, red, tot);
+    __syncthreads();
+    if (threadIdx.x < N) P.cm_partial[(size_t)blockIdx.x * 27 + threadIdx.x] = tot[threadIdx.x];
+}
+
+// Sum the tile partials of each camera in tile order: cam_acc[c*n_val + k] (k < n_val).
+__global__ void k_camera_sum(Params P, int n_val, int pcg_gated) {
+    if (pcg_gated && P.st->pcg_done) return;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P.n_cams * n_val) return;
+    const int c = idx / n_val, k = idx - c * n_val;
+    const int t0 = __ldg(P.cam_tile_off + c), t1 = __ldg(P.cam_tile_off + c + 1);
+    double s = 0.0;
+    for (int t = t0; t < t1; ++t) s += P.cm_partial[(size_t)t * 27 + k];
+    P.cam_acc[(size_t)c * n_val + k] = s;
+}
+
+// After K-LINC (+ all-reduce): store U, g_c, D_c = clamp(diag U).
+__global__ void k_camera_finish_lin(Params P, double dmin, double dmax) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= P.n_cams) return;
+    const double* a = P.cam_acc + (size_t)c * 27;
+    for (int k = 0; k < 21; ++k) P.cam_U[(size_t)c * 21 + k] = a[k];
+    for (int k = 0; k < 6; ++k) {
+        P.cam_g[(size_t)c * 6 + k] = a[21 + k];
+        P.cam_D[(size_t)c * 6 + k] = fmin(fmax(a[sym6(k, k)], dmin), dmax);
+    }
+}
+
+// After K-SCHURC (+ all-reduce): M_c = U_c + lambda D_c - corr_c, Minv_c; b_c = -g_c + (E Vinv g_p)_c.
+__global__ void k_camera_finish_schur(Params P, int with_schur_diag) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= P.n_cams) return;
+    const double lam = P.st->lambda;
+    const double* a = P.cam_acc + (size_t)c * 27;
+    const double* U = P.cam_U + (size_t)c * 21;
+    double M[36];
+    for (int i = 0; i < 6; ++i)
+        for (int j = i; j < 6; ++j) {
+            double v = U[sym6(i, j)] - (with_schur_diag ? a[sym6(i, j)] : 0.0);
+            if (i == j) v += lam * P.cam_D[(size_t)c * 6 + i];
+            M[6 * i + j] = v; M[6 * j + i] = v;
+        }
+    if (!spd6_inverse(M)) {  // numerically indefinite: fall back to the damped block of J^T J, then to its diagonal
+        for (int i = 0; i < 6; ++i)
+            for (int j = i; j < 6; ++j) {
+                double v = U[sym6(i, j)];
+                if (i == j) v += lam * P.cam_D[(size_t)c * 6 + i];
+                M[6 * i + j] = v; M[6 * j + i] = v;
+            }
+        if (!spd6_inverse(M)) {
+            for (int i = 0; i < 36; ++i) M[i] = 0.0;
+            for (int i = 0; i < 6; ++i) M[7 * i] = 1.0 / ((1.0 + lam) * P.cam_D[(size_t)c * 6 + i]);
+        }
+    }
+    for (int k = 0; k < 36; ++k) P.cam_Minv[(size_t)c * 36 + k] = M[k];
+    for (int k = 0; k < 6; ++k) P.v_b[(size_t)c * 6 + k] = a[21 + k] - P.cam_g[(size_t)c * 6 + k];
+}
+
+// ---------------------------------------------------------------------------------------------
+// single-CTA vector kernels of the PCG (camera-sized vectors: n_cams*6 doubles)
+// ---------------------------------------------------------------------------------------------
+constexpr int VEC_THREADS = 1024;
+
+BA_D double cta_sum(double v, double* sm) {  // all threads get the total; sm >= 33 doubles
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    v = warp_sum(v);
+    __syncthreads();
+    if (lane == 0) sm[w] = v;
+    __syncthreads();
+    if (w == 0) {
+        double s = (lane < (int)(blockDim.x >> 5)) ? sm[lane] : 0.0;
+        s = warp_sum(s);
+        if (lane == 0) sm[32] = s;
+    }
+    __syncthreads();
+    return sm[32];
+}
+
+BA_D void minv_apply(const double* __restrict__ Minv, const double* __restrict__ r, double* z) {
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        double s = 0.0;
+#pragma unroll
+        for (int j = 0; j < 6; ++j) s += Minv[6 * i + j] * r[j];
+        z[i] = s;
+    }
+}
+
+// x = 0, r = b, p = z = Minv r, rz = r.z
+__global__ void __launch_bounds__(VEC_THREADS) k_pcg_init(Params P) {
+    __shared__ double sm[33];
+    double part = 0.0;
+    for (int c = threadIdx.x; c < P.n_cams; c += VEC_THREADS) {
+        double r[6], z[6];
+        for (int k = 0; k < 6; ++k) r[k] = P.v_b[(size_t)c * 6 + k];
+        minv_apply(P.cam_Minv + (size_t)c * 36, r, z);
+        for (int k = 0; k < 6; ++k) {
+            P.v_x[(size_t)c * 6 + k] = 0.0;
+            P.v_r[(size_t)c * 6 + k] = r[k];
+            P.v_p[(size_t)c * 6 + k] = z[k];
+            part += r[k] * z[k];
+        }
+    }
+    const double rz = cta_sum(part, sm);
+    if (threadIdx.x == 0) {
+        LMState* st = P.st;
+        st->rz = rz; st->rz0 = rz; st->pcg_iter = 0;
+        st->pcg_done = !(rz > 0.0);  // zero (or non-finite) right-hand side: nothing to solve
+    }
+}
+
+// q = cam_acc (summed mat-vec partials, all-reduced) + lambda D p; then one PCG update.
+__global__ void __launch_bounds__(VEC_THREADS) k_pcg_update(Params P, double tol, int max_iters) {
+    __shared__ double sm[33];
+    LMState* st = P.st;
+    if (st->pcg_done) return;
+    const double lam = st->lambda;
+    double part = 0.0;
+    for (int c = threadIdx.x; c < P.n_cams; c += VEC_THREADS) {
+        for (int k = 0; k < 6; ++k) {
+            const double p = P.v_p[(size_t)c * 6 + k];
+            const double q = P.cam_acc[(size_t)c * 6 + k] + lam * P.cam_D[(size_t)c * 6 + k] * p;
+            P.v_q[(size_t)c * 6 + k] = q;
+            part += p * q;
+        }
+    }
+    const double pq = cta_sum(part, sm);
+    const double rz = st->rz;
+    const double alpha = (pq > 0.0) ? rz / pq : 0.0;
+    part = 0.0;
+    for (int c = threadIdx.x; c < P.n_cams; c += VEC_THREADS) {
+        double r[6], z[6];
+        for (int k = 0; k < 6; ++k) {
+            const size_t i = (size_t)c * 6 + k;
+            P.v_x[i] += alpha * P.v_p[i];
+            r[k] = P.v_r[i] - alpha * P.v_q[i];
+            P.v_r[i] = r[k];
+        }
+        minv_apply(P.cam_Minv + (size_t)c * 36, r, z);
+        for (int k = 0; k < 6; ++k) {
+            P.v_q[(size_t)c * 6 + k] = z[k];  // q is free again: keep z there
+            part += r[k] * z[k];
+        }
+    }
+    const double rz_new = cta_sum(part, sm);
+    const double beta = (rz > 0.0) ? rz_new / rz : 0.0;
+    for (int i = threadIdx.x; i < P.n_cams * 6; i += VEC_THREADS) P.v_p[i] = P.v_q[i] + beta * P.v_p[i];
+    if (threadIdx.x == 0) {
+        st->pq = pq; st->alpha = alpha; st->beta = beta; st->rz = rz_new;
+        const int it = st->pcg_iter + 1;
+        st->pcg_iter = it; st->pcg_total += 1;
+        if (!(pq > 0.0) || !(rz_new > tol * tol * st->rz0) || it >= max_iters) st->pcg_done = 1;
+    }
+}
+
+// Trial camera poses from the PCG solution x: R <- R Exp(w), t <- t + R v; rvec = Log(R).
+__global__ void k_camera_update(Params P) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c > P.n_cams) return;
+    const int b = P.st->cur;
+    const size_t nc1 = (size_t)P.n_cams + 1;
+    const double* rt = P.cam_rt + (size_t)b * nc1 * 6 + (size_t)c * 6;
+    double* rt_new = P.cam_rt + (size_t)(b ^ 1) * nc1 * 6 + (size_t)c * 6;
+    double* R_new = P.cam_R + (size_t)(b ^ 1) * nc1 * 12 + (size_t)c * 12;
+    const double* Rt = P.cam_R + (size_t)b * nc1 * 12 + (size_t)c * 12;
+    if (c == P.n_cams) {  // fixed camera: copy
+        for (int k = 0; k < 6; ++k) rt_new[k] = rt[k];
+        for (int k = 0; k < 12; ++k) R_new[k] = Rt[k];
+        return;
+    }
+    double x[6], E[9], Rn[9], rv[3];
+    for (int k = 0; k < 6; ++k) x[k] = P.v_x[(size_t)c * 6 + k];
+    rodrigues(x, E);
+    mat3_mul(Rt, E, Rn);
+    log_so3(Rn, rv);
+    double tn[3];
+    for (int k = 0; k < 3; ++k) tn[k] = Rt[9 + k] + Rt[3 * k] * x[3] + Rt[3 * k + 1] * x[4] + Rt[3 * k + 2] * x[5];
+    // keep R consistent with the stored rvec (what ba_get_params returns)
+    rodrigues(rv, Rn);
+    for (int k = 0; k < 3; ++k) { rt_new[k] = rv[k]; rt_new[3 + k] = tn[k]; }
+    for (int k = 0; k < 9; ++k) R_new[k] = Rn[k];
+    for (int k = 0; k < 3; ++k) R_new[9 + k] = tn[k];
+    double* out = P.cam_partial + (size_t)c * NSCAL;
+    double gd = 0, dd = 0, rd = 0, d2 = 0, x2 = 0;
+    for (int k = 0; k < 6; ++k) {
+        gd += P.cam_g[(size_t)c * 6 + k] * x[k];
+        dd += P.cam_D[(size_t)c * 6 + k] * x[k] * x[k];
+        rd += P.v_r[(size_t)c * 6 + k] * x[k];
+        d2 += x[k] * x[k];
+        x2 += rt[k] * rt[k];
+    }
+    out[S_GDC] = gd; out[S_DDC] = dd; out[S_RDC] = rd; out[S_DC2] = d2; out[S_XC2] = x2;
+}
+
+// Reduce per-tile / per-camera scalar partials into st->scal (fixed order).  mask selects the slots.
+__global__ void __launch_bounds__(VEC_THREADS) k_reduce_scalars(Params P, unsigned pm_mask, unsigned cam_mask) {
+    __shared__ double sm[33];
+    for (int s = 0; s < NSCAL; ++s) {
+        const bool pm = (pm_mask >> s) & 1u, cm = (cam_mask >> s) & 1u;
+        if (!pm && !cm) continue;
+        double v = 0.0;
+        if (s == S_GPMAX) {
+            for (int t = threadIdx.x; t < P.pm_tiles; t += VEC_THREADS) v = fmax(v, P.pm_partial[(size_t)t * NSCAL + s]);
+            v = warp_max(v);
+            __syncthreads();
+            if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                double m = 0.0;
+                for (int i = 0; i < VEC_THREADS / 32; ++i) m = fmax(m, sm[i]);
+                P.st->scal[s] = m;
+            }
+            __syncthreads();
+            continue;
+        }
+        if (pm) for (int t = threadIdx.x; t < P.pm_tiles; t += VEC_THREADS) v += P.pm_partial[(size_t)t * NSCAL + s];
+        if (cm) for (int c = threadIdx.x; c < P.n_cams; c += VEC_THREADS) v += P.cam_partial[(size_t)c * NSCAL + s];
+        const double tot = cta_sum(v, sm);
+        if (threadIdx.x == 0) P.st->scal[s] = tot;
+    }
+}
+
+// gmax = max(|g_c|, |g_p|) at the current point; gtol test.
+__global__ void __launch_bounds__(VEC_THREADS) k_gradient_check(Params P, double gtol) {
+    __shared__ double sm[32];
+    double v = 0.0;
+    for (int i = threadIdx.x; i < P.n_cams * 6; i += VEC_THREADS) v = fmax(v, fabs(P.cam_g[i]));
+    v = warp_max(v);
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double m = P.st->scal[S_GPMAX];
+        for (int i = 0; i < VEC_THREADS / 32; ++i) m = fmax(m, sm[i]);
+        P.st->gmax = m;
+        if (P.st->status == 0 && m < gtol) P.st->status = 1;
+    }
+}
+
+// Record the cost of buffer `which` from st->scal (after k_lin_points + k_reduce_scalars).
+__global__ void k_store_cost(Params P, int which) {
+    LMState* st = P.st;
+    const int b = resolve_buf(st, which);
+    st->cost[b] = st->scal[S_COST];
+    st->raw[b] = st->scal[S_RAW];
+    if (st->scal[S_BAD] > 0.0 || !isfinite(st->scal[S_COST])) st->bad = 1;
+}
+
+// Accept / reject the trial point, update the damping (Nielsen), test ftol / xtol.
+__global__ void k_lm_decide(Params P, double ftol, double xtol, double lam_min, double lam_max, int max_iters) {
+    LMState* st = P.st;
+    if (st->status != 0) return;  // already terminated (gtol at the current point)
+    const double* s = st->scal;
+    const int cur = st->cur, tri = cur ^ 1;
+    const double cost_new = s[S_COST], raw_new = s[S_RAW];
+    const bool finite_new = isfinite(cost_new) && !(s[S_BAD] > 0.0);
+    const double gd = s[S_GDP] + s[S_GDC];
+    const double dDd = s[S_DDP] + s[S_DDC];
+    const double model = -0.5 * gd + 0.5 * s[S_RDC] + 0.5 * st->lambda * dDd;
+    const double cost = st->cost[cur];
+    const double dcost = cost - cost_new;
+    const double rho = (model > 0.0 && finite_new) ? dcost / model : -1.0;
+    const double step = sqrt(s[S_DP2] + s[S_DC2]);
+    const double xn = sqrt(s[S_XP2] + s[S_XC2]);
+    st->model = model; st->rho = rho; st->dcost = dcost; st->step_norm = step; st->x_norm = xn;
+    st->iter += 1;
+    const bool accept = finite_new && rho > 0.0 && dcost >= 0.0;
+    if (accept) {
+        st->cost[tri] = cost_new; st->raw[tri] = raw_new;
+        st->cur = tri;
+        st->accepted += 1; st->last_accepted = 1;
+        const double t = 2.0 * rho - 1.0;
+        st->lambda = fmax(st->lambda * fmax(1.0 / 3.0, 1.0 - t * t * t), lam_min);
+        st->nu = 2.0;
+        const bool f_ok = dcost <= ftol * cost;
+        const bool x_ok = step < xtol * (xtol + xn);
+        if (st->status == 0) {
+            if (f_ok && x_ok) st->status = 4;
+            else if (f_ok) st->status = 2;
+            else if (x_ok) st->status = 3;
+        }
+    } else {
+        st->rejected += 1; st->last_accepted = 0;
+        st->lambda *= st->nu;
+        st->nu *= 2.0;
+        if (st->status == 0 && st->lambda > lam_max) st->status = 5;
+    }
+    if (st->status == 0 && st->iter >= max_iters) st->status = 6;  // iteration limit (reported as 0)
+}
+
+}  // namespace ba

@@ -1,0 +1,945 @@
+// ba_solver.cu - host side of libba_b200.so: device buffers, problem upload + device-side
+// permutation build, the Levenberg-Marquardt launch sequence, NCCL plumbing and the C ABI
+// declared in include/ba_b200.h.
+//
+// The host never touches problem data during a solve: it enqueues kernels and reads back one small
+// status struct per LM iteration (and one int every few PCG iterations).  There is no CPU fallback:
+// every entry point fails with BA_ERR_CUDA when no usable device is present.
+#include "../../include/ba_b200.h"
+#include "ba_kernels.cuh"
+
+#include <cub/cub.cuh>
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace ba {
+
+// ---------------------------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------------------------
+static thread_local std::string g_last_error;
+
+struct BaError : std::runtime_error {
+    int code;
+    BaError(int c, const std::string& m) : std::runtime_error(m), code(c) {}
+};
+
+[[noreturn]] static void fail(int code, const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    throw BaError(code, buf);
+}
+
+#define CK(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess) fail(BA_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// NCCL, resolved at run time so that single-GPU use needs no NCCL at all
+// ---------------------------------------------------------------------------------------------
+struct NcclApi {
+    void* lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+
+static NcclApi& nccl_api() {
+    static NcclApi api;
+    if (api.lib) return api;
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char* n : names) {
+        api.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+        if (api.lib) break;
+    }
+    if (!api.lib) fail(BA_ERR_NCCL, "cannot load libnccl.so.2: %s", dlerror());
+    auto sym = [&](const char* s) {
+        void* p = dlsym(api.lib, s);
+        if (!p) fail(BA_ERR_NCCL, "libnccl lacks %s", s);
+        return p;
+    };
+    api.GetUniqueId = reinterpret_cast<decltype(api.GetUniqueId)>(sym("ncclGetUniqueId"));
+    api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(sym("ncclCommInitRank"));
+    api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(sym("ncclCommDestroy"));
+    api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(sym("ncclAllReduce"));
+    api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
+    return api;
+}
+
+#define NK(call)                                                                                   \
+    do {                                                                                           \
+        ncclResult_t r_ = (call);                                                                  \
+        if (r_ != ncclSuccess) fail(BA_ERR_NCCL, "%s failed: %s", #call, nccl_api().GetErrorString(r_)); \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// device buffer
+// ---------------------------------------------------------------------------------------------
+template <class T>
+struct DBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    DBuf() = default;
+    DBuf(const DBuf&) = delete;
+    DBuf& operator=(const DBuf&) = delete;
+    ~DBuf() { release(); }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = 0;
+    }
+    void alloc(size_t count) {
+        if (count <= n && p) return;
+        release();
+        if (count) CK(cudaMalloc(&p, count * sizeof(T)));
+        n = count;
+    }
+    void zero(cudaStream_t s) {
+        if (p) CK(cudaMemsetAsync(p, 0, n * sizeof(T), s));
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// kernel kinds (accounting)
+// ---------------------------------------------------------------------------------------------
+enum Kind {
+    KN_SETUP = 0, KN_CAM_PREP, KN_RESID, KN_JAC, KN_LIN_PTS, KN_PT_PREP, KN_PT_PASS, KN_BACKSUB, KN_LIN_CAM,
+    KN_SCHUR_CAM, KN_MATVEC_CAM, KN_CAM_SUM, KN_CAM_FIN, KN_PCG_INIT, KN_PCG_UPDATE, KN_CAM_UPDATE, KN_REDUCE,
+    KN_GRAD, KN_DECIDE, KN_COUNT
+};
+static const char* kKindNames[KN_COUNT] = {
+    "setup", "cam_prepare", "residuals", "jacobian_blocks", "lin_points", "point_prepare", "schur_matvec_points",
+    "backsub_points", "lin_cameras", "schur_rhs_cameras", "schur_matvec_cameras", "camera_sum", "camera_finish",
+    "pcg_init", "pcg_update", "camera_update", "reduce_scalars", "gradient_check", "lm_decide"};
+
+// ---------------------------------------------------------------------------------------------
+// setup kernels (device-side construction of the two observation orders)
+// ---------------------------------------------------------------------------------------------
+__global__ void k_setup_keys(int n_obs, int n_cams, int n_pts, const int* __restrict__ obs_cam,
+                             const int* __restrict__ obs_pt, int2* __restrict__ o_idx, unsigned* __restrict__ key_pt,
+                             unsigned long long* __restrict__ key_cam, int* __restrict__ iota, int* __restrict__ err) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_obs) return;
+    const int c = obs_cam[i], p = obs_pt[i];
+    if (c < -1 || c >= n_cams || p < 0 || p >= n_pts) {
+        atomicOr(err, 1);
+        o_idx[i] = make_int2(n_cams, 0);
+        key_pt[i] = 0; key_cam[i] = ((unsigned long long)n_cams << 32); iota[i] = i;
+        return;
+    }
+    const int slot = c < 0 ? n_cams : c;
+    o_idx[i] = make_int2(slot, p);
+    key_pt[i] = (unsigned)p;
+    key_cam[i] = ((unsigned long long)slot << 32) | (unsigned)p;
+    iota[i] = i;
+}
+
+__global__ void k_gather_pm(int n, const int* __restrict__ perm, const double2* __restrict__ o_uv,
+                            const int2* __restrict__ o_idx, double2* __restrict__ pm_uv, int2* __restrict__ pm_idx) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int j = perm[i];
+    pm_uv[i] = o_uv[j];
+    pm_idx[i] = o_idx[j];
+}
+
+__global__ void k_gather_cm(int n, const int* __restrict__ perm, const double2* __restrict__ o_uv,
+                            const int2* __restrict__ o_idx, double2* __restrict__ cm_uv, int* __restrict__ cm_pt) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int j = perm[i];
+    cm_uv[i] = o_uv[j];
+    cm_pt[i] = o_idx[j].y;
+}
+
+// out[q] = first index i in sorted keys[0..n) with keys[i] >= q * scale_shifted  (lower bound)
+__global__ void k_lower_bound_u32(int n, const unsigned* __restrict__ keys, int nq, int* __restrict__ out) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nq) return;
+    int lo = 0, hi = n;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (keys[mid] < (unsigned)q) lo = mid + 1; else hi = mid;
+    }
+    out[q] = lo;
+}
+__global__ void k_lower_bound_cam(int n, const unsigned long long* __restrict__ keys, int nq, int* __restrict__ out) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nq) return;
+    const unsigned long long target = (unsigned long long)q << 32;
+    int lo = 0, hi = n;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (keys[mid] < target) lo = mid + 1; else hi = mid;
+    }
+    out[q] = lo;
+}
+// pm_tile_pt[t] = first point whose first observation index is >= t * PM_THREADS (clamped to n_pts)
+__global__ void k_pm_tiles(int n_pts, const int* __restrict__ pt_off, int n_tiles, int* __restrict__ tile_pt) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t > n_tiles) return;
+    if (t == n_tiles) { tile_pt[t] = n_pts; return; }
+    const int target = t * PM_THREADS;
+    int lo = 0, hi = n_pts;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (pt_off[mid] < target) lo = mid + 1; else hi = mid;
+    }
+    tile_pt[t] = lo;
+}
+__global__ void k_max_track(int n_pts, const int* __restrict__ pt_off, int* __restrict__ out) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pts) return;
+    atomicMax(out, pt_off[p + 1] - pt_off[p]);
+}
+__global__ void k_pack_points(int n, const double* __restrict__ in3, double* __restrict__ out4) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    double2* o = reinterpret_cast<double2*>(out4 + (size_t)p * 4);
+    o[0] = make_double2(in3[3 * (size_t)p], in3[3 * (size_t)p + 1]);
+    o[1] = make_double2(in3[3 * (size_t)p + 2], 0.0);
+}
+__global__ void k_unpack_points(int n, const double* __restrict__ in4, double* __restrict__ out3) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    out3[3 * (size_t)p] = in4[4 * (size_t)p];
+    out3[3 * (size_t)p + 1] = in4[4 * (size_t)p + 1];
+    out3[3 * (size_t)p + 2] = in4[4 * (size_t)p + 2];
+}
+__global__ void k_pack_cams(int n_cams, const double* __restrict__ rvec, const double* __restrict__ tvec,
+                            double fr0, double fr1, double fr2, double ft0, double ft1, double ft2, double* __restrict__ rt) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c > n_cams) return;
+    double* o = rt + (size_t)c * 6;
+    if (c == n_cams) { o[0] = fr0; o[1] = fr1; o[2] = fr2; o[3] = ft0; o[4] = ft1; o[5] = ft2; return; }
+    for (int k = 0; k < 3; ++k) { o[k] = rvec[3 * (size_t)c + k]; o[3 + k] = tvec[3 * (size_t)c + k]; }
+}
+__global__ void k_unpack_cams(int n_cams, const double* __restrict__ rt, double* __restrict__ rvec, double* __restrict__ tvec) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n_cams) return;
+    for (int k = 0; k < 3; ++k) { rvec[3 * (size_t)c + k] = rt[6 * (size_t)c + k]; tvec[3 * (size_t)c + k] = rt[6 * (size_t)c + 3 + k]; }
+}
+// CSR pattern of the reference's _prepare_sparsity_matrix (src/bundle_adjuster.py:74-120)
+__global__ void k_sparsity_counts(int n_obs, int n_cams, const int2* __restrict__ o_idx, long long* __restrict__ cnt) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_obs) return;
+    cnt[i] = (o_idx[i].x < n_cams) ? 18 : 6;
+}
+__global__ void k_sparsity_fill(int n_obs, int n_cams, const int2* __restrict__ o_idx, const long long* __restrict__ start,
+                                long long* __restrict__ indptr, long long* __restrict__ indices) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_obs) return;
+    const int2 id = o_idx[i];
+    const long long s = start[i];
+    const bool adj = id.x < n_cams;
+    const int per = adj ? 9 : 3;
+    indptr[2 * (size_t)i] = s;
+    indptr[2 * (size_t)i + 1] = s + per;
+    if (i == n_obs - 1) indptr[2 * (size_t)n_obs] = s + 2 * per;
+    if (!indices) return;
+    for (int row = 0; row < 2; ++row) {
+        long long* o = indices + s + row * per;
+        int q = 0;
+        if (adj) {
+            for (int k = 0; k < 3; ++k) o[q++] = 3LL * id.x + k;
+            for (int k = 0; k < 3; ++k) o[q++] = 3LL * n_cams + 3LL * id.x + k;
+        }
+        for (int k = 0; k < 3; ++k) o[q++] = 6LL * n_cams + 3LL * id.y + k;
+    }
+}
+__global__ void k_init_state(LMState* st, double lambda) {
+    LMState z;
+    memset(&z, 0, sizeof z);
+    z.lambda = lambda;
+    z.nu = 2.0;
+    z.cur = st->cur;  // the parameter buffer selector survives across solves
+    *st = z;
+}
+
+}  // namespace ba
+
+// ---------------------------------------------------------------------------------------------
+// the handle
+// ---------------------------------------------------------------------------------------------
+using namespace ba;
+
+struct ba_handle {
+    int device = 0;
+    int rank = 0, nranks = 1;
+    cudaStream_t stream = nullptr;
+    ncclComm_t comm = nullptr;
+    bool have_problem = false;
+    Params P{};
+    int max_track = 0;
+    size_t smem_lin = 0, smem_pass = 0;
+
+    DBuf<double> cam_rt, cam_R, pt_X, pt_V, pt_g, pt_Vinv, pt_h, pt_z, pt_D;
+    DBuf<double> cam_U, cam_g, cam_D, cam_Minv, cam_acc, v_b, v_x, v_r, v_p, v_q;
+    DBuf<double2> o_uv, pm_uv, cm_uv;
+    DBuf<int2> o_idx, pm_idx;
+    DBuf<int> pt_off, pm_tile_pt, cm_pt, cam_tile_off;
+    DBuf<int4> cm_tile;
+    DBuf<double> cm_partial, pm_partial, cam_partial;
+    DBuf<LMState> st;
+    DBuf<double> io;  // staging for parameter upload / download
+    LMState* h_state = nullptr;  // pinned
+    int* h_flag = nullptr;       // pinned
+
+    long long launches[KN_COUNT] = {0};
+    double kernel_ms[KN_COUNT] = {0};
+    bool time_kernels = false;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_solve0 = nullptr, ev_solve1 = nullptr;
+
+    ~ba_handle() {
+        if (comm) nccl_api().CommDestroy(comm);
+        if (h_state) cudaFreeHost(h_state);
+        if (h_flag) cudaFreeHost(h_flag);
+        if (ev0) cudaEventDestroy(ev0);
+        if (ev1) cudaEventDestroy(ev1);
+        if (ev_solve0) cudaEventDestroy(ev_solve0);
+        if (ev_solve1) cudaEventDestroy(ev_solve1);
+        if (stream) cudaStreamDestroy(stream);
+    }
+};
+
+namespace ba {
+
+template <class... KArgs, class... Args>
+static void launch(ba_handle* h, Kind kind, void (*kernel)(KArgs...), int grid, int block, size_t smem, Args... args) {
+    if (grid <= 0) return;
+    if (h->time_kernels) CK(cudaEventRecord(h->ev0, h->stream));
+    kernel<<<grid, block, smem, h->stream>>>(args...);
+    CK(cudaGetLastError());
+    h->launches[kind] += 1;
+    if (h->time_kernels) {
+        CK(cudaEventRecord(h->ev1, h->stream));
+        CK(cudaEventSynchronize(h->ev1));
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+        h->kernel_ms[kind] += ms;
+    }
+}
+
+static inline int cdiv(long long a, int b) { return (int)((a + b - 1) / b); }
+
+static void allreduce_sum(ba_handle* h, double* buf, size_t count) {
+    if (h->nranks <= 1 || count == 0) return;
+    NK(nccl_api().AllReduce(buf, buf, count, ncclDouble, ncclSum, h->comm, h->stream));
+}
+static void allreduce_max(ba_handle* h, double* buf, size_t count) {
+    if (h->nranks <= 1 || count == 0) return;
+    NK(nccl_api().AllReduce(buf, buf, count, ncclDouble, ncclMax, h->comm, h->stream));
+}
+
+static void create_common(ba_handle* h, int device) {
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        fail(BA_ERR_CUDA, "no CUDA device available (%s); this library has no CPU path",
+             e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) fail(BA_ERR_ARG, "device %d out of range (0..%d)", device, ndev - 1);
+    h->device = device;
+    CK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        fail(BA_ERR_CUDA, "device %d is sm_%d%d; libba_b200 is built for sm_100a only", device, prop.major, prop.minor);
+    CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CK(cudaMallocHost(&h->h_state, sizeof(LMState)));
+    CK(cudaMallocHost(&h->h_flag, sizeof(int)));
+    CK(cudaEventCreate(&h->ev0));
+    CK(cudaEventCreate(&h->ev1));
+    CK(cudaEventCreate(&h->ev_solve0));
+    CK(cudaEventCreate(&h->ev_solve1));
+    h->st.alloc(1);
+    h->st.zero(h->stream);
+}
+
+static void use(ba_handle* h) {
+    if (!h) fail(BA_ERR_ARG, "null handle");
+    CK(cudaSetDevice(h->device));
+}
+
+static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy, int n_cams, int n_pts, int n_obs,
+                        const double* rvec, const double* tvec, const double* frv, const double* ftv, const double* pts,
+                        const int* obs_cam, const int* obs_pt, const double* obs_uv) {
+    use(h);
+    if (n_cams < 0 || n_pts <= 0 || n_obs <= 0) fail(BA_ERR_ARG, "need n_adj_cams >= 0, n_pts > 0, n_obs > 0");
+    if (!frv || !ftv || !pts || !obs_cam || !obs_pt || !obs_uv || (n_cams > 0 && (!rvec || !tvec)))
+        fail(BA_ERR_ARG, "null array argument");
+    cudaStream_t s = h->stream;
+    h->have_problem = false;
+    const size_t nc1 = (size_t)n_cams + 1;
+
+    h->cam_rt.alloc(2 * nc1 * 6); h->cam_R.alloc(2 * nc1 * 12);
+    h->pt_X.alloc(2 * (size_t)n_pts * 4); h->pt_V.alloc(2 * (size_t)n_pts * 6); h->pt_g.alloc(2 * (size_t)n_pts * 4);
+    h->pt_Vinv.alloc((size_t)n_pts * 6); h->pt_h.alloc((size_t)n_pts * 4); h->pt_z.alloc((size_t)n_pts * 4);
+    h->pt_D.alloc((size_t)n_pts * 4);
+    const size_t ncz = std::max<size_t>(n_cams, 1);
+    h->cam_U.alloc(ncz * 21); h->cam_g.alloc(ncz * 6); h->cam_D.alloc(ncz * 6); h->cam_Minv.alloc(ncz * 36);
+    h->cam_acc.alloc(ncz * 27); h->cam_partial.alloc(ncz * NSCAL);
+    h->v_b.alloc(nc1 * 6); h->v_x.alloc(nc1 * 6); h->v_r.alloc(nc1 * 6); h->v_p.alloc(nc1 * 6); h->v_q.alloc(nc1 * 6);
+    h->v_b.zero(s); h->v_x.zero(s); h->v_r.zero(s); h->v_p.zero(s); h->v_q.zero(s);
+    h->cam_partial.zero(s); h->cam_g.zero(s); h->cam_D.zero(s); h->cam_U.zero(s);
+    h->o_uv.alloc(n_obs); h->o_idx.alloc(n_obs); h->pm_uv.alloc(n_obs); h->pm_idx.alloc(n_obs);
+    h->cm_uv.alloc(n_obs); h->cm_pt.alloc(n_obs);
+    h->pt_off.alloc((size_t)n_pts + 1);
+    h->cam_tile_off.alloc(nc1);
+
+    // ---- upload -------------------------------------------------------------------------------
+    DBuf<int> d_cam, d_pt, d_iota, d_perm, d_err, d_camoff;
+    DBuf<unsigned> d_kpt, d_kpt_s;
+    DBuf<unsigned long long> d_kcam, d_kcam_s;
+    d_cam.alloc(n_obs); d_pt.alloc(n_obs); d_iota.alloc(n_obs); d_perm.alloc(n_obs); d_err.alloc(2);
+    d_kpt.alloc(n_obs); d_kpt_s.alloc(n_obs); d_kcam.alloc(n_obs); d_kcam_s.alloc(n_obs); d_camoff.alloc(nc1 + 1);
+    d_err.zero(s);
+    CK(cudaMemcpyAsync(d_cam.p, obs_cam, (size_t)n_obs * sizeof(int), cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_pt.p, obs_pt, (size_t)n_obs * sizeof(int), cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(h->o_uv.p, obs_uv, (size_t)n_obs * sizeof(double2), cudaMemcpyHostToDevice, s));
+
+    Params& P = h->P;
+    memset(&P, 0, sizeof P);
+    P.K = Intr{fx, fy, cx, cy};
+    P.delta = 1.0; P.mode = ROBUST_IRLS;
+    P.n_cams = n_cams; P.n_pts = n_pts; P.n_obs = n_obs;
+
+    const int B = 256;
+    launch(h, KN_SETUP, k_setup_keys, cdiv(n_obs, B), B, 0, n_obs, n_cams, n_pts, (const int*)d_cam.p, (const int*)d_pt.p,
+           h->o_idx.p, d_kpt.p, d_kcam.p, d_iota.p, d_err.p);
+
+    // ---- point-major order: stable radix sort of (point, original index) ----------------------
+    int pt_bits = 1;
+    while ((1LL << pt_bits) < n_pts) ++pt_bits;
+    size_t tmp_bytes = 0, tb2 = 0;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, d_kpt.p, d_kpt_s.p, d_iota.p, d_perm.p, n_obs, 0, pt_bits, s));
+    int cam_bits = 1;
+    while ((1LL << cam_bits) < (long long)n_cams + 1) ++cam_bits;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, tb2, d_kcam.p, d_kcam_s.p, d_iota.p, d_perm.p, n_obs, 0, 32 + cam_bits, s));
+    DBuf<unsigned char> d_tmp;
+    d_tmp.alloc(std::max(tmp_bytes, tb2));
+    tmp_bytes = d_tmp.n;
+    CK(cub::DeviceRadixSort::SortPairs(d_tmp.p, tmp_bytes, d_kpt.p, d_kpt_s.p, d_iota.p, d_perm.p, n_obs, 0, pt_bits, s));
+    h->launches[KN_SETUP] += 1;
+    launch(h, KN_SETUP, k_gather_pm, cdiv(n_obs, B), B, 0, n_obs, (const int*)d_perm.p, (const double2*)h->o_uv.p,
+           (const int2*)h->o_idx.p, h->pm_uv.p, h->pm_idx.p);
+    launch(h, KN_SETUP, k_lower_bound_u32, cdiv(n_pts + 1, B), B, 0, n_obs, (const unsigned*)d_kpt_s.p, n_pts + 1, h->pt_off.p);
+    const int pm_tiles = cdiv(n_obs, PM_THREADS);
+    h->pm_tile_pt.alloc((size_t)pm_tiles + 1);
+    launch(h, KN_SETUP, k_pm_tiles, cdiv(pm_tiles + 1, B), B, 0, n_pts, (const int*)h->pt_off.p, pm_tiles, h->pm_tile_pt.p);
+    launch(h, KN_SETUP, k_max_track, cdiv(n_pts, B), B, 0, n_pts, (const int*)h->pt_off.p, d_err.p + 1);
+
+    // ---- camera-major order: stable sort of ((camera, point), original index); fixed camera last ----
+    tmp_bytes = d_tmp.n;
+    CK(cub::DeviceRadixSort::SortPairs(d_tmp.p, tmp_bytes, d_kcam.p, d_kcam_s.p, d_iota.p, d_perm.p, n_obs, 0, 32 + cam_bits, s));
+    h->launches[KN_SETUP] += 1;
+    launch(h, KN_SETUP, k_lower_bound_cam, cdiv((int)nc1 + 1, B), B, 0, n_obs, (const unsigned long long*)d_kcam_s.p, (int)nc1 + 1,
+           d_camoff.p);
+    std::vector<int> camoff(nc1 + 1);
+    int err_track[2] = {0, 0};
+    CK(cudaMemcpyAsync(camoff.data(), d_camoff.p, (nc1 + 1) * sizeof(int), cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(err_track, d_err.p, 2 * sizeof(int), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    if (err_track[0]) fail(BA_ERR_ARG, "observation index out of range (obs_cam must be in [-1, n_adj_cams), obs_pt in [0, n_pts))");
+    const int n_obs_adj = camoff[n_cams];
+    launch(h, KN_SETUP, k_gather_cm, cdiv(n_obs_adj, B), B, 0, n_obs_adj, (const int*)d_perm.p, (const double2*)h->o_uv.p,
+           (const int2*)h->o_idx.p, h->cm_uv.p, h->cm_pt.p);
+    std::vector<int4> tiles;
+    std::vector<int> tile_off(nc1, 0);
+    for (int c = 0; c < n_cams; ++c) {
+        tile_off[c] = (int)tiles.size();
+        for (int o = camoff[c]; o < camoff[c + 1]; o += CM_TILE)
+            tiles.push_back(make_int4(c, o, std::min(CM_TILE, camoff[c + 1] - o), 0));
+    }
+    tile_off[n_cams] = (int)tiles.size();
+    const int cm_tiles = (int)tiles.size();
+    h->cm_tile.alloc(std::max<size_t>(cm_tiles, 1));
+    if (cm_tiles) CK(cudaMemcpyAsync(h->cm_tile.p, tiles.data(), (size_t)cm_tiles * sizeof(int4), cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(h->cam_tile_off.p, tile_off.data(), nc1 * sizeof(int), cudaMemcpyHostToDevice, s));
+    h->cm_partial.alloc(std::max<size_t>((size_t)cm_tiles * 27, 27));
+    h->pm_partial.alloc((size_t)pm_tiles * NSCAL);
+    h->pm_partial.zero(s);
+
+    h->max_track = err_track[1];
+    const int cap = PM_THREADS + h->max_track;
+    h->smem_lin = (size_t)9 * cap * sizeof(double);
+    h->smem_pass = (size_t)3 * cap * sizeof(double);
+    if (h->smem_lin > 227 * 1024)
+        fail(BA_ERR_ARG, "a point is observed %d times; this build supports track lengths up to %d", h->max_track,
+             (int)(227 * 1024 / 72) - PM_THREADS);
+    CK(cudaFuncSetAttribute(k_lin_points, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_lin));
+    CK(cudaFuncSetAttribute(k_point_pass<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_pass));
+    CK(cudaFuncSetAttribute(k_point_pass<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_pass));
+
+    // ---- parameters -----------------------------------------------------------------------------
+    h->io.alloc(std::max<size_t>((size_t)n_pts * 3, nc1 * 6));
+    P.n_obs_adj = n_obs_adj; P.pm_tiles = pm_tiles; P.cm_tiles = cm_tiles; P.pm_cap = cap;
+    P.cam_rt = h->cam_rt.p; P.cam_R = h->cam_R.p; P.pt_X = h->pt_X.p; P.pt_V = h->pt_V.p; P.pt_g = h->pt_g.p;
+    P.pt_Vinv = h->pt_Vinv.p; P.pt_h = h->pt_h.p; P.pt_z = h->pt_z.p; P.pt_D = h->pt_D.p;
+    P.cam_U = h->cam_U.p; P.cam_g = h->cam_g.p; P.cam_D = h->cam_D.p; P.cam_Minv = h->cam_Minv.p; P.cam_acc = h->cam_acc.p;
+    P.v_b = h->v_b.p; P.v_x = h->v_x.p; P.v_r = h->v_r.p; P.v_p = h->v_p.p; P.v_q = h->v_q.p;
+    P.o_uv = h->o_uv.p; P.o_idx = h->o_idx.p; P.pm_uv = h->pm_uv.p; P.pm_idx = h->pm_idx.p; P.pt_off = h->pt_off.p;
+    P.pm_tile_pt = h->pm_tile_pt.p; P.cm_uv = h->cm_uv.p; P.cm_pt = h->cm_pt.p; P.cm_tile = h->cm_tile.p;
+    P.cam_tile_off = h->cam_tile_off.p; P.cm_partial = h->cm_partial.p; P.pm_partial = h->pm_partial.p;
+    P.cam_partial = h->cam_partial.p; P.st = h->st.p;
+    h->st.zero(s);
+    CK(cudaStreamSynchronize(s));  // the sort scratch buffers die at scope exit
+    h->have_problem = true;
+}
+
+static void set_params(ba_handle* h, const double* rvec, const double* tvec, const double* frv, const double* ftv,
+                       const double* pts) {
+    // writes parameter buffer 0 and makes it current
+    use(h);
+    cudaStream_t s = h->stream;
+    const Params& P = h->P;
+    const int B = 256;
+    const size_t nc1 = (size_t)P.n_cams + 1;
+    CK(cudaMemsetAsync(&h->st.p->cur, 0, sizeof(int), s));
+    if (pts) {
+        CK(cudaMemcpyAsync(h->io.p, pts, (size_t)P.n_pts * 3 * sizeof(double), cudaMemcpyHostToDevice, s));
+        launch(h, KN_SETUP, k_pack_points, cdiv(P.n_pts, B), B, 0, P.n_pts, (const double*)h->io.p, h->pt_X.p);
+    }
+    if (frv) {
+        DBuf<double> tmp;
+        tmp.alloc(std::max<size_t>((size_t)P.n_cams * 6, 1));
+        if (P.n_cams) {
+            CK(cudaMemcpyAsync(tmp.p, rvec, (size_t)P.n_cams * 3 * sizeof(double), cudaMemcpyHostToDevice, s));
+            CK(cudaMemcpyAsync(tmp.p + (size_t)P.n_cams * 3, tvec, (size_t)P.n_cams * 3 * sizeof(double), cudaMemcpyHostToDevice, s));
+        }
+        launch(h, KN_SETUP, k_pack_cams, cdiv((int)nc1, B), B, 0, P.n_cams, (const double*)tmp.p,
+               (const double*)(tmp.p + (size_t)P.n_cams * 3), frv[0], frv[1], frv[2], ftv[0], ftv[1], ftv[2], h->cam_rt.p);
+        CK(cudaStreamSynchronize(s));
+    }
+    launch(h, KN_CAM_PREP, k_cam_prepare, cdiv((int)nc1, B), B, 0, P, 0);
+    CK(cudaStreamSynchronize(s));
+}
+
+static void read_state(ba_handle* h) {
+    CK(cudaMemcpyAsync(h->h_state, h->st.p, sizeof(LMState), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+}
+
+static void need_problem(ba_handle* h) {
+    use(h);
+    if (!h->have_problem) fail(BA_ERR_STATE, "no problem uploaded: call ba_set_problem first");
+}
+
+static void apply_robust(ba_handle* h, const ba_options* opt) {
+    h->P.delta = opt->huber_delta;
+    h->P.mode = opt->robust_mode;
+    if (!(opt->huber_delta > 0.0)) fail(BA_ERR_ARG, "huber_delta must be positive");
+    if (opt->robust_mode < 0 || opt->robust_mode > 2) fail(BA_ERR_ARG, "unknown robust_mode %d", opt->robust_mode);
+}
+
+// linearise the point side at buffer `which` and reduce the cost scalars
+static void lin_points_and_cost(ba_handle* h, int which) {
+    const Params& P = h->P;
+    launch(h, KN_LIN_PTS, k_lin_points, P.pm_tiles, PM_THREADS, h->smem_lin, P, which);
+}
+
+static const unsigned MASK_LIN = (1u << S_COST) | (1u << S_RAW) | (1u << S_BAD) | (1u << S_GPMAX);
+static const unsigned MASK_STEP_PM = (1u << S_GDP) | (1u << S_DDP) | (1u << S_DP2) | (1u << S_XP2);
+static const unsigned MASK_STEP_CAM = (1u << S_GDC) | (1u << S_DDC) | (1u << S_RDC) | (1u << S_DC2) | (1u << S_XC2);
+
+static void reduce_scalars(ba_handle* h, unsigned pm_mask, unsigned cam_mask) {
+    const Params& P = h->P;
+    launch(h, KN_REDUCE, k_reduce_scalars, 1, VEC_THREADS, 0, P, pm_mask, cam_mask);
+    if (h->nranks > 1) {
+        double* scal = reinterpret_cast<double*>(reinterpret_cast<char*>(h->st.p) + offsetof(LMState, scal));
+        allreduce_sum(h, scal, N_PT_SCAL);
+        if (pm_mask & (1u << S_GPMAX)) allreduce_max(h, scal + S_GPMAX, 1);
+    }
+}
+
+static void lin_cameras(ba_handle* h, double dmin, double dmax) {
+    const Params& P = h->P;
+    if (P.n_cams == 0) return;
+    launch(h, KN_LIN_CAM, k_camera_pass<0>, P.cm_tiles, CM_THREADS, 0, P, (const double*)nullptr, 0);
+    launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 27, 256), 256, 0, P, 27, 0);
+    allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 27);
+    launch(h, KN_CAM_FIN, k_camera_finish_lin, cdiv(P.n_cams, 128), 128, 0, P, dmin, dmax);
+}
+
+static const double kDiagMin = 1e-6, kDiagMax = 1e32;
+
+static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
+    need_problem(h);
+    apply_robust(h, opt);
+    if (opt->max_iters < 0 || opt->pcg_max_iters < 1) fail(BA_ERR_ARG, "bad iteration limits");
+    const Params& P = h->P;
+    cudaStream_t s = h->stream;
+    for (int k = 0; k < KN_COUNT; ++k) { h->launches[k] = 0; h->kernel_ms[k] = 0.0; }
+    h->time_kernels = opt->verbose >= 2;
+    const int check_every = std::max(1, opt->pcg_check_every);
+    const int with_schur = opt->precond == BA_PRECOND_SCHUR_JACOBI ? 1 : 0;
+    const int nc1 = P.n_cams + 1;
+
+    CK(cudaEventRecord(h->ev_solve0, s));
+    launch(h, KN_SETUP, k_init_state, 1, 1, 0, h->st.p, opt->initial_lambda);
+    launch(h, KN_CAM_PREP, k_cam_prepare, cdiv(nc1, 256), 256, 0, P, 2);
+    lin_points_and_cost(h, 2);
+    reduce_scalars(h, MASK_LIN, 0);
+    launch(h, KN_DECIDE, k_store_cost, 1, 1, 0, P, 2);
+    read_state(h);
+    if (h->h_state->bad) fail(BA_ERR_NONFINITE, "Residuals are not finite in the initial point.");
+    const double cost0 = h->h_state->cost[h->h_state->cur], raw0 = h->h_state->raw[h->h_state->cur];
+
+    bool need_lin = true;
+    int status = opt->max_iters == 0 ? 6 : 0;
+    while (status == 0) {
+        if (need_lin) {
+            lin_cameras(h, kDiagMin, kDiagMax);
+            launch(h, KN_GRAD, k_gradient_check, 1, VEC_THREADS, 0, P, opt->gtol);
+        }
+        launch(h, KN_PT_PREP, k_point_prepare, cdiv(P.n_pts, 256), 256, 0, P, kDiagMin, kDiagMax);
+        if (P.n_cams > 0) {
+            launch(h, KN_SCHUR_CAM, k_camera_pass<1>, P.cm_tiles, CM_THREADS, 0, P, (const double*)nullptr, with_schur);
+            launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 27, 256), 256, 0, P, 27, 0);
+            allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 27);
+            launch(h, KN_CAM_FIN, k_camera_finish_schur, cdiv(P.n_cams, 128), 128, 0, P, with_schur);
+            launch(h, KN_PCG_INIT, k_pcg_init, 1, VEC_THREADS, 0, P);
+            for (int it = 0; it < opt->pcg_max_iters; ++it) {
+                launch(h, KN_PT_PASS, k_point_pass<0>, P.pm_tiles, PM_THREADS, h->smem_pass, P, (const double*)h->v_p.p);
+                launch(h, KN_MATVEC_CAM, k_camera_pass<2>, P.cm_tiles, CM_THREADS, 0, P, (const double*)h->v_p.p, 0);
+                launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 6, 256), 256, 0, P, 6, 1);
+                allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 6);
+                launch(h, KN_PCG_UPDATE, k_pcg_update, 1, VEC_THREADS, 0, P, opt->pcg_tol, opt->pcg_max_iters);
+                if ((it + 1) % check_every == 0 && it + 1 < opt->pcg_max_iters) {
+                    CK(cudaMemcpyAsync(h->h_flag, &h->st.p->pcg_done, sizeof(int), cudaMemcpyDeviceToHost, s));
+                    CK(cudaStreamSynchronize(s));
+                    if (*h->h_flag) break;
+                }
+            }
+        }
+        launch(h, KN_BACKSUB, k_point_pass<1>, P.pm_tiles, PM_THREADS, h->smem_pass, P, (const double*)h->v_x.p);
+        launch(h, KN_CAM_UPDATE, k_camera_update, cdiv(nc1, 128), 128, 0, P);
+        lin_points_and_cost(h, 3);
+        reduce_scalars(h, MASK_LIN | MASK_STEP_PM, MASK_STEP_CAM);
+        launch(h, KN_DECIDE, k_lm_decide, 1, 1, 0, P, opt->ftol, opt->xtol, opt->lambda_min, opt->lambda_max, opt->max_iters);
+        read_state(h);
+        const LMState& st = *h->h_state;
+        status = st.status;
+        need_lin = st.last_accepted != 0;
+        if (opt->verbose)
+            fprintf(stderr, "[ba_b200] it %3d %s cost %.9e -> trial %.9e  rho %+.3e  lambda %.3e  pcg %d  |g| %.3e  |dx| %.3e\n",
+                    st.iter, st.last_accepted ? "acc" : "REJ", st.cost[st.cur ^ (st.last_accepted ? 1 : 0)], st.scal[S_COST], st.rho,
+                    st.lambda, st.pcg_iter, st.gmax, st.step_norm);
+    }
+    if (opt->max_iters == 0) read_state(h);
+    CK(cudaEventRecord(h->ev_solve1, s));
+    CK(cudaEventSynchronize(h->ev_solve1));
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, h->ev_solve0, h->ev_solve1));
+    h->time_kernels = false;
+    if (out) {
+        const LMState& st = *h->h_state;
+        memset(out, 0, sizeof *out);
+        out->status = status == 6 ? 0 : status;
+        out->iterations = st.iter; out->accepted = st.accepted; out->rejected = st.rejected;
+        out->pcg_iterations = st.pcg_total;
+        long long L = 0;
+        for (int k = 0; k < KN_COUNT; ++k) L += h->launches[k];
+        out->launches = (int)L;
+        out->initial_raw_cost = raw0; out->initial_cost = cost0;
+        out->final_raw_cost = st.raw[st.cur]; out->final_cost = st.cost[st.cur];
+        out->gradient_max = st.gmax; out->final_lambda = st.lambda; out->solve_ms = ms;
+    }
+}
+
+}  // namespace ba
+
+// ---------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------
+#define API_BEGIN try {
+#define API_END                                  \
+    }                                            \
+    catch (const ba::BaError& e) {               \
+        ba::g_last_error = e.what();             \
+        return e.code;                           \
+    }                                            \
+    catch (const std::exception& e) {            \
+        ba::g_last_error = e.what();             \
+        return BA_ERR_STATE;                     \
+    }                                            \
+    return BA_OK;
+
+extern "C" {
+
+const char* ba_last_error(void) { return ba::g_last_error.c_str(); }
+
+void ba_default_options(ba_options* o) {
+    if (!o) return;
+    memset(o, 0, sizeof *o);
+    o->max_iters = 50;
+    o->gtol = 1e-8; o->ftol = 1e-6; o->xtol = 1e-8;
+    o->huber_delta = 1.0; o->robust_mode = BA_ROBUST_IRLS;
+    o->initial_lambda = 1e-4; o->lambda_min = 1e-12; o->lambda_max = 1e16;
+    o->precond = BA_PRECOND_SCHUR_JACOBI;
+    o->pcg_max_iters = 100; o->pcg_tol = 0.1; o->pcg_check_every = 4;
+    o->verbose = 0;
+}
+
+int ba_create(int device, ba_handle** out) {
+    API_BEGIN
+    if (!out) ba::fail(BA_ERR_ARG, "null out pointer");
+    *out = nullptr;
+    ba_handle* h = new ba_handle();
+    try {
+        ba::create_common(h, device);
+    } catch (...) {
+        delete h;
+        throw;
+    }
+    *out = h;
+    API_END
+}
+
+int ba_nccl_unique_id(char id_out[128]) {
+    API_BEGIN
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+    ncclUniqueId id;
+    NK(ba::nccl_api().GetUniqueId(&id));
+    memcpy(id_out, &id, 128);
+    API_END
+}
+
+int ba_create_distributed(int device, int rank, int nranks, const char nccl_id[128], ba_handle** out) {
+    API_BEGIN
+    if (!out || !nccl_id) ba::fail(BA_ERR_ARG, "null pointer");
+    if (nranks < 1 || rank < 0 || rank >= nranks) ba::fail(BA_ERR_ARG, "bad rank %d of %d", rank, nranks);
+    *out = nullptr;
+    ba_handle* h = new ba_handle();
+    try {
+        ba::create_common(h, device);
+        h->rank = rank; h->nranks = nranks;
+        if (nranks > 1) {
+            ncclUniqueId id;
+            memcpy(&id, nccl_id, 128);
+            NK(ba::nccl_api().CommInitRank(&h->comm, nranks, id, rank));
+        }
+    } catch (...) {
+        delete h;
+        throw;
+    }
+    *out = h;
+    API_END
+}
+
+int ba_destroy(ba_handle* h) {
+    API_BEGIN
+    if (h) {
+        cudaSetDevice(h->device);
+        cudaStreamSynchronize(h->stream);
+        delete h;
+    }
+    API_END
+}
+
+int ba_set_problem(ba_handle* h, double fx, double fy, double cx, double cy, int32_t n_adj_cams, int32_t n_pts, int32_t n_obs,
+                   const double* rvec, const double* tvec, const double fixed_rvec[3], const double fixed_tvec[3],
+                   const double* pts, const int32_t* obs_cam, const int32_t* obs_pt, const double* obs_uv) {
+    API_BEGIN
+    ba::set_problem(h, fx, fy, cx, cy, n_adj_cams, n_pts, n_obs, rvec, tvec, fixed_rvec, fixed_tvec, pts, obs_cam, obs_pt, obs_uv);
+    ba::set_params(h, rvec, tvec, fixed_rvec, fixed_tvec, pts);
+    API_END
+}
+
+int ba_set_params(ba_handle* h, const double* rvec, const double* tvec, const double* pts) {
+    API_BEGIN
+    ba::need_problem(h);
+    const ba::Params& P = h->P;
+    if (!pts || (P.n_cams > 0 && (!rvec || !tvec))) ba::fail(BA_ERR_ARG, "null array argument");
+    // the fixed pose stays what ba_set_problem uploaded: fetch it from the current buffer
+    ba::read_state(h);
+    const int b = h->h_state->cur;
+    double f[6];
+    CK(cudaMemcpy(f, h->cam_rt.p + (size_t)b * (P.n_cams + 1) * 6 + (size_t)P.n_cams * 6, sizeof f, cudaMemcpyDeviceToHost));
+    ba::set_params(h, rvec, tvec, f, f + 3, pts);
+    API_END
+}
+
+int ba_get_params(ba_handle* h, double* rvec, double* tvec, double* pts) {
+    API_BEGIN
+    ba::need_problem(h);
+    const ba::Params& P = h->P;
+    cudaStream_t s = h->stream;
+    ba::read_state(h);
+    const int b = h->h_state->cur;
+    if (pts) {
+        ba::launch(h, ba::KN_SETUP, ba::k_unpack_points, ba::cdiv(P.n_pts, 256), 256, 0, P.n_pts,
+                   (const double*)(h->pt_X.p + (size_t)b * P.n_pts * 4), h->io.p);
+        CK(cudaMemcpyAsync(pts, h->io.p, (size_t)P.n_pts * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+    }
+    if ((rvec || tvec) && P.n_cams > 0) {
+        ba::DBuf<double> tmp;
+        tmp.alloc((size_t)P.n_cams * 6);
+        ba::launch(h, ba::KN_SETUP, ba::k_unpack_cams, ba::cdiv(P.n_cams, 256), 256, 0, P.n_cams,
+                   (const double*)(h->cam_rt.p + (size_t)b * (P.n_cams + 1) * 6), tmp.p, tmp.p + (size_t)P.n_cams * 3);
+        if (rvec) CK(cudaMemcpyAsync(rvec, tmp.p, (size_t)P.n_cams * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
+        if (tvec) CK(cudaMemcpyAsync(tvec, tmp.p + (size_t)P.n_cams * 3, (size_t)P.n_cams * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+    }
+    API_END
+}
+
+int ba_residuals(ba_handle* h, double* r_out) {
+    API_BEGIN
+    ba::need_problem(h);
+    if (!r_out) ba::fail(BA_ERR_ARG, "null output");
+    const ba::Params& P = h->P;
+    ba::DBuf<double2> d;
+    d.alloc(P.n_obs);
+    ba::launch(h, ba::KN_RESID, ba::k_residuals, ba::cdiv(P.n_obs, 256), 256, 0, P, d.p);
+    CK(cudaMemcpyAsync(r_out, d.p, (size_t)P.n_obs * sizeof(double2), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    API_END
+}
+
+int ba_cost(ba_handle* h, double huber_delta, double* raw_out, double* robust_out) {
+    API_BEGIN
+    ba::need_problem(h);
+    if (!(huber_delta > 0.0)) ba::fail(BA_ERR_ARG, "huber_delta must be positive");
+    h->P.delta = huber_delta;
+    h->P.mode = ba::ROBUST_IRLS;
+    ba::lin_points_and_cost(h, 2);
+    ba::reduce_scalars(h, ba::MASK_LIN, 0);
+    ba::read_state(h);
+    if (raw_out) *raw_out = h->h_state->scal[ba::S_RAW];
+    if (robust_out) *robust_out = h->h_state->scal[ba::S_COST];
+    API_END
+}
+
+int ba_jacobian_blocks(ba_handle* h, double* jc_out, double* jp_out) {
+    API_BEGIN
+    ba::need_problem(h);
+    if (!jc_out || !jp_out) ba::fail(BA_ERR_ARG, "null output");
+    const ba::Params& P = h->P;
+    ba::DBuf<double> jc, jp;
+    jc.alloc((size_t)P.n_obs * 12);
+    jp.alloc((size_t)P.n_obs * 6);
+    ba::launch(h, ba::KN_JAC, ba::k_jacobian_blocks, ba::cdiv(P.n_obs, 256), 256, 0, P, jc.p, jp.p);
+    CK(cudaMemcpyAsync(jc_out, jc.p, jc.n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(jp_out, jp.p, jp.n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    API_END
+}
+
+int ba_sparsity_csr(ba_handle* h, int64_t* indptr, int64_t* indices, int64_t* nnz_out) {
+    API_BEGIN
+    ba::need_problem(h);
+    static_assert(sizeof(long long) == sizeof(int64_t), "int64");
+    const ba::Params& P = h->P;
+    cudaStream_t s = h->stream;
+    ba::DBuf<long long> cnt, start, d_indptr, d_indices;
+    cnt.alloc(P.n_obs); start.alloc(P.n_obs); d_indptr.alloc(2 * (size_t)P.n_obs + 1);
+    ba::launch(h, ba::KN_SETUP, ba::k_sparsity_counts, ba::cdiv(P.n_obs, 256), 256, 0, P.n_obs, P.n_cams, P.o_idx, cnt.p);
+    size_t tb = 0;
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt.p, start.p, P.n_obs, s));
+    ba::DBuf<unsigned char> tmp;
+    tmp.alloc(tb);
+    CK(cub::DeviceScan::ExclusiveSum(tmp.p, tb, cnt.p, start.p, P.n_obs, s));
+    long long last_start = 0, last_cnt = 0;
+    CK(cudaMemcpyAsync(&last_start, start.p + P.n_obs - 1, sizeof(long long), cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(&last_cnt, cnt.p + P.n_obs - 1, sizeof(long long), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    const long long nnz = last_start + last_cnt;
+    if (nnz_out) *nnz_out = nnz;
+    if (indptr || indices) {
+        if (indices) d_indices.alloc((size_t)nnz);
+        ba::launch(h, ba::KN_SETUP, ba::k_sparsity_fill, ba::cdiv(P.n_obs, 256), 256, 0, P.n_obs, P.n_cams, P.o_idx,
+                   (const long long*)start.p, d_indptr.p, indices ? d_indices.p : (long long*)nullptr);
+        if (indptr) CK(cudaMemcpyAsync(indptr, d_indptr.p, d_indptr.n * sizeof(long long), cudaMemcpyDeviceToHost, s));
+        if (indices) CK(cudaMemcpyAsync(indices, d_indices.p, (size_t)nnz * sizeof(long long), cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+    }
+    API_END
+}
+
+int ba_normal_blocks(ba_handle* h, const ba_options* opt, double* gc, double* gp, double* U, double* V) {
+    API_BEGIN
+    ba::need_problem(h);
+    ba_options o;
+    if (opt) o = *opt; else ba_default_options(&o);
+    ba::apply_robust(h, &o);
+    const ba::Params& P = h->P;
+    cudaStream_t s = h->stream;
+    ba::launch(h, ba::KN_CAM_PREP, ba::k_cam_prepare, ba::cdiv(P.n_cams + 1, 256), 256, 0, P, 2);
+    ba::lin_points_and_cost(h, 2);
+    ba::lin_cameras(h, ba::kDiagMin, ba::kDiagMax);
+    ba::read_state(h);
+    const int b = h->h_state->cur;
+    if (gc && P.n_cams) CK(cudaMemcpyAsync(gc, h->cam_g.p, (size_t)P.n_cams * 6 * sizeof(double), cudaMemcpyDeviceToHost, s));
+    std::vector<double> u21, v6, g4;
+    if (U && P.n_cams) {
+        u21.resize((size_t)P.n_cams * 21);
+        CK(cudaMemcpyAsync(u21.data(), h->cam_U.p, u21.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
+    }
+    if (V) {
+        v6.resize((size_t)P.n_pts * 6);
+        CK(cudaMemcpyAsync(v6.data(), h->pt_V.p + (size_t)b * P.n_pts * 6, v6.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
+    }
+    if (gp) {
+        g4.resize((size_t)P.n_pts * 4);
+        CK(cudaMemcpyAsync(g4.data(), h->pt_g.p + (size_t)b * P.n_pts * 4, g4.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
+    }
+    CK(cudaStreamSynchronize(s));
+    if (U)
+        for (int c = 0; c < P.n_cams; ++c)
+            for (int i = 0; i < 6; ++i)
+                for (int j = i; j < 6; ++j) {
+                    const double v = u21[(size_t)c * 21 + ba::sym6(i, j)];
+                    U[(size_t)c * 36 + 6 * i + j] = v;
+                    U[(size_t)c * 36 + 6 * j + i] = v;
+                }
+    if (V)
+        for (int p = 0; p < P.n_pts; ++p)
+            for (int i = 0; i < 3; ++i)
+                for (int j = i; j < 3; ++j) {
+                    const double v = v6[(size_t)p * 6 + ba::sym3(i, j)];
+                    V[(size_t)p * 9 + 3 * i + j] = v;
+                    V[(size_t)p * 9 + 3 * j + i] = v;
+                }
+    if (gp)
+        for (int p = 0; p < P.n_pts; ++p)
+            for (int k = 0; k < 3; ++k) gp[(size_t)p * 3 + k] = g4[(size_t)p * 4 + k];
+    API_END
+}
+
+int ba_solve(ba_handle* h, const ba_options* opt, ba_stats* stats_out) {
+    API_BEGIN
+    ba_options o;
+    if (opt) o = *opt; else ba_default_options(&o);
+    ba::solve(h, &o, stats_out);
+    API_END
+}
+
+int ba_kernel_count(void) { return ba::KN_COUNT; }
+const char* ba_kernel_name(int k) { return (k >= 0 && k < ba::KN_COUNT) ? ba::kKindNames[k] : ""; }
+int ba_kernel_stats(ba_handle* h, int64_t* launches, double* ms) {
+    API_BEGIN
+    if (!h) ba::fail(BA_ERR_ARG, "null handle");
+    for (int k = 0; k < ba::KN_COUNT; ++k) {
+        if (launches) launches[k] = h->launches[k];
+        if (ms) ms[k] = h->kernel_ms[k];
+    }
+    API_END
+}
+
+}  // extern "C"

@@ -1,0 +1,158 @@
+/*
+ * ba_b200.h - C ABI of libba_b200.so, the B200 (sm_100a) bundle-adjustment back end.
+ *
+ * Drop-in boundary for the local/global BA step of egirgin/bundle_adjustment
+ * (reference: src/bundle_adjuster.py).  The reference is pure Python and has no FFI; a maintainer
+ * binds this library with ctypes.  Each entry point below names the reference
+ * code it replaces.  Plain pointers and sizes only; all arrays are caller-owned HOST memory, borrowed
+ * for the duration of the call; all floating point is IEEE binary64; all indices are int32.
+ *
+ * Conventions shared with the reference:
+ *   pose      x_cam = R(rvec) * X + t          (cv2.projectPoints, src/bundle_adjuster.py:67)
+ *   pinhole   u = fx x/z + cx, v = fy y/z + cy (no distortion, no skew)
+ *   residual  r[2i], r[2i+1] = observed(u,v)_i - projected(u,v)_i      (src/bundle_adjuster.py:68-70)
+ *   params    [rvec_0..rvec_{Nc-1} | t_0..t_{Nc-1} | X_0..X_{Np-1}]      (src/bundle_adjuster.py:157-162)
+ *   loss      Huber per scalar residual, threshold huber_delta (=1 px), cost = 0.5 * sum rho(r^2)
+ *             (scipy.optimize.least_squares(loss='huber', f_scale=1), src/bundle_adjuster.py:170-174)
+ *
+ * Return value of every int function: 0 = ok, < 0 = error (text via ba_last_error()).
+ * ba_solve additionally reports the termination reason in ba_stats.status (> 0, mirrors SciPy's
+ * OptimizeResult.status: 1 gtol, 2 ftol, 3 xtol, 4 ftol and xtol; 0 = iteration limit; 5 = damping
+ * limit reached).
+ */
+#ifndef BA_B200_H
+#define BA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ba_handle ba_handle;
+
+#define BA_OK 0
+#define BA_ERR_ARG (-1)
+#define BA_ERR_CUDA (-2)
+#define BA_ERR_NCCL (-3)
+#define BA_ERR_STATE (-4)
+#define BA_ERR_NONFINITE (-5) /* residuals not finite at the initial point (SciPy raises ValueError there) */
+
+#define BA_ROBUST_NONE 0   /* plain least squares */
+#define BA_ROBUST_IRLS 1   /* curvature weight = gradient weight = rho'(r^2)            (default) */
+#define BA_ROBUST_TRIGGS 2 /* SciPy's scale_for_robust_loss_function: max(rho'+2 rho'' r^2, eps) */
+
+#define BA_PRECOND_JACOBI 0       /* camera blocks of J^T J                                    */
+#define BA_PRECOND_SCHUR_JACOBI 1 /* diagonal blocks of the Schur complement          (default) */
+
+typedef struct ba_options {
+    int32_t max_iters;        /* LM iterations, accepted + rejected (reference: max_nfev = 50)      */
+    double gtol;              /* stop when max |gradient| < gtol               (SciPy default 1e-8) */
+    double ftol;              /* stop when cost decrease < ftol * cost          (reference 1e-5)    */
+    double xtol;              /* stop when |step| < xtol * (xtol + |x|)         (reference 1e-5)    */
+    double huber_delta;       /* Huber threshold in pixels (reference: f_scale = 1.0)               */
+    int32_t robust_mode;      /* BA_ROBUST_*                                                        */
+    double initial_lambda;    /* LM damping at the first iteration                                  */
+    double lambda_min, lambda_max;
+    int32_t precond;          /* BA_PRECOND_*                                                       */
+    int32_t pcg_max_iters;    /* per LM iteration                                                   */
+    double pcg_tol;           /* forcing term: stop PCG when |r|_M^-1 <= pcg_tol * |b|_M^-1          */
+    int32_t pcg_check_every;  /* host polls the device "PCG converged" flag every this many iterations */
+    int32_t verbose;          /* 1: one stderr line per LM iteration                                */
+    int32_t reserved[7];
+} ba_options;
+
+typedef struct ba_stats {
+    int32_t status;           /* termination reason, see top of file                                */
+    int32_t iterations;       /* LM iterations run (accepted + rejected)                            */
+    int32_t accepted, rejected;
+    int32_t pcg_iterations;   /* total over the solve                                               */
+    int32_t launches;         /* CUDA kernels launched by the solve                                 */
+    double initial_raw_cost;  /* sum r^2 at the initial point  (src/bundle_adjuster.py:165)         */
+    double final_raw_cost;    /* sum r^2 at the returned point (src/bundle_adjuster.py:176)         */
+    double initial_cost;      /* 0.5 * sum rho at the initial point (SciPy's cost)                  */
+    double final_cost;        /* 0.5 * sum rho at the returned point                                */
+    double gradient_max;      /* max |g| at the returned point (local camera coordinates)           */
+    double final_lambda;
+    double solve_ms;          /* CUDA-event time of the device LM loop                              */
+    double reserved[8];
+} ba_stats;
+
+/* Defaults: max_iters 50, gtol 1e-8, ftol 1e-6, xtol 1e-8, huber 1.0, IRLS, lambda 1e-4, Schur-Jacobi PCG. */
+void ba_default_options(ba_options* opt);
+
+/* One handle = one GPU + one CUDA stream.  `device` is a CUDA ordinal.  Replaces nothing in the
+ * reference (which keeps no state between run() calls); device buffers live inside the handle. */
+int ba_create(int device, ba_handle** out);
+
+/* Multi-GPU handle: rank `rank` of `nranks` one-process-per-GPU solvers that each own a contiguous
+ * range of the points (and those points' observations) and replicate all cameras.  `nccl_id` is the
+ * 128-byte id from ba_nccl_unique_id() on rank 0, distributed by the host (torch.distributed in
+ * bench.py).  Camera-side sums and scalar costs are all-reduced over NCCL; nothing else moves. */
+int ba_nccl_unique_id(char id_out[128]);
+int ba_create_distributed(int device, int rank, int nranks, const char nccl_id[128], ba_handle** out);
+
+int ba_destroy(ba_handle* h);
+
+/* Upload one problem.  Replaces the flattening at src/bundle_adjuster.py:150-162 on the device side:
+ * the host passes the arrays in the reference's own order (observations keyframe-major as
+ * _gather_local_data :195-218 emits them; obs_cam = index into the adjustable keyframes or -1 for the
+ * fixed keyframe; obs_pt = index into the sorted map-point ids).  The point-major and camera-major
+ * permutations the kernels need are built on the device.  n_adj_cams may be 0. */
+int ba_set_problem(ba_handle* h, double fx, double fy, double cx, double cy,
+                   int32_t n_adj_cams, int32_t n_pts, int32_t n_obs,
+                   const double* rvec /* [n_adj_cams*3] */, const double* tvec /* [n_adj_cams*3] */,
+                   const double fixed_rvec[3], const double fixed_tvec[3],
+                   const double* pts /* [n_pts*3] */,
+                   const int32_t* obs_cam /* [n_obs] */, const int32_t* obs_pt /* [n_obs] */,
+                   const double* obs_uv /* [n_obs*2] */);
+
+/* Overwrite / read back the parameters of the uploaded problem (same layouts as ba_set_problem).
+ * ba_get_params replaces the unpacking half of _update_map (src/bundle_adjuster.py:220-233). */
+int ba_set_params(ba_handle* h, const double* rvec, const double* tvec, const double* pts);
+int ba_get_params(ba_handle* h, double* rvec, double* tvec, double* pts);
+
+/* r_out[2*n_obs] in the reference's observation order.  Replaces _cost_function
+ * (src/bundle_adjuster.py:24-72). */
+int ba_residuals(ba_handle* h, double* r_out);
+
+/* sum r^2 (what the reference prints and guards on, :165/:176) and 0.5*sum rho(r^2) (SciPy's cost)
+ * at the current parameters, with the Huber threshold `huber_delta`. */
+int ba_cost(ba_handle* h, double huber_delta, double* raw_out, double* robust_out);
+
+/* Analytic Jacobian blocks of the residuals in the reference's parameterisation:
+ * jc_out[n_obs*12]: d r_i / d(rvec_c, t_c) row-major 2x6 (all zero for fixed-keyframe rows),
+ * jp_out[n_obs*6] : d r_i / d X_p       row-major 2x3.
+ * Replaces the 2-point finite differences SciPy takes over jac_sparsity
+ * (src/bundle_adjuster.py:167-171; scipy/optimize/_numdiff.py approx_derivative). */
+int ba_jacobian_blocks(ba_handle* h, double* jc_out, double* jp_out);
+
+/* CSR sparsity pattern of the Jacobian, bit-identical to
+ * _prepare_sparsity_matrix(...).tocsr() (src/bundle_adjuster.py:74-120): indptr[2*n_obs+1],
+ * indices[nnz] with nnz = 18 per adjustable-keyframe observation and 6 per fixed-keyframe one.
+ * Pass indices = NULL to query only nnz (returned through nnz_out). */
+int ba_sparsity_csr(ba_handle* h, int64_t* indptr, int64_t* indices, int64_t* nnz_out);
+
+/* Gradient and Gauss-Newton Hessian blocks at the current parameters in the solver's local camera
+ * coordinates (world-frame twist), for tests: gc[n_adj*6], gp[n_pts*3], U[n_adj*36], V[n_pts*9].
+ * Any pointer may be NULL. */
+int ba_normal_blocks(ba_handle* h, const ba_options* opt, double* gc, double* gp, double* U, double* V);
+
+/* Run the Levenberg-Marquardt loop on the device from the current parameters; the parameters are
+ * replaced by the result.  Replaces the least_squares call at src/bundle_adjuster.py:170-174. */
+int ba_solve(ba_handle* h, const ba_options* opt, ba_stats* stats_out);
+
+/* Per-kernel accounting of the last ba_solve: for each of the `n` kernel kinds (ba_kernel_name(k)),
+ * number of launches and summed CUDA-event milliseconds (only filled when opt->verbose >= 2, which
+ * serialises the launches; otherwise launches only). */
+int ba_kernel_count(void);
+const char* ba_kernel_name(int k);
+int ba_kernel_stats(ba_handle* h, int64_t* launches /* [n] */, double* ms /* [n] */);
+
+/* Thread-local text of the last error returned on this thread. */
+const char* ba_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BA_B200_H */

@@ -1,0 +1,330 @@
+"""CPU oracle for the local-BA hot path of egirgin/bundle_adjustment.  TEST INFRASTRUCTURE ONLY.
+
+This module restates, in numpy + SciPy, what ``/root/reference/src/bundle_adjuster.py`` computes.
+It is the checker for the CUDA path and the timed CPU baseline; only ``tests/``,
+``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` / ``--impl reference`` legs may import
+it.  Nothing under ``bundle_adjustment_b200/`` imports it, and the product path has no CPU fallback.
+
+Parity status: the reference ships no tests or golden vectors, so this
+restatement is PINNED AGAINST THE REFERENCE ITSELF, executed unmodified in the build container:
+``oracle/gen_golden.py`` imports ``BundleAdjuster`` from ``/root/reference/src`` (stubbing only the
+absent ``open3d``/``matplotlib`` imports), runs ``_gather_local_data``, ``_cost_function``,
+``_prepare_sparsity_matrix`` and the full ``run`` on synthetic windows, and commits the outputs under
+``tests/golden/``; ``tests/test_oracle_golden.py`` checks every function below against them.
+
+Third-party arithmetic on the path (not vendored in the reference, no version pinned there):
+``scipy.optimize.least_squares`` (installed 1.18.1: method 'trf' -> ``trf_no_bounds``, 2-point finite
+differences over ``jac_sparsity`` column groups, ``loss='huber'`` per scalar residual with
+``f_scale=1``, ``tr_solver='lsmr'``) - called here exactly as the reference calls it
+(``src/bundle_adjuster.py:170-174``); ``cv2.Rodrigues`` / ``cv2.projectPoints`` (installed 4.13.0) -
+restated as the Rodrigues formula + distortion-free pinhole model.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Sequence, Tuple
+
+import numpy as np
+from scipy.optimize import least_squares
+from scipy.sparse import csr_matrix
+
+DBL_EPS = float(np.finfo(np.float64).eps)
+
+
+# ----------------------------------------------------------------------------------------------
+# rotation helpers (cv2.Rodrigues, both directions)
+# ----------------------------------------------------------------------------------------------
+
+def rodrigues(rvec: np.ndarray) -> np.ndarray:
+    """rvec (...,3) -> R (...,3,3).  Same formula as cv2.Rodrigues (used by the reference at
+    ``src/bundle_adjuster.py:59, 235`` and inside ``cv2.projectPoints`` at ``:67``)."""
+    r = np.asarray(rvec, dtype=np.float64)
+    th = np.sqrt((r * r).sum(-1))
+    small = th < DBL_EPS
+    k = r / np.where(small, 1.0, th)[..., None]
+    c, s = np.cos(th)[..., None, None], np.sin(th)[..., None, None]
+    z = np.zeros_like(th)
+    K = np.stack([np.stack([z, -k[..., 2], k[..., 1]], -1),
+                  np.stack([k[..., 2], z, -k[..., 0]], -1),
+                  np.stack([-k[..., 1], k[..., 0], z], -1)], -2)
+    eye = np.broadcast_to(np.eye(3), K.shape)
+    R = c * eye + (1.0 - c) * (k[..., :, None] * k[..., None, :]) + s * K
+    return np.where(small[..., None, None], eye, R)
+
+
+def rotation_to_rvec(R: np.ndarray) -> np.ndarray:
+    """R (3,3) -> rvec (3,), the inverse map cv2.Rodrigues applies at ``src/bundle_adjuster.py:157``
+    (nearest rotation by SVD first, then axis * angle; the theta ~ pi branch reads the axis off the diagonal)."""
+    R = np.asarray(R, dtype=np.float64).reshape(3, 3)
+    U, _, Vt = np.linalg.svd(R)
+    R = U @ Vt
+    r = np.array([R[2, 1] - R[1, 2], R[0, 2] - R[2, 0], R[1, 0] - R[0, 1]])
+    s = np.sqrt((r * r).sum() * 0.25)
+    c = np.clip((R[0, 0] + R[1, 1] + R[2, 2] - 1.0) * 0.5, -1.0, 1.0)
+    theta = np.arccos(c)
+    if s < 1e-5:
+        if c > 0:
+            return np.zeros(3)
+        t = np.sqrt(np.maximum((np.diag(R) + 1.0) * 0.5, 0.0))
+        t[1] = t[1] * (-1.0 if R[0, 1] < 0 else 1.0)
+        t[2] = t[2] * (-1.0 if R[0, 2] < 0 else 1.0)
+        if abs(t[0]) < abs(t[1]) and abs(t[0]) < abs(t[2]) and ((R[1, 2] > 0) != (t[1] * t[2] > 0)):
+            t[2] = -t[2]
+        return t * (theta / np.sqrt((t * t).sum()))
+    return r * (theta / (2.0 * s))
+
+
+# ----------------------------------------------------------------------------------------------
+# window selection / flattening  (src/bundle_adjuster.py:135-162, 195-218)
+# ----------------------------------------------------------------------------------------------
+
+def select_window(kf_ids: Sequence[int], window_size: int):
+    """-> (local_kf_ids, fixed_kf_id, adjustable_kf_ids) or a skip-reason string.
+    Restates ``run`` lines 135-146: sorted ids, need at least ``window_size`` keyframes, window =
+    ``ids[-(w+1):-1]`` (the newest keyframe is excluded), oldest of the window is fixed."""
+    all_ids = sorted(kf_ids)
+    if len(all_ids) < window_size:
+        return "Not enough keyframes."
+    local = all_ids[-(window_size + 1): -1]
+    if not local[1:]:
+        return "No adjustable keyframes."
+    return local, local[0], local[1:]
+
+
+def gather_local_data(gmap, local_kf_ids):
+    """Restates ``_gather_local_data`` (``src/bundle_adjuster.py:195-218``): observation rows in
+    keyframe-major insertion order, sorted unique map point ids, and the (kf, mp) -> uv dict whose
+    duplicate keys keep the LAST keypoint."""
+    mp_set, observations, kp2d = set(), [], {}
+    for kf_id in local_kf_ids:
+        kf = gmap.keyframes[kf_id]
+        for mp_id, kp_idx in kf.observations:
+            if mp_id in gmap.map_points:
+                mp_set.add(mp_id)
+                observations.append((kf_id, mp_id))
+                kp2d[(kf_id, mp_id)] = kf.keypoints[kp_idx].pt
+    return sorted(mp_set), observations, kp2d
+
+
+def flatten_window(gmap, window_size: int) -> Dict[str, np.ndarray] | str:
+    """Window -> flat arrays in the reference's parameter/observation order.  Returns a skip-reason
+    string where ``run`` would print a skip (``:136-138, 144-146, 151-153``)."""
+    sel = select_window(list(gmap.keyframes.keys()), window_size)
+    if isinstance(sel, str):
+        return sel
+    local, fixed_id, adj_ids = sel
+    mp_ids, observations, kp2d = gather_local_data(gmap, local)
+    if not mp_ids:
+        return "No points in the local window."
+    kf_idx = {k: i for i, k in enumerate(adj_ids)}
+    mp_idx = {m: i for i, m in enumerate(mp_ids)}
+    obs_cam = np.array([kf_idx.get(k, -1) for k, _ in observations], dtype=np.int32)
+    obs_pt = np.array([mp_idx[m] for _, m in observations], dtype=np.int32)
+    obs_uv = np.array([kp2d[o] for o in observations], dtype=np.float64).reshape(-1, 2)
+    rvec = np.array([rotation_to_rvec(gmap.keyframes[i].R) for i in adj_ids]).reshape(-1, 3)
+    tvec = np.array([np.asarray(gmap.keyframes[i].t, dtype=np.float64).ravel() for i in adj_ids]).reshape(-1, 3)
+    pts = np.array([np.asarray(gmap.map_points[i].position, dtype=np.float64).ravel() for i in mp_ids]).reshape(-1, 3)
+    fk = gmap.keyframes[fixed_id]
+    return {"local_kf_ids": np.array(local), "fixed_kf_id": fixed_id, "adj_kf_ids": np.array(adj_ids),
+            "mp_ids": np.array(mp_ids), "obs_cam": obs_cam, "obs_pt": obs_pt, "obs_uv": obs_uv,
+            "rvec": rvec, "tvec": tvec, "pts": pts,
+            "fixed_rvec": rotation_to_rvec(fk.R), "fixed_tvec": np.asarray(fk.t, dtype=np.float64).ravel()}
+
+
+# ----------------------------------------------------------------------------------------------
+# residuals (src/bundle_adjuster.py:24-72), vectorised
+# ----------------------------------------------------------------------------------------------
+
+class Problem:
+    """Constants of one solve: intrinsics, fixed pose, observation arrays (reference order)."""
+
+    def __init__(self, fx, fy, cx, cy, n_cams, n_pts, fixed_rvec, fixed_tvec, obs_cam, obs_pt, obs_uv):
+        self.fx, self.fy, self.cx, self.cy = float(fx), float(fy), float(cx), float(cy)
+        self.n_cams, self.n_pts = int(n_cams), int(n_pts)
+        self.fixed_rvec = np.asarray(fixed_rvec, dtype=np.float64).reshape(3)
+        self.fixed_tvec = np.asarray(fixed_tvec, dtype=np.float64).reshape(3)
+        self.obs_cam = np.asarray(obs_cam, dtype=np.int64)
+        self.obs_pt = np.asarray(obs_pt, dtype=np.int64)
+        self.obs_uv = np.asarray(obs_uv, dtype=np.float64).reshape(-1, 2)
+        self.cam_slot = np.where(self.obs_cam < 0, self.n_cams, self.obs_cam)   # fixed pose in the last slot
+
+    @staticmethod
+    def from_flat(fp) -> "Problem":
+        return Problem(fp.fx, fp.fy, fp.cx, fp.cy, fp.n_cams, fp.n_pts, fp.fixed_rvec, fp.fixed_tvec,
+                       fp.obs_cam, fp.obs_pt, fp.obs_uv)
+
+    @property
+    def n_obs(self):
+        return self.obs_cam.shape[0]
+
+    def unpack(self, x):
+        nc = self.n_cams
+        return x[:3 * nc].reshape(nc, 3), x[3 * nc:6 * nc].reshape(nc, 3), x[6 * nc:].reshape(self.n_pts, 3)
+
+    def camera_points(self, x):
+        rvec, tvec, pts = self.unpack(np.asarray(x, dtype=np.float64))
+        R = rodrigues(np.concatenate([rvec, self.fixed_rvec[None]]))
+        t = np.concatenate([tvec, self.fixed_tvec[None]])
+        P = pts[self.obs_pt]
+        Rg = R[self.cam_slot]
+        xc = Rg[:, :, 0] * P[:, 0:1] + Rg[:, :, 1] * P[:, 1:2] + Rg[:, :, 2] * P[:, 2:3] + t[self.cam_slot]
+        return xc, Rg, P
+
+    def residuals(self, x) -> np.ndarray:
+        """r[2i:2i+2] = observed_uv_i - project(R(rvec_c) X_p + t_c)  (sign and order of ``:68-70``)."""
+        xc, _, _ = self.camera_points(x)
+        out = np.empty((self.n_obs, 2))
+        out[:, 0] = self.obs_uv[:, 0] - (self.fx * xc[:, 0] / xc[:, 2] + self.cx)
+        out[:, 1] = self.obs_uv[:, 1] - (self.fy * xc[:, 1] / xc[:, 2] + self.cy)
+        return out.ravel()
+
+    # -- analytic Jacobian (not in the reference, which differentiates numerically; used to cross-check
+    #    the CUDA blocks independently of finite-difference noise) --------------------------------
+    def jacobian_blocks(self, x) -> Tuple[np.ndarray, np.ndarray]:
+        """d r / d(rvec_c, t_c) as (No,2,6) and d r / d X_p as (No,2,3).  Fixed-keyframe rows have a
+        zero camera block."""
+        rvec, _, _ = self.unpack(np.asarray(x, dtype=np.float64))
+        xc, Rg, P = self.camera_points(x)
+        iz = 1.0 / xc[:, 2]
+        dpi = np.zeros((self.n_obs, 2, 3))
+        dpi[:, 0, 0] = self.fx * iz
+        dpi[:, 0, 2] = -self.fx * xc[:, 0] * iz * iz
+        dpi[:, 1, 1] = self.fy * iz
+        dpi[:, 1, 2] = -self.fy * xc[:, 1] * iz * iz
+        Jp = -np.einsum("nij,njk->nik", dpi, Rg)
+        dR = rodrigues_derivative(np.concatenate([rvec, self.fixed_rvec[None]]))     # (Nc+1, 3(k), 3, 3)
+        dxc = np.einsum("nkij,nj->nik", dR[self.cam_slot], P)                       # d xc / d rvec_k
+        Jc = np.concatenate([-np.einsum("nij,njk->nik", dpi, dxc), -dpi], axis=2)
+        Jc[self.obs_cam < 0] = 0.0
+        return Jc, Jp
+
+
+def rodrigues_derivative(rvec: np.ndarray) -> np.ndarray:
+    """dR/dr_k for k = 0..2, shape (..., 3, 3, 3), by the closed form
+    dR/dr_k = (r_k [r]x + [r x (I - R) e_k]x) R / |r|^2  (Gallego & Yezzi 2015), generators at r = 0."""
+    r = np.asarray(rvec, dtype=np.float64)
+    R = rodrigues(r)
+    th2 = (r * r).sum(-1)
+    out = np.zeros(r.shape[:-1] + (3, 3, 3))
+
+    def skew(v):
+        z = np.zeros_like(v[..., 0])
+        return np.stack([np.stack([z, -v[..., 2], v[..., 1]], -1),
+                         np.stack([v[..., 2], z, -v[..., 0]], -1),
+                         np.stack([-v[..., 1], v[..., 0], z], -1)], -2)
+
+    small = th2 < 1e-24
+    safe = np.where(small, 1.0, th2)
+    for k in range(3):
+        e = np.zeros(3); e[k] = 1.0
+        w = np.cross(r, np.einsum("...ij,j->...i", np.eye(3) - R, e))
+        M = (r[..., k, None, None] * skew(r) + skew(w)) / safe[..., None, None]
+        gen = skew(np.broadcast_to(e, r.shape))
+        out[..., k, :, :] = np.where(small[..., None, None], gen, np.einsum("...ij,...jk->...ik", M, R))
+    return out
+
+
+# ----------------------------------------------------------------------------------------------
+# sparsity pattern (src/bundle_adjuster.py:74-120), vectorised, bit-identical to lil_matrix.tocsr()
+# ----------------------------------------------------------------------------------------------
+
+def sparsity_csr(n_cams: int, n_pts: int, obs_cam: np.ndarray, obs_pt: np.ndarray) -> csr_matrix:
+    obs_cam = np.asarray(obs_cam, dtype=np.int64)
+    obs_pt = np.asarray(obs_pt, dtype=np.int64)
+    n_obs = obs_cam.shape[0]
+    adj = obs_cam >= 0
+    per_row = np.where(adj, 9, 3)
+    nnz_row = np.repeat(per_row, 2)
+    indptr = np.zeros(2 * n_obs + 1, dtype=np.int64)
+    np.cumsum(nnz_row, out=indptr[1:])
+    k3 = np.arange(3)
+    cols_adj = np.concatenate([3 * obs_cam[adj, None] + k3, 3 * n_cams + 3 * obs_cam[adj, None] + k3,
+                               6 * n_cams + 3 * obs_pt[adj, None] + k3], axis=1)          # ascending: rot < trans < point
+    cols_fix = 6 * n_cams + 3 * obs_pt[~adj, None] + k3
+    indices = np.empty(int(indptr[-1]), dtype=np.int64)
+    row0 = indptr[0:-1:2]
+    idx_adj = row0[adj, None] + np.arange(9)
+    indices[idx_adj] = cols_adj
+    indices[idx_adj + 9] = cols_adj
+    idx_fix = row0[~adj, None] + np.arange(3)
+    indices[idx_fix] = cols_fix
+    indices[idx_fix + 3] = cols_fix
+    data = np.ones(indices.shape[0], dtype=np.int64)
+    idx_dtype = np.int32 if max(indptr[-1], 6 * n_cams + 3 * n_pts) < 2**31 else np.int64
+    return csr_matrix((data, indices.astype(idx_dtype), indptr.astype(idx_dtype)),
+                      shape=(2 * n_obs, 6 * n_cams + 3 * n_pts))
+
+
+# ----------------------------------------------------------------------------------------------
+# Huber loss exactly as SciPy applies it (scipy/optimize/_lsq/least_squares.py: huber,
+# construct_loss_function; scipy/optimize/_lsq/common.py: scale_for_robust_loss_function)
+# ----------------------------------------------------------------------------------------------
+
+def huber_rho(z: np.ndarray):
+    z = np.asarray(z, dtype=np.float64)
+    mask = z <= 1.0
+    safe = np.where(mask, 1.0, z)
+    rho0 = np.where(mask, z, 2.0 * np.sqrt(safe) - 1.0)
+    rho1 = np.where(mask, 1.0, safe ** -0.5)
+    rho2 = np.where(mask, 0.0, -0.5 * safe ** -1.5)
+    return rho0, rho1, rho2
+
+
+def huber_cost(r: np.ndarray) -> float:
+    """SciPy's ``cost``: 0.5 * sum(rho(r^2)), f_scale = 1 (per scalar residual)."""
+    return 0.5 * float(huber_rho(np.asarray(r) ** 2)[0].sum())
+
+
+def raw_cost(r: np.ndarray) -> float:
+    """The number the reference prints and guards on: sum(r^2) (``src/bundle_adjuster.py:165, 176``)."""
+    return float((np.asarray(r) ** 2).sum())
+
+
+def robust_scales(r: np.ndarray):
+    """(J_scale, f_scale_factor) of ``scale_for_robust_loss_function``: J rows are multiplied by
+    J_scale = sqrt(max(rho1 + 2 rho2 r^2, EPS)), residuals by rho1 / J_scale."""
+    _, rho1, rho2 = huber_rho(np.asarray(r) ** 2)
+    js = np.maximum(rho1 + 2.0 * rho2 * np.asarray(r) ** 2, DBL_EPS) ** 0.5
+    return js, rho1 / js
+
+
+# ----------------------------------------------------------------------------------------------
+# the solver call (src/bundle_adjuster.py:170-174)
+# ----------------------------------------------------------------------------------------------
+
+def solve_reference(prob: Problem, x0: np.ndarray, *, tight: bool = False, max_nfev: int | None = None,
+                    verbose: int = 0):
+    """The reference's ``least_squares`` call with the vectorised residual (tier T1).  ``tight=True``
+    is tier T1-tight: same objective run to xtol=ftol=gtol=1e-12 (the "converged cost" reference)."""
+    A = sparsity_csr(prob.n_cams, prob.n_pts, prob.obs_cam, prob.obs_pt)
+    if tight:
+        kw = dict(xtol=1e-12, ftol=1e-12, gtol=1e-12, max_nfev=max_nfev or 2000)
+    else:
+        kw = dict(xtol=1e-5, ftol=1e-5, max_nfev=max_nfev or 50)
+    return least_squares(prob.residuals, np.asarray(x0, dtype=np.float64), jac_sparsity=A, loss="huber",
+                         verbose=verbose, **kw)
+
+
+def fd_jacobian(prob: Problem, x: np.ndarray):
+    """The Jacobian SciPy hands the reference's solver: 2-point finite differences over the column
+    groups of the sparsity pattern (scipy/optimize/_numdiff.py approx_derivative)."""
+    from scipy.optimize._numdiff import approx_derivative
+    A = sparsity_csr(prob.n_cams, prob.n_pts, prob.obs_cam, prob.obs_pt)
+    return approx_derivative(prob.residuals, np.asarray(x, dtype=np.float64), method="2-point", sparsity=A)
+
+
+def blocks_from_sparse(J, prob: Problem):
+    """Slice a (2No x n) sparse Jacobian into per-observation (No,2,6) camera and (No,2,3) point blocks."""
+    J = csr_matrix(J)
+    n_obs, nc = prob.n_obs, prob.n_cams
+    Jc = np.zeros((n_obs, 2, 6))
+    Jp = np.zeros((n_obs, 2, 3))
+    Jd = J.toarray() if J.shape[0] * J.shape[1] < 5e7 else None
+    for i in range(n_obs):
+        rows = Jd[2 * i:2 * i + 2] if Jd is not None else J[2 * i:2 * i + 2].toarray()
+        p = prob.obs_pt[i]
+        Jp[i] = rows[:, 6 * nc + 3 * p: 6 * nc + 3 * p + 3]
+        c = prob.obs_cam[i]
+        if c >= 0:
+            Jc[i, :, :3] = rows[:, 3 * c:3 * c + 3]
+            Jc[i, :, 3:] = rows[:, 3 * nc + 3 * c:3 * nc + 3 * c + 3]
+    return Jc, Jp

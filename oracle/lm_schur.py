@@ -1,0 +1,204 @@
+"""numpy restatement of the DEVICE algorithm (LM + Schur complement), TEST INFRASTRUCTURE ONLY.
+
+The reference solves the local-BA objective with SciPy's trust-region-reflective method
+(``src/bundle_adjuster.py:170-174``).  The CUDA path minimises the SAME objective
+(0.5 * sum(huber(r_k^2)) per scalar residual, threshold 1 px) with Levenberg-Marquardt on the Schur
+complement, as BASELINE.json's north_star prescribes.  This file restates that LM loop on the CPU with
+exact (dense Cholesky) solves of the reduced camera system, so the GPU tests can check the kernels'
+intermediate quantities (gradient, Hessian blocks, Schur right-hand side, step, cost trajectory) and not
+only the final cost.  It is not used for timing and not shipped.
+
+Parameterisation (matches ``bundle_adjustment_b200/csrc/ba_kernels.cuh``): the camera increment is the
+world-frame twist (w, v) with  x_cam = R (X + w x X + v) + t,  i.e.  R <- R Exp(w),  t <- t + R v;  the point
+increment is additive.  The stationary points and the cost are those of the reference's
+(rvec, t, X) parameterisation because the map between the two increments is a smooth bijection
+(dw = J_r(rvec) d rvec, v = R^T dt).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import List
+
+import numpy as np
+
+from . import ba_oracle as O
+
+
+def skew(v):
+    z = np.zeros_like(v[..., 0])
+    return np.stack([np.stack([z, -v[..., 2], v[..., 1]], -1),
+                     np.stack([v[..., 2], z, -v[..., 0]], -1),
+                     np.stack([-v[..., 1], v[..., 0], z], -1)], -2)
+
+
+def log_so3(R):
+    """Rotation matrix (3,3) -> rotation vector via the unit quaternion (stable for all angles < pi)."""
+    tr = R[0, 0] + R[1, 1] + R[2, 2]
+    if tr > 0:
+        s = np.sqrt(tr + 1.0) * 2
+        q = np.array([0.25 * s, (R[2, 1] - R[1, 2]) / s, (R[0, 2] - R[2, 0]) / s, (R[1, 0] - R[0, 1]) / s])
+    elif R[0, 0] > R[1, 1] and R[0, 0] > R[2, 2]:
+        s = np.sqrt(1.0 + R[0, 0] - R[1, 1] - R[2, 2]) * 2
+        q = np.array([(R[2, 1] - R[1, 2]) / s, 0.25 * s, (R[0, 1] + R[1, 0]) / s, (R[0, 2] + R[2, 0]) / s])
+    elif R[1, 1] > R[2, 2]:
+        s = np.sqrt(1.0 + R[1, 1] - R[0, 0] - R[2, 2]) * 2
+        q = np.array([(R[0, 2] - R[2, 0]) / s, (R[0, 1] + R[1, 0]) / s, 0.25 * s, (R[1, 2] + R[2, 1]) / s])
+    else:
+        s = np.sqrt(1.0 + R[2, 2] - R[0, 0] - R[1, 1]) * 2
+        q = np.array([(R[1, 0] - R[0, 1]) / s, (R[0, 2] + R[2, 0]) / s, (R[1, 2] + R[2, 1]) / s, 0.25 * s])
+    if q[0] < 0:
+        q = -q
+    n = np.linalg.norm(q[1:])
+    if n < 1e-12:
+        return 2.0 * q[1:]
+    return q[1:] * (2.0 * np.arctan2(n, q[0]) / n)
+
+
+@dataclass
+class Linearization:
+    cost: float                 # 0.5 * sum rho
+    raw: float                  # sum r^2
+    r: np.ndarray               # (No,2) residuals
+    wH: np.ndarray              # (No,2) curvature weights
+    wg: np.ndarray              # (No,2) gradient weights
+    Jp: np.ndarray              # (No,2,3)
+    Jc: np.ndarray              # (No,2,6) local (world-twist) camera Jacobian, zero for fixed-keyframe rows
+    V: np.ndarray               # (Np,3,3)
+    gp: np.ndarray              # (Np,3)
+    U: np.ndarray               # (Nc,6,6)
+    gc: np.ndarray              # (Nc,6)
+
+
+@dataclass
+class LMResult:
+    rvec: np.ndarray
+    tvec: np.ndarray
+    pts: np.ndarray
+    cost: float
+    raw: float
+    iterations: int
+    status: int
+    history: List[dict] = field(default_factory=list)
+
+    def x(self):
+        return np.concatenate([self.rvec.ravel(), self.tvec.ravel(), self.pts.ravel()])
+
+
+def weights(r, mode: str):
+    """(curvature weight, gradient weight) per scalar residual.  'irls': both rho'(r^2);
+    'triggs': SciPy's scale_for_robust_loss_function (max(rho' + 2 rho'' r^2, EPS), rho')."""
+    _, rho1, rho2 = O.huber_rho(r * r)
+    if mode == "irls":
+        return rho1, rho1
+    if mode == "triggs":
+        return np.maximum(rho1 + 2.0 * rho2 * r * r, O.DBL_EPS), rho1
+    if mode == "none":
+        return np.ones_like(r), np.ones_like(r)
+    raise ValueError(mode)
+
+
+def linearize(prob: O.Problem, rvec, tvec, pts, mode="irls", huber=True) -> Linearization:
+    x = np.concatenate([rvec.ravel(), tvec.ravel(), pts.ravel()])
+    xc, Rg, P = prob.camera_points(x)
+    r = prob.residuals(x).reshape(-1, 2)
+    iz = 1.0 / xc[:, 2]
+    dpi = np.zeros((prob.n_obs, 2, 3))
+    dpi[:, 0, 0] = prob.fx * iz
+    dpi[:, 0, 2] = -prob.fx * xc[:, 0] * iz * iz
+    dpi[:, 1, 1] = prob.fy * iz
+    dpi[:, 1, 2] = -prob.fy * xc[:, 1] * iz * iz
+    Jp = -np.einsum("nij,njk->nik", dpi, Rg)
+    G = np.concatenate([-skew(P), np.broadcast_to(np.eye(3), (prob.n_obs, 3, 3))], axis=2)   # (No,3,6)
+    Jc = np.einsum("nij,njk->nik", Jp, G)
+    adj = prob.obs_cam >= 0
+    Jc[~adj] = 0.0
+    wH, wg = weights(r, mode if huber else "none")
+    cost = O.huber_cost(r.ravel()) if huber else 0.5 * float((r * r).sum())
+    V = np.zeros((prob.n_pts, 3, 3)); gp = np.zeros((prob.n_pts, 3))
+    U = np.zeros((prob.n_cams, 6, 6)); gc = np.zeros((prob.n_cams, 6))
+    np.add.at(V, prob.obs_pt, np.einsum("nki,nk,nkj->nij", Jp, wH, Jp))
+    np.add.at(gp, prob.obs_pt, np.einsum("nki,nk->ni", Jp, wg * r))
+    np.add.at(U, prob.obs_cam[adj], np.einsum("nki,nk,nkj->nij", Jc[adj], wH[adj], Jc[adj]))
+    np.add.at(gc, prob.obs_cam[adj], np.einsum("nki,nk->ni", Jc[adj], (wg * r)[adj]))
+    return Linearization(cost, float((r * r).sum()), r, wH, wg, Jp, Jc, V, gp, U, gc)
+
+
+def schur_step(prob: O.Problem, lin: Linearization, lam: float, dmin=1e-6, dmax=1e32):
+    """Solve (H + lam D) delta = -g exactly through the Schur complement.  D = clamp(diag(H))."""
+    adj = prob.obs_cam >= 0
+    nc = prob.n_cams
+    Dp = np.clip(np.einsum("nii->ni", lin.V), dmin, dmax)
+    Dc = np.clip(np.einsum("nii->ni", lin.U), dmin, dmax)
+    Vd = lin.V + lam * np.einsum("ni,ij->nij", Dp, np.eye(3))
+    Vinv = np.linalg.inv(Vd)
+    E = np.einsum("nki,nk,nkj->nij", lin.Jc[adj], lin.wH[adj], lin.Jp[adj])          # (Na,6,3)
+    ca, pa = prob.obs_cam[adj], prob.obs_pt[adj]
+    S = np.zeros((6 * nc, 6 * nc))
+    for c in range(nc):
+        S[6 * c:6 * c + 6, 6 * c:6 * c + 6] = lin.U[c] + lam * np.diag(Dc[c])
+    EV = np.einsum("nij,njk->nik", E, Vinv[pa])                                      # (Na,6,3)
+    rhs = -lin.gc.copy()
+    np.add.at(rhs, ca, np.einsum("nij,nj->ni", EV, lin.gp[pa]))
+    # S -= sum_p E_cp Vinv E_c'p^T over camera pairs sharing a point
+    order = np.argsort(pa, kind="stable")
+    pa_s, ca_s, E_s, EV_s = pa[order], ca[order], E[order], EV[order]
+    bounds = np.flatnonzero(np.diff(pa_s)) + 1
+    starts = np.concatenate([[0], bounds]); ends = np.concatenate([bounds, [pa_s.size]])
+    for a, b in zip(starts, ends):
+        for i in range(a, b):
+            for j in range(a, b):
+                S[6 * ca_s[i]:6 * ca_s[i] + 6, 6 * ca_s[j]:6 * ca_s[j] + 6] -= EV_s[i] @ E_s[j].T
+    dc = np.linalg.solve(S, rhs.ravel()).reshape(nc, 6)
+    w = lin.gp.copy()
+    np.add.at(w, pa, np.einsum("nij,ni->nj", E, dc[ca]))
+    dp = -np.einsum("nij,nj->ni", Vinv, w)
+    model = -(np.sum(lin.gc * dc) + np.sum(lin.gp * dp)) - 0.5 * (
+        np.einsum("ni,nij,nj->", dc, lin.U, dc) + np.einsum("ni,nij,nj->", dp, lin.V, dp)
+        + 2.0 * np.einsum("ni,nij,nj->", dc[ca], E, dp[pa]))
+    return dc, dp, float(model), {"rhs": rhs, "S": S, "Dp": Dp, "Dc": Dc, "Vinv": Vinv}
+
+
+def retract(rvec, tvec, pts, dc, dp):
+    R = O.rodrigues(rvec)
+    Rn = np.einsum("nij,njk->nik", R, O.rodrigues(dc[:, :3]))
+    rv = np.array([log_so3(Rn[i]) for i in range(Rn.shape[0])]).reshape(-1, 3)
+    tv = tvec + np.einsum("nij,nj->ni", R, dc[:, 3:])
+    return rv, tv, pts + dp
+
+
+def solve(prob: O.Problem, rvec, tvec, pts, *, mode="irls", huber=True, max_iters=100, lam0=1e-4, ftol=1e-12,
+          gtol=1e-10, lam_min=1e-12, lam_max=1e16, verbose=False) -> LMResult:
+    """Levenberg-Marquardt with Nielsen's damping update (the rule the device loop uses)."""
+    rvec, tvec, pts = rvec.copy(), tvec.copy(), pts.copy()
+    lam, nu = lam0, 2.0
+    lin = linearize(prob, rvec, tvec, pts, mode, huber)
+    hist, status, it = [], 0, 0
+    for it in range(1, max_iters + 1):
+        gmax = max(np.abs(lin.gc).max() if lin.gc.size else 0.0, np.abs(lin.gp).max())
+        if gmax < gtol:
+            status = 1
+            break
+        dc, dp, model, _ = schur_step(prob, lin, lam)
+        rv, tv, pn = retract(rvec, tvec, pts, dc, dp)
+        lin_new = linearize(prob, rv, tv, pn, mode, huber)
+        rho = (lin.cost - lin_new.cost) / model if model > 0 else -1.0
+        accepted = bool(np.isfinite(lin_new.cost) and rho > 0)
+        hist.append(dict(it=it, lam=lam, cost=lin.cost, cost_new=lin_new.cost, model=model, rho=rho,
+                         accepted=accepted, gmax=gmax))
+        if verbose:
+            print(hist[-1])
+        if accepted:
+            dcost = lin.cost - lin_new.cost
+            rvec, tvec, pts, lin = rv, tv, pn, lin_new
+            lam = max(lam * max(1.0 / 3.0, 1.0 - (2.0 * rho - 1.0) ** 3), lam_min)
+            nu = 2.0
+            if dcost <= ftol * lin.cost:
+                status = 2
+                break
+        else:
+            lam *= nu
+            nu *= 2.0
+            if lam > lam_max:
+                status = 5
+                break
+    return LMResult(rvec, tvec, pts, lin.cost, lin.raw, it, status, hist)
