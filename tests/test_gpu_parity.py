@@ -1,0 +1,335 @@
+"""GPU (B200): the CUDA path, called through the C ABI, against the oracle.
+
+Tolerances are the ones BASELINE.json's north_star states: residuals 1e-9 relative, Jacobian blocks 1e-5
+relative to the reference's finite-difference Jacobian, converged cost 1e-6 relative, index / sparsity
+construction bit-exact.
+"""
+import numpy as np
+import pytest
+
+from conftest import golden_names, load_golden, mirror_map, oracle_problem
+from bundle_adjustment_b200 import FlatSolver, synthetic as S
+from oracle import ba_oracle as O, lm_schur as L
+
+pytestmark = pytest.mark.gpu
+
+
+def _golden_problem(name):
+    g, spec = load_golden(name)
+    flat = O.flatten_window(mirror_map(spec), int(g["window_size"]))
+    return g, spec, flat, oracle_problem(spec, flat)
+
+
+def _upload(solver, prob, flat):
+    solver.set_problem(prob.fx, prob.fy, prob.cx, prob.cy, flat["rvec"], flat["tvec"], flat["fixed_rvec"],
+                       flat["fixed_tvec"], flat["pts"], flat["obs_cam"], flat["obs_pt"], flat["obs_uv"])
+
+
+# ------------------------------------------------------------------------------------------------
+# residuals / cost / Jacobian / sparsity
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", golden_names())
+def test_residuals_against_reference_golden(gpu_solver, name):
+    """ba_residuals == the reference's _cost_function output stored in the fixture (1e-9 relative)."""
+    g, spec, flat, prob = _golden_problem(name)
+    _upload(gpu_solver, prob, flat)
+    r = gpu_solver.residuals()
+    assert r.shape == g["r0"].shape
+    assert np.linalg.norm(r - g["r0"]) <= 1e-9 * np.linalg.norm(g["r0"])
+    raw, rob = gpu_solver.cost()
+    assert abs(raw - float(g["initial_cost"])) <= 1e-9 * float(g["initial_cost"])
+    assert abs(rob - O.huber_cost(g["r0"])) <= 1e-9 * O.huber_cost(g["r0"])
+    # and at the reference's own solution
+    gpu_solver.set_x(g["res_x"])
+    r = gpu_solver.residuals()
+    assert np.linalg.norm(r - g["res_fun"]) <= 1e-9 * np.linalg.norm(g["res_fun"])
+    raw, rob = gpu_solver.cost()
+    assert abs(rob - float(g["res_cost"])) <= 1e-9 * float(g["res_cost"])          # SciPy's res.cost
+    assert abs(raw - float(g["final_cost"])) <= 1e-9 * float(g["final_cost"])
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_sparsity_bit_exact(gpu_solver, name):
+    g, spec, flat, prob = _golden_problem(name)
+    _upload(gpu_solver, prob, flat)
+    indptr, indices, shape = gpu_solver.sparsity_csr()
+    assert tuple(shape) == tuple(g["sp_shape"])
+    assert np.array_equal(indptr, g["sp_indptr"]) and np.array_equal(indices, g["sp_indices"])
+
+
+@pytest.mark.parametrize("seed,shape", [(1, (6, 150, 600)), (2, (30, 2000, 9000)), (3, (3, 40, 90))])
+def test_residuals_and_jacobian_blocks(gpu_solver, seed, shape):
+    fp = S.make_flat_problem(*shape, seed=seed)
+    prob = O.Problem.from_flat(fp)
+    x0 = fp.x0()
+    gpu_solver.set_flat(fp)
+    r, r_ref = gpu_solver.residuals(), prob.residuals(x0)
+    assert np.linalg.norm(r - r_ref) <= 1e-9 * np.linalg.norm(r_ref)
+    jc, jp = gpu_solver.jacobian_blocks()
+    Jc, Jp = prob.jacobian_blocks(x0)                         # analytic oracle: tight
+    assert np.abs(jc - Jc).max() <= 1e-10 * np.abs(Jc).max()
+    assert np.abs(jp - Jp).max() <= 1e-10 * np.abs(Jp).max()
+    assert np.all(jc[fp.obs_cam < 0] == 0.0)
+    if fp.n_obs <= 1000:                                      # the reference's Jacobian: SciPy 2-point FD over jac_sparsity
+        Jc_fd, Jp_fd = O.blocks_from_sparse(O.fd_jacobian(prob, x0), prob)
+        assert np.abs(jc - Jc_fd).max() <= 1e-5 * np.abs(Jc_fd).max()
+        assert np.abs(jp - Jp_fd).max() <= 1e-5 * np.abs(Jp_fd).max()
+    ip, ii, shp = gpu_solver.sparsity_csr()
+    A = O.sparsity_csr(prob.n_cams, prob.n_pts, prob.obs_cam, prob.obs_pt)
+    assert np.array_equal(ip, A.indptr) and np.array_equal(ii, A.indices) and tuple(shp) == A.shape
+
+
+def test_jacobian_small_and_large_rotations(gpu_solver):
+    """rvec = 0 exactly, tiny, and close to pi: the analytic d/d rvec must stay accurate (series / closed form)."""
+    fp = S.make_flat_problem(8, 100, 400, seed=5)
+    rng = np.random.default_rng(0)
+    fp.rvec[0] = 0.0
+    fp.rvec[1] = rng.normal(0, 1e-9, 3)
+    fp.rvec[2] = rng.normal(0, 1e-4, 3)
+    fp.rvec[3] = np.array([0.0, 0.0, 3.0])
+    prob = O.Problem.from_flat(fp)
+    gpu_solver.set_flat(fp)
+    r = gpu_solver.residuals()
+    assert np.linalg.norm(r - prob.residuals(fp.x0())) <= 1e-9 * np.linalg.norm(r)
+    jc, jp = gpu_solver.jacobian_blocks()
+    from scipy.optimize._numdiff import approx_derivative
+    J = approx_derivative(prob.residuals, fp.x0(), method="3-point")
+    Jc_n, Jp_n = O.blocks_from_sparse(J, prob)
+    assert np.abs(jc - Jc_n).max() <= 1e-6 * np.abs(Jc_n).max()
+    assert np.abs(jp - Jp_n).max() <= 1e-6 * np.abs(Jp_n).max()
+
+
+@pytest.mark.parametrize("mode", ["irls", "triggs", "none"])
+def test_normal_equation_blocks(gpu_solver, mode):
+    """Schur-assembly inputs (U, V, g_c, g_p) against the CPU restatement, all robust modes."""
+    fp = S.make_flat_problem(9, 500, 2200, seed=8)
+    prob = O.Problem.from_flat(fp)
+    gpu_solver.set_flat(fp)
+    nb = gpu_solver.normal_blocks(robust_mode=mode)
+    lin = L.linearize(prob, fp.rvec, fp.tvec, fp.pts, mode=mode, huber=(mode != "none"))
+    for k, ref in (("gc", lin.gc), ("gp", lin.gp), ("U", lin.U), ("V", lin.V)):
+        assert np.abs(nb[k] - ref).max() <= 1e-11 * np.abs(ref).max(), k
+
+
+def test_triggs_scaling_is_scipys(gpu_solver):
+    """In 'triggs' mode J^T W J uses SciPy's scale_for_robust_loss_function factors."""
+    fp = S.make_flat_problem(4, 60, 200, seed=12)
+    prob = O.Problem.from_flat(fp)
+    x0 = fp.x0()
+    gpu_solver.set_flat(fp)
+    nb = gpu_solver.normal_blocks(robust_mode="triggs")
+    r = prob.residuals(x0)
+    js, fs = O.robust_scales(r)
+    _, Jp = prob.jacobian_blocks(x0)
+    Jp_s = Jp * js.reshape(-1, 2, 1)
+    V = np.zeros((prob.n_pts, 3, 3)); gp = np.zeros((prob.n_pts, 3))
+    np.add.at(V, prob.obs_pt, np.einsum("nki,nkj->nij", Jp_s, Jp_s))
+    np.add.at(gp, prob.obs_pt, np.einsum("nki,nk->ni", Jp_s, (fs * r).reshape(-1, 2)))
+    assert np.abs(nb["V"] - V).max() <= 1e-11 * np.abs(V).max()
+    assert np.abs(nb["gp"] - gp).max() <= 1e-11 * np.abs(gp).max()
+
+
+# ------------------------------------------------------------------------------------------------
+# the LM loop
+# ------------------------------------------------------------------------------------------------
+def test_lm_iterates_match_cpu_restatement(gpu_solver):
+    """With a tight PCG tolerance the device loop takes the same steps as the exact-solve restatement."""
+    fp = S.make_flat_problem(6, 300, 1200, seed=3)
+    prob = O.Problem.from_flat(fp)
+    gpu_solver.set_flat(fp)
+    st = gpu_solver.solve(max_iters=6, pcg_tol=1e-12, pcg_max_iters=500, ftol=0.0, xtol=0.0, gtol=0.0)
+    ref = L.solve(prob, fp.rvec, fp.tvec, fp.pts, max_iters=6, ftol=0.0, gtol=0.0)
+    assert st["iterations"] == 6
+    assert abs(st["final_cost"] - ref.cost) <= 1e-9 * ref.cost
+    assert abs(st["final_raw_cost"] - ref.raw) <= 1e-9 * ref.raw
+    assert np.abs(gpu_solver.get_x() - ref.x()).max() <= 1e-8
+
+
+@pytest.mark.parametrize("name", ["window_short", "window_cfg1", "global_cfg1"])
+def test_converged_cost_against_reference_objective(gpu_solver, name):
+    """Same objective as the reference (Huber, 1 px, per coordinate).  Run to convergence the device
+    solver must (a) end at or below every cost the reference's own solver reached (reference settings
+    and 2000 evaluations of them), (b) on the small window, match SciPy's converged optimum (analytic
+    Jacobian + exact trust-region sub-problems, tier T2) to 1e-6 relative."""
+    g, spec, flat, prob = _golden_problem(name)
+    _upload(gpu_solver, prob, flat)
+    st = gpu_solver.solve(max_iters=1500, ftol=1e-13, xtol=0.0, gtol=1e-9, pcg_tol=1e-3, pcg_max_iters=300)
+    assert st["final_cost"] <= float(g["res_cost"])
+    assert st["final_cost"] <= float(g["tight_cost"])
+    x = gpu_solver.get_x()
+    assert abs(O.huber_cost(prob.residuals(x)) - st["final_cost"]) <= 1e-9 * st["final_cost"]
+    if name == "window_short":
+        conv = O.solve_converged(prob, g["x0"])
+        assert abs(st["final_cost"] - conv.cost) <= 1e-6 * conv.cost
+        # same optimum: poses and points agree once the free scale (one fixed camera leaves it open) is aligned
+        nc = prob.n_cams
+        c_fix = -O.rodrigues(flat["fixed_rvec"]).T @ flat["fixed_tvec"]
+        def centred(xv):
+            pts = xv[6 * nc:].reshape(-1, 3) - c_fix
+            return pts
+        a, b = centred(x), centred(conv.x)
+        na, nb_ = np.linalg.norm(a, axis=1), np.linalg.norm(b, axis=1)
+        scale = float(np.median(nb_ / na))                 # robust: a few low-parallax points sit far out in depth
+        assert abs(scale - 1.0) < 5e-2
+        err = np.linalg.norm(a * scale - b, axis=1) / nb_
+        assert np.median(err) <= 1e-2 and np.mean(err <= 5e-2) >= 0.9, (np.median(err), np.mean(err <= 5e-2))
+        assert np.abs(x[:3 * nc] - conv.x[:3 * nc]).max() <= 1e-3
+
+
+def test_solver_beats_reference_settings_on_bal_shape(gpu_solver):
+    """Config 2 (50 cameras / 20 k points / 100 k observations): device result vs the reference's
+    least_squares call with the reference's tolerances (tier T1), same x0."""
+    fp = S.make_named_problem("bal50")
+    prob = O.Problem.from_flat(fp)
+    ref = O.solve_reference(prob, fp.x0())
+    gpu_solver.set_flat(fp)
+    st = gpu_solver.solve()
+    assert st["final_cost"] <= ref.cost
+    assert st["final_raw_cost"] < st["initial_raw_cost"]
+    assert abs(st["initial_cost"] - O.huber_cost(prob.residuals(fp.x0()))) <= 1e-9 * st["initial_cost"]
+    x = gpu_solver.get_x()
+    assert abs(O.huber_cost(prob.residuals(x)) - st["final_cost"]) <= 1e-9 * st["final_cost"]
+
+
+def test_bitwise_reproducible(gpu_solver):
+    """No floating-point atomics: two solves of the same problem give identical bits."""
+    fp = S.make_flat_problem(40, 6000, 30000, seed=4)
+    outs = []
+    for _ in range(2):
+        gpu_solver.set_flat(fp)
+        st = gpu_solver.solve(max_iters=8)
+        outs.append((gpu_solver.get_x(), st["final_cost"], st["pcg_iterations"]))
+    assert np.array_equal(outs[0][0], outs[1][0])
+    assert outs[0][1] == outs[1][1] and outs[0][2] == outs[1][2]
+
+
+def test_observation_order_does_not_matter(gpu_solver):
+    """The device builds its own point-major / camera-major orders: permuting the input rows only
+    permutes the residual vector."""
+    fp = S.make_flat_problem(7, 400, 1700, seed=6)
+    gpu_solver.set_flat(fp)
+    r = gpu_solver.residuals().reshape(-1, 2)
+    st = gpu_solver.solve(max_iters=10)
+    perm = np.random.default_rng(0).permutation(fp.n_obs)
+    fp2 = S.FlatProblem(fp.fx, fp.fy, fp.cx, fp.cy, fp.rvec, fp.tvec, fp.fixed_rvec, fp.fixed_tvec, fp.pts,
+                        fp.obs_cam[perm], fp.obs_pt[perm], fp.obs_uv[perm])
+    gpu_solver.set_flat(fp2)
+    assert np.array_equal(gpu_solver.residuals().reshape(-1, 2), r[perm])
+    st2 = gpu_solver.solve(max_iters=10)
+    assert abs(st2["final_cost"] - st["final_cost"]) <= 1e-9 * st["final_cost"]
+
+
+# ------------------------------------------------------------------------------------------------
+# edge cases
+# ------------------------------------------------------------------------------------------------
+def test_points_without_observations_and_single_observation_tracks(gpu_solver):
+    fp = S.make_flat_problem(5, 120, 400, seed=13)
+    keep = np.ones(fp.n_obs, dtype=bool)
+    keep[fp.obs_pt == 7] = False                                  # point 7: no observations at all
+    first = np.flatnonzero(fp.obs_pt == 11)
+    keep[first[1:]] = False                                       # point 11: a single observation
+    fp2 = S.FlatProblem(fp.fx, fp.fy, fp.cx, fp.cy, fp.rvec, fp.tvec, fp.fixed_rvec, fp.fixed_tvec, fp.pts,
+                        fp.obs_cam[keep], fp.obs_pt[keep], fp.obs_uv[keep])
+    prob = O.Problem.from_flat(fp2)
+    gpu_solver.set_flat(fp2)
+    r = gpu_solver.residuals()
+    assert np.linalg.norm(r - prob.residuals(fp2.x0())) <= 1e-9 * np.linalg.norm(r)
+    st = gpu_solver.solve(max_iters=20)
+    assert st["final_cost"] < st["initial_cost"]
+    _, _, pts = gpu_solver.get_params()
+    assert np.array_equal(pts[7], fp.pts[7])                      # untouched: zero gradient
+
+
+def test_duplicate_observations_keep_both_rows(gpu_solver):
+    """Reference quirk (src/bundle_adjuster.py:216): a (keyframe, point) pair listed twice gives two
+    residual rows with the same uv - the device must treat them as two observations."""
+    fp = S.make_flat_problem(5, 100, 350, seed=14)
+    dup = np.array([3, 50, 51])
+    cam = np.concatenate([fp.obs_cam, fp.obs_cam[dup]])
+    pt = np.concatenate([fp.obs_pt, fp.obs_pt[dup]])
+    uv = np.concatenate([fp.obs_uv, fp.obs_uv[dup]])
+    fp2 = S.FlatProblem(fp.fx, fp.fy, fp.cx, fp.cy, fp.rvec, fp.tvec, fp.fixed_rvec, fp.fixed_tvec, fp.pts, cam, pt, uv)
+    prob = O.Problem.from_flat(fp2)
+    gpu_solver.set_flat(fp2)
+    nb = gpu_solver.normal_blocks()
+    lin = L.linearize(prob, fp2.rvec, fp2.tvec, fp2.pts)
+    assert np.abs(nb["V"] - lin.V).max() <= 1e-11 * np.abs(lin.V).max()
+    assert np.abs(nb["U"] - lin.U).max() <= 1e-11 * np.abs(lin.U).max()
+
+
+def test_only_fixed_camera_observations_structure_only(gpu_solver):
+    """n_adj_cams = 0: every observation belongs to the fixed keyframe; points are still refined."""
+    fp = S.make_flat_problem(3, 50, 120, seed=15)
+    sel = fp.obs_cam < 0
+    fp2 = S.FlatProblem(fp.fx, fp.fy, fp.cx, fp.cy, np.zeros((0, 3)), np.zeros((0, 3)), fp.fixed_rvec, fp.fixed_tvec,
+                        fp.pts, fp.obs_cam[sel], fp.obs_pt[sel], fp.obs_uv[sel])
+    gpu_solver.set_flat(fp2)
+    st = gpu_solver.solve(max_iters=10)
+    assert st["final_cost"] <= st["initial_cost"]
+
+
+def test_long_track_spanning_tiles(gpu_solver):
+    """A point seen by several hundred cameras: its observations overflow the nominal 256-observation tile."""
+    n_cams, n_pts = 700, 40
+    rng = np.random.default_rng(3)
+    base = S.make_flat_problem(n_cams, n_pts, n_pts * 2, seed=16)
+    truth = base.truth
+    cam = np.concatenate([base.obs_cam, np.arange(-1, n_cams - 1)])
+    pt = np.concatenate([base.obs_pt, np.full(n_cams, 5)])
+    rv = np.concatenate([base.fixed_rvec[None], truth["rvec"]]); tv = np.concatenate([base.fixed_tvec[None], truth["tvec"]])
+    uv5 = S.project(rv, tv, np.repeat(truth["pts"][5][None], n_cams, 0)) + rng.normal(0, 0.5, (n_cams, 2))
+    uv = np.concatenate([base.obs_uv, uv5.astype(np.float32).astype(np.float64)])
+    fp = S.FlatProblem(base.fx, base.fy, base.cx, base.cy, base.rvec, base.tvec, base.fixed_rvec, base.fixed_tvec,
+                       base.pts, cam.astype(np.int32), pt.astype(np.int32), uv)
+    prob = O.Problem.from_flat(fp)
+    gpu_solver.set_flat(fp)
+    nb = gpu_solver.normal_blocks()
+    lin = L.linearize(prob, fp.rvec, fp.tvec, fp.pts)
+    assert np.abs(nb["V"] - lin.V).max() <= 1e-11 * np.abs(lin.V).max()
+    assert np.abs(nb["gp"] - lin.gp).max() <= 1e-11 * np.abs(lin.gp).max()
+    st = gpu_solver.solve(max_iters=5)
+    assert np.isfinite(st["final_cost"]) and st["final_cost"] <= st["initial_cost"]
+
+
+def test_error_reporting(gpu_solver):
+    from bundle_adjustment_b200._capi import BaError
+    fp = S.make_flat_problem(4, 50, 150, seed=17)
+    bad = fp.obs_pt.copy(); bad[3] = fp.n_pts
+    with pytest.raises(BaError, match="out of range"):
+        gpu_solver.set_problem(fp.fx, fp.fy, fp.cx, fp.cy, fp.rvec, fp.tvec, fp.fixed_rvec, fp.fixed_tvec, fp.pts,
+                               fp.obs_cam, bad, fp.obs_uv)
+    with pytest.raises(BaError):                       # state was invalidated by the failed upload
+        gpu_solver.residuals()
+    pts = fp.pts.copy(); pts[0] = np.nan
+    gpu_solver.set_problem(fp.fx, fp.fy, fp.cx, fp.cy, fp.rvec, fp.tvec, fp.fixed_rvec, fp.fixed_tvec, pts,
+                           fp.obs_cam, fp.obs_pt, fp.obs_uv)
+    with pytest.raises(BaError, match="not finite"):   # SciPy raises ValueError at the same place
+        gpu_solver.solve()
+
+
+# ------------------------------------------------------------------------------------------------
+# full-size, size-independent properties (configs 3 and 4)
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["ladybug", "venice"])
+def test_full_size_properties(gpu_solver, name):
+    fp = S.make_named_problem(name, keep_truth=False)
+    gpu_solver.set_flat(fp)
+    # (1) the device's reduced cost equals the cost of the residual vector it returns
+    r = gpu_solver.residuals()
+    raw, rob = gpu_solver.cost()
+    assert abs(raw - float((r * r).sum())) <= 1e-10 * raw
+    assert abs(rob - O.huber_cost(r)) <= 1e-10 * rob
+    # (2) a sampled slice of the residuals equals the oracle's on the same rows
+    prob = O.Problem.from_flat(fp)
+    sub = slice(0, fp.n_obs, max(1, fp.n_obs // 50_000))
+    prob_sub = O.Problem(fp.fx, fp.fy, fp.cx, fp.cy, fp.n_cams, fp.n_pts, fp.fixed_rvec, fp.fixed_tvec,
+                         fp.obs_cam[sub], fp.obs_pt[sub], fp.obs_uv[sub])
+    r_sub = prob_sub.residuals(fp.x0()).reshape(-1, 2)
+    assert np.linalg.norm(r.reshape(-1, 2)[sub] - r_sub) <= 1e-9 * np.linalg.norm(r_sub)
+    # (3) LM: cost never increases, accepted steps only, result reproducible and consistent
+    st = gpu_solver.solve(max_iters=12)
+    assert st["final_cost"] < 0.1 * st["initial_cost"]
+    r = gpu_solver.residuals()
+    assert abs(O.huber_cost(r) - st["final_cost"]) <= 1e-9 * st["final_cost"]
+    assert abs(float((r * r).sum()) - st["final_raw_cost"]) <= 1e-9 * st["final_raw_cost"]
+    del prob

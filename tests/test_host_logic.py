@@ -1,0 +1,143 @@
+"""CPU: host-side logic of the drop-in (no compute calls), the C-ABI library's exports, sharding."""
+import ctypes
+import io
+import os
+import re
+from contextlib import redirect_stdout
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, golden_names, load_golden, mirror_map
+from bundle_adjustment_b200 import BundleAdjuster, _capi, geometry, sharding, synthetic as S
+from bundle_adjustment_b200.map_structures import Keyframe, KeyPoint, Map, MapPoint
+from oracle import ba_oracle as O
+
+
+def test_library_exports_every_declared_symbol():
+    """libba_b200.so loads without a GPU and exports exactly what include/ba_b200.h declares."""
+    header = open(os.path.join(ROOT, "include", "ba_b200.h")).read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    declared = set(re.findall(r"\b(ba_[a-z_0-9]+)\s*\(", header))
+    assert declared, "no declarations parsed"
+    assert declared == set(_capi.SYMBOLS), (declared ^ set(_capi.SYMBOLS))
+    assert os.path.isfile(_capi.LIB_PATH), "build the library first (python -m bundle_adjustment_b200.build)"
+    lib = ctypes.CDLL(_capi.LIB_PATH)
+    for name in declared:
+        assert hasattr(lib, name), name
+
+
+def test_default_options_without_gpu():
+    o = _capi.Options()
+    _capi.lib().ba_default_options(ctypes.byref(o))
+    assert o.max_iters == 50 and o.huber_delta == 1.0 and o.robust_mode == _capi.ROBUST["irls"]
+    assert o.precond == _capi.PRECOND["schur_jacobi"] and o.pcg_max_iters > 0
+
+
+def test_struct_sizes_match_header():
+    # int32 + 3 doubles ... layout must match the C structs (natural alignment)
+    assert ctypes.sizeof(_capi.Options) % 8 == 0
+    assert ctypes.sizeof(_capi.Stats) == 6 * 4 + 7 * 8 + 8 * 8
+
+
+def test_geometry_matches_oracle():
+    rng = np.random.default_rng(1)
+    for _ in range(100):
+        r = rng.normal(0, 1, 3) * rng.choice([1e-10, 1e-2, 1.0, 2.5])
+        R = geometry.rvec_to_matrix(r)
+        assert np.abs(R - O.rodrigues(r)).max() < 1e-15
+        assert np.abs(geometry.matrix_to_rvec(R) - O.rotation_to_rvec(R)).max() < 1e-13
+        if np.linalg.norm(r) < 3.0:          # beyond pi the vector wraps
+            assert np.abs(geometry.matrix_to_rvec(R) - r).max() < 1e-9
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_gather_and_indexing_match_reference(name):
+    g, spec = load_golden(name)
+    gmap = mirror_map(spec)
+    adj = BundleAdjuster(spec["camera_matrix"], window_size=int(g["window_size"]))
+    mp_ids, obs, kp2d = adj._gather_local_data(gmap, g["local_kf_ids"].tolist())
+    assert mp_ids == g["mp_ids"].tolist()
+    assert [o[0] for o in obs] == g["obs_kf"].tolist() and [o[1] for o in obs] == g["obs_mp"].tolist()
+    assert np.array_equal(np.array([kp2d[o] for o in obs]), g["obs_uv"])
+    cam, pt, uv = adj._index_observations(g["adj_kf_ids"].tolist(), mp_ids, obs, kp2d, int(g["fixed_kf_id"]))
+    flat = O.flatten_window(gmap, int(g["window_size"]))
+    assert np.array_equal(cam, flat["obs_cam"]) and np.array_equal(pt, flat["obs_pt"]) and np.array_equal(uv, flat["obs_uv"])
+
+
+def test_update_map_shapes_and_values():
+    g, spec = load_golden("window_short")
+    gmap = mirror_map(spec)
+    adj = BundleAdjuster(spec["camera_matrix"])
+    adj._update_map(gmap, g["res_x"], g["adj_kf_ids"].tolist(), g["mp_ids"].tolist())
+    all_ids = sorted(gmap.keyframes)
+    R = np.array([gmap.keyframes[i].R for i in all_ids])
+    t = np.array([gmap.keyframes[i].t for i in all_ids])
+    pos = np.array([gmap.map_points[i].position for i in sorted(gmap.map_points)])
+    assert t.shape[1:] == (3, 1) and pos.shape[1:] == (3, 1)
+    assert np.abs(R - g["out_kf_R"]).max() < 1e-13        # cv2.Rodrigues vs numpy
+    assert np.array_equal(t, g["out_kf_t"]) and np.array_equal(pos, g["out_mp_pos"])
+
+
+def test_run_skips_like_the_reference():
+    K = S.CAMERA_MATRIX
+    adj = BundleAdjuster(K, window_size=5)
+    gmap = Map()
+    for i in range(3):
+        gmap.add_keyframe(Keyframe(id=i, R=np.eye(3), t=np.zeros((3, 1))))
+    out = io.StringIO()
+    with redirect_stdout(out):
+        assert adj.run(gmap) is None
+    assert "LBA Skipped: Not enough keyframes." in out.getvalue()
+    adj.window_size = 1                    # window = ids[-2:-1] -> one keyframe, nothing adjustable
+    out = io.StringIO()
+    with redirect_stdout(out):
+        adj.run(gmap)
+    assert "LBA Skipped: No adjustable keyframes." in out.getvalue()
+    adj.window_size = 2                    # adjustable keyframes but no observations at all
+    out = io.StringIO()
+    with redirect_stdout(out):
+        adj.run(gmap)
+    assert "LBA Skipped: No points in the local window." in out.getvalue()
+
+
+def test_map_rejects_duplicate_ids():
+    gmap = Map()
+    gmap.add_keyframe(Keyframe(id=0, R=np.eye(3), t=np.zeros((3, 1))))
+    with pytest.raises(ValueError):
+        gmap.add_keyframe(Keyframe(id=0, R=np.eye(3), t=np.zeros((3, 1))))
+    gmap.add_map_point(MapPoint(id=4, position=np.zeros((3, 1))))
+    with pytest.raises(ValueError):
+        gmap.add_map_point(MapPoint(id=4, position=np.zeros((3, 1))))
+    assert KeyPoint.from_xy(0.1, 0.2).pt == (float(np.float32(0.1)), float(np.float32(0.2)))
+
+
+def test_synthetic_shapes_and_order():
+    fp = S.make_named_problem("bal50")
+    assert (fp.n_cams + 1, fp.n_pts, fp.n_obs) == S.SHAPES["bal50"]
+    assert np.all(np.diff(fp.obs_cam) >= 0), "observations must be keyframe-major"
+    assert fp.obs_cam.min() == -1 and fp.obs_cam.max() == fp.n_cams - 1
+    assert np.bincount(fp.obs_pt, minlength=fp.n_pts).min() >= 2
+    key = fp.obs_pt.astype(np.int64) * (fp.n_cams + 2) + fp.obs_cam + 1
+    assert np.unique(key).size == fp.n_obs, "a point is seen at most once per camera"
+    assert np.array_equal(fp.obs_uv, fp.obs_uv.astype(np.float32).astype(np.float64))
+    fp2 = S.make_named_problem("bal50")
+    assert np.array_equal(fp.obs_uv, fp2.obs_uv) and np.array_equal(fp.pts, fp2.pts)     # seeded
+
+
+def test_partition_points_balanced_and_complete():
+    fp = S.make_flat_problem(20, 5000, 24000, seed=9)
+    for n in (1, 2, 3, 8):
+        b = sharding.partition_points(fp.obs_pt, fp.n_pts, n)
+        assert b[0] == 0 and b[-1] == fp.n_pts and np.all(np.diff(b) >= 0) and b.size == n + 1
+        counts = np.bincount(fp.obs_pt, minlength=fp.n_pts)
+        per = np.array([counts[b[r]:b[r + 1]].sum() for r in range(n)])
+        assert per.sum() == fp.n_obs
+        assert per.max() - per.min() <= 2 * counts.max()
+        total = 0
+        for r in range(n):
+            sh, (lo, hi) = sharding.shard_problem(fp, r, n)
+            assert sh.n_pts == hi - lo and sh.n_cams == fp.n_cams
+            assert sh.obs_pt.min() >= 0 and sh.obs_pt.max() < sh.n_pts
+            total += sh.n_obs
+        assert total == fp.n_obs
