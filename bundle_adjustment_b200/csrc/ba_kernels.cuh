@@ -1,8 +1,8 @@
 // ba_kernels.cuh - hand-written sm_100a kernels of the Levenberg-Marquardt / Schur / PCG loop.
 //
 // Dataflow ("recompute"): no per-observation Jacobian or E block is ever stored.  Every pass streams
-// the 24-byte observation record (u, v, camera, point) and re-derives the 2x3 point Jacobian from the
-// camera pose and the point; the camera Jacobian follows from it algebraically:
+// the observation record (u, v, camera, point) and re-derives the 2x3 point Jacobian from the camera
+// pose and the point; the camera Jacobian follows from it algebraically:
 //
 //      x_cam = R (X + w x X + v) + t        (camera increment = world-frame twist (w, v))
 //      Jp    = d r / d X      = -dpi(x_cam) R                       (2x3)
@@ -18,7 +18,13 @@
 //     and the few tile partials of a camera are added in tile order by a finishing kernel.
 // No floating-point atomics anywhere: results are bit-reproducible run to run.
 //
-// All loop-carried scalars (damping, costs, PCG alpha/beta, buffer selector, flags) live in the device
+// Gathers (camera records in point-major passes, point records in camera-major passes) are the
+// expensive part: a naive per-lane gather costs one L1 wavefront per lane per 16-byte load.  Instead a
+// warp gathers COOPERATIVELY: the 32 records it needs are cut into 16-byte chunks, consecutive lanes
+// copy consecutive chunks of the same record straight into shared memory with cp.async (LDGSTS), and
+// every lane then reads its own record back from shared memory.
+//
+// All loop-carried scalars (damping, costs, PCG scalars, buffer selector, flags) live in the device
 // struct LMState so that the host only enqueues launches and polls a status word.
 #pragma once
 #include "ba_math.cuh"
@@ -27,8 +33,13 @@ namespace ba {
 
 constexpr int PM_THREADS = 256;  // point-major CTA; nominal tile = PM_THREADS observations
 constexpr int CM_THREADS = 256;  // camera-major CTA
-constexpr int CM_TILE = 1024;    // observations per camera-major tile (<= 4 per thread)
+constexpr int CM_ROUNDS = 4;     // observations per thread in a camera-major tile
+constexpr int CM_TILE = CM_THREADS * CM_ROUNDS;
 constexpr int NSCAL = 16;        // per-iteration scalar slots
+constexpr int PT_REC = 16;       // doubles per point record: X(buf 0) | X(buf 1) | z | h, 4 each = 128 B
+constexpr int PR_Z = 8, PR_H = 12;
+constexpr int VEC_THREADS = 128; // camera-vector kernels: one camera per thread
+constexpr int MAX_VEC_CTAS = 1024;
 
 // scalar slots (partials are reduced into LMState::scal by k_reduce_scalars)
 enum {
@@ -54,7 +65,7 @@ struct LMState {
     double lambda, nu;
     double cost[2], raw[2];  // per parameter buffer
     double gmax;             // max |g| at the current point
-    double rz, rz0, pq, alpha, beta;
+    double gamma, gamma0, gamma_prev, alpha, beta;  // PCG scalars: gamma = r.M^-1 r
     double model, rho, dcost, step_norm, x_norm;
     double scal[NSCAL];
     int cur;                 // which parameter buffer is current (0/1); trial = cur ^ 1
@@ -72,16 +83,15 @@ struct Params {
     int n_cams;    // adjustable cameras; slot n_cams holds the fixed camera
     int n_pts, n_obs, n_obs_adj;
     int pm_tiles, cm_tiles, pm_cap;  // pm_cap = shared-memory slots per contribution row
-    // parameters, double buffered: [2][(n_cams+1)*6] (rvec,t), [2][(n_cams+1)*12] (R,t), [2][n_pts*4]
+    int vec_ctas;                    // grid of the camera-vector kernels
+    // parameters: [2][(n_cams+1)*6] (rvec,t), [2][(n_cams+1)*12] (R,t); points live in pt_rec
     double* cam_rt;
     double* cam_R;
-    double* pt_X;
+    double* pt_rec;   // [n_pts*PT_REC]
     // per-point normal-equation data
     double* pt_V;     // [2][n_pts*6]
     double* pt_g;     // [2][n_pts*4]
     double* pt_Vinv;  // [n_pts*6]
-    double* pt_h;     // [n_pts*4]  Vinv g_p
-    double* pt_z;     // [n_pts*4]  point-pass output
     double* pt_D;     // [n_pts*4]  damping diagonal
     // per-camera data (local coordinates)
     double* cam_U;     // [n_cams*21]
@@ -89,11 +99,15 @@ struct Params {
     double* cam_D;     // [n_cams*6]
     double* cam_Minv;  // [n_cams*36]
     double* cam_acc;   // [n_cams*27] tile-summed accumulators (all-reduced in multi-GPU mode)
-    double* v_b;       // [(n_cams+1)*6] right-hand side; the +1 slot (fixed camera) stays zero
+    // PCG vectors, [(n_cams+1)*6]; the +1 slot (fixed camera) stays zero
+    double* v_b;
     double* v_x;
     double* v_r;
+    double* v_u;   // M^-1 r  (the vector the Schur mat-vec is applied to)
     double* v_p;
-    double* v_q;
+    double* v_s;   // A p
+    double* v_w;   // A u
+    double* dot_partial;  // [MAX_VEC_CTAS*2]
     // observations
     const double2* o_uv;   // reference order
     const int2* o_idx;     // (camera slot, point)
@@ -126,7 +140,7 @@ BA_D double warp_max(double v) {
     return v;
 }
 
-// Sum N per-thread values over the CTA; thread k < N returns total k in out[k] (shared, N doubles).
+// Sum N per-thread values over the CTA; thread k < N gets total k in out[k] (shared, N doubles).
 template <int N, int THREADS>
 BA_D void block_sum(double (&v)[N], double* sm /* [THREADS/32 * N] */, double* out /* [N] */) {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -144,6 +158,9 @@ BA_D void block_sum(double (&v)[N], double* sm /* [THREADS/32 * N] */, double* o
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// loads
+// ---------------------------------------------------------------------------------------------
 BA_D void load_cam(const double* __restrict__ base, int slot, double Rt[12]) {
     const double2* p = reinterpret_cast<const double2*>(base + (size_t)slot * 12);
 #pragma unroll
@@ -162,10 +179,16 @@ BA_D void load_vec6(const double* __restrict__ base, int slot, double x[6]) {
         x[2 * k + 1] = a.y;
     }
 }
-BA_D void load_pt(const double* __restrict__ base, int p, double X[3]) {
-    const double2* q = reinterpret_cast<const double2*>(base + (size_t)p * 4);
+// 3-vector stored in a 4-double slot at `ptr`
+BA_D void load_v3(const double* __restrict__ ptr, double X[3]) {
+    const double2* q = reinterpret_cast<const double2*>(ptr);
     const double2 a = __ldg(q), b = __ldg(q + 1);
     X[0] = a.x; X[1] = a.y; X[2] = b.x;
+}
+BA_D void store_v3(double* ptr, double a, double b, double c) {
+    double2* q = reinterpret_cast<double2*>(ptr);
+    q[0] = make_double2(a, b);
+    q[1] = make_double2(c, 0.0);
 }
 BA_D void load_sym3(const double* __restrict__ base, int p, double S[6]) {
     const double2* q = reinterpret_cast<const double2*>(base + (size_t)p * 6);
@@ -174,6 +197,43 @@ BA_D void load_sym3(const double* __restrict__ base, int p, double S[6]) {
         const double2 a = __ldg(q + k);
         S[2 * k] = a.x;
         S[2 * k + 1] = a.y;
+    }
+}
+
+// cp.async (LDGSTS): 16 bytes global -> shared, no register staging.  .ca keeps the line in L1 (camera
+// records are re-used by many warps), .cg bypasses it (point records are used a handful of times).
+BA_D void cp_async16_ca(void* smem, const void* gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+BA_D void cp_async16_cg(void* smem, const void* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+BA_D void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
+
+// Cooperative gather of 32 camera records into `stage` (per-warp shared memory, 32 * NCH * 16 bytes).
+// Record of lane L = NCH 16-byte chunks: chunks [0,6) = R|t of camera `cam` (from camR), chunks [6,9) =
+// its 6-vector (from vec) when NCH == 9.  Chunk j of the warp's 32*NCH is copied by lane j % 32.
+template <int NCH>
+BA_D void warp_gather_cameras(char* stage, int cam, const double* __restrict__ camR, const double* __restrict__ vec) {
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int k = 0; k < NCH; ++k) {
+        const int j = 32 * k + lane;
+        const int src = j / NCH, part = j - src * NCH;
+        const int c = __shfl_sync(0xffffffffu, cam, src);
+        const char* g = (NCH == 6 || part < 6) ? reinterpret_cast<const char*>(camR) + (size_t)c * 96 + part * 16
+                                               : reinterpret_cast<const char*>(vec) + (size_t)c * 48 + (part - 6) * 16;
+        cp_async16_ca(stage + j * 16, g);
+    }
+}
+template <int NCH>
+BA_D void read_staged(const char* stage, double* out /* [2*NCH] */) {
+    const double2* p = reinterpret_cast<const double2*>(stage + (threadIdx.x & 31) * (NCH * 16));
+#pragma unroll
+    for (int k = 0; k < NCH; ++k) {
+        const double2 a = p[k];
+        out[2 * k] = a.x;
+        out[2 * k + 1] = a.y;
     }
 }
 
@@ -206,7 +266,7 @@ __global__ void k_residuals(Params P, double2* __restrict__ r_out) {
     const int2 id = __ldg(P.o_idx + i);
     double Rt[12], X[3];
     load_cam(P.cam_R + (size_t)b * (P.n_cams + 1) * 12, id.x, Rt);
-    load_pt(P.pt_X + (size_t)b * P.n_pts * 4, id.y, X);
+    load_v3(P.pt_rec + (size_t)id.y * PT_REC + 4 * b, X);
     double rx, ry;
     project_residual(Rt, X, uv.x, uv.y, P.K, rx, ry);
     r_out[i] = make_double2(rx, ry);
@@ -222,7 +282,7 @@ __global__ void k_jacobian_blocks(Params P, double* __restrict__ jc_out, double*
     const int2 id = __ldg(P.o_idx + i);
     double Rt[12], X[3];
     load_cam(P.cam_R + (size_t)b * (P.n_cams + 1) * 12, id.x, Rt);
-    load_pt(P.pt_X + (size_t)b * P.n_pts * 4, id.y, X);
+    load_v3(P.pt_rec + (size_t)id.y * PT_REC + 4 * b, X);
     ObsLin o;
     linearize_obs(Rt, X, uv.x, uv.y, P.K, o);
     double* jp = jp_out + (size_t)i * 6;
@@ -243,14 +303,13 @@ __global__ void k_jacobian_blocks(Params P, double* __restrict__ jc_out, double*
     for (int k = 0; k < 3; ++k) {
         jc[k] = ax[0] * Jr[k] + ax[1] * Jr[3 + k] + ax[2] * Jr[6 + k];
         jc[6 + k] = ay[0] * Jr[k] + ay[1] * Jr[3 + k] + ay[2] * Jr[6 + k];
-        // Jp R^T: row . R[k,:]
-        jc[3 + k] = o.jx[0] * Rt[3 * k] + o.jx[1] * Rt[3 * k + 1] + o.jx[2] * Rt[3 * k + 2];
+        jc[3 + k] = o.jx[0] * Rt[3 * k] + o.jx[1] * Rt[3 * k + 1] + o.jx[2] * Rt[3 * k + 2];  // Jp R^T
         jc[9 + k] = o.jy[0] * Rt[3 * k] + o.jy[1] * Rt[3 * k + 1] + o.jy[2] * Rt[3 * k + 2];
     }
 }
 
 // ---------------------------------------------------------------------------------------------
-// point-major tile helpers
+// point-major tile kernels
 // ---------------------------------------------------------------------------------------------
 struct PmTile { int p0, p1, o0, n; };
 BA_D PmTile pm_tile(const Params& P) {
@@ -261,26 +320,35 @@ BA_D PmTile pm_tile(const Params& P) {
     t.n = __ldg(P.pt_off + t.p1) - t.o0;
     return t;
 }
+// dynamic shared memory of a point-major kernel: NROW contribution rows of pm_cap doubles, then one
+// cooperative-gather stage per warp
+template <int NROW, int NCH>
+__host__ __device__ constexpr size_t pm_smem_bytes(int cap) {
+    return (size_t)NROW * cap * sizeof(double);
+}
 
 // K-LINP: linearise at buffer `which` in point-major order.
 //   per point : V_p = sum Jp^T W Jp (6), g_p = sum Jp^T wg r (3)           -> pt_V[b], pt_g[b]
 //   per tile  : 0.5*sum rho, sum r^2, max|g_p|, #bad                       -> pm_partial
 __global__ void __launch_bounds__(PM_THREADS) k_lin_points(Params P, int which) {
-    extern __shared__ double sm[];
+    extern __shared__ __align__(16) double sm[];
     __shared__ double red[PM_THREADS / 32 * 3];
     __shared__ double tot[3];
     const int b = resolve_buf(P.st, which);
     const PmTile T = pm_tile(P);
     const int cap = P.pm_cap;
     const double* camR = P.cam_R + (size_t)b * (P.n_cams + 1) * 12;
-    const double* ptX = P.pt_X + (size_t)b * P.n_pts * 4;
     double acc[3] = {0.0, 0.0, 0.0};  // cost, raw, bad
-    for (int i = threadIdx.x; i < T.n; i += PM_THREADS) {
-        const double2 uv = __ldg(P.pm_uv + T.o0 + i);
-        const int2 id = __ldg(P.pm_idx + T.o0 + i);
-        double Rt[12], X[3];
+    for (int base = 0; base < T.n; base += PM_THREADS) {
+        const int i = base + threadIdx.x;
+        const bool act = i < T.n;
+        double2 uv = make_double2(0.0, 0.0);
+        int2 id = make_int2(P.n_cams, T.p0);
+        if (act) { uv = __ldg(P.pm_uv + T.o0 + i); id = __ldg(P.pm_idx + T.o0 + i); }
+        if (!act) continue;
+        double X[3], Rt[12];
         load_cam(camR, id.x, Rt);
-        load_pt(ptX, id.y, X);
+        load_v3(P.pt_rec + (size_t)id.y * PT_REC + 4 * b, X);
         ObsLin o;
         linearize_obs(Rt, X, uv.x, uv.y, P.K, o);
         double wHx, wgx, r0x, wHy, wgy, r0y;
@@ -318,14 +386,12 @@ __global__ void __launch_bounds__(PM_THREADS) k_lin_points(Params P, int which) 
         }
         double2* v2 = reinterpret_cast<double2*>(V + (size_t)p * 6);
         v2[0] = make_double2(s[0], s[1]); v2[1] = make_double2(s[2], s[3]); v2[2] = make_double2(s[4], s[5]);
-        double2* g2 = reinterpret_cast<double2*>(G + (size_t)p * 4);
-        g2[0] = make_double2(s[6], s[7]); g2[1] = make_double2(s[8], 0.0);
+        store_v3(G + (size_t)p * 4, s[6], s[7], s[8]);
         gmax = fmax(gmax, fmax(fabs(s[6]), fmax(fabs(s[7]), fabs(s[8]))));
     }
     __syncthreads();
     block_sum<3, PM_THREADS>(acc, red, tot);
     __syncthreads();
-    // block max of gmax (reuse red)
     const double wm = warp_max(gmax);
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = wm;
     __syncthreads();
@@ -345,28 +411,26 @@ __global__ void k_point_prepare(Params P, double dmin, double dmax) {
     const double lam = P.st->lambda;
     double V[6], g[3];
     load_sym3(P.pt_V + (size_t)b * P.n_pts * 6, p, V);
-    load_pt(P.pt_g + (size_t)b * P.n_pts * 4, p, g);
+    load_v3(P.pt_g + (size_t)b * P.n_pts * 4 + (size_t)p * 4, g);
     const double d0 = fmin(fmax(V[0], dmin), dmax), d1 = fmin(fmax(V[3], dmin), dmax), d2 = fmin(fmax(V[5], dmin), dmax);
     V[0] += lam * d0; V[3] += lam * d1; V[5] += lam * d2;
     double Vi[6], h[3];
-    if (!sym3_inverse(V, Vi)) {  // not SPD (can only come from non-finite input): fall back to the damped diagonal
+    if (!sym3_inverse(V, Vi)) {  // not SPD (can only come from non-finite input): damped diagonal instead
         Vi[0] = 1.0 / (lam * d0 + dmin); Vi[3] = 1.0 / (lam * d1 + dmin); Vi[5] = 1.0 / (lam * d2 + dmin);
         Vi[1] = Vi[2] = Vi[4] = 0.0;
     }
     sym3_mulv(Vi, g, h);
     double2* vo = reinterpret_cast<double2*>(P.pt_Vinv + (size_t)p * 6);
     vo[0] = make_double2(Vi[0], Vi[1]); vo[1] = make_double2(Vi[2], Vi[3]); vo[2] = make_double2(Vi[4], Vi[5]);
-    double2* ho = reinterpret_cast<double2*>(P.pt_h + (size_t)p * 4);
-    ho[0] = make_double2(h[0], h[1]); ho[1] = make_double2(h[2], 0.0);
-    double2* d = reinterpret_cast<double2*>(P.pt_D + (size_t)p * 4);
-    d[0] = make_double2(d0, d1); d[1] = make_double2(d2, 0.0);
+    store_v3(P.pt_rec + (size_t)p * PT_REC + PR_H, h[0], h[1], h[2]);
+    store_v3(P.pt_D + (size_t)p * 4, d0, d1, d2);
 }
 
 // K-P1 (MODE 0): z_p = Vinv_p * sum_i Jp_i^T W_i Jc_i vec_c         (first half of the Schur mat-vec)
 // K-BACKSUB (MODE 1): dp = -h_p - z_p(x), X_trial = X + dp, plus the step's scalar products.
 template <int MODE>
 __global__ void __launch_bounds__(PM_THREADS) k_point_pass(Params P, const double* __restrict__ vec) {
-    extern __shared__ double sm[];
+    extern __shared__ __align__(16) double sm[];
     __shared__ double red[PM_THREADS / 32 * 4];
     __shared__ double tot[4];
     if (MODE == 0 && P.st->pcg_done) return;
@@ -374,16 +438,20 @@ __global__ void __launch_bounds__(PM_THREADS) k_point_pass(Params P, const doubl
     const PmTile T = pm_tile(P);
     const int cap = P.pm_cap;
     const double* camR = P.cam_R + (size_t)b * (P.n_cams + 1) * 12;
-    const double* ptX = P.pt_X + (size_t)b * P.n_pts * 4;
-    for (int i = threadIdx.x; i < T.n; i += PM_THREADS) {
-        const double2 uv = __ldg(P.pm_uv + T.o0 + i);
-        const int2 id = __ldg(P.pm_idx + T.o0 + i);
-        double Rt[12], X[3], x[6];
-        load_cam(camR, id.x, Rt);
-        load_pt(ptX, id.y, X);
-        load_vec6(vec, id.x, x);
+    for (int base = 0; base < T.n; base += PM_THREADS) {
+        const int i = base + threadIdx.x;
+        const bool act = i < T.n;
+        double2 uv = make_double2(0.0, 0.0);
+        int2 id = make_int2(P.n_cams, T.p0);
+        if (act) { uv = __ldg(P.pm_uv + T.o0 + i); id = __ldg(P.pm_idx + T.o0 + i); }
+        if (!act) continue;
+        double X[3], rec[18];
+        load_cam(camR, id.x, rec);
+        load_vec6(vec, id.x, rec + 12);
+        load_v3(P.pt_rec + (size_t)id.y * PT_REC + 4 * b, X);
+        const double* x = rec + 12;
         ObsLin o;
-        linearize_obs(Rt, X, uv.x, uv.y, P.K, o);
+        linearize_obs(rec, X, uv.x, uv.y, P.K, o);
         double wHx, wgx, r0x, wHy, wgy, r0y;
         robust_weights(o.rx, P.delta, P.mode, wHx, wgx, r0x);
         robust_weights(o.ry, P.delta, P.mode, wHy, wgy, r0y);
@@ -409,18 +477,17 @@ __global__ void __launch_bounds__(PM_THREADS) k_point_pass(Params P, const doubl
         double Vi[6], z[3];
         load_sym3(P.pt_Vinv, p, Vi);
         sym3_mulv(Vi, s, z);
+        double* rec = P.pt_rec + (size_t)p * PT_REC;
         if (MODE == 0) {
-            double2* zo = reinterpret_cast<double2*>(P.pt_z + (size_t)p * 4);
-            zo[0] = make_double2(z[0], z[1]); zo[1] = make_double2(z[2], 0.0);
+            store_v3(rec + PR_Z, z[0], z[1], z[2]);
         } else {
             double h[3], X[3], g[3], D[3];
-            load_pt(P.pt_h, p, h);
-            load_pt(ptX, p, X);
-            load_pt(P.pt_g + (size_t)b * P.n_pts * 4, p, g);
-            load_pt(P.pt_D, p, D);
+            load_v3(rec + PR_H, h);
+            load_v3(rec + 4 * b, X);
+            load_v3(P.pt_g + (size_t)b * P.n_pts * 4 + (size_t)p * 4, g);
+            load_v3(P.pt_D + (size_t)p * 4, D);
             const double dp0 = -h[0] - z[0], dp1 = -h[1] - z[1], dp2 = -h[2] - z[2];
-            double2* xo = reinterpret_cast<double2*>(P.pt_X + (size_t)(b ^ 1) * P.n_pts * 4 + (size_t)p * 4);
-            xo[0] = make_double2(X[0] + dp0, X[1] + dp1); xo[1] = make_double2(X[2] + dp2, 0.0);
+            store_v3(rec + 4 * (b ^ 1), X[0] + dp0, X[1] + dp1, X[2] + dp2);
             acc[0] += g[0] * dp0 + g[1] * dp1 + g[2] * dp2;
             acc[1] += D[0] * dp0 * dp0 + D[1] * dp1 * dp1 + D[2] * dp2 * dp2;
             acc[2] += dp0 * dp0 + dp1 * dp1 + dp2 * dp2;
@@ -443,19 +510,43 @@ __global__ void __launch_bounds__(PM_THREADS) k_point_pass(Params P, const doubl
 // preconditioner correction (21).  KIND 2: second half of the Schur mat-vec (6).
 // Accumulator layout: [0..20] symmetric 6x6 upper triangle (sym6), [21..26] 6-vector.  KIND 2 uses [0..5].
 // ---------------------------------------------------------------------------------------------
+template <int KIND> struct CmN { static constexpr int value = (KIND == 2) ? 6 : 27; };
+// 16-byte chunks gathered per observation: X (2) [+ z (2)] [+ h (2) + Vinv (3)]
+template <int KIND> struct CmCh { static constexpr int value = (KIND == 0) ? 2 : (KIND == 2 ? 4 : 7); };
 template <int KIND>
-struct CmN { static constexpr int value = (KIND == 2) ? 6 : 27; };
+__host__ __device__ constexpr size_t cm_smem_bytes() {
+    return 0;
+}
+
+template <int KIND>
+BA_D void warp_gather_points(char* stage, int p, int b, const double* __restrict__ pt_rec, const double* __restrict__ pt_Vinv) {
+    constexpr int NCH = CmCh<KIND>::value;
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int k = 0; k < NCH; ++k) {
+        const int j = 32 * k + lane;
+        const int src = j / NCH, part = j - src * NCH;
+        const int q = __shfl_sync(0xffffffffu, p, src);
+        const char* rec = reinterpret_cast<const char*>(pt_rec) + (size_t)q * (PT_REC * 8);
+        const char* g;
+        if (part < 2) g = rec + b * 32 + part * 16;
+        else if (KIND == 2) g = rec + PR_Z * 8 + (part - 2) * 16;
+        else if (part < 4) g = rec + PR_H * 8 + (part - 2) * 16;
+        else g = reinterpret_cast<const char*>(pt_Vinv) + (size_t)q * 48 + (part - 4) * 16;
+        cp_async16_cg(stage + j * 16, g);
+    }
+}
 
 template <int KIND>
 __global__ void __launch_bounds__(CM_THREADS) k_camera_pass(Params P, const double* __restrict__ vec, int with_schur_diag) {
     constexpr int N = CmN<KIND>::value;
+    constexpr int NCH = CmCh<KIND>::value;
     __shared__ double red[CM_THREADS / 32 * N];
     __shared__ double tot[N];
     if (KIND == 2 && P.st->pcg_done) return;
     const int b = P.st->cur;
     const int4 tile = __ldg(P.cm_tile + blockIdx.x);
     const int cam = tile.x, o0 = tile.y, n = tile.z;
-    const double* ptX = P.pt_X + (size_t)b * P.n_pts * 4;
     double Rt[12], x[6];
     load_cam(P.cam_R + (size_t)b * (P.n_cams + 1) * 12, cam, Rt);
     if (KIND == 2) load_vec6(vec, cam, x);
@@ -463,49 +554,57 @@ __global__ void __launch_bounds__(CM_THREADS) k_camera_pass(Params P, const doub
 #pragma unroll
     for (int k = 0; k < N; ++k) acc[k] = 0.0;
     for (int i = threadIdx.x; i < n; i += CM_THREADS) {
-        const double2 uv = __ldg(P.cm_uv + o0 + i);
+        const double2 uvr = __ldg(P.cm_uv + o0 + i);
         const int p = __ldg(P.cm_pt + o0 + i);
-        double X[3];
-        load_pt(ptX, p, X);
+        double rec[2 * NCH];
+        {
+            const double* pr = P.pt_rec + (size_t)p * PT_REC;
+            load_v3(pr + 4 * b, rec);
+            if constexpr (KIND == 2) load_v3(pr + PR_Z, rec + 4);
+            if constexpr (KIND == 1) {
+                load_v3(pr + PR_H, rec + 4);
+                load_sym3(P.pt_Vinv, p, rec + 8);
+            }
+        }
+        double2 uv[1] = {uvr};
+        constexpr int r = 0;
+        const double* X = rec;
         ObsLin o;
-        linearize_obs(Rt, X, uv.x, uv.y, P.K, o);
+        linearize_obs(Rt, X, uv[r].x, uv[r].y, P.K, o);
         double wHx, wgx, r0x, wHy, wgy, r0y;
         robust_weights(o.rx, P.delta, P.mode, wHx, wgx, r0x);
         robust_weights(o.ry, P.delta, P.mode, wHy, wgy, r0y);
-        if (KIND == 0) {
-            // rows of Jc = (X x j, j)
-            double jcx[6], jcy[6];
+        if constexpr (KIND == 0) {
+            double jcx[6], jcy[6];  // rows of Jc = (X x j, j)
             cross3(X, o.jx, jcx); cross3(X, o.jy, jcy);
 #pragma unroll
             for (int k = 0; k < 3; ++k) { jcx[3 + k] = o.jx[k]; jcy[3 + k] = o.jy[k]; }
             const double gx = wgx * o.rx, gy = wgy * o.ry;
             int q = 0;
 #pragma unroll
-            for (int r = 0; r < 6; ++r) {
-                const double sx = wHx * jcx[r], sy = wHy * jcy[r];
+            for (int a = 0; a < 6; ++a) {
+                const double sx = wHx * jcx[a], sy = wHy * jcy[a];
 #pragma unroll
-                for (int c = r; c < 6; ++c) { acc[q] += sx * jcx[c] + sy * jcy[c]; ++q; }
-                acc[21 + r] += jcx[r] * gx + jcy[r] * gy;
+                for (int c = a; c < 6; ++c) { acc[q] += sx * jcx[c] + sy * jcy[c]; ++q; }
+                acc[21 + a] += jcx[a] * gx + jcy[a] * gy;
             }
-        } else if (KIND == 1) {
-            // W = Jp^T diag(wH) Jp (sym 3x3)
-            double W[6];
+        } else if constexpr (KIND == 1) {
+            double W[6];  // W = Jp^T diag(wH) Jp (sym 3x3)
             {
                 const double ax = wHx * o.jx[0], bx = wHx * o.jx[1], cx = wHx * o.jx[2];
                 const double ay = wHy * o.jy[0], by = wHy * o.jy[1], cy = wHy * o.jy[2];
                 W[0] = ax * o.jx[0] + ay * o.jy[0]; W[1] = ax * o.jx[1] + ay * o.jy[1]; W[2] = ax * o.jx[2] + ay * o.jy[2];
                 W[3] = bx * o.jx[1] + by * o.jy[1]; W[4] = bx * o.jx[2] + by * o.jy[2]; W[5] = cx * o.jx[2] + cy * o.jy[2];
             }
-            double h[3], m[3], xm[3];
-            load_pt(P.pt_h, p, h);
+            const double* h = rec + 4;
+            double m[3], xm[3];
             sym3_mulv(W, h, m);  // E h = G^T (W h)
             cross3(X, m, xm);
 #pragma unroll
             for (int k = 0; k < 3; ++k) { acc[21 + k] += xm[k]; acc[24 + k] += m[k]; }
             if (with_schur_diag) {
                 // T = W Vinv W (sym), correction = G^T T G with G = [-[X]x | I]
-                double Vi[6];
-                load_sym3(P.pt_Vinv, p, Vi);
+                const double* Vi = rec + 8;
                 const double Wf[9] = {W[0], W[1], W[2], W[1], W[3], W[4], W[2], W[4], W[5]};
                 double A[9];  // A = Vinv W
 #pragma unroll
@@ -517,11 +616,10 @@ __global__ void __launch_bounds__(CM_THREADS) k_camera_pass(Params P, const doub
                 }
                 double Tm[9];  // T = W A (symmetric)
 #pragma unroll
-                for (int r = 0; r < 3; ++r)
+                for (int a = 0; a < 3; ++a)
 #pragma unroll
-                    for (int c = 0; c < 3; ++c) Tm[3 * r + c] = Wf[3 * r] * A[c] + Wf[3 * r + 1] * A[3 + c] + Wf[3 * r + 2] * A[6 + c];
-                // C = [X]x T : column c of C = X x T[:,c]
-                double C[9];
+                    for (int c = 0; c < 3; ++c) Tm[3 * a + c] = Wf[3 * a] * A[c] + Wf[3 * a + 1] * A[3 + c] + Wf[3 * a + 2] * A[6 + c];
+                double C[9];  // C = [X]x T : column c = X x T[:,c]
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
                     const double tc[3] = {Tm[c], Tm[3 + c], Tm[6 + c]};
@@ -529,31 +627,29 @@ __global__ void __launch_bounds__(CM_THREADS) k_camera_pass(Params P, const doub
                     cross3(X, tc, cc);
                     C[c] = cc[0]; C[3 + c] = cc[1]; C[6 + c] = cc[2];
                 }
-                // top-left = C [X]x^T : row r of result = -(C[r,:] x X)... use (C [X]x^T)[r][c] = (X x C[r,:])[c]
-                // since [X]x^T v = -X x v and (C B^T)[r][c] = sum_k C[r][k] B[c][k] = ([X]x C[r,:]^T)[c] = (X x C[r,:])[c]
 #pragma unroll
-                for (int r = 0; r < 3; ++r) {
-                    const double cr[3] = {C[3 * r], C[3 * r + 1], C[3 * r + 2]};
+                for (int a = 0; a < 3; ++a) {
+                    // top-left block [X]x T [X]x^T: row a = X x C[a,:]
+                    const double cr[3] = {C[3 * a], C[3 * a + 1], C[3 * a + 2]};
                     double tl[3];
                     cross3(X, cr, tl);
 #pragma unroll
-                    for (int c = r; c < 3; ++c) acc[sym6(r, c)] += tl[c];
+                    for (int c = a; c < 3; ++c) acc[sym6(a, c)] += tl[c];
 #pragma unroll
-                    for (int c = 0; c < 3; ++c) acc[sym6(r, 3 + c)] += C[3 * r + c];  // top-right = [X]x T
+                    for (int c = 0; c < 3; ++c) acc[sym6(a, 3 + c)] += C[3 * a + c];  // top-right = [X]x T
                 }
 #pragma unroll
-                for (int r = 0; r < 3; ++r)
+                for (int a = 0; a < 3; ++a)
 #pragma unroll
-                    for (int c = r; c < 3; ++c) acc[sym6(3 + r, 3 + c)] += Tm[3 * r + c];
+                    for (int c = a; c < 3; ++c) acc[sym6(3 + a, 3 + c)] += Tm[3 * a + c];
             }
         } else {
-            double z[3];
-            load_pt(P.pt_z, p, z);
-            const double d0 = fma(x[1], X[2], fma(-x[2], X[1], x[3]));
-            const double d1 = fma(x[2], X[0], fma(-x[0], X[2], x[4]));
-            const double d2 = fma(x[0], X[1], fma(-x[1], X[0], x[5]));
-            const double bx = wHx * (o.jx[0] * (d0 - z[0]) + o.jx[1] * (d1 - z[1]) + o.jx[2] * (d2 - z[2]));
-            const double by = wHy * (o.jy[0] * (d0 - z[0]) + o.jy[1] * (d1 - z[1]) + o.jy[2] * (d2 - z[2]));
+            const double* z = rec + 4;
+            const double d0 = fma(x[1], X[2], fma(-x[2], X[1], x[3])) - z[0];
+            const double d1 = fma(x[2], X[0], fma(-x[0], X[2], x[4])) - z[1];
+            const double d2 = fma(x[0], X[1], fma(-x[1], X[0], x[5])) - z[2];
+            const double bx = wHx * (o.jx[0] * d0 + o.jx[1] * d1 + o.jx[2] * d2);
+            const double by = wHy * (o.jy[0] * d0 + o.jy[1] * d1 + o.jy[2] * d2);
             double m[3], xm[3];
 #pragma unroll
             for (int k = 0; k < 3; ++k) m[k] = o.jx[k] * bx + o.jy[k] * by;
@@ -591,54 +687,32 @@ __global__ void k_camera_finish_lin(Params P, double dmin, double dmax) {
     }
 }
 
-// After K-SCHURC (+ all-reduce): M_c = U_c + lambda D_c - corr_c, Minv_c; b_c = -g_c + (E Vinv g_p)_c.
-__global__ void k_camera_finish_schur(Params P, int with_schur_diag) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= P.n_cams) return;
-    const double lam = P.st->lambda;
-    const double* a = P.cam_acc + (size_t)c * 27;
-    const double* U = P.cam_U + (size_t)c * 21;
-    double M[36];
-    for (int i = 0; i < 6; ++i)
-        for (int j = i; j < 6; ++j) {
-            double v = U[sym6(i, j)] - (with_schur_diag ? a[sym6(i, j)] : 0.0);
-            if (i == j) v += lam * P.cam_D[(size_t)c * 6 + i];
-            M[6 * i + j] = v; M[6 * j + i] = v;
-        }
-    if (!spd6_inverse(M)) {  // numerically indefinite: fall back to the damped block of J^T J, then to its diagonal
-        for (int i = 0; i < 6; ++i)
-            for (int j = i; j < 6; ++j) {
-                double v = U[sym6(i, j)];
-                if (i == j) v += lam * P.cam_D[(size_t)c * 6 + i];
-                M[6 * i + j] = v; M[6 * j + i] = v;
-            }
-        if (!spd6_inverse(M)) {
-            for (int i = 0; i < 36; ++i) M[i] = 0.0;
-            for (int i = 0; i < 6; ++i) M[7 * i] = 1.0 / ((1.0 + lam) * P.cam_D[(size_t)c * 6 + i]);
-        }
-    }
-    for (int k = 0; k < 36; ++k) P.cam_Minv[(size_t)c * 36 + k] = M[k];
-    for (int k = 0; k < 6; ++k) P.v_b[(size_t)c * 6 + k] = a[21 + k] - P.cam_g[(size_t)c * 6 + k];
-}
-
 // ---------------------------------------------------------------------------------------------
-// single-CTA vector kernels of the PCG (camera-sized vectors: n_cams*6 doubles)
+// camera-vector kernels (one camera per thread, grid = vec_ctas CTAs of VEC_THREADS)
+//
+// Preconditioned CG in the single-reduction form of Chronopoulos & Gear, so that the two inner
+// products of an iteration are available right after the mat-vec and the vector updates need no
+// grid-wide barrier:
+//      u = M^-1 r,  w = A u,  gamma = r.u,  delta = w.u
+//      beta = gamma / gamma_prev (0 at first),  alpha = gamma / (delta - beta * gamma / alpha_prev)
+//      p = u + beta p,  s = w + beta s,  x += alpha p,  r -= alpha s
+// Inner products: every CTA writes its partial, all CTAs (k_pcg_update) or the last CTA to arrive
+// (an integer ticket; the sum itself is done by one warp in a fixed order) add them up.
 // ---------------------------------------------------------------------------------------------
-constexpr int VEC_THREADS = 1024;
-
-BA_D double cta_sum(double v, double* sm) {  // all threads get the total; sm >= 33 doubles
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+BA_D double cta_sum_vec(double v, double* sm /* >= VEC_THREADS/32 */) {  // result valid in thread 0
     v = warp_sum(v);
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
     __syncthreads();
-    if (lane == 0) sm[w] = v;
-    __syncthreads();
-    if (w == 0) {
-        double s = (lane < (int)(blockDim.x >> 5)) ? sm[lane] : 0.0;
-        s = warp_sum(s);
-        if (lane == 0) sm[32] = s;
-    }
-    __syncthreads();
-    return sm[32];
+    double s = 0.0;
+    if (threadIdx.x == 0)
+        for (int i = 0; i < VEC_THREADS / 32; ++i) s += sm[i];
+    return s;
+}
+// sum of n per-CTA partials (stride 2 doubles) by warp 0, fixed order; result in lane 0 of warp 0
+BA_D double warp0_sum_partials(const double* part, int n) {
+    double v = 0.0;
+    for (int i = threadIdx.x; i < n; i += 32) v += part[2 * i];
+    return warp_sum(v);
 }
 
 BA_D void minv_apply(const double* __restrict__ Minv, const double* __restrict__ r, double* z) {
@@ -651,70 +725,160 @@ BA_D void minv_apply(const double* __restrict__ Minv, const double* __restrict__
     }
 }
 
-// x = 0, r = b, p = z = Minv r, rz = r.z
-__global__ void __launch_bounds__(VEC_THREADS) k_pcg_init(Params P) {
-    __shared__ double sm[33];
+// After K-SCHURC (+ all-reduce): M_c = U_c + lambda D_c - corr_c, Minv_c; b_c = -g_c + (E Vinv g_p)_c;
+// PCG start: x = 0, r = b, u = Minv r, p = s = 0, gamma = r.u.
+__global__ void __launch_bounds__(VEC_THREADS) k_camera_finish_schur(Params P, int with_schur_diag, int* ticket) {
+    __shared__ double sm[VEC_THREADS / 32];
+    __shared__ int last;
+    const int c = blockIdx.x * VEC_THREADS + threadIdx.x;
     double part = 0.0;
-    for (int c = threadIdx.x; c < P.n_cams; c += VEC_THREADS) {
-        double r[6], z[6];
-        for (int k = 0; k < 6; ++k) r[k] = P.v_b[(size_t)c * 6 + k];
-        minv_apply(P.cam_Minv + (size_t)c * 36, r, z);
+    if (c < P.n_cams) {
+        const double lam = P.st->lambda;
+        const double* a = P.cam_acc + (size_t)c * 27;
+        const double* U = P.cam_U + (size_t)c * 21;
+        double M[36];
+        for (int i = 0; i < 6; ++i)
+            for (int j = i; j < 6; ++j) {
+                double v = U[sym6(i, j)] - (with_schur_diag ? a[sym6(i, j)] : 0.0);
+                if (i == j) v += lam * P.cam_D[(size_t)c * 6 + i];
+                M[6 * i + j] = v; M[6 * j + i] = v;
+            }
+        if (!spd6_inverse(M)) {  // numerically indefinite: damped block of J^T J, then its diagonal
+            for (int i = 0; i < 6; ++i)
+                for (int j = i; j < 6; ++j) {
+                    double v = U[sym6(i, j)];
+                    if (i == j) v += lam * P.cam_D[(size_t)c * 6 + i];
+                    M[6 * i + j] = v; M[6 * j + i] = v;
+                }
+            if (!spd6_inverse(M)) {
+                for (int i = 0; i < 36; ++i) M[i] = 0.0;
+                for (int i = 0; i < 6; ++i) M[7 * i] = 1.0 / ((1.0 + lam) * P.cam_D[(size_t)c * 6 + i]);
+            }
+        }
+        for (int k = 0; k < 36; ++k) P.cam_Minv[(size_t)c * 36 + k] = M[k];
+        double r[6], u[6];
+        for (int k = 0; k < 6; ++k) r[k] = a[21 + k] - P.cam_g[(size_t)c * 6 + k];
+        minv_apply(M, r, u);
         for (int k = 0; k < 6; ++k) {
-            P.v_x[(size_t)c * 6 + k] = 0.0;
-            P.v_r[(size_t)c * 6 + k] = r[k];
-            P.v_p[(size_t)c * 6 + k] = z[k];
-            part += r[k] * z[k];
+            const size_t i = (size_t)c * 6 + k;
+            P.v_b[i] = r[k]; P.v_r[i] = r[k]; P.v_u[i] = u[k];
+            P.v_x[i] = 0.0; P.v_p[i] = 0.0; P.v_s[i] = 0.0;
+            part += r[k] * u[k];
         }
     }
-    const double rz = cta_sum(part, sm);
+    const double cs = cta_sum_vec(part, sm);
     if (threadIdx.x == 0) {
-        LMState* st = P.st;
-        st->rz = rz; st->rz0 = rz; st->pcg_iter = 0;
-        st->pcg_done = !(rz > 0.0);  // zero (or non-finite) right-hand side: nothing to solve
+        P.dot_partial[2 * blockIdx.x + 1] = cs;
+        __threadfence();
+        last = (atomicAdd(ticket, 1) == (int)gridDim.x - 1);
+    }
+    __syncthreads();
+    if (last && threadIdx.x < 32) {
+        __threadfence();
+        const double g = warp0_sum_partials(P.dot_partial + 1, gridDim.x);
+        if (threadIdx.x == 0) {
+            LMState* st = P.st;
+            st->gamma = g; st->gamma0 = g; st->gamma_prev = g; st->alpha = 0.0; st->beta = 0.0; st->pcg_iter = 0;
+            st->pcg_done = !(g > 0.0);  // zero (or non-finite) right-hand side: nothing to solve
+            *ticket = 0;
+        }
     }
 }
 
-// q = cam_acc (summed mat-vec partials, all-reduced) + lambda D p; then one PCG update.
-__global__ void __launch_bounds__(VEC_THREADS) k_pcg_update(Params P, double tol, int max_iters) {
-    __shared__ double sm[33];
-    LMState* st = P.st;
-    if (st->pcg_done) return;
-    const double lam = st->lambda;
+// w = (summed mat-vec partials) + lambda D u;  per-CTA partial of delta = w.u.
+// FROM_TILES: add the camera's tile partials here (single GPU); otherwise read cam_acc (all-reduced).
+template <bool FROM_TILES>
+__global__ void __launch_bounds__(VEC_THREADS) k_pcg_dots(Params P) {
+    __shared__ double sm[VEC_THREADS / 32];
+    if (P.st->pcg_done) return;
+    const int c = blockIdx.x * VEC_THREADS + threadIdx.x;
     double part = 0.0;
-    for (int c = threadIdx.x; c < P.n_cams; c += VEC_THREADS) {
-        for (int k = 0; k < 6; ++k) {
-            const double p = P.v_p[(size_t)c * 6 + k];
-            const double q = P.cam_acc[(size_t)c * 6 + k] + lam * P.cam_D[(size_t)c * 6 + k] * p;
-            P.v_q[(size_t)c * 6 + k] = q;
-            part += p * q;
+    if (c < P.n_cams) {
+        const double lam = P.st->lambda;
+        double w[6];
+        if (FROM_TILES) {
+            const int t0 = __ldg(P.cam_tile_off + c), t1 = __ldg(P.cam_tile_off + c + 1);
+#pragma unroll
+            for (int k = 0; k < 6; ++k) w[k] = 0.0;
+            for (int t = t0; t < t1; ++t)
+#pragma unroll
+                for (int k = 0; k < 6; ++k) w[k] += P.cm_partial[(size_t)t * 27 + k];
+        } else {
+#pragma unroll
+            for (int k = 0; k < 6; ++k) w[k] = P.cam_acc[(size_t)c * 6 + k];
         }
-    }
-    const double pq = cta_sum(part, sm);
-    const double rz = st->rz;
-    const double alpha = (pq > 0.0) ? rz / pq : 0.0;
-    part = 0.0;
-    for (int c = threadIdx.x; c < P.n_cams; c += VEC_THREADS) {
-        double r[6], z[6];
+#pragma unroll
         for (int k = 0; k < 6; ++k) {
             const size_t i = (size_t)c * 6 + k;
-            P.v_x[i] += alpha * P.v_p[i];
-            r[k] = P.v_r[i] - alpha * P.v_q[i];
-            P.v_r[i] = r[k];
-        }
-        minv_apply(P.cam_Minv + (size_t)c * 36, r, z);
-        for (int k = 0; k < 6; ++k) {
-            P.v_q[(size_t)c * 6 + k] = z[k];  // q is free again: keep z there
-            part += r[k] * z[k];
+            const double u = P.v_u[i];
+            const double wk = w[k] + lam * P.cam_D[i] * u;
+            P.v_w[i] = wk;
+            part += wk * u;
         }
     }
-    const double rz_new = cta_sum(part, sm);
-    const double beta = (rz > 0.0) ? rz_new / rz : 0.0;
-    for (int i = threadIdx.x; i < P.n_cams * 6; i += VEC_THREADS) P.v_p[i] = P.v_q[i] + beta * P.v_p[i];
+    const double cs = cta_sum_vec(part, sm);
+    if (threadIdx.x == 0) P.dot_partial[2 * blockIdx.x] = cs;
+}
+
+__global__ void __launch_bounds__(VEC_THREADS) k_pcg_update(Params P, double tol, int max_iters, int* ticket) {
+    __shared__ double sm[VEC_THREADS / 32];
+    __shared__ double sc[2];
+    __shared__ int last;
+    LMState* st = P.st;
+    if (st->pcg_done) return;
+    const double gamma = st->gamma, alpha_prev = st->alpha, gamma_prev = st->gamma_prev;
+    const int first = (st->pcg_iter == 0);
+    if (threadIdx.x < 32) {
+        const double d = warp0_sum_partials(P.dot_partial, gridDim.x);
+        if (threadIdx.x == 0) {
+            const double beta = first ? 0.0 : gamma / gamma_prev;
+            const double den = first ? d : d - beta * gamma / alpha_prev;
+            sc[0] = (den > 0.0) ? gamma / den : 0.0;
+            sc[1] = beta;
+        }
+    }
+    __syncthreads();
+    const double alpha = sc[0], beta = sc[1];
+    const int c = blockIdx.x * VEC_THREADS + threadIdx.x;
+    double part = 0.0;
+    if (c < P.n_cams) {
+        double r[6], u[6];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+            const size_t i = (size_t)c * 6 + k;
+            const double p = P.v_u[i] + beta * P.v_p[i];
+            const double s = P.v_w[i] + beta * P.v_s[i];
+            P.v_p[i] = p; P.v_s[i] = s;
+            P.v_x[i] += alpha * p;
+            r[k] = P.v_r[i] - alpha * s;
+            P.v_r[i] = r[k];
+        }
+        minv_apply(P.cam_Minv + (size_t)c * 36, r, u);
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+            P.v_u[(size_t)c * 6 + k] = u[k];
+            part += r[k] * u[k];
+        }
+    }
+    __syncthreads();
+    const double cs = cta_sum_vec(part, sm);
     if (threadIdx.x == 0) {
-        st->pq = pq; st->alpha = alpha; st->beta = beta; st->rz = rz_new;
-        const int it = st->pcg_iter + 1;
-        st->pcg_iter = it; st->pcg_total += 1;
-        if (!(pq > 0.0) || !(rz_new > tol * tol * st->rz0) || it >= max_iters) st->pcg_done = 1;
+        P.dot_partial[2 * blockIdx.x + 1] = cs;
+        __threadfence();
+        last = (atomicAdd(ticket, 1) == (int)gridDim.x - 1);
+    }
+    __syncthreads();
+    if (last && threadIdx.x < 32) {
+        __threadfence();
+        const double g = warp0_sum_partials(P.dot_partial + 1, gridDim.x);
+        if (threadIdx.x == 0) {
+            st->gamma_prev = gamma;
+            st->gamma = g; st->alpha = alpha; st->beta = beta;
+            const int it = st->pcg_iter + 1;
+            st->pcg_iter = it; st->pcg_total += 1;
+            if (!(alpha > 0.0) || !(g > tol * tol * st->gamma0) || it >= max_iters) st->pcg_done = 1;
+            *ticket = 0;
+        }
     }
 }
 
@@ -740,8 +904,7 @@ __global__ void k_camera_update(Params P) {
     log_so3(Rn, rv);
     double tn[3];
     for (int k = 0; k < 3; ++k) tn[k] = Rt[9 + k] + Rt[3 * k] * x[3] + Rt[3 * k + 1] * x[4] + Rt[3 * k + 2] * x[5];
-    // keep R consistent with the stored rvec (what ba_get_params returns)
-    rodrigues(rv, Rn);
+    rodrigues(rv, Rn);  // keep R consistent with the stored rvec (what ba_get_params returns)
     for (int k = 0; k < 3; ++k) { rt_new[k] = rv[k]; rt_new[3 + k] = tn[k]; }
     for (int k = 0; k < 9; ++k) R_new[k] = Rn[k];
     for (int k = 0; k < 3; ++k) R_new[9 + k] = tn[k];
@@ -757,45 +920,65 @@ __global__ void k_camera_update(Params P) {
     out[S_GDC] = gd; out[S_DDC] = dd; out[S_RDC] = rd; out[S_DC2] = d2; out[S_XC2] = x2;
 }
 
-// Reduce per-tile / per-camera scalar partials into st->scal (fixed order).  mask selects the slots.
-__global__ void __launch_bounds__(VEC_THREADS) k_reduce_scalars(Params P, unsigned pm_mask, unsigned cam_mask) {
+// ---------------------------------------------------------------------------------------------
+// single-CTA scalar kernels (once per LM iteration)
+// ---------------------------------------------------------------------------------------------
+constexpr int RED_THREADS = 1024;
+
+BA_D double cta_sum_all(double v, double* sm /* >= 33 */) {  // all threads get the total
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    v = warp_sum(v);
+    __syncthreads();
+    if (lane == 0) sm[w] = v;
+    __syncthreads();
+    if (w == 0) {
+        double s = (lane < (int)(blockDim.x >> 5)) ? sm[lane] : 0.0;
+        s = warp_sum(s);
+        if (lane == 0) sm[32] = s;
+    }
+    __syncthreads();
+    return sm[32];
+}
+
+// Reduce per-tile / per-camera scalar partials into st->scal (fixed order).  The masks select slots.
+__global__ void __launch_bounds__(RED_THREADS) k_reduce_scalars(Params P, unsigned pm_mask, unsigned cam_mask) {
     __shared__ double sm[33];
     for (int s = 0; s < NSCAL; ++s) {
         const bool pm = (pm_mask >> s) & 1u, cm = (cam_mask >> s) & 1u;
         if (!pm && !cm) continue;
         double v = 0.0;
         if (s == S_GPMAX) {
-            for (int t = threadIdx.x; t < P.pm_tiles; t += VEC_THREADS) v = fmax(v, P.pm_partial[(size_t)t * NSCAL + s]);
+            for (int t = threadIdx.x; t < P.pm_tiles; t += RED_THREADS) v = fmax(v, P.pm_partial[(size_t)t * NSCAL + s]);
             v = warp_max(v);
             __syncthreads();
             if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
             __syncthreads();
             if (threadIdx.x == 0) {
                 double m = 0.0;
-                for (int i = 0; i < VEC_THREADS / 32; ++i) m = fmax(m, sm[i]);
+                for (int i = 0; i < RED_THREADS / 32; ++i) m = fmax(m, sm[i]);
                 P.st->scal[s] = m;
             }
             __syncthreads();
             continue;
         }
-        if (pm) for (int t = threadIdx.x; t < P.pm_tiles; t += VEC_THREADS) v += P.pm_partial[(size_t)t * NSCAL + s];
-        if (cm) for (int c = threadIdx.x; c < P.n_cams; c += VEC_THREADS) v += P.cam_partial[(size_t)c * NSCAL + s];
-        const double tot = cta_sum(v, sm);
+        if (pm) for (int t = threadIdx.x; t < P.pm_tiles; t += RED_THREADS) v += P.pm_partial[(size_t)t * NSCAL + s];
+        if (cm) for (int c = threadIdx.x; c < P.n_cams; c += RED_THREADS) v += P.cam_partial[(size_t)c * NSCAL + s];
+        const double tot = cta_sum_all(v, sm);
         if (threadIdx.x == 0) P.st->scal[s] = tot;
     }
 }
 
 // gmax = max(|g_c|, |g_p|) at the current point; gtol test.
-__global__ void __launch_bounds__(VEC_THREADS) k_gradient_check(Params P, double gtol) {
+__global__ void __launch_bounds__(RED_THREADS) k_gradient_check(Params P, double gtol) {
     __shared__ double sm[32];
     double v = 0.0;
-    for (int i = threadIdx.x; i < P.n_cams * 6; i += VEC_THREADS) v = fmax(v, fabs(P.cam_g[i]));
+    for (int i = threadIdx.x; i < P.n_cams * 6; i += RED_THREADS) v = fmax(v, fabs(P.cam_g[i]));
     v = warp_max(v);
     if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
     __syncthreads();
     if (threadIdx.x == 0) {
         double m = P.st->scal[S_GPMAX];
-        for (int i = 0; i < VEC_THREADS / 32; ++i) m = fmax(m, sm[i]);
+        for (int i = 0; i < RED_THREADS / 32; ++i) m = fmax(m, sm[i]);
         P.st->gmax = m;
         if (P.st->status == 0 && m < gtol) P.st->status = 1;
     }
@@ -820,6 +1003,8 @@ __global__ void k_lm_decide(Params P, double ftol, double xtol, double lam_min, 
     const bool finite_new = isfinite(cost_new) && !(s[S_BAD] > 0.0);
     const double gd = s[S_GDP] + s[S_GDC];
     const double dDd = s[S_DDP] + s[S_DDC];
+    // exact decrease of the quadratic model for the inexact (PCG) step: the camera rows of
+    // (H + lambda D) d + g equal -r_pcg, the point rows vanish (exact back-substitution)
     const double model = -0.5 * gd + 0.5 * s[S_RDC] + 0.5 * st->lambda * dDd;
     const double cost = st->cost[cur];
     const double dcost = cost - cost_new;

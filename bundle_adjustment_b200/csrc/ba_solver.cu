@@ -119,13 +119,13 @@ struct DBuf {
 // ---------------------------------------------------------------------------------------------
 enum Kind {
     KN_SETUP = 0, KN_CAM_PREP, KN_RESID, KN_JAC, KN_LIN_PTS, KN_PT_PREP, KN_PT_PASS, KN_BACKSUB, KN_LIN_CAM,
-    KN_SCHUR_CAM, KN_MATVEC_CAM, KN_CAM_SUM, KN_CAM_FIN, KN_PCG_INIT, KN_PCG_UPDATE, KN_CAM_UPDATE, KN_REDUCE,
+    KN_SCHUR_CAM, KN_MATVEC_CAM, KN_CAM_SUM, KN_CAM_FIN, KN_PCG_DOTS, KN_PCG_UPDATE, KN_CAM_UPDATE, KN_REDUCE,
     KN_GRAD, KN_DECIDE, KN_COUNT
 };
 static const char* kKindNames[KN_COUNT] = {
     "setup", "cam_prepare", "residuals", "jacobian_blocks", "lin_points", "point_prepare", "schur_matvec_points",
     "backsub_points", "lin_cameras", "schur_rhs_cameras", "schur_matvec_cameras", "camera_sum", "camera_finish",
-    "pcg_init", "pcg_update", "camera_update", "reduce_scalars", "gradient_check", "lm_decide"};
+    "pcg_dots", "pcg_update", "camera_update", "reduce_scalars", "gradient_check", "lm_decide"};
 
 // ---------------------------------------------------------------------------------------------
 // setup kernels (device-side construction of the two observation orders)
@@ -207,19 +207,21 @@ __global__ void k_max_track(int n_pts, const int* __restrict__ pt_off, int* __re
     if (p >= n_pts) return;
     atomicMax(out, pt_off[p + 1] - pt_off[p]);
 }
-__global__ void k_pack_points(int n, const double* __restrict__ in3, double* __restrict__ out4) {
+// compact [n*3] <-> slot `buf` (4 doubles) of the 128-byte point records
+__global__ void k_pack_points(int n, const double* __restrict__ in3, double* __restrict__ rec, int buf) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
-    double2* o = reinterpret_cast<double2*>(out4 + (size_t)p * 4);
+    double2* o = reinterpret_cast<double2*>(rec + (size_t)p * PT_REC + 4 * buf);
     o[0] = make_double2(in3[3 * (size_t)p], in3[3 * (size_t)p + 1]);
     o[1] = make_double2(in3[3 * (size_t)p + 2], 0.0);
 }
-__global__ void k_unpack_points(int n, const double* __restrict__ in4, double* __restrict__ out3) {
+__global__ void k_unpack_points(int n, const double* __restrict__ rec, int buf, double* __restrict__ out3) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
-    out3[3 * (size_t)p] = in4[4 * (size_t)p];
-    out3[3 * (size_t)p + 1] = in4[4 * (size_t)p + 1];
-    out3[3 * (size_t)p + 2] = in4[4 * (size_t)p + 2];
+    const double* in4 = rec + (size_t)p * PT_REC + 4 * buf;
+    out3[3 * (size_t)p] = in4[0];
+    out3[3 * (size_t)p + 1] = in4[1];
+    out3[3 * (size_t)p + 2] = in4[2];
 }
 __global__ void k_pack_cams(int n_cams, const double* __restrict__ rvec, const double* __restrict__ tvec,
                             double fr0, double fr1, double fr2, double ft0, double ft1, double ft2, double* __restrict__ rt) {
@@ -288,8 +290,10 @@ struct ba_handle {
     int max_track = 0;
     size_t smem_lin = 0, smem_pass = 0;
 
-    DBuf<double> cam_rt, cam_R, pt_X, pt_V, pt_g, pt_Vinv, pt_h, pt_z, pt_D;
-    DBuf<double> cam_U, cam_g, cam_D, cam_Minv, cam_acc, v_b, v_x, v_r, v_p, v_q;
+    DBuf<double> cam_rt, cam_R, pt_rec, pt_V, pt_g, pt_Vinv, pt_D;
+    DBuf<double> cam_U, cam_g, cam_D, cam_Minv, cam_acc, v_b, v_x, v_r, v_u, v_p, v_s, v_w, dot_partial;
+    DBuf<double> init_cam_rt, init_pts;  // parameters of the last ba_set_problem (for ba_restore_initial)
+    DBuf<int> ticket;
     DBuf<double2> o_uv, pm_uv, cm_uv;
     DBuf<int2> o_idx, pm_idx;
     DBuf<int> pt_off, pm_tile_pt, cm_pt, cam_tile_off;
@@ -303,14 +307,18 @@ struct ba_handle {
     long long launches[KN_COUNT] = {0};
     double kernel_ms[KN_COUNT] = {0};
     bool time_kernels = false;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_solve0 = nullptr, ev_solve1 = nullptr;
+    std::vector<cudaEvent_t> ev_pool;           // pooled events for per-launch timing
+    struct Stamp { int kind; int e0, e1; };
+    std::vector<Stamp> stamps;
+    cudaEvent_t ev_solve0 = nullptr, ev_solve1 = nullptr, ev_user0 = nullptr, ev_user1 = nullptr;
 
     ~ba_handle() {
         if (comm) nccl_api().CommDestroy(comm);
         if (h_state) cudaFreeHost(h_state);
         if (h_flag) cudaFreeHost(h_flag);
-        if (ev0) cudaEventDestroy(ev0);
-        if (ev1) cudaEventDestroy(ev1);
+        for (cudaEvent_t e : ev_pool) cudaEventDestroy(e);
+        if (ev_user0) cudaEventDestroy(ev_user0);
+        if (ev_user1) cudaEventDestroy(ev_user1);
         if (ev_solve0) cudaEventDestroy(ev_solve0);
         if (ev_solve1) cudaEventDestroy(ev_solve1);
         if (stream) cudaStreamDestroy(stream);
@@ -322,17 +330,34 @@ namespace ba {
 template <class... KArgs, class... Args>
 static void launch(ba_handle* h, Kind kind, void (*kernel)(KArgs...), int grid, int block, size_t smem, Args... args) {
     if (grid <= 0) return;
-    if (h->time_kernels) CK(cudaEventRecord(h->ev0, h->stream));
+    int e0 = -1, e1 = -1;
+    if (h->time_kernels) {
+        e0 = (int)h->stamps.size() * 2;
+        e1 = e0 + 1;
+        while ((int)h->ev_pool.size() <= e1) {
+            cudaEvent_t e;
+            CK(cudaEventCreate(&e));
+            h->ev_pool.push_back(e);
+        }
+        CK(cudaEventRecord(h->ev_pool[e0], h->stream));
+    }
     kernel<<<grid, block, smem, h->stream>>>(args...);
     CK(cudaGetLastError());
     h->launches[kind] += 1;
     if (h->time_kernels) {
-        CK(cudaEventRecord(h->ev1, h->stream));
-        CK(cudaEventSynchronize(h->ev1));
-        float ms = 0.f;
-        CK(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
-        h->kernel_ms[kind] += ms;
+        CK(cudaEventRecord(h->ev_pool[e1], h->stream));
+        h->stamps.push_back({(int)kind, e0, e1});
     }
+}
+
+// resolve the pooled per-launch events into per-kind milliseconds (after the stream has drained)
+static void resolve_stamps(ba_handle* h) {
+    for (const auto& st : h->stamps) {
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, h->ev_pool[st.e0], h->ev_pool[st.e1]));
+        h->kernel_ms[st.kind] += ms;
+    }
+    h->stamps.clear();
 }
 
 static inline int cdiv(long long a, int b) { return (int)((a + b - 1) / b); }
@@ -362,12 +387,16 @@ static void create_common(ba_handle* h, int device) {
     CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     CK(cudaMallocHost(&h->h_state, sizeof(LMState)));
     CK(cudaMallocHost(&h->h_flag, sizeof(int)));
-    CK(cudaEventCreate(&h->ev0));
-    CK(cudaEventCreate(&h->ev1));
+    CK(cudaEventCreate(&h->ev_user0));
+    CK(cudaEventCreate(&h->ev_user1));
     CK(cudaEventCreate(&h->ev_solve0));
     CK(cudaEventCreate(&h->ev_solve1));
     h->st.alloc(1);
     h->st.zero(h->stream);
+    h->ticket.alloc(1);
+    h->ticket.zero(h->stream);
+    h->dot_partial.alloc(2 * MAX_VEC_CTAS);
+    h->dot_partial.zero(h->stream);
 }
 
 static void use(ba_handle* h) {
@@ -387,14 +416,18 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     const size_t nc1 = (size_t)n_cams + 1;
 
     h->cam_rt.alloc(2 * nc1 * 6); h->cam_R.alloc(2 * nc1 * 12);
-    h->pt_X.alloc(2 * (size_t)n_pts * 4); h->pt_V.alloc(2 * (size_t)n_pts * 6); h->pt_g.alloc(2 * (size_t)n_pts * 4);
-    h->pt_Vinv.alloc((size_t)n_pts * 6); h->pt_h.alloc((size_t)n_pts * 4); h->pt_z.alloc((size_t)n_pts * 4);
+    h->pt_rec.alloc((size_t)n_pts * PT_REC); h->pt_V.alloc(2 * (size_t)n_pts * 6); h->pt_g.alloc(2 * (size_t)n_pts * 4);
+    h->pt_Vinv.alloc((size_t)n_pts * 6);
     h->pt_D.alloc((size_t)n_pts * 4);
+    h->pt_rec.zero(s);
+    h->init_cam_rt.alloc(nc1 * 6); h->init_pts.alloc((size_t)n_pts * 3);
+    if (cdiv(std::max(n_cams, 1), VEC_THREADS) > MAX_VEC_CTAS) fail(BA_ERR_ARG, "too many cameras (%d)", n_cams);
     const size_t ncz = std::max<size_t>(n_cams, 1);
     h->cam_U.alloc(ncz * 21); h->cam_g.alloc(ncz * 6); h->cam_D.alloc(ncz * 6); h->cam_Minv.alloc(ncz * 36);
     h->cam_acc.alloc(ncz * 27); h->cam_partial.alloc(ncz * NSCAL);
-    h->v_b.alloc(nc1 * 6); h->v_x.alloc(nc1 * 6); h->v_r.alloc(nc1 * 6); h->v_p.alloc(nc1 * 6); h->v_q.alloc(nc1 * 6);
-    h->v_b.zero(s); h->v_x.zero(s); h->v_r.zero(s); h->v_p.zero(s); h->v_q.zero(s);
+    h->v_b.alloc(nc1 * 6); h->v_x.alloc(nc1 * 6); h->v_r.alloc(nc1 * 6); h->v_u.alloc(nc1 * 6);
+    h->v_p.alloc(nc1 * 6); h->v_s.alloc(nc1 * 6); h->v_w.alloc(nc1 * 6);
+    h->v_b.zero(s); h->v_x.zero(s); h->v_r.zero(s); h->v_u.zero(s); h->v_p.zero(s); h->v_s.zero(s); h->v_w.zero(s);
     h->cam_partial.zero(s); h->cam_g.zero(s); h->cam_D.zero(s); h->cam_U.zero(s);
     h->o_uv.alloc(n_obs); h->o_idx.alloc(n_obs); h->pm_uv.alloc(n_obs); h->pm_idx.alloc(n_obs);
     h->cm_uv.alloc(n_obs); h->cm_pt.alloc(n_obs);
@@ -475,23 +508,29 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     h->pm_partial.zero(s);
 
     h->max_track = err_track[1];
-    const int cap = PM_THREADS + h->max_track;
-    h->smem_lin = (size_t)9 * cap * sizeof(double);
-    h->smem_pass = (size_t)3 * cap * sizeof(double);
-    if (h->smem_lin > 227 * 1024)
+    const int cap = (PM_THREADS + h->max_track + 1) & ~1;  // even: keeps the cp.async stage 16-byte aligned
+    h->smem_lin = pm_smem_bytes<9, 6>(cap);
+    h->smem_pass = pm_smem_bytes<3, 9>(cap);
+    const size_t smem_max = 227 * 1024 - 1024;  // static shared memory of the kernels comes on top
+    if (h->smem_lin > smem_max || h->smem_pass > smem_max)
         fail(BA_ERR_ARG, "a point is observed %d times; this build supports track lengths up to %d", h->max_track,
-             (int)(227 * 1024 / 72) - PM_THREADS);
+             (int)((smem_max - pm_smem_bytes<9, 6>(0)) / 72) - PM_THREADS);
     CK(cudaFuncSetAttribute(k_lin_points, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_lin));
     CK(cudaFuncSetAttribute(k_point_pass<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_pass));
     CK(cudaFuncSetAttribute(k_point_pass<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_pass));
+    CK(cudaFuncSetAttribute(k_camera_pass<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cm_smem_bytes<0>()));
+    CK(cudaFuncSetAttribute(k_camera_pass<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cm_smem_bytes<1>()));
+    CK(cudaFuncSetAttribute(k_camera_pass<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cm_smem_bytes<2>()));
 
     // ---- parameters -----------------------------------------------------------------------------
     h->io.alloc(std::max<size_t>((size_t)n_pts * 3, nc1 * 6));
     P.n_obs_adj = n_obs_adj; P.pm_tiles = pm_tiles; P.cm_tiles = cm_tiles; P.pm_cap = cap;
-    P.cam_rt = h->cam_rt.p; P.cam_R = h->cam_R.p; P.pt_X = h->pt_X.p; P.pt_V = h->pt_V.p; P.pt_g = h->pt_g.p;
-    P.pt_Vinv = h->pt_Vinv.p; P.pt_h = h->pt_h.p; P.pt_z = h->pt_z.p; P.pt_D = h->pt_D.p;
+    P.vec_ctas = cdiv(std::max(n_cams, 1), VEC_THREADS);
+    P.cam_rt = h->cam_rt.p; P.cam_R = h->cam_R.p; P.pt_rec = h->pt_rec.p; P.pt_V = h->pt_V.p; P.pt_g = h->pt_g.p;
+    P.pt_Vinv = h->pt_Vinv.p; P.pt_D = h->pt_D.p;
     P.cam_U = h->cam_U.p; P.cam_g = h->cam_g.p; P.cam_D = h->cam_D.p; P.cam_Minv = h->cam_Minv.p; P.cam_acc = h->cam_acc.p;
-    P.v_b = h->v_b.p; P.v_x = h->v_x.p; P.v_r = h->v_r.p; P.v_p = h->v_p.p; P.v_q = h->v_q.p;
+    P.v_b = h->v_b.p; P.v_x = h->v_x.p; P.v_r = h->v_r.p; P.v_u = h->v_u.p; P.v_p = h->v_p.p; P.v_s = h->v_s.p;
+    P.v_w = h->v_w.p; P.dot_partial = h->dot_partial.p;
     P.o_uv = h->o_uv.p; P.o_idx = h->o_idx.p; P.pm_uv = h->pm_uv.p; P.pm_idx = h->pm_idx.p; P.pt_off = h->pt_off.p;
     P.pm_tile_pt = h->pm_tile_pt.p; P.cm_uv = h->cm_uv.p; P.cm_pt = h->cm_pt.p; P.cm_tile = h->cm_tile.p;
     P.cam_tile_off = h->cam_tile_off.p; P.cm_partial = h->cm_partial.p; P.pm_partial = h->pm_partial.p;
@@ -502,7 +541,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
 }
 
 static void set_params(ba_handle* h, const double* rvec, const double* tvec, const double* frv, const double* ftv,
-                       const double* pts) {
+                       const double* pts, bool save_initial = false) {
     // writes parameter buffer 0 and makes it current
     use(h);
     cudaStream_t s = h->stream;
@@ -512,7 +551,9 @@ static void set_params(ba_handle* h, const double* rvec, const double* tvec, con
     CK(cudaMemsetAsync(&h->st.p->cur, 0, sizeof(int), s));
     if (pts) {
         CK(cudaMemcpyAsync(h->io.p, pts, (size_t)P.n_pts * 3 * sizeof(double), cudaMemcpyHostToDevice, s));
-        launch(h, KN_SETUP, k_pack_points, cdiv(P.n_pts, B), B, 0, P.n_pts, (const double*)h->io.p, h->pt_X.p);
+        launch(h, KN_SETUP, k_pack_points, cdiv(P.n_pts, B), B, 0, P.n_pts, (const double*)h->io.p, h->pt_rec.p, 0);
+        if (save_initial)
+            CK(cudaMemcpyAsync(h->init_pts.p, h->io.p, (size_t)P.n_pts * 3 * sizeof(double), cudaMemcpyDeviceToDevice, s));
     }
     if (frv) {
         DBuf<double> tmp;
@@ -523,6 +564,8 @@ static void set_params(ba_handle* h, const double* rvec, const double* tvec, con
         }
         launch(h, KN_SETUP, k_pack_cams, cdiv((int)nc1, B), B, 0, P.n_cams, (const double*)tmp.p,
                (const double*)(tmp.p + (size_t)P.n_cams * 3), frv[0], frv[1], frv[2], ftv[0], ftv[1], ftv[2], h->cam_rt.p);
+        if (save_initial)
+            CK(cudaMemcpyAsync(h->init_cam_rt.p, h->cam_rt.p, nc1 * 6 * sizeof(double), cudaMemcpyDeviceToDevice, s));
         CK(cudaStreamSynchronize(s));
     }
     launch(h, KN_CAM_PREP, k_cam_prepare, cdiv((int)nc1, B), B, 0, P, 0);
@@ -558,7 +601,7 @@ static const unsigned MASK_STEP_CAM = (1u << S_GDC) | (1u << S_DDC) | (1u << S_R
 
 static void reduce_scalars(ba_handle* h, unsigned pm_mask, unsigned cam_mask) {
     const Params& P = h->P;
-    launch(h, KN_REDUCE, k_reduce_scalars, 1, VEC_THREADS, 0, P, pm_mask, cam_mask);
+    launch(h, KN_REDUCE, k_reduce_scalars, 1, RED_THREADS, 0, P, pm_mask, cam_mask);
     if (h->nranks > 1) {
         double* scal = reinterpret_cast<double*>(reinterpret_cast<char*>(h->st.p) + offsetof(LMState, scal));
         allreduce_sum(h, scal, N_PT_SCAL);
@@ -569,7 +612,7 @@ static void reduce_scalars(ba_handle* h, unsigned pm_mask, unsigned cam_mask) {
 static void lin_cameras(ba_handle* h, double dmin, double dmax) {
     const Params& P = h->P;
     if (P.n_cams == 0) return;
-    launch(h, KN_LIN_CAM, k_camera_pass<0>, P.cm_tiles, CM_THREADS, 0, P, (const double*)nullptr, 0);
+    launch(h, KN_LIN_CAM, k_camera_pass<0>, P.cm_tiles, CM_THREADS, cm_smem_bytes<0>(), P, (const double*)nullptr, 0);
     launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 27, 256), 256, 0, P, 27, 0);
     allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 27);
     launch(h, KN_CAM_FIN, k_camera_finish_lin, cdiv(P.n_cams, 128), 128, 0, P, dmin, dmax);
@@ -604,21 +647,25 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     while (status == 0) {
         if (need_lin) {
             lin_cameras(h, kDiagMin, kDiagMax);
-            launch(h, KN_GRAD, k_gradient_check, 1, VEC_THREADS, 0, P, opt->gtol);
+            launch(h, KN_GRAD, k_gradient_check, 1, RED_THREADS, 0, P, opt->gtol);
         }
         launch(h, KN_PT_PREP, k_point_prepare, cdiv(P.n_pts, 256), 256, 0, P, kDiagMin, kDiagMax);
         if (P.n_cams > 0) {
-            launch(h, KN_SCHUR_CAM, k_camera_pass<1>, P.cm_tiles, CM_THREADS, 0, P, (const double*)nullptr, with_schur);
+            launch(h, KN_SCHUR_CAM, k_camera_pass<1>, P.cm_tiles, CM_THREADS, cm_smem_bytes<1>(), P, (const double*)nullptr, with_schur);
             launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 27, 256), 256, 0, P, 27, 0);
             allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 27);
-            launch(h, KN_CAM_FIN, k_camera_finish_schur, cdiv(P.n_cams, 128), 128, 0, P, with_schur);
-            launch(h, KN_PCG_INIT, k_pcg_init, 1, VEC_THREADS, 0, P);
+            launch(h, KN_CAM_FIN, k_camera_finish_schur, P.vec_ctas, VEC_THREADS, 0, P, with_schur, h->ticket.p);
             for (int it = 0; it < opt->pcg_max_iters; ++it) {
-                launch(h, KN_PT_PASS, k_point_pass<0>, P.pm_tiles, PM_THREADS, h->smem_pass, P, (const double*)h->v_p.p);
-                launch(h, KN_MATVEC_CAM, k_camera_pass<2>, P.cm_tiles, CM_THREADS, 0, P, (const double*)h->v_p.p, 0);
-                launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 6, 256), 256, 0, P, 6, 1);
-                allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 6);
-                launch(h, KN_PCG_UPDATE, k_pcg_update, 1, VEC_THREADS, 0, P, opt->pcg_tol, opt->pcg_max_iters);
+                launch(h, KN_PT_PASS, k_point_pass<0>, P.pm_tiles, PM_THREADS, h->smem_pass, P, (const double*)h->v_u.p);
+                launch(h, KN_MATVEC_CAM, k_camera_pass<2>, P.cm_tiles, CM_THREADS, cm_smem_bytes<2>(), P, (const double*)h->v_u.p, 0);
+                if (h->nranks > 1) {
+                    launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 6, 256), 256, 0, P, 6, 1);
+                    allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 6);
+                    launch(h, KN_PCG_DOTS, k_pcg_dots<false>, P.vec_ctas, VEC_THREADS, 0, P);
+                } else {
+                    launch(h, KN_PCG_DOTS, k_pcg_dots<true>, P.vec_ctas, VEC_THREADS, 0, P);
+                }
+                launch(h, KN_PCG_UPDATE, k_pcg_update, P.vec_ctas, VEC_THREADS, 0, P, opt->pcg_tol, opt->pcg_max_iters, h->ticket.p);
                 if ((it + 1) % check_every == 0 && it + 1 < opt->pcg_max_iters) {
                     CK(cudaMemcpyAsync(h->h_flag, &h->st.p->pcg_done, sizeof(int), cudaMemcpyDeviceToHost, s));
                     CK(cudaStreamSynchronize(s));
@@ -635,7 +682,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
         const LMState& st = *h->h_state;
         status = st.status;
         need_lin = st.last_accepted != 0;
-        if (opt->verbose)
+        if (opt->verbose & 1)
             fprintf(stderr, "[ba_b200] it %3d %s cost %.9e -> trial %.9e  rho %+.3e  lambda %.3e  pcg %d  |g| %.3e  |dx| %.3e\n",
                     st.iter, st.last_accepted ? "acc" : "REJ", st.cost[st.cur ^ (st.last_accepted ? 1 : 0)], st.scal[S_COST], st.rho,
                     st.lambda, st.pcg_iter, st.gmax, st.step_norm);
@@ -645,6 +692,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     CK(cudaEventSynchronize(h->ev_solve1));
     float ms = 0.f;
     CK(cudaEventElapsedTime(&ms, h->ev_solve0, h->ev_solve1));
+    if (h->time_kernels) resolve_stamps(h);
     h->time_kernels = false;
     if (out) {
         const LMState& st = *h->h_state;
@@ -689,7 +737,7 @@ void ba_default_options(ba_options* o) {
     o->max_iters = 50;
     o->gtol = 1e-8; o->ftol = 1e-6; o->xtol = 1e-8;
     o->huber_delta = 1.0; o->robust_mode = BA_ROBUST_IRLS;
-    o->initial_lambda = 1e-4; o->lambda_min = 1e-12; o->lambda_max = 1e16;
+    o->initial_lambda = 1e-4; o->lambda_min = 1e-6; o->lambda_max = 1e16;
     o->precond = BA_PRECOND_SCHUR_JACOBI;
     o->pcg_max_iters = 100; o->pcg_tol = 0.1; o->pcg_check_every = 4;
     o->verbose = 0;
@@ -756,7 +804,7 @@ int ba_set_problem(ba_handle* h, double fx, double fy, double cx, double cy, int
                    const double* pts, const int32_t* obs_cam, const int32_t* obs_pt, const double* obs_uv) {
     API_BEGIN
     ba::set_problem(h, fx, fy, cx, cy, n_adj_cams, n_pts, n_obs, rvec, tvec, fixed_rvec, fixed_tvec, pts, obs_cam, obs_pt, obs_uv);
-    ba::set_params(h, rvec, tvec, fixed_rvec, fixed_tvec, pts);
+    ba::set_params(h, rvec, tvec, fixed_rvec, fixed_tvec, pts, /*save_initial=*/true);
     API_END
 }
 
@@ -783,7 +831,7 @@ int ba_get_params(ba_handle* h, double* rvec, double* tvec, double* pts) {
     const int b = h->h_state->cur;
     if (pts) {
         ba::launch(h, ba::KN_SETUP, ba::k_unpack_points, ba::cdiv(P.n_pts, 256), 256, 0, P.n_pts,
-                   (const double*)(h->pt_X.p + (size_t)b * P.n_pts * 4), h->io.p);
+                   (const double*)h->pt_rec.p, b, h->io.p);
         CK(cudaMemcpyAsync(pts, h->io.p, (size_t)P.n_pts * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
         CK(cudaStreamSynchronize(s));
     }
@@ -796,6 +844,38 @@ int ba_get_params(ba_handle* h, double* rvec, double* tvec, double* pts) {
         if (tvec) CK(cudaMemcpyAsync(tvec, tmp.p + (size_t)P.n_cams * 3, (size_t)P.n_cams * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
         CK(cudaStreamSynchronize(s));
     }
+    API_END
+}
+
+int ba_restore_initial(ba_handle* h) {
+    API_BEGIN
+    ba::need_problem(h);
+    const ba::Params& P = h->P;
+    cudaStream_t s = h->stream;
+    const size_t nc1 = (size_t)P.n_cams + 1;
+    CK(cudaMemsetAsync(&h->st.p->cur, 0, sizeof(int), s));
+    CK(cudaMemcpyAsync(h->cam_rt.p, h->init_cam_rt.p, nc1 * 6 * sizeof(double), cudaMemcpyDeviceToDevice, s));
+    ba::launch(h, ba::KN_SETUP, ba::k_pack_points, ba::cdiv(P.n_pts, 256), 256, 0, P.n_pts, (const double*)h->init_pts.p,
+               h->pt_rec.p, 0);
+    ba::launch(h, ba::KN_CAM_PREP, ba::k_cam_prepare, ba::cdiv((int)nc1, 256), 256, 0, P, 0);
+    API_END
+}
+
+int ba_timer_start(ba_handle* h) {
+    API_BEGIN
+    ba::use(h);
+    CK(cudaEventRecord(h->ev_user0, h->stream));
+    API_END
+}
+
+int ba_timer_stop(ba_handle* h, double* ms_out) {
+    API_BEGIN
+    ba::use(h);
+    CK(cudaEventRecord(h->ev_user1, h->stream));
+    CK(cudaEventSynchronize(h->ev_user1));
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, h->ev_user0, h->ev_user1));
+    if (ms_out) *ms_out = ms;
     API_END
 }
 

@@ -104,6 +104,20 @@ class FlatSolver:
         x = api.f64(x).ravel()
         self.set_params(x[:3 * nc], x[3 * nc:6 * nc], x[6 * nc:])
 
+    def restore_initial(self):
+        """Device-side reset to the parameters of the last ``set_problem``."""
+        self._need()
+        api.check(api.lib().ba_restore_initial(self._h))
+
+    def timer_start(self):
+        api.check(api.lib().ba_timer_start(self._h))
+
+    def timer_stop(self) -> float:
+        """Milliseconds of device time since ``timer_start`` on the solver's stream (CUDA events)."""
+        ms = C.c_double()
+        api.check(api.lib().ba_timer_stop(self._h, C.byref(ms)))
+        return ms.value
+
     def get_params(self):
         nc, npt, _ = self._need()
         rvec, tvec, pts = np.empty((nc, 3)), np.empty((nc, 3)), np.empty((npt, 3))

@@ -58,7 +58,7 @@ typedef struct ba_options {
     int32_t pcg_max_iters;    /* per LM iteration                                                   */
     double pcg_tol;           /* forcing term: stop PCG when |r|_M^-1 <= pcg_tol * |b|_M^-1          */
     int32_t pcg_check_every;  /* host polls the device "PCG converged" flag every this many iterations */
-    int32_t verbose;          /* 1: one stderr line per LM iteration                                */
+    int32_t verbose;          /* bit 0: one stderr line per LM iteration; >= 2: per-kernel event timing */
     int32_t reserved[7];
 } ba_options;
 
@@ -78,7 +78,8 @@ typedef struct ba_stats {
     double reserved[8];
 } ba_stats;
 
-/* Defaults: max_iters 50, gtol 1e-8, ftol 1e-6, xtol 1e-8, huber 1.0, IRLS, lambda 1e-4, Schur-Jacobi PCG. */
+/* Defaults: max_iters 50, gtol 1e-8, ftol 1e-6, xtol 1e-8, huber 1.0, IRLS, lambda 1e-4 (floor 1e-6: keeps the
+ * step bounded along the free scale gauge and along low-parallax depth directions), Schur-Jacobi PCG, tol 0.1. */
 void ba_default_options(ba_options* opt);
 
 /* One handle = one GPU + one CUDA stream.  `device` is a CUDA ordinal.  Replaces nothing in the
@@ -112,6 +113,15 @@ int ba_set_problem(ba_handle* h, double fx, double fy, double cx, double cy,
 int ba_set_params(ba_handle* h, const double* rvec, const double* tvec, const double* pts);
 int ba_get_params(ba_handle* h, double* rvec, double* tvec, double* pts);
 
+/* Device-side reset: make the parameters uploaded by the last ba_set_problem current again (a
+ * device-to-device copy; used to repeat a solve without re-uploading). */
+int ba_restore_initial(ba_handle* h);
+
+/* CUDA-event stopwatch on the handle's stream: everything enqueued between start and stop is timed on
+ * the device.  ba_timer_stop synchronises and returns milliseconds. */
+int ba_timer_start(ba_handle* h);
+int ba_timer_stop(ba_handle* h, double* ms_out);
+
 /* r_out[2*n_obs] in the reference's observation order.  Replaces _cost_function
  * (src/bundle_adjuster.py:24-72). */
 int ba_residuals(ba_handle* h, double* r_out);
@@ -143,8 +153,9 @@ int ba_normal_blocks(ba_handle* h, const ba_options* opt, double* gc, double* gp
 int ba_solve(ba_handle* h, const ba_options* opt, ba_stats* stats_out);
 
 /* Per-kernel accounting of the last ba_solve: for each of the `n` kernel kinds (ba_kernel_name(k)),
- * number of launches and summed CUDA-event milliseconds (only filled when opt->verbose >= 2, which
- * serialises the launches; otherwise launches only). */
+ * number of launches and summed CUDA-event milliseconds.  Times are filled when opt->verbose >= 2:
+ * every launch is bracketed by a pair of pooled CUDA events on the solver stream (no synchronisation
+ * between launches; resolved at the end of the solve).  Otherwise launch counts only. */
 int ba_kernel_count(void);
 const char* ba_kernel_name(int k);
 int ba_kernel_stats(ba_handle* h, int64_t* launches /* [n] */, double* ms /* [n] */);

@@ -137,7 +137,7 @@ def test_lm_iterates_match_cpu_restatement(gpu_solver):
     fp = S.make_flat_problem(6, 300, 1200, seed=3)
     prob = O.Problem.from_flat(fp)
     gpu_solver.set_flat(fp)
-    st = gpu_solver.solve(max_iters=6, pcg_tol=1e-12, pcg_max_iters=500, ftol=0.0, xtol=0.0, gtol=0.0)
+    st = gpu_solver.solve(max_iters=6, pcg_tol=1e-12, pcg_max_iters=500, ftol=0.0, xtol=0.0, gtol=0.0, lambda_min=1e-12)
     ref = L.solve(prob, fp.rvec, fp.tvec, fp.pts, max_iters=6, ftol=0.0, gtol=0.0)
     assert st["iterations"] == 6
     assert abs(st["final_cost"] - ref.cost) <= 1e-9 * ref.cost
@@ -153,7 +153,8 @@ def test_converged_cost_against_reference_objective(gpu_solver, name):
     Jacobian + exact trust-region sub-problems, tier T2) to 1e-6 relative."""
     g, spec, flat, prob = _golden_problem(name)
     _upload(gpu_solver, prob, flat)
-    st = gpu_solver.solve(max_iters=1500, ftol=1e-13, xtol=0.0, gtol=1e-9, pcg_tol=1e-3, pcg_max_iters=300)
+    st = gpu_solver.solve(max_iters=1000, ftol=1e-13, xtol=0.0, gtol=1e-9, pcg_tol=1e-6, pcg_max_iters=300,
+                          lambda_min=1e-9)
     assert st["final_cost"] <= float(g["res_cost"])
     assert st["final_cost"] <= float(g["tight_cost"])
     x = gpu_solver.get_x()
@@ -170,10 +171,14 @@ def test_converged_cost_against_reference_objective(gpu_solver, name):
         a, b = centred(x), centred(conv.x)
         na, nb_ = np.linalg.norm(a, axis=1), np.linalg.norm(b, axis=1)
         scale = float(np.median(nb_ / na))                 # robust: a few low-parallax points sit far out in depth
-        assert abs(scale - 1.0) < 5e-2
+        # one fixed camera leaves the global scale free (the cost is exactly invariant), and the two solvers
+        # walk differently along that orbit: only the aligned shapes are comparable
+        assert np.isfinite(scale) and scale > 0.0
         err = np.linalg.norm(a * scale - b, axis=1) / nb_
-        assert np.median(err) <= 1e-2 and np.mean(err <= 5e-2) >= 0.9, (np.median(err), np.mean(err <= 5e-2))
-        assert np.abs(x[:3 * nc] - conv.x[:3 * nc]).max() <= 1e-3
+        # well-determined points agree to ~1e-6; the few low-parallax / outlier-only points sit on a flat valley
+        # of the Huber cost (depth undetermined) and are excluded by the quantile
+        assert np.median(err) <= 1e-4 and np.mean(err <= 1e-3) >= 0.75, (np.median(err), np.mean(err <= 1e-3))
+        assert np.abs(x[:3 * nc] - conv.x[:3 * nc]).max() <= 1e-3      # rotations do not depend on the gauge
 
 
 def test_solver_beats_reference_settings_on_bal_shape(gpu_solver):
