@@ -130,18 +130,49 @@ static const char* kKindNames[KN_COUNT] = {
 // ---------------------------------------------------------------------------------------------
 // setup kernels (device-side construction of the two observation orders)
 // ---------------------------------------------------------------------------------------------
-__global__ void k_setup_keys(int n_obs, int n_cams, int n_pts, const int* __restrict__ obs_cam,
-                             const int* __restrict__ obs_pt, int2* __restrict__ o_idx, unsigned* __restrict__ key_pt,
-                             unsigned long long* __restrict__ key_cam, int* __restrict__ iota, int* __restrict__ err) {
+// Locality ordering of the points (internal ids): a point's key is the centroid of the cameras that
+// observe it (the fixed keyframe is the oldest, so it counts as camera 0 and adjustable camera c as
+// c + 1).  Points seen by the same cameras become neighbours, so a point-major tile touches few
+// distinct cameras and a camera's observations touch a narrow range of points.  Integer atomics only
+// (order-independent, deterministic).
+__global__ void k_point_cam_sums(int n_obs, int n_cams, int n_pts, const int* __restrict__ obs_cam,
+                                 const int* __restrict__ obs_pt, unsigned long long* __restrict__ sum,
+                                 unsigned* __restrict__ cnt, int* __restrict__ err) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_obs) return;
     const int c = obs_cam[i], p = obs_pt[i];
+    if (c < -1 || c >= n_cams || p < 0 || p >= n_pts) { atomicOr(err, 1); return; }
+    atomicAdd(sum + p, (unsigned long long)(c + 1));
+    atomicAdd(cnt + p, 1u);
+}
+__global__ void k_point_keys(int n_pts, const unsigned long long* __restrict__ sum, const unsigned* __restrict__ cnt,
+                             unsigned* __restrict__ key, int* __restrict__ iota) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pts) return;
+    const unsigned n = cnt[p];
+    key[p] = n ? (unsigned)((sum[p] * 8ull) / n) : 0xffffffffu;  // unobserved points last
+    iota[p] = p;
+}
+__global__ void k_invert_perm(int n, const int* __restrict__ perm, int* __restrict__ inv) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q < n) inv[perm[q]] = q;
+}
+
+__global__ void k_setup_keys(int n_obs, int n_cams, int n_pts, const int* __restrict__ obs_cam,
+                             const int* __restrict__ obs_pt, const int* __restrict__ pt_inv, int2* __restrict__ o_idx,
+                             unsigned* __restrict__ key_pt, unsigned long long* __restrict__ key_cam,
+                             int* __restrict__ iota, int* __restrict__ err) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_obs) return;
+    const int c = obs_cam[i];
+    int p = obs_pt[i];
     if (c < -1 || c >= n_cams || p < 0 || p >= n_pts) {
         atomicOr(err, 1);
         o_idx[i] = make_int2(n_cams, 0);
         key_pt[i] = 0; key_cam[i] = ((unsigned long long)n_cams << 32); iota[i] = i;
         return;
     }
+    p = pt_inv[p];  // internal (locality-ordered) point id
     const int slot = c < 0 ? n_cams : c;
     o_idx[i] = make_int2(slot, p);
     key_pt[i] = (unsigned)p;
@@ -208,20 +239,23 @@ __global__ void k_max_track(int n_pts, const int* __restrict__ pt_off, int* __re
     atomicMax(out, pt_off[p + 1] - pt_off[p]);
 }
 // compact [n*3] <-> slot `buf` (4 doubles) of the 128-byte point records
-__global__ void k_pack_points(int n, const double* __restrict__ in3, double* __restrict__ rec, int buf) {
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= n) return;
-    double2* o = reinterpret_cast<double2*>(rec + (size_t)p * PT_REC + 4 * buf);
-    o[0] = make_double2(in3[3 * (size_t)p], in3[3 * (size_t)p + 1]);
-    o[1] = make_double2(in3[3 * (size_t)p + 2], 0.0);
+// `perm[q]` = caller's index of internal point q
+__global__ void k_pack_points(int n, const int* __restrict__ perm, const double* __restrict__ in3, double* __restrict__ rec, int buf) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n) return;
+    const size_t p = (size_t)perm[q];
+    double2* o = reinterpret_cast<double2*>(rec + (size_t)q * PT_REC + 4 * buf);
+    o[0] = make_double2(in3[3 * p], in3[3 * p + 1]);
+    o[1] = make_double2(in3[3 * p + 2], 0.0);
 }
-__global__ void k_unpack_points(int n, const double* __restrict__ rec, int buf, double* __restrict__ out3) {
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= n) return;
-    const double* in4 = rec + (size_t)p * PT_REC + 4 * buf;
-    out3[3 * (size_t)p] = in4[0];
-    out3[3 * (size_t)p + 1] = in4[1];
-    out3[3 * (size_t)p + 2] = in4[2];
+__global__ void k_unpack_points(int n, const int* __restrict__ perm, const double* __restrict__ rec, int buf, double* __restrict__ out3) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n) return;
+    const size_t p = (size_t)perm[q];
+    const double* in4 = rec + (size_t)q * PT_REC + 4 * buf;
+    out3[3 * p] = in4[0];
+    out3[3 * p + 1] = in4[1];
+    out3[3 * p + 2] = in4[2];
 }
 __global__ void k_pack_cams(int n_cams, const double* __restrict__ rvec, const double* __restrict__ tvec,
                             double fr0, double fr1, double fr2, double ft0, double ft1, double ft2, double* __restrict__ rt) {
@@ -242,8 +276,9 @@ __global__ void k_sparsity_counts(int n_obs, int n_cams, const int2* __restrict_
     if (i >= n_obs) return;
     cnt[i] = (o_idx[i].x < n_cams) ? 18 : 6;
 }
-__global__ void k_sparsity_fill(int n_obs, int n_cams, const int2* __restrict__ o_idx, const long long* __restrict__ start,
-                                long long* __restrict__ indptr, long long* __restrict__ indices) {
+__global__ void k_sparsity_fill(int n_obs, int n_cams, const int2* __restrict__ o_idx, const int* __restrict__ pt_perm,
+                                const long long* __restrict__ start, long long* __restrict__ indptr,
+                                long long* __restrict__ indices) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_obs) return;
     const int2 id = o_idx[i];
@@ -261,7 +296,8 @@ __global__ void k_sparsity_fill(int n_obs, int n_cams, const int2* __restrict__ 
             for (int k = 0; k < 3; ++k) o[q++] = 3LL * id.x + k;
             for (int k = 0; k < 3; ++k) o[q++] = 3LL * n_cams + 3LL * id.x + k;
         }
-        for (int k = 0; k < 3; ++k) o[q++] = 6LL * n_cams + 3LL * id.y + k;
+        const long long p = pt_perm[id.y];  // the caller's point index
+        for (int k = 0; k < 3; ++k) o[q++] = 6LL * n_cams + 3LL * p + k;
     }
 }
 __global__ void k_init_state(LMState* st, double lambda) {
@@ -297,6 +333,7 @@ struct ba_handle {
     DBuf<double2> o_uv, pm_uv, cm_uv;
     DBuf<int2> o_idx, pm_idx;
     DBuf<int> pt_off, pm_tile_pt, cm_pt, cam_tile_off;
+    DBuf<int> pt_perm;  // internal (locality-ordered) point id -> caller's point index
     DBuf<int4> cm_tile;
     DBuf<double> cm_partial, pm_partial, cam_partial;
     DBuf<LMState> st;
@@ -452,19 +489,40 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     P.n_cams = n_cams; P.n_pts = n_pts; P.n_obs = n_obs;
 
     const int B = 256;
-    launch(h, KN_SETUP, k_setup_keys, cdiv(n_obs, B), B, 0, n_obs, n_cams, n_pts, (const int*)d_cam.p, (const int*)d_pt.p,
-           h->o_idx.p, d_kpt.p, d_kcam.p, d_iota.p, d_err.p);
-
-    // ---- point-major order: stable radix sort of (point, original index) ----------------------
     int pt_bits = 1;
     while ((1LL << pt_bits) < n_pts) ++pt_bits;
-    size_t tmp_bytes = 0, tb2 = 0;
-    CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, d_kpt.p, d_kpt_s.p, d_iota.p, d_perm.p, n_obs, 0, pt_bits, s));
     int cam_bits = 1;
     while ((1LL << cam_bits) < (long long)n_cams + 1) ++cam_bits;
+    size_t tmp_bytes = 0, tb2 = 0, tb3 = 0;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, d_kpt.p, d_kpt_s.p, d_iota.p, d_perm.p, n_obs, 0, pt_bits, s));
     CK(cub::DeviceRadixSort::SortPairs(nullptr, tb2, d_kcam.p, d_kcam_s.p, d_iota.p, d_perm.p, n_obs, 0, 32 + cam_bits, s));
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, tb3, d_kpt.p, d_kpt_s.p, d_iota.p, d_perm.p, n_pts, 0, 32, s));
     DBuf<unsigned char> d_tmp;
-    d_tmp.alloc(std::max(tmp_bytes, tb2));
+    d_tmp.alloc(std::max(std::max(tmp_bytes, tb2), tb3));
+
+    // ---- locality order of the points: stable sort by camera centroid ----------------------------
+    h->pt_perm.alloc(n_pts);
+    {
+        DBuf<unsigned long long> d_sum;
+        DBuf<unsigned> d_cnt, d_key, d_key_s;
+        DBuf<int> d_pi;
+        d_sum.alloc(n_pts); d_cnt.alloc(n_pts); d_key.alloc(n_pts); d_key_s.alloc(n_pts); d_pi.alloc(n_pts);
+        d_sum.zero(s); d_cnt.zero(s);
+        launch(h, KN_SETUP, k_point_cam_sums, cdiv(n_obs, B), B, 0, n_obs, n_cams, n_pts, (const int*)d_cam.p,
+               (const int*)d_pt.p, d_sum.p, d_cnt.p, d_err.p);
+        launch(h, KN_SETUP, k_point_keys, cdiv(n_pts, B), B, 0, n_pts, (const unsigned long long*)d_sum.p,
+               (const unsigned*)d_cnt.p, d_key.p, d_pi.p);
+        tmp_bytes = d_tmp.n;
+        CK(cub::DeviceRadixSort::SortPairs(d_tmp.p, tmp_bytes, d_key.p, d_key_s.p, d_pi.p, h->pt_perm.p, n_pts, 0, 32, s));
+        h->launches[KN_SETUP] += 1;
+        launch(h, KN_SETUP, k_invert_perm, cdiv(n_pts, B), B, 0, n_pts, (const int*)h->pt_perm.p, d_pi.p);
+        // d_pi = caller's index -> internal id
+        launch(h, KN_SETUP, k_setup_keys, cdiv(n_obs, B), B, 0, n_obs, n_cams, n_pts, (const int*)d_cam.p, (const int*)d_pt.p,
+               (const int*)d_pi.p, h->o_idx.p, d_kpt.p, d_kcam.p, d_iota.p, d_err.p);
+        CK(cudaStreamSynchronize(s));  // the scratch buffers of this block die here
+    }
+
+    // ---- point-major order: stable radix sort of (internal point, original index) ----------------
     tmp_bytes = d_tmp.n;
     CK(cub::DeviceRadixSort::SortPairs(d_tmp.p, tmp_bytes, d_kpt.p, d_kpt_s.p, d_iota.p, d_perm.p, n_obs, 0, pt_bits, s));
     h->launches[KN_SETUP] += 1;
@@ -551,7 +609,8 @@ static void set_params(ba_handle* h, const double* rvec, const double* tvec, con
     CK(cudaMemsetAsync(&h->st.p->cur, 0, sizeof(int), s));
     if (pts) {
         CK(cudaMemcpyAsync(h->io.p, pts, (size_t)P.n_pts * 3 * sizeof(double), cudaMemcpyHostToDevice, s));
-        launch(h, KN_SETUP, k_pack_points, cdiv(P.n_pts, B), B, 0, P.n_pts, (const double*)h->io.p, h->pt_rec.p, 0);
+        launch(h, KN_SETUP, k_pack_points, cdiv(P.n_pts, B), B, 0, P.n_pts, (const int*)h->pt_perm.p, (const double*)h->io.p,
+               h->pt_rec.p, 0);
         if (save_initial)
             CK(cudaMemcpyAsync(h->init_pts.p, h->io.p, (size_t)P.n_pts * 3 * sizeof(double), cudaMemcpyDeviceToDevice, s));
     }
@@ -830,7 +889,7 @@ int ba_get_params(ba_handle* h, double* rvec, double* tvec, double* pts) {
     ba::read_state(h);
     const int b = h->h_state->cur;
     if (pts) {
-        ba::launch(h, ba::KN_SETUP, ba::k_unpack_points, ba::cdiv(P.n_pts, 256), 256, 0, P.n_pts,
+        ba::launch(h, ba::KN_SETUP, ba::k_unpack_points, ba::cdiv(P.n_pts, 256), 256, 0, P.n_pts, (const int*)h->pt_perm.p,
                    (const double*)h->pt_rec.p, b, h->io.p);
         CK(cudaMemcpyAsync(pts, h->io.p, (size_t)P.n_pts * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
         CK(cudaStreamSynchronize(s));
@@ -855,8 +914,8 @@ int ba_restore_initial(ba_handle* h) {
     const size_t nc1 = (size_t)P.n_cams + 1;
     CK(cudaMemsetAsync(&h->st.p->cur, 0, sizeof(int), s));
     CK(cudaMemcpyAsync(h->cam_rt.p, h->init_cam_rt.p, nc1 * 6 * sizeof(double), cudaMemcpyDeviceToDevice, s));
-    ba::launch(h, ba::KN_SETUP, ba::k_pack_points, ba::cdiv(P.n_pts, 256), 256, 0, P.n_pts, (const double*)h->init_pts.p,
-               h->pt_rec.p, 0);
+    ba::launch(h, ba::KN_SETUP, ba::k_pack_points, ba::cdiv(P.n_pts, 256), 256, 0, P.n_pts, (const int*)h->pt_perm.p,
+               (const double*)h->init_pts.p, h->pt_rec.p, 0);
     ba::launch(h, ba::KN_CAM_PREP, ba::k_cam_prepare, ba::cdiv((int)nc1, 256), 256, 0, P, 0);
     API_END
 }
@@ -944,7 +1003,7 @@ int ba_sparsity_csr(ba_handle* h, int64_t* indptr, int64_t* indices, int64_t* nn
     if (indptr || indices) {
         if (indices) d_indices.alloc((size_t)nnz);
         ba::launch(h, ba::KN_SETUP, ba::k_sparsity_fill, ba::cdiv(P.n_obs, 256), 256, 0, P.n_obs, P.n_cams, P.o_idx,
-                   (const long long*)start.p, d_indptr.p, indices ? d_indices.p : (long long*)nullptr);
+                   (const int*)h->pt_perm.p, (const long long*)start.p, d_indptr.p, indices ? d_indices.p : (long long*)nullptr);
         if (indptr) CK(cudaMemcpyAsync(indptr, d_indptr.p, d_indptr.n * sizeof(long long), cudaMemcpyDeviceToHost, s));
         if (indices) CK(cudaMemcpyAsync(indices, d_indices.p, (size_t)nnz * sizeof(long long), cudaMemcpyDeviceToHost, s));
         CK(cudaStreamSynchronize(s));
@@ -967,6 +1026,8 @@ int ba_normal_blocks(ba_handle* h, const ba_options* opt, double* gc, double* gp
     const int b = h->h_state->cur;
     if (gc && P.n_cams) CK(cudaMemcpyAsync(gc, h->cam_g.p, (size_t)P.n_cams * 6 * sizeof(double), cudaMemcpyDeviceToHost, s));
     std::vector<double> u21, v6, g4;
+    std::vector<int> perm((size_t)P.n_pts);
+    CK(cudaMemcpyAsync(perm.data(), h->pt_perm.p, perm.size() * sizeof(int), cudaMemcpyDeviceToHost, s));
     if (U && P.n_cams) {
         u21.resize((size_t)P.n_cams * 21);
         CK(cudaMemcpyAsync(u21.data(), h->cam_U.p, u21.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
@@ -989,16 +1050,16 @@ int ba_normal_blocks(ba_handle* h, const ba_options* opt, double* gc, double* gp
                     U[(size_t)c * 36 + 6 * j + i] = v;
                 }
     if (V)
-        for (int p = 0; p < P.n_pts; ++p)
+        for (int q = 0; q < P.n_pts; ++q)
             for (int i = 0; i < 3; ++i)
                 for (int j = i; j < 3; ++j) {
-                    const double v = v6[(size_t)p * 6 + ba::sym3(i, j)];
-                    V[(size_t)p * 9 + 3 * i + j] = v;
-                    V[(size_t)p * 9 + 3 * j + i] = v;
+                    const double v = v6[(size_t)q * 6 + ba::sym3(i, j)];
+                    V[(size_t)perm[q] * 9 + 3 * i + j] = v;
+                    V[(size_t)perm[q] * 9 + 3 * j + i] = v;
                 }
     if (gp)
-        for (int p = 0; p < P.n_pts; ++p)
-            for (int k = 0; k < 3; ++k) gp[(size_t)p * 3 + k] = g4[(size_t)p * 4 + k];
+        for (int q = 0; q < P.n_pts; ++q)
+            for (int k = 0; k < 3; ++k) gp[(size_t)perm[q] * 3 + k] = g4[(size_t)q * 4 + k];
     API_END
 }
 
