@@ -16,6 +16,7 @@ LIB_PATH = os.path.join(_HERE, "libba_b200.so")
 
 ROBUST = {"none": 0, "irls": 1, "triggs": 2}
 PRECOND = {"jacobi": 0, "schur_jacobi": 1}
+SCHUR_PATH = {"tiles": 0, "two_pass": 1}
 STATUS_TEXT = {0: "iteration limit", 1: "gtol", 2: "ftol", 3: "xtol", 4: "ftol and xtol", 5: "damping limit"}
 
 
@@ -30,7 +31,7 @@ class Options(C.Structure):
                 ("huber_delta", C.c_double), ("robust_mode", C.c_int32), ("initial_lambda", C.c_double),
                 ("lambda_min", C.c_double), ("lambda_max", C.c_double), ("precond", C.c_int32),
                 ("pcg_max_iters", C.c_int32), ("pcg_tol", C.c_double), ("pcg_check_every", C.c_int32),
-                ("verbose", C.c_int32), ("reserved", C.c_int32 * 7)]
+                ("verbose", C.c_int32), ("schur_path", C.c_int32), ("reserved", C.c_int32 * 6)]
 
 
 class Stats(C.Structure):
@@ -71,10 +72,13 @@ SYMBOLS = {
     "ba_jacobian_blocks": (C.c_int, [C.c_void_p, _dp, _dp]),
     "ba_sparsity_csr": (C.c_int, [C.c_void_p, _lp, _lp, _lp]),
     "ba_normal_blocks": (C.c_int, [C.c_void_p, C.POINTER(Options), _dp, _dp, _dp, _dp]),
+    "ba_schur_matvec": (C.c_int, [C.c_void_p, C.POINTER(Options), C.c_double, _dp, _dp]),
     "ba_solve": (C.c_int, [C.c_void_p, C.POINTER(Options), C.POINTER(Stats)]),
     "ba_kernel_count": (C.c_int, []),
     "ba_kernel_name": (C.c_char_p, [C.c_int]),
     "ba_kernel_stats": (C.c_int, [C.c_void_p, _lp, _dp]),
+    "ba_layout_info": (C.c_int, [C.c_void_p, _lp]),
+    "ba_tile_layout": (C.c_int, [C.c_void_p, _ip, _ip, _ip, C.POINTER(C.c_uint32), _dp, _ip, _ip, _ip, _ip, _ip]),
     "ba_last_error": (C.c_char_p, []),
 }
 

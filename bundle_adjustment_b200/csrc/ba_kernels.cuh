@@ -36,10 +36,8 @@ constexpr int CM_THREADS = 256;  // camera-major CTA
 constexpr int CM_ROUNDS = 4;     // observations per thread in a camera-major tile
 constexpr int CM_TILE = CM_THREADS * CM_ROUNDS;
 constexpr int NSCAL = 16;        // per-iteration scalar slots
-constexpr int PT_REC = 16;       // doubles per point record: X(buf 0) | X(buf 1) | z | h, 4 each = 128 B
-constexpr int PR_Z = 8, PR_H = 12;
 constexpr int VEC_THREADS = 128; // camera-vector kernels: one camera per thread
-constexpr int MAX_VEC_CTAS = 1024;
+constexpr int MAX_VEC_CTAS = 8192;
 
 // scalar slots (partials are reduced into LMState::scal by k_reduce_scalars)
 enum {
@@ -84,10 +82,12 @@ struct Params {
     int n_pts, n_obs, n_obs_adj;
     int pm_tiles, cm_tiles, pm_cap;  // pm_cap = shared-memory slots per contribution row
     int vec_ctas;                    // grid of the camera-vector kernels
-    // parameters: [2][(n_cams+1)*6] (rvec,t), [2][(n_cams+1)*12] (R,t); points live in pt_rec
+    // parameters: [2][(n_cams+1)*6] (rvec,t), [2][(n_cams+1)*12] (R,t), [2][n_pts*4] points (32-byte slots)
     double* cam_rt;
     double* cam_R;
-    double* pt_rec;   // [n_pts*PT_REC]
+    double* pt_X;     // [2][n_pts*4]  point positions, one 32-byte sector each
+    double* pt_z;     // [n_pts*4]     V^-1 E^T u of the two-pass Schur mat-vec
+    double* pt_h;     // [n_pts*4]     V^-1 g_p
     // per-point normal-equation data
     double* pt_V;     // [2][n_pts*6]
     double* pt_g;     // [2][n_pts*4]
@@ -119,12 +119,28 @@ struct Params {
     const int* cm_pt;
     const int4* cm_tile;      // (camera, first obs, count, 0)
     const int* cam_tile_off;  // [n_cams+1]
+    // fused point tiles (ba_tiles.cuh)
+    int ft_tiles, n_seg;
+    int n_partial_rows;       // rows of pm_partial = max(pm_tiles, ft_tiles)
+    const int* ft_pt;         // [ft_tiles+1] first point of a tile
+    const int* ft_obs;        // [ft_tiles+1] first observation of a tile (same range in both tile orders)
+    const int* ft_seg;        // [ft_tiles+1] first segment of a tile
+    const double2* tc_uv;     // [n_obs] tile-camera order
+    const unsigned* tc_word;  // [n_obs] local point | point-major position << 10 | local segment << 20
+    const int* seg_cam;       // [n_seg]
+    const int* seg_start;     // [n_seg+1] first tile-camera index of a segment
+    const int* seg_row;       // [n_seg] row slot of a segment (camera-major)
+    const int* cam_row_off;   // [n_cams+2]
+    double* rows;             // [n_seg*6]
     // partial sums
     double* cm_partial;  // [cm_tiles*27]
-    double* pm_partial;  // [pm_tiles*NSCAL]
+    double* pm_partial;  // [n_partial_rows*NSCAL]
     double* cam_partial; // [n_cams*NSCAL]
     LMState* st;
 };
+
+// position slot of point p in parameter buffer b
+BA_D double* pt_x(const Params& P, int b, int p) { return P.pt_X + ((size_t)b * P.n_pts + (size_t)p) * 4; }
 
 // ---------------------------------------------------------------------------------------------
 // reductions (fixed trees -> deterministic)
@@ -266,7 +282,7 @@ __global__ void k_residuals(Params P, double2* __restrict__ r_out) {
     const int2 id = __ldg(P.o_idx + i);
     double Rt[12], X[3];
     load_cam(P.cam_R + (size_t)b * (P.n_cams + 1) * 12, id.x, Rt);
-    load_v3(P.pt_rec + (size_t)id.y * PT_REC + 4 * b, X);
+    load_v3(pt_x(P, b, id.y), X);
     double rx, ry;
     project_residual(Rt, X, uv.x, uv.y, P.K, rx, ry);
     r_out[i] = make_double2(rx, ry);
@@ -282,7 +298,7 @@ __global__ void k_jacobian_blocks(Params P, double* __restrict__ jc_out, double*
     const int2 id = __ldg(P.o_idx + i);
     double Rt[12], X[3];
     load_cam(P.cam_R + (size_t)b * (P.n_cams + 1) * 12, id.x, Rt);
-    load_v3(P.pt_rec + (size_t)id.y * PT_REC + 4 * b, X);
+    load_v3(pt_x(P, b, id.y), X);
     ObsLin o;
     linearize_obs(Rt, X, uv.x, uv.y, P.K, o);
     double* jp = jp_out + (size_t)i * 6;
@@ -348,7 +364,7 @@ __global__ void __launch_bounds__(PM_THREADS) k_lin_points(Params P, int which) 
         if (!act) continue;
         double X[3], Rt[12];
         load_cam(camR, id.x, Rt);
-        load_v3(P.pt_rec + (size_t)id.y * PT_REC + 4 * b, X);
+        load_v3(pt_x(P, b, id.y), X);
         ObsLin o;
         linearize_obs(Rt, X, uv.x, uv.y, P.K, o);
         double wHx, wgx, r0x, wHy, wgy, r0y;
@@ -422,7 +438,7 @@ __global__ void k_point_prepare(Params P, double dmin, double dmax) {
     sym3_mulv(Vi, g, h);
     double2* vo = reinterpret_cast<double2*>(P.pt_Vinv + (size_t)p * 6);
     vo[0] = make_double2(Vi[0], Vi[1]); vo[1] = make_double2(Vi[2], Vi[3]); vo[2] = make_double2(Vi[4], Vi[5]);
-    store_v3(P.pt_rec + (size_t)p * PT_REC + PR_H, h[0], h[1], h[2]);
+    store_v3(P.pt_h + (size_t)p * 4, h[0], h[1], h[2]);
     store_v3(P.pt_D + (size_t)p * 4, d0, d1, d2);
 }
 
@@ -448,7 +464,7 @@ __global__ void __launch_bounds__(PM_THREADS) k_point_pass(Params P, const doubl
         double X[3], rec[18];
         load_cam(camR, id.x, rec);
         load_vec6(vec, id.x, rec + 12);
-        load_v3(P.pt_rec + (size_t)id.y * PT_REC + 4 * b, X);
+        load_v3(pt_x(P, b, id.y), X);
         const double* x = rec + 12;
         ObsLin o;
         linearize_obs(rec, X, uv.x, uv.y, P.K, o);
@@ -477,17 +493,16 @@ __global__ void __launch_bounds__(PM_THREADS) k_point_pass(Params P, const doubl
         double Vi[6], z[3];
         load_sym3(P.pt_Vinv, p, Vi);
         sym3_mulv(Vi, s, z);
-        double* rec = P.pt_rec + (size_t)p * PT_REC;
         if (MODE == 0) {
-            store_v3(rec + PR_Z, z[0], z[1], z[2]);
+            store_v3(P.pt_z + (size_t)p * 4, z[0], z[1], z[2]);
         } else {
             double h[3], X[3], g[3], D[3];
-            load_v3(rec + PR_H, h);
-            load_v3(rec + 4 * b, X);
+            load_v3(P.pt_h + (size_t)p * 4, h);
+            load_v3(pt_x(P, b, p), X);
             load_v3(P.pt_g + (size_t)b * P.n_pts * 4 + (size_t)p * 4, g);
             load_v3(P.pt_D + (size_t)p * 4, D);
             const double dp0 = -h[0] - z[0], dp1 = -h[1] - z[1], dp2 = -h[2] - z[2];
-            store_v3(rec + 4 * (b ^ 1), X[0] + dp0, X[1] + dp1, X[2] + dp2);
+            store_v3(pt_x(P, b ^ 1, p), X[0] + dp0, X[1] + dp1, X[2] + dp2);
             acc[0] += g[0] * dp0 + g[1] * dp1 + g[2] * dp2;
             acc[1] += D[0] * dp0 * dp0 + D[1] * dp1 * dp1 + D[2] * dp2 * dp2;
             acc[2] += dp0 * dp0 + dp1 * dp1 + dp2 * dp2;
@@ -519,25 +534,6 @@ __host__ __device__ constexpr size_t cm_smem_bytes() {
 }
 
 template <int KIND>
-BA_D void warp_gather_points(char* stage, int p, int b, const double* __restrict__ pt_rec, const double* __restrict__ pt_Vinv) {
-    constexpr int NCH = CmCh<KIND>::value;
-    const int lane = threadIdx.x & 31;
-#pragma unroll
-    for (int k = 0; k < NCH; ++k) {
-        const int j = 32 * k + lane;
-        const int src = j / NCH, part = j - src * NCH;
-        const int q = __shfl_sync(0xffffffffu, p, src);
-        const char* rec = reinterpret_cast<const char*>(pt_rec) + (size_t)q * (PT_REC * 8);
-        const char* g;
-        if (part < 2) g = rec + b * 32 + part * 16;
-        else if (KIND == 2) g = rec + PR_Z * 8 + (part - 2) * 16;
-        else if (part < 4) g = rec + PR_H * 8 + (part - 2) * 16;
-        else g = reinterpret_cast<const char*>(pt_Vinv) + (size_t)q * 48 + (part - 4) * 16;
-        cp_async16_cg(stage + j * 16, g);
-    }
-}
-
-template <int KIND>
 __global__ void __launch_bounds__(CM_THREADS) k_camera_pass(Params P, const double* __restrict__ vec, int with_schur_diag) {
     constexpr int N = CmN<KIND>::value;
     constexpr int NCH = CmCh<KIND>::value;
@@ -558,11 +554,10 @@ __global__ void __launch_bounds__(CM_THREADS) k_camera_pass(Params P, const doub
         const int p = __ldg(P.cm_pt + o0 + i);
         double rec[2 * NCH];
         {
-            const double* pr = P.pt_rec + (size_t)p * PT_REC;
-            load_v3(pr + 4 * b, rec);
-            if constexpr (KIND == 2) load_v3(pr + PR_Z, rec + 4);
+            load_v3(pt_x(P, b, p), rec);
+            if constexpr (KIND == 2) load_v3(P.pt_z + (size_t)p * 4, rec + 4);
             if constexpr (KIND == 1) {
-                load_v3(pr + PR_H, rec + 4);
+                load_v3(P.pt_h + (size_t)p * 4, rec + 4);
                 load_sym3(P.pt_Vinv, p, rec + 8);
             }
         }
@@ -820,7 +815,7 @@ __global__ void __launch_bounds__(VEC_THREADS) k_pcg_dots(Params P) {
     if (threadIdx.x == 0) P.dot_partial[2 * blockIdx.x] = cs;
 }
 
-__global__ void __launch_bounds__(VEC_THREADS) k_pcg_update(Params P, double tol, int max_iters, int* ticket) {
+__global__ void __launch_bounds__(VEC_THREADS) k_pcg_update(Params P, double tol, int max_iters, int n_dot_partials, int* ticket) {
     __shared__ double sm[VEC_THREADS / 32];
     __shared__ double sc[2];
     __shared__ int last;
@@ -829,7 +824,7 @@ __global__ void __launch_bounds__(VEC_THREADS) k_pcg_update(Params P, double tol
     const double gamma = st->gamma, alpha_prev = st->alpha, gamma_prev = st->gamma_prev;
     const int first = (st->pcg_iter == 0);
     if (threadIdx.x < 32) {
-        const double d = warp0_sum_partials(P.dot_partial, gridDim.x);
+        const double d = warp0_sum_partials(P.dot_partial, n_dot_partials);
         if (threadIdx.x == 0) {
             const double beta = first ? 0.0 : gamma / gamma_prev;
             const double den = first ? d : d - beta * gamma / alpha_prev;
@@ -948,7 +943,7 @@ __global__ void __launch_bounds__(RED_THREADS) k_reduce_scalars(Params P, unsign
         if (!pm && !cm) continue;
         double v = 0.0;
         if (s == S_GPMAX) {
-            for (int t = threadIdx.x; t < P.pm_tiles; t += RED_THREADS) v = fmax(v, P.pm_partial[(size_t)t * NSCAL + s]);
+            for (int t = threadIdx.x; t < P.n_partial_rows; t += RED_THREADS) v = fmax(v, P.pm_partial[(size_t)t * NSCAL + s]);
             v = warp_max(v);
             __syncthreads();
             if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
@@ -961,7 +956,7 @@ __global__ void __launch_bounds__(RED_THREADS) k_reduce_scalars(Params P, unsign
             __syncthreads();
             continue;
         }
-        if (pm) for (int t = threadIdx.x; t < P.pm_tiles; t += RED_THREADS) v += P.pm_partial[(size_t)t * NSCAL + s];
+        if (pm) for (int t = threadIdx.x; t < P.n_partial_rows; t += RED_THREADS) v += P.pm_partial[(size_t)t * NSCAL + s];
         if (cm) for (int c = threadIdx.x; c < P.n_cams; c += RED_THREADS) v += P.cam_partial[(size_t)c * NSCAL + s];
         const double tot = cta_sum_all(v, sm);
         if (threadIdx.x == 0) P.st->scal[s] = tot;

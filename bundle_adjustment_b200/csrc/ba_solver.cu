@@ -7,6 +7,7 @@
 // every entry point fails with BA_ERR_CUDA when no usable device is present.
 #include "../../include/ba_b200.h"
 #include "ba_kernels.cuh"
+#include "ba_tiles.cuh"
 
 #include <cub/cub.cuh>
 #include <dlfcn.h>
@@ -120,12 +121,13 @@ struct DBuf {
 enum Kind {
     KN_SETUP = 0, KN_CAM_PREP, KN_RESID, KN_JAC, KN_LIN_PTS, KN_PT_PREP, KN_PT_PASS, KN_BACKSUB, KN_LIN_CAM,
     KN_SCHUR_CAM, KN_MATVEC_CAM, KN_CAM_SUM, KN_CAM_FIN, KN_PCG_DOTS, KN_PCG_UPDATE, KN_CAM_UPDATE, KN_REDUCE,
-    KN_GRAD, KN_DECIDE, KN_COUNT
+    KN_GRAD, KN_DECIDE, KN_TILE_MV, KN_TILE_BACKSUB, KN_ROWS_FIN, KN_COUNT
 };
 static const char* kKindNames[KN_COUNT] = {
     "setup", "cam_prepare", "residuals", "jacobian_blocks", "lin_points", "point_prepare", "schur_matvec_points",
     "backsub_points", "lin_cameras", "schur_rhs_cameras", "schur_matvec_cameras", "camera_sum", "camera_finish",
-    "pcg_dots", "pcg_update", "camera_update", "reduce_scalars", "gradient_check", "lm_decide"};
+    "pcg_dots", "pcg_update", "camera_update", "reduce_scalars", "gradient_check", "lm_decide",
+    "schur_matvec_tiles", "backsub_tiles", "rows_finish"};
 
 // ---------------------------------------------------------------------------------------------
 // setup kernels (device-side construction of the two observation orders)
@@ -239,20 +241,20 @@ __global__ void k_max_track(int n_pts, const int* __restrict__ pt_off, int* __re
     atomicMax(out, pt_off[p + 1] - pt_off[p]);
 }
 // compact [n*3] <-> slot `buf` (4 doubles) of the 128-byte point records
-// `perm[q]` = caller's index of internal point q
-__global__ void k_pack_points(int n, const int* __restrict__ perm, const double* __restrict__ in3, double* __restrict__ rec, int buf) {
+// `perm[q]` = caller's index of internal point q; `X4` = one parameter buffer of 4-double slots
+__global__ void k_pack_points(int n, const int* __restrict__ perm, const double* __restrict__ in3, double* __restrict__ X4) {
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= n) return;
     const size_t p = (size_t)perm[q];
-    double2* o = reinterpret_cast<double2*>(rec + (size_t)q * PT_REC + 4 * buf);
+    double2* o = reinterpret_cast<double2*>(X4 + (size_t)q * 4);
     o[0] = make_double2(in3[3 * p], in3[3 * p + 1]);
     o[1] = make_double2(in3[3 * p + 2], 0.0);
 }
-__global__ void k_unpack_points(int n, const int* __restrict__ perm, const double* __restrict__ rec, int buf, double* __restrict__ out3) {
+__global__ void k_unpack_points(int n, const int* __restrict__ perm, const double* __restrict__ X4, double* __restrict__ out3) {
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= n) return;
     const size_t p = (size_t)perm[q];
-    const double* in4 = rec + (size_t)q * PT_REC + 4 * buf;
+    const double* in4 = X4 + (size_t)q * 4;
     out3[3 * p] = in4[0];
     out3[3 * p + 1] = in4[1];
     out3[3 * p + 2] = in4[2];
@@ -326,7 +328,7 @@ struct ba_handle {
     int max_track = 0;
     size_t smem_lin = 0, smem_pass = 0;
 
-    DBuf<double> cam_rt, cam_R, pt_rec, pt_V, pt_g, pt_Vinv, pt_D;
+    DBuf<double> cam_rt, cam_R, pt_X, pt_z, pt_h, pt_V, pt_g, pt_Vinv, pt_D;
     DBuf<double> cam_U, cam_g, cam_D, cam_Minv, cam_acc, v_b, v_x, v_r, v_u, v_p, v_s, v_w, dot_partial;
     DBuf<double> init_cam_rt, init_pts;  // parameters of the last ba_set_problem (for ba_restore_initial)
     DBuf<int> ticket;
@@ -334,6 +336,13 @@ struct ba_handle {
     DBuf<int2> o_idx, pm_idx;
     DBuf<int> pt_off, pm_tile_pt, cm_pt, cam_tile_off;
     DBuf<int> pt_perm;  // internal (locality-ordered) point id -> caller's point index
+    // fused point tiles
+    bool fused_ok = false;
+    int ft_tiles = 0, n_seg = 0;
+    DBuf<int> ft_pt, ft_obs, ft_seg, seg_cam, seg_start, seg_row, cam_row_off;
+    DBuf<double2> tc_uv;
+    DBuf<unsigned> tc_word;
+    DBuf<double> rows;
     DBuf<int4> cm_tile;
     DBuf<double> cm_partial, pm_partial, cam_partial;
     DBuf<LMState> st;
@@ -441,6 +450,90 @@ static void use(ba_handle* h) {
     CK(cudaSetDevice(h->device));
 }
 
+struct MaxOp {
+    __host__ __device__ int operator()(int a, int b) const { return a > b ? a : b; }
+};
+
+// Build the fused point tiles (ba_tiles.cuh) from the point-major order: greedy cut of the point
+// sequence on the host (one pass over the track offsets), everything per-observation on the device.
+static void build_tiles(ba_handle* h, int n_cams, int n_pts, int n_obs) {
+    cudaStream_t s = h->stream;
+    const int B = 256;
+    h->fused_ok = false;
+    h->ft_tiles = 0; h->n_seg = 0;
+    if (h->max_track > FT_THREADS) return;  // a track does not fit one tile: the two-pass kernels serve this problem
+
+    std::vector<int> off((size_t)n_pts + 1);
+    CK(cudaMemcpyAsync(off.data(), h->pt_off.p, off.size() * sizeof(int), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    std::vector<int> tp{0}, to{0};
+    for (int p = 0; p < n_pts;) {
+        const int o_begin = off[p];
+        int q = p + 1;  // every track fits, so a tile always takes at least one point
+        while (q < n_pts && off[q + 1] - o_begin <= FT_THREADS && q - p < FT_THREADS) ++q;
+        tp.push_back(q); to.push_back(off[q]);
+        p = q;
+    }
+    const int T = (int)tp.size() - 1;
+    h->ft_pt.alloc(tp.size()); h->ft_obs.alloc(to.size()); h->ft_seg.alloc(tp.size());
+    CK(cudaMemcpyAsync(h->ft_pt.p, tp.data(), tp.size() * sizeof(int), cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(h->ft_obs.p, to.data(), to.size() * sizeof(int), cudaMemcpyHostToDevice, s));
+
+    // tile-camera order: stable sort of the point-major indices by (tile, camera)
+    DBuf<unsigned long long> key, key_s;
+    DBuf<int> ia, ib, ic;
+    key.alloc(n_obs); key_s.alloc(n_obs); ia.alloc(n_obs); ib.alloc(n_obs); ic.alloc(n_obs);
+    launch(h, KN_SETUP, k_ft_keys, cdiv(n_obs, B), B, 0, n_obs, T, (const int*)h->ft_obs.p, (const int2*)h->pm_idx.p, key.p, ia.p);
+    int tile_bits = 1;
+    while ((1LL << tile_bits) < T) ++tile_bits;
+    size_t tb_sort = 0, tb_max = 0, tb_sum = 0, tb_seg = 0;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, tb_sort, key.p, key_s.p, ia.p, ib.p, n_obs, 0, 32 + tile_bits, s));
+    CK(cub::DeviceScan::InclusiveScan(nullptr, tb_max, ia.p, ic.p, MaxOp(), n_obs, s));
+    CK(cub::DeviceScan::InclusiveSum(nullptr, tb_sum, ia.p, ic.p, n_obs, s));
+    DBuf<unsigned char> tmp;
+    tmp.alloc(std::max(std::max(tb_sort, tb_max), tb_sum));
+    size_t tb = tmp.n;
+    CK(cub::DeviceRadixSort::SortPairs(tmp.p, tb, key.p, key_s.p, ia.p, ib.p, n_obs, 0, 32 + tile_bits, s));  // ib = source index
+    launch(h, KN_SETUP, k_ft_run_heads, cdiv(n_obs, B), B, 0, n_obs, (const unsigned long long*)key_s.p, ia.p);
+    tb = tmp.n;
+    CK(cub::DeviceScan::InclusiveScan(tmp.p, tb, ia.p, ic.p, MaxOp(), n_obs, s));                             // ic = run start
+    launch(h, KN_SETUP, k_ft_seg_flags, cdiv(n_obs, B), B, 0, n_obs, (const int*)ic.p, ia.p);               // ia = segment head flag
+    tb = tmp.n;
+    CK(cub::DeviceScan::InclusiveSum(tmp.p, tb, ia.p, ic.p, n_obs, s));                                      // ic = segment id + 1
+    h->launches[KN_SETUP] += 3;
+    int S = 0;
+    CK(cudaMemcpyAsync(&S, ic.p + n_obs - 1, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+
+    h->tc_uv.alloc(n_obs); h->tc_word.alloc(n_obs);
+    h->seg_cam.alloc(S); h->seg_start.alloc((size_t)S + 1); h->seg_row.alloc(S); h->cam_row_off.alloc((size_t)n_cams + 2);
+    h->rows.alloc((size_t)S * 6);
+    DBuf<unsigned> skey, skey_s;
+    DBuf<int> sidx, sidx_s;
+    skey.alloc(S); skey_s.alloc(S); sidx.alloc(S); sidx_s.alloc(S);
+    launch(h, KN_SETUP, k_ft_tile_seg, cdiv(T + 1, B), B, 0, T, n_obs, S, (const int*)h->ft_obs.p, (const int*)ic.p, h->ft_seg.p,
+           h->seg_start.p);
+    launch(h, KN_SETUP, k_ft_fill, cdiv(n_obs, B), B, 0, n_obs, (const unsigned long long*)key_s.p, (const int*)ib.p,
+           (const int*)ia.p, (const int*)ic.p, (const int*)h->ft_obs.p, (const int*)h->ft_pt.p, (const int*)h->ft_seg.p,
+           (const double2*)h->pm_uv.p, (const int2*)h->pm_idx.p, h->tc_uv.p, h->tc_word.p, h->seg_cam.p, h->seg_start.p, skey.p);
+    // rows camera-major: stable sort of the segments by camera
+    launch(h, KN_SETUP, k_iota, cdiv(S, B), B, 0, S, sidx.p);
+    int cam_bits = 1;
+    while ((1LL << cam_bits) < (long long)n_cams + 1) ++cam_bits;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, tb_seg, skey.p, skey_s.p, sidx.p, sidx_s.p, S, 0, cam_bits, s));
+    if (tb_seg > tmp.n) { CK(cudaStreamSynchronize(s)); tmp.alloc(tb_seg); }
+    tb = tmp.n;
+    CK(cub::DeviceRadixSort::SortPairs(tmp.p, tb, skey.p, skey_s.p, sidx.p, sidx_s.p, S, 0, cam_bits, s));
+    h->launches[KN_SETUP] += 1;
+    launch(h, KN_SETUP, k_ft_seg_rows, cdiv(S, B), B, 0, S, (const int*)sidx_s.p, h->seg_row.p);
+    launch(h, KN_SETUP, k_lower_bound_u32, cdiv(n_cams + 2, B), B, 0, S, (const unsigned*)skey_s.p, n_cams + 2, h->cam_row_off.p);
+    CK(cudaFuncSetAttribute(k_tile_pass<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ft_smem_bytes(FT_ROWS_MV)));
+    CK(cudaFuncSetAttribute(k_tile_pass<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ft_smem_bytes(FT_ROWS_MV)));
+    CK(cudaStreamSynchronize(s));  // scratch dies here
+    h->ft_tiles = T; h->n_seg = S;
+    h->fused_ok = true;
+}
+
 static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy, int n_cams, int n_pts, int n_obs,
                         const double* rvec, const double* tvec, const double* frv, const double* ftv, const double* pts,
                         const int* obs_cam, const int* obs_pt, const double* obs_uv) {
@@ -453,12 +546,13 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     const size_t nc1 = (size_t)n_cams + 1;
 
     h->cam_rt.alloc(2 * nc1 * 6); h->cam_R.alloc(2 * nc1 * 12);
-    h->pt_rec.alloc((size_t)n_pts * PT_REC); h->pt_V.alloc(2 * (size_t)n_pts * 6); h->pt_g.alloc(2 * (size_t)n_pts * 4);
+    h->pt_X.alloc(2 * (size_t)n_pts * 4); h->pt_z.alloc((size_t)n_pts * 4); h->pt_h.alloc((size_t)n_pts * 4);
+    h->pt_V.alloc(2 * (size_t)n_pts * 6); h->pt_g.alloc(2 * (size_t)n_pts * 4);
     h->pt_Vinv.alloc((size_t)n_pts * 6);
     h->pt_D.alloc((size_t)n_pts * 4);
-    h->pt_rec.zero(s);
+    h->pt_X.zero(s); h->pt_z.zero(s); h->pt_h.zero(s);
     h->init_cam_rt.alloc(nc1 * 6); h->init_pts.alloc((size_t)n_pts * 3);
-    if (cdiv(std::max(n_cams, 1), VEC_THREADS) > MAX_VEC_CTAS) fail(BA_ERR_ARG, "too many cameras (%d)", n_cams);
+    if (cdiv(std::max(n_cams, 1), RS_WARPS) > MAX_VEC_CTAS) fail(BA_ERR_ARG, "too many cameras (%d)", n_cams);
     const size_t ncz = std::max<size_t>(n_cams, 1);
     h->cam_U.alloc(ncz * 21); h->cam_g.alloc(ncz * 6); h->cam_D.alloc(ncz * 6); h->cam_Minv.alloc(ncz * 36);
     h->cam_acc.alloc(ncz * 27); h->cam_partial.alloc(ncz * NSCAL);
@@ -562,10 +656,11 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     if (cm_tiles) CK(cudaMemcpyAsync(h->cm_tile.p, tiles.data(), (size_t)cm_tiles * sizeof(int4), cudaMemcpyHostToDevice, s));
     CK(cudaMemcpyAsync(h->cam_tile_off.p, tile_off.data(), nc1 * sizeof(int), cudaMemcpyHostToDevice, s));
     h->cm_partial.alloc(std::max<size_t>((size_t)cm_tiles * 27, 27));
-    h->pm_partial.alloc((size_t)pm_tiles * NSCAL);
-    h->pm_partial.zero(s);
-
     h->max_track = err_track[1];
+    build_tiles(h, n_cams, n_pts, n_obs);
+    const int n_partial_rows = std::max(pm_tiles, h->ft_tiles);
+    h->pm_partial.alloc((size_t)n_partial_rows * NSCAL);
+    h->pm_partial.zero(s);
     const int cap = (PM_THREADS + h->max_track + 1) & ~1;  // even: keeps the cp.async stage 16-byte aligned
     h->smem_lin = pm_smem_bytes<9, 6>(cap);
     h->smem_pass = pm_smem_bytes<3, 9>(cap);
@@ -584,7 +679,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     h->io.alloc(std::max<size_t>((size_t)n_pts * 3, nc1 * 6));
     P.n_obs_adj = n_obs_adj; P.pm_tiles = pm_tiles; P.cm_tiles = cm_tiles; P.pm_cap = cap;
     P.vec_ctas = cdiv(std::max(n_cams, 1), VEC_THREADS);
-    P.cam_rt = h->cam_rt.p; P.cam_R = h->cam_R.p; P.pt_rec = h->pt_rec.p; P.pt_V = h->pt_V.p; P.pt_g = h->pt_g.p;
+    P.cam_rt = h->cam_rt.p; P.cam_R = h->cam_R.p; P.pt_X = h->pt_X.p; P.pt_z = h->pt_z.p; P.pt_h = h->pt_h.p; P.pt_V = h->pt_V.p; P.pt_g = h->pt_g.p;
     P.pt_Vinv = h->pt_Vinv.p; P.pt_D = h->pt_D.p;
     P.cam_U = h->cam_U.p; P.cam_g = h->cam_g.p; P.cam_D = h->cam_D.p; P.cam_Minv = h->cam_Minv.p; P.cam_acc = h->cam_acc.p;
     P.v_b = h->v_b.p; P.v_x = h->v_x.p; P.v_r = h->v_r.p; P.v_u = h->v_u.p; P.v_p = h->v_p.p; P.v_s = h->v_s.p;
@@ -593,6 +688,10 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     P.pm_tile_pt = h->pm_tile_pt.p; P.cm_uv = h->cm_uv.p; P.cm_pt = h->cm_pt.p; P.cm_tile = h->cm_tile.p;
     P.cam_tile_off = h->cam_tile_off.p; P.cm_partial = h->cm_partial.p; P.pm_partial = h->pm_partial.p;
     P.cam_partial = h->cam_partial.p; P.st = h->st.p;
+    P.ft_tiles = h->ft_tiles; P.n_seg = h->n_seg; P.n_partial_rows = n_partial_rows;
+    P.ft_pt = h->ft_pt.p; P.ft_obs = h->ft_obs.p; P.ft_seg = h->ft_seg.p; P.tc_uv = h->tc_uv.p; P.tc_word = h->tc_word.p;
+    P.seg_cam = h->seg_cam.p; P.seg_start = h->seg_start.p; P.seg_row = h->seg_row.p; P.cam_row_off = h->cam_row_off.p;
+    P.rows = h->rows.p;
     h->st.zero(s);
     CK(cudaStreamSynchronize(s));  // the sort scratch buffers die at scope exit
     h->have_problem = true;
@@ -610,7 +709,7 @@ static void set_params(ba_handle* h, const double* rvec, const double* tvec, con
     if (pts) {
         CK(cudaMemcpyAsync(h->io.p, pts, (size_t)P.n_pts * 3 * sizeof(double), cudaMemcpyHostToDevice, s));
         launch(h, KN_SETUP, k_pack_points, cdiv(P.n_pts, B), B, 0, P.n_pts, (const int*)h->pt_perm.p, (const double*)h->io.p,
-               h->pt_rec.p, 0);
+               h->pt_X.p);
         if (save_initial)
             CK(cudaMemcpyAsync(h->init_pts.p, h->io.p, (size_t)P.n_pts * 3 * sizeof(double), cudaMemcpyDeviceToDevice, s));
     }
@@ -690,6 +789,8 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     const int check_every = std::max(1, opt->pcg_check_every);
     const int with_schur = opt->precond == BA_PRECOND_SCHUR_JACOBI ? 1 : 0;
     const int nc1 = P.n_cams + 1;
+    if (opt->schur_path != BA_PATH_TILES && opt->schur_path != BA_PATH_TWO_PASS) fail(BA_ERR_ARG, "unknown schur_path %d", opt->schur_path);
+    const bool tiles = opt->schur_path == BA_PATH_TILES && h->fused_ok;
 
     CK(cudaEventRecord(h->ev_solve0, s));
     launch(h, KN_SETUP, k_init_state, 1, 1, 0, h->st.p, opt->initial_lambda);
@@ -715,16 +816,29 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
             allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 27);
             launch(h, KN_CAM_FIN, k_camera_finish_schur, P.vec_ctas, VEC_THREADS, 0, P, with_schur, h->ticket.p);
             for (int it = 0; it < opt->pcg_max_iters; ++it) {
-                launch(h, KN_PT_PASS, k_point_pass<0>, P.pm_tiles, PM_THREADS, h->smem_pass, P, (const double*)h->v_u.p);
-                launch(h, KN_MATVEC_CAM, k_camera_pass<2>, P.cm_tiles, CM_THREADS, cm_smem_bytes<2>(), P, (const double*)h->v_u.p, 0);
-                if (h->nranks > 1) {
-                    launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 6, 256), 256, 0, P, 6, 1);
-                    allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 6);
-                    launch(h, KN_PCG_DOTS, k_pcg_dots<false>, P.vec_ctas, VEC_THREADS, 0, P);
+                int n_dots = P.vec_ctas;
+                if (tiles) {
+                    launch(h, KN_TILE_MV, k_tile_pass<0>, P.ft_tiles, FT_THREADS, ft_smem_bytes(FT_ROWS_MV), P, (const double*)h->v_u.p);
+                    if (h->nranks > 1) {
+                        launch(h, KN_ROWS_FIN, k_rows_finish<true>, cdiv(P.n_cams, RS_WARPS), RS_WARPS * 32, 0, P);
+                        allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 6);
+                        launch(h, KN_PCG_DOTS, k_pcg_dots<false>, P.vec_ctas, VEC_THREADS, 0, P);
+                    } else {
+                        n_dots = cdiv(P.n_cams, RS_WARPS);
+                        launch(h, KN_ROWS_FIN, k_rows_finish<false>, n_dots, RS_WARPS * 32, 0, P);
+                    }
                 } else {
-                    launch(h, KN_PCG_DOTS, k_pcg_dots<true>, P.vec_ctas, VEC_THREADS, 0, P);
+                    launch(h, KN_PT_PASS, k_point_pass<0>, P.pm_tiles, PM_THREADS, h->smem_pass, P, (const double*)h->v_u.p);
+                    launch(h, KN_MATVEC_CAM, k_camera_pass<2>, P.cm_tiles, CM_THREADS, cm_smem_bytes<2>(), P, (const double*)h->v_u.p, 0);
+                    if (h->nranks > 1) {
+                        launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 6, 256), 256, 0, P, 6, 1);
+                        allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 6);
+                        launch(h, KN_PCG_DOTS, k_pcg_dots<false>, P.vec_ctas, VEC_THREADS, 0, P);
+                    } else {
+                        launch(h, KN_PCG_DOTS, k_pcg_dots<true>, P.vec_ctas, VEC_THREADS, 0, P);
+                    }
                 }
-                launch(h, KN_PCG_UPDATE, k_pcg_update, P.vec_ctas, VEC_THREADS, 0, P, opt->pcg_tol, opt->pcg_max_iters, h->ticket.p);
+                launch(h, KN_PCG_UPDATE, k_pcg_update, P.vec_ctas, VEC_THREADS, 0, P, opt->pcg_tol, opt->pcg_max_iters, n_dots, h->ticket.p);
                 if ((it + 1) % check_every == 0 && it + 1 < opt->pcg_max_iters) {
                     CK(cudaMemcpyAsync(h->h_flag, &h->st.p->pcg_done, sizeof(int), cudaMemcpyDeviceToHost, s));
                     CK(cudaStreamSynchronize(s));
@@ -732,7 +846,10 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
                 }
             }
         }
-        launch(h, KN_BACKSUB, k_point_pass<1>, P.pm_tiles, PM_THREADS, h->smem_pass, P, (const double*)h->v_x.p);
+        if (tiles)
+            launch(h, KN_TILE_BACKSUB, k_tile_pass<1>, P.ft_tiles, FT_THREADS, ft_smem_bytes(FT_ROWS_MV), P, (const double*)h->v_x.p);
+        else
+            launch(h, KN_BACKSUB, k_point_pass<1>, P.pm_tiles, PM_THREADS, h->smem_pass, P, (const double*)h->v_x.p);
         launch(h, KN_CAM_UPDATE, k_camera_update, cdiv(nc1, 128), 128, 0, P);
         lin_points_and_cost(h, 3);
         reduce_scalars(h, MASK_LIN | MASK_STEP_PM, MASK_STEP_CAM);
@@ -800,6 +917,7 @@ void ba_default_options(ba_options* o) {
     o->precond = BA_PRECOND_SCHUR_JACOBI;
     o->pcg_max_iters = 100; o->pcg_tol = 0.1; o->pcg_check_every = 4;
     o->verbose = 0;
+    o->schur_path = BA_PATH_TILES;
 }
 
 int ba_create(int device, ba_handle** out) {
@@ -890,7 +1008,7 @@ int ba_get_params(ba_handle* h, double* rvec, double* tvec, double* pts) {
     const int b = h->h_state->cur;
     if (pts) {
         ba::launch(h, ba::KN_SETUP, ba::k_unpack_points, ba::cdiv(P.n_pts, 256), 256, 0, P.n_pts, (const int*)h->pt_perm.p,
-                   (const double*)h->pt_rec.p, b, h->io.p);
+                   (const double*)(h->pt_X.p + (size_t)b * P.n_pts * 4), h->io.p);
         CK(cudaMemcpyAsync(pts, h->io.p, (size_t)P.n_pts * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
         CK(cudaStreamSynchronize(s));
     }
@@ -915,7 +1033,7 @@ int ba_restore_initial(ba_handle* h) {
     CK(cudaMemsetAsync(&h->st.p->cur, 0, sizeof(int), s));
     CK(cudaMemcpyAsync(h->cam_rt.p, h->init_cam_rt.p, nc1 * 6 * sizeof(double), cudaMemcpyDeviceToDevice, s));
     ba::launch(h, ba::KN_SETUP, ba::k_pack_points, ba::cdiv(P.n_pts, 256), 256, 0, P.n_pts, (const int*)h->pt_perm.p,
-               (const double*)h->init_pts.p, h->pt_rec.p, 0);
+               (const double*)h->init_pts.p, h->pt_X.p);
     ba::launch(h, ba::KN_CAM_PREP, ba::k_cam_prepare, ba::cdiv((int)nc1, 256), 256, 0, P, 0);
     API_END
 }
@@ -1063,11 +1181,73 @@ int ba_normal_blocks(ba_handle* h, const ba_options* opt, double* gc, double* gp
     API_END
 }
 
+int ba_schur_matvec(ba_handle* h, const ba_options* opt, double lambda, const double* u, double* w_out) {
+    API_BEGIN
+    ba::need_problem(h);
+    if (!u || !w_out) ba::fail(BA_ERR_ARG, "null array argument");
+    if (h->nranks > 1) ba::fail(BA_ERR_STATE, "ba_schur_matvec is a single-GPU test hook");
+    ba_options o;
+    if (opt) o = *opt; else ba_default_options(&o);
+    ba::apply_robust(h, &o);
+    const ba::Params& P = h->P;
+    cudaStream_t s = h->stream;
+    if (P.n_cams == 0) return BA_OK;
+    const bool tiles = o.schur_path == BA_PATH_TILES && h->fused_ok;
+    ba::launch(h, ba::KN_SETUP, ba::k_init_state, 1, 1, 0, h->st.p, lambda);
+    ba::launch(h, ba::KN_CAM_PREP, ba::k_cam_prepare, ba::cdiv(P.n_cams + 1, 256), 256, 0, P, 2);
+    ba::lin_points_and_cost(h, 2);
+    ba::lin_cameras(h, ba::kDiagMin, ba::kDiagMax);
+    ba::launch(h, ba::KN_PT_PREP, ba::k_point_prepare, ba::cdiv(P.n_pts, 256), 256, 0, P, ba::kDiagMin, ba::kDiagMax);
+    CK(cudaMemcpyAsync(h->v_u.p, u, (size_t)P.n_cams * 6 * sizeof(double), cudaMemcpyHostToDevice, s));
+    if (tiles) {
+        ba::launch(h, ba::KN_TILE_MV, ba::k_tile_pass<0>, P.ft_tiles, ba::FT_THREADS, ba::ft_smem_bytes(ba::FT_ROWS_MV), P,
+                   (const double*)h->v_u.p);
+        ba::launch(h, ba::KN_ROWS_FIN, ba::k_rows_finish<false>, ba::cdiv(P.n_cams, ba::RS_WARPS), ba::RS_WARPS * 32, 0, P);
+    } else {
+        ba::launch(h, ba::KN_PT_PASS, ba::k_point_pass<0>, P.pm_tiles, ba::PM_THREADS, h->smem_pass, P, (const double*)h->v_u.p);
+        ba::launch(h, ba::KN_MATVEC_CAM, ba::k_camera_pass<2>, P.cm_tiles, ba::CM_THREADS, ba::cm_smem_bytes<2>(), P,
+                   (const double*)h->v_u.p, 0);
+        ba::launch(h, ba::KN_PCG_DOTS, ba::k_pcg_dots<true>, P.vec_ctas, ba::VEC_THREADS, 0, P);
+    }
+    CK(cudaMemcpyAsync(w_out, h->v_w.p, (size_t)P.n_cams * 6 * sizeof(double), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    API_END
+}
+
 int ba_solve(ba_handle* h, const ba_options* opt, ba_stats* stats_out) {
     API_BEGIN
     ba_options o;
     if (opt) o = *opt; else ba_default_options(&o);
     ba::solve(h, &o, stats_out);
+    API_END
+}
+
+int ba_layout_info(ba_handle* h, int64_t out[8]) {
+    API_BEGIN
+    ba::need_problem(h);
+    if (!out) ba::fail(BA_ERR_ARG, "null output");
+    const ba::Params& P = h->P;
+    const int64_t v[8] = {P.n_obs, P.n_obs_adj, P.n_pts, P.n_cams, h->fused_ok ? h->ft_tiles : 0, h->n_seg, P.pm_tiles, P.cm_tiles};
+    for (int k = 0; k < 8; ++k) out[k] = v[k];
+    API_END
+}
+
+int ba_tile_layout(ba_handle* h, int32_t* ft_pt, int32_t* ft_obs, int32_t* ft_seg, uint32_t* tc_word, double* tc_uv,
+                   int32_t* seg_cam, int32_t* seg_start, int32_t* seg_row, int32_t* cam_row_off, int32_t* pt_perm) {
+    API_BEGIN
+    ba::need_problem(h);
+    if (!h->fused_ok) ba::fail(BA_ERR_STATE, "no point tiles for this problem (a track is longer than a tile)");
+    const ba::Params& P = h->P;
+    cudaStream_t s = h->stream;
+    const size_t T = (size_t)h->ft_tiles, S = (size_t)h->n_seg;
+    auto get = [&](void* dst, const void* src, size_t bytes) {
+        if (dst) CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, s));
+    };
+    get(ft_pt, h->ft_pt.p, (T + 1) * 4); get(ft_obs, h->ft_obs.p, (T + 1) * 4); get(ft_seg, h->ft_seg.p, (T + 1) * 4);
+    get(tc_word, h->tc_word.p, (size_t)P.n_obs * 4); get(tc_uv, h->tc_uv.p, (size_t)P.n_obs * 16);
+    get(seg_cam, h->seg_cam.p, S * 4); get(seg_start, h->seg_start.p, (S + 1) * 4); get(seg_row, h->seg_row.p, S * 4);
+    get(cam_row_off, h->cam_row_off.p, ((size_t)P.n_cams + 2) * 4); get(pt_perm, h->pt_perm.p, (size_t)P.n_pts * 4);
+    CK(cudaStreamSynchronize(s));
     API_END
 }
 

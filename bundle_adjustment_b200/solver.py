@@ -26,6 +26,8 @@ def make_options(**kw) -> api.Options:
             v = api.ROBUST[v]
         if k == "precond" and isinstance(v, str):
             v = api.PRECOND[v]
+        if k == "schur_path" and isinstance(v, str):
+            v = api.SCHUR_PATH[v]
         if not hasattr(o, k) or k == "reserved":
             raise TypeError(f"unknown solver option {k!r}")
         setattr(o, k, v)
@@ -163,6 +165,15 @@ class FlatSolver:
         api.check(api.lib().ba_normal_blocks(self._h, C.byref(o), api.dptr(gc), api.dptr(gp), api.dptr(U), api.dptr(V)))
         return {"gc": gc, "gp": gp, "U": U, "V": V}
 
+    def schur_matvec(self, u, lam: float, **opts) -> np.ndarray:
+        """Damped Schur complement at the current parameters applied to u (n_adj, 6); test hook."""
+        nc, _, _ = self._need()
+        o = make_options(**opts)
+        u = api.f64(u).reshape(nc, 6)
+        w = np.zeros((nc, 6))
+        api.check(api.lib().ba_schur_matvec(self._h, C.byref(o), float(lam), api.dptr(u), api.dptr(w)))
+        return w
+
     # -- solve -----------------------------------------------------------------------------------
     def solve(self, **opts) -> Dict[str, float]:
         self._need()
@@ -170,6 +181,26 @@ class FlatSolver:
         st = api.Stats()
         api.check(api.lib().ba_solve(self._h, C.byref(o), C.byref(st)))
         return st.as_dict()
+
+    def layout_info(self) -> Dict[str, int]:
+        out = np.zeros(8, dtype=np.int64)
+        api.check(api.lib().ba_layout_info(self._h, api.lptr(out)))
+        keys = ("n_obs", "n_obs_adj", "n_pts", "n_cams", "point_tiles", "segments", "pm_windows", "cm_tiles")
+        return {k: int(v) for k, v in zip(keys, out)}
+
+    def tile_layout(self) -> Dict[str, np.ndarray]:
+        """The point-tile structure (test hook, ``ba_tile_layout``)."""
+        info = self.layout_info()
+        T, Sg, no, nc, npt = info["point_tiles"], info["segments"], info["n_obs"], info["n_cams"], info["n_pts"]
+        i32 = lambda n: np.zeros(n, dtype=np.int32)
+        out = {"ft_pt": i32(T + 1), "ft_obs": i32(T + 1), "ft_seg": i32(T + 1), "tc_word": np.zeros(no, dtype=np.uint32),
+               "tc_uv": np.zeros((no, 2)), "seg_cam": i32(Sg), "seg_start": i32(Sg + 1), "seg_row": i32(Sg),
+               "cam_row_off": i32(nc + 2), "pt_perm": i32(npt)}
+        api.check(api.lib().ba_tile_layout(
+            self._h, api.iptr(out["ft_pt"]), api.iptr(out["ft_obs"]), api.iptr(out["ft_seg"]),
+            out["tc_word"].ctypes.data_as(C.POINTER(C.c_uint32)), api.dptr(out["tc_uv"]), api.iptr(out["seg_cam"]),
+            api.iptr(out["seg_start"]), api.iptr(out["seg_row"]), api.iptr(out["cam_row_off"]), api.iptr(out["pt_perm"])))
+        return out
 
     def kernel_stats(self) -> Dict[str, Tuple[int, float]]:
         L = api.lib()

@@ -45,6 +45,10 @@ typedef struct ba_handle ba_handle;
 #define BA_PRECOND_JACOBI 0       /* camera blocks of J^T J                                    */
 #define BA_PRECOND_SCHUR_JACOBI 1 /* diagonal blocks of the Schur complement          (default) */
 
+#define BA_PATH_TILES 0    /* fused point-tile passes: one kernel per Schur mat-vec          (default) */
+#define BA_PATH_TWO_PASS 1 /* point-major pass + camera-major pass (also used when a track is longer
+                              than one tile, 512 observations)                                       */
+
 typedef struct ba_options {
     int32_t max_iters;        /* LM iterations, accepted + rejected (reference: max_nfev = 50)      */
     double gtol;              /* stop when max |gradient| < gtol               (SciPy default 1e-8) */
@@ -59,7 +63,8 @@ typedef struct ba_options {
     double pcg_tol;           /* forcing term: stop PCG when |r|_M^-1 <= pcg_tol * |b|_M^-1          */
     int32_t pcg_check_every;  /* host polls the device "PCG converged" flag every this many iterations */
     int32_t verbose;          /* bit 0: one stderr line per LM iteration; >= 2: per-kernel event timing */
-    int32_t reserved[7];
+    int32_t schur_path;       /* BA_PATH_*                                                          */
+    int32_t reserved[6];
 } ba_options;
 
 typedef struct ba_stats {
@@ -148,6 +153,11 @@ int ba_sparsity_csr(ba_handle* h, int64_t* indptr, int64_t* indices, int64_t* nn
  * Any pointer may be NULL. */
 int ba_normal_blocks(ba_handle* h, const ba_options* opt, double* gc, double* gp, double* U, double* V);
 
+/* Test hook: w = (U + lambda D - E (V + lambda D_p)^-1 E^T) u, the damped Schur complement of the
+ * Gauss-Newton system at the current parameters applied to u[n_adj*6], through the kernels of
+ * opt->schur_path (exactly what one PCG iteration runs).  Single-GPU handles only. */
+int ba_schur_matvec(ba_handle* h, const ba_options* opt, double lambda, const double* u, double* w_out);
+
 /* Run the Levenberg-Marquardt loop on the device from the current parameters; the parameters are
  * replaced by the result.  Replaces the least_squares call at src/bundle_adjuster.py:170-174. */
 int ba_solve(ba_handle* h, const ba_options* opt, ba_stats* stats_out);
@@ -159,6 +169,18 @@ int ba_solve(ba_handle* h, const ba_options* opt, ba_stats* stats_out);
 int ba_kernel_count(void);
 const char* ba_kernel_name(int k);
 int ba_kernel_stats(ba_handle* h, int64_t* launches /* [n] */, double* ms /* [n] */);
+
+/* Layout of the uploaded problem, for byte accounting: out[0..7] = n_obs, observations of adjustable
+ * cameras, n_pts, n_adj_cams, point tiles, tile segments (= mat-vec rows), point-major windows,
+ * camera-major tiles.  Point tiles = 0 when the fused path is unavailable (a track longer than a tile). */
+int ba_layout_info(ba_handle* h, int64_t out[8]);
+
+/* Test hook: copy out the point-tile structure built by ba_set_problem (sizes from ba_layout_info:
+ * T = point tiles, S = segments).  ft_pt/ft_obs/ft_seg[T+1], tc_word[n_obs], tc_uv[n_obs*2],
+ * seg_cam[S], seg_start[S+1], seg_row[S], cam_row_off[n_adj+2], pt_perm[n_pts] (internal point ->
+ * caller's index).  Any pointer may be NULL. */
+int ba_tile_layout(ba_handle* h, int32_t* ft_pt, int32_t* ft_obs, int32_t* ft_seg, uint32_t* tc_word, double* tc_uv,
+                   int32_t* seg_cam, int32_t* seg_start, int32_t* seg_row, int32_t* cam_row_off, int32_t* pt_perm);
 
 /* Thread-local text of the last error returned on this thread. */
 const char* ba_last_error(void);

@@ -145,6 +145,45 @@ def test_lm_iterates_match_cpu_restatement(gpu_solver):
     assert np.abs(gpu_solver.get_x() - ref.x()).max() <= 1e-8
 
 
+@pytest.mark.parametrize("path", ["tiles", "two_pass"])
+@pytest.mark.parametrize("shape,seed", [((6, 300, 1200), 3), ((25, 900, 4000), 5)])
+def test_schur_matvec_against_dense_schur_complement(gpu_solver, path, shape, seed):
+    """One implicit Schur mat-vec of the device (either kernel path) == the dense reduced camera matrix of
+    the CPU restatement times the same vector."""
+    fp = S.make_flat_problem(*shape, seed=seed)
+    prob = O.Problem.from_flat(fp)
+    lam = 1e-3
+    lin = L.linearize(prob, fp.rvec, fp.tvec, fp.pts)
+    _, _, _, aux = L.schur_step(prob, lin, lam)
+    u = np.random.default_rng(seed).normal(size=(prob.n_cams, 6))
+    w_ref = (aux["S"] @ u.ravel()).reshape(-1, 6)
+    gpu_solver.set_flat(fp)
+    w = gpu_solver.schur_matvec(u, lam, schur_path=path)
+    assert np.abs(w - w_ref).max() <= 1e-10 * np.abs(w_ref).max()
+
+
+@pytest.mark.parametrize("shape,seed", [((6, 300, 1200), 3), ((60, 5000, 26000), 8), ((3, 700, 1500), 9)])
+def test_fused_tiles_match_two_pass(gpu_solver, shape, seed):
+    """The fused point-tile mat-vec / back-substitution and the two-pass kernels are the same arithmetic
+    in a different summation order: identical LM trajectories to rounding."""
+    fp = S.make_flat_problem(*shape, seed=seed)
+    kw = dict(max_iters=5, pcg_tol=1e-10, pcg_max_iters=300, ftol=0.0, xtol=0.0, gtol=0.0)
+    out = {}
+    for path in ("tiles", "two_pass"):
+        gpu_solver.set_flat(fp)
+        st = gpu_solver.solve(schur_path=path, **kw)
+        ks = gpu_solver.kernel_stats()
+        out[path] = (st, gpu_solver.get_x(), ks)
+    assert out["tiles"][2]["schur_matvec_tiles"][0] > 0 and out["tiles"][2]["schur_matvec_points"][0] == 0
+    assert out["two_pass"][2]["schur_matvec_tiles"][0] == 0 and out["two_pass"][2]["schur_matvec_points"][0] > 0
+    a, b = out["tiles"][0], out["two_pass"][0]
+    assert a["iterations"] == b["iterations"] == 5
+    assert abs(a["final_cost"] - b["final_cost"]) <= 1e-9 * b["final_cost"]
+    assert np.abs(out["tiles"][1] - out["two_pass"][1]).max() <= 1e-7
+    info = gpu_solver.layout_info()
+    assert info["point_tiles"] > 0 and info["segments"] >= info["point_tiles"]
+
+
 @pytest.mark.parametrize("name", ["window_short", "window_cfg1", "global_cfg1"])
 def test_converged_cost_against_reference_objective(gpu_solver, name):
     """Same objective as the reference (Huber, 1 px, per coordinate).  Run to convergence the device
