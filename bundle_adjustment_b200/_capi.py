@@ -78,7 +78,7 @@ SYMBOLS = {
     "ba_kernel_name": (C.c_char_p, [C.c_int]),
     "ba_kernel_stats": (C.c_int, [C.c_void_p, _lp, _dp]),
     "ba_layout_info": (C.c_int, [C.c_void_p, _lp]),
-    "ba_tile_layout": (C.c_int, [C.c_void_p, _ip, _ip, _ip, C.POINTER(C.c_uint32), _dp, _ip, _ip, _ip, _ip, _ip]),
+    "ba_tile_layout": (C.c_int, [C.c_void_p, _ip, _ip, _ip, _ip, _dp, _ip, _ip, _ip, _ip, _ip]),
     "ba_last_error": (C.c_char_p, []),
 }
 

@@ -125,8 +125,12 @@ struct Params {
     const int* ft_pt;         // [ft_tiles+1] first point of a tile
     const int* ft_obs;        // [ft_tiles+1] first observation of a tile (same range in both tile orders)
     const int* ft_seg;        // [ft_tiles+1] first segment of a tile
+    const int4* ft_hdr;       // [2*ft_tiles] (p0, points, o0, observations), (s0, segments, -, -)
     const double2* tc_uv;     // [n_obs] tile-camera order
-    const unsigned* tc_word;  // [n_obs] local point | point-major position << 10 | local segment << 20
+    const int2* tc_meta;      // [n_obs] (camera slot, local point | point-major position << 10)
+    const int* pm_tc;         // [n_obs] point-major index -> tile-camera index
+    double2* tc_J;            // [2][3][n_obs] Jacobian cache W^1/2 Jp of the linearisation at parameter buffer b:
+                              // planes (jx0, jx1), (jx2, jy0), (jy1, jy2), tile-camera order
     const int* seg_cam;       // [n_seg]
     const int* seg_start;     // [n_seg+1] first tile-camera index of a segment
     const int* seg_row;       // [n_seg] row slot of a segment (camera-major)
@@ -373,6 +377,13 @@ __global__ void __launch_bounds__(PM_THREADS) k_lin_points(Params P, int which) 
         acc[0] += 0.5 * (r0x + r0y);
         acc[1] += o.rx * o.rx + o.ry * o.ry;
         if (!(isfinite(o.rx) && isfinite(o.ry))) acc[2] += 1.0;
+        if (P.tc_J) {
+            const double sx = sqrt(wHx), sy = sqrt(wHy);
+            double2* J = P.tc_J + (size_t)b * 3 * P.n_obs + __ldg(P.pm_tc + T.o0 + i);
+            J[0] = make_double2(sx * o.jx[0], sx * o.jx[1]);
+            J[P.n_obs] = make_double2(sx * o.jx[2], sy * o.jy[0]);
+            J[2 * (size_t)P.n_obs] = make_double2(sy * o.jy[1], sy * o.jy[2]);
+        }
         const double ax = wHx * o.jx[0], bx = wHx * o.jx[1], cx = wHx * o.jx[2];
         const double ay = wHy * o.jy[0], by = wHy * o.jy[1], cy = wHy * o.jy[2];
         sm[0 * cap + i] = ax * o.jx[0] + ay * o.jy[0];

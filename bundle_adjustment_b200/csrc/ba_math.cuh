@@ -136,6 +136,21 @@ BA_D void linearize_obs(const double* Rt, const double X[3], double u, double v,
     }
 }
 
+// rows of d r / d X only (what the Schur mat-vec needs: no measurement, no residual)
+BA_D void point_jacobian(const double* Rt, const double X[3], const Intr& K, double jx[3], double jy[3]) {
+    const double xc = fma(Rt[0], X[0], fma(Rt[1], X[1], fma(Rt[2], X[2], Rt[9])));
+    const double yc = fma(Rt[3], X[0], fma(Rt[4], X[1], fma(Rt[5], X[2], Rt[10])));
+    const double zc = fma(Rt[6], X[0], fma(Rt[7], X[1], fma(Rt[8], X[2], Rt[11])));
+    const double iz = 1.0 / zc;
+    const double un = xc * iz, vn = yc * iz;
+    const double sx = -K.fx * iz, sy = -K.fy * iz;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        jx[k] = sx * fma(-un, Rt[6 + k], Rt[k]);
+        jy[k] = sy * fma(-vn, Rt[6 + k], Rt[3 + k]);
+    }
+}
+
 BA_HD void cross3(const double a[3], const double b[3], double c[3]) {
     c[0] = a[1] * b[2] - a[2] * b[1];
     c[1] = a[2] * b[0] - a[0] * b[2];

@@ -338,10 +338,12 @@ struct ba_handle {
     DBuf<int> pt_perm;  // internal (locality-ordered) point id -> caller's point index
     // fused point tiles
     bool fused_ok = false;
-    int ft_tiles = 0, n_seg = 0;
+    int ft_tiles = 0, n_seg = 0, ft_grid = 0, sm_count = 0;
     DBuf<int> ft_pt, ft_obs, ft_seg, seg_cam, seg_start, seg_row, cam_row_off;
-    DBuf<double2> tc_uv;
-    DBuf<unsigned> tc_word;
+    DBuf<double2> tc_uv, tc_J;
+    DBuf<int2> tc_meta;
+    DBuf<int4> ft_hdr;
+    DBuf<int> pm_tc;
     DBuf<double> rows;
     DBuf<int4> cm_tile;
     DBuf<double> cm_partial, pm_partial, cam_partial;
@@ -430,6 +432,7 @@ static void create_common(ba_handle* h, int device) {
     CK(cudaGetDeviceProperties(&prop, device));
     if (prop.major < 10)
         fail(BA_ERR_CUDA, "device %d is sm_%d%d; libba_b200 is built for sm_100a only", device, prop.major, prop.minor);
+    h->sm_count = prop.multiProcessorCount;
     CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     CK(cudaMallocHost(&h->h_state, sizeof(LMState)));
     CK(cudaMallocHost(&h->h_flag, sizeof(int)));
@@ -470,7 +473,7 @@ static void build_tiles(ba_handle* h, int n_cams, int n_pts, int n_obs) {
     for (int p = 0; p < n_pts;) {
         const int o_begin = off[p];
         int q = p + 1;  // every track fits, so a tile always takes at least one point
-        while (q < n_pts && off[q + 1] - o_begin <= FT_THREADS && q - p < FT_THREADS) ++q;
+        while (q < n_pts && off[q + 1] - o_begin <= FT_THREADS && q - p < FT_PTS) ++q;
         tp.push_back(q); to.push_back(off[q]);
         p = q;
     }
@@ -505,8 +508,10 @@ static void build_tiles(ba_handle* h, int n_cams, int n_pts, int n_obs) {
     CK(cudaMemcpyAsync(&S, ic.p + n_obs - 1, sizeof(int), cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
 
-    h->tc_uv.alloc(n_obs); h->tc_word.alloc(n_obs);
-    h->seg_cam.alloc(S); h->seg_start.alloc((size_t)S + 1); h->seg_row.alloc(S); h->cam_row_off.alloc((size_t)n_cams + 2);
+    h->tc_uv.alloc(n_obs); h->tc_meta.alloc((size_t)n_obs + 2); h->pm_tc.alloc(n_obs); h->tc_J.alloc(6 * (size_t)n_obs);
+    h->ft_hdr.alloc(2 * (size_t)T);
+    h->seg_cam.alloc(S); h->seg_start.alloc((size_t)S + 1 + 4); h->seg_row.alloc((size_t)S + 4);  // + TMA window slack
+    h->cam_row_off.alloc((size_t)n_cams + 2);
     h->rows.alloc((size_t)S * 6);
     DBuf<unsigned> skey, skey_s;
     DBuf<int> sidx, sidx_s;
@@ -515,7 +520,8 @@ static void build_tiles(ba_handle* h, int n_cams, int n_pts, int n_obs) {
            h->seg_start.p);
     launch(h, KN_SETUP, k_ft_fill, cdiv(n_obs, B), B, 0, n_obs, (const unsigned long long*)key_s.p, (const int*)ib.p,
            (const int*)ia.p, (const int*)ic.p, (const int*)h->ft_obs.p, (const int*)h->ft_pt.p, (const int*)h->ft_seg.p,
-           (const double2*)h->pm_uv.p, (const int2*)h->pm_idx.p, h->tc_uv.p, h->tc_word.p, h->seg_cam.p, h->seg_start.p, skey.p);
+           (const double2*)h->pm_uv.p, (const int2*)h->pm_idx.p, h->tc_uv.p, h->tc_meta.p, h->pm_tc.p, h->seg_cam.p, h->seg_start.p, skey.p);
+    launch(h, KN_SETUP, k_ft_headers, cdiv(T, B), B, 0, T, (const int*)h->ft_pt.p, (const int*)h->ft_obs.p, (const int*)h->ft_seg.p, h->ft_hdr.p);
     // rows camera-major: stable sort of the segments by camera
     launch(h, KN_SETUP, k_iota, cdiv(S, B), B, 0, S, sidx.p);
     int cam_bits = 1;
@@ -531,6 +537,7 @@ static void build_tiles(ba_handle* h, int n_cams, int n_pts, int n_obs) {
     CK(cudaFuncSetAttribute(k_tile_pass<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ft_smem_bytes(FT_ROWS_MV)));
     CK(cudaStreamSynchronize(s));  // scratch dies here
     h->ft_tiles = T; h->n_seg = S;
+    h->ft_grid = std::min(T, 2 * h->sm_count);  // persistent CTAs, two per SM
     h->fused_ok = true;
 }
 
@@ -562,7 +569,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     h->cam_partial.zero(s); h->cam_g.zero(s); h->cam_D.zero(s); h->cam_U.zero(s);
     h->o_uv.alloc(n_obs); h->o_idx.alloc(n_obs); h->pm_uv.alloc(n_obs); h->pm_idx.alloc(n_obs);
     h->cm_uv.alloc(n_obs); h->cm_pt.alloc(n_obs);
-    h->pt_off.alloc((size_t)n_pts + 1);
+    h->pt_off.alloc((size_t)n_pts + 1 + 4);  // + TMA window slack
     h->cam_tile_off.alloc(nc1);
 
     // ---- upload -------------------------------------------------------------------------------
@@ -689,7 +696,9 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     P.cam_tile_off = h->cam_tile_off.p; P.cm_partial = h->cm_partial.p; P.pm_partial = h->pm_partial.p;
     P.cam_partial = h->cam_partial.p; P.st = h->st.p;
     P.ft_tiles = h->ft_tiles; P.n_seg = h->n_seg; P.n_partial_rows = n_partial_rows;
-    P.ft_pt = h->ft_pt.p; P.ft_obs = h->ft_obs.p; P.ft_seg = h->ft_seg.p; P.tc_uv = h->tc_uv.p; P.tc_word = h->tc_word.p;
+    P.ft_pt = h->ft_pt.p; P.ft_obs = h->ft_obs.p; P.ft_seg = h->ft_seg.p; P.tc_uv = h->tc_uv.p;
+    P.ft_hdr = h->ft_hdr.p; P.tc_meta = h->tc_meta.p; P.pm_tc = h->fused_ok ? h->pm_tc.p : nullptr;
+    P.tc_J = h->fused_ok ? h->tc_J.p : nullptr;
     P.seg_cam = h->seg_cam.p; P.seg_start = h->seg_start.p; P.seg_row = h->seg_row.p; P.cam_row_off = h->cam_row_off.p;
     P.rows = h->rows.p;
     h->st.zero(s);
@@ -818,7 +827,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
             for (int it = 0; it < opt->pcg_max_iters; ++it) {
                 int n_dots = P.vec_ctas;
                 if (tiles) {
-                    launch(h, KN_TILE_MV, k_tile_pass<0>, P.ft_tiles, FT_THREADS, ft_smem_bytes(FT_ROWS_MV), P, (const double*)h->v_u.p);
+                    launch(h, KN_TILE_MV, k_tile_pass<0>, h->ft_grid, FT_THREADS, ft_smem_bytes(FT_ROWS_MV), P, (const double*)h->v_u.p);
                     if (h->nranks > 1) {
                         launch(h, KN_ROWS_FIN, k_rows_finish<true>, cdiv(P.n_cams, RS_WARPS), RS_WARPS * 32, 0, P);
                         allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 6);
@@ -847,7 +856,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
             }
         }
         if (tiles)
-            launch(h, KN_TILE_BACKSUB, k_tile_pass<1>, P.ft_tiles, FT_THREADS, ft_smem_bytes(FT_ROWS_MV), P, (const double*)h->v_x.p);
+            launch(h, KN_TILE_BACKSUB, k_tile_pass<1>, h->ft_grid, FT_THREADS, ft_smem_bytes(FT_ROWS_MV), P, (const double*)h->v_x.p);
         else
             launch(h, KN_BACKSUB, k_point_pass<1>, P.pm_tiles, PM_THREADS, h->smem_pass, P, (const double*)h->v_x.p);
         launch(h, KN_CAM_UPDATE, k_camera_update, cdiv(nc1, 128), 128, 0, P);
@@ -1200,7 +1209,7 @@ int ba_schur_matvec(ba_handle* h, const ba_options* opt, double lambda, const do
     ba::launch(h, ba::KN_PT_PREP, ba::k_point_prepare, ba::cdiv(P.n_pts, 256), 256, 0, P, ba::kDiagMin, ba::kDiagMax);
     CK(cudaMemcpyAsync(h->v_u.p, u, (size_t)P.n_cams * 6 * sizeof(double), cudaMemcpyHostToDevice, s));
     if (tiles) {
-        ba::launch(h, ba::KN_TILE_MV, ba::k_tile_pass<0>, P.ft_tiles, ba::FT_THREADS, ba::ft_smem_bytes(ba::FT_ROWS_MV), P,
+        ba::launch(h, ba::KN_TILE_MV, ba::k_tile_pass<0>, h->ft_grid, ba::FT_THREADS, ba::ft_smem_bytes(ba::FT_ROWS_MV), P,
                    (const double*)h->v_u.p);
         ba::launch(h, ba::KN_ROWS_FIN, ba::k_rows_finish<false>, ba::cdiv(P.n_cams, ba::RS_WARPS), ba::RS_WARPS * 32, 0, P);
     } else {
@@ -1232,7 +1241,7 @@ int ba_layout_info(ba_handle* h, int64_t out[8]) {
     API_END
 }
 
-int ba_tile_layout(ba_handle* h, int32_t* ft_pt, int32_t* ft_obs, int32_t* ft_seg, uint32_t* tc_word, double* tc_uv,
+int ba_tile_layout(ba_handle* h, int32_t* ft_pt, int32_t* ft_obs, int32_t* ft_seg, int32_t* tc_meta, double* tc_uv,
                    int32_t* seg_cam, int32_t* seg_start, int32_t* seg_row, int32_t* cam_row_off, int32_t* pt_perm) {
     API_BEGIN
     ba::need_problem(h);
@@ -1244,7 +1253,7 @@ int ba_tile_layout(ba_handle* h, int32_t* ft_pt, int32_t* ft_obs, int32_t* ft_se
         if (dst) CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, s));
     };
     get(ft_pt, h->ft_pt.p, (T + 1) * 4); get(ft_obs, h->ft_obs.p, (T + 1) * 4); get(ft_seg, h->ft_seg.p, (T + 1) * 4);
-    get(tc_word, h->tc_word.p, (size_t)P.n_obs * 4); get(tc_uv, h->tc_uv.p, (size_t)P.n_obs * 16);
+    get(tc_meta, h->tc_meta.p, (size_t)P.n_obs * 8); get(tc_uv, h->tc_uv.p, (size_t)P.n_obs * 16);
     get(seg_cam, h->seg_cam.p, S * 4); get(seg_start, h->seg_start.p, (S + 1) * 4); get(seg_row, h->seg_row.p, S * 4);
     get(cam_row_off, h->cam_row_off.p, ((size_t)P.n_cams + 2) * 4); get(pt_perm, h->pt_perm.p, (size_t)P.n_pts * 4);
     CK(cudaStreamSynchronize(s));

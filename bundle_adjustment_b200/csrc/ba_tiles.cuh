@@ -21,28 +21,77 @@
 //   * rows are laid out camera-major, so the per-camera finish is a contiguous, fixed-order sum.
 // No floating-point atomics: every sum has a fixed order, results are bit-reproducible.
 //
-// Per-observation word (tc_word): bits 0-9 local point index, 10-19 position of the observation in
-// the tile's point-major order (where its per-point contribution is parked), 20-31 local segment.
+// Per-observation record (tc_meta): .x camera slot, .y = local point index | position of the observation
+// in the tile's point-major order << 10 (where its per-point contribution is parked).
 #pragma once
 #include "ba_kernels.cuh"
 
 namespace ba {
 
 constexpr int FT_THREADS = 512;        // threads per CTA = observation capacity of a tile
-constexpr int FT_SEG_MAX = 32;         // observations per segment (one output row each)
+constexpr int FT_PTS = 256;            // point capacity of a tile
+constexpr int FT_SEG_MAX = 16;         // observations per segment (one output row each)
 constexpr int FT_LD = FT_THREADS + 2;  // row stride of the per-observation scratch (doubles); 2*FT_LD mod 32 = 4 banks
 constexpr int FT_ROWS_MV = 6;          // scratch rows of the mat-vec pass
-constexpr size_t ft_smem_bytes(int rows) { return (size_t)(FT_THREADS * 3 + rows * FT_LD) * sizeof(double); }
+
+// dynamic shared memory of a tile pass (16-byte aligned regions): per-observation scratch rows | Jacobian
+// cache planes [3][FT_THREADS] double2 | observation records | X [FT_PTS][4] | z [FT_PTS][4] | Vinv [FT_PTS][6] |
+// track offsets | segment starts x2 | segment rows x2 | two mbarriers.  The x2 regions are double-buffered
+// by tile parity; everything else is refilled by the TMA as soon as its last reader has passed a barrier.
+constexpr int FT_META_N = FT_THREADS + 2, FT_OFF_N = FT_PTS + 8, FT_SEG_N = FT_THREADS + 8;
+struct FtSmem {
+    double* sO; double2* sJ; int2* sMeta; double* sX; double* sZ; double* sVi; int* sOff; int* sSeg; int* sRow;
+    unsigned long long* bar;
+};
+__host__ __device__ constexpr size_t ft_smem_bytes(int rows) {
+    return (size_t)(rows * FT_LD) * 8 + 3 * FT_THREADS * 16 + FT_META_N * 8 + (size_t)FT_PTS * (4 + 4 + 6) * 8 +
+           (size_t)(FT_OFF_N + 4 * FT_SEG_N) * 4 + 16;
+}
+BA_D FtSmem ft_carve(double* sm, int rows) {
+    FtSmem S;
+    S.sO = sm;
+    S.sJ = reinterpret_cast<double2*>(S.sO + rows * FT_LD);
+    S.sMeta = reinterpret_cast<int2*>(S.sJ + 3 * FT_THREADS);
+    S.sX = reinterpret_cast<double*>(S.sMeta + FT_META_N);
+    S.sZ = S.sX + FT_PTS * 4;
+    S.sVi = S.sZ + FT_PTS * 4;
+    S.sOff = reinterpret_cast<int*>(S.sVi + FT_PTS * 6);
+    S.sSeg = S.sOff + FT_OFF_N;
+    S.sRow = S.sSeg + 2 * FT_SEG_N;
+    S.bar = reinterpret_cast<unsigned long long*>(S.sRow + 2 * FT_SEG_N);
+    return S;
+}
+
+// ---- TMA (bulk asynchronous copy, global -> shared) and its mbarrier --------------------------------
+BA_D unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+BA_D void mbar_init(unsigned long long* bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+BA_D void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+    asm volatile("{\n.reg .b64 st;\nmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n}\n" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+BA_D void mbar_wait(unsigned long long* bar, unsigned parity) {
+    unsigned ok;
+    do {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+                     : "=r"(ok)
+                     : "r"(smem_u32(bar)), "r"(parity)
+                     : "memory");
+    } while (!ok);
+}
+// bytes must be a positive multiple of 16, both addresses 16-byte aligned
+BA_D void tma_load(void* smem, const void* gmem, unsigned bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(smem_u32(smem)),
+                 "l"(gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
 
 struct TileHdr { int p0, m, o0, n, s0, ns; };
 BA_D TileHdr tile_hdr(const Params& P, int t) {
+    const int4 a = __ldg(P.ft_hdr + 2 * t), b = __ldg(P.ft_hdr + 2 * t + 1);
     TileHdr T;
-    T.p0 = __ldg(P.ft_pt + t);
-    T.m = __ldg(P.ft_pt + t + 1) - T.p0;
-    T.o0 = __ldg(P.ft_obs + t);
-    T.n = __ldg(P.ft_obs + t + 1) - T.o0;
-    T.s0 = __ldg(P.ft_seg + t);
-    T.ns = __ldg(P.ft_seg + t + 1) - T.s0;
+    T.p0 = a.x; T.m = a.y; T.o0 = a.z; T.n = a.w; T.s0 = b.x; T.ns = b.y;
     return T;
 }
 
@@ -50,126 +99,210 @@ BA_D TileHdr tile_hdr(const Params& P, int t) {
 //         rows[seg] = sum over the segment of Jc^T W (Jc vec_c - Jp z_p),  z_p = Vinv_p sum Jp^T W Jc vec_c.
 // MODE 1: back-substitution with the PCG solution `vec`: dp = -h_p - z_p(vec), X_trial = X + dp, and the
 //         step's scalar products (per tile partials).
+// The pass streams the JACOBIAN CACHE of the current linearisation: Jt = W^1/2 Jp (2x3, 48 bytes per
+// observation, tile-camera order, written by k_lin_points).  With the weights folded in,
+//         a = Jt (w x X + v),  s_p = sum Jt^T a,  z = Vinv s,  b = a - Jt z,  m = Jt^T b,  row += [X x m ; m],
+// so the pass needs no camera pose, no measurement, no division: per observation 56 bytes from HBM, the
+// camera's 6-vector from L1 (broadcast inside a camera run) and the point from shared memory.
+//
+// Persistent CTAs (grid = 2 per SM) walk the tiles round-robin.  All HBM traffic of a tile is moved by
+// the TMA (cp.async.bulk) while the PREVIOUS tile is being computed: group 1 (observation records,
+// Jacobian cache, points, segment table) is re-armed right after phase A has pulled its operands into
+// registers, group 2 (Vinv, track offsets) right after phase B; each group completes on its own mbarrier.
+struct TileCopy {  // 16-byte aligned source windows of one tile
+    int meta_lo, off_lo, seg_lo;  // first element copied (<= the tile's first) of tc_meta / pt_off / seg arrays
+};
+
+template <int MODE>
+BA_D void ft_issue_group1(const Params& P, const FtSmem& S, const TileHdr& T, int b, int buf, unsigned long long* bar) {
+    const int meta_lo = T.o0 & ~1, seg_lo = T.s0 & ~3;
+    const unsigned meta_b = (unsigned)(((T.o0 + T.n - meta_lo) * 8 + 15) & ~15);
+    const unsigned j_b = (unsigned)T.n * 16u, x_b = (unsigned)T.m * 32u;
+    const unsigned seg_b = (unsigned)(((T.s0 + T.ns + 1 - seg_lo) * 4 + 15) & ~15);
+    unsigned total = x_b;
+    if (T.n > 0) total += meta_b + 3 * j_b;
+    if (MODE == 0) total += 2 * seg_b;
+    mbar_expect_tx(bar, total);
+    if (T.n > 0) {
+        tma_load(S.sMeta, P.tc_meta + meta_lo, meta_b, bar);
+        const double2* J = P.tc_J + (size_t)b * 3 * P.n_obs + T.o0;
+#pragma unroll
+        for (int r = 0; r < 3; ++r) tma_load(S.sJ + r * FT_THREADS, J + (size_t)r * P.n_obs, j_b, bar);
+    }
+    tma_load(S.sX, pt_x(P, b, T.p0), x_b, bar);
+    if (MODE == 0) {
+        tma_load(S.sSeg + buf * FT_SEG_N, P.seg_start + seg_lo, seg_b, bar);
+        tma_load(S.sRow + buf * FT_SEG_N, P.seg_row + seg_lo, seg_b, bar);
+    }
+}
+BA_D void ft_issue_group2(const Params& P, const FtSmem& S, const TileHdr& T, unsigned long long* bar) {
+    const int off_lo = T.p0 & ~3;
+    const unsigned vi_b = (unsigned)T.m * 48u;
+    const unsigned off_b = (unsigned)(((T.p0 + T.m + 1 - off_lo) * 4 + 15) & ~15);
+    mbar_expect_tx(bar, vi_b + off_b);
+    tma_load(S.sVi, P.pt_Vinv + (size_t)T.p0 * 6, vi_b, bar);
+    tma_load(S.sOff, P.pt_off + off_lo, off_b, bar);
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(FT_THREADS, 2) k_tile_pass(Params P, const double* __restrict__ vec) {
     extern __shared__ __align__(16) double sm[];
-    double* sP = sm;                   // [m][3]  point positions (phase A), then z_p (phase C)
-    double* sO = sm + FT_THREADS * 3;  // scratch rows of FT_LD doubles
     __shared__ double red[FT_THREADS / 32 * 4];
     __shared__ double tot[4];
     if (MODE == 0 && P.st->pcg_done) return;
+    int t = blockIdx.x;
+    if (t >= P.ft_tiles) return;
+    const FtSmem S = ft_carve(sm, FT_ROWS_MV);
     const int b = P.st->cur;
     const int tid = threadIdx.x;
-    const TileHdr T = tile_hdr(P, blockIdx.x);
-    const bool act = tid < T.n;
-
-    // ---- phase 0: stage the tile's points, fetch this thread's observation and camera ----------
-    double2 uv = make_double2(0.0, 0.0);
-    unsigned word = 0;
-    double rec[18];
-    if (act) {
-        uv = __ldg(P.tc_uv + T.o0 + tid);
-        word = __ldg(P.tc_word + T.o0 + tid);
-    }
-    if (tid < T.m) {
-        const double2* q = reinterpret_cast<const double2*>(pt_x(P, b, T.p0 + tid));
-        const double2 a = __ldg(q), c = __ldg(q + 1);
-        sP[3 * tid] = a.x; sP[3 * tid + 1] = a.y; sP[3 * tid + 2] = c.x;
-    }
-    if (act) {
-        const int cam = __ldg(P.seg_cam + T.s0 + (word >> 20));
-        load_cam(P.cam_R + (size_t)b * (P.n_cams + 1) * 12, cam, rec);
-        load_vec6(vec, cam, rec + 12);
+    TileHdr T = tile_hdr(P, t);
+    if (tid == 0) {
+        mbar_init(S.bar, 1);
+        mbar_init(S.bar + 1, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+        ft_issue_group1<MODE>(P, S, T, b, 0, S.bar);
+        ft_issue_group2(P, S, T, S.bar + 1);
     }
     __syncthreads();
 
-    // ---- phase A: linearise; park Jp^T W Jc vec_c at the observation's point-major position ------
-    double X[3] = {0.0, 0.0, 0.0}, jx[3] = {0.0, 0.0, 0.0}, jy[3] = {0.0, 0.0, 0.0};
-    double ax = 0.0, ay = 0.0, wHx = 0.0, wHy = 0.0;
-    const int pl = word & 1023u;
-    if (act) {
-        const int pos = (word >> 10) & 1023u;
-        X[0] = sP[3 * pl]; X[1] = sP[3 * pl + 1]; X[2] = sP[3 * pl + 2];
-        ObsLin o;
-        linearize_obs(rec, X, uv.x, uv.y, P.K, o);
-        double wgx, r0x, wgy, r0y;
-        robust_weights(o.rx, P.delta, P.mode, wHx, wgx, r0x);
-        robust_weights(o.ry, P.delta, P.mode, wHy, wgy, r0y);
-        const double* x = rec + 12;
-        const double d0 = fma(x[1], X[2], fma(-x[2], X[1], x[3]));  // d = w x X + v
-        const double d1 = fma(x[2], X[0], fma(-x[0], X[2], x[4]));
-        const double d2 = fma(x[0], X[1], fma(-x[1], X[0], x[5]));
-#pragma unroll
-        for (int k = 0; k < 3; ++k) { jx[k] = o.jx[k]; jy[k] = o.jy[k]; }
-        ax = wHx * (jx[0] * d0 + jx[1] * d1 + jx[2] * d2);
-        ay = wHy * (jy[0] * d0 + jy[1] * d1 + jy[2] * d2);
-        sO[pos] = jx[0] * ax + jy[0] * ay;
-        sO[FT_LD + pos] = jx[1] * ax + jy[1] * ay;
-        sO[2 * FT_LD + pos] = jx[2] * ax + jy[2] * ay;
-    }
-    __syncthreads();
+    for (unsigned it = 0;; ++it) {
+        const int buf = it & 1;
+        const int tn = t + gridDim.x;
+        const bool have_next = tn < P.ft_tiles;
+        TileHdr Tn = T;
+        if (have_next && tid == 0) Tn = tile_hdr(P, tn);
+        const bool act = tid < T.n;
 
-    // ---- phase B: one thread per point: sum its track in observation order, apply Vinv -----------
-    double acc[4] = {0.0, 0.0, 0.0, 0.0};  // MODE 1: g.dp, dp D dp, |dp|^2, |X|^2
-    if (tid < T.m) {
-        const int p = T.p0 + tid;
-        const int a = __ldg(P.pt_off + p) - T.o0, e = __ldg(P.pt_off + p + 1) - T.o0;
-        double s[3] = {0.0, 0.0, 0.0};
-        for (int i = a; i < e; ++i) {
-            s[0] += sO[i]; s[1] += sO[FT_LD + i]; s[2] += sO[2 * FT_LD + i];
+        // ---- phase A: operands to registers; a = Jt (w x X + v); park Jt^T a at the point-major position --
+        mbar_wait(S.bar, it & 1);
+        int2 meta = make_int2(P.n_cams, 0);
+        double2 j0 = make_double2(0.0, 0.0), j1 = j0, j2 = j0;  // (jx0, jx1) (jx2, jy0) (jy1, jy2)
+        if (act) {
+            meta = S.sMeta[(T.o0 & 1) + tid];
+            j0 = S.sJ[tid]; j1 = S.sJ[FT_THREADS + tid]; j2 = S.sJ[2 * FT_THREADS + tid];
         }
-        double Vi[6], z[3];
-        load_sym3(P.pt_Vinv, p, Vi);
-        sym3_mulv(Vi, s, z);
-        if (MODE == 0) {
-            sP[3 * tid] = z[0]; sP[3 * tid + 1] = z[1]; sP[3 * tid + 2] = z[2];
-        } else {
-            double h[3], g[3], D[3];
-            const double Xp[3] = {sP[3 * tid], sP[3 * tid + 1], sP[3 * tid + 2]};
-            load_v3(P.pt_h + (size_t)p * 4, h);
-            load_v3(P.pt_g + (size_t)b * P.n_pts * 4 + (size_t)p * 4, g);
-            load_v3(P.pt_D + (size_t)p * 4, D);
-            const double dp0 = -h[0] - z[0], dp1 = -h[1] - z[1], dp2 = -h[2] - z[2];
-            store_v3(pt_x(P, b ^ 1, p), Xp[0] + dp0, Xp[1] + dp1, Xp[2] + dp2);
-            acc[0] = g[0] * dp0 + g[1] * dp1 + g[2] * dp2;
-            acc[1] = D[0] * dp0 * dp0 + D[1] * dp1 * dp1 + D[2] * dp2 * dp2;
-            acc[2] = dp0 * dp0 + dp1 * dp1 + dp2 * dp2;
-            acc[3] = Xp[0] * Xp[0] + Xp[1] * Xp[1] + Xp[2] * Xp[2];
+        double x[6];
+        load_vec6(vec, meta.x, x);
+        double X[3] = {0.0, 0.0, 0.0};
+        double ax = 0.0, ay = 0.0;
+        const int pl = meta.y & 1023;
+        if (act) {
+            const int pos = (meta.y >> 10) & 1023;
+            const double2 x01 = *reinterpret_cast<const double2*>(S.sX + 4 * pl);
+            X[0] = x01.x; X[1] = x01.y; X[2] = S.sX[4 * pl + 2];
+            const double d0 = fma(x[1], X[2], fma(-x[2], X[1], x[3]));  // d = w x X + v
+            const double d1 = fma(x[2], X[0], fma(-x[0], X[2], x[4]));
+            const double d2 = fma(x[0], X[1], fma(-x[1], X[0], x[5]));
+            ax = j0.x * d0 + j0.y * d1 + j1.x * d2;
+            ay = j1.y * d0 + j2.x * d1 + j2.y * d2;
+            S.sO[pos] = j0.x * ax + j1.y * ay;
+            S.sO[FT_LD + pos] = j0.y * ax + j2.x * ay;
+            S.sO[2 * FT_LD + pos] = j1.x * ax + j2.y * ay;
         }
-    }
-    if (MODE == 1) {
-        block_sum<4, FT_THREADS>(acc, red, tot);
         __syncthreads();
-        if (tid == 0) {
-            double* out = P.pm_partial + (size_t)blockIdx.x * NSCAL;
-            out[S_GDP] = tot[0]; out[S_DDP] = tot[1]; out[S_DP2] = tot[2]; out[S_XP2] = tot[3];
+        if (MODE == 0 && have_next && tid == 0) ft_issue_group1<MODE>(P, S, Tn, b, buf ^ 1, S.bar);
+
+        // ---- phase B: four lanes per point: lane k < 3 adds component k of the track in observation
+        //      order, the quad exchanges the three sums and lane k forms row k of Vinv * s --------------
+        mbar_wait(S.bar + 1, it & 1);
+        double acc[4] = {0.0, 0.0, 0.0, 0.0};  // MODE 1: g.dp, dp D dp, |dp|^2, |X|^2
+        {
+            const int k = tid & 3, lane = tid & 31;
+            const int* off = S.sOff + (T.p0 & 3);
+            for (int q0 = (tid & ~31) >> 2; q0 < T.m; q0 += FT_THREADS / 4) {  // warp-uniform bounds
+                const int q = q0 + (lane >> 2);
+                const bool valid = q < T.m;
+                double sk = 0.0;
+                if (valid && k < 3) {
+                    const int a = off[q] - T.o0, e = off[q + 1] - T.o0;
+                    const double* src = S.sO + k * FT_LD;
+                    for (int i0 = a; i0 < e; i0 += 8) {  // loads first, then the (ordered) adds; x + 0.0 is exact
+                        double v[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) v[j] = (i0 + j < e) ? src[i0 + j] : 0.0;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) sk += v[j];
+                    }
+                }
+                const double s0 = __shfl_sync(0xffffffffu, sk, (lane & ~3));
+                const double s1 = __shfl_sync(0xffffffffu, sk, (lane & ~3) + 1);
+                const double s2 = __shfl_sync(0xffffffffu, sk, (lane & ~3) + 2);
+                double zk = 0.0;
+                if (valid && k < 3) {
+                    const double* Vi = S.sVi + 6 * q;  // 00 01 02 11 12 22
+                    const double v0 = Vi[k], v1 = Vi[k == 0 ? 1 : (k == 1 ? 3 : 4)], v2 = Vi[k == 2 ? 5 : (k == 1 ? 4 : 2)];
+                    zk = v0 * s0 + v1 * s1 + v2 * s2;
+                }
+                if (MODE == 0) {
+                    if (valid && k < 3) S.sZ[4 * q + k] = zk;
+                } else if (valid) {
+                    const size_t p4 = (size_t)(T.p0 + q) * 4 + k;
+                    const double Xk = S.sX[4 * q + k];
+                    const double dp = -__ldg(P.pt_h + p4) - zk;  // the pad lane carries zeros throughout
+                    const double gk = __ldg(P.pt_g + (size_t)b * P.n_pts * 4 + p4), Dk = __ldg(P.pt_D + p4);
+                    P.pt_X[(size_t)(b ^ 1) * P.n_pts * 4 + p4] = Xk + dp;
+                    acc[0] += gk * dp; acc[1] += Dk * dp * dp; acc[2] += dp * dp; acc[3] += Xk * Xk;
+                }
+            }
         }
-        return;
-    }
-    __syncthreads();
+        if (MODE == 1) {
+            block_sum<4, FT_THREADS>(acc, red, tot);
+            __syncthreads();
+            if (tid == 0) {
+                double* out = P.pm_partial + (size_t)t * NSCAL;
+                out[S_GDP] = tot[0]; out[S_DDP] = tot[1]; out[S_DP2] = tot[2]; out[S_XP2] = tot[3];
+                if (have_next) {
+                    ft_issue_group1<MODE>(P, S, Tn, b, buf ^ 1, S.bar);
+                    ft_issue_group2(P, S, Tn, S.bar + 1);
+                }
+            }
+        } else {
+            __syncthreads();
+            if (have_next && tid == 0) ft_issue_group2(P, S, Tn, S.bar + 1);
 
-    // ---- phase C: camera-side product of every observation, parked at its tile-camera position ----
-    if (act) {
-        const double z0 = sP[3 * pl], z1 = sP[3 * pl + 1], z2 = sP[3 * pl + 2];
-        const double bx = ax - wHx * (jx[0] * z0 + jx[1] * z1 + jx[2] * z2);
-        const double by = ay - wHy * (jy[0] * z0 + jy[1] * z1 + jy[2] * z2);
-        double mm[3], xm[3];
+            // ---- phase C: camera-side product of every observation, parked at its tile-camera position --
+            if (act) {
+                const double2 z01 = *reinterpret_cast<const double2*>(S.sZ + 4 * pl);
+                const double z2 = S.sZ[4 * pl + 2];
+                const double bx = ax - (j0.x * z01.x + j0.y * z01.y + j1.x * z2);
+                const double by = ay - (j1.y * z01.x + j2.x * z01.y + j2.y * z2);
+                const double mm[3] = {j0.x * bx + j1.y * by, j0.y * bx + j2.x * by, j1.x * bx + j2.y * by};
+                double xm[3];
+                cross3(X, mm, xm);
 #pragma unroll
-        for (int k = 0; k < 3; ++k) mm[k] = jx[k] * bx + jy[k] * by;
-        cross3(X, mm, xm);
-#pragma unroll
-        for (int k = 0; k < 3; ++k) { sO[k * FT_LD + tid] = xm[k]; sO[(3 + k) * FT_LD + tid] = mm[k]; }
-    }
-    __syncthreads();
+                for (int k = 0; k < 3; ++k) { S.sO[k * FT_LD + tid] = xm[k]; S.sO[(3 + k) * FT_LD + tid] = mm[k]; }
+            }
+            __syncthreads();
 
-    // ---- phase D: one thread per (segment, component): fixed-order sum -> one row per segment -----
-    for (int w = tid; w < T.ns * 6; w += FT_THREADS) {
-        const int seg = w / 6, k = w - 6 * seg;
-        const int a = __ldg(P.seg_start + T.s0 + seg) - T.o0, e = __ldg(P.seg_start + T.s0 + seg + 1) - T.o0;
-        const double* src = sO + k * FT_LD;
-        double s = 0.0;
-        for (int i = a; i < e; ++i) s += src[i];
-        P.rows[(size_t)__ldg(P.seg_row + T.s0 + seg) * 6 + k] = s;
+            // ---- phase D: one thread per (segment, component): fixed-order sum -> one row per segment ---
+            const int* seg_s = S.sSeg + buf * FT_SEG_N + (T.s0 & 3);
+            const int* seg_r = S.sRow + buf * FT_SEG_N + (T.s0 & 3);
+            for (int w = tid; w < T.ns * 6; w += FT_THREADS) {
+                const int seg = w / 6, k = w - 6 * seg;
+                const int a = seg_s[seg] - T.o0, e = seg_s[seg + 1] - T.o0;
+                const double* src = S.sO + k * FT_LD;
+                double v[FT_SEG_MAX];
+#pragma unroll
+                for (int j = 0; j < FT_SEG_MAX; ++j) v[j] = (a + j < e) ? src[a + j] : 0.0;
+                double sum = 0.0;
+#pragma unroll
+                for (int j = 0; j < FT_SEG_MAX; ++j) sum += v[j];
+                P.rows[(size_t)seg_r[seg] * 6 + k] = sum;
+            }
+        }
+        if (!have_next) break;
+        // the next tile's header travels from thread 0 to everybody through shared memory
+        if (tid == 0) {
+            int* hs = reinterpret_cast<int*>(tot);  // free between tiles in MODE 0; MODE 1 has consumed tot above
+            hs[0] = Tn.p0; hs[1] = Tn.m; hs[2] = Tn.o0; hs[3] = Tn.n; hs[4] = Tn.s0; hs[5] = Tn.ns;
+        }
+        __syncthreads();
+        {
+            const int* hs = reinterpret_cast<const int*>(tot);
+            T.p0 = hs[0]; T.m = hs[1]; T.o0 = hs[2]; T.n = hs[3]; T.s0 = hs[4]; T.ns = hs[5];
+        }
+        t = tn;
     }
 }
 
@@ -264,17 +397,26 @@ __global__ void k_ft_tile_seg(int n_tiles, int n_obs, int n_seg, const int* __re
 __global__ void k_ft_fill(int n_obs, const unsigned long long* __restrict__ key_s, const int* __restrict__ src,
                           const int* __restrict__ flag, const int* __restrict__ seg_inc, const int* __restrict__ ft_obs,
                           const int* __restrict__ ft_pt, const int* __restrict__ ft_seg, const double2* __restrict__ pm_uv,
-                          const int2* __restrict__ pm_idx, double2* __restrict__ tc_uv, unsigned* __restrict__ tc_word,
-                          int* __restrict__ seg_cam, int* __restrict__ seg_start, unsigned* __restrict__ seg_key) {
+                          const int2* __restrict__ pm_idx, double2* __restrict__ tc_uv, int2* __restrict__ tc_meta,
+                          int* __restrict__ pm_tc, int* __restrict__ seg_cam, int* __restrict__ seg_start,
+                          unsigned* __restrict__ seg_key) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_obs) return;
     const int j = src[i];
     const int t = (int)(key_s[i] >> 32), cam = (int)(unsigned)key_s[i];
     const int s = seg_inc[i] - 1;
-    const unsigned pl = (unsigned)(pm_idx[j].y - ft_pt[t]), pos = (unsigned)(j - ft_obs[t]), sl = (unsigned)(s - ft_seg[t]);
+    const unsigned pl = (unsigned)(pm_idx[j].y - ft_pt[t]), pos = (unsigned)(j - ft_obs[t]);
     tc_uv[i] = pm_uv[j];
-    tc_word[i] = pl | (pos << 10) | (sl << 20);
+    tc_meta[i] = make_int2(cam, (int)(pl | (pos << 10)));
+    pm_tc[j] = i;
     if (flag[i]) { seg_cam[s] = cam; seg_start[s] = i; seg_key[s] = (unsigned)cam; }
+}
+__global__ void k_ft_headers(int n_tiles, const int* __restrict__ ft_pt, const int* __restrict__ ft_obs,
+                             const int* __restrict__ ft_seg, int4* __restrict__ hdr) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_tiles) return;
+    hdr[2 * t] = make_int4(ft_pt[t], ft_pt[t + 1] - ft_pt[t], ft_obs[t], ft_obs[t + 1] - ft_obs[t]);
+    hdr[2 * t + 1] = make_int4(ft_seg[t], ft_seg[t + 1] - ft_seg[t], 0, 0);
 }
 __global__ void k_ft_seg_rows(int n_seg, const int* __restrict__ sorted_seg, int* __restrict__ seg_row) {
     const int r = blockIdx.x * blockDim.x + threadIdx.x;

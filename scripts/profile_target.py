@@ -13,5 +13,5 @@ pcg = int(sys.argv[2]) if len(sys.argv) > 2 else 3
 fp = S.make_named_problem(shape, keep_truth=False)
 s = FlatSolver(0)
 s.set_flat(fp)
-st = s.solve(max_iters=1, pcg_max_iters=pcg, pcg_check_every=100)
+st = s.solve(max_iters=1, pcg_max_iters=pcg, pcg_check_every=100, pcg_tol=1e-30)
 print(shape, fp.n_cams, fp.n_pts, fp.n_obs, st["iterations"], st["pcg_iterations"], st["launches"], st["solve_ms"])
