@@ -155,6 +155,25 @@ __global__ void k_point_keys(int n_pts, const unsigned long long* __restrict__ s
     key[p] = n ? (unsigned)((sum[p] * 8ull) / n) : 0xffffffffu;  // unobserved points last
     iota[p] = p;
 }
+// track length of every point in the (first) locality order, plus a trailing zero for the scan
+__global__ void k_gather_counts(int n_pts, const int* __restrict__ perm, const unsigned* __restrict__ cnt, int* __restrict__ out) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q > n_pts) return;
+    out[q] = q < n_pts ? (int)cnt[perm[q]] : 0;
+}
+// second-level key: (tile of the point, longest track first): inside a tile the points are ordered by
+// track length so that the lanes of a warp that sum tracks side by side run equally long loops
+__global__ void k_point_tile_keys(int n_pts, int n_tiles, const int* __restrict__ tile_pt, const int* __restrict__ len,
+                                  unsigned* __restrict__ key) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n_pts) return;
+    int lo = 0, hi = n_tiles;  // last tile with tile_pt[t] <= q
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (tile_pt[mid] <= q) lo = mid; else hi = mid;
+    }
+    key[q] = ((unsigned)lo << 10) | (unsigned)(1023 - min(len[q], 1023));
+}
 __global__ void k_invert_perm(int n, const int* __restrict__ perm, int* __restrict__ inv) {
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q < n) inv[perm[q]] = q;
@@ -339,6 +358,7 @@ struct ba_handle {
     // fused point tiles
     bool fused_ok = false;
     int ft_tiles = 0, n_seg = 0, ft_grid = 0, sm_count = 0;
+    std::vector<int> ft_pt_h, ft_obs_h;  // host copy of the tile cuts (empty: no tiles for this problem)
     DBuf<int> ft_pt, ft_obs, ft_seg, seg_cam, seg_start, seg_row, cam_row_off;
     DBuf<double2> tc_uv, tc_J;
     DBuf<int2> tc_meta;
@@ -464,19 +484,8 @@ static void build_tiles(ba_handle* h, int n_cams, int n_pts, int n_obs) {
     const int B = 256;
     h->fused_ok = false;
     h->ft_tiles = 0; h->n_seg = 0;
-    if (h->max_track > FT_THREADS) return;  // a track does not fit one tile: the two-pass kernels serve this problem
-
-    std::vector<int> off((size_t)n_pts + 1);
-    CK(cudaMemcpyAsync(off.data(), h->pt_off.p, off.size() * sizeof(int), cudaMemcpyDeviceToHost, s));
-    CK(cudaStreamSynchronize(s));
-    std::vector<int> tp{0}, to{0};
-    for (int p = 0; p < n_pts;) {
-        const int o_begin = off[p];
-        int q = p + 1;  // every track fits, so a tile always takes at least one point
-        while (q < n_pts && off[q + 1] - o_begin <= FT_THREADS && q - p < FT_PTS) ++q;
-        tp.push_back(q); to.push_back(off[q]);
-        p = q;
-    }
+    if (h->ft_pt_h.empty()) return;  // a track does not fit one tile: the two-pass kernels serve this problem
+    const std::vector<int>&tp = h->ft_pt_h, &to = h->ft_obs_h;
     const int T = (int)tp.size() - 1;
     h->ft_pt.alloc(tp.size()); h->ft_obs.alloc(to.size()); h->ft_seg.alloc(tp.size());
     CK(cudaMemcpyAsync(h->ft_pt.p, tp.data(), tp.size() * sizeof(int), cudaMemcpyHostToDevice, s));
@@ -616,6 +625,47 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
         tmp_bytes = d_tmp.n;
         CK(cub::DeviceRadixSort::SortPairs(d_tmp.p, tmp_bytes, d_key.p, d_key_s.p, d_pi.p, h->pt_perm.p, n_pts, 0, 32, s));
         h->launches[KN_SETUP] += 1;
+        // tile cuts: greedy on the host over the track offsets of this order (<= FT_THREADS observations and
+        // <= FT_PTS points per tile); then the points of each tile are re-ordered by track length
+        {
+            DBuf<int> d_len, d_off;
+            d_len.alloc((size_t)n_pts + 1); d_off.alloc((size_t)n_pts + 1);
+            launch(h, KN_SETUP, k_gather_counts, cdiv(n_pts + 1, B), B, 0, n_pts, (const int*)h->pt_perm.p, (const unsigned*)d_cnt.p, d_len.p);
+            size_t tbs = 0;
+            CK(cub::DeviceScan::ExclusiveSum(nullptr, tbs, d_len.p, d_off.p, n_pts + 1, s));
+            if (tbs > d_tmp.n) { CK(cudaStreamSynchronize(s)); d_tmp.alloc(tbs); }
+            tbs = d_tmp.n;
+            CK(cub::DeviceScan::ExclusiveSum(d_tmp.p, tbs, d_len.p, d_off.p, n_pts + 1, s));
+            std::vector<int> off((size_t)n_pts + 1);
+            CK(cudaMemcpyAsync(off.data(), d_off.p, off.size() * sizeof(int), cudaMemcpyDeviceToHost, s));
+            CK(cudaStreamSynchronize(s));
+            h->ft_pt_h.assign(1, 0); h->ft_obs_h.assign(1, 0);
+            bool fits = true;
+            for (int p = 0; p < n_pts && fits;) {
+                const int o_begin = off[p];
+                if (off[p + 1] - o_begin > FT_THREADS) { fits = false; break; }
+                int q = p + 1;
+                while (q < n_pts && off[q + 1] - o_begin <= FT_THREADS && q - p < FT_PTS) ++q;
+                h->ft_pt_h.push_back(q); h->ft_obs_h.push_back(off[q]);
+                p = q;
+            }
+            if (!fits) { h->ft_pt_h.clear(); h->ft_obs_h.clear(); }
+            if (fits) {
+                const int T = (int)h->ft_pt_h.size() - 1;
+                DBuf<int> d_tp, d_perm2;
+                d_tp.alloc(h->ft_pt_h.size()); d_perm2.alloc(n_pts);
+                CK(cudaMemcpyAsync(d_tp.p, h->ft_pt_h.data(), h->ft_pt_h.size() * sizeof(int), cudaMemcpyHostToDevice, s));
+                launch(h, KN_SETUP, k_point_tile_keys, cdiv(n_pts, B), B, 0, n_pts, T, (const int*)d_tp.p, (const int*)d_len.p, d_key.p);
+                int bits = 11;
+                while ((1LL << (bits - 10)) < T) ++bits;
+                tmp_bytes = d_tmp.n;
+                CK(cub::DeviceRadixSort::SortPairs(d_tmp.p, tmp_bytes, d_key.p, d_key_s.p, h->pt_perm.p, d_perm2.p, n_pts, 0,
+                                                   std::min(bits, 32), s));
+                CK(cudaMemcpyAsync(h->pt_perm.p, d_perm2.p, (size_t)n_pts * sizeof(int), cudaMemcpyDeviceToDevice, s));
+                CK(cudaStreamSynchronize(s));
+                h->launches[KN_SETUP] += 2;
+            }
+        }
         launch(h, KN_SETUP, k_invert_perm, cdiv(n_pts, B), B, 0, n_pts, (const int*)h->pt_perm.p, d_pi.p);
         // d_pi = caller's index -> internal id
         launch(h, KN_SETUP, k_setup_keys, cdiv(n_obs, B), B, 0, n_obs, n_cams, n_pts, (const int*)d_cam.p, (const int*)d_pt.p,

@@ -105,7 +105,7 @@ BA_D TileHdr tile_hdr(const Params& P, int t) {
 // so the pass needs no camera pose, no measurement, no division: per observation 56 bytes from HBM, the
 // camera's 6-vector from L1 (broadcast inside a camera run) and the point from shared memory.
 //
-// Persistent CTAs (grid = 2 per SM) walk the tiles round-robin.  All HBM traffic of a tile is moved by
+// Persistent CTAs (grid = 2 per SM) each walk a contiguous run of tiles.  All HBM traffic of a tile is moved by
 // the TMA (cp.async.bulk) while the PREVIOUS tile is being computed: group 1 (observation records,
 // Jacobian cache, points, segment table) is re-armed right after phase A has pulled its operands into
 // registers, group 2 (Vinv, track offsets) right after phase B; each group completes on its own mbarrier.
@@ -150,8 +150,10 @@ __global__ void __launch_bounds__(FT_THREADS, 2) k_tile_pass(Params P, const dou
     __shared__ double red[FT_THREADS / 32 * 4];
     __shared__ double tot[4];
     if (MODE == 0 && P.st->pcg_done) return;
-    int t = blockIdx.x;
-    if (t >= P.ft_tiles) return;
+    // contiguous run of tiles per CTA: neighbouring tiles share cameras, so the camera vectors stay in L1
+    int t = (int)((long long)blockIdx.x * P.ft_tiles / gridDim.x);
+    const int t_end = (int)((long long)(blockIdx.x + 1) * P.ft_tiles / gridDim.x);
+    if (t >= t_end) return;
     const FtSmem S = ft_carve(sm, FT_ROWS_MV);
     const int b = P.st->cur;
     const int tid = threadIdx.x;
@@ -168,8 +170,8 @@ __global__ void __launch_bounds__(FT_THREADS, 2) k_tile_pass(Params P, const dou
 
     for (unsigned it = 0;; ++it) {
         const int buf = it & 1;
-        const int tn = t + gridDim.x;
-        const bool have_next = tn < P.ft_tiles;
+        const int tn = t + 1;
+        const bool have_next = tn < t_end;
         TileHdr Tn = T;
         if (have_next && tid == 0) Tn = tile_hdr(P, tn);
         const bool act = tid < T.n;
@@ -217,12 +219,12 @@ __global__ void __launch_bounds__(FT_THREADS, 2) k_tile_pass(Params P, const dou
                 if (valid && k < 3) {
                     const int a = off[q] - T.o0, e = off[q + 1] - T.o0;
                     const double* src = S.sO + k * FT_LD;
-                    for (int i0 = a; i0 < e; i0 += 8) {  // loads first, then the (ordered) adds; x + 0.0 is exact
-                        double v[8];
+                    for (int i0 = a; i0 < e; i0 += 4) {  // loads first, then the (ordered) adds; x + 0.0 is exact
+                        double v[4];
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) v[j] = (i0 + j < e) ? src[i0 + j] : 0.0;
+                        for (int j = 0; j < 4; ++j) v[j] = (i0 + j < e) ? src[i0 + j] : 0.0;
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) sk += v[j];
+                        for (int j = 0; j < 4; ++j) sk += v[j];
                     }
                 }
                 const double s0 = __shfl_sync(0xffffffffu, sk, (lane & ~3));
