@@ -85,7 +85,11 @@ struct Params {
     // parameters: [2][(n_cams+1)*6] (rvec,t), [2][(n_cams+1)*12] (R,t), [2][n_pts*4] points (32-byte slots)
     double* cam_rt;
     double* cam_R;
-    double* pt_X;     // [2][n_pts*4]  point positions, one 32-byte sector each
+    double* pt_X;     // [2][pt_stride] point positions per parameter buffer: plane (X0, X1) [n_pad] double2, then
+                      //                plane X2 [n_pad] (two planes: conflict-free 16-byte / 8-byte gathers once a
+                      //                tile's points sit in shared memory)
+    int n_pad;        // n_pts rounded up to even
+    long long pt_stride;  // doubles per parameter buffer = 3 * n_pad
     double* pt_z;     // [n_pts*4]     V^-1 E^T u of the two-pass Schur mat-vec
     double* pt_h;     // [n_pts*4]     V^-1 g_p
     // per-point normal-equation data
@@ -143,8 +147,18 @@ struct Params {
     LMState* st;
 };
 
-// position slot of point p in parameter buffer b
-BA_D double* pt_x(const Params& P, int b, int p) { return P.pt_X + ((size_t)b * P.n_pts + (size_t)p) * 4; }
+// position of point p in parameter buffer b
+BA_D const double* pt_base(const Params& P, int b) { return P.pt_X + (size_t)b * P.pt_stride; }
+BA_D void load_pt(const Params& P, int b, int p, double X[3]) {
+    const double* base = pt_base(P, b);
+    const double2 a = __ldg(reinterpret_cast<const double2*>(base) + p);
+    X[0] = a.x; X[1] = a.y; X[2] = __ldg(base + 2 * (size_t)P.n_pad + p);
+}
+BA_D void store_pt(const Params& P, int b, int p, double x0, double x1, double x2) {
+    double* base = P.pt_X + (size_t)b * P.pt_stride;
+    reinterpret_cast<double2*>(base)[p] = make_double2(x0, x1);
+    base[2 * (size_t)P.n_pad + p] = x2;
+}
 
 // ---------------------------------------------------------------------------------------------
 // reductions (fixed trees -> deterministic)
@@ -286,7 +300,7 @@ __global__ void k_residuals(Params P, double2* __restrict__ r_out) {
     const int2 id = __ldg(P.o_idx + i);
     double Rt[12], X[3];
     load_cam(P.cam_R + (size_t)b * (P.n_cams + 1) * 12, id.x, Rt);
-    load_v3(pt_x(P, b, id.y), X);
+    load_pt(P, b, id.y, X);
     double rx, ry;
     project_residual(Rt, X, uv.x, uv.y, P.K, rx, ry);
     r_out[i] = make_double2(rx, ry);
@@ -302,7 +316,7 @@ __global__ void k_jacobian_blocks(Params P, double* __restrict__ jc_out, double*
     const int2 id = __ldg(P.o_idx + i);
     double Rt[12], X[3];
     load_cam(P.cam_R + (size_t)b * (P.n_cams + 1) * 12, id.x, Rt);
-    load_v3(pt_x(P, b, id.y), X);
+    load_pt(P, b, id.y, X);
     ObsLin o;
     linearize_obs(Rt, X, uv.x, uv.y, P.K, o);
     double* jp = jp_out + (size_t)i * 6;
@@ -368,7 +382,7 @@ __global__ void __launch_bounds__(PM_THREADS) k_lin_points(Params P, int which) 
         if (!act) continue;
         double X[3], Rt[12];
         load_cam(camR, id.x, Rt);
-        load_v3(pt_x(P, b, id.y), X);
+        load_pt(P, b, id.y, X);
         ObsLin o;
         linearize_obs(Rt, X, uv.x, uv.y, P.K, o);
         double wHx, wgx, r0x, wHy, wgy, r0y;
@@ -475,7 +489,7 @@ __global__ void __launch_bounds__(PM_THREADS) k_point_pass(Params P, const doubl
         double X[3], rec[18];
         load_cam(camR, id.x, rec);
         load_vec6(vec, id.x, rec + 12);
-        load_v3(pt_x(P, b, id.y), X);
+        load_pt(P, b, id.y, X);
         const double* x = rec + 12;
         ObsLin o;
         linearize_obs(rec, X, uv.x, uv.y, P.K, o);
@@ -509,11 +523,11 @@ __global__ void __launch_bounds__(PM_THREADS) k_point_pass(Params P, const doubl
         } else {
             double h[3], X[3], g[3], D[3];
             load_v3(P.pt_h + (size_t)p * 4, h);
-            load_v3(pt_x(P, b, p), X);
+            load_pt(P, b, p, X);
             load_v3(P.pt_g + (size_t)b * P.n_pts * 4 + (size_t)p * 4, g);
             load_v3(P.pt_D + (size_t)p * 4, D);
             const double dp0 = -h[0] - z[0], dp1 = -h[1] - z[1], dp2 = -h[2] - z[2];
-            store_v3(pt_x(P, b ^ 1, p), X[0] + dp0, X[1] + dp1, X[2] + dp2);
+            store_pt(P, b ^ 1, p, X[0] + dp0, X[1] + dp1, X[2] + dp2);
             acc[0] += g[0] * dp0 + g[1] * dp1 + g[2] * dp2;
             acc[1] += D[0] * dp0 * dp0 + D[1] * dp1 * dp1 + D[2] * dp2 * dp2;
             acc[2] += dp0 * dp0 + dp1 * dp1 + dp2 * dp2;
@@ -565,7 +579,7 @@ __global__ void __launch_bounds__(CM_THREADS) k_camera_pass(Params P, const doub
         const int p = __ldg(P.cm_pt + o0 + i);
         double rec[2 * NCH];
         {
-            load_v3(pt_x(P, b, p), rec);
+            load_pt(P, b, p, rec);
             if constexpr (KIND == 2) load_v3(P.pt_z + (size_t)p * 4, rec + 4);
             if constexpr (KIND == 1) {
                 load_v3(P.pt_h + (size_t)p * 4, rec + 4);

@@ -260,23 +260,22 @@ __global__ void k_max_track(int n_pts, const int* __restrict__ pt_off, int* __re
     atomicMax(out, pt_off[p + 1] - pt_off[p]);
 }
 // compact [n*3] <-> slot `buf` (4 doubles) of the 128-byte point records
-// `perm[q]` = caller's index of internal point q; `X4` = one parameter buffer of 4-double slots
-__global__ void k_pack_points(int n, const int* __restrict__ perm, const double* __restrict__ in3, double* __restrict__ X4) {
+// `perm[q]` = caller's index of internal point q; `base` = one parameter buffer (planes (X0,X1) and X2)
+__global__ void k_pack_points(int n, int n_pad, const int* __restrict__ perm, const double* __restrict__ in3, double* __restrict__ base) {
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= n) return;
     const size_t p = (size_t)perm[q];
-    double2* o = reinterpret_cast<double2*>(X4 + (size_t)q * 4);
-    o[0] = make_double2(in3[3 * p], in3[3 * p + 1]);
-    o[1] = make_double2(in3[3 * p + 2], 0.0);
+    reinterpret_cast<double2*>(base)[q] = make_double2(in3[3 * p], in3[3 * p + 1]);
+    base[2 * (size_t)n_pad + q] = in3[3 * p + 2];
 }
-__global__ void k_unpack_points(int n, const int* __restrict__ perm, const double* __restrict__ X4, double* __restrict__ out3) {
+__global__ void k_unpack_points(int n, int n_pad, const int* __restrict__ perm, const double* __restrict__ base, double* __restrict__ out3) {
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= n) return;
     const size_t p = (size_t)perm[q];
-    const double* in4 = X4 + (size_t)q * 4;
-    out3[3 * p] = in4[0];
-    out3[3 * p + 1] = in4[1];
-    out3[3 * p + 2] = in4[2];
+    const double2 a = reinterpret_cast<const double2*>(base)[q];
+    out3[3 * p] = a.x;
+    out3[3 * p + 1] = a.y;
+    out3[3 * p + 2] = base[2 * (size_t)n_pad + q];
 }
 __global__ void k_pack_cams(int n_cams, const double* __restrict__ rvec, const double* __restrict__ tvec,
                             double fr0, double fr1, double fr2, double ft0, double ft1, double ft2, double* __restrict__ rt) {
@@ -562,7 +561,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     const size_t nc1 = (size_t)n_cams + 1;
 
     h->cam_rt.alloc(2 * nc1 * 6); h->cam_R.alloc(2 * nc1 * 12);
-    h->pt_X.alloc(2 * (size_t)n_pts * 4); h->pt_z.alloc((size_t)n_pts * 4); h->pt_h.alloc((size_t)n_pts * 4);
+    h->pt_X.alloc(2 * 3 * (size_t)((n_pts + 1) & ~1) + 4); h->pt_z.alloc((size_t)n_pts * 4); h->pt_h.alloc((size_t)n_pts * 4);
     h->pt_V.alloc(2 * (size_t)n_pts * 6); h->pt_g.alloc(2 * (size_t)n_pts * 4);
     h->pt_Vinv.alloc((size_t)n_pts * 6);
     h->pt_D.alloc((size_t)n_pts * 4);
@@ -597,6 +596,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     P.K = Intr{fx, fy, cx, cy};
     P.delta = 1.0; P.mode = ROBUST_IRLS;
     P.n_cams = n_cams; P.n_pts = n_pts; P.n_obs = n_obs;
+    P.n_pad = (n_pts + 1) & ~1; P.pt_stride = 3LL * P.n_pad;
 
     const int B = 256;
     int pt_bits = 1;
@@ -767,7 +767,7 @@ static void set_params(ba_handle* h, const double* rvec, const double* tvec, con
     CK(cudaMemsetAsync(&h->st.p->cur, 0, sizeof(int), s));
     if (pts) {
         CK(cudaMemcpyAsync(h->io.p, pts, (size_t)P.n_pts * 3 * sizeof(double), cudaMemcpyHostToDevice, s));
-        launch(h, KN_SETUP, k_pack_points, cdiv(P.n_pts, B), B, 0, P.n_pts, (const int*)h->pt_perm.p, (const double*)h->io.p,
+        launch(h, KN_SETUP, k_pack_points, cdiv(P.n_pts, B), B, 0, P.n_pts, P.n_pad, (const int*)h->pt_perm.p, (const double*)h->io.p,
                h->pt_X.p);
         if (save_initial)
             CK(cudaMemcpyAsync(h->init_pts.p, h->io.p, (size_t)P.n_pts * 3 * sizeof(double), cudaMemcpyDeviceToDevice, s));
@@ -1066,8 +1066,8 @@ int ba_get_params(ba_handle* h, double* rvec, double* tvec, double* pts) {
     ba::read_state(h);
     const int b = h->h_state->cur;
     if (pts) {
-        ba::launch(h, ba::KN_SETUP, ba::k_unpack_points, ba::cdiv(P.n_pts, 256), 256, 0, P.n_pts, (const int*)h->pt_perm.p,
-                   (const double*)(h->pt_X.p + (size_t)b * P.n_pts * 4), h->io.p);
+        ba::launch(h, ba::KN_SETUP, ba::k_unpack_points, ba::cdiv(P.n_pts, 256), 256, 0, P.n_pts, P.n_pad, (const int*)h->pt_perm.p,
+                   (const double*)(h->pt_X.p + (size_t)b * P.pt_stride), h->io.p);
         CK(cudaMemcpyAsync(pts, h->io.p, (size_t)P.n_pts * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
         CK(cudaStreamSynchronize(s));
     }
@@ -1091,7 +1091,7 @@ int ba_restore_initial(ba_handle* h) {
     const size_t nc1 = (size_t)P.n_cams + 1;
     CK(cudaMemsetAsync(&h->st.p->cur, 0, sizeof(int), s));
     CK(cudaMemcpyAsync(h->cam_rt.p, h->init_cam_rt.p, nc1 * 6 * sizeof(double), cudaMemcpyDeviceToDevice, s));
-    ba::launch(h, ba::KN_SETUP, ba::k_pack_points, ba::cdiv(P.n_pts, 256), 256, 0, P.n_pts, (const int*)h->pt_perm.p,
+    ba::launch(h, ba::KN_SETUP, ba::k_pack_points, ba::cdiv(P.n_pts, 256), 256, 0, P.n_pts, P.n_pad, (const int*)h->pt_perm.p,
                (const double*)h->init_pts.p, h->pt_X.p);
     ba::launch(h, ba::KN_CAM_PREP, ba::k_cam_prepare, ba::cdiv((int)nc1, 256), 256, 0, P, 0);
     API_END

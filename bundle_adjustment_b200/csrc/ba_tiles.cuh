@@ -35,26 +35,29 @@ constexpr int FT_LD = FT_THREADS + 2;  // row stride of the per-observation scra
 constexpr int FT_ROWS_MV = 6;          // scratch rows of the mat-vec pass
 
 // dynamic shared memory of a tile pass (16-byte aligned regions): per-observation scratch rows | Jacobian
-// cache planes [3][FT_THREADS] double2 | observation records | X [FT_PTS][4] | z [FT_PTS][4] | Vinv [FT_PTS][6] |
+// cache planes [3][FT_THREADS] double2 | observation records | X as planes (X0,X1)[FT_PTS], X2[FT_PTS+2] | z likewise | Vinv [FT_PTS][6] |
 // track offsets | segment starts x2 | segment rows x2 | two mbarriers.  The x2 regions are double-buffered
 // by tile parity; everything else is refilled by the TMA as soon as its last reader has passed a barrier.
 constexpr int FT_META_N = FT_THREADS + 2, FT_OFF_N = FT_PTS + 8, FT_SEG_N = FT_THREADS + 8;
 struct FtSmem {
-    double* sO; double2* sJ; int2* sMeta; double* sX; double* sZ; double* sVi; int* sOff; int* sSeg; int* sRow;
+    double* sO; double2* sJ; int2* sMeta; double2* sX01; double* sX2; double2* sZ01; double* sZ2; double* sVi;
+    int* sOff; int* sSeg; int* sRow;
     unsigned long long* bar;
 };
 __host__ __device__ constexpr size_t ft_smem_bytes(int rows) {
-    return (size_t)(rows * FT_LD) * 8 + 3 * FT_THREADS * 16 + FT_META_N * 8 + (size_t)FT_PTS * (4 + 4 + 6) * 8 +
-           (size_t)(FT_OFF_N + 4 * FT_SEG_N) * 4 + 16;
+    return (size_t)(rows * FT_LD) * 8 + 3 * FT_THREADS * 16 + FT_META_N * 8 + (size_t)FT_PTS * (2 + 2 + 6) * 8 +
+           2 * (size_t)(FT_PTS + 2) * 8 + (size_t)(FT_OFF_N + 4 * FT_SEG_N) * 4 + 16;
 }
 BA_D FtSmem ft_carve(double* sm, int rows) {
     FtSmem S;
     S.sO = sm;
     S.sJ = reinterpret_cast<double2*>(S.sO + rows * FT_LD);
     S.sMeta = reinterpret_cast<int2*>(S.sJ + 3 * FT_THREADS);
-    S.sX = reinterpret_cast<double*>(S.sMeta + FT_META_N);
-    S.sZ = S.sX + FT_PTS * 4;
-    S.sVi = S.sZ + FT_PTS * 4;
+    S.sX01 = reinterpret_cast<double2*>(S.sMeta + FT_META_N);
+    S.sX2 = reinterpret_cast<double*>(S.sX01 + FT_PTS);
+    S.sZ01 = reinterpret_cast<double2*>(S.sX2 + FT_PTS + 2);
+    S.sZ2 = reinterpret_cast<double*>(S.sZ01 + FT_PTS);
+    S.sVi = S.sZ2 + FT_PTS + 2;
     S.sOff = reinterpret_cast<int*>(S.sVi + FT_PTS * 6);
     S.sSeg = S.sOff + FT_OFF_N;
     S.sRow = S.sSeg + 2 * FT_SEG_N;
@@ -117,9 +120,11 @@ template <int MODE>
 BA_D void ft_issue_group1(const Params& P, const FtSmem& S, const TileHdr& T, int b, int buf, unsigned long long* bar) {
     const int meta_lo = T.o0 & ~1, seg_lo = T.s0 & ~3;
     const unsigned meta_b = (unsigned)(((T.o0 + T.n - meta_lo) * 8 + 15) & ~15);
-    const unsigned j_b = (unsigned)T.n * 16u, x_b = (unsigned)T.m * 32u;
+    const unsigned j_b = (unsigned)T.n * 16u, x01_b = (unsigned)T.m * 16u;
+    const int x2_lo = T.p0 & ~1;
+    const unsigned x2_b = (unsigned)(((T.p0 + T.m - x2_lo) * 8 + 15) & ~15);
     const unsigned seg_b = (unsigned)(((T.s0 + T.ns + 1 - seg_lo) * 4 + 15) & ~15);
-    unsigned total = x_b;
+    unsigned total = x01_b + x2_b;
     if (T.n > 0) total += meta_b + 3 * j_b;
     if (MODE == 0) total += 2 * seg_b;
     mbar_expect_tx(bar, total);
@@ -129,7 +134,8 @@ BA_D void ft_issue_group1(const Params& P, const FtSmem& S, const TileHdr& T, in
 #pragma unroll
         for (int r = 0; r < 3; ++r) tma_load(S.sJ + r * FT_THREADS, J + (size_t)r * P.n_obs, j_b, bar);
     }
-    tma_load(S.sX, pt_x(P, b, T.p0), x_b, bar);
+    tma_load(S.sX01, reinterpret_cast<const double2*>(pt_base(P, b)) + T.p0, x01_b, bar);
+    tma_load(S.sX2, pt_base(P, b) + 2 * (size_t)P.n_pad + x2_lo, x2_b, bar);
     if (MODE == 0) {
         tma_load(S.sSeg + buf * FT_SEG_N, P.seg_start + seg_lo, seg_b, bar);
         tma_load(S.sRow + buf * FT_SEG_N, P.seg_row + seg_lo, seg_b, bar);
@@ -191,8 +197,8 @@ __global__ void __launch_bounds__(FT_THREADS, 2) k_tile_pass(Params P, const dou
         const int pl = meta.y & 1023;
         if (act) {
             const int pos = (meta.y >> 10) & 1023;
-            const double2 x01 = *reinterpret_cast<const double2*>(S.sX + 4 * pl);
-            X[0] = x01.x; X[1] = x01.y; X[2] = S.sX[4 * pl + 2];
+            const double2 x01 = S.sX01[pl];
+            X[0] = x01.x; X[1] = x01.y; X[2] = S.sX2[(T.p0 & 1) + pl];
             const double d0 = fma(x[1], X[2], fma(-x[2], X[1], x[3]));  // d = w x X + v
             const double d1 = fma(x[2], X[0], fma(-x[0], X[2], x[4]));
             const double d2 = fma(x[0], X[1], fma(-x[1], X[0], x[5]));
@@ -237,13 +243,15 @@ __global__ void __launch_bounds__(FT_THREADS, 2) k_tile_pass(Params P, const dou
                     zk = v0 * s0 + v1 * s1 + v2 * s2;
                 }
                 if (MODE == 0) {
-                    if (valid && k < 3) S.sZ[4 * q + k] = zk;
-                } else if (valid) {
-                    const size_t p4 = (size_t)(T.p0 + q) * 4 + k;
-                    const double Xk = S.sX[4 * q + k];
-                    const double dp = -__ldg(P.pt_h + p4) - zk;  // the pad lane carries zeros throughout
+                    if (valid && k < 2) reinterpret_cast<double*>(S.sZ01)[2 * q + k] = zk;
+                    if (valid && k == 2) S.sZ2[q] = zk;
+                } else if (valid && k < 3) {
+                    const size_t p = (size_t)(T.p0 + q), p4 = p * 4 + k;
+                    const double Xk = k < 2 ? reinterpret_cast<const double*>(S.sX01)[2 * q + k] : S.sX2[(T.p0 & 1) + q];
+                    const double dp = -__ldg(P.pt_h + p4) - zk;
                     const double gk = __ldg(P.pt_g + (size_t)b * P.n_pts * 4 + p4), Dk = __ldg(P.pt_D + p4);
-                    P.pt_X[(size_t)(b ^ 1) * P.n_pts * 4 + p4] = Xk + dp;
+                    double* out = P.pt_X + (size_t)(b ^ 1) * P.pt_stride;
+                    out[k < 2 ? 2 * p + k : 2 * (size_t)P.n_pad + p] = Xk + dp;
                     acc[0] += gk * dp; acc[1] += Dk * dp * dp; acc[2] += dp * dp; acc[3] += Xk * Xk;
                 }
             }
@@ -265,8 +273,8 @@ __global__ void __launch_bounds__(FT_THREADS, 2) k_tile_pass(Params P, const dou
 
             // ---- phase C: camera-side product of every observation, parked at its tile-camera position --
             if (act) {
-                const double2 z01 = *reinterpret_cast<const double2*>(S.sZ + 4 * pl);
-                const double z2 = S.sZ[4 * pl + 2];
+                const double2 z01 = S.sZ01[pl];
+                const double z2 = S.sZ2[pl];
                 const double bx = ax - (j0.x * z01.x + j0.y * z01.y + j1.x * z2);
                 const double by = ay - (j1.y * z01.x + j2.x * z01.y + j2.y * z2);
                 const double mm[3] = {j0.x * bx + j1.y * by, j0.y * bx + j2.x * by, j1.x * bx + j2.y * by};
