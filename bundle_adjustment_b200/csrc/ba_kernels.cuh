@@ -129,14 +129,15 @@ struct Params {
     const int* ft_pt;         // [ft_tiles+1] first point of a tile
     const int* ft_obs;        // [ft_tiles+1] first observation of a tile (same range in both tile orders)
     const int* ft_seg;        // [ft_tiles+1] first segment of a tile
-    const int4* ft_hdr;       // [2*ft_tiles] (p0, points, o0, observations), (s0, segments, -, -)
+    const int4* ft_hdr;       // [2*ft_tiles] (p0, points, o0, observations), (s0, segments, first track row, longest track)
+    const int* ft_rs;         // per tile: start of track row i in the transposed point-side scratch layout
     const double2* tc_uv;     // [n_obs] tile-camera order
-    const int2* tc_meta;      // [n_obs] (camera slot, local point | point-major position << 10)
+    const int2* tc_meta;      // [n_obs] (camera slot, local point | point-side scratch slot << 10)
     const int* pm_tc;         // [n_obs] point-major index -> tile-camera index
     double2* tc_J;            // [2][3][n_obs] Jacobian cache W^1/2 Jp of the linearisation at parameter buffer b:
                               // planes (jx0, jx1), (jx2, jy0), (jy1, jy2), tile-camera order
     const int* seg_cam;       // [n_seg]
-    const int* seg_start;     // [n_seg+1] first tile-camera index of a segment
+    const int* seg_info;      // [n_seg] first tile-camera position inside the tile | length << 16 (longest first per tile)
     const int* seg_row;       // [n_seg] row slot of a segment (camera-major)
     const int* cam_row_off;   // [n_cams+2]
     double* rows;             // [n_seg*6]

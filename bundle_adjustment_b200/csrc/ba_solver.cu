@@ -357,8 +357,8 @@ struct ba_handle {
     // fused point tiles
     bool fused_ok = false;
     int ft_tiles = 0, n_seg = 0, ft_grid = 0, sm_count = 0;
-    std::vector<int> ft_pt_h, ft_obs_h;  // host copy of the tile cuts (empty: no tiles for this problem)
-    DBuf<int> ft_pt, ft_obs, ft_seg, seg_cam, seg_start, seg_row, cam_row_off;
+    std::vector<int> ft_pt_h, ft_obs_h, ft_maxlen_h;  // host copy of the tile cuts and longest tracks (empty: no tiles)
+    DBuf<int> ft_pt, ft_obs, ft_seg, ft_rs, seg_cam, seg_info, seg_row, cam_row_off;
     DBuf<double2> tc_uv, tc_J;
     DBuf<int2> tc_meta;
     DBuf<int4> ft_hdr;
@@ -518,27 +518,44 @@ static void build_tiles(ba_handle* h, int n_cams, int n_pts, int n_obs) {
 
     h->tc_uv.alloc(n_obs); h->tc_meta.alloc((size_t)n_obs + 2); h->pm_tc.alloc(n_obs); h->tc_J.alloc(6 * (size_t)n_obs);
     h->ft_hdr.alloc(2 * (size_t)T);
-    h->seg_cam.alloc(S); h->seg_start.alloc((size_t)S + 1 + 4); h->seg_row.alloc((size_t)S + 4);  // + TMA window slack
+    h->seg_cam.alloc(S); h->seg_info.alloc((size_t)S + 4); h->seg_row.alloc((size_t)S + 4);  // + TMA window slack
     h->cam_row_off.alloc((size_t)n_cams + 2);
     h->rows.alloc((size_t)S * 6);
+    // track-row tables of the transposed point-side layout: one per tile, padded to 16 bytes
+    std::vector<int> rs0((size_t)T + 1, 0);
+    for (int t = 0; t < T; ++t) rs0[t + 1] = rs0[t] + ((h->ft_maxlen_h[t] + 3) & ~3);
+    DBuf<int> d_rs0, d_maxlen, seg_start, seg_cam0;
+    d_rs0.alloc((size_t)T + 1); d_maxlen.alloc(T); seg_start.alloc((size_t)S + 1); seg_cam0.alloc(S);
+    h->ft_rs.alloc((size_t)rs0[T] + 4);
+    h->ft_rs.zero(s);
+    CK(cudaMemcpyAsync(d_rs0.p, rs0.data(), rs0.size() * sizeof(int), cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_maxlen.p, h->ft_maxlen_h.data(), (size_t)T * sizeof(int), cudaMemcpyHostToDevice, s));
+    launch(h, KN_SETUP, k_ft_rowstart, T, FT_THREADS, 0, (const int*)h->ft_pt.p, (const int*)h->pt_off.p, (const int*)d_rs0.p,
+           (const int*)d_maxlen.p, h->ft_rs.p);
+    launch(h, KN_SETUP, k_ft_tile_seg, cdiv(T + 1, B), B, 0, T, n_obs, S, (const int*)h->ft_obs.p, (const int*)ic.p, h->ft_seg.p,
+           seg_start.p);
+    launch(h, KN_SETUP, k_ft_fill, cdiv(n_obs, B), B, 0, n_obs, (const unsigned long long*)key_s.p, (const int*)ib.p,
+           (const int*)ia.p, (const int*)ic.p, (const int*)h->ft_pt.p, (const int*)h->pt_off.p, (const int*)d_rs0.p,
+           (const int*)h->ft_rs.p, (const double2*)h->pm_uv.p, (const int2*)h->pm_idx.p, h->tc_uv.p, h->tc_meta.p, h->pm_tc.p,
+           seg_cam0.p, seg_start.p);
+    launch(h, KN_SETUP, k_ft_headers, cdiv(T, B), B, 0, T, (const int*)h->ft_pt.p, (const int*)h->ft_obs.p, (const int*)h->ft_seg.p,
+           (const int*)d_rs0.p, (const int*)d_maxlen.p, h->ft_hdr.p);
+    // segments longest first inside each tile, then rows camera-major (stable sort of the segments by camera)
     DBuf<unsigned> skey, skey_s;
     DBuf<int> sidx, sidx_s;
     skey.alloc(S); skey_s.alloc(S); sidx.alloc(S); sidx_s.alloc(S);
-    launch(h, KN_SETUP, k_ft_tile_seg, cdiv(T + 1, B), B, 0, T, n_obs, S, (const int*)h->ft_obs.p, (const int*)ic.p, h->ft_seg.p,
-           h->seg_start.p);
-    launch(h, KN_SETUP, k_ft_fill, cdiv(n_obs, B), B, 0, n_obs, (const unsigned long long*)key_s.p, (const int*)ib.p,
-           (const int*)ia.p, (const int*)ic.p, (const int*)h->ft_obs.p, (const int*)h->ft_pt.p, (const int*)h->ft_seg.p,
-           (const double2*)h->pm_uv.p, (const int2*)h->pm_idx.p, h->tc_uv.p, h->tc_meta.p, h->pm_tc.p, h->seg_cam.p, h->seg_start.p, skey.p);
-    launch(h, KN_SETUP, k_ft_headers, cdiv(T, B), B, 0, T, (const int*)h->ft_pt.p, (const int*)h->ft_obs.p, (const int*)h->ft_seg.p, h->ft_hdr.p);
-    // rows camera-major: stable sort of the segments by camera
-    launch(h, KN_SETUP, k_iota, cdiv(S, B), B, 0, S, sidx.p);
     int cam_bits = 1;
     while ((1LL << cam_bits) < (long long)n_cams + 1) ++cam_bits;
-    CK(cub::DeviceRadixSort::SortPairs(nullptr, tb_seg, skey.p, skey_s.p, sidx.p, sidx_s.p, S, 0, cam_bits, s));
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, tb_seg, skey.p, skey_s.p, sidx.p, sidx_s.p, S, 0, 32, s));
     if (tb_seg > tmp.n) { CK(cudaStreamSynchronize(s)); tmp.alloc(tb_seg); }
+    launch(h, KN_SETUP, k_ft_seg_keys, cdiv(S, B), B, 0, S, T, (const int*)seg_start.p, (const int*)h->ft_obs.p, skey.p, sidx.p);
+    tb = tmp.n;
+    CK(cub::DeviceRadixSort::SortPairs(tmp.p, tb, skey.p, skey_s.p, sidx.p, sidx_s.p, S, 0, std::min(32, 5 + tile_bits), s));
+    launch(h, KN_SETUP, k_ft_seg_apply, cdiv(S, B), B, 0, S, (const unsigned*)skey_s.p, (const int*)sidx_s.p, (const int*)seg_start.p,
+           (const int*)seg_cam0.p, (const int*)h->ft_obs.p, h->seg_info.p, h->seg_cam.p, skey.p, sidx.p);
     tb = tmp.n;
     CK(cub::DeviceRadixSort::SortPairs(tmp.p, tb, skey.p, skey_s.p, sidx.p, sidx_s.p, S, 0, cam_bits, s));
-    h->launches[KN_SETUP] += 1;
+    h->launches[KN_SETUP] += 2;
     launch(h, KN_SETUP, k_ft_seg_rows, cdiv(S, B), B, 0, S, (const int*)sidx_s.p, h->seg_row.p);
     launch(h, KN_SETUP, k_lower_bound_u32, cdiv(n_cams + 2, B), B, 0, S, (const unsigned*)skey_s.p, n_cams + 2, h->cam_row_off.p);
     CK(cudaFuncSetAttribute(k_tile_pass<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ft_smem_bytes(FT_ROWS_MV)));
@@ -639,17 +656,20 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
             std::vector<int> off((size_t)n_pts + 1);
             CK(cudaMemcpyAsync(off.data(), d_off.p, off.size() * sizeof(int), cudaMemcpyDeviceToHost, s));
             CK(cudaStreamSynchronize(s));
-            h->ft_pt_h.assign(1, 0); h->ft_obs_h.assign(1, 0);
+            h->ft_pt_h.assign(1, 0); h->ft_obs_h.assign(1, 0); h->ft_maxlen_h.clear();
             bool fits = true;
             for (int p = 0; p < n_pts && fits;) {
                 const int o_begin = off[p];
                 if (off[p + 1] - o_begin > FT_THREADS) { fits = false; break; }
-                int q = p + 1;
-                while (q < n_pts && off[q + 1] - o_begin <= FT_THREADS && q - p < FT_PTS) ++q;
-                h->ft_pt_h.push_back(q); h->ft_obs_h.push_back(off[q]);
+                int q = p + 1, longest = off[p + 1] - o_begin;
+                while (q < n_pts && off[q + 1] - o_begin <= FT_THREADS && q - p < FT_PTS) {
+                    longest = std::max(longest, off[q + 1] - off[q]);
+                    ++q;
+                }
+                h->ft_pt_h.push_back(q); h->ft_obs_h.push_back(off[q]); h->ft_maxlen_h.push_back(longest);
                 p = q;
             }
-            if (!fits) { h->ft_pt_h.clear(); h->ft_obs_h.clear(); }
+            if (!fits) { h->ft_pt_h.clear(); h->ft_obs_h.clear(); h->ft_maxlen_h.clear(); }
             if (fits) {
                 const int T = (int)h->ft_pt_h.size() - 1;
                 DBuf<int> d_tp, d_perm2;
@@ -749,7 +769,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     P.ft_pt = h->ft_pt.p; P.ft_obs = h->ft_obs.p; P.ft_seg = h->ft_seg.p; P.tc_uv = h->tc_uv.p;
     P.ft_hdr = h->ft_hdr.p; P.tc_meta = h->tc_meta.p; P.pm_tc = h->fused_ok ? h->pm_tc.p : nullptr;
     P.tc_J = h->fused_ok ? h->tc_J.p : nullptr;
-    P.seg_cam = h->seg_cam.p; P.seg_start = h->seg_start.p; P.seg_row = h->seg_row.p; P.cam_row_off = h->cam_row_off.p;
+    P.seg_cam = h->seg_cam.p; P.seg_info = h->seg_info.p; P.ft_rs = h->ft_rs.p; P.seg_row = h->seg_row.p; P.cam_row_off = h->cam_row_off.p;
     P.rows = h->rows.p;
     h->st.zero(s);
     CK(cudaStreamSynchronize(s));  // the sort scratch buffers die at scope exit
@@ -1292,7 +1312,7 @@ int ba_layout_info(ba_handle* h, int64_t out[8]) {
 }
 
 int ba_tile_layout(ba_handle* h, int32_t* ft_pt, int32_t* ft_obs, int32_t* ft_seg, int32_t* tc_meta, double* tc_uv,
-                   int32_t* seg_cam, int32_t* seg_start, int32_t* seg_row, int32_t* cam_row_off, int32_t* pt_perm) {
+                   int32_t* seg_cam, int32_t* seg_info, int32_t* seg_row, int32_t* cam_row_off, int32_t* pt_perm) {
     API_BEGIN
     ba::need_problem(h);
     if (!h->fused_ok) ba::fail(BA_ERR_STATE, "no point tiles for this problem (a track is longer than a tile)");
@@ -1304,7 +1324,7 @@ int ba_tile_layout(ba_handle* h, int32_t* ft_pt, int32_t* ft_obs, int32_t* ft_se
     };
     get(ft_pt, h->ft_pt.p, (T + 1) * 4); get(ft_obs, h->ft_obs.p, (T + 1) * 4); get(ft_seg, h->ft_seg.p, (T + 1) * 4);
     get(tc_meta, h->tc_meta.p, (size_t)P.n_obs * 8); get(tc_uv, h->tc_uv.p, (size_t)P.n_obs * 16);
-    get(seg_cam, h->seg_cam.p, S * 4); get(seg_start, h->seg_start.p, (S + 1) * 4); get(seg_row, h->seg_row.p, S * 4);
+    get(seg_cam, h->seg_cam.p, S * 4); get(seg_info, h->seg_info.p, S * 4); get(seg_row, h->seg_row.p, S * 4);
     get(cam_row_off, h->cam_row_off.p, ((size_t)P.n_cams + 2) * 4); get(pt_perm, h->pt_perm.p, (size_t)P.n_pts * 4);
     CK(cudaStreamSynchronize(s));
     API_END

@@ -26,27 +26,32 @@
 #pragma once
 #include "ba_kernels.cuh"
 
+#include <cub/block/block_scan.cuh>
+
 namespace ba {
 
 constexpr int FT_THREADS = 512;        // threads per CTA = observation capacity of a tile
 constexpr int FT_PTS = 256;            // point capacity of a tile
 constexpr int FT_SEG_MAX = 16;         // observations per segment (one output row each)
-constexpr int FT_LD = FT_THREADS + 2;  // row stride of the per-observation scratch (doubles); 2*FT_LD mod 32 = 4 banks
+constexpr int FT_LD = FT_THREADS + 2;  // row stride of the camera-side scratch (phases C/D): 2*FT_LD mod 32 = 4 banks, so the
+                                       // six components of one segment fall on different banks
+constexpr int FT_LDB = FT_THREADS + 4; // row stride of the point-side scratch (phases A/B): 2*FT_LDB mod 32 = 8 banks, so the
+                                       // three rows read by the four points of a half-warp are disjoint
 constexpr int FT_ROWS_MV = 6;          // scratch rows of the mat-vec pass
 
 // dynamic shared memory of a tile pass (16-byte aligned regions): per-observation scratch rows | Jacobian
 // cache planes [3][FT_THREADS] double2 | observation records | X as planes (X0,X1)[FT_PTS], X2[FT_PTS+2] | z likewise | Vinv [FT_PTS][6] |
-// track offsets | segment starts x2 | segment rows x2 | two mbarriers.  The x2 regions are double-buffered
+// track offsets | track-row starts | segment table x2 | segment rows x2 | two mbarriers.  The x2 regions are double-buffered
 // by tile parity; everything else is refilled by the TMA as soon as its last reader has passed a barrier.
 constexpr int FT_META_N = FT_THREADS + 2, FT_OFF_N = FT_PTS + 8, FT_SEG_N = FT_THREADS + 8;
 struct FtSmem {
     double* sO; double2* sJ; int2* sMeta; double2* sX01; double* sX2; double2* sZ01; double* sZ2; double* sVi;
-    int* sOff; int* sSeg; int* sRow;
+    int* sOff; int* sRs; int* sSeg; int* sRow;
     unsigned long long* bar;
 };
 __host__ __device__ constexpr size_t ft_smem_bytes(int rows) {
     return (size_t)(rows * FT_LD) * 8 + 3 * FT_THREADS * 16 + FT_META_N * 8 + (size_t)FT_PTS * (2 + 2 + 6) * 8 +
-           2 * (size_t)(FT_PTS + 2) * 8 + (size_t)(FT_OFF_N + 4 * FT_SEG_N) * 4 + 16;
+           2 * (size_t)(FT_PTS + 2) * 8 + (size_t)(FT_OFF_N + 5 * FT_SEG_N) * 4 + 16;
 }
 BA_D FtSmem ft_carve(double* sm, int rows) {
     FtSmem S;
@@ -59,7 +64,8 @@ BA_D FtSmem ft_carve(double* sm, int rows) {
     S.sZ2 = reinterpret_cast<double*>(S.sZ01 + FT_PTS);
     S.sVi = S.sZ2 + FT_PTS + 2;
     S.sOff = reinterpret_cast<int*>(S.sVi + FT_PTS * 6);
-    S.sSeg = S.sOff + FT_OFF_N;
+    S.sRs = S.sOff + FT_OFF_N;
+    S.sSeg = S.sRs + FT_SEG_N;
     S.sRow = S.sSeg + 2 * FT_SEG_N;
     S.bar = reinterpret_cast<unsigned long long*>(S.sRow + 2 * FT_SEG_N);
     return S;
@@ -90,11 +96,11 @@ BA_D void tma_load(void* smem, const void* gmem, unsigned bytes, unsigned long l
                  : "memory");
 }
 
-struct TileHdr { int p0, m, o0, n, s0, ns; };
+struct TileHdr { int p0, m, o0, n, s0, ns, r0, maxlen; };
 BA_D TileHdr tile_hdr(const Params& P, int t) {
     const int4 a = __ldg(P.ft_hdr + 2 * t), b = __ldg(P.ft_hdr + 2 * t + 1);
     TileHdr T;
-    T.p0 = a.x; T.m = a.y; T.o0 = a.z; T.n = a.w; T.s0 = b.x; T.ns = b.y;
+    T.p0 = a.x; T.m = a.y; T.o0 = a.z; T.n = a.w; T.s0 = b.x; T.ns = b.y; T.r0 = b.z; T.maxlen = b.w;
     return T;
 }
 
@@ -123,10 +129,10 @@ BA_D void ft_issue_group1(const Params& P, const FtSmem& S, const TileHdr& T, in
     const unsigned j_b = (unsigned)T.n * 16u, x01_b = (unsigned)T.m * 16u;
     const int x2_lo = T.p0 & ~1;
     const unsigned x2_b = (unsigned)(((T.p0 + T.m - x2_lo) * 8 + 15) & ~15);
-    const unsigned seg_b = (unsigned)(((T.s0 + T.ns + 1 - seg_lo) * 4 + 15) & ~15);
+    const unsigned seg_b = (unsigned)(((T.s0 + T.ns - seg_lo) * 4 + 15) & ~15);
     unsigned total = x01_b + x2_b;
     if (T.n > 0) total += meta_b + 3 * j_b;
-    if (MODE == 0) total += 2 * seg_b;
+    if (MODE == 0 && seg_b) total += 2 * seg_b;
     mbar_expect_tx(bar, total);
     if (T.n > 0) {
         tma_load(S.sMeta, P.tc_meta + meta_lo, meta_b, bar);
@@ -136,8 +142,8 @@ BA_D void ft_issue_group1(const Params& P, const FtSmem& S, const TileHdr& T, in
     }
     tma_load(S.sX01, reinterpret_cast<const double2*>(pt_base(P, b)) + T.p0, x01_b, bar);
     tma_load(S.sX2, pt_base(P, b) + 2 * (size_t)P.n_pad + x2_lo, x2_b, bar);
-    if (MODE == 0) {
-        tma_load(S.sSeg + buf * FT_SEG_N, P.seg_start + seg_lo, seg_b, bar);
+    if (MODE == 0 && seg_b) {
+        tma_load(S.sSeg + buf * FT_SEG_N, P.seg_info + seg_lo, seg_b, bar);
         tma_load(S.sRow + buf * FT_SEG_N, P.seg_row + seg_lo, seg_b, bar);
     }
 }
@@ -145,9 +151,11 @@ BA_D void ft_issue_group2(const Params& P, const FtSmem& S, const TileHdr& T, un
     const int off_lo = T.p0 & ~3;
     const unsigned vi_b = (unsigned)T.m * 48u;
     const unsigned off_b = (unsigned)(((T.p0 + T.m + 1 - off_lo) * 4 + 15) & ~15);
-    mbar_expect_tx(bar, vi_b + off_b);
+    const unsigned rs_b = (unsigned)((T.maxlen * 4 + 15) & ~15);  // r0 is a multiple of 4
+    mbar_expect_tx(bar, vi_b + off_b + rs_b);
     tma_load(S.sVi, P.pt_Vinv + (size_t)T.p0 * 6, vi_b, bar);
     tma_load(S.sOff, P.pt_off + off_lo, off_b, bar);
+    if (rs_b) tma_load(S.sRs, P.ft_rs + T.r0, rs_b, bar);
 }
 
 template <int MODE>
@@ -205,8 +213,8 @@ __global__ void __launch_bounds__(FT_THREADS, 2) k_tile_pass(Params P, const dou
             ax = j0.x * d0 + j0.y * d1 + j1.x * d2;
             ay = j1.y * d0 + j2.x * d1 + j2.y * d2;
             S.sO[pos] = j0.x * ax + j1.y * ay;
-            S.sO[FT_LD + pos] = j0.y * ax + j2.x * ay;
-            S.sO[2 * FT_LD + pos] = j1.x * ax + j2.y * ay;
+            S.sO[FT_LDB + pos] = j0.y * ax + j2.x * ay;
+            S.sO[2 * FT_LDB + pos] = j1.x * ax + j2.y * ay;
         }
         __syncthreads();
         if (MODE == 0 && have_next && tid == 0) ft_issue_group1<MODE>(P, S, Tn, b, buf ^ 1, S.bar);
@@ -221,17 +229,20 @@ __global__ void __launch_bounds__(FT_THREADS, 2) k_tile_pass(Params P, const dou
             for (int q0 = (tid & ~31) >> 2; q0 < T.m; q0 += FT_THREADS / 4) {  // warp-uniform bounds
                 const int q = q0 + (lane >> 2);
                 const bool valid = q < T.m;
+                // transposed track layout: observation i of point q sits at rs[i] + q, so the lanes of
+                // neighbouring points read neighbouring words; tracks of a warp are (nearly) equally long
+                const int len = (valid && k < 3) ? off[q + 1] - off[q] : 0;
+                const int wmax = __reduce_max_sync(0xffffffffu, len);
+                const double* src = S.sO + k * FT_LDB + q;
                 double sk = 0.0;
-                if (valid && k < 3) {
-                    const int a = off[q] - T.o0, e = off[q + 1] - T.o0;
-                    const double* src = S.sO + k * FT_LD;
-                    for (int i0 = a; i0 < e; i0 += 4) {  // loads first, then the (ordered) adds; x + 0.0 is exact
-                        double v[4];
+                for (int i0 = 0; i0 < wmax; i0 += 4) {  // loads first, then the (ordered) adds; x + 0.0 is exact
+                    const int4 r4 = *reinterpret_cast<const int4*>(S.sRs + i0);  // broadcast
+                    const int rs[4] = {r4.x, r4.y, r4.z, r4.w};
+                    double v[4];
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) v[j] = (i0 + j < e) ? src[i0 + j] : 0.0;
+                    for (int j = 0; j < 4; ++j) v[j] = (i0 + j < len) ? src[rs[j]] : 0.0;
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) sk += v[j];
-                    }
+                    for (int j = 0; j < 4; ++j) sk += v[j];
                 }
                 const double s0 = __shfl_sync(0xffffffffu, sk, (lane & ~3));
                 const double s1 = __shfl_sync(0xffffffffu, sk, (lane & ~3) + 1);
@@ -286,31 +297,37 @@ __global__ void __launch_bounds__(FT_THREADS, 2) k_tile_pass(Params P, const dou
             __syncthreads();
 
             // ---- phase D: one thread per (segment, component): fixed-order sum -> one row per segment ---
-            const int* seg_s = S.sSeg + buf * FT_SEG_N + (T.s0 & 3);
+            const int* seg_i = S.sSeg + buf * FT_SEG_N + (T.s0 & 3);
             const int* seg_r = S.sRow + buf * FT_SEG_N + (T.s0 & 3);
-            for (int w = tid; w < T.ns * 6; w += FT_THREADS) {
+            for (int w0 = tid & ~31; w0 < T.ns * 6; w0 += FT_THREADS) {  // warp-uniform bounds
+                const int w = w0 + (tid & 31);
+                const bool valid = w < T.ns * 6;
                 const int seg = w / 6, k = w - 6 * seg;
-                const int a = seg_s[seg] - T.o0, e = seg_s[seg + 1] - T.o0;
-                const double* src = S.sO + k * FT_LD;
-                double v[FT_SEG_MAX];
-#pragma unroll
-                for (int j = 0; j < FT_SEG_MAX; ++j) v[j] = (a + j < e) ? src[a + j] : 0.0;
+                const int info = valid ? seg_i[seg] : 0;  // first tile-camera position | length << 16; longest first
+                const int a = info & 0xffff, len = info >> 16;
+                const int wmax = __reduce_max_sync(0xffffffffu, len);
+                const double* src = S.sO + k * FT_LD + a;
                 double sum = 0.0;
+                for (int j0 = 0; j0 < wmax; j0 += 4) {
+                    double v[4];
 #pragma unroll
-                for (int j = 0; j < FT_SEG_MAX; ++j) sum += v[j];
-                P.rows[(size_t)seg_r[seg] * 6 + k] = sum;
+                    for (int j = 0; j < 4; ++j) v[j] = (j0 + j < len) ? src[j0 + j] : 0.0;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) sum += v[j];
+                }
+                if (valid) P.rows[(size_t)seg_r[seg] * 6 + k] = sum;
             }
         }
         if (!have_next) break;
         // the next tile's header travels from thread 0 to everybody through shared memory
         if (tid == 0) {
             int* hs = reinterpret_cast<int*>(tot);  // free between tiles in MODE 0; MODE 1 has consumed tot above
-            hs[0] = Tn.p0; hs[1] = Tn.m; hs[2] = Tn.o0; hs[3] = Tn.n; hs[4] = Tn.s0; hs[5] = Tn.ns;
+            hs[0] = Tn.p0; hs[1] = Tn.m; hs[2] = Tn.o0; hs[3] = Tn.n; hs[4] = Tn.s0; hs[5] = Tn.ns; hs[6] = Tn.r0; hs[7] = Tn.maxlen;
         }
         __syncthreads();
         {
             const int* hs = reinterpret_cast<const int*>(tot);
-            T.p0 = hs[0]; T.m = hs[1]; T.o0 = hs[2]; T.n = hs[3]; T.s0 = hs[4]; T.ns = hs[5];
+            T.p0 = hs[0]; T.m = hs[1]; T.o0 = hs[2]; T.n = hs[3]; T.s0 = hs[4]; T.ns = hs[5]; T.r0 = hs[6]; T.maxlen = hs[7];
         }
         t = tn;
     }
@@ -404,29 +421,82 @@ __global__ void k_ft_tile_seg(int n_tiles, int n_obs, int n_seg, const int* __re
     const int o = ft_obs[t];
     ft_seg[t] = o < n_obs ? seg_inc[o] - 1 : n_seg;  // trailing tiles of unobserved points own no segment
 }
+// Transposed track layout of a tile (its points are ordered by track length, longest first):
+// observation i of local point q is parked at rs[i] + q, rs[i] = sum over i' < i of #{points longer than i'}.
+__global__ void __launch_bounds__(FT_THREADS) k_ft_rowstart(const int* __restrict__ ft_pt, const int* __restrict__ pt_off,
+                                                            const int* __restrict__ rs0, const int* __restrict__ maxlen,
+                                                            int* __restrict__ rs) {
+    typedef cub::BlockScan<int, FT_THREADS> Scan;
+    __shared__ typename Scan::TempStorage tmp;
+    const int t = blockIdx.x, i = threadIdx.x;
+    const int p0 = ft_pt[t], m = ft_pt[t + 1] - p0, ml = maxlen[t];
+    int mi = 0;
+    if (i < ml) {  // first q whose track is not longer than i
+        int lo = 0, hi = m;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (pt_off[p0 + mid + 1] - pt_off[p0 + mid] > i) lo = mid + 1; else hi = mid;
+        }
+        mi = lo;
+    }
+    int ex;
+    Scan(tmp).ExclusiveSum(mi, ex);
+    if (i < ml) rs[rs0[t] + i] = ex;
+}
 __global__ void k_ft_fill(int n_obs, const unsigned long long* __restrict__ key_s, const int* __restrict__ src,
-                          const int* __restrict__ flag, const int* __restrict__ seg_inc, const int* __restrict__ ft_obs,
-                          const int* __restrict__ ft_pt, const int* __restrict__ ft_seg, const double2* __restrict__ pm_uv,
-                          const int2* __restrict__ pm_idx, double2* __restrict__ tc_uv, int2* __restrict__ tc_meta,
-                          int* __restrict__ pm_tc, int* __restrict__ seg_cam, int* __restrict__ seg_start,
-                          unsigned* __restrict__ seg_key) {
+                          const int* __restrict__ flag, const int* __restrict__ seg_inc, const int* __restrict__ ft_pt,
+                          const int* __restrict__ pt_off, const int* __restrict__ rs0, const int* __restrict__ rs,
+                          const double2* __restrict__ pm_uv, const int2* __restrict__ pm_idx, double2* __restrict__ tc_uv,
+                          int2* __restrict__ tc_meta, int* __restrict__ pm_tc, int* __restrict__ seg_cam,
+                          int* __restrict__ seg_start) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_obs) return;
     const int j = src[i];
     const int t = (int)(key_s[i] >> 32), cam = (int)(unsigned)key_s[i];
     const int s = seg_inc[i] - 1;
-    const unsigned pl = (unsigned)(pm_idx[j].y - ft_pt[t]), pos = (unsigned)(j - ft_obs[t]);
+    const int p = pm_idx[j].y;
+    const unsigned pl = (unsigned)(p - ft_pt[t]);
+    const unsigned pos = (unsigned)rs[rs0[t] + (j - pt_off[p])] + pl;
     tc_uv[i] = pm_uv[j];
     tc_meta[i] = make_int2(cam, (int)(pl | (pos << 10)));
     pm_tc[j] = i;
-    if (flag[i]) { seg_cam[s] = cam; seg_start[s] = i; seg_key[s] = (unsigned)cam; }
+    if (flag[i]) { seg_cam[s] = cam; seg_start[s] = i; }
+}
+// Segments of a tile are renumbered longest first (so that the lanes that sum segments side by side run
+// equally long loops): sort key = (tile, FT_SEG_MAX - length).
+__global__ void k_ft_seg_keys(int n_seg, int n_tiles, const int* __restrict__ seg_start, const int* __restrict__ ft_obs,
+                              unsigned* __restrict__ key, int* __restrict__ iota) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_seg) return;
+    const int a = seg_start[s], len = seg_start[s + 1] - a;
+    int lo = 0, hi = n_tiles;  // last tile with ft_obs[t] <= a
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (ft_obs[mid] <= a) lo = mid; else hi = mid;
+    }
+    key[s] = ((unsigned)lo << 5) | (unsigned)(FT_SEG_MAX - len);
+    iota[s] = s;
+}
+__global__ void k_ft_seg_apply(int n_seg, const unsigned* __restrict__ key_s, const int* __restrict__ order,
+                               const int* __restrict__ seg_start, const int* __restrict__ seg_cam_in,
+                               const int* __restrict__ ft_obs, int* __restrict__ seg_info, int* __restrict__ seg_cam,
+                               unsigned* __restrict__ cam_key, int* __restrict__ iota) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n_seg) return;
+    const int s = order[r], t = (int)(key_s[r] >> 5);
+    const int a = seg_start[s], len = seg_start[s + 1] - a;
+    seg_info[r] = (a - ft_obs[t]) | (len << 16);
+    seg_cam[r] = seg_cam_in[s];
+    cam_key[r] = (unsigned)seg_cam_in[s];
+    iota[r] = r;
 }
 __global__ void k_ft_headers(int n_tiles, const int* __restrict__ ft_pt, const int* __restrict__ ft_obs,
-                             const int* __restrict__ ft_seg, int4* __restrict__ hdr) {
+                             const int* __restrict__ ft_seg, const int* __restrict__ rs0, const int* __restrict__ maxlen,
+                             int4* __restrict__ hdr) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_tiles) return;
     hdr[2 * t] = make_int4(ft_pt[t], ft_pt[t + 1] - ft_pt[t], ft_obs[t], ft_obs[t + 1] - ft_obs[t]);
-    hdr[2 * t + 1] = make_int4(ft_seg[t], ft_seg[t + 1] - ft_seg[t], 0, 0);
+    hdr[2 * t + 1] = make_int4(ft_seg[t], ft_seg[t + 1] - ft_seg[t], rs0[t], maxlen[t]);
 }
 __global__ void k_ft_seg_rows(int n_seg, const int* __restrict__ sorted_seg, int* __restrict__ seg_row) {
     const int r = blockIdx.x * blockDim.x + threadIdx.x;

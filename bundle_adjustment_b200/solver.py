@@ -194,12 +194,12 @@ class FlatSolver:
         T, Sg, no, nc, npt = info["point_tiles"], info["segments"], info["n_obs"], info["n_cams"], info["n_pts"]
         i32 = lambda n: np.zeros(n, dtype=np.int32)
         out = {"ft_pt": i32(T + 1), "ft_obs": i32(T + 1), "ft_seg": i32(T + 1), "tc_meta": np.zeros((no, 2), dtype=np.int32),
-               "tc_uv": np.zeros((no, 2)), "seg_cam": i32(Sg), "seg_start": i32(Sg + 1), "seg_row": i32(Sg),
+               "tc_uv": np.zeros((no, 2)), "seg_cam": i32(Sg), "seg_info": i32(Sg), "seg_row": i32(Sg),
                "cam_row_off": i32(nc + 2), "pt_perm": i32(npt)}
         api.check(api.lib().ba_tile_layout(
             self._h, api.iptr(out["ft_pt"]), api.iptr(out["ft_obs"]), api.iptr(out["ft_seg"]),
             api.iptr(out["tc_meta"]), api.dptr(out["tc_uv"]), api.iptr(out["seg_cam"]),
-            api.iptr(out["seg_start"]), api.iptr(out["seg_row"]), api.iptr(out["cam_row_off"]), api.iptr(out["pt_perm"])))
+            api.iptr(out["seg_info"]), api.iptr(out["seg_row"]), api.iptr(out["cam_row_off"]), api.iptr(out["pt_perm"])))
         return out
 
     def kernel_stats(self) -> Dict[str, Tuple[int, float]]:

@@ -178,10 +178,10 @@ int ba_layout_info(ba_handle* h, int64_t out[8]);
 /* Test hook: copy out the point-tile structure built by ba_set_problem (sizes from ba_layout_info:
  * T = point tiles, S = segments).  ft_pt/ft_obs/ft_seg[T+1], tc_meta[n_obs*2] (camera slot, local point |
  * point-major position << 10), tc_uv[n_obs*2],
- * seg_cam[S], seg_start[S+1], seg_row[S], cam_row_off[n_adj+2], pt_perm[n_pts] (internal point ->
+ * seg_cam[S], seg_info[S] (first position inside the tile | length << 16), seg_row[S], cam_row_off[n_adj+2], pt_perm[n_pts] (internal point ->
  * caller's index).  Any pointer may be NULL. */
 int ba_tile_layout(ba_handle* h, int32_t* ft_pt, int32_t* ft_obs, int32_t* ft_seg, int32_t* tc_meta, double* tc_uv,
-                   int32_t* seg_cam, int32_t* seg_start, int32_t* seg_row, int32_t* cam_row_off, int32_t* pt_perm);
+                   int32_t* seg_cam, int32_t* seg_info, int32_t* seg_row, int32_t* cam_row_off, int32_t* pt_perm);
 
 /* Thread-local text of the last error returned on this thread. */
 const char* ba_last_error(void);
