@@ -562,7 +562,7 @@ static void build_tiles(ba_handle* h, int n_cams, int n_pts, int n_obs) {
     CK(cudaFuncSetAttribute(k_tile_pass<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ft_smem_bytes(FT_ROWS_MV)));
     CK(cudaStreamSynchronize(s));  // scratch dies here
     h->ft_tiles = T; h->n_seg = S;
-    h->ft_grid = std::min(T, 2 * h->sm_count);  // persistent CTAs, two per SM
+    h->ft_grid = std::min(T, FT_CTAS_PER_SM * h->sm_count);  // persistent CTAs
     h->fused_ok = true;
 }
 

@@ -30,8 +30,9 @@
 
 namespace ba {
 
-constexpr int FT_THREADS = 512;        // threads per CTA = observation capacity of a tile
-constexpr int FT_PTS = 256;            // point capacity of a tile
+constexpr int FT_THREADS = 256;        // threads per CTA = observation capacity of a tile
+constexpr int FT_PTS = 128;            // point capacity of a tile
+constexpr int FT_CTAS_PER_SM = 1024 / FT_THREADS;  // register file: 64 registers per thread
 constexpr int FT_SEG_MAX = 16;         // observations per segment (one output row each)
 constexpr int FT_LD = FT_THREADS + 2;  // row stride of the camera-side scratch (phases C/D): 2*FT_LD mod 32 = 4 banks, so the
                                        // six components of one segment fall on different banks
@@ -41,7 +42,7 @@ constexpr int FT_ROWS_MV = 6;          // scratch rows of the mat-vec pass
 
 // dynamic shared memory of a tile pass (16-byte aligned regions): per-observation scratch rows | Jacobian
 // cache planes [3][FT_THREADS] double2 | observation records | X as planes (X0,X1)[FT_PTS], X2[FT_PTS+2] | z likewise | Vinv [FT_PTS][6] |
-// track offsets | track-row starts | segment table x2 | segment rows x2 | two mbarriers.  The x2 regions are double-buffered
+// Vinv x2 ... | track offsets x2 | track-row starts x2 | segment table x2 | segment rows x2 | two mbarriers.  The x2 regions are double-buffered
 // by tile parity; everything else is refilled by the TMA as soon as its last reader has passed a barrier.
 constexpr int FT_META_N = FT_THREADS + 2, FT_OFF_N = FT_PTS + 8, FT_SEG_N = FT_THREADS + 8;
 struct FtSmem {
@@ -50,8 +51,8 @@ struct FtSmem {
     unsigned long long* bar;
 };
 __host__ __device__ constexpr size_t ft_smem_bytes(int rows) {
-    return (size_t)(rows * FT_LD) * 8 + 3 * FT_THREADS * 16 + FT_META_N * 8 + (size_t)FT_PTS * (2 + 2 + 6) * 8 +
-           2 * (size_t)(FT_PTS + 2) * 8 + (size_t)(FT_OFF_N + 5 * FT_SEG_N) * 4 + 16;
+    return (size_t)(rows * FT_LD) * 8 + 3 * FT_THREADS * 16 + FT_META_N * 8 + (size_t)FT_PTS * (2 + 2 + 2 * 6) * 8 +
+           2 * (size_t)(FT_PTS + 2) * 8 + (size_t)(2 * FT_OFF_N + 6 * FT_SEG_N) * 4 + 16;
 }
 BA_D FtSmem ft_carve(double* sm, int rows) {
     FtSmem S;
@@ -63,9 +64,9 @@ BA_D FtSmem ft_carve(double* sm, int rows) {
     S.sZ01 = reinterpret_cast<double2*>(S.sX2 + FT_PTS + 2);
     S.sZ2 = reinterpret_cast<double*>(S.sZ01 + FT_PTS);
     S.sVi = S.sZ2 + FT_PTS + 2;
-    S.sOff = reinterpret_cast<int*>(S.sVi + FT_PTS * 6);
-    S.sRs = S.sOff + FT_OFF_N;
-    S.sSeg = S.sRs + FT_SEG_N;
+    S.sOff = reinterpret_cast<int*>(S.sVi + 2 * FT_PTS * 6);
+    S.sRs = S.sOff + 2 * FT_OFF_N;
+    S.sSeg = S.sRs + 2 * FT_SEG_N;
     S.sRow = S.sSeg + 2 * FT_SEG_N;
     S.bar = reinterpret_cast<unsigned long long*>(S.sRow + 2 * FT_SEG_N);
     return S;
@@ -117,7 +118,8 @@ BA_D TileHdr tile_hdr(const Params& P, int t) {
 // Persistent CTAs (grid = 2 per SM) each walk a contiguous run of tiles.  All HBM traffic of a tile is moved by
 // the TMA (cp.async.bulk) while the PREVIOUS tile is being computed: group 1 (observation records,
 // Jacobian cache, points, segment table) is re-armed right after phase A has pulled its operands into
-// registers, group 2 (Vinv, track offsets) right after phase B; each group completes on its own mbarrier.
+// registers, together with group 2 (Vinv, track offsets, track rows; double-buffered) - by the first lane of
+// the last warp, which has no work in phase B; each group completes on its own mbarrier.
 struct TileCopy {  // 16-byte aligned source windows of one tile
     int meta_lo, off_lo, seg_lo;  // first element copied (<= the tile's first) of tc_meta / pt_off / seg arrays
 };
@@ -147,22 +149,23 @@ BA_D void ft_issue_group1(const Params& P, const FtSmem& S, const TileHdr& T, in
         tma_load(S.sRow + buf * FT_SEG_N, P.seg_row + seg_lo, seg_b, bar);
     }
 }
-BA_D void ft_issue_group2(const Params& P, const FtSmem& S, const TileHdr& T, unsigned long long* bar) {
+BA_D void ft_issue_group2(const Params& P, const FtSmem& S, const TileHdr& T, int buf, unsigned long long* bar) {
     const int off_lo = T.p0 & ~3;
     const unsigned vi_b = (unsigned)T.m * 48u;
     const unsigned off_b = (unsigned)(((T.p0 + T.m + 1 - off_lo) * 4 + 15) & ~15);
     const unsigned rs_b = (unsigned)((T.maxlen * 4 + 15) & ~15);  // r0 is a multiple of 4
     mbar_expect_tx(bar, vi_b + off_b + rs_b);
-    tma_load(S.sVi, P.pt_Vinv + (size_t)T.p0 * 6, vi_b, bar);
-    tma_load(S.sOff, P.pt_off + off_lo, off_b, bar);
-    if (rs_b) tma_load(S.sRs, P.ft_rs + T.r0, rs_b, bar);
+    tma_load(S.sVi + buf * FT_PTS * 6, P.pt_Vinv + (size_t)T.p0 * 6, vi_b, bar);
+    tma_load(S.sOff + buf * FT_OFF_N, P.pt_off + off_lo, off_b, bar);
+    if (rs_b) tma_load(S.sRs + buf * FT_SEG_N, P.ft_rs + T.r0, rs_b, bar);
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(FT_THREADS, 2) k_tile_pass(Params P, const double* __restrict__ vec) {
+__global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params P, const double* __restrict__ vec) {
     extern __shared__ __align__(16) double sm[];
     __shared__ double red[FT_THREADS / 32 * 4];
     __shared__ double tot[4];
+    __shared__ int hs[8];
     if (MODE == 0 && P.st->pcg_done) return;
     // contiguous run of tiles per CTA: neighbouring tiles share cameras, so the camera vectors stay in L1
     int t = (int)((long long)blockIdx.x * P.ft_tiles / gridDim.x);
@@ -178,7 +181,7 @@ __global__ void __launch_bounds__(FT_THREADS, 2) k_tile_pass(Params P, const dou
         asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
         ft_issue_group1<MODE>(P, S, T, b, 0, S.bar);
-        ft_issue_group2(P, S, T, S.bar + 1);
+        ft_issue_group2(P, S, T, 0, S.bar + 1);
     }
     __syncthreads();
 
@@ -187,7 +190,8 @@ __global__ void __launch_bounds__(FT_THREADS, 2) k_tile_pass(Params P, const dou
         const int tn = t + 1;
         const bool have_next = tn < t_end;
         TileHdr Tn = T;
-        if (have_next && tid == 0) Tn = tile_hdr(P, tn);
+        const bool issuer = tid == FT_THREADS - 32;  // first lane of the last warp, which is idle in phase B
+        if (have_next && issuer) Tn = tile_hdr(P, tn);
         const bool act = tid < T.n;
 
         // ---- phase A: operands to registers; a = Jt (w x X + v); park Jt^T a at the point-major position --
@@ -216,16 +220,21 @@ __global__ void __launch_bounds__(FT_THREADS, 2) k_tile_pass(Params P, const dou
             S.sO[FT_LDB + pos] = j0.y * ax + j2.x * ay;
             S.sO[2 * FT_LDB + pos] = j1.x * ax + j2.y * ay;
         }
+        mbar_wait(S.bar + 1, it & 1);  // every thread sees group 2 complete BEFORE the barrier, so re-arming is safe after it
         __syncthreads();
-        if (MODE == 0 && have_next && tid == 0) ft_issue_group1<MODE>(P, S, Tn, b, buf ^ 1, S.bar);
+        if (MODE == 0 && have_next && issuer) {
+            ft_issue_group1<MODE>(P, S, Tn, b, buf ^ 1, S.bar);
+            ft_issue_group2(P, S, Tn, buf ^ 1, S.bar + 1);
+        }
 
         // ---- phase B: four lanes per point: lane k < 3 adds component k of the track in observation
         //      order, the quad exchanges the three sums and lane k forms row k of Vinv * s --------------
-        mbar_wait(S.bar + 1, it & 1);
         double acc[4] = {0.0, 0.0, 0.0, 0.0};  // MODE 1: g.dp, dp D dp, |dp|^2, |X|^2
         {
             const int k = tid & 3, lane = tid & 31;
-            const int* off = S.sOff + (T.p0 & 3);
+            const int* off = S.sOff + buf * FT_OFF_N + (T.p0 & 3);
+            const int* rsb = S.sRs + buf * FT_SEG_N;
+            const double* sVi = S.sVi + buf * FT_PTS * 6;
             for (int q0 = (tid & ~31) >> 2; q0 < T.m; q0 += FT_THREADS / 4) {  // warp-uniform bounds
                 const int q = q0 + (lane >> 2);
                 const bool valid = q < T.m;
@@ -236,7 +245,7 @@ __global__ void __launch_bounds__(FT_THREADS, 2) k_tile_pass(Params P, const dou
                 const double* src = S.sO + k * FT_LDB + q;
                 double sk = 0.0;
                 for (int i0 = 0; i0 < wmax; i0 += 4) {  // loads first, then the (ordered) adds; x + 0.0 is exact
-                    const int4 r4 = *reinterpret_cast<const int4*>(S.sRs + i0);  // broadcast
+                    const int4 r4 = *reinterpret_cast<const int4*>(rsb + i0);  // broadcast
                     const int rs[4] = {r4.x, r4.y, r4.z, r4.w};
                     double v[4];
 #pragma unroll
@@ -249,7 +258,7 @@ __global__ void __launch_bounds__(FT_THREADS, 2) k_tile_pass(Params P, const dou
                 const double s2 = __shfl_sync(0xffffffffu, sk, (lane & ~3) + 2);
                 double zk = 0.0;
                 if (valid && k < 3) {
-                    const double* Vi = S.sVi + 6 * q;  // 00 01 02 11 12 22
+                    const double* Vi = sVi + 6 * q;  // 00 01 02 11 12 22
                     const double v0 = Vi[k], v1 = Vi[k == 0 ? 1 : (k == 1 ? 3 : 4)], v2 = Vi[k == 2 ? 5 : (k == 1 ? 4 : 2)];
                     zk = v0 * s0 + v1 * s1 + v2 * s2;
                 }
@@ -273,14 +282,13 @@ __global__ void __launch_bounds__(FT_THREADS, 2) k_tile_pass(Params P, const dou
             if (tid == 0) {
                 double* out = P.pm_partial + (size_t)t * NSCAL;
                 out[S_GDP] = tot[0]; out[S_DDP] = tot[1]; out[S_DP2] = tot[2]; out[S_XP2] = tot[3];
-                if (have_next) {
-                    ft_issue_group1<MODE>(P, S, Tn, b, buf ^ 1, S.bar);
-                    ft_issue_group2(P, S, Tn, S.bar + 1);
-                }
+            }
+            if (have_next && issuer) {  // phase B has read the points: everything may be refilled now
+                ft_issue_group1<MODE>(P, S, Tn, b, buf ^ 1, S.bar);
+                ft_issue_group2(P, S, Tn, buf ^ 1, S.bar + 1);
             }
         } else {
             __syncthreads();
-            if (have_next && tid == 0) ft_issue_group2(P, S, Tn, S.bar + 1);
 
             // ---- phase C: camera-side product of every observation, parked at its tile-camera position --
             if (act) {
@@ -319,14 +327,12 @@ __global__ void __launch_bounds__(FT_THREADS, 2) k_tile_pass(Params P, const dou
             }
         }
         if (!have_next) break;
-        // the next tile's header travels from thread 0 to everybody through shared memory
-        if (tid == 0) {
-            int* hs = reinterpret_cast<int*>(tot);  // free between tiles in MODE 0; MODE 1 has consumed tot above
+        // the next tile's header travels from the issuing thread to everybody through shared memory
+        if (issuer) {
             hs[0] = Tn.p0; hs[1] = Tn.m; hs[2] = Tn.o0; hs[3] = Tn.n; hs[4] = Tn.s0; hs[5] = Tn.ns; hs[6] = Tn.r0; hs[7] = Tn.maxlen;
         }
         __syncthreads();
         {
-            const int* hs = reinterpret_cast<const int*>(tot);
             T.p0 = hs[0]; T.m = hs[1]; T.o0 = hs[2]; T.n = hs[3]; T.s0 = hs[4]; T.ns = hs[5]; T.r0 = hs[6]; T.maxlen = hs[7];
         }
         t = tn;
