@@ -1,4 +1,4 @@
-"""Per-kernel CUDA-event times of a short solve (3 LM iterations) on a BASELINE shape.
+"""Per-kernel CUDA-event times of a short solve (3 LM iterations x 8 PCG iterations, none skipped) on a BASELINE shape.
 
     python scripts/quick_kernels.py [shape] [schur_path]
 """
@@ -16,7 +16,7 @@ s.set_flat(fp)
 print(s.layout_info())
 for rep in range(2):
     s.restore_initial()
-    st = s.solve(max_iters=3, verbose=2, schur_path=path)
+    st = s.solve(max_iters=3, verbose=2, schur_path=path, pcg_tol=1e-30, pcg_max_iters=8, pcg_check_every=100)
 ks = s.kernel_stats()
 print(shape, st["iterations"], st["pcg_iterations"], round(st["solve_ms"], 2), "ms", st["final_cost"])
 for k, (n, ms) in ks.items():
