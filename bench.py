@@ -9,8 +9,9 @@ of the workload from the same initial guess.  ``value`` = observations x LM iter
 problem resident in HBM (device-side parameter reset between steps); ``e2e`` = the same through the
 C ABI with HOST buffers: ``ba_set_problem`` (H2D + device-side sort) + ``ba_solve`` + ``ba_get_params``
 (D2H) inside the timed region.  N > 1: one process per GPU (torchrun), points sharded by rank, cameras
-replicated, NCCL all-reduce of camera-sized sums inside the library; weak scaling (the workload grows
-with N: N x 993 k points / N x 5 M observations / N x 1778 cameras).
+replicated, NCCL all-reduce of camera-sized sums inside the library; weak scaling (what is sharded grows
+with N: N x 993 k points / N x 5 M observations; the 1778 replicated cameras stay), `--scaling strong` keeps
+the N = 1 problem.
 """
 from __future__ import annotations
 
@@ -89,11 +90,14 @@ class ClockSampler(threading.Thread):
 
 
 def make_workload(name, n_gpus, scaling):
+    """Weak scaling grows what is sharded - points and their observations - with the number of GPUs and keeps
+    the cameras (replicated on every rank) fixed, so the work per GPU and the size of the reduced camera
+    system stay what they are at N = 1.  Strong scaling solves the N = 1 problem on N GPUs."""
     from bundle_adjustment_b200 import synthetic as S
     n_cams, n_pts, n_obs = S.SHAPES[name]
     mult = n_gpus if scaling == "weak" else 1
-    fp = S.make_flat_problem(n_cams * mult, n_pts * mult, n_obs * mult, S.SEEDS[name], keep_truth=False)
-    label = f"{name}-shape synthetic: {n_cams * mult} cameras / {n_pts * mult} points / {n_obs * mult} observations"
+    fp = S.make_flat_problem(n_cams, n_pts * mult, n_obs * mult, S.SEEDS[name], keep_truth=False)
+    label = f"{name}-shape synthetic: {n_cams} cameras / {n_pts * mult} points / {n_obs * mult} observations"
     return fp, label
 
 
@@ -169,6 +173,10 @@ def algorithmic_bytes(kernel, n_obs, n_obs_adj, n_pts, n_cams, n_seg=0):
 
 
 def run_ours(args, rank, world, local_rank):
+    # libraries (NCCL) may write to fd 1; keep the JSON line the only thing on stdout
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     import torch
     from bundle_adjustment_b200 import FlatSolver, sharding
 
@@ -310,7 +318,10 @@ def run_ours(args, rank, world, local_rank):
         "gpu_launches": int(launches),
         "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
     }
-    print(json.dumps(line))
+    sys.stdout.flush()
+    os.dup2(real_stdout, 1)
+    print(json.dumps(line), flush=True)
+    os.dup2(2, 1)
     solver.close()
     if dist is not None:
         dist.barrier(); dist.destroy_process_group()

@@ -14,6 +14,7 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -472,6 +473,22 @@ static void use(ba_handle* h) {
     CK(cudaSetDevice(h->device));
 }
 
+// Stage timing of ba_set_problem on stderr when the environment variable BA_B200_TRACE is set (each mark
+// synchronises the stream, so it is a diagnostic, not a mode to benchmark in).
+struct StageTimer {
+    bool on;
+    cudaStream_t s;
+    std::chrono::steady_clock::time_point t0;
+    explicit StageTimer(cudaStream_t st) : on(getenv("BA_B200_TRACE") != nullptr), s(st), t0(std::chrono::steady_clock::now()) {}
+    void mark(const char* what) {
+        if (!on) return;
+        cudaStreamSynchronize(s);
+        const auto t1 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[ba_b200] set_problem %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    }
+};
+
 struct MaxOp {
     __host__ __device__ int operator()(int a, int b) const { return a > b ? a : b; }
 };
@@ -576,6 +593,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     cudaStream_t s = h->stream;
     h->have_problem = false;
     const size_t nc1 = (size_t)n_cams + 1;
+    StageTimer tm(s);
 
     h->cam_rt.alloc(2 * nc1 * 6); h->cam_R.alloc(2 * nc1 * 12);
     h->pt_X.alloc(2 * 3 * (size_t)((n_pts + 1) & ~1) + 4); h->pt_z.alloc((size_t)n_pts * 4); h->pt_h.alloc((size_t)n_pts * 4);
@@ -608,6 +626,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     CK(cudaMemcpyAsync(d_pt.p, obs_pt, (size_t)n_obs * sizeof(int), cudaMemcpyHostToDevice, s));
     CK(cudaMemcpyAsync(h->o_uv.p, obs_uv, (size_t)n_obs * sizeof(double2), cudaMemcpyHostToDevice, s));
 
+    tm.mark("allocate + upload");
     Params& P = h->P;
     memset(&P, 0, sizeof P);
     P.K = Intr{fx, fy, cx, cy};
@@ -693,6 +712,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
         CK(cudaStreamSynchronize(s));  // the scratch buffers of this block die here
     }
 
+    tm.mark("locality order + tile cuts");
     // ---- point-major order: stable radix sort of (internal point, original index) ----------------
     tmp_bytes = d_tmp.n;
     CK(cub::DeviceRadixSort::SortPairs(d_tmp.p, tmp_bytes, d_kpt.p, d_kpt_s.p, d_iota.p, d_perm.p, n_obs, 0, pt_bits, s));
@@ -705,6 +725,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     launch(h, KN_SETUP, k_pm_tiles, cdiv(pm_tiles + 1, B), B, 0, n_pts, (const int*)h->pt_off.p, pm_tiles, h->pm_tile_pt.p);
     launch(h, KN_SETUP, k_max_track, cdiv(n_pts, B), B, 0, n_pts, (const int*)h->pt_off.p, d_err.p + 1);
 
+    tm.mark("point-major order");
     // ---- camera-major order: stable sort of ((camera, point), original index); fixed camera last ----
     tmp_bytes = d_tmp.n;
     CK(cub::DeviceRadixSort::SortPairs(d_tmp.p, tmp_bytes, d_kcam.p, d_kcam_s.p, d_iota.p, d_perm.p, n_obs, 0, 32 + cam_bits, s));
@@ -734,7 +755,9 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     CK(cudaMemcpyAsync(h->cam_tile_off.p, tile_off.data(), nc1 * sizeof(int), cudaMemcpyHostToDevice, s));
     h->cm_partial.alloc(std::max<size_t>((size_t)cm_tiles * 27, 27));
     h->max_track = err_track[1];
+    tm.mark("camera-major order");
     build_tiles(h, n_cams, n_pts, n_obs);
+    tm.mark("point tiles");
     const int n_partial_rows = std::max(pm_tiles, h->ft_tiles);
     h->pm_partial.alloc((size_t)n_partial_rows * NSCAL);
     h->pm_partial.zero(s);
@@ -773,6 +796,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     P.rows = h->rows.p;
     h->st.zero(s);
     CK(cudaStreamSynchronize(s));  // the sort scratch buffers die at scope exit
+    tm.mark("finish");
     h->have_problem = true;
 }
 
@@ -870,6 +894,10 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     const int nc1 = P.n_cams + 1;
     if (opt->schur_path != BA_PATH_TILES && opt->schur_path != BA_PATH_TWO_PASS) fail(BA_ERR_ARG, "unknown schur_path %d", opt->schur_path);
     const bool tiles = opt->schur_path == BA_PATH_TILES && h->fused_ok;
+    // the PCG iterations of a solve are replayed from a CUDA graph (single GPU, no per-kernel event timing)
+    const bool use_graph = h->nranks == 1 && !h->time_kernels && check_every > 1;
+    cudaGraphExec_t pcg_graph = nullptr;
+    long long graph_launches[KN_COUNT] = {0};
 
     CK(cudaEventRecord(h->ev_solve0, s));
     launch(h, KN_SETUP, k_init_state, 1, 1, 0, h->st.p, opt->initial_lambda);
@@ -894,7 +922,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
             launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 27, 256), 256, 0, P, 27, 0);
             allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 27);
             launch(h, KN_CAM_FIN, k_camera_finish_schur, P.vec_ctas, VEC_THREADS, 0, P, with_schur, h->ticket.p);
-            for (int it = 0; it < opt->pcg_max_iters; ++it) {
+            auto pcg_iteration = [&]() {
                 int n_dots = P.vec_ctas;
                 if (tiles) {
                     launch(h, KN_TILE_MV, k_tile_pass<0>, h->ft_grid, FT_THREADS, ft_smem_bytes(FT_ROWS_MV), P, (const double*)h->v_u.p);
@@ -918,10 +946,34 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
                     }
                 }
                 launch(h, KN_PCG_UPDATE, k_pcg_update, P.vec_ctas, VEC_THREADS, 0, P, opt->pcg_tol, opt->pcg_max_iters, n_dots, h->ticket.p);
-                if ((it + 1) % check_every == 0 && it + 1 < opt->pcg_max_iters) {
-                    CK(cudaMemcpyAsync(h->h_flag, &h->st.p->pcg_done, sizeof(int), cudaMemcpyDeviceToHost, s));
-                    CK(cudaStreamSynchronize(s));
-                    if (*h->h_flag) break;
+            };
+            auto pcg_converged = [&]() {
+                CK(cudaMemcpyAsync(h->h_flag, &h->st.p->pcg_done, sizeof(int), cudaMemcpyDeviceToHost, s));
+                CK(cudaStreamSynchronize(s));
+                return *h->h_flag != 0;
+            };
+            if (use_graph) {
+                // `check_every` PCG iterations = one CUDA graph launch (kernels early-exit once the device flag is set)
+                if (!pcg_graph) {
+                    long long before[KN_COUNT];
+                    memcpy(before, h->launches, sizeof before);
+                    cudaGraph_t g = nullptr;
+                    CK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+                    for (int k = 0; k < check_every; ++k) pcg_iteration();
+                    CK(cudaStreamEndCapture(s, &g));
+                    CK(cudaGraphInstantiate(&pcg_graph, g, 0));
+                    CK(cudaGraphDestroy(g));
+                    for (int k = 0; k < KN_COUNT; ++k) { graph_launches[k] = h->launches[k] - before[k]; h->launches[k] = before[k]; }
+                }
+                for (int it = 0; it < opt->pcg_max_iters; it += check_every) {
+                    CK(cudaGraphLaunch(pcg_graph, s));
+                    for (int k = 0; k < KN_COUNT; ++k) h->launches[k] += graph_launches[k];
+                    if (it + check_every < opt->pcg_max_iters && pcg_converged()) break;
+                }
+            } else {
+                for (int it = 0; it < opt->pcg_max_iters; ++it) {
+                    pcg_iteration();
+                    if ((it + 1) % check_every == 0 && it + 1 < opt->pcg_max_iters && pcg_converged()) break;
                 }
             }
         }
@@ -943,6 +995,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
                     st.lambda, st.pcg_iter, st.gmax, st.step_norm);
     }
     if (opt->max_iters == 0) read_state(h);
+    if (pcg_graph) CK(cudaGraphExecDestroy(pcg_graph));
     CK(cudaEventRecord(h->ev_solve1, s));
     CK(cudaEventSynchronize(h->ev_solve1));
     float ms = 0.f;
@@ -994,7 +1047,7 @@ void ba_default_options(ba_options* o) {
     o->huber_delta = 1.0; o->robust_mode = BA_ROBUST_IRLS;
     o->initial_lambda = 1e-4; o->lambda_min = 1e-6; o->lambda_max = 1e16;
     o->precond = BA_PRECOND_SCHUR_JACOBI;
-    o->pcg_max_iters = 100; o->pcg_tol = 0.1; o->pcg_check_every = 4;
+    o->pcg_max_iters = 100; o->pcg_tol = 0.1; o->pcg_check_every = 8;
     o->verbose = 0;
     o->schur_path = BA_PATH_TILES;
 }
