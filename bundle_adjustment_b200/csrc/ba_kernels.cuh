@@ -963,29 +963,31 @@ BA_D double cta_sum_all(double v, double* sm /* >= 33 */) {  // all threads get 
 
 // Reduce per-tile / per-camera scalar partials into st->scal (fixed order).  The masks select slots.
 __global__ void __launch_bounds__(RED_THREADS) k_reduce_scalars(Params P, unsigned pm_mask, unsigned cam_mask) {
-    __shared__ double sm[33];
-    for (int s = 0; s < NSCAL; ++s) {
-        const bool pm = (pm_mask >> s) & 1u, cm = (cam_mask >> s) & 1u;
-        if (!pm && !cm) continue;
-        double v = 0.0;
-        if (s == S_GPMAX) {
-            for (int t = threadIdx.x; t < P.n_partial_rows; t += RED_THREADS) v = fmax(v, P.pm_partial[(size_t)t * NSCAL + s]);
-            v = warp_max(v);
-            __syncthreads();
-            if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
-            __syncthreads();
-            if (threadIdx.x == 0) {
-                double m = 0.0;
-                for (int i = 0; i < RED_THREADS / 32; ++i) m = fmax(m, sm[i]);
-                P.st->scal[s] = m;
-            }
-            __syncthreads();
-            continue;
+    // 16 lanes per partial row (one 128-byte line): thread t owns slot t & 15 of rows t >> 4, t >> 4 + 64, ...
+    static_assert(NSCAL == 16, "row layout");
+    __shared__ double sm[RED_THREADS];
+    const int s = threadIdx.x & 15, g = threadIdx.x >> 4;
+    constexpr int G = RED_THREADS / 16;
+    const bool pm = (pm_mask >> s) & 1u, cm = (cam_mask >> s) & 1u, is_max = (s == S_GPMAX);
+    double v = 0.0;
+    if (pm) {
+        for (int t = g; t < P.n_partial_rows; t += G) {
+            const double x = P.pm_partial[(size_t)t * NSCAL + s];
+            v = is_max ? fmax(v, x) : v + x;
         }
-        if (pm) for (int t = threadIdx.x; t < P.n_partial_rows; t += RED_THREADS) v += P.pm_partial[(size_t)t * NSCAL + s];
-        if (cm) for (int c = threadIdx.x; c < P.n_cams; c += RED_THREADS) v += P.cam_partial[(size_t)c * NSCAL + s];
-        const double tot = cta_sum_all(v, sm);
-        if (threadIdx.x == 0) P.st->scal[s] = tot;
+    }
+    if (cm) {
+        for (int c = g; c < P.n_cams; c += G) v += P.cam_partial[(size_t)c * NSCAL + s];
+    }
+    sm[g * 16 + s] = v;
+    __syncthreads();
+    if (threadIdx.x < 16 && (pm || cm)) {  // fixed order over the 64 row groups
+        double tot = 0.0;
+        for (int i = 0; i < G; ++i) {
+            const double x = sm[i * 16 + s];
+            tot = is_max ? fmax(tot, x) : tot + x;
+        }
+        P.st->scal[s] = tot;
     }
 }
 

@@ -8,6 +8,7 @@
 #include "../../include/ba_b200.h"
 #include "ba_kernels.cuh"
 #include "ba_tiles.cuh"
+#include "ba_peer.cuh"
 
 #include <cub/cub.cuh>
 #include <dlfcn.h>
@@ -58,6 +59,7 @@ struct NcclApi {
     ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
 };
 
@@ -79,6 +81,7 @@ static NcclApi& nccl_api() {
     api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(sym("ncclCommInitRank"));
     api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(sym("ncclCommDestroy"));
     api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(sym("ncclAllReduce"));
+    api.AllGather = reinterpret_cast<decltype(api.AllGather)>(sym("ncclAllGather"));
     api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
     return api;
 }
@@ -122,13 +125,13 @@ struct DBuf {
 enum Kind {
     KN_SETUP = 0, KN_CAM_PREP, KN_RESID, KN_JAC, KN_LIN_PTS, KN_PT_PREP, KN_PT_PASS, KN_BACKSUB, KN_LIN_CAM,
     KN_SCHUR_CAM, KN_MATVEC_CAM, KN_CAM_SUM, KN_CAM_FIN, KN_PCG_DOTS, KN_PCG_UPDATE, KN_CAM_UPDATE, KN_REDUCE,
-    KN_GRAD, KN_DECIDE, KN_TILE_MV, KN_TILE_BACKSUB, KN_ROWS_FIN, KN_COUNT
+    KN_GRAD, KN_DECIDE, KN_TILE_MV, KN_TILE_BACKSUB, KN_ROWS_FIN, KN_ROWS_XCHG, KN_DOTS_PEER, KN_COUNT
 };
 static const char* kKindNames[KN_COUNT] = {
     "setup", "cam_prepare", "residuals", "jacobian_blocks", "lin_points", "point_prepare", "schur_matvec_points",
     "backsub_points", "lin_cameras", "schur_rhs_cameras", "schur_matvec_cameras", "camera_sum", "camera_finish",
     "pcg_dots", "pcg_update", "camera_update", "reduce_scalars", "gradient_check", "lm_decide",
-    "schur_matvec_tiles", "backsub_tiles", "rows_finish"};
+    "schur_matvec_tiles", "backsub_tiles", "rows_finish", "rows_finish_xchg", "pcg_dots_peer"};
 
 // ---------------------------------------------------------------------------------------------
 // setup kernels (device-side construction of the two observation orders)
@@ -365,6 +368,13 @@ struct ba_handle {
     DBuf<int4> ft_hdr;
     DBuf<int> pm_tc;
     DBuf<double> rows;
+    // peer-memory exchange of the PCG mat-vec partials (ba_peer.cuh); multi-GPU handles only
+    bool peer_ok = false;
+    int xcap = 0;
+    DBuf<double> xbuf;
+    DBuf<int> xstate;
+    DBuf<double*> d_peers;
+    std::vector<double*> peer_ptr;  // exchange buffer of every rank as mapped here (own rank: xbuf.p)
     DBuf<int4> cm_tile;
     DBuf<double> cm_partial, pm_partial, cam_partial;
     DBuf<LMState> st;
@@ -381,6 +391,8 @@ struct ba_handle {
     cudaEvent_t ev_solve0 = nullptr, ev_solve1 = nullptr, ev_user0 = nullptr, ev_user1 = nullptr;
 
     ~ba_handle() {
+        for (size_t r = 0; r < peer_ptr.size(); ++r)
+            if (peer_ptr[r] && (int)r != rank) cudaIpcCloseMemHandle(peer_ptr[r]);
         if (comm) nccl_api().CommDestroy(comm);
         if (h_state) cudaFreeHost(h_state);
         if (h_flag) cudaFreeHost(h_flag);
@@ -581,6 +593,67 @@ static void build_tiles(ba_handle* h, int n_cams, int n_pts, int n_obs) {
     h->ft_tiles = T; h->n_seg = S;
     h->ft_grid = std::min(T, FT_CTAS_PER_SM * h->sm_count);  // persistent CTAs
     h->fused_ok = true;
+}
+
+// Map every rank's exchange buffer into this process (collective: all ranks call it with the same n_cams).
+// Falls back to the NCCL all-reduce (peer_ok = false on EVERY rank) if any rank cannot map a peer.
+static void setup_peer_exchange(ba_handle* h, int n_cams) {
+    if (h->nranks <= 1) return;
+    const int need = ((std::max(n_cams, 1) * 6 + 15) / 16) * 16;
+    if (h->xcap >= need) return;  // same decision on every rank: cameras are replicated
+    cudaStream_t s = h->stream;
+    CK(cudaStreamSynchronize(s));
+    for (size_t r = 0; r < h->peer_ptr.size(); ++r)
+        if (h->peer_ptr[r] && (int)r != h->rank) cudaIpcCloseMemHandle(h->peer_ptr[r]);
+    h->peer_ptr.assign(h->nranks, nullptr);
+    h->peer_ok = false;
+    h->xbuf.release();
+    h->xbuf.alloc((size_t)XB_HDR + 2 * (size_t)need);
+    h->xbuf.zero(s);
+    h->xstate.alloc(4);
+    h->xstate.zero(s);
+    h->xcap = need;
+    h->d_peers.alloc(h->nranks);
+    int good = getenv("BA_B200_NO_PEER") ? 0 : 1;
+    struct Card { cudaIpcMemHandle_t mem; char uuid[16]; } mine;
+    memset(&mine, 0, sizeof mine);
+    if (good && cudaIpcGetMemHandle(&mine.mem, h->xbuf.p) != cudaSuccess) { cudaGetLastError(); good = 0; }
+    {
+        int dev = 0;
+        cudaDeviceProp prop;
+        CK(cudaGetDevice(&dev));
+        CK(cudaGetDeviceProperties(&prop, dev));
+        memcpy(mine.uuid, prop.uuid.bytes, 16);
+    }
+    DBuf<unsigned char> d_h;
+    d_h.alloc((size_t)h->nranks * sizeof mine);
+    CK(cudaMemcpyAsync(d_h.p + (size_t)h->rank * sizeof mine, &mine, sizeof mine, cudaMemcpyHostToDevice, s));
+    NK(nccl_api().AllGather(d_h.p + (size_t)h->rank * sizeof mine, d_h.p, sizeof mine, ncclChar, h->comm, s));
+    std::vector<Card> all(h->nranks);
+    CK(cudaMemcpyAsync(all.data(), d_h.p, all.size() * sizeof mine, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    // ranks that share a GPU must not wait for each other inside kernels: NCCL path for them
+    for (int a = 0; a < h->nranks; ++a)
+        for (int b = a + 1; b < h->nranks; ++b)
+            if (memcmp(all[a].uuid, all[b].uuid, 16) == 0) good = 0;
+    for (int r = 0; r < h->nranks && good; ++r) {
+        if (r == h->rank) { h->peer_ptr[r] = h->xbuf.p; continue; }
+        void* p = nullptr;
+        if (cudaIpcOpenMemHandle(&p, all[r].mem, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); good = 0; break; }
+        h->peer_ptr[r] = static_cast<double*>(p);
+    }
+    // consensus: everybody or nobody
+    DBuf<double> d_flag;
+    d_flag.alloc(1);
+    const double mine_ok = good ? 1.0 : 0.0;
+    double all_ok = 0.0;
+    CK(cudaMemcpyAsync(d_flag.p, &mine_ok, sizeof(double), cudaMemcpyHostToDevice, s));
+    NK(nccl_api().AllReduce(d_flag.p, d_flag.p, 1, ncclDouble, ncclMin, h->comm, s));
+    CK(cudaMemcpyAsync(&all_ok, d_flag.p, sizeof(double), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    h->peer_ok = all_ok > 0.5;
+    if (h->peer_ok) CK(cudaMemcpyAsync(h->d_peers.p, h->peer_ptr.data(), h->nranks * sizeof(double*), cudaMemcpyHostToDevice, s));
+    CK(cudaStreamSynchronize(s));
 }
 
 static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy, int n_cams, int n_pts, int n_obs,
@@ -796,6 +869,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     P.rows = h->rows.p;
     h->st.zero(s);
     CK(cudaStreamSynchronize(s));  // the sort scratch buffers die at scope exit
+    setup_peer_exchange(h, n_cams);
     tm.mark("finish");
     h->have_problem = true;
 }
@@ -894,8 +968,8 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     const int nc1 = P.n_cams + 1;
     if (opt->schur_path != BA_PATH_TILES && opt->schur_path != BA_PATH_TWO_PASS) fail(BA_ERR_ARG, "unknown schur_path %d", opt->schur_path);
     const bool tiles = opt->schur_path == BA_PATH_TILES && h->fused_ok;
-    // the PCG iterations of a solve are replayed from a CUDA graph (single GPU, no per-kernel event timing)
-    const bool use_graph = h->nranks == 1 && !h->time_kernels && check_every > 1;
+    // the PCG iterations of a solve are replayed from a CUDA graph (no NCCL call inside, no per-kernel event timing)
+    const bool use_graph = (h->nranks == 1 || (h->peer_ok && tiles)) && !h->time_kernels && check_every > 1;
     cudaGraphExec_t pcg_graph = nullptr;
     long long graph_launches[KN_COUNT] = {0};
 
@@ -926,7 +1000,10 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
                 int n_dots = P.vec_ctas;
                 if (tiles) {
                     launch(h, KN_TILE_MV, k_tile_pass<0>, h->ft_grid, FT_THREADS, ft_smem_bytes(FT_ROWS_MV), P, (const double*)h->v_u.p);
-                    if (h->nranks > 1) {
+                    if (h->nranks > 1 && h->peer_ok) {  // exchange through peer memory, fused into both neighbours
+                        launch(h, KN_ROWS_XCHG, k_rows_finish_xchg, cdiv(P.n_cams, RS_WARPS), RS_WARPS * 32, 0, P, h->xbuf.p, h->xcap, h->xstate.p);
+                        launch(h, KN_DOTS_PEER, k_pcg_dots_peer, P.vec_ctas, VEC_THREADS, 0, P, (double* const*)h->d_peers.p, h->nranks, h->xcap, h->xstate.p);
+                    } else if (h->nranks > 1) {
                         launch(h, KN_ROWS_FIN, k_rows_finish<true>, cdiv(P.n_cams, RS_WARPS), RS_WARPS * 32, 0, P);
                         allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 6);
                         launch(h, KN_PCG_DOTS, k_pcg_dots<false>, P.vec_ctas, VEC_THREADS, 0, P);
@@ -996,6 +1073,12 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     }
     if (opt->max_iters == 0) read_state(h);
     if (pcg_graph) CK(cudaGraphExecDestroy(pcg_graph));
+    if (h->nranks > 1 && h->peer_ok) {
+        int xs[4] = {0, 0, 0, 0};
+        CK(cudaMemcpyAsync(xs, h->xstate.p, sizeof xs, cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+        if (xs[2]) fail(BA_ERR_NCCL, "peer-memory exchange timed out waiting for another rank");
+    }
     CK(cudaEventRecord(h->ev_solve1, s));
     CK(cudaEventSynchronize(h->ev_solve1));
     float ms = 0.f;
