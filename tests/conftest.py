@@ -23,7 +23,29 @@ def _built_library():
 
 
 def golden_names():
-    return sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz"))
+    """Window fixtures (one reference ``run`` each); recordings of whole pipelines are named pipeline_*."""
+    return sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz") and not f.startswith("pipeline_"))
+
+
+def recorded_map(g, k, which="before"):
+    """Map of call k of a pipeline recording (``oracle/gen_pipeline_golden.py``), rebuilt from the repo's
+    own map classes.  which = "before" (what ``run`` was given) or "after" (what the reference left)."""
+    from bundle_adjustment_b200.map_structures import Keyframe, KeyPoint, Map, MapPoint
+    pre = f"c{k}_"
+    out = "" if which == "before" else "out_"
+    gmap = Map()
+    kf_ids = g[pre + "kf_ids"].tolist()
+    obs_kf, obs_mp, obs_kp, obs_uv = (g[pre + n] for n in ("obs_kf", "obs_mp", "obs_kp", "obs_uv"))
+    for i, kid in enumerate(kf_ids):
+        rows = np.nonzero(obs_kf == kid)[0]
+        kps = [None] * int(g[pre + "kf_nkp"][i])
+        for r in rows:
+            kps[int(obs_kp[r])] = KeyPoint((float(obs_uv[r, 0]), float(obs_uv[r, 1])))
+        gmap.add_keyframe(Keyframe(id=kid, R=g[pre + out + "kf_R"][i].copy(), t=g[pre + out + "kf_t"][i].copy(), keypoints=kps,
+                                   observations=[(int(obs_mp[r]), int(obs_kp[r])) for r in rows]))
+    for i, mid in enumerate(g[pre + "mp_ids"].tolist()):
+        gmap.add_map_point(MapPoint(id=mid, position=g[pre + out + "mp_pos"][i].copy()))
+    return gmap
 
 
 def load_golden(name):

@@ -102,3 +102,54 @@ def test_global_ba_call_pattern_and_divergence_guard(tmp_path):
     assert "LBA Diverged!" in out.getvalue() and "Discarding results." in out.getvalue()
     for k, kf in gmap2.keyframes.items():
         assert np.array_equal(kf.R, before_kf[k][0]) and np.array_equal(kf.t, before_kf[k][1])
+
+
+# ---------------------------------------------------------------------------------------------------
+# the maps the UNMODIFIED reference pipeline handed to its bundle adjuster on real frames
+# (tests/golden/pipeline_desk.npz, recorded by oracle/gen_pipeline_golden.py), replayed call by call
+# ---------------------------------------------------------------------------------------------------
+def _huber_of(gmap, window_size, K):
+    flat = O.flatten_window(gmap, window_size)
+    prob = O.Problem(K[0, 0], K[1, 1], K[0, 2], K[1, 2], len(flat["adj_kf_ids"]), len(flat["mp_ids"]),
+                     flat["fixed_rvec"], flat["fixed_tvec"], flat["obs_cam"], flat["obs_pt"], flat["obs_uv"])
+    x = np.concatenate([flat["rvec"].ravel(), flat["tvec"].ravel(), flat["pts"].ravel()])
+    r = prob.residuals(x)
+    return O.huber_cost(r), O.raw_cost(r)
+
+
+def test_replay_of_the_reference_pipeline_calls():
+    from conftest import GOLDEN_DIR, recorded_map
+    import os
+    g = np.load(os.path.join(GOLDEN_DIR, "pipeline_desk.npz"))
+    K = g["camera_matrix"]
+    adj = BundleAdjuster(K, window_size=int(g["ba_window_size"]))        # src/pipeline.py:39
+    n_solved = 0
+    for k in range(int(g["n_calls"])):
+        ref_lines = [str(s) for s in g[f"c{k}_lines"]]
+        gmap = recorded_map(g, k)
+        adj.window_size = int(g[f"c{k}_window_size"])                    # src/main.py:83-86 mutates the attribute
+        out = io.StringIO()
+        with redirect_stdout(out):
+            assert adj.run(gmap) is None
+        text = out.getvalue()
+        ref_skipped = [ln for ln in ref_lines if "Skipped" in ln]
+        if ref_skipped:
+            assert ref_skipped[0].strip() in text                        # same skip, same words
+            assert adj.last_stats is None
+            continue
+        ref_m = LOG_RE.search("\n".join(ref_lines))
+        m = LOG_RE.search(text)
+        assert ref_m and m, (ref_lines, text)
+        ref_ini, ini, fin = float(ref_m.group(1)), float(m.group(1)), float(m.group(2))
+        assert abs(ini - ref_ini) <= 0.011 + 1e-9 * ref_ini              # same map, same raw cost at the start
+        assert fin < ini
+        # same objective (Huber, 1 px): the device solve ends at or below what the reference's call reached
+        ws = int(g[f"c{k}_window_size"])
+        ref_huber, _ = _huber_of(recorded_map(g, k, "after"), ws, K)
+        mine_huber, mine_raw = _huber_of(gmap, ws, K)
+        st = adj.last_stats
+        assert abs(mine_huber - st["final_cost"]) <= 1e-8 * st["final_cost"]
+        assert abs(mine_raw - fin) <= 0.011 + 1e-8 * mine_raw
+        assert mine_huber <= ref_huber * (1.0 + 1e-6), (k, mine_huber, ref_huber)
+        n_solved += 1
+    assert n_solved >= 3

@@ -141,3 +141,40 @@ def test_partition_points_balanced_and_complete():
             assert sh.obs_pt.min() >= 0 and sh.obs_pt.max() < sh.n_pts
             total += sh.n_obs
         assert total == fp.n_obs
+
+
+def test_injected_into_the_unmodified_reference_pipeline(tmp_path, monkeypatch, capsys):
+    """SURVEY 8f-1 on the CPU side: the reference's VisualOdometryPipeline constructs and calls the drop-in
+    class exactly as it does its own (src/pipeline.py:39, :99).  Real frames (desk_images) through the
+    unmodified front end; the two calls made before five keyframes exist are skips, which need no device;
+    the global-BA call of src/main.py:81-87 reaches the device library, which has no CPU path and must say so."""
+    from oracle.reference_loader import load_reference, reference_available
+    if not reference_available():
+        pytest.skip("reference sources are not on this machine (GPU box)")
+    cv2 = pytest.importorskip("cv2")
+    import bundle_adjustment_b200
+    from bundle_adjustment_b200 import _capi, bundle_adjuster as mine
+    load_reference()
+    import features, parameters, pipeline
+    monkeypatch.setattr(pipeline, "BundleAdjuster", mine.BundleAdjuster)
+    monkeypatch.chdir(tmp_path)
+    for d in [parameters.OUTPUT_DIR, parameters.TRAJECTORY_DIR_2D, parameters.TRAJECTORY_DIR_3D, *parameters.DEBUG_DIRS.values()]:
+        os.makedirs(d, exist_ok=True)
+    K = np.array([[912.7820434570312, 0.0, 650.2929077148438], [0.0, 913.0294189453125, 362.7241516113281], [0.0, 0.0, 1.0]])
+    crit = {"min_pixel_displacement": 20.0, "min_rotation": 0.15, "min_feature_ratio": 0.25, "min_parallax_deg": 1.0,
+            "min_tracked_for_parallax": 20}
+    vo = pipeline.VisualOdometryPipeline(camera_matrix=K, dist_coeffs=np.zeros(5), feature_extractor=features.ORBExtractor(n_features=4000),
+                                         feature_matcher=features.BruteForceMatcher(), keyframe_criteria=crit)
+    assert isinstance(vo.bundle_adjuster, mine.BundleAdjuster)
+    assert vo.bundle_adjuster.window_size == parameters.BA_WINDOW_SIZE and vo.bundle_adjuster.camera_matrix is K
+    for n in (11, 22, 33):
+        vo.process_frame(cv2.imread(f"/root/reference/desk_images/image{n}.png"))
+    text = capsys.readouterr().out
+    assert vo.map.next_keyframe_id == 3 and len(vo.map.map_points) > 100
+    assert text.count("--- Running Local Bundle Adjustment ---") == 2
+    assert text.count("-> LBA Skipped: Not enough keyframes.") == 2
+    import torch
+    if not torch.cuda.is_available():
+        vo.bundle_adjuster.window_size = vo.map.next_keyframe_id
+        with pytest.raises(_capi.BaError, match="no CPU path"):
+            vo.bundle_adjuster.run(vo.map)
