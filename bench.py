@@ -147,16 +147,19 @@ def run_reference(args, rank):
     print(json.dumps(line))
 
 
-def algorithmic_bytes(kernel, n_obs, n_obs_adj, n_pts, n_cams, n_seg=0):
+def algorithmic_bytes(kernel, n_obs, n_obs_adj, n_pts, n_cams, n_seg=0, n_rows=None):
     """Bytes one launch must move.  Tile passes stream the Jacobian cache (48 B) and the
     observation record (8 B) per observation; two-pass / linearisation kernels recompute from the 24 B
     (point-major) or 20 B (camera-major) observation record.  Each point / camera record is counted once."""
-    if kernel == "schur_matvec_tiles":       # per point X (32) + Vinv (48) + track offset (4); camera vector; one 48 B row
-        return 56 * n_obs + 84 * n_pts + 48 * (n_cams + 1) + (48 + 8) * n_seg   # + 8 B table entry per segment
+    n_rows = n_seg if n_rows is None else n_rows
+    if kernel == "schur_matvec_tiles":       # per point X (32) + Vinv (48) + track offset (4); camera vector; 8 B table entry
+        return 56 * n_obs + 84 * n_pts + 48 * (n_cams + 1) + 8 * n_seg + 48 * n_rows   # per segment; one 48 B row per accumulator slot
+    if kernel == "pcg_tail":                 # rows read; u, p, s, x, r, D, w streamed once or twice; Minv (288 B per camera)
+        return 48 * n_rows + (48 * 12 + 288) * n_cams
     if kernel == "backsub_tiles":            # + h, g, D read (32 each), X_trial written (32)
         return 56 * n_obs + (84 + 96 + 32) * n_pts + 48 * (n_cams + 1)
     if kernel == "rows_finish":
-        return 48 * n_seg + 144 * n_cams
+        return 48 * n_rows + 144 * n_cams
     if kernel == "schur_matvec_points":      # uv+idx; per point X (32) + Vinv (48) read, z (32) written; camera R|t|vec
         return 24 * n_obs + 112 * n_pts + 144 * (n_cams + 1)
     if kernel == "schur_matvec_cameras":     # uv+pt; per point X (32) + z (32) read; camera R|t|vec; 6-double partial per tile
@@ -272,12 +275,13 @@ def run_ours(args, rank, world, local_rank):
     st_p = solver.solve(verbose=2, **{**opts, "pcg_check_every": 1})
     ks = solver.kernel_stats()
     total_kernel_ms = sum(v[1] for v in ks.values())
-    top = max((k for k in ks if algorithmic_bytes(k, 1, 1, 1, 1, 1) is not None), key=lambda k: ks[k][1])
+    top = max((k for k in ks if algorithmic_bytes(k, 1, 1, 1, 1, 1, 1) is not None), key=lambda k: ks[k][1])
     n_obs_adj = int((fp.obs_cam >= 0).sum())
     layout = solver.layout_info()
     n_seg = layout["segments"]
     peak, peak_src = peaks()
-    ab = algorithmic_bytes(top, fp.n_obs, n_obs_adj, fp.n_pts, fp.n_cams, n_seg)
+    n_rows = layout["matvec_rows"]
+    ab = algorithmic_bytes(top, fp.n_obs, n_obs_adj, fp.n_pts, fp.n_cams, n_seg, n_rows)
     avg_ms = ks[top][1] / max(ks[top][0], 1)
     achieved = ab / (avg_ms * 1e-3) / 1e9
     traffic = None
@@ -290,7 +294,7 @@ def run_ours(args, rank, world, local_rank):
                 "launches_per_solve": ks[top][0], "share_of_kernel_time": ks[top][1] / max(total_kernel_ms, 1e-9),
                 "peak_source": peak_src, "layout": layout,
                 "kernels": {k: {"launches": v[0], "ms": round(v[1], 3),
-                                "GBps": (algorithmic_bytes(k, fp.n_obs, n_obs_adj, fp.n_pts, fp.n_cams, n_seg) or 0) * v[0] / max(v[1], 1e-9) / 1e6}
+                                "GBps": (algorithmic_bytes(k, fp.n_obs, n_obs_adj, fp.n_pts, fp.n_cams, n_seg, n_rows) or 0) * v[0] / max(v[1], 1e-9) / 1e6}
                             for k, v in ks.items() if v[0] and v[1] > 0.0}}
 
     if rank != 0:

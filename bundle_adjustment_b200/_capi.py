@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(_HERE, "libba_b200.so")
 
 ROBUST = {"none": 0, "irls": 1, "triggs": 2}
 PRECOND = {"jacobi": 0, "schur_jacobi": 1}
-SCHUR_PATH = {"tiles": 0, "two_pass": 1}
+SCHUR_PATH = {"tiles": 0, "two_pass": 1, "tiles_rows": 2}
 STATUS_TEXT = {0: "iteration limit", 1: "gtol", 2: "ftol", 3: "xtol", 4: "ftol and xtol", 5: "damping limit"}
 
 
@@ -31,7 +31,8 @@ class Options(C.Structure):
                 ("huber_delta", C.c_double), ("robust_mode", C.c_int32), ("initial_lambda", C.c_double),
                 ("lambda_min", C.c_double), ("lambda_max", C.c_double), ("precond", C.c_int32),
                 ("pcg_max_iters", C.c_int32), ("pcg_tol", C.c_double), ("pcg_check_every", C.c_int32),
-                ("verbose", C.c_int32), ("schur_path", C.c_int32), ("reserved", C.c_int32 * 6)]
+                ("verbose", C.c_int32), ("schur_path", C.c_int32), ("pcg_tail", C.c_int32),
+                ("reserved", C.c_int32 * 5)]
 
 
 class Stats(C.Structure):

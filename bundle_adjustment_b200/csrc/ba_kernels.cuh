@@ -138,9 +138,15 @@ struct Params {
                               // planes (jx0, jx1), (jx2, jy0), (jy1, jy2), tile-camera order
     const int* seg_cam;       // [n_seg]
     const int* seg_info;      // [n_seg] first tile-camera position inside the tile | length << 16 (longest first per tile)
-    const int* seg_row;       // [n_seg] row slot of a segment (camera-major)
+    const int* seg_row;       // [n_seg] row slot of a segment (camera-major); accumulator slot inside its epoch when ep_target > 0
     const int* cam_row_off;   // [n_cams+2]
     double* rows;             // [n_seg*6]
+    // epoch accumulators (ba_tiles.cuh): a CTA adds the segment sums of ep_len consecutive tiles in shared memory and
+    // writes one row per (epoch, camera, split) instead of one per segment
+    int ep_target;            // tiles per epoch aimed at (0 = one row per segment)
+    const int* cta_ep0;       // [grid] first epoch of a CTA
+    const int* ep_g0;         // [epochs+1 (+2 slack)] first accumulator slot (= row) of an epoch
+    const int* slot_row;      // [slots] row of an accumulator slot (rows are camera-major)
     // partial sums
     double* cm_partial;  // [cm_tiles*27]
     double* pm_partial;  // [n_partial_rows*NSCAL]

@@ -24,6 +24,8 @@
 #pragma once
 #include "ba_tiles.cuh"
 
+#include <cooperative_groups.h>
+
 namespace ba {
 
 constexpr int XB_HDR = 16;                 // doubles reserved in front of the payloads (flags, padding to 128 B)
@@ -118,6 +120,169 @@ __global__ void __launch_bounds__(VEC_THREADS) k_pcg_dots_peer(Params P, double*
     }
     const double cs = cta_sum_vec(part, sm);
     if (threadIdx.x == 0) P.dot_partial[2 * blockIdx.x] = cs;
+}
+
+// ---------------------------------------------------------------------------------------------
+// The TAIL of a PCG iteration in one kernel: everything between two tile passes.
+//
+//   rows (one per accumulator slot / segment)  ->  per-camera sums  [-> exchange with the other GPUs]
+//   -> w = sum + lambda D u,  delta = w.u  ->  alpha, beta  ->  p, s, x, r  ->  u = Minv r,  gamma = r.u
+//   -> PCG state (iteration count, convergence flag)
+//
+// One thread-block CLUSTER (8 or 16 CTAs on neighbouring SMs) does all of it: the two inner products need a
+// barrier across all cameras, and a cluster has one in hardware (barrier.cluster) plus distributed shared
+// memory for the partial sums - no second and third kernel launch, no ticket, and the camera vectors of the
+// iteration stay in shared memory between the two halves.  Each CTA owns a contiguous chunk of cameras.
+// All sums have a fixed order (lane order, warp order, CTA rank order, GPU rank order): bit-reproducible,
+// and identical on every GPU of a multi-GPU run.
+//
+// PEER: the per-camera sums of this GPU go to its exchange slot (see above), the cluster publishes the slot,
+// waits for the flags of all ranks and adds the ranks' partials in rank order.
+// ---------------------------------------------------------------------------------------------
+namespace cg = cooperative_groups;
+constexpr int PT_THREADS = 1024;
+constexpr int PT_MAX_CLUSTER = 16;
+__host__ __device__ inline size_t pt_smem_bytes(int n_cams, int cluster) {
+    const int chunk = (n_cams + cluster - 1) / cluster;
+    return (size_t)chunk * 6 * 2 * sizeof(double);
+}
+
+template <bool PEER>
+__global__ void __launch_bounds__(PT_THREADS, 1) k_pcg_tail(Params P, double tol, int max_iters, double* __restrict__ xbuf,
+                                                            double* const* __restrict__ peers, int nranks, int cap,
+                                                            int* __restrict__ xstate) {
+    extern __shared__ __align__(16) double dsm[];
+    __shared__ double part_d[PT_MAX_CLUSTER];  // delta partials of all CTAs (every CTA gets all of them)
+    __shared__ double part_g[PT_MAX_CLUSTER];  // gamma partials (CTA 0 only)
+    __shared__ double red[33];
+    __shared__ int ok;
+    LMState* st = P.st;
+    if (st->pcg_done) return;  // same value in every CTA: it is only written after the last cluster barrier
+    cg::cluster_group cl = cg::this_cluster();
+    const int R = (int)cl.block_rank(), CL = (int)cl.num_blocks();
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int chunk = (P.n_cams + CL - 1) / CL;
+    const int c0 = min(R * chunk, P.n_cams), c1 = min(c0 + chunk, P.n_cams);
+    const int n_el = (c1 - c0) * 6;
+    double* sW = dsm;              // [chunk*6] mat-vec result of the chunk, later s
+    double* sR = dsm + chunk * 6;  // [chunk*6] new residual of the chunk
+    const double gamma = st->gamma, alpha_prev = st->alpha, gamma_prev = st->gamma_prev, lam = st->lambda;
+    const int first = (st->pcg_iter == 0);
+    const long long seq = PEER ? (long long)xstate[0] + 1 : 0;
+    const size_t slot_off = PEER ? XB_HDR + (size_t)(seq & 1) * cap : 0;
+
+    // ---- per-camera sums of this GPU's rows (camera-major, so a chunk's rows are one contiguous range):
+    //      a group of `lpc` lanes per camera, all cameras of the chunk side by side --------------------------
+    {
+        int lpc = 32;  // largest power of two with chunk * lpc <= PT_THREADS
+        while (lpc > 1 && chunk * lpc > PT_THREADS) lpc >>= 1;
+        const int li = tid & (lpc - 1);
+        const int gpw = 32 / lpc;  // groups (cameras) per warp
+        for (int cb = c0 + wid * gpw; cb < c1; cb += (PT_THREADS / 32) * gpw) {  // warp-uniform; one trip unless chunk > PT_THREADS
+            const int c = cb + lane / lpc;
+            const bool valid = c < c1;
+            const int r0 = valid ? __ldg(P.cam_row_off + c) : 0, r1 = valid ? __ldg(P.cam_row_off + c + 1) : 0;
+            double a[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+            for (int r = r0 + li; r < r1; r += 2 * lpc) {  // two rows in flight per lane
+                const double2* q = reinterpret_cast<const double2*>(P.rows + (size_t)r * 6);
+                const bool two = r + lpc < r1;
+                const double2 v0 = q[0], v1 = q[1], v2 = q[2];
+                const double2 z = make_double2(0.0, 0.0);
+                const double2 w0 = two ? q[3 * lpc] : z, w1 = two ? q[3 * lpc + 1] : z, w2 = two ? q[3 * lpc + 2] : z;
+                a[0] += v0.x; a[1] += v0.y; a[2] += v1.x; a[3] += v1.y; a[4] += v2.x; a[5] += v2.y;
+                a[0] += w0.x; a[1] += w0.y; a[2] += w1.x; a[3] += w1.y; a[4] += w2.x; a[5] += w2.y;
+            }
+            for (int d = lpc >> 1; d > 0; d >>= 1)  // fixed order inside the group
+#pragma unroll
+                for (int k = 0; k < 6; ++k) a[k] += __shfl_down_sync(0xffffffffu, a[k], d, 32);
+            if (li == 0 && valid) {
+                double2* o = reinterpret_cast<double2*>(PEER ? xbuf + slot_off + (size_t)c * 6 : sW + (size_t)(c - c0) * 6);
+                o[0] = make_double2(a[0], a[1]); o[1] = make_double2(a[2], a[3]); o[2] = make_double2(a[4], a[5]);
+            }
+        }
+    }
+    if (PEER) {
+        __threadfence_system();  // this thread's part of the slot, before the cluster says "complete"
+        cl.sync();
+        if (R == 0 && tid == 0) {
+            xstate[0] = (int)seq;
+            st_release_sys(reinterpret_cast<long long*>(xbuf) + (seq & 1), seq);  // publish
+        }
+        if (tid == 0) {
+            int good = 1;
+            for (int r = 0; r < nranks && good; ++r) {
+                const long long* flag = reinterpret_cast<const long long*>(peers[r]) + (seq & 1);
+                long long spins = 0;
+                while (ld_acquire_sys(flag) < seq)
+                    if (++spins > XB_SPIN_LIMIT) { good = 0; break; }
+            }
+            if (!good) atomicExch(xstate + 2, 1);
+            ok = good;
+        }
+    }
+    __syncthreads();
+
+    // ---- w = sum (+ the other ranks' sums, rank order) + lambda D u;  delta = w.u -------------------------
+    double part = 0.0;
+    for (int e = tid; e < n_el; e += PT_THREADS) {
+        const size_t i = (size_t)c0 * 6 + e;
+        double w = 0.0;
+        if (PEER) {
+            if (ok)
+                for (int r = 0; r < nranks; ++r) w += __ldcv(peers[r] + slot_off + i);
+        } else {
+            w = sW[e];
+        }
+        const double u = P.v_u[i];
+        w += lam * P.cam_D[i] * u;
+        sW[e] = w;
+        part += w * u;
+    }
+    const double dpart = cta_sum_all(part, red);
+    if (tid < CL) cl.map_shared_rank(part_d, tid)[R] = dpart;  // my partial into every CTA's table
+    cl.sync();
+    double delta = 0.0;
+    for (int r = 0; r < CL; ++r) delta += part_d[r];
+    const double beta = first ? 0.0 : gamma / gamma_prev;
+    const double den = first ? delta : delta - beta * gamma / alpha_prev;
+    const double alpha = (den > 0.0) ? gamma / den : 0.0;
+
+    // ---- p = u + beta p,  s = w + beta s,  x += alpha p,  r -= alpha s ------------------------------------
+    for (int e = tid; e < n_el; e += PT_THREADS) {
+        const size_t i = (size_t)c0 * 6 + e;
+        const double p = P.v_u[i] + beta * P.v_p[i];
+        const double sv = sW[e] + beta * P.v_s[i];
+        P.v_p[i] = p; P.v_s[i] = sv;
+        P.v_x[i] += alpha * p;
+        const double r = P.v_r[i] - alpha * sv;
+        P.v_r[i] = r;
+        sR[e] = r;
+    }
+    __syncthreads();
+    // ---- u = Minv r (6x6 block per camera),  gamma = r.u ---------------------------------------------------
+    part = 0.0;
+    for (int e = tid; e < n_el; e += PT_THREADS) {
+        const int cl_ = e / 6, k = e - 6 * cl_;
+        const double* M = P.cam_Minv + ((size_t)(c0 + cl_) * 36 + 6 * k);
+        const double* r = sR + 6 * cl_;
+        double u = 0.0;
+#pragma unroll
+        for (int j = 0; j < 6; ++j) u += __ldg(M + j) * r[j];
+        P.v_u[(size_t)c0 * 6 + e] = u;
+        part += sR[e] * u;
+    }
+    const double gpart = cta_sum_all(part, red);
+    if (tid == 0) cl.map_shared_rank(part_g, 0)[R] = gpart;
+    cl.sync();
+    if (R == 0 && tid == 0) {
+        double g = 0.0;
+        for (int r = 0; r < CL; ++r) g += part_g[r];
+        st->gamma_prev = gamma;
+        st->gamma = g; st->alpha = alpha; st->beta = beta;
+        const int it = st->pcg_iter + 1;
+        st->pcg_iter = it; st->pcg_total += 1;
+        if (!(alpha > 0.0) || !(g > tol * tol * st->gamma0) || it >= max_iters) st->pcg_done = 1;
+    }
 }
 
 }  // namespace ba

@@ -119,19 +119,54 @@ struct DBuf {
     }
 };
 
+// Scratch buffer of one call: comes from the device's stream-ordered memory pool (kept warm: the pool's release
+// threshold is raised in create_common), so per-call scratch costs microseconds instead of a cudaMalloc /
+// cudaFree pair (each a device-wide synchronisation).  Used on ONE stream, the one current when it is allocated.
+static thread_local cudaStream_t g_scratch_stream = nullptr;
+struct ScratchScope {
+    cudaStream_t prev;
+    explicit ScratchScope(cudaStream_t s) : prev(g_scratch_stream) { g_scratch_stream = s; }
+    ~ScratchScope() { g_scratch_stream = prev; }
+};
+template <class T>
+struct TBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    cudaStream_t s = nullptr;
+    TBuf() = default;
+    TBuf(const TBuf&) = delete;
+    TBuf& operator=(const TBuf&) = delete;
+    ~TBuf() { release(); }
+    void release() {
+        if (p) cudaFreeAsync(p, s);
+        p = nullptr;
+        n = 0;
+    }
+    void alloc(size_t count) {
+        if (count <= n && p) return;
+        release();
+        s = g_scratch_stream;
+        if (count) CK(cudaMallocAsync(&p, count * sizeof(T), s));
+        n = count;
+    }
+    void zero(cudaStream_t st) {
+        if (p) CK(cudaMemsetAsync(p, 0, n * sizeof(T), st));
+    }
+};
+
 // ---------------------------------------------------------------------------------------------
 // kernel kinds (accounting)
 // ---------------------------------------------------------------------------------------------
 enum Kind {
     KN_SETUP = 0, KN_CAM_PREP, KN_RESID, KN_JAC, KN_LIN_PTS, KN_PT_PREP, KN_PT_PASS, KN_BACKSUB, KN_LIN_CAM,
     KN_SCHUR_CAM, KN_MATVEC_CAM, KN_CAM_SUM, KN_CAM_FIN, KN_PCG_DOTS, KN_PCG_UPDATE, KN_CAM_UPDATE, KN_REDUCE,
-    KN_GRAD, KN_DECIDE, KN_TILE_MV, KN_TILE_BACKSUB, KN_ROWS_FIN, KN_ROWS_XCHG, KN_DOTS_PEER, KN_COUNT
+    KN_GRAD, KN_DECIDE, KN_TILE_MV, KN_TILE_BACKSUB, KN_ROWS_FIN, KN_ROWS_XCHG, KN_DOTS_PEER, KN_PCG_TAIL, KN_COUNT
 };
 static const char* kKindNames[KN_COUNT] = {
     "setup", "cam_prepare", "residuals", "jacobian_blocks", "lin_points", "point_prepare", "schur_matvec_points",
     "backsub_points", "lin_cameras", "schur_rhs_cameras", "schur_matvec_cameras", "camera_sum", "camera_finish",
     "pcg_dots", "pcg_update", "camera_update", "reduce_scalars", "gradient_check", "lm_decide",
-    "schur_matvec_tiles", "backsub_tiles", "rows_finish", "rows_finish_xchg", "pcg_dots_peer"};
+    "schur_matvec_tiles", "backsub_tiles", "rows_finish", "rows_finish_xchg", "pcg_dots_peer", "pcg_tail"};
 
 // ---------------------------------------------------------------------------------------------
 // setup kernels (device-side construction of the two observation orders)
@@ -360,6 +395,13 @@ struct ba_handle {
     DBuf<int> pt_perm;  // internal (locality-ordered) point id -> caller's point index
     // fused point tiles
     bool fused_ok = false;
+    // epoch accumulators of the mat-vec tile pass (ba_tiles.cuh); acc_ok = every epoch fits FT_ACC_CAP slots
+    bool acc_ok = false;
+    int tail_cluster = 0;  // CTAs of the PCG tail cluster (ba_peer.cuh); 0 = tail kernel not usable for this problem
+    int tail_cached = 0;   // last answer of the (slow) cluster occupancy query and the shared-memory size it holds for
+    size_t tail_cached_bytes = 0;
+    int ep_target = 0, n_epochs = 0, n_slots = 0, max_ep_slots = 0;
+    DBuf<int> seg_slot, slot_row, ep_g0, cta_ep0, cam_row_off2;
     int ft_tiles = 0, n_seg = 0, ft_grid = 0, sm_count = 0;
     std::vector<int> ft_pt_h, ft_obs_h, ft_maxlen_h;  // host copy of the tile cuts and longest tracks (empty: no tiles)
     DBuf<int> ft_pt, ft_obs, ft_seg, ft_rs, seg_cam, seg_info, seg_row, cam_row_off;
@@ -430,6 +472,34 @@ static void launch(ba_handle* h, Kind kind, void (*kernel)(KArgs...), int grid, 
     }
 }
 
+// one thread-block cluster of `cluster` CTAs
+template <class... KArgs, class... Args>
+static void launch_cluster(ba_handle* h, Kind kind, void (*kernel)(KArgs...), int cluster, int block, size_t smem, Args... args) {
+    int e0 = -1, e1 = -1;
+    if (h->time_kernels) {
+        e0 = (int)h->stamps.size() * 2;
+        e1 = e0 + 1;
+        while ((int)h->ev_pool.size() <= e1) {
+            cudaEvent_t e;
+            CK(cudaEventCreate(&e));
+            h->ev_pool.push_back(e);
+        }
+        CK(cudaEventRecord(h->ev_pool[e0], h->stream));
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(cluster); cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = smem; cfg.stream = h->stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    CK(cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...));
+    h->launches[kind] += 1;
+    if (h->time_kernels) {
+        CK(cudaEventRecord(h->ev_pool[e1], h->stream));
+        h->stamps.push_back({(int)kind, e0, e1});
+    }
+}
+
 // resolve the pooled per-launch events into per-kind milliseconds (after the stream has drained)
 static void resolve_stamps(ba_handle* h) {
     for (const auto& st : h->stamps) {
@@ -465,6 +535,12 @@ static void create_common(ba_handle* h, int device) {
     if (prop.major < 10)
         fail(BA_ERR_CUDA, "device %d is sm_%d%d; libba_b200 is built for sm_100a only", device, prop.major, prop.minor);
     h->sm_count = prop.multiProcessorCount;
+    {
+        cudaMemPool_t pool;
+        CK(cudaDeviceGetDefaultMemPool(&pool, device));
+        unsigned long long keep = ~0ULL;  // freed scratch stays in the pool for the next call
+        CK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    }
     CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     CK(cudaMallocHost(&h->h_state, sizeof(LMState)));
     CK(cudaMallocHost(&h->h_flag, sizeof(int)));
@@ -509,6 +585,7 @@ struct MaxOp {
 // sequence on the host (one pass over the track offsets), everything per-observation on the device.
 static void build_tiles(ba_handle* h, int n_cams, int n_pts, int n_obs) {
     cudaStream_t s = h->stream;
+    ScratchScope scratch(s);
     const int B = 256;
     h->fused_ok = false;
     h->ft_tiles = 0; h->n_seg = 0;
@@ -520,9 +597,9 @@ static void build_tiles(ba_handle* h, int n_cams, int n_pts, int n_obs) {
     CK(cudaMemcpyAsync(h->ft_obs.p, to.data(), to.size() * sizeof(int), cudaMemcpyHostToDevice, s));
 
     // tile-camera order: stable sort of the point-major indices by (tile, camera)
-    DBuf<unsigned long long> key, key_s;
-    DBuf<int> ia, ib, ic;
-    key.alloc(n_obs); key_s.alloc(n_obs); ia.alloc(n_obs); ib.alloc(n_obs); ic.alloc(n_obs);
+    TBuf<unsigned long long> key, key_s;
+    TBuf<int> ia, ib, ic, id;
+    key.alloc(n_obs); key_s.alloc(n_obs); ia.alloc(n_obs); ib.alloc(n_obs); ic.alloc(n_obs); id.alloc(n_obs);
     launch(h, KN_SETUP, k_ft_keys, cdiv(n_obs, B), B, 0, n_obs, T, (const int*)h->ft_obs.p, (const int2*)h->pm_idx.p, key.p, ia.p);
     int tile_bits = 1;
     while ((1LL << tile_bits) < T) ++tile_bits;
@@ -530,14 +607,14 @@ static void build_tiles(ba_handle* h, int n_cams, int n_pts, int n_obs) {
     CK(cub::DeviceRadixSort::SortPairs(nullptr, tb_sort, key.p, key_s.p, ia.p, ib.p, n_obs, 0, 32 + tile_bits, s));
     CK(cub::DeviceScan::InclusiveScan(nullptr, tb_max, ia.p, ic.p, MaxOp(), n_obs, s));
     CK(cub::DeviceScan::InclusiveSum(nullptr, tb_sum, ia.p, ic.p, n_obs, s));
-    DBuf<unsigned char> tmp;
+    TBuf<unsigned char> tmp;
     tmp.alloc(std::max(std::max(tb_sort, tb_max), tb_sum));
     size_t tb = tmp.n;
     CK(cub::DeviceRadixSort::SortPairs(tmp.p, tb, key.p, key_s.p, ia.p, ib.p, n_obs, 0, 32 + tile_bits, s));  // ib = source index
     launch(h, KN_SETUP, k_ft_run_heads, cdiv(n_obs, B), B, 0, n_obs, (const unsigned long long*)key_s.p, ia.p);
     tb = tmp.n;
-    CK(cub::DeviceScan::InclusiveScan(tmp.p, tb, ia.p, ic.p, MaxOp(), n_obs, s));                             // ic = run start
-    launch(h, KN_SETUP, k_ft_seg_flags, cdiv(n_obs, B), B, 0, n_obs, (const int*)ic.p, ia.p);               // ia = segment head flag
+    CK(cub::DeviceScan::InclusiveScan(tmp.p, tb, ia.p, id.p, MaxOp(), n_obs, s));                             // id = run start
+    launch(h, KN_SETUP, k_ft_seg_flags, cdiv(n_obs, B), B, 0, n_obs, (const int*)id.p, ia.p);               // ia = segment head flag
     tb = tmp.n;
     CK(cub::DeviceScan::InclusiveSum(tmp.p, tb, ia.p, ic.p, n_obs, s));                                      // ic = segment id + 1
     h->launches[KN_SETUP] += 3;
@@ -553,8 +630,9 @@ static void build_tiles(ba_handle* h, int n_cams, int n_pts, int n_obs) {
     // track-row tables of the transposed point-side layout: one per tile, padded to 16 bytes
     std::vector<int> rs0((size_t)T + 1, 0);
     for (int t = 0; t < T; ++t) rs0[t + 1] = rs0[t] + ((h->ft_maxlen_h[t] + 3) & ~3);
-    DBuf<int> d_rs0, d_maxlen, seg_start, seg_cam0;
+    TBuf<int> d_rs0, d_maxlen, seg_start, seg_cam0, seg_split0, seg_tile, seg_split;
     d_rs0.alloc((size_t)T + 1); d_maxlen.alloc(T); seg_start.alloc((size_t)S + 1); seg_cam0.alloc(S);
+    seg_split0.alloc(S); seg_tile.alloc(S); seg_split.alloc(S);
     h->ft_rs.alloc((size_t)rs0[T] + 4);
     h->ft_rs.zero(s);
     CK(cudaMemcpyAsync(d_rs0.p, rs0.data(), rs0.size() * sizeof(int), cudaMemcpyHostToDevice, s));
@@ -566,12 +644,12 @@ static void build_tiles(ba_handle* h, int n_cams, int n_pts, int n_obs) {
     launch(h, KN_SETUP, k_ft_fill, cdiv(n_obs, B), B, 0, n_obs, (const unsigned long long*)key_s.p, (const int*)ib.p,
            (const int*)ia.p, (const int*)ic.p, (const int*)h->ft_pt.p, (const int*)h->pt_off.p, (const int*)d_rs0.p,
            (const int*)h->ft_rs.p, (const double2*)h->pm_uv.p, (const int2*)h->pm_idx.p, h->tc_uv.p, h->tc_meta.p, h->pm_tc.p,
-           seg_cam0.p, seg_start.p);
+           seg_cam0.p, seg_start.p, (const int*)id.p, seg_split0.p);
     launch(h, KN_SETUP, k_ft_headers, cdiv(T, B), B, 0, T, (const int*)h->ft_pt.p, (const int*)h->ft_obs.p, (const int*)h->ft_seg.p,
            (const int*)d_rs0.p, (const int*)d_maxlen.p, h->ft_hdr.p);
     // segments longest first inside each tile, then rows camera-major (stable sort of the segments by camera)
-    DBuf<unsigned> skey, skey_s;
-    DBuf<int> sidx, sidx_s;
+    TBuf<unsigned> skey, skey_s;
+    TBuf<int> sidx, sidx_s;
     skey.alloc(S); skey_s.alloc(S); sidx.alloc(S); sidx_s.alloc(S);
     int cam_bits = 1;
     while ((1LL << cam_bits) < (long long)n_cams + 1) ++cam_bits;
@@ -581,7 +659,8 @@ static void build_tiles(ba_handle* h, int n_cams, int n_pts, int n_obs) {
     tb = tmp.n;
     CK(cub::DeviceRadixSort::SortPairs(tmp.p, tb, skey.p, skey_s.p, sidx.p, sidx_s.p, S, 0, std::min(32, 5 + tile_bits), s));
     launch(h, KN_SETUP, k_ft_seg_apply, cdiv(S, B), B, 0, S, (const unsigned*)skey_s.p, (const int*)sidx_s.p, (const int*)seg_start.p,
-           (const int*)seg_cam0.p, (const int*)h->ft_obs.p, h->seg_info.p, h->seg_cam.p, skey.p, sidx.p);
+           (const int*)seg_cam0.p, (const int*)h->ft_obs.p, h->seg_info.p, h->seg_cam.p, skey.p, sidx.p, (const int*)seg_split0.p,
+           seg_tile.p, seg_split.p);
     tb = tmp.n;
     CK(cub::DeviceRadixSort::SortPairs(tmp.p, tb, skey.p, skey_s.p, sidx.p, sidx_s.p, S, 0, cam_bits, s));
     h->launches[KN_SETUP] += 2;
@@ -589,10 +668,120 @@ static void build_tiles(ba_handle* h, int n_cams, int n_pts, int n_obs) {
     launch(h, KN_SETUP, k_lower_bound_u32, cdiv(n_cams + 2, B), B, 0, S, (const unsigned*)skey_s.p, n_cams + 2, h->cam_row_off.p);
     CK(cudaFuncSetAttribute(k_tile_pass<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ft_smem_bytes(FT_ROWS_MV)));
     CK(cudaFuncSetAttribute(k_tile_pass<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ft_smem_bytes(FT_ROWS_MV)));
-    CK(cudaStreamSynchronize(s));  // scratch dies here
+    CK(cudaFuncSetAttribute(k_tile_pass<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ft_smem_bytes(FT_ROWS_MV, true)));
     h->ft_tiles = T; h->n_seg = S;
     h->ft_grid = std::min(T, FT_CTAS_PER_SM * h->sm_count);  // persistent CTAs
+    if (const char* g = getenv("BA_B200_TILE_GRID"))           // test hook: few CTAs, so that small problems have long tile runs
+        h->ft_grid = std::max(1, std::min(h->ft_grid, atoi(g)));
+
+    // ---- epoch accumulators: slots = distinct (epoch, camera, split) of the segments; rows = slots, camera-major ----
+    h->acc_ok = false; h->n_slots = 0; h->n_epochs = 0; h->max_ep_slots = 0; h->ep_target = 0;
+    if (S > 0 && !getenv("BA_B200_NO_EPOCHS")) {
+        const int G = h->ft_grid;
+        TBuf<unsigned long long> k64, k64_s;
+        TBuf<int> sord, sord_s, sinc, d_ep_ts;
+        TBuf<unsigned> scam, scam_s;
+        k64.alloc(S); k64_s.alloc(S); sord.alloc(S); sord_s.alloc(S); sinc.alloc(S); scam.alloc(S); scam_s.alloc(S);
+        h->seg_slot.alloc((size_t)S + 4); h->slot_row.alloc(S); h->cam_row_off2.alloc((size_t)n_cams + 2); h->cta_ep0.alloc(G);
+        size_t tb64 = 0, tbs = 0;
+        CK(cub::DeviceRadixSort::SortPairs(nullptr, tb64, k64.p, k64_s.p, sord.p, sord_s.p, S, 0, 40 + tile_bits, s));
+        CK(cub::DeviceScan::InclusiveSum(nullptr, tbs, sord.p, sinc.p, S, s));
+        if (std::max(tb64, tbs) > tmp.n) { CK(cudaStreamSynchronize(s)); tmp.alloc(std::max(tb64, tbs)); }
+        for (int target = 32; target >= 1 && !h->acc_ok; target /= 2) {
+            std::vector<int> ep_ts, cta_ep0(G);
+            for (int b = 0; b < G; ++b) {
+                const int t0 = ft_cta_begin(b, T, G), t1 = ft_cta_begin(b + 1, T, G);
+                cta_ep0[b] = (int)ep_ts.size();
+                if (t1 <= t0) continue;
+                const int el = ft_epoch_len(t1 - t0, target);
+                for (int t = t0; t < t1; t += el) ep_ts.push_back(t);
+            }
+            const int E = (int)ep_ts.size();
+            d_ep_ts.alloc(E); h->ep_g0.alloc((size_t)E + 3); h->ep_g0.zero(s);
+            CK(cudaMemcpyAsync(d_ep_ts.p, ep_ts.data(), (size_t)E * sizeof(int), cudaMemcpyHostToDevice, s));
+            CK(cudaMemcpyAsync(h->cta_ep0.p, cta_ep0.data(), (size_t)G * sizeof(int), cudaMemcpyHostToDevice, s));
+            launch(h, KN_SETUP, k_ft_slot_keys, cdiv(S, B), B, 0, S, T, G, target, (const int*)seg_tile.p, (const int*)h->seg_cam.p,
+                   (const int*)seg_split.p, k64.p, sord.p);
+            tb = tmp.n;
+            CK(cub::DeviceRadixSort::SortPairs(tmp.p, tb, k64.p, k64_s.p, sord.p, sord_s.p, S, 0, 40 + tile_bits, s));
+            launch(h, KN_SETUP, k_ft_slot_heads, cdiv(S, B), B, 0, S, (const unsigned long long*)k64_s.p, sord.p);
+            tb = tmp.n;
+            CK(cub::DeviceScan::InclusiveSum(tmp.p, tb, sord.p, sinc.p, S, s));
+            int R = 0;
+            CK(cudaMemcpyAsync(&R, sinc.p + S - 1, sizeof(int), cudaMemcpyDeviceToHost, s));
+            CK(cudaStreamSynchronize(s));
+            launch(h, KN_SETUP, k_ft_epoch_base, cdiv(E + 1, B), B, 0, E, S, R, (const int*)d_ep_ts.p, (const unsigned long long*)k64_s.p,
+                   (const int*)sinc.p, h->ep_g0.p);
+            std::vector<int> g0((size_t)E + 1);
+            CK(cudaMemcpyAsync(g0.data(), h->ep_g0.p, g0.size() * sizeof(int), cudaMemcpyDeviceToHost, s));
+            CK(cudaStreamSynchronize(s));
+            int mx = 0;
+            for (int e = 0; e < E; ++e) mx = std::max(mx, g0[e + 1] - g0[e]);
+            h->max_ep_slots = mx; h->n_slots = R; h->n_epochs = E; h->ep_target = target;
+            if (getenv("BA_B200_TRACE"))
+                fprintf(stderr, "[ba_b200] epochs of %d tiles: %d epochs, %d slots, at most %d per epoch (capacity %d)\n", target, E, R, mx, FT_ACC_CAP);
+            if (mx > FT_ACC_CAP) continue;
+            launch(h, KN_SETUP, k_ft_slot_assign, cdiv(S, B), B, 0, S, E, (const unsigned long long*)k64_s.p, (const int*)sord_s.p,
+                   (const int*)sinc.p, (const int*)d_ep_ts.p, (const int*)h->ep_g0.p, h->seg_slot.p, scam.p, sord.p);
+            // rows of the slots, camera-major: stable sort of the slot numbers by camera
+            tb = tmp.n;
+            CK(cub::DeviceRadixSort::SortPairs(tmp.p, tb, scam.p, scam_s.p, sord.p, sinc.p, R, 0, cam_bits, s));
+            launch(h, KN_SETUP, k_ft_seg_rows, cdiv(R, B), B, 0, R, (const int*)sinc.p, h->slot_row.p);
+            launch(h, KN_SETUP, k_lower_bound_u32, cdiv(n_cams + 2, B), B, 0, R, (const unsigned*)scam_s.p, n_cams + 2, h->cam_row_off2.p);
+            h->acc_ok = true;
+        }
+    }
+    CK(cudaStreamSynchronize(s));  // scratch dies here
     h->fused_ok = true;
+    // PCG tail: the largest cluster (16, 8, ... CTAs of 1024 threads) this device can co-schedule with the chunk in shared memory
+    h->tail_cluster = 0;
+    if (n_cams > 0 && !getenv("BA_B200_NO_TAIL")) {
+        if (h->tail_cached > 0 && pt_smem_bytes(n_cams, h->tail_cached) <= h->tail_cached_bytes) h->tail_cluster = h->tail_cached;
+        for (int cl = PT_MAX_CLUSTER; cl >= 1 && !h->tail_cluster; cl /= 2) {
+            const size_t bytes = (pt_smem_bytes(n_cams, cl) + 16383) & ~(size_t)16383;  // a size class, so the answer can be reused
+            if (bytes > 208 * 1024) break;
+            bool good = true;
+            for (int peer = 0; peer < 2 && good; ++peer) {
+                const void* fn = peer ? (const void*)k_pcg_tail<true> : (const void*)k_pcg_tail<false>;
+                good = cudaFuncSetAttribute(fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess &&
+                       cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(bytes, (size_t)1024)) == cudaSuccess;
+                if (!good) break;
+                cudaLaunchConfig_t cfg = {};
+                cfg.gridDim = dim3(cl); cfg.blockDim = dim3(PT_THREADS); cfg.dynamicSmemBytes = bytes;
+                cudaLaunchAttribute at[1];
+                at[0].id = cudaLaunchAttributeClusterDimension;
+                at[0].val.clusterDim.x = cl; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+                cfg.attrs = at; cfg.numAttrs = 1;
+                int n = 0;
+                good = cudaOccupancyMaxActiveClusters(&n, fn, &cfg) == cudaSuccess && n >= 1;
+            }
+            cudaGetLastError();
+            if (good) { h->tail_cluster = cl; h->tail_cached = cl; h->tail_cached_bytes = bytes; }
+        }
+    }
+    if (getenv("BA_B200_TRACE")) {
+        fprintf(stderr, "[ba_b200] PCG tail cluster: %d CTAs\n", h->tail_cluster);
+        int o0 = 0, o1 = 0, o2 = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o0, k_tile_pass<0, false>, FT_THREADS, ft_smem_bytes(FT_ROWS_MV));
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, k_tile_pass<0, true>, FT_THREADS, ft_smem_bytes(FT_ROWS_MV, true));
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, k_tile_pass<1, false>, FT_THREADS, ft_smem_bytes(FT_ROWS_MV));
+        fprintf(stderr, "[ba_b200] tile pass CTAs/SM: mat-vec %d, mat-vec with accumulators %d, back-substitution %d; grid %d, %d tiles, "
+                "%d segments, %d slots in %d epochs (max %d per epoch)\n", o0, o1, o2, h->ft_grid, T, S, h->n_slots, h->n_epochs, h->max_ep_slots);
+    }
+}
+
+// Parameter block of the mat-vec tile pass and its row finish: per-segment rows, or epoch accumulator slots
+static Params matvec_params(const ba_handle* h, bool acc) {
+    Params Q = h->P;
+    if (acc) {
+        Q.seg_row = h->seg_slot.p; Q.cam_row_off = h->cam_row_off2.p; Q.ep_target = h->ep_target;
+        Q.cta_ep0 = h->cta_ep0.p; Q.ep_g0 = h->ep_g0.p; Q.slot_row = h->slot_row.p;
+    }
+    return Q;
+}
+static void launch_tile_matvec(ba_handle* h, const Params& Q, bool acc, const double* vec) {
+    if (acc) launch(h, KN_TILE_MV, k_tile_pass<0, true>, h->ft_grid, FT_THREADS, ft_smem_bytes(FT_ROWS_MV, true), Q, vec);
+    else launch(h, KN_TILE_MV, k_tile_pass<0, false>, h->ft_grid, FT_THREADS, ft_smem_bytes(FT_ROWS_MV), Q, vec);
 }
 
 // Map every rank's exchange buffer into this process (collective: all ranks call it with the same n_cams).
@@ -602,6 +791,7 @@ static void setup_peer_exchange(ba_handle* h, int n_cams) {
     const int need = ((std::max(n_cams, 1) * 6 + 15) / 16) * 16;
     if (h->xcap >= need) return;  // same decision on every rank: cameras are replicated
     cudaStream_t s = h->stream;
+    ScratchScope scratch(s);
     CK(cudaStreamSynchronize(s));
     for (size_t r = 0; r < h->peer_ptr.size(); ++r)
         if (h->peer_ptr[r] && (int)r != h->rank) cudaIpcCloseMemHandle(h->peer_ptr[r]);
@@ -625,7 +815,7 @@ static void setup_peer_exchange(ba_handle* h, int n_cams) {
         CK(cudaGetDeviceProperties(&prop, dev));
         memcpy(mine.uuid, prop.uuid.bytes, 16);
     }
-    DBuf<unsigned char> d_h;
+    TBuf<unsigned char> d_h;
     d_h.alloc((size_t)h->nranks * sizeof mine);
     CK(cudaMemcpyAsync(d_h.p + (size_t)h->rank * sizeof mine, &mine, sizeof mine, cudaMemcpyHostToDevice, s));
     NK(nccl_api().AllGather(d_h.p + (size_t)h->rank * sizeof mine, d_h.p, sizeof mine, ncclChar, h->comm, s));
@@ -643,7 +833,7 @@ static void setup_peer_exchange(ba_handle* h, int n_cams) {
         h->peer_ptr[r] = static_cast<double*>(p);
     }
     // consensus: everybody or nobody
-    DBuf<double> d_flag;
+    TBuf<double> d_flag;
     d_flag.alloc(1);
     const double mine_ok = good ? 1.0 : 0.0;
     double all_ok = 0.0;
@@ -664,6 +854,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     if (!frv || !ftv || !pts || !obs_cam || !obs_pt || !obs_uv || (n_cams > 0 && (!rvec || !tvec)))
         fail(BA_ERR_ARG, "null array argument");
     cudaStream_t s = h->stream;
+    ScratchScope scratch(s);
     h->have_problem = false;
     const size_t nc1 = (size_t)n_cams + 1;
     StageTimer tm(s);
@@ -689,9 +880,9 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     h->cam_tile_off.alloc(nc1);
 
     // ---- upload -------------------------------------------------------------------------------
-    DBuf<int> d_cam, d_pt, d_iota, d_perm, d_err, d_camoff;
-    DBuf<unsigned> d_kpt, d_kpt_s;
-    DBuf<unsigned long long> d_kcam, d_kcam_s;
+    TBuf<int> d_cam, d_pt, d_iota, d_perm, d_err, d_camoff;
+    TBuf<unsigned> d_kpt, d_kpt_s;
+    TBuf<unsigned long long> d_kcam, d_kcam_s;
     d_cam.alloc(n_obs); d_pt.alloc(n_obs); d_iota.alloc(n_obs); d_perm.alloc(n_obs); d_err.alloc(2);
     d_kpt.alloc(n_obs); d_kpt_s.alloc(n_obs); d_kcam.alloc(n_obs); d_kcam_s.alloc(n_obs); d_camoff.alloc(nc1 + 1);
     d_err.zero(s);
@@ -716,15 +907,15 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, d_kpt.p, d_kpt_s.p, d_iota.p, d_perm.p, n_obs, 0, pt_bits, s));
     CK(cub::DeviceRadixSort::SortPairs(nullptr, tb2, d_kcam.p, d_kcam_s.p, d_iota.p, d_perm.p, n_obs, 0, 32 + cam_bits, s));
     CK(cub::DeviceRadixSort::SortPairs(nullptr, tb3, d_kpt.p, d_kpt_s.p, d_iota.p, d_perm.p, n_pts, 0, 32, s));
-    DBuf<unsigned char> d_tmp;
+    TBuf<unsigned char> d_tmp;
     d_tmp.alloc(std::max(std::max(tmp_bytes, tb2), tb3));
 
     // ---- locality order of the points: stable sort by camera centroid ----------------------------
     h->pt_perm.alloc(n_pts);
     {
-        DBuf<unsigned long long> d_sum;
-        DBuf<unsigned> d_cnt, d_key, d_key_s;
-        DBuf<int> d_pi;
+        TBuf<unsigned long long> d_sum;
+        TBuf<unsigned> d_cnt, d_key, d_key_s;
+        TBuf<int> d_pi;
         d_sum.alloc(n_pts); d_cnt.alloc(n_pts); d_key.alloc(n_pts); d_key_s.alloc(n_pts); d_pi.alloc(n_pts);
         d_sum.zero(s); d_cnt.zero(s);
         launch(h, KN_SETUP, k_point_cam_sums, cdiv(n_obs, B), B, 0, n_obs, n_cams, n_pts, (const int*)d_cam.p,
@@ -737,7 +928,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
         // tile cuts: greedy on the host over the track offsets of this order (<= FT_THREADS observations and
         // <= FT_PTS points per tile); then the points of each tile are re-ordered by track length
         {
-            DBuf<int> d_len, d_off;
+            TBuf<int> d_len, d_off;
             d_len.alloc((size_t)n_pts + 1); d_off.alloc((size_t)n_pts + 1);
             launch(h, KN_SETUP, k_gather_counts, cdiv(n_pts + 1, B), B, 0, n_pts, (const int*)h->pt_perm.p, (const unsigned*)d_cnt.p, d_len.p);
             size_t tbs = 0;
@@ -764,7 +955,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
             if (!fits) { h->ft_pt_h.clear(); h->ft_obs_h.clear(); h->ft_maxlen_h.clear(); }
             if (fits) {
                 const int T = (int)h->ft_pt_h.size() - 1;
-                DBuf<int> d_tp, d_perm2;
+                TBuf<int> d_tp, d_perm2;
                 d_tp.alloc(h->ft_pt_h.size()); d_perm2.alloc(n_pts);
                 CK(cudaMemcpyAsync(d_tp.p, h->ft_pt_h.data(), h->ft_pt_h.size() * sizeof(int), cudaMemcpyHostToDevice, s));
                 launch(h, KN_SETUP, k_point_tile_keys, cdiv(n_pts, B), B, 0, n_pts, T, (const int*)d_tp.p, (const int*)d_len.p, d_key.p);
@@ -867,6 +1058,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     P.tc_J = h->fused_ok ? h->tc_J.p : nullptr;
     P.seg_cam = h->seg_cam.p; P.seg_info = h->seg_info.p; P.ft_rs = h->ft_rs.p; P.seg_row = h->seg_row.p; P.cam_row_off = h->cam_row_off.p;
     P.rows = h->rows.p;
+    P.ep_target = 0; P.cta_ep0 = nullptr; P.ep_g0 = nullptr; P.slot_row = nullptr;
     h->st.zero(s);
     CK(cudaStreamSynchronize(s));  // the sort scratch buffers die at scope exit
     setup_peer_exchange(h, n_cams);
@@ -966,8 +1158,11 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     const int check_every = std::max(1, opt->pcg_check_every);
     const int with_schur = opt->precond == BA_PRECOND_SCHUR_JACOBI ? 1 : 0;
     const int nc1 = P.n_cams + 1;
-    if (opt->schur_path != BA_PATH_TILES && opt->schur_path != BA_PATH_TWO_PASS) fail(BA_ERR_ARG, "unknown schur_path %d", opt->schur_path);
-    const bool tiles = opt->schur_path == BA_PATH_TILES && h->fused_ok;
+    if (opt->schur_path < BA_PATH_TILES || opt->schur_path > BA_PATH_TILES_ROWS) fail(BA_ERR_ARG, "unknown schur_path %d", opt->schur_path);
+    const bool tiles = opt->schur_path != BA_PATH_TWO_PASS && h->fused_ok;
+    const bool acc = tiles && opt->schur_path == BA_PATH_TILES && h->acc_ok;
+    const Params PA = matvec_params(h, acc);  // what the mat-vec tile pass and its row finish see
+    const bool tail = tiles && h->tail_cluster > 0 && (h->nranks == 1 || h->peer_ok) && opt->pcg_tail != 0;
     // the PCG iterations of a solve are replayed from a CUDA graph (no NCCL call inside, no per-kernel event timing)
     const bool use_graph = (h->nranks == 1 || (h->peer_ok && tiles)) && !h->time_kernels && check_every > 1;
     cudaGraphExec_t pcg_graph = nullptr;
@@ -998,18 +1193,29 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
             launch(h, KN_CAM_FIN, k_camera_finish_schur, P.vec_ctas, VEC_THREADS, 0, P, with_schur, h->ticket.p);
             auto pcg_iteration = [&]() {
                 int n_dots = P.vec_ctas;
+                if (tiles && tail) {  // two kernels per iteration: the tile pass, then everything else in one cluster
+                    launch_tile_matvec(h, PA, acc, h->v_u.p);
+                    const size_t bytes = pt_smem_bytes(P.n_cams, h->tail_cluster);
+                    if (h->nranks > 1)
+                        launch_cluster(h, KN_PCG_TAIL, k_pcg_tail<true>, h->tail_cluster, PT_THREADS, bytes, PA, opt->pcg_tol, opt->pcg_max_iters,
+                                       h->xbuf.p, (double* const*)h->d_peers.p, h->nranks, h->xcap, h->xstate.p);
+                    else
+                        launch_cluster(h, KN_PCG_TAIL, k_pcg_tail<false>, h->tail_cluster, PT_THREADS, bytes, PA, opt->pcg_tol, opt->pcg_max_iters,
+                                       (double*)nullptr, (double* const*)nullptr, 1, 0, (int*)nullptr);
+                    return;
+                }
                 if (tiles) {
-                    launch(h, KN_TILE_MV, k_tile_pass<0>, h->ft_grid, FT_THREADS, ft_smem_bytes(FT_ROWS_MV), P, (const double*)h->v_u.p);
+                    launch_tile_matvec(h, PA, acc, h->v_u.p);
                     if (h->nranks > 1 && h->peer_ok) {  // exchange through peer memory, fused into both neighbours
-                        launch(h, KN_ROWS_XCHG, k_rows_finish_xchg, cdiv(P.n_cams, RS_WARPS), RS_WARPS * 32, 0, P, h->xbuf.p, h->xcap, h->xstate.p);
+                        launch(h, KN_ROWS_XCHG, k_rows_finish_xchg, cdiv(P.n_cams, RS_WARPS), RS_WARPS * 32, 0, PA, h->xbuf.p, h->xcap, h->xstate.p);
                         launch(h, KN_DOTS_PEER, k_pcg_dots_peer, P.vec_ctas, VEC_THREADS, 0, P, (double* const*)h->d_peers.p, h->nranks, h->xcap, h->xstate.p);
                     } else if (h->nranks > 1) {
-                        launch(h, KN_ROWS_FIN, k_rows_finish<true>, cdiv(P.n_cams, RS_WARPS), RS_WARPS * 32, 0, P);
+                        launch(h, KN_ROWS_FIN, k_rows_finish<true>, cdiv(P.n_cams, RS_WARPS), RS_WARPS * 32, 0, PA);
                         allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 6);
                         launch(h, KN_PCG_DOTS, k_pcg_dots<false>, P.vec_ctas, VEC_THREADS, 0, P);
                     } else {
                         n_dots = cdiv(P.n_cams, RS_WARPS);
-                        launch(h, KN_ROWS_FIN, k_rows_finish<false>, n_dots, RS_WARPS * 32, 0, P);
+                        launch(h, KN_ROWS_FIN, k_rows_finish<false>, n_dots, RS_WARPS * 32, 0, PA);
                     }
                 } else {
                     launch(h, KN_PT_PASS, k_point_pass<0>, P.pm_tiles, PM_THREADS, h->smem_pass, P, (const double*)h->v_u.p);
@@ -1133,6 +1339,7 @@ void ba_default_options(ba_options* o) {
     o->pcg_max_iters = 100; o->pcg_tol = 0.1; o->pcg_check_every = 8;
     o->verbose = 0;
     o->schur_path = BA_PATH_TILES;
+    o->pcg_tail = 1;
 }
 
 int ba_create(int device, ba_handle** out) {
@@ -1407,7 +1614,9 @@ int ba_schur_matvec(ba_handle* h, const ba_options* opt, double lambda, const do
     const ba::Params& P = h->P;
     cudaStream_t s = h->stream;
     if (P.n_cams == 0) return BA_OK;
-    const bool tiles = o.schur_path == BA_PATH_TILES && h->fused_ok;
+    const bool tiles = o.schur_path != BA_PATH_TWO_PASS && h->fused_ok;
+    const bool acc = tiles && o.schur_path == BA_PATH_TILES && h->acc_ok;
+    const ba::Params PA = ba::matvec_params(h, acc);
     ba::launch(h, ba::KN_SETUP, ba::k_init_state, 1, 1, 0, h->st.p, lambda);
     ba::launch(h, ba::KN_CAM_PREP, ba::k_cam_prepare, ba::cdiv(P.n_cams + 1, 256), 256, 0, P, 2);
     ba::lin_points_and_cost(h, 2);
@@ -1415,9 +1624,8 @@ int ba_schur_matvec(ba_handle* h, const ba_options* opt, double lambda, const do
     ba::launch(h, ba::KN_PT_PREP, ba::k_point_prepare, ba::cdiv(P.n_pts, 256), 256, 0, P, ba::kDiagMin, ba::kDiagMax);
     CK(cudaMemcpyAsync(h->v_u.p, u, (size_t)P.n_cams * 6 * sizeof(double), cudaMemcpyHostToDevice, s));
     if (tiles) {
-        ba::launch(h, ba::KN_TILE_MV, ba::k_tile_pass<0>, h->ft_grid, ba::FT_THREADS, ba::ft_smem_bytes(ba::FT_ROWS_MV), P,
-                   (const double*)h->v_u.p);
-        ba::launch(h, ba::KN_ROWS_FIN, ba::k_rows_finish<false>, ba::cdiv(P.n_cams, ba::RS_WARPS), ba::RS_WARPS * 32, 0, P);
+        ba::launch_tile_matvec(h, PA, acc, h->v_u.p);
+        ba::launch(h, ba::KN_ROWS_FIN, ba::k_rows_finish<false>, ba::cdiv(P.n_cams, ba::RS_WARPS), ba::RS_WARPS * 32, 0, PA);
     } else {
         ba::launch(h, ba::KN_PT_PASS, ba::k_point_pass<0>, P.pm_tiles, ba::PM_THREADS, h->smem_pass, P, (const double*)h->v_u.p);
         ba::launch(h, ba::KN_MATVEC_CAM, ba::k_camera_pass<2>, P.cm_tiles, ba::CM_THREADS, ba::cm_smem_bytes<2>(), P,
@@ -1437,13 +1645,15 @@ int ba_solve(ba_handle* h, const ba_options* opt, ba_stats* stats_out) {
     API_END
 }
 
-int ba_layout_info(ba_handle* h, int64_t out[8]) {
+int ba_layout_info(ba_handle* h, int64_t out[12]) {
     API_BEGIN
     ba::need_problem(h);
     if (!out) ba::fail(BA_ERR_ARG, "null output");
     const ba::Params& P = h->P;
-    const int64_t v[8] = {P.n_obs, P.n_obs_adj, P.n_pts, P.n_cams, h->fused_ok ? h->ft_tiles : 0, h->n_seg, P.pm_tiles, P.cm_tiles};
-    for (int k = 0; k < 8; ++k) out[k] = v[k];
+    const bool acc = h->fused_ok && h->acc_ok;
+    const int64_t v[12] = {P.n_obs, P.n_obs_adj, P.n_pts, P.n_cams, h->fused_ok ? h->ft_tiles : 0, h->n_seg, P.pm_tiles, P.cm_tiles,
+                           acc ? h->n_slots : h->n_seg, acc ? h->n_epochs : 0, h->max_ep_slots, acc ? h->ep_target : 0};
+    for (int k = 0; k < 12; ++k) out[k] = v[k];
     API_END
 }
 

@@ -39,6 +39,16 @@ constexpr int FT_LD = FT_THREADS + 2;  // row stride of the camera-side scratch 
 constexpr int FT_LDB = FT_THREADS + 4; // row stride of the point-side scratch (phases A/B): 2*FT_LDB mod 32 = 8 banks, so the
                                        // three rows read by the four points of a half-warp are disjoint
 constexpr int FT_ROWS_MV = 6;          // scratch rows of the mat-vec pass
+constexpr int FT_ACC_CAP = 72;         // accumulator slots (6 doubles + row number each) of an epoch; what is left of 228 KB / 4 CTAs
+
+// Tiles of persistent CTA b of a grid of G over T tiles, and the way a CTA cuts its run into EPOCHS of about
+// `target` tiles (equal lengths, the last one may be shorter).  Host and device use the same two functions.
+__host__ __device__ inline int ft_cta_begin(int b, int T, int G) { return (int)((long long)b * T / G); }
+__host__ __device__ inline int ft_cta_of_tile(int t, int T, int G) { return (int)((((long long)t + 1) * G - 1) / T); }
+__host__ __device__ inline int ft_epoch_len(int len, int target) {
+    const int ne = (len + target - 1) / target;
+    return ne > 0 ? (len + ne - 1) / ne : 1;
+}
 
 // dynamic shared memory of a tile pass (16-byte aligned regions): per-observation scratch rows | Jacobian
 // cache planes [3][FT_THREADS] double2 | observation records | X as planes (X0,X1)[FT_PTS], X2[FT_PTS+2] | z likewise | Vinv [FT_PTS][6] |
@@ -49,10 +59,12 @@ struct FtSmem {
     double* sO; double2* sJ; int2* sMeta; double2* sX01; double* sX2; double2* sZ01; double* sZ2; double* sVi;
     int* sOff; int* sRs; int* sSeg; int* sRow;
     unsigned long long* bar;
+    double* sAcc;  // [FT_ACC_CAP][6] epoch accumulators (only when the pass is instantiated with them)
+    int* sSlot;    // [FT_ACC_CAP] row of every slot of the current epoch
 };
-__host__ __device__ constexpr size_t ft_smem_bytes(int rows) {
+__host__ __device__ constexpr size_t ft_smem_bytes(int rows, bool acc = false) {
     return (size_t)(rows * FT_LD) * 8 + 3 * FT_THREADS * 16 + FT_META_N * 8 + (size_t)FT_PTS * (2 + 2 + 2 * 6) * 8 +
-           2 * (size_t)(FT_PTS + 2) * 8 + (size_t)(2 * FT_OFF_N + 6 * FT_SEG_N) * 4 + 16;
+           2 * (size_t)(FT_PTS + 2) * 8 + (size_t)(2 * FT_OFF_N + 6 * FT_SEG_N) * 4 + 16 + (acc ? FT_ACC_CAP * 52 : 0);
 }
 BA_D FtSmem ft_carve(double* sm, int rows) {
     FtSmem S;
@@ -69,6 +81,8 @@ BA_D FtSmem ft_carve(double* sm, int rows) {
     S.sSeg = S.sRs + 2 * FT_SEG_N;
     S.sRow = S.sSeg + 2 * FT_SEG_N;
     S.bar = reinterpret_cast<unsigned long long*>(S.sRow + 2 * FT_SEG_N);
+    S.sAcc = reinterpret_cast<double*>(S.bar + 2);
+    S.sSlot = reinterpret_cast<int*>(S.sAcc + FT_ACC_CAP * 6);
     return S;
 }
 
@@ -160,21 +174,29 @@ BA_D void ft_issue_group2(const Params& P, const FtSmem& S, const TileHdr& T, in
     if (rs_b) tma_load(S.sRs + buf * FT_SEG_N, P.ft_rs + T.r0, rs_b, bar);
 }
 
-template <int MODE>
+// ACC (mat-vec only): the segment sums of an EPOCH (a few consecutive tiles of the CTA) are added up in shared
+// memory, slot = (camera, split index) of the epoch, and leave ONE row per slot when the epoch ends - several
+// times fewer rows for k_rows_finish to read than one per segment.  Fixed order (tile by tile), no atomics.
+template <int MODE, bool ACC = false>
 __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params P, const double* __restrict__ vec) {
     extern __shared__ __align__(16) double sm[];
     __shared__ double red[FT_THREADS / 32 * 4];
     __shared__ double tot[4];
     __shared__ int hs[8];
+    __shared__ int es[4];  // [0] first tile of the CTA, [1] epoch length, [2] first epoch, [3] 6 x slots of the current epoch
     if (MODE == 0 && P.st->pcg_done) return;
     // contiguous run of tiles per CTA: neighbouring tiles share cameras, so the camera vectors stay in L1
-    int t = (int)((long long)blockIdx.x * P.ft_tiles / gridDim.x);
-    const int t_end = (int)((long long)(blockIdx.x + 1) * P.ft_tiles / gridDim.x);
+    int t = ft_cta_begin(blockIdx.x, P.ft_tiles, gridDim.x);
+    const int t_end = ft_cta_begin(blockIdx.x + 1, P.ft_tiles, gridDim.x);
     if (t >= t_end) return;
     const FtSmem S = ft_carve(sm, FT_ROWS_MV);
     const int b = P.st->cur;
     const int tid = threadIdx.x;
     TileHdr T = tile_hdr(P, t);
+    if (ACC) {
+        for (int l = tid; l < FT_ACC_CAP * 6; l += FT_THREADS) S.sAcc[l] = 0.0;
+        if (tid == 0) { es[0] = t; es[1] = ft_epoch_len(t_end - t, P.ep_target); es[2] = P.cta_ep0[blockIdx.x]; }
+    }
     if (tid == 0) {
         mbar_init(S.bar, 1);
         mbar_init(S.bar + 1, 1);
@@ -225,6 +247,14 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
         if (MODE == 0 && have_next && issuer) {
             ft_issue_group1<MODE>(P, S, Tn, b, buf ^ 1, S.bar);
             ft_issue_group2(P, S, Tn, buf ^ 1, S.bar + 1);
+        }
+        if (ACC && tid >= FT_THREADS - 32 && (t - es[0]) % es[1] == 0) {
+            // first tile of an epoch: the last warp (idle in phase B) fetches the rows of the epoch's slots; the
+            // previous epoch was flushed before the barrier above, this one is flushed after later barriers
+            const int ep = es[2] + (t - es[0]) / es[1];
+            const int g0 = __ldg(P.ep_g0 + ep), n = __ldg(P.ep_g0 + ep + 1) - g0;
+            for (int l = tid - (FT_THREADS - 32); l < n; l += 32) S.sSlot[l] = __ldg(P.slot_row + g0 + l);
+            if (issuer) es[3] = n * 6;
         }
 
         // ---- phase B: four lanes per point: lane k < 3 adds component k of the track in observation
@@ -315,6 +345,9 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
                 const int a = info & 0xffff, len = info >> 16;
                 const int wmax = __reduce_max_sync(0xffffffffu, len);
                 const double* src = S.sO + k * FT_LD + a;
+                // a slot occurs at most once per tile; its running sum is fetched ahead of the segment's loop
+                double* slot = ACC ? S.sAcc + (valid ? seg_r[seg] * 6 + k : 0) : nullptr;
+                const double before = (ACC && valid) ? *slot : 0.0;
                 double sum = 0.0;
                 for (int j0 = 0; j0 < wmax; j0 += 4) {
                     double v[4];
@@ -323,10 +356,26 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
 #pragma unroll
                     for (int j = 0; j < 4; ++j) sum += v[j];
                 }
-                if (valid) P.rows[(size_t)seg_r[seg] * 6 + k] = sum;
+                if (valid) {
+                    if (ACC) *slot = before + sum;
+                    else P.rows[(size_t)seg_r[seg] * 6 + k] = sum;
+                }
             }
         }
-        if (!have_next) break;
+        // end of an epoch: its slots become rows (camera-major, like the per-segment rows).  Every thread flushes and
+        // clears the same words; the next tile adds to them only after further barriers.
+        auto flush = [&]() {
+            const int n6 = es[3];
+            for (int l = tid; l < n6; l += FT_THREADS) {
+                const int slot = l / 6;
+                P.rows[(size_t)S.sSlot[slot] * 6 + (l - 6 * slot)] = S.sAcc[l];
+                S.sAcc[l] = 0.0;
+            }
+        };
+        if (!have_next) {
+            if (ACC) { __syncthreads(); flush(); }
+            break;
+        }
         // the next tile's header travels from the issuing thread to everybody through shared memory
         if (issuer) {
             hs[0] = Tn.p0; hs[1] = Tn.m; hs[2] = Tn.o0; hs[3] = Tn.n; hs[4] = Tn.s0; hs[5] = Tn.ns; hs[6] = Tn.r0; hs[7] = Tn.maxlen;
@@ -335,6 +384,7 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
         {
             T.p0 = hs[0]; T.m = hs[1]; T.o0 = hs[2]; T.n = hs[3]; T.s0 = hs[4]; T.ns = hs[5]; T.r0 = hs[6]; T.maxlen = hs[7];
         }
+        if (ACC && (t + 1 - es[0]) % es[1] == 0) flush();
         t = tn;
     }
 }
@@ -454,7 +504,7 @@ __global__ void k_ft_fill(int n_obs, const unsigned long long* __restrict__ key_
                           const int* __restrict__ pt_off, const int* __restrict__ rs0, const int* __restrict__ rs,
                           const double2* __restrict__ pm_uv, const int2* __restrict__ pm_idx, double2* __restrict__ tc_uv,
                           int2* __restrict__ tc_meta, int* __restrict__ pm_tc, int* __restrict__ seg_cam,
-                          int* __restrict__ seg_start) {
+                          int* __restrict__ seg_start, const int* __restrict__ run_start, int* __restrict__ seg_split) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_obs) return;
     const int j = src[i];
@@ -466,7 +516,7 @@ __global__ void k_ft_fill(int n_obs, const unsigned long long* __restrict__ key_
     tc_uv[i] = pm_uv[j];
     tc_meta[i] = make_int2(cam, (int)(pl | (pos << 10)));
     pm_tc[j] = i;
-    if (flag[i]) { seg_cam[s] = cam; seg_start[s] = i; }
+    if (flag[i]) { seg_cam[s] = cam; seg_start[s] = i; seg_split[s] = (i - run_start[i]) / FT_SEG_MAX; }
 }
 // Segments of a tile are renumbered longest first (so that the lanes that sum segments side by side run
 // equally long loops): sort key = (tile, FT_SEG_MAX - length).
@@ -486,7 +536,8 @@ __global__ void k_ft_seg_keys(int n_seg, int n_tiles, const int* __restrict__ se
 __global__ void k_ft_seg_apply(int n_seg, const unsigned* __restrict__ key_s, const int* __restrict__ order,
                                const int* __restrict__ seg_start, const int* __restrict__ seg_cam_in,
                                const int* __restrict__ ft_obs, int* __restrict__ seg_info, int* __restrict__ seg_cam,
-                               unsigned* __restrict__ cam_key, int* __restrict__ iota) {
+                               unsigned* __restrict__ cam_key, int* __restrict__ iota, const int* __restrict__ seg_split_in,
+                               int* __restrict__ seg_tile, int* __restrict__ seg_split) {
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n_seg) return;
     const int s = order[r], t = (int)(key_s[r] >> 5);
@@ -495,6 +546,8 @@ __global__ void k_ft_seg_apply(int n_seg, const unsigned* __restrict__ key_s, co
     seg_cam[r] = seg_cam_in[s];
     cam_key[r] = (unsigned)seg_cam_in[s];
     iota[r] = r;
+    seg_tile[r] = t;
+    seg_split[r] = seg_split_in[s];
 }
 __global__ void k_ft_headers(int n_tiles, const int* __restrict__ ft_pt, const int* __restrict__ ft_obs,
                              const int* __restrict__ ft_seg, const int* __restrict__ rs0, const int* __restrict__ maxlen,
@@ -507,6 +560,56 @@ __global__ void k_ft_headers(int n_tiles, const int* __restrict__ ft_pt, const i
 __global__ void k_ft_seg_rows(int n_seg, const int* __restrict__ sorted_seg, int* __restrict__ seg_row) {
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r < n_seg) seg_row[sorted_seg[r]] = r;
+}
+// ---- epoch accumulator slots ------------------------------------------------------------------------
+// key of segment r = (first tile of its epoch << 40) | (camera << 8) | split index of the segment in its run
+__global__ void k_ft_slot_keys(int n_seg, int n_tiles, int grid, int target, const int* __restrict__ seg_tile,
+                               const int* __restrict__ seg_cam, const int* __restrict__ seg_split,
+                               unsigned long long* __restrict__ key, int* __restrict__ iota) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n_seg) return;
+    const int t = seg_tile[r];
+    const int b = ft_cta_of_tile(t, n_tiles, grid);
+    const int t0 = ft_cta_begin(b, n_tiles, grid), t1 = ft_cta_begin(b + 1, n_tiles, grid);
+    const int el = ft_epoch_len(t1 - t0, target);
+    const int ts = t0 + ((t - t0) / el) * el;
+    key[r] = ((unsigned long long)ts << 40) | ((unsigned long long)(unsigned)seg_cam[r] << 8) | (unsigned)seg_split[r];
+    iota[r] = r;
+}
+__global__ void k_ft_slot_heads(int n_seg, const unsigned long long* __restrict__ key_s, int* __restrict__ head) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_seg) head[i] = (i == 0 || key_s[i] != key_s[i - 1]) ? 1 : 0;
+}
+// first slot of every epoch (ep_ts = first tile of the epoch, ascending; one extra entry = number of slots)
+__global__ void k_ft_epoch_base(int n_ep, int n_seg, int n_slots, const int* __restrict__ ep_ts,
+                                const unsigned long long* __restrict__ key_s, const int* __restrict__ slot_inc,
+                                int* __restrict__ ep_g0) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e > n_ep) return;
+    if (e == n_ep) { ep_g0[e] = n_slots; return; }
+    const unsigned long long want = (unsigned long long)ep_ts[e];
+    int lo = 0, hi = n_seg;  // first position whose epoch tile >= want
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if ((key_s[mid] >> 40) < want) lo = mid + 1; else hi = mid;
+    }
+    ep_g0[e] = lo < n_seg ? slot_inc[lo] - 1 : n_slots;
+}
+// local slot of every segment, camera of every slot
+__global__ void k_ft_slot_assign(int n_seg, int n_ep, const unsigned long long* __restrict__ key_s, const int* __restrict__ order,
+                                 const int* __restrict__ slot_inc, const int* __restrict__ ep_ts, const int* __restrict__ ep_g0,
+                                 int* __restrict__ seg_slot, unsigned* __restrict__ slot_cam, int* __restrict__ iota) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_seg) return;
+    const int g = slot_inc[i] - 1;
+    const int ts = (int)(key_s[i] >> 40);
+    int lo = 0, hi = n_ep;  // last epoch with ep_ts <= ts
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (ep_ts[mid] <= ts) lo = mid; else hi = mid;
+    }
+    seg_slot[order[i]] = g - ep_g0[lo];
+    if (i == 0 || key_s[i] != key_s[i - 1]) { slot_cam[g] = (unsigned)((key_s[i] >> 8) & 0xffffffffu); iota[g] = g; }
 }
 __global__ void k_iota(int n, int* __restrict__ out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;

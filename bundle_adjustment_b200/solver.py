@@ -183,9 +183,10 @@ class FlatSolver:
         return st.as_dict()
 
     def layout_info(self) -> Dict[str, int]:
-        out = np.zeros(8, dtype=np.int64)
+        out = np.zeros(12, dtype=np.int64)
         api.check(api.lib().ba_layout_info(self._h, api.lptr(out)))
-        keys = ("n_obs", "n_obs_adj", "n_pts", "n_cams", "point_tiles", "segments", "pm_windows", "cm_tiles")
+        keys = ("n_obs", "n_obs_adj", "n_pts", "n_cams", "point_tiles", "segments", "pm_windows", "cm_tiles", "matvec_rows",
+                "epochs", "max_epoch_slots", "epoch_tiles")
         return {k: int(v) for k, v in zip(keys, out)}
 
     def tile_layout(self) -> Dict[str, np.ndarray]:

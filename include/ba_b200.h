@@ -47,7 +47,9 @@ typedef struct ba_handle ba_handle;
 
 #define BA_PATH_TILES 0    /* fused point-tile passes: one kernel per Schur mat-vec          (default) */
 #define BA_PATH_TWO_PASS 1 /* point-major pass + camera-major pass (also used when a track is longer
-                              than one tile, 512 observations)                                       */
+                              than one tile, 256 observations)                                       */
+#define BA_PATH_TILES_ROWS 2 /* fused tiles writing one row per segment (no shared-memory epoch accumulators); also the
+                                automatic choice when an epoch of a problem needs more accumulator slots than fit */
 
 typedef struct ba_options {
     int32_t max_iters;        /* LM iterations, accepted + rejected (reference: max_nfev = 50)      */
@@ -64,7 +66,9 @@ typedef struct ba_options {
     int32_t pcg_check_every;  /* host polls the device "PCG converged" flag every this many iterations */
     int32_t verbose;          /* bit 0: one stderr line per LM iteration; >= 2: per-kernel event timing */
     int32_t schur_path;       /* BA_PATH_*                                                          */
-    int32_t reserved[6];
+    int32_t pcg_tail;         /* 1 (default): everything between two tile passes of a PCG iteration runs in ONE
+                                 thread-block-cluster kernel; 0: row finish / inner products / update kernels */
+    int32_t reserved[5];
 } ba_options;
 
 typedef struct ba_stats {
@@ -170,10 +174,12 @@ int ba_kernel_count(void);
 const char* ba_kernel_name(int k);
 int ba_kernel_stats(ba_handle* h, int64_t* launches /* [n] */, double* ms /* [n] */);
 
-/* Layout of the uploaded problem, for byte accounting: out[0..7] = n_obs, observations of adjustable
- * cameras, n_pts, n_adj_cams, point tiles, tile segments (= mat-vec rows), point-major windows,
- * camera-major tiles.  Point tiles = 0 when the fused path is unavailable (a track longer than a tile). */
-int ba_layout_info(ba_handle* h, int64_t out[8]);
+/* Layout of the uploaded problem, for byte accounting: out[0..11] = n_obs, observations of adjustable
+ * cameras, n_pts, n_adj_cams, point tiles, tile segments, point-major windows, camera-major tiles,
+ * mat-vec rows (= epoch accumulator slots, or = segments when the accumulators are not in use), epochs,
+ * largest number of slots of an epoch, tiles per epoch aimed at (0 = no accumulators).
+ * Point tiles = 0 when the fused path is unavailable (a track longer than a tile). */
+int ba_layout_info(ba_handle* h, int64_t out[12]);
 
 /* Test hook: copy out the point-tile structure built by ba_set_problem (sizes from ba_layout_info:
  * T = point tiles, S = segments).  ft_pt/ft_obs/ft_seg[T+1], tc_meta[n_obs*2] (camera slot, local point |

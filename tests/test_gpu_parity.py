@@ -145,11 +145,17 @@ def test_lm_iterates_match_cpu_restatement(gpu_solver):
     assert np.abs(gpu_solver.get_x() - ref.x()).max() <= 1e-8
 
 
-@pytest.mark.parametrize("path", ["tiles", "two_pass"])
+@pytest.mark.parametrize("grid", [None, 2, 3])
+@pytest.mark.parametrize("path", ["tiles", "tiles_rows", "two_pass"])
 @pytest.mark.parametrize("shape,seed", [((6, 300, 1200), 3), ((25, 900, 4000), 5)])
-def test_schur_matvec_against_dense_schur_complement(gpu_solver, path, shape, seed):
-    """One implicit Schur mat-vec of the device (either kernel path) == the dense reduced camera matrix of
-    the CPU restatement times the same vector."""
+def test_schur_matvec_against_dense_schur_complement(gpu_solver, monkeypatch, path, shape, seed, grid):
+    """One implicit Schur mat-vec of the device (every kernel path) == the dense reduced camera matrix of
+    the CPU restatement times the same vector.  grid = number of persistent CTAs of the tile pass (test hook):
+    with 2 or 3 CTAs each one walks several tiles, so the epoch accumulators span tiles and flush mid-run."""
+    if grid is not None:
+        if path == "two_pass":
+            pytest.skip("grid only concerns the tile pass")
+        monkeypatch.setenv("BA_B200_TILE_GRID", str(grid))
     fp = S.make_flat_problem(*shape, seed=seed)
     prob = O.Problem.from_flat(fp)
     lam = 1e-3
@@ -160,6 +166,11 @@ def test_schur_matvec_against_dense_schur_complement(gpu_solver, path, shape, se
     gpu_solver.set_flat(fp)
     w = gpu_solver.schur_matvec(u, lam, schur_path=path)
     assert np.abs(w - w_ref).max() <= 1e-10 * np.abs(w_ref).max()
+    info = gpu_solver.layout_info()
+    assert info["epoch_tiles"] > 0 and info["max_epoch_slots"] <= 72     # these scenes fit the accumulators
+    assert info["matvec_rows"] <= info["segments"]
+    if grid is not None and shape[2] >= 4000:
+        assert info["matvec_rows"] < info["segments"] and info["epochs"] < info["point_tiles"]
 
 
 @pytest.mark.parametrize("shape,seed", [((6, 300, 1200), 3), ((60, 5000, 26000), 8), ((3, 700, 1500), 9)])
@@ -169,11 +180,18 @@ def test_fused_tiles_match_two_pass(gpu_solver, shape, seed):
     fp = S.make_flat_problem(*shape, seed=seed)
     kw = dict(max_iters=5, pcg_tol=1e-10, pcg_max_iters=300, ftol=0.0, xtol=0.0, gtol=0.0)
     out = {}
-    for path in ("tiles", "two_pass"):
+    for path in ("tiles", "tiles_rows", "two_pass", "tiles/kernels"):
         gpu_solver.set_flat(fp)
-        st = gpu_solver.solve(schur_path=path, **kw)
+        st = gpu_solver.solve(schur_path=path.split("/")[0], pcg_tail=0 if path.endswith("/kernels") else 1, **kw)
         ks = gpu_solver.kernel_stats()
         out[path] = (st, gpu_solver.get_x(), ks)
+    for other in ("tiles_rows", "tiles/kernels"):
+        assert abs(out[other][0]["final_cost"] - out["tiles"][0]["final_cost"]) <= 1e-9 * out["tiles"][0]["final_cost"]
+        assert out[other][2]["schur_matvec_tiles"][0] > 0
+        assert abs(out[other][0]["pcg_iterations"] - out["tiles"][0]["pcg_iterations"]) <= 0.05 * out["tiles"][0]["pcg_iterations"]
+    # one cluster kernel per PCG iteration after the tile pass, or the three separate kernels
+    assert out["tiles"][2]["pcg_tail"][0] >= out["tiles"][0]["pcg_iterations"] and out["tiles"][2]["pcg_update"][0] == 0
+    assert out["tiles/kernels"][2]["pcg_tail"][0] == 0 and out["tiles/kernels"][2]["pcg_update"][0] > 0
     assert out["tiles"][2]["schur_matvec_tiles"][0] > 0 and out["tiles"][2]["schur_matvec_points"][0] == 0
     assert out["two_pass"][2]["schur_matvec_tiles"][0] == 0 and out["two_pass"][2]["schur_matvec_points"][0] > 0
     a, b = out["tiles"][0], out["two_pass"][0]
