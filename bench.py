@@ -41,7 +41,7 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="venice", choices=["bal50", "ladybug", "venice", "shard50m"])
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
-    ap.add_argument("--cpu-sample-obs", type=int, default=100_000, help="observations in the CPU-baseline sample")
+    ap.add_argument("--cpu-sample-obs", type=int, default=1_000_000, help="observations in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 

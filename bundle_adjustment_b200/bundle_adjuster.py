@@ -41,6 +41,8 @@ class BundleAdjuster:
         self.lba_steps_dir = lba_steps_dir
         self.last_stats: Optional[dict] = None
         self._solver: Optional[FlatSolver] = None
+        # incremental flattening: per keyframe, the arrays of its observation list as last seen
+        self._kf_cache: Dict[int, tuple] = {}
 
     # ------------------------------------------------------------------------------------------
     def _get_solver(self) -> FlatSolver:
@@ -92,6 +94,60 @@ class BundleAdjuster:
                     observations.append((kf_id, mp_id))
                     keypoints_2d[(kf_id, mp_id)] = kps[kp_idx].pt
         return sorted(seen), observations, keypoints_2d
+
+    # -- incremental, vectorised flattening of a window (what run() uses) ------------------------------
+    def _keyframe_arrays(self, kf_id, kf):
+        """(map point ids, uv) of one keyframe's observation list, cached.  The pipeline only ever APPENDS to a
+        keyframe's list (``src/pipeline.py:305-306``), so a cached prefix stays valid and only the tail is
+        converted; any other change of the list (shorter, another list object) rebuilds the entry.  A (keyframe,
+        map point) pair listed twice keeps both rows with the LAST keypoint, as the reference's dict does (``:216``)."""
+        obs = kf.observations
+        n = len(obs)
+        ent = self._kf_cache.get(kf_id)
+        if ent is not None and ent[0] is obs and ent[1] is kf.keypoints and ent[2] == n:
+            return ent[5], ent[6]
+        if ent is not None and ent[0] is obs and ent[1] is kf.keypoints and ent[2] < n:
+            start, mp_raw, uv_raw = ent[2], ent[3], ent[4]
+        else:
+            start, mp_raw, uv_raw = 0, np.zeros(0, dtype=np.int64), np.zeros((0, 2))
+        kps = kf.keypoints
+        tail = obs[start:]
+        mp_new = np.fromiter((o[0] for o in tail), dtype=np.int64, count=len(tail))
+        uv_new = np.array([kps[o[1]].pt for o in tail], dtype=np.float64).reshape(-1, 2)
+        mp_raw = np.concatenate([mp_raw, mp_new])
+        uv_raw = np.concatenate([uv_raw, uv_new])
+        # duplicates of a map point inside this keyframe: every row takes the uv of the last one
+        uniq, inv = np.unique(mp_raw, return_inverse=True)
+        uv_eff = uv_raw
+        if uniq.shape[0] != mp_raw.shape[0]:
+            last = np.zeros(uniq.shape[0], dtype=np.int64)
+            last[inv] = np.arange(mp_raw.shape[0])          # later rows overwrite earlier ones
+            uv_eff = uv_raw[last[inv]]
+        self._kf_cache[kf_id] = (obs, kps, n, mp_raw, uv_raw, mp_raw, uv_eff)
+        return mp_raw, uv_eff
+
+    def _gather_flat(self, gmap, local_kf_ids: list, fixed_kf_id):
+        """Vectorised equivalent of ``_gather_local_data`` + ``_index_observations``:
+        -> (sorted map point ids, obs_cam, obs_pt, obs_uv) with identical contents and row order."""
+        mps, uvs, cams = [], [], []
+        slot = {kf_id: i - 1 for i, kf_id in enumerate(local_kf_ids)}      # fixed keyframe (first) -> -1
+        for kf_id in local_kf_ids:
+            mp, uv = self._keyframe_arrays(kf_id, gmap.keyframes[kf_id])
+            mps.append(mp); uvs.append(uv)
+            cams.append(np.full(mp.shape[0], -1 if kf_id == fixed_kf_id else slot[kf_id], dtype=np.int32))
+        mp = np.concatenate(mps) if mps else np.zeros(0, dtype=np.int64)
+        uv = np.concatenate(uvs) if uvs else np.zeros((0, 2))
+        cam = np.concatenate(cams) if cams else np.zeros(0, dtype=np.int32)
+        ids = np.unique(mp)
+        # `mp_id in gmap.map_points` (:213), once per distinct id
+        mpd = gmap.map_points
+        known = np.fromiter((m in mpd for m in ids.tolist()), dtype=bool, count=ids.shape[0])
+        if not known.all():
+            keep = known[np.searchsorted(ids, mp)]
+            mp, uv, cam = mp[keep], uv[keep], cam[keep]
+            ids = ids[known]
+        obs_pt = np.searchsorted(ids, mp).astype(np.int32)
+        return ids.tolist(), cam, obs_pt, np.ascontiguousarray(uv)
 
     def _cost_function(self, params, fixed_kf_pose, fixed_kf_id, adjustable_kf_ids, map_point_ids, observations,
                        keypoints_2d):
@@ -162,18 +218,18 @@ class BundleAdjuster:
             print("    -> LBA Skipped: No adjustable keyframes.")
             return
 
-        local_map_point_ids, observations, keypoints_2d = self._gather_local_data(gmap, local_kf_ids)
+        local_map_point_ids, obs_cam, obs_pt, obs_uv = self._gather_flat(gmap, local_kf_ids, fixed_kf_id)
         if not local_map_point_ids:
             print("    -> LBA Skipped: No points in the local window.")
             return
+        for stale in [k for k in self._kf_cache if k not in gmap.keyframes]:
+            del self._kf_cache[stale]
 
         rvecs = np.array([matrix_to_rvec(gmap.keyframes[i].R) for i in adjustable_kf_ids]).reshape(-1, 3)
         tvecs = np.array([np.asarray(gmap.keyframes[i].t, dtype=np.float64).ravel() for i in adjustable_kf_ids]).reshape(-1, 3)
         pts = np.array([np.asarray(gmap.map_points[i].position, dtype=np.float64).ravel()
                         for i in local_map_point_ids]).reshape(-1, 3)
         fixed_kf = gmap.keyframes[fixed_kf_id]
-        obs_cam, obs_pt, obs_uv = self._index_observations(adjustable_kf_ids, local_map_point_ids, observations,
-                                                           keypoints_2d, fixed_kf_id)
 
         fx, fy, cx, cy = self._intrinsics()
         solver = self._get_solver()

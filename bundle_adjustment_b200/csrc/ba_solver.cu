@@ -9,6 +9,7 @@
 #include "ba_kernels.cuh"
 #include "ba_tiles.cuh"
 #include "ba_peer.cuh"
+#include "ba_triangulate.cuh"
 
 #include <cub/cub.cuh>
 #include <dlfcn.h>
@@ -1672,6 +1673,36 @@ int ba_tile_layout(ba_handle* h, int32_t* ft_pt, int32_t* ft_obs, int32_t* ft_se
     get(tc_meta, h->tc_meta.p, (size_t)P.n_obs * 8); get(tc_uv, h->tc_uv.p, (size_t)P.n_obs * 16);
     get(seg_cam, h->seg_cam.p, S * 4); get(seg_info, h->seg_info.p, S * 4); get(seg_row, h->seg_row.p, S * 4);
     get(cam_row_off, h->cam_row_off.p, ((size_t)P.n_cams + 2) * 4); get(pt_perm, h->pt_perm.p, (size_t)P.n_pts * 4);
+    CK(cudaStreamSynchronize(s));
+    API_END
+}
+
+int ba_triangulate(ba_handle* h, const double P1[12], const double P2[12], const double* R_rel, const double* t_rel, int32_t n,
+                   const double* pts1, const double* pts2, double* hom, double* xyz, uint8_t* valid) {
+    API_BEGIN
+    ba::use(h);
+    if (n < 0 || !P1 || !P2 || (n > 0 && (!pts1 || !pts2))) ba::fail(BA_ERR_ARG, "null or negative argument");
+    if (valid && (!R_rel || !t_rel)) ba::fail(BA_ERR_ARG, "the cheirality test needs R_rel and t_rel");
+    if (n == 0) return BA_OK;
+    cudaStream_t s = h->stream;
+    ba::ScratchScope scratch(s);
+    ba::TriParams T;
+    memcpy(T.P1, P1, sizeof T.P1); memcpy(T.P2, P2, sizeof T.P2);
+    for (int k = 0; k < 9; ++k) T.R[k] = R_rel ? R_rel[k] : (k % 4 == 0 ? 1.0 : 0.0);
+    for (int k = 0; k < 3; ++k) T.t[k] = t_rel ? t_rel[k] : 0.0;
+    ba::TBuf<double> d1, d2, dh, dx;
+    ba::TBuf<unsigned char> dv;
+    d1.alloc((size_t)n * 2); d2.alloc((size_t)n * 2);
+    if (hom) dh.alloc((size_t)n * 4);
+    if (xyz) dx.alloc((size_t)n * 3);
+    if (valid) dv.alloc(n);
+    CK(cudaMemcpyAsync(d1.p, pts1, (size_t)n * 2 * sizeof(double), cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d2.p, pts2, (size_t)n * 2 * sizeof(double), cudaMemcpyHostToDevice, s));
+    ba::launch(h, ba::KN_SETUP, ba::k_triangulate, ba::cdiv(n, 128), 128, 0, T, (int)n, (const double*)d1.p, (const double*)d2.p, dh.p, dx.p,
+               dv.p);
+    if (hom) CK(cudaMemcpyAsync(hom, dh.p, (size_t)n * 4 * sizeof(double), cudaMemcpyDeviceToHost, s));
+    if (xyz) CK(cudaMemcpyAsync(xyz, dx.p, (size_t)n * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
+    if (valid) CK(cudaMemcpyAsync(valid, dv.p, (size_t)n, cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
     API_END
 }

@@ -189,6 +189,15 @@ int ba_layout_info(ba_handle* h, int64_t out[12]);
 int ba_tile_layout(ba_handle* h, int32_t* ft_pt, int32_t* ft_obs, int32_t* ft_seg, int32_t* tc_meta, double* tc_uv,
                    int32_t* seg_cam, int32_t* seg_info, int32_t* seg_row, int32_t* cam_row_off, int32_t* pt_perm);
 
+/* Two-view linear triangulation of n correspondences and the cheirality test, on the device: replaces the
+ * reference's  cv2.triangulatePoints(P1, P2, pts1.T, pts2.T)  followed by  X = h[:3] / (h[3] + 1e-6), z > 0 in
+ * both views  (src/pipeline.py:315-336).  P1, P2: row-major 3x4 projection matrices; R_rel[9] (row-major), t_rel[3]:
+ * pose of the second view (only used for `valid`, may be NULL when valid is NULL); pts1, pts2 [n*2] pixels.
+ * Outputs, each may be NULL: hom[n*4] unit homogeneous solutions (sign arbitrary, as OpenCV's), xyz[n*3],
+ * valid[n] (1 = in front of both cameras).  Needs no uploaded problem. */
+int ba_triangulate(ba_handle* h, const double P1[12], const double P2[12], const double* R_rel, const double* t_rel,
+                   int32_t n, const double* pts1, const double* pts2, double* hom, double* xyz, uint8_t* valid);
+
 /* Thread-local text of the last error returned on this thread. */
 const char* ba_last_error(void);
 

@@ -178,3 +178,55 @@ def test_injected_into_the_unmodified_reference_pipeline(tmp_path, monkeypatch, 
         vo.bundle_adjuster.window_size = vo.map.next_keyframe_id
         with pytest.raises(_capi.BaError, match="no CPU path"):
             vo.bundle_adjuster.run(vo.map)
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_incremental_flattening_equals_the_reference_gather(name):
+    """the cached, vectorised window flattening that run() uses produces exactly what the
+    reference-contract helpers produce (_gather_local_data + row indexing): ids, row order, duplicates with the
+    last keypoint, dangling observations dropped."""
+    g, spec = load_golden(name)
+    gmap = mirror_map(spec)
+    adj = BundleAdjuster(spec["camera_matrix"], window_size=int(g["window_size"]))
+    local = g["local_kf_ids"].tolist()
+    fixed, adjustable = local[0], local[1:]
+    for rep in range(2):                                         # second pass is served from the cache
+        mp_ids, obs, kp = adj._gather_local_data(gmap, local)
+        oc, op, ouv = adj._index_observations(adjustable, mp_ids, obs, kp, fixed)
+        ids2, oc2, op2, ouv2 = adj._gather_flat(gmap, local, fixed)
+        assert ids2 == mp_ids == g["mp_ids"].tolist()
+        assert np.array_equal(oc2, oc) and np.array_equal(op2, op) and np.array_equal(ouv2, ouv)
+        assert oc2.dtype == np.int32 and op2.dtype == np.int32 and ouv2.dtype == np.float64
+
+
+def test_incremental_flattening_follows_a_growing_map():
+    """Observation lists grow between calls (the pipeline appends to the last keyframe when it triangulates,
+    src/pipeline.py:305-306); cached prefixes are reused, tails converted, replaced lists rebuilt."""
+    spec = S.make_window_spec(n_kfs=7, n_pts=200, seed=11, duplicates=3, dangling=2)
+    gmap = mirror_map(spec)
+    adj = BundleAdjuster(spec["camera_matrix"], window_size=5)
+    local = sorted(gmap.keyframes)[-6:-1]
+
+    def both():
+        mp_ids, obs, kp = adj._gather_local_data(gmap, local)
+        ref = adj._index_observations(local[1:], mp_ids, obs, kp, local[0])
+        got = adj._gather_flat(gmap, local, local[0])
+        assert got[0] == mp_ids
+        for a, b in zip(ref, got[1:]):
+            assert np.array_equal(a, b)
+
+    both()
+    kf = gmap.keyframes[local[2]]
+    new_id = gmap.next_map_point_id
+    gmap.add_map_point(MapPoint(id=new_id, position=np.array([[0.1], [0.2], [9.0]])))
+    kf.keypoints.append(KeyPoint.from_xy(321.5, 222.25))
+    kf.observations.append((new_id, len(kf.keypoints) - 1))      # appended: tail conversion
+    kf.observations.append((kf.observations[0][0], len(kf.keypoints) - 1))   # duplicate pair: last keypoint wins for both rows
+    both()
+    kf2 = gmap.keyframes[local[3]]
+    kf2.observations = list(reversed(kf2.observations))          # another list object: entry rebuilt
+    both()
+    kf2.observations.pop()                                       # shorter: rebuilt
+    both()
+    kf.observations.append((10 ** 6, 0))                         # observation of a map point that is not in the map: dropped
+    both()
