@@ -29,12 +29,14 @@
 #pragma once
 #include "ba_math.cuh"
 
+#include <cooperative_groups.h>
+
 namespace ba {
 
 constexpr int PM_THREADS = 256;  // point-major CTA; nominal tile = PM_THREADS observations
 constexpr int CM_THREADS = 256;  // camera-major CTA
-constexpr int CM_ROUNDS = 4;     // observations per thread in a camera-major tile
-constexpr int CM_TILE = CM_THREADS * CM_ROUNDS;
+constexpr int CM_ROUNDS = 4;     // observations per thread in the smallest camera-major tile
+constexpr int CM_TILE = CM_THREADS * CM_ROUNDS;  // tiles grow up to 8 x this on large problems (fewer 27-value CTA reductions)
 constexpr int NSCAL = 16;        // per-iteration scalar slots
 constexpr int VEC_THREADS = 128; // camera-vector kernels: one camera per thread
 constexpr int MAX_VEC_CTAS = 8192;
@@ -969,28 +971,41 @@ BA_D double cta_sum_all(double v, double* sm /* >= 33 */) {  // all threads get 
 
 // Reduce per-tile / per-camera scalar partials into st->scal (fixed order).  The masks select slots.
 __global__ void __launch_bounds__(RED_THREADS) k_reduce_scalars(Params P, unsigned pm_mask, unsigned cam_mask) {
-    // 16 lanes per partial row (one 128-byte line): thread t owns slot t & 15 of rows t >> 4, t >> 4 + 64, ...
+    // One thread-block cluster (1..16 CTAs): CTA r takes the row groups r, r + CL, ...; 16 lanes per partial row (one
+    // 128-byte line): thread t owns slot t & 15.  CTA totals meet in CTA 0's shared memory and are added in rank order.
     static_assert(NSCAL == 16, "row layout");
     __shared__ double sm[RED_THREADS];
+    __shared__ double part[16 * 16];  // [rank][slot], CTA 0 only
+    cooperative_groups::cluster_group cl = cooperative_groups::this_cluster();
+    const int R = (int)cl.block_rank(), CL = (int)cl.num_blocks();
     const int s = threadIdx.x & 15, g = threadIdx.x >> 4;
     constexpr int G = RED_THREADS / 16;
     const bool pm = (pm_mask >> s) & 1u, cm = (cam_mask >> s) & 1u, is_max = (s == S_GPMAX);
     double v = 0.0;
     if (pm) {
-        for (int t = g; t < P.n_partial_rows; t += G) {
+        for (int t = R * G + g; t < P.n_partial_rows; t += CL * G) {
             const double x = P.pm_partial[(size_t)t * NSCAL + s];
             v = is_max ? fmax(v, x) : v + x;
         }
     }
     if (cm) {
-        for (int c = g; c < P.n_cams; c += G) v += P.cam_partial[(size_t)c * NSCAL + s];
+        for (int c = R * G + g; c < P.n_cams; c += CL * G) v += P.cam_partial[(size_t)c * NSCAL + s];
     }
     sm[g * 16 + s] = v;
     __syncthreads();
-    if (threadIdx.x < 16 && (pm || cm)) {  // fixed order over the 64 row groups
+    if (threadIdx.x < 16) {  // fixed order over the 64 row groups
         double tot = 0.0;
         for (int i = 0; i < G; ++i) {
             const double x = sm[i * 16 + s];
+            tot = is_max ? fmax(tot, x) : tot + x;
+        }
+        cl.map_shared_rank(part, 0)[R * 16 + s] = tot;
+    }
+    cl.sync();
+    if (R == 0 && threadIdx.x < 16 && (pm || cm)) {
+        double tot = 0.0;
+        for (int r = 0; r < CL; ++r) {
+            const double x = part[r * 16 + s];
             tot = is_max ? fmax(tot, x) : tot + x;
         }
         P.st->scal[s] = tot;

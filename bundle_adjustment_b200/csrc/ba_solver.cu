@@ -399,6 +399,7 @@ struct ba_handle {
     // epoch accumulators of the mat-vec tile pass (ba_tiles.cuh); acc_ok = every epoch fits FT_ACC_CAP slots
     bool acc_ok = false;
     int tail_cluster = 0;  // CTAs of the PCG tail cluster (ba_peer.cuh); 0 = tail kernel not usable for this problem
+    int red_cluster = 1;   // CTAs of the scalar-reduction cluster
     int tail_cached = 0;   // last answer of the (slow) cluster occupancy query and the shared-memory size it holds for
     size_t tail_cached_bytes = 0;
     int ep_target = 0, n_epochs = 0, n_slots = 0, max_ep_slots = 0;
@@ -760,6 +761,11 @@ static void build_tiles(ba_handle* h, int n_cams, int n_pts, int n_obs) {
             if (good) { h->tail_cluster = cl; h->tail_cached = cl; h->tail_cached_bytes = bytes; }
         }
     }
+    h->red_cluster = std::max(1, h->tail_cluster);  // a 1024-thread kernel with less shared memory: schedulable wherever the tail is
+    if (h->red_cluster > 1 && cudaFuncSetAttribute(k_reduce_scalars, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+        cudaGetLastError();
+        h->red_cluster = std::min(h->red_cluster, 8);
+    }
     if (getenv("BA_B200_TRACE")) {
         fprintf(stderr, "[ba_b200] PCG tail cluster: %d CTAs\n", h->tail_cluster);
         int o0 = 0, o1 = 0, o2 = 0;
@@ -1008,10 +1014,12 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
            (const int2*)h->o_idx.p, h->cm_uv.p, h->cm_pt.p);
     std::vector<int4> tiles;
     std::vector<int> tile_off(nc1, 0);
+    // tile length: as long as possible (every tile ends in a 27-value CTA reduction) while there are still about four tiles per SM
+    const int cm_len = std::min(8 * CM_TILE, std::max(CM_TILE, cdiv(cdiv(n_obs_adj, 4 * h->sm_count), CM_THREADS) * CM_THREADS));
     for (int c = 0; c < n_cams; ++c) {
         tile_off[c] = (int)tiles.size();
-        for (int o = camoff[c]; o < camoff[c + 1]; o += CM_TILE)
-            tiles.push_back(make_int4(c, o, std::min(CM_TILE, camoff[c + 1] - o), 0));
+        for (int o = camoff[c]; o < camoff[c + 1]; o += cm_len)
+            tiles.push_back(make_int4(c, o, std::min(cm_len, camoff[c + 1] - o), 0));
     }
     tile_off[n_cams] = (int)tiles.size();
     const int cm_tiles = (int)tiles.size();
@@ -1129,7 +1137,7 @@ static const unsigned MASK_STEP_CAM = (1u << S_GDC) | (1u << S_DDC) | (1u << S_R
 
 static void reduce_scalars(ba_handle* h, unsigned pm_mask, unsigned cam_mask) {
     const Params& P = h->P;
-    launch(h, KN_REDUCE, k_reduce_scalars, 1, RED_THREADS, 0, P, pm_mask, cam_mask);
+    launch_cluster(h, KN_REDUCE, k_reduce_scalars, std::max(1, h->red_cluster), RED_THREADS, 0, P, pm_mask, cam_mask);
     if (h->nranks > 1) {
         double* scal = reinterpret_cast<double*>(reinterpret_cast<char*>(h->st.p) + offsetof(LMState, scal));
         allreduce_sum(h, scal, N_PT_SCAL);
