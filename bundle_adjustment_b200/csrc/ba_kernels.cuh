@@ -567,15 +567,23 @@ __host__ __device__ constexpr size_t cm_smem_bytes() {
     return 0;
 }
 
-template <int KIND>
+// WARP = false: one CTA per tile, long tiles (thousands of observations of one camera), CTA reduction of the N sums.
+// WARP = true : one warp per tile (<= CM_TILE observations): the N sums of a tile are a shuffle tree, no shared memory,
+//               no barrier - faster when a camera has only a few hundred observations (many cameras, or a rank of a
+//               multi-GPU run that holds 1/N of every camera's observations).
+template <int KIND, bool WARP>
 __global__ void __launch_bounds__(CM_THREADS) k_camera_pass(Params P, const double* __restrict__ vec, int with_schur_diag) {
     constexpr int N = CmN<KIND>::value;
     constexpr int NCH = CmCh<KIND>::value;
-    __shared__ double red[CM_THREADS / 32 * N];
-    __shared__ double tot[N];
+    __shared__ double red[WARP ? 1 : CM_THREADS / 32 * N];
+    __shared__ double tot[WARP ? 1 : N];
     if (KIND == 2 && P.st->pcg_done) return;
+    const int lane = WARP ? (threadIdx.x & 31) : threadIdx.x;
+    constexpr int STRIDE = WARP ? 32 : CM_THREADS;
+    const int tile_id = WARP ? blockIdx.x * (CM_THREADS / 32) + (threadIdx.x >> 5) : blockIdx.x;
+    if (WARP && tile_id >= P.cm_tiles) return;
     const int b = P.st->cur;
-    const int4 tile = __ldg(P.cm_tile + blockIdx.x);
+    const int4 tile = __ldg(P.cm_tile + tile_id);
     const int cam = tile.x, o0 = tile.y, n = tile.z;
     double Rt[12], x[6];
     load_cam(P.cam_R + (size_t)b * (P.n_cams + 1) * 12, cam, Rt);
@@ -583,7 +591,7 @@ __global__ void __launch_bounds__(CM_THREADS) k_camera_pass(Params P, const doub
     double acc[N];
 #pragma unroll
     for (int k = 0; k < N; ++k) acc[k] = 0.0;
-    for (int i = threadIdx.x; i < n; i += CM_THREADS) {
+    for (int i = lane; i < n; i += STRIDE) {
         const double2 uvr = __ldg(P.cm_uv + o0 + i);
         const int p = __ldg(P.cm_pt + o0 + i);
         double rec[2 * NCH];
@@ -687,9 +695,18 @@ __global__ void __launch_bounds__(CM_THREADS) k_camera_pass(Params P, const doub
             for (int k = 0; k < 3; ++k) { acc[k] += xm[k]; acc[3 + k] += m[k]; }
         }
     }
-    block_sum<N, CM_THREADS>(acc, red, tot);
-    __syncthreads();
-    if (threadIdx.x < N) P.cm_partial[(size_t)blockIdx.x * 27 + threadIdx.x] = tot[threadIdx.x];
+    double* out = P.cm_partial + (size_t)tile_id * 27;
+    if constexpr (WARP) {
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+            const double tsum = warp_sum(acc[k]);  // fixed shuffle order; total in lane 0
+            if (lane == 0) out[k] = tsum;
+        }
+    } else {
+        block_sum<N, CM_THREADS>(acc, red, tot);
+        __syncthreads();
+        if (threadIdx.x < N) out[threadIdx.x] = tot[threadIdx.x];
+    }
 }
 
 // Sum the tile partials of each camera in tile order: cam_acc[c*n_val + k] (k < n_val).

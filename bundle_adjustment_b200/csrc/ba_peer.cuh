@@ -208,16 +208,15 @@ __global__ void __launch_bounds__(PT_THREADS, 1) k_pcg_tail(Params P, double tol
             xstate[0] = (int)seq;
             st_release_sys(reinterpret_cast<long long*>(xbuf) + (seq & 1), seq);  // publish
         }
-        if (tid == 0) {
-            int good = 1;
-            for (int r = 0; r < nranks && good; ++r) {
-                const long long* flag = reinterpret_cast<const long long*>(peers[r]) + (seq & 1);
-                long long spins = 0;
-                while (ld_acquire_sys(flag) < seq)
-                    if (++spins > XB_SPIN_LIMIT) { good = 0; break; }
-            }
-            if (!good) atomicExch(xstate + 2, 1);
-            ok = good;
+        if (tid == 0) ok = 1;
+        __syncthreads();
+        if (tid < nranks) {  // one thread per rank polls that rank's flag: the NVLink round trips overlap
+            const long long* flag = reinterpret_cast<const long long*>(peers[tid]) + (seq & 1);
+            long long spins = 0;
+            bool good = true;
+            while (ld_acquire_sys(flag) < seq)
+                if (++spins > XB_SPIN_LIMIT) { good = false; break; }
+            if (!good) { atomicExch(xstate + 2, 1); ok = 0; }
         }
     }
     __syncthreads();
@@ -229,7 +228,13 @@ __global__ void __launch_bounds__(PT_THREADS, 1) k_pcg_tail(Params P, double tol
         double w = 0.0;
         if (PEER) {
             if (ok)
-                for (int r = 0; r < nranks; ++r) w += __ldcv(peers[r] + slot_off + i);
+                for (int r0 = 0; r0 < nranks; r0 += 8) {  // eight remote loads in flight, then the adds in rank order
+                    double v[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) v[j] = (r0 + j < nranks) ? __ldcv(peers[r0 + j] + slot_off + i) : 0.0;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) w += v[j];
+                }
         } else {
             w = sW[e];
         }

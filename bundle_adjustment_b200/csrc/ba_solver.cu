@@ -398,6 +398,7 @@ struct ba_handle {
     bool fused_ok = false;
     // epoch accumulators of the mat-vec tile pass (ba_tiles.cuh); acc_ok = every epoch fits FT_ACC_CAP slots
     bool acc_ok = false;
+    bool cm_warp = false;  // camera-major passes: one warp per tile instead of one CTA per tile
     int tail_cluster = 0;  // CTAs of the PCG tail cluster (ba_peer.cuh); 0 = tail kernel not usable for this problem
     int red_cluster = 1;   // CTAs of the scalar-reduction cluster
     int tail_cached = 0;   // last answer of the (slow) cluster occupancy query and the shared-memory size it holds for
@@ -1014,8 +1015,12 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
            (const int2*)h->o_idx.p, h->cm_uv.p, h->cm_pt.p);
     std::vector<int4> tiles;
     std::vector<int> tile_off(nc1, 0);
-    // tile length: as long as possible (every tile ends in a 27-value CTA reduction) while there are still about four tiles per SM
-    const int cm_len = std::min(8 * CM_TILE, std::max(CM_TILE, cdiv(cdiv(n_obs_adj, 4 * h->sm_count), CM_THREADS) * CM_THREADS));
+    // cameras with thousands of observations here: long tiles, one CTA each (few 27-value CTA reductions, about four
+    // tiles per SM); otherwise tiles of <= CM_TILE observations, one WARP each (shuffle-tree reductions only)
+    h->cm_warp = n_cams > 0 && n_obs_adj / n_cams < 2 * CM_TILE;
+    if (const char* e = getenv("BA_B200_CM_WARP")) h->cm_warp = atoi(e) != 0;
+    const int cm_len = h->cm_warp ? CM_TILE
+                                  : std::min(8 * CM_TILE, std::max(CM_TILE, cdiv(cdiv(n_obs_adj, 4 * h->sm_count), CM_THREADS) * CM_THREADS));
     for (int c = 0; c < n_cams; ++c) {
         tile_off[c] = (int)tiles.size();
         for (int o = camoff[c]; o < camoff[c + 1]; o += cm_len)
@@ -1030,6 +1035,31 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     h->max_track = err_track[1];
     tm.mark("camera-major order");
     build_tiles(h, n_cams, n_pts, n_obs);
+    if (h->nranks > 1) {
+        // every rank must run the same kernels per PCG iteration (they exchange inside them) and add the partial sums
+        // in the same order: agree on "tiles usable" and on the size of the tail cluster (minimum over the ranks)
+        TBuf<double> d_agree;
+        d_agree.alloc(2);
+        double mine[2] = {h->fused_ok ? 1.0 : 0.0, (double)h->tail_cluster}, all[2] = {0.0, 0.0};
+        CK(cudaMemcpyAsync(d_agree.p, mine, sizeof mine, cudaMemcpyHostToDevice, s));
+        NK(nccl_api().AllReduce(d_agree.p, d_agree.p, 2, ncclDouble, ncclMin, h->comm, s));
+        CK(cudaMemcpyAsync(all, d_agree.p, sizeof all, cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+        if (all[0] < 0.5) h->fused_ok = false;
+        if ((int)all[1] < h->tail_cluster) {  // a smaller cluster means larger chunks per CTA
+            h->tail_cluster = (int)all[1];
+            if (h->tail_cluster > 0) {
+                const int bytes = (int)std::max(pt_smem_bytes(n_cams, h->tail_cluster), (size_t)1024);
+                if (cudaFuncSetAttribute(k_pcg_tail<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess ||
+                    cudaFuncSetAttribute(k_pcg_tail<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess) {
+                    cudaGetLastError();
+                    fail(BA_ERR_CUDA, "the ranks disagree on the PCG tail cluster and %d CTAs do not fit this device", h->tail_cluster);
+                }
+            }
+            h->tail_cached = 0;
+        }
+        h->red_cluster = std::max(1, std::min(h->red_cluster, std::max(1, (int)all[1])));
+    }
     tm.mark("point tiles");
     const int n_partial_rows = std::max(pm_tiles, h->ft_tiles);
     h->pm_partial.alloc((size_t)n_partial_rows * NSCAL);
@@ -1044,9 +1074,6 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     CK(cudaFuncSetAttribute(k_lin_points, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_lin));
     CK(cudaFuncSetAttribute(k_point_pass<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_pass));
     CK(cudaFuncSetAttribute(k_point_pass<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_pass));
-    CK(cudaFuncSetAttribute(k_camera_pass<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cm_smem_bytes<0>()));
-    CK(cudaFuncSetAttribute(k_camera_pass<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cm_smem_bytes<1>()));
-    CK(cudaFuncSetAttribute(k_camera_pass<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cm_smem_bytes<2>()));
 
     // ---- parameters -----------------------------------------------------------------------------
     h->io.alloc(std::max<size_t>((size_t)n_pts * 3, nc1 * 6));
@@ -1135,6 +1162,13 @@ static const unsigned MASK_LIN = (1u << S_COST) | (1u << S_RAW) | (1u << S_BAD) 
 static const unsigned MASK_STEP_PM = (1u << S_GDP) | (1u << S_DDP) | (1u << S_DP2) | (1u << S_XP2);
 static const unsigned MASK_STEP_CAM = (1u << S_GDC) | (1u << S_DDC) | (1u << S_RDC) | (1u << S_DC2) | (1u << S_XC2);
 
+template <int KIND>
+static void launch_camera_pass(ba_handle* h, Kind kind, const double* vec, int with_schur) {
+    const Params& P = h->P;
+    if (h->cm_warp) launch(h, kind, k_camera_pass<KIND, true>, cdiv(P.cm_tiles, CM_THREADS / 32), CM_THREADS, 0, P, vec, with_schur);
+    else launch(h, kind, k_camera_pass<KIND, false>, P.cm_tiles, CM_THREADS, 0, P, vec, with_schur);
+}
+
 static void reduce_scalars(ba_handle* h, unsigned pm_mask, unsigned cam_mask) {
     const Params& P = h->P;
     launch_cluster(h, KN_REDUCE, k_reduce_scalars, std::max(1, h->red_cluster), RED_THREADS, 0, P, pm_mask, cam_mask);
@@ -1148,7 +1182,7 @@ static void reduce_scalars(ba_handle* h, unsigned pm_mask, unsigned cam_mask) {
 static void lin_cameras(ba_handle* h, double dmin, double dmax) {
     const Params& P = h->P;
     if (P.n_cams == 0) return;
-    launch(h, KN_LIN_CAM, k_camera_pass<0>, P.cm_tiles, CM_THREADS, cm_smem_bytes<0>(), P, (const double*)nullptr, 0);
+    launch_camera_pass<0>(h, KN_LIN_CAM, nullptr, 0);
     launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 27, 256), 256, 0, P, 27, 0);
     allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 27);
     launch(h, KN_CAM_FIN, k_camera_finish_lin, cdiv(P.n_cams, 128), 128, 0, P, dmin, dmax);
@@ -1196,7 +1230,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
         }
         launch(h, KN_PT_PREP, k_point_prepare, cdiv(P.n_pts, 256), 256, 0, P, kDiagMin, kDiagMax);
         if (P.n_cams > 0) {
-            launch(h, KN_SCHUR_CAM, k_camera_pass<1>, P.cm_tiles, CM_THREADS, cm_smem_bytes<1>(), P, (const double*)nullptr, with_schur);
+            launch_camera_pass<1>(h, KN_SCHUR_CAM, nullptr, with_schur);
             launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 27, 256), 256, 0, P, 27, 0);
             allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 27);
             launch(h, KN_CAM_FIN, k_camera_finish_schur, P.vec_ctas, VEC_THREADS, 0, P, with_schur, h->ticket.p);
@@ -1228,7 +1262,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
                     }
                 } else {
                     launch(h, KN_PT_PASS, k_point_pass<0>, P.pm_tiles, PM_THREADS, h->smem_pass, P, (const double*)h->v_u.p);
-                    launch(h, KN_MATVEC_CAM, k_camera_pass<2>, P.cm_tiles, CM_THREADS, cm_smem_bytes<2>(), P, (const double*)h->v_u.p, 0);
+                    launch_camera_pass<2>(h, KN_MATVEC_CAM, h->v_u.p, 0);
                     if (h->nranks > 1) {
                         launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 6, 256), 256, 0, P, 6, 1);
                         allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 6);
@@ -1637,8 +1671,7 @@ int ba_schur_matvec(ba_handle* h, const ba_options* opt, double lambda, const do
         ba::launch(h, ba::KN_ROWS_FIN, ba::k_rows_finish<false>, ba::cdiv(P.n_cams, ba::RS_WARPS), ba::RS_WARPS * 32, 0, PA);
     } else {
         ba::launch(h, ba::KN_PT_PASS, ba::k_point_pass<0>, P.pm_tiles, ba::PM_THREADS, h->smem_pass, P, (const double*)h->v_u.p);
-        ba::launch(h, ba::KN_MATVEC_CAM, ba::k_camera_pass<2>, P.cm_tiles, ba::CM_THREADS, ba::cm_smem_bytes<2>(), P,
-                   (const double*)h->v_u.p, 0);
+        ba::launch_camera_pass<2>(h, ba::KN_MATVEC_CAM, h->v_u.p, 0);
         ba::launch(h, ba::KN_PCG_DOTS, ba::k_pcg_dots<true>, P.vec_ctas, ba::VEC_THREADS, 0, P);
     }
     CK(cudaMemcpyAsync(w_out, h->v_w.p, (size_t)P.n_cams * 6 * sizeof(double), cudaMemcpyDeviceToHost, s));
