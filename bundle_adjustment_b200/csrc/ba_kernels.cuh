@@ -424,20 +424,20 @@ __global__ void __launch_bounds__(PM_THREADS) k_lin_points(Params P, int which) 
     double gmax = 0.0;
     double* V = P.pt_V + (size_t)b * P.n_pts * 6;
     double* G = P.pt_g + (size_t)b * P.n_pts * 4;
-    for (int j = threadIdx.x; j < T.p1 - T.p0; j += PM_THREADS) {
+    // one thread per (point, value): nine short sums side by side instead of one thread walking nine rows
+    for (int w = threadIdx.x; w < (T.p1 - T.p0) * 9; w += PM_THREADS) {
+        const int j = w / 9, k = w - 9 * j;
         const int p = T.p0 + j;
         const int a = __ldg(P.pt_off + p) - T.o0, e = __ldg(P.pt_off + p + 1) - T.o0;
-        double s[9];
-#pragma unroll
-        for (int k = 0; k < 9; ++k) s[k] = 0.0;
-        for (int i = a; i < e; ++i) {
-#pragma unroll
-            for (int k = 0; k < 9; ++k) s[k] += sm[k * cap + i];
+        const double* row = sm + (size_t)k * cap;
+        double sk = 0.0;
+        for (int i = a; i < e; ++i) sk += row[i];
+        if (k < 6) {
+            V[(size_t)p * 6 + k] = sk;
+        } else {
+            G[(size_t)p * 4 + (k - 6)] = sk;
+            gmax = fmax(gmax, fabs(sk));
         }
-        double2* v2 = reinterpret_cast<double2*>(V + (size_t)p * 6);
-        v2[0] = make_double2(s[0], s[1]); v2[1] = make_double2(s[2], s[3]); v2[2] = make_double2(s[4], s[5]);
-        store_v3(G + (size_t)p * 4, s[6], s[7], s[8]);
-        gmax = fmax(gmax, fmax(fabs(s[6]), fmax(fabs(s[7]), fabs(s[8]))));
     }
     __syncthreads();
     block_sum<3, PM_THREADS>(acc, red, tot);
