@@ -39,7 +39,7 @@ constexpr int FT_LD = FT_THREADS + 2;  // row stride of the camera-side scratch 
 constexpr int FT_LDB = FT_THREADS + 4; // row stride of the point-side scratch (phases A/B): 2*FT_LDB mod 32 = 8 banks, so the
                                        // three rows read by the four points of a half-warp are disjoint
 constexpr int FT_ROWS_MV = 6;          // scratch rows of the mat-vec pass
-constexpr int FT_ACC_CAP = 72;         // accumulator slots (6 doubles + row number each) of an epoch; what is left of 228 KB / 4 CTAs
+constexpr int FT_ACC_CAP = 96;         // accumulator slots (6 doubles + row number each) of an epoch; what is left of 228 KB / 4 CTAs
 
 // Tiles of persistent CTA b of a grid of G over T tiles, and the way a CTA cuts its run into EPOCHS of about
 // `target` tiles (equal lengths, the last one may be shorter).  Host and device use the same two functions.
@@ -56,6 +56,7 @@ __host__ __device__ inline int ft_epoch_len(int len, int target) {
 // by tile parity; everything else is refilled by the TMA as soon as its last reader has passed a barrier.
 constexpr int FT_META_N = FT_THREADS + 2, FT_OFF_N = FT_PTS + 8, FT_SEG_N = FT_THREADS + 8;
 struct FtSmem {
+    double* sA;  // [3][FT_LDB] point-side scratch (phases A/B); separate from sO so that phase D of a tile and phase A of the next overlap
     double* sO; double2* sJ; int2* sMeta; double2* sX01; double* sX2; double2* sZ01; double* sZ2; double* sVi;
     int* sOff; int* sRs; int* sSeg; int* sRow;
     unsigned long long* bar;
@@ -63,22 +64,23 @@ struct FtSmem {
     int* sSlot;    // [FT_ACC_CAP] row of every slot of the current epoch
 };
 __host__ __device__ constexpr size_t ft_smem_bytes(int rows, bool acc = false) {
-    return (size_t)(rows * FT_LD) * 8 + 3 * FT_THREADS * 16 + FT_META_N * 8 + (size_t)FT_PTS * (2 + 2 + 2 * 6) * 8 +
-           2 * (size_t)(FT_PTS + 2) * 8 + (size_t)(2 * FT_OFF_N + 6 * FT_SEG_N) * 4 + 16 + (acc ? FT_ACC_CAP * 52 : 0);
+    return (size_t)(rows * FT_LD + 3 * FT_LDB) * 8 + 3 * FT_THREADS * 16 + FT_META_N * 8 + (size_t)FT_PTS * (2 + 2 + 6) * 8 +
+           2 * (size_t)(FT_PTS + 2) * 8 + (size_t)(FT_OFF_N + 5 * FT_SEG_N) * 4 + 16 + (acc ? FT_ACC_CAP * 52 : 0);
 }
 BA_D FtSmem ft_carve(double* sm, int rows) {
     FtSmem S;
     S.sO = sm;
-    S.sJ = reinterpret_cast<double2*>(S.sO + rows * FT_LD);
+    S.sA = S.sO + rows * FT_LD;
+    S.sJ = reinterpret_cast<double2*>(S.sA + 3 * FT_LDB);
     S.sMeta = reinterpret_cast<int2*>(S.sJ + 3 * FT_THREADS);
     S.sX01 = reinterpret_cast<double2*>(S.sMeta + FT_META_N);
     S.sX2 = reinterpret_cast<double*>(S.sX01 + FT_PTS);
     S.sZ01 = reinterpret_cast<double2*>(S.sX2 + FT_PTS + 2);
     S.sZ2 = reinterpret_cast<double*>(S.sZ01 + FT_PTS);
     S.sVi = S.sZ2 + FT_PTS + 2;
-    S.sOff = reinterpret_cast<int*>(S.sVi + 2 * FT_PTS * 6);
-    S.sRs = S.sOff + 2 * FT_OFF_N;
-    S.sSeg = S.sRs + 2 * FT_SEG_N;
+    S.sOff = reinterpret_cast<int*>(S.sVi + FT_PTS * 6);
+    S.sRs = S.sOff + FT_OFF_N;
+    S.sSeg = S.sRs + FT_SEG_N;
     S.sRow = S.sSeg + 2 * FT_SEG_N;
     S.bar = reinterpret_cast<unsigned long long*>(S.sRow + 2 * FT_SEG_N);
     S.sAcc = reinterpret_cast<double*>(S.bar + 2);
@@ -163,15 +165,15 @@ BA_D void ft_issue_group1(const Params& P, const FtSmem& S, const TileHdr& T, in
         tma_load(S.sRow + buf * FT_SEG_N, P.seg_row + seg_lo, seg_b, bar);
     }
 }
-BA_D void ft_issue_group2(const Params& P, const FtSmem& S, const TileHdr& T, int buf, unsigned long long* bar) {
+BA_D void ft_issue_group2(const Params& P, const FtSmem& S, const TileHdr& T, unsigned long long* bar) {
     const int off_lo = T.p0 & ~3;
     const unsigned vi_b = (unsigned)T.m * 48u;
     const unsigned off_b = (unsigned)(((T.p0 + T.m + 1 - off_lo) * 4 + 15) & ~15);
     const unsigned rs_b = (unsigned)((T.maxlen * 4 + 15) & ~15);  // r0 is a multiple of 4
     mbar_expect_tx(bar, vi_b + off_b + rs_b);
-    tma_load(S.sVi + buf * FT_PTS * 6, P.pt_Vinv + (size_t)T.p0 * 6, vi_b, bar);
-    tma_load(S.sOff + buf * FT_OFF_N, P.pt_off + off_lo, off_b, bar);
-    if (rs_b) tma_load(S.sRs + buf * FT_SEG_N, P.ft_rs + T.r0, rs_b, bar);
+    tma_load(S.sVi, P.pt_Vinv + (size_t)T.p0 * 6, vi_b, bar);
+    tma_load(S.sOff, P.pt_off + off_lo, off_b, bar);
+    if (rs_b) tma_load(S.sRs, P.ft_rs + T.r0, rs_b, bar);
 }
 
 // ACC (mat-vec only): the segment sums of an EPOCH (a few consecutive tiles of the CTA) are added up in shared
@@ -203,7 +205,7 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
         asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
         ft_issue_group1<MODE>(P, S, T, b, 0, S.bar);
-        ft_issue_group2(P, S, T, 0, S.bar + 1);
+        ft_issue_group2(P, S, T, S.bar + 1);
     }
     __syncthreads();
 
@@ -238,15 +240,17 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
             const double d2 = fma(x[0], X[1], fma(-x[1], X[0], x[5]));
             ax = j0.x * d0 + j0.y * d1 + j1.x * d2;
             ay = j1.y * d0 + j2.x * d1 + j2.y * d2;
-            S.sO[pos] = j0.x * ax + j1.y * ay;
-            S.sO[FT_LDB + pos] = j0.y * ax + j2.x * ay;
-            S.sO[2 * FT_LDB + pos] = j1.x * ax + j2.y * ay;
+            S.sA[pos] = j0.x * ax + j1.y * ay;
+            S.sA[FT_LDB + pos] = j0.y * ax + j2.x * ay;
+            S.sA[2 * FT_LDB + pos] = j1.x * ax + j2.y * ay;
         }
         mbar_wait(S.bar + 1, it & 1);  // every thread sees group 2 complete BEFORE the barrier, so re-arming is safe after it
         __syncthreads();
         if (MODE == 0 && have_next && issuer) {
+            // phase A has its operands in registers: observation records, Jacobian cache, points and the segment table of
+            // the next tile may land.  The next header goes to shared memory here; everybody reads it after later barriers.
             ft_issue_group1<MODE>(P, S, Tn, b, buf ^ 1, S.bar);
-            ft_issue_group2(P, S, Tn, buf ^ 1, S.bar + 1);
+            hs[0] = Tn.p0; hs[1] = Tn.m; hs[2] = Tn.o0; hs[3] = Tn.n; hs[4] = Tn.s0; hs[5] = Tn.ns; hs[6] = Tn.r0; hs[7] = Tn.maxlen;
         }
         if (ACC && tid >= FT_THREADS - 32 && (t - es[0]) % es[1] == 0) {
             // first tile of an epoch: the last warp (idle in phase B) fetches the rows of the epoch's slots; the
@@ -262,9 +266,9 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
         double acc[4] = {0.0, 0.0, 0.0, 0.0};  // MODE 1: g.dp, dp D dp, |dp|^2, |X|^2
         {
             const int k = tid & 3, lane = tid & 31;
-            const int* off = S.sOff + buf * FT_OFF_N + (T.p0 & 3);
-            const int* rsb = S.sRs + buf * FT_SEG_N;
-            const double* sVi = S.sVi + buf * FT_PTS * 6;
+            const int* off = S.sOff + (T.p0 & 3);
+            const int* rsb = S.sRs;
+            const double* sVi = S.sVi;
             for (int q0 = (tid & ~31) >> 2; q0 < T.m; q0 += FT_THREADS / 4) {  // warp-uniform bounds
                 const int q = q0 + (lane >> 2);
                 const bool valid = q < T.m;
@@ -272,7 +276,7 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
                 // neighbouring points read neighbouring words; tracks of a warp are (nearly) equally long
                 const int len = (valid && k < 3) ? off[q + 1] - off[q] : 0;
                 const int wmax = __reduce_max_sync(0xffffffffu, len);
-                const double* src = S.sO + k * FT_LDB + q;
+                const double* src = S.sA + k * FT_LDB + q;
                 double sk = 0.0;
                 for (int i0 = 0; i0 < wmax; i0 += 4) {  // loads first, then the (ordered) adds; x + 0.0 is exact
                     const int4 r4 = *reinterpret_cast<const int4*>(rsb + i0);  // broadcast
@@ -315,10 +319,15 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
             }
             if (have_next && issuer) {  // phase B has read the points: everything may be refilled now
                 ft_issue_group1<MODE>(P, S, Tn, b, buf ^ 1, S.bar);
-                ft_issue_group2(P, S, Tn, buf ^ 1, S.bar + 1);
+                ft_issue_group2(P, S, Tn, S.bar + 1);
+                hs[0] = Tn.p0; hs[1] = Tn.m; hs[2] = Tn.o0; hs[3] = Tn.n; hs[4] = Tn.s0; hs[5] = Tn.ns; hs[6] = Tn.r0; hs[7] = Tn.maxlen;
             }
+            if (!have_next) break;
+            __syncthreads();
         } else {
             __syncthreads();
+            // phase B is over: V^-1, track offsets and track rows of the next tile may land (single-buffered)
+            if (have_next && issuer) ft_issue_group2(P, S, Tn, S.bar + 1);
 
             // ---- phase C: camera-side product of every observation, parked at its tile-camera position --
             if (act) {
@@ -372,19 +381,15 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
                 S.sAcc[l] = 0.0;
             }
         };
-        if (!have_next) {
-            if (ACC) { __syncthreads(); flush(); }
-            break;
+        if (MODE == 0) {
+            // No barrier between phase D of this tile and phase A of the next: they use different scratch (sO / sA), and
+            // everything the next phase A reads arrived through the TMA.  Only the end of an epoch needs all of phase D.
+            const bool epoch_end = ACC && (!have_next || (t + 1 - es[0]) % es[1] == 0);
+            if (epoch_end) { __syncthreads(); flush(); }
+            if (!have_next) break;
         }
-        // the next tile's header travels from the issuing thread to everybody through shared memory
-        if (issuer) {
-            hs[0] = Tn.p0; hs[1] = Tn.m; hs[2] = Tn.o0; hs[3] = Tn.n; hs[4] = Tn.s0; hs[5] = Tn.ns; hs[6] = Tn.r0; hs[7] = Tn.maxlen;
-        }
-        __syncthreads();
-        {
-            T.p0 = hs[0]; T.m = hs[1]; T.o0 = hs[2]; T.n = hs[3]; T.s0 = hs[4]; T.ns = hs[5]; T.r0 = hs[6]; T.maxlen = hs[7];
-        }
-        if (ACC && (t + 1 - es[0]) % es[1] == 0) flush();
+        // the next tile's header was put into shared memory by the issuing thread before the last barrier(s)
+        T.p0 = hs[0]; T.m = hs[1]; T.o0 = hs[2]; T.n = hs[3]; T.s0 = hs[4]; T.ns = hs[5]; T.r0 = hs[6]; T.maxlen = hs[7];
         t = tn;
     }
 }

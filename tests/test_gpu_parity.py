@@ -167,7 +167,7 @@ def test_schur_matvec_against_dense_schur_complement(gpu_solver, monkeypatch, pa
     w = gpu_solver.schur_matvec(u, lam, schur_path=path)
     assert np.abs(w - w_ref).max() <= 1e-10 * np.abs(w_ref).max()
     info = gpu_solver.layout_info()
-    assert info["epoch_tiles"] > 0 and info["max_epoch_slots"] <= 72     # these scenes fit the accumulators
+    assert info["epoch_tiles"] > 0 and info["max_epoch_slots"] <= 96     # these scenes fit the accumulators
     assert info["matvec_rows"] <= info["segments"]
     if grid is not None and shape[2] >= 4000:
         assert info["matvec_rows"] < info["segments"] and info["epochs"] < info["point_tiles"]
