@@ -354,6 +354,49 @@ def test_long_track_spanning_tiles(gpu_solver):
     assert np.isfinite(st["final_cost"]) and st["final_cost"] <= st["initial_cost"]
 
 
+def _dense_visibility_problem(n_cams=300, n_pts=50, track=120, seed=21):
+    """Every point is seen by `track` random cameras that all look at the same small volume: a tile holds two points and
+    ~200 different cameras (internet-photo-collection structure, the opposite of the trajectory scenes)."""
+    rng = np.random.default_rng(seed)
+    rv_t = rng.normal(0, 0.08, (n_cams, 3))
+    tv_t = np.array([0.0, 0.0, 10.0]) + rng.normal(0, 0.5, (n_cams, 3))
+    X_t = rng.uniform(-1.5, 1.5, (n_pts, 3))
+    cam = np.concatenate([rng.choice(n_cams, track, replace=False) for _ in range(n_pts)])
+    pt = np.repeat(np.arange(n_pts), track)
+    uv = S.project(rv_t[cam], tv_t[cam], X_t[pt]) + rng.normal(0, 0.5, (cam.size, 2))
+    order = np.argsort(cam, kind="stable")
+    cam, pt, uv = cam[order], pt[order], uv[order].astype(np.float32).astype(np.float64)
+    rv0 = rv_t + rng.normal(0, 0.002, rv_t.shape); tv0 = tv_t + rng.normal(0, 0.01, tv_t.shape)
+    return S.FlatProblem(S.FX, S.FY, S.CX, S.CY, rv0[1:].copy(), tv0[1:].copy(), rv_t[0].copy(), tv_t[0].copy(),
+                         X_t + rng.normal(0, 0.03, X_t.shape), (cam - 1).astype(np.int32), pt.astype(np.int32), uv)
+
+
+def test_tiles_with_more_cameras_than_accumulator_slots(gpu_solver):
+    """When an epoch of even one tile needs more accumulator slots than fit, the tile pass writes one row per segment
+    (automatic `tiles_rows`); the mat-vec is still the dense Schur complement's and the solve the two-pass solve."""
+    fp = _dense_visibility_problem()
+    prob = O.Problem.from_flat(fp)
+    gpu_solver.set_flat(fp)
+    info = gpu_solver.layout_info()
+    assert info["point_tiles"] > 0 and info["epoch_tiles"] == 0 and info["max_epoch_slots"] > 96
+    assert info["matvec_rows"] == info["segments"]
+    lam = 1e-3
+    lin = L.linearize(prob, fp.rvec, fp.tvec, fp.pts)
+    _, _, _, aux = L.schur_step(prob, lin, lam)
+    u = np.random.default_rng(2).normal(size=(prob.n_cams, 6))
+    w_ref = (aux["S"] @ u.ravel()).reshape(-1, 6)
+    w = gpu_solver.schur_matvec(u, lam)
+    assert np.abs(w - w_ref).max() <= 1e-10 * np.abs(w_ref).max()
+    kw = dict(max_iters=6, pcg_tol=1e-10, pcg_max_iters=400, ftol=0.0, xtol=0.0, gtol=0.0)
+    a = gpu_solver.solve(**kw)
+    ks = gpu_solver.kernel_stats()
+    assert ks["schur_matvec_tiles"][0] > 0
+    gpu_solver.set_flat(fp)
+    b = gpu_solver.solve(schur_path="two_pass", **kw)
+    assert abs(a["final_cost"] - b["final_cost"]) <= 1e-9 * b["final_cost"]
+    assert a["final_cost"] < 0.2 * a["initial_cost"]
+
+
 def test_error_reporting(gpu_solver):
     from bundle_adjustment_b200._capi import BaError
     fp = S.make_flat_problem(4, 50, 150, seed=17)
