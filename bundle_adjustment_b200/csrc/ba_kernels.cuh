@@ -572,7 +572,7 @@ __host__ __device__ constexpr size_t cm_smem_bytes() {
 //               no barrier - faster when a camera has only a few hundred observations (many cameras, or a rank of a
 //               multi-GPU run that holds 1/N of every camera's observations).
 template <int KIND, bool WARP>
-__global__ void __launch_bounds__(CM_THREADS) k_camera_pass(Params P, const double* __restrict__ vec, int with_schur_diag) {
+__global__ void __launch_bounds__(CM_THREADS, 2) k_camera_pass(Params P, const double* __restrict__ vec, int with_schur_diag) {
     constexpr int N = CmN<KIND>::value;
     constexpr int NCH = CmCh<KIND>::value;
     __shared__ double red[WARP ? 1 : CM_THREADS / 32 * N];
@@ -591,9 +591,14 @@ __global__ void __launch_bounds__(CM_THREADS) k_camera_pass(Params P, const doub
     double acc[N];
 #pragma unroll
     for (int k = 0; k < N; ++k) acc[k] = 0.0;
+    // the record of the NEXT observation is fetched one trip ahead: its point index is the address of the gathers
+    double2 uv_next = make_double2(0.0, 0.0);
+    int p_next = 0;
+    if (lane < n) { uv_next = __ldg(P.cm_uv + o0 + lane); p_next = __ldg(P.cm_pt + o0 + lane); }
     for (int i = lane; i < n; i += STRIDE) {
-        const double2 uvr = __ldg(P.cm_uv + o0 + i);
-        const int p = __ldg(P.cm_pt + o0 + i);
+        const double2 uvr = uv_next;
+        const int p = p_next;
+        if (i + STRIDE < n) { uv_next = __ldg(P.cm_uv + o0 + i + STRIDE); p_next = __ldg(P.cm_pt + o0 + i + STRIDE); }
         double rec[2 * NCH];
         {
             load_pt(P, b, p, rec);
