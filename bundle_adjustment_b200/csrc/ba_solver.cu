@@ -398,6 +398,7 @@ struct ba_handle {
     bool fused_ok = false;
     // epoch accumulators of the mat-vec tile pass (ba_tiles.cuh); acc_ok = every epoch fits FT_ACC_CAP slots
     bool acc_ok = false;
+    bool tile_lin = false;  // point-side linearisation on the tiles (k_tile_lin) instead of the point-major kernel
     bool cm_warp = false;  // camera-major passes: one warp per tile instead of one CTA per tile
     int tail_cluster = 0;  // CTAs of the PCG tail cluster (ba_peer.cuh); 0 = tail kernel not usable for this problem
     int red_cluster = 1;   // CTAs of the scalar-reduction cluster
@@ -1092,6 +1093,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     P.ft_pt = h->ft_pt.p; P.ft_obs = h->ft_obs.p; P.ft_seg = h->ft_seg.p; P.tc_uv = h->tc_uv.p;
     P.ft_hdr = h->ft_hdr.p; P.tc_meta = h->tc_meta.p; P.pm_tc = h->fused_ok ? h->pm_tc.p : nullptr;
     P.tc_J = h->fused_ok ? h->tc_J.p : nullptr;
+    h->tile_lin = h->fused_ok && !getenv("BA_B200_NO_TILE_LIN");
     P.seg_cam = h->seg_cam.p; P.seg_info = h->seg_info.p; P.ft_rs = h->ft_rs.p; P.seg_row = h->seg_row.p; P.cam_row_off = h->cam_row_off.p;
     P.rows = h->rows.p;
     P.ep_target = 0; P.cta_ep0 = nullptr; P.ep_g0 = nullptr; P.slot_row = nullptr;
@@ -1155,7 +1157,8 @@ static void apply_robust(ba_handle* h, const ba_options* opt) {
 // linearise the point side at buffer `which` and reduce the cost scalars
 static void lin_points_and_cost(ba_handle* h, int which) {
     const Params& P = h->P;
-    launch(h, KN_LIN_PTS, k_lin_points, P.pm_tiles, PM_THREADS, h->smem_lin, P, which);
+    if (h->tile_lin) launch(h, KN_LIN_PTS, k_tile_lin, P.ft_tiles, FT_THREADS, 0, P, which);
+    else launch(h, KN_LIN_PTS, k_lin_points, P.pm_tiles, PM_THREADS, h->smem_lin, P, which);
 }
 
 static const unsigned MASK_LIN = (1u << S_COST) | (1u << S_RAW) | (1u << S_BAD) | (1u << S_GPMAX);

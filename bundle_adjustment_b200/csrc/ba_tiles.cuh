@@ -395,6 +395,93 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
 }
 
 // ---------------------------------------------------------------------------------------------
+// Point-side linearisation on the tiles (replaces k_lin_points when the tile layout exists): one CTA per
+// tile, one thread per observation in tile-camera order.  Against the point-major kernel the camera pose
+// is a broadcast load inside a camera run (not one gather per lane), the Jacobian cache is written at the
+// thread's own position (coalesced, not scattered through pm_tc) and the measurement comes from tc_uv.
+// The nine per-point sums (V 6, g_p 3) use the transposed track layout of the mat-vec: observation i of
+// local point q parks at rs[i] + q, thread (q, value) adds the track in observation order.
+// ---------------------------------------------------------------------------------------------
+constexpr int FT_LDL = FT_THREADS + 2;  // 2 mod 16 words: the nine values of two neighbouring points fall on (nearly) disjoint banks
+
+__global__ void __launch_bounds__(FT_THREADS) k_tile_lin(Params P, int which) {
+    __shared__ double sA[9 * FT_LDL];
+    __shared__ int sRs[FT_THREADS];
+    __shared__ int sOff[FT_PTS + 1];
+    __shared__ double red[FT_THREADS / 32 * 3];
+    __shared__ double tot[3];
+    const int b = resolve_buf(P.st, which);
+    const int tid = threadIdx.x;
+    const TileHdr T = tile_hdr(P, blockIdx.x);
+    const double* camR = P.cam_R + (size_t)b * (P.n_cams + 1) * 12;
+    if (tid < T.maxlen) sRs[tid] = __ldg(P.ft_rs + T.r0 + tid);
+    if (tid <= T.m) sOff[tid] = __ldg(P.pt_off + T.p0 + tid);
+    double acc[3] = {0.0, 0.0, 0.0};  // cost, raw, bad
+    if (tid < T.n) {
+        const int2 meta = __ldg(P.tc_meta + T.o0 + tid);
+        const double2 uv = __ldg(P.tc_uv + T.o0 + tid);
+        const int pos = (meta.y >> 10) & 1023;
+        double X[3], Rt[12];
+        load_cam(camR, meta.x, Rt);
+        load_pt(P, b, T.p0 + (meta.y & 1023), X);
+        ObsLin o;
+        linearize_obs(Rt, X, uv.x, uv.y, P.K, o);
+        double wHx, wgx, r0x, wHy, wgy, r0y;
+        robust_weights(o.rx, P.delta, P.mode, wHx, wgx, r0x);
+        robust_weights(o.ry, P.delta, P.mode, wHy, wgy, r0y);
+        acc[0] = 0.5 * (r0x + r0y);
+        acc[1] = o.rx * o.rx + o.ry * o.ry;
+        if (!(isfinite(o.rx) && isfinite(o.ry))) acc[2] = 1.0;
+        const double sx = sqrt(wHx), sy = sqrt(wHy);
+        double2* J = P.tc_J + (size_t)b * 3 * P.n_obs + T.o0 + tid;
+        J[0] = make_double2(sx * o.jx[0], sx * o.jx[1]);
+        J[P.n_obs] = make_double2(sx * o.jx[2], sy * o.jy[0]);
+        J[2 * (size_t)P.n_obs] = make_double2(sy * o.jy[1], sy * o.jy[2]);
+        const double ax = wHx * o.jx[0], bx = wHx * o.jx[1], cx = wHx * o.jx[2];
+        const double ay = wHy * o.jy[0], by = wHy * o.jy[1], cy = wHy * o.jy[2];
+        double* dst = sA + pos;
+        dst[0 * FT_LDL] = ax * o.jx[0] + ay * o.jy[0];
+        dst[1 * FT_LDL] = ax * o.jx[1] + ay * o.jy[1];
+        dst[2 * FT_LDL] = ax * o.jx[2] + ay * o.jy[2];
+        dst[3 * FT_LDL] = bx * o.jx[1] + by * o.jy[1];
+        dst[4 * FT_LDL] = bx * o.jx[2] + by * o.jy[2];
+        dst[5 * FT_LDL] = cx * o.jx[2] + cy * o.jy[2];
+        const double gx = wgx * o.rx, gy = wgy * o.ry;
+        dst[6 * FT_LDL] = o.jx[0] * gx + o.jy[0] * gy;
+        dst[7 * FT_LDL] = o.jx[1] * gx + o.jy[1] * gy;
+        dst[8 * FT_LDL] = o.jx[2] * gx + o.jy[2] * gy;
+    }
+    __syncthreads();
+    double gmax = 0.0;
+    double* V = P.pt_V + ((size_t)b * P.n_pts + T.p0) * 6;
+    double* G = P.pt_g + ((size_t)b * P.n_pts + T.p0) * 4;
+    for (int w = tid; w < T.m * 9; w += FT_THREADS) {
+        const int q = w / 9, k = w - 9 * q;
+        const int len = sOff[q + 1] - sOff[q];
+        const double* src = sA + k * FT_LDL + q;
+        double sk = 0.0;
+        for (int i = 0; i < len; ++i) sk += src[sRs[i]];
+        if (k < 6) {
+            V[q * 6 + k] = sk;
+        } else {
+            G[q * 4 + (k - 6)] = sk;
+            gmax = fmax(gmax, fabs(sk));
+        }
+    }
+    block_sum<3, FT_THREADS>(acc, red, tot);
+    __syncthreads();
+    const double wm = warp_max(gmax);
+    if ((tid & 31) == 0) red[tid >> 5] = wm;
+    __syncthreads();
+    if (tid == 0) {
+        double m = 0.0;
+        for (int i = 0; i < FT_THREADS / 32; ++i) m = fmax(m, red[i]);
+        double* out = P.pm_partial + (size_t)blockIdx.x * NSCAL;
+        out[S_COST] = tot[0]; out[S_RAW] = tot[1]; out[S_BAD] = tot[2]; out[S_GPMAX] = m;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // per-camera finish of the mat-vec rows: one warp per camera adds the camera's rows (contiguous,
 // fixed lane/shuffle order).  TO_ACC: write the sums to cam_acc (all-reduced by the caller, multi-GPU);
 // otherwise finish the PCG inner product here: w = sum + lambda D u, per-CTA partial of w.u.
