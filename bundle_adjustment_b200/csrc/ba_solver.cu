@@ -1157,7 +1157,7 @@ static void apply_robust(ba_handle* h, const ba_options* opt) {
 // linearise the point side at buffer `which` and reduce the cost scalars
 static void lin_points_and_cost(ba_handle* h, int which) {
     const Params& P = h->P;
-    if (h->tile_lin) launch(h, KN_LIN_PTS, k_tile_lin, P.ft_tiles, FT_THREADS, 0, P, which);
+    if (h->tile_lin) launch(h, KN_LIN_PTS, k_tile_lin, h->ft_grid, FT_THREADS, 0, P, which);
     else launch(h, KN_LIN_PTS, k_lin_points, P.pm_tiles, PM_THREADS, h->smem_lin, P, which);
 }
 

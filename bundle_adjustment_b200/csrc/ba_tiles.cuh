@@ -404,69 +404,112 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
 // ---------------------------------------------------------------------------------------------
 constexpr int FT_LDL = FT_THREADS + 2;  // 2 mod 16 words: the nine values of two neighbouring points fall on (nearly) disjoint banks
 
-__global__ void __launch_bounds__(FT_THREADS) k_tile_lin(Params P, int which) {
+BA_D void cp_async8(void* smem, const void* gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(smem_u32(smem)), "l"(gmem) : "memory");
+}
+BA_D void cp_async16(void* smem, const void* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(smem_u32(smem)), "l"(gmem) : "memory");
+}
+
+// Persistent CTAs over contiguous runs of tiles.  Every thread stages the record and the measurement of ITS
+// observation of the next tile with cp.async while the current tile is computed (a thread only reads what it
+// copied itself: cp.async.wait_group, no barrier), and the tile headers are fetched two tiles ahead - the chain
+// header -> record -> pose/point of a tile no longer sits in front of its arithmetic.
+__global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_lin(Params P, int which) {
     __shared__ double sA[9 * FT_LDL];
+    __shared__ __align__(16) double2 sUv[2][FT_THREADS];
+    __shared__ __align__(16) int2 sMeta[2][FT_THREADS];
     __shared__ int sRs[FT_THREADS];
     __shared__ int sOff[FT_PTS + 1];
     __shared__ double red[FT_THREADS / 32 * 3];
     __shared__ double tot[3];
     const int b = resolve_buf(P.st, which);
     const int tid = threadIdx.x;
-    const TileHdr T = tile_hdr(P, blockIdx.x);
+    int t = ft_cta_begin(blockIdx.x, P.ft_tiles, gridDim.x);
+    const int t_end = ft_cta_begin(blockIdx.x + 1, P.ft_tiles, gridDim.x);
     const double* camR = P.cam_R + (size_t)b * (P.n_cams + 1) * 12;
-    if (tid < T.maxlen) sRs[tid] = __ldg(P.ft_rs + T.r0 + tid);
-    if (tid <= T.m) sOff[tid] = __ldg(P.pt_off + T.p0 + tid);
+    double2* const Jb = P.tc_J + (size_t)b * 3 * P.n_obs;
+    double* const Vb = P.pt_V + (size_t)b * P.n_pts * 6;
+    double* const Gb = P.pt_g + (size_t)b * P.n_pts * 4;
     double acc[3] = {0.0, 0.0, 0.0};  // cost, raw, bad
-    if (tid < T.n) {
-        const int2 meta = __ldg(P.tc_meta + T.o0 + tid);
-        const double2 uv = __ldg(P.tc_uv + T.o0 + tid);
-        const int pos = (meta.y >> 10) & 1023;
-        double X[3], Rt[12];
-        load_cam(camR, meta.x, Rt);
-        load_pt(P, b, T.p0 + (meta.y & 1023), X);
-        ObsLin o;
-        linearize_obs(Rt, X, uv.x, uv.y, P.K, o);
-        double wHx, wgx, r0x, wHy, wgy, r0y;
-        robust_weights(o.rx, P.delta, P.mode, wHx, wgx, r0x);
-        robust_weights(o.ry, P.delta, P.mode, wHy, wgy, r0y);
-        acc[0] = 0.5 * (r0x + r0y);
-        acc[1] = o.rx * o.rx + o.ry * o.ry;
-        if (!(isfinite(o.rx) && isfinite(o.ry))) acc[2] = 1.0;
-        const double sx = sqrt(wHx), sy = sqrt(wHy);
-        double2* J = P.tc_J + (size_t)b * 3 * P.n_obs + T.o0 + tid;
-        J[0] = make_double2(sx * o.jx[0], sx * o.jx[1]);
-        J[P.n_obs] = make_double2(sx * o.jx[2], sy * o.jy[0]);
-        J[2 * (size_t)P.n_obs] = make_double2(sy * o.jy[1], sy * o.jy[2]);
-        const double ax = wHx * o.jx[0], bx = wHx * o.jx[1], cx = wHx * o.jx[2];
-        const double ay = wHy * o.jy[0], by = wHy * o.jy[1], cy = wHy * o.jy[2];
-        double* dst = sA + pos;
-        dst[0 * FT_LDL] = ax * o.jx[0] + ay * o.jy[0];
-        dst[1 * FT_LDL] = ax * o.jx[1] + ay * o.jy[1];
-        dst[2 * FT_LDL] = ax * o.jx[2] + ay * o.jy[2];
-        dst[3 * FT_LDL] = bx * o.jx[1] + by * o.jy[1];
-        dst[4 * FT_LDL] = bx * o.jx[2] + by * o.jy[2];
-        dst[5 * FT_LDL] = cx * o.jx[2] + cy * o.jy[2];
-        const double gx = wgx * o.rx, gy = wgy * o.ry;
-        dst[6 * FT_LDL] = o.jx[0] * gx + o.jy[0] * gy;
-        dst[7 * FT_LDL] = o.jx[1] * gx + o.jy[1] * gy;
-        dst[8 * FT_LDL] = o.jx[2] * gx + o.jy[2] * gy;
-    }
-    __syncthreads();
     double gmax = 0.0;
-    double* V = P.pt_V + ((size_t)b * P.n_pts + T.p0) * 6;
-    double* G = P.pt_g + ((size_t)b * P.n_pts + T.p0) * 4;
-    for (int w = tid; w < T.m * 9; w += FT_THREADS) {
-        const int q = w / 9, k = w - 9 * q;
-        const int len = sOff[q + 1] - sOff[q];
-        const double* src = sA + k * FT_LDL + q;
-        double sk = 0.0;
-        for (int i = 0; i < len; ++i) sk += src[sRs[i]];
-        if (k < 6) {
-            V[q * 6 + k] = sk;
-        } else {
-            G[q * 4 + (k - 6)] = sk;
-            gmax = fmax(gmax, fabs(sk));
+    auto stage = [&](int buf, const int4& h) {  // h = (p0, m, o0, n)
+        if (tid < h.w) {
+            cp_async16(&sUv[buf][tid], P.tc_uv + h.z + tid);
+            cp_async8(&sMeta[buf][tid], P.tc_meta + h.z + tid);
         }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+    int4 ha = make_int4(0, 0, 0, 0), han = ha;
+    if (t < t_end) {
+        ha = __ldg(P.ft_hdr + 2 * t);
+        han = t + 1 < t_end ? __ldg(P.ft_hdr + 2 * (t + 1)) : ha;
+        stage(0, ha);
+    }
+    for (int it = 0; t < t_end; ++t, ++it) {
+        const int buf = it & 1;
+        const int4 hann = t + 2 < t_end ? __ldg(P.ft_hdr + 2 * (t + 2)) : han;
+        const int4 hb = __ldg(P.ft_hdr + 2 * t + 1);  // (s0, ns, r0, maxlen)
+        const int p0 = ha.x, m = ha.y, o0 = ha.z, n = ha.w;
+        const int rsv = tid < hb.w ? __ldg(P.ft_rs + hb.z + tid) : 0;
+        const int offv = tid <= m ? __ldg(P.pt_off + p0 + tid) : 0;
+        if (t + 1 < t_end) stage(buf ^ 1, han);
+        else asm volatile("cp.async.commit_group;\n" ::: "memory");
+        asm volatile("cp.async.wait_group 1;\n" ::: "memory");  // this tile's copies (of this thread) have landed
+        if (tid < n) {
+            const int2 meta = sMeta[buf][tid];
+            const double2 uv = sUv[buf][tid];
+            const int pos = (meta.y >> 10) & 1023;
+            double X[3], Rt[12];
+            load_cam(camR, meta.x, Rt);
+            load_pt(P, b, p0 + (meta.y & 1023), X);
+            ObsLin o;
+            linearize_obs(Rt, X, uv.x, uv.y, P.K, o);
+            double wHx, wgx, r0x, wHy, wgy, r0y;
+            robust_weights(o.rx, P.delta, P.mode, wHx, wgx, r0x);
+            robust_weights(o.ry, P.delta, P.mode, wHy, wgy, r0y);
+            acc[0] += 0.5 * (r0x + r0y);
+            acc[1] += o.rx * o.rx + o.ry * o.ry;
+            if (!(isfinite(o.rx) && isfinite(o.ry))) acc[2] += 1.0;
+            const double sx = sqrt(wHx), sy = sqrt(wHy);
+            double2* J = Jb + o0 + tid;
+            J[0] = make_double2(sx * o.jx[0], sx * o.jx[1]);
+            J[P.n_obs] = make_double2(sx * o.jx[2], sy * o.jy[0]);
+            J[2 * (size_t)P.n_obs] = make_double2(sy * o.jy[1], sy * o.jy[2]);
+            const double ax = wHx * o.jx[0], bx = wHx * o.jx[1], cx = wHx * o.jx[2];
+            const double ay = wHy * o.jy[0], by = wHy * o.jy[1], cy = wHy * o.jy[2];
+            double* dst = sA + pos;
+            dst[0 * FT_LDL] = ax * o.jx[0] + ay * o.jy[0];
+            dst[1 * FT_LDL] = ax * o.jx[1] + ay * o.jy[1];
+            dst[2 * FT_LDL] = ax * o.jx[2] + ay * o.jy[2];
+            dst[3 * FT_LDL] = bx * o.jx[1] + by * o.jy[1];
+            dst[4 * FT_LDL] = bx * o.jx[2] + by * o.jy[2];
+            dst[5 * FT_LDL] = cx * o.jx[2] + cy * o.jy[2];
+            const double gx = wgx * o.rx, gy = wgy * o.ry;
+            dst[6 * FT_LDL] = o.jx[0] * gx + o.jy[0] * gy;
+            dst[7 * FT_LDL] = o.jx[1] * gx + o.jy[1] * gy;
+            dst[8 * FT_LDL] = o.jx[2] * gx + o.jy[2] * gy;
+        }
+        if (tid < hb.w) sRs[tid] = rsv;
+        if (tid <= m) sOff[tid] = offv;
+        __syncthreads();
+        double* V = Vb + (size_t)p0 * 6;
+        double* G = Gb + (size_t)p0 * 4;
+        for (int w = tid; w < m * 9; w += FT_THREADS) {
+            const int q = w / 9, k = w - 9 * q;
+            const int len = sOff[q + 1] - sOff[q];
+            const double* src = sA + k * FT_LDL + q;
+            double sk = 0.0;
+            for (int i = 0; i < len; ++i) sk += src[sRs[i]];
+            if (k < 6) {
+                V[q * 6 + k] = sk;
+            } else {
+                G[q * 4 + (k - 6)] = sk;
+                gmax = fmax(gmax, fabs(sk));
+            }
+        }
+        __syncthreads();  // the scratch and the track tables are rewritten by the next tile
+        ha = han; han = hann;
     }
     block_sum<3, FT_THREADS>(acc, red, tot);
     __syncthreads();
@@ -474,10 +517,10 @@ __global__ void __launch_bounds__(FT_THREADS) k_tile_lin(Params P, int which) {
     if ((tid & 31) == 0) red[tid >> 5] = wm;
     __syncthreads();
     if (tid == 0) {
-        double m = 0.0;
-        for (int i = 0; i < FT_THREADS / 32; ++i) m = fmax(m, red[i]);
+        double mx = 0.0;
+        for (int i = 0; i < FT_THREADS / 32; ++i) mx = fmax(mx, red[i]);
         double* out = P.pm_partial + (size_t)blockIdx.x * NSCAL;
-        out[S_COST] = tot[0]; out[S_RAW] = tot[1]; out[S_BAD] = tot[2]; out[S_GPMAX] = m;
+        out[S_COST] = tot[0]; out[S_RAW] = tot[1]; out[S_BAD] = tot[2]; out[S_GPMAX] = mx;
     }
 }
 
