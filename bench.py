@@ -175,6 +175,17 @@ def algorithmic_bytes(kernel, n_obs, n_obs_adj, n_pts, n_cams, n_seg=0, n_rows=N
     return None
 
 
+def algorithmic_flops(kernel, n_obs, n_pts):
+    """FP64 flops one launch must do (FMA = 2).  Tile mat-vec per observation: d = w x X + v (12), a = Jt d (10),
+    Jt^T a (12), track sum (3), b = a - Jt z (12), m = Jt^T b (12), X x m (9), segment sums (6) = 76; per point
+    z = Vinv s (15)."""
+    if kernel == "schur_matvec_tiles":
+        return 76 * n_obs + 15 * n_pts
+    if kernel == "backsub_tiles":
+        return 43 * n_obs + 40 * n_pts
+    return None
+
+
 def run_ours(args, rank, world, local_rank):
     # libraries (NCCL) may write to fd 1; keep the JSON line the only thing on stdout
     sys.stdout.flush()
@@ -289,7 +300,16 @@ def run_ours(args, rank, world, local_rank):
     if os.path.isfile(tpath) and world == 1:
         with open(tpath) as f:
             traffic = json.load(f).get(args.workload, {}).get(top)
+    # FP64 pipe (north_star: reported beside the HBM fraction): measured DFMA rate of this device against the
+    # arithmetic of the dominant kernel (FMA = 2 flops)
+    fp64_peak = solver.fp64_peak()
+    fl = algorithmic_flops(top, fp.n_obs, fp.n_pts)
+    fp64 = {"peak_tflops": fp64_peak, "kernel": top, "flops_per_launch": fl,
+            "achieved_tflops": (fl / (avg_ms * 1e-3) / 1e12) if fl else None,
+            "util": (fl / (avg_ms * 1e-3) / 1e12 / fp64_peak) if fl and fp64_peak > 0 else None,
+            "how": "ba_fp64_peak: 16 independent DFMA chains per thread, 8 CTAs x 256 threads per SM, best of 3 (CUDA events)"}
     roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "frac_of_nominal_8000": achieved / 8000.0, "fp64": fp64,
                 "traffic": traffic, "algorithmic_bytes_per_launch": ab, "avg_launch_us": 1e3 * avg_ms,
                 "launches_per_solve": ks[top][0], "share_of_kernel_time": ks[top][1] / max(total_kernel_ms, 1e-9),
                 "peak_source": peak_src, "layout": layout,

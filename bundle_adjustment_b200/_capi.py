@@ -68,6 +68,7 @@ SYMBOLS = {
     "ba_restore_initial": (C.c_int, [C.c_void_p]),
     "ba_timer_start": (C.c_int, [C.c_void_p]),
     "ba_timer_stop": (C.c_int, [C.c_void_p, _dp]),
+    "ba_fp64_peak": (C.c_int, [C.c_void_p, _dp]),
     "ba_residuals": (C.c_int, [C.c_void_p, _dp]),
     "ba_cost": (C.c_int, [C.c_void_p, C.c_double, _dp, _dp]),
     "ba_jacobian_blocks": (C.c_int, [C.c_void_p, _dp, _dp]),

@@ -714,6 +714,22 @@ __global__ void __launch_bounds__(CM_THREADS, 2) k_camera_pass(Params P, const d
     }
 }
 
+// FP64 FMA rate: 16 independent chains per thread, nothing else in the loop (ba_fp64_peak).
+__global__ void __launch_bounds__(256) k_fp64_peak(double* __restrict__ sink, int iters, double m) {
+    double a[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) a[k] = 1e-3 * (threadIdx.x + k);
+    const double c = 1e-7;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) a[k] = fma(a[k], m, c);
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) s += a[k];
+    sink[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 // Sum the tile partials of each camera in tile order: cam_acc[c*n_val + k] (k < n_val).
 __global__ void k_camera_sum(Params P, int n_val, int pcg_gated) {
     if (pcg_gated && P.st->pcg_done) return;

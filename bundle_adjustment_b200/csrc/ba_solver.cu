@@ -1524,6 +1524,31 @@ int ba_timer_stop(ba_handle* h, double* ms_out) {
     API_END
 }
 
+int ba_fp64_peak(ba_handle* h, double* tflops_out) {
+    API_BEGIN
+    ba::use(h);
+    if (!tflops_out) ba::fail(BA_ERR_ARG, "null pointer");
+    int sms = 0;
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
+    const int grid = sms * 8, block = 256, iters = 4096;
+    ba::DBuf<double> sink;
+    sink.alloc((size_t)grid * block);
+    double best = 0.0;
+    for (int rep = 0; rep < 4; ++rep) {  // the first one warms up
+        CK(cudaEventRecord(h->ev_user0, h->stream));
+        ba::k_fp64_peak<<<grid, block, 0, h->stream>>>(sink.p, iters, 1.0 + 1e-9 * rep);
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(h->ev_user1, h->stream));
+        CK(cudaEventSynchronize(h->ev_user1));
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, h->ev_user0, h->ev_user1));
+        const double flops = 2.0 * 16.0 * iters * (double)grid * block;
+        if (rep > 0) best = std::max(best, flops / (ms * 1e-3) / 1e12);
+    }
+    *tflops_out = best;
+    API_END
+}
+
 int ba_residuals(ba_handle* h, double* r_out) {
     API_BEGIN
     ba::need_problem(h);

@@ -120,6 +120,12 @@ class FlatSolver:
         api.check(api.lib().ba_timer_stop(self._h, C.byref(ms)))
         return ms.value
 
+    def fp64_peak(self) -> float:
+        """Measured FP64 FMA rate of the device in TFLOP/s (``ba_fp64_peak``)."""
+        v = C.c_double()
+        api.check(api.lib().ba_fp64_peak(self._h, C.byref(v)))
+        return v.value
+
     def get_params(self):
         nc, npt, _ = self._need()
         rvec, tvec, pts = np.empty((nc, 3)), np.empty((nc, 3)), np.empty((npt, 3))

@@ -131,6 +131,10 @@ int ba_restore_initial(ba_handle* h);
 int ba_timer_start(ba_handle* h);
 int ba_timer_stop(ba_handle* h, double* ms_out);
 
+/* Measured FP64 FMA rate of the device (dependent-free DFMA chains on every SM, CUDA events): the denominator of
+ * the "FP64 pipe utilisation" figure bench.py reports (not in MEASURED_PEAKS.json).  Needs no problem. */
+int ba_fp64_peak(ba_handle* h, double* tflops_out);
+
 /* r_out[2*n_obs] in the reference's observation order.  Replaces _cost_function
  * (src/bundle_adjuster.py:24-72). */
 int ba_residuals(ba_handle* h, double* r_out);
