@@ -14,13 +14,19 @@
 //                        (so all ranks get bit-identical sums, and the same bits run to run), and goes on
 //                        with what k_pcg_dots does: w = sum + lambda D u, partial of w.u.
 //
-// Two slots alternate by sequence parity: a rank can only be one exchange ahead of the slowest rank
-// (exchange n+1 needs everybody's flag n+1, which a rank sets after it has finished reading n), so slot
-// (n & 1) is never rewritten while a peer still reads exchange n.
+// PUSH (default) or PULL.  Pull is what is described above: a rank writes its own buffer, the peers poll and read
+// it over NVLink (two round trips after the slowest rank has published: flag, then data).  Push turns both
+// around: a rank STORES its partials into the slot it owns in EVERY rank's buffer, fences, and stores the flag into
+// every rank's buffer; the receivers poll and read LOCAL memory.  Stores are one-way and pipelined, so the exchange
+// costs one fence (the round trip that acknowledges the remote stores) instead of two dependent remote reads.
 //
-// Exchange buffer of a rank (doubles): [0] flag of slot 0, [1] flag of slot 1 (sequence numbers stored as
-// doubles' bit patterns are avoided: flags are 64-bit integers in the same words), [16 ...) slot 0 payload,
-// [16 + cap ...) slot 1 payload.
+// Two slot sets alternate by sequence parity: a rank can only be one exchange ahead of the slowest rank
+// (exchange n+1 needs everybody's flag n+1, which a rank sets after it has finished reading n), so the set
+// (n & 1) is never rewritten while a rank still reads exchange n.
+//
+// Exchange buffer of a rank (doubles): [parity * XB_MAX_RANKS + src] 64-bit flags = sequence number of the last
+// exchange whose partials of rank `src` are complete, then payload slots [parity][src][cap].  Pull uses only the
+// slots src = own rank of the own buffer.
 #pragma once
 #include "ba_tiles.cuh"
 
@@ -28,8 +34,31 @@
 
 namespace ba {
 
-constexpr int XB_HDR = 16;                 // doubles reserved in front of the payloads (flags, padding to 128 B)
+constexpr int XB_MAX_RANKS = 16;           // ranks that can exchange through peer memory (more: NCCL all-reduce)
+constexpr int XB_HDR = 2 * XB_MAX_RANKS;   // doubles reserved in front of the payloads (the flags)
 constexpr long long XB_SPIN_LIMIT = 1LL << 28;  // polls before a rank gives up on a peer (~ seconds) and flags an error
+__host__ __device__ inline size_t xb_slot(long long seq, int src, int nranks, int cap) {
+    return (size_t)XB_HDR + ((size_t)(seq & 1) * nranks + src) * cap;
+}
+// LL slots (k_pcg_tail, push == 2): every double travels as two 8-byte words (32 data bits | 32-bit sequence number), so
+// the data is its own flag - no fence, no flag store, no barrier between them (the scheme of NCCL's LL protocol; 8-byte
+// stores are single-copy atomic).  [parity][src][cap] pairs of words, behind the flag-synchronised slots.
+__host__ __device__ inline size_t xb_ll_base(int nranks, int cap) { return (size_t)XB_HDR + 2 * (size_t)nranks * cap; }
+__host__ __device__ inline size_t xb_doubles(int nranks, int cap) { return xb_ll_base(nranks, cap) + 4 * (size_t)nranks * cap; }
+BA_D ulonglong2* xb_ll_slot(double* buf, long long seq, int src, int nranks, int cap) {
+    return reinterpret_cast<ulonglong2*>(buf + xb_ll_base(nranks, cap)) + ((size_t)(seq & 1) * nranks + src) * cap;
+}
+BA_D void st_relaxed_sys_v2(ulonglong2* p, unsigned long long a, unsigned long long b) {
+    asm volatile("st.relaxed.sys.global.v2.b64 [%0], {%1, %2};\n" ::"l"(p), "l"(a), "l"(b) : "memory");
+}
+BA_D ulonglong2 ld_relaxed_sys_v2(const ulonglong2* p) {
+    ulonglong2 v;
+    asm volatile("ld.relaxed.sys.global.v2.b64 {%0, %1}, [%2];\n" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
+    return v;
+}
+BA_D long long* xb_flag(double* buf, long long seq, int src) {
+    return reinterpret_cast<long long*>(buf) + (seq & 1) * XB_MAX_RANKS + src;
+}
 
 BA_D void st_release_sys(long long* p, long long v) {
     asm volatile("st.release.sys.global.s64 [%0], %1;\n" ::"l"(p), "l"(v) : "memory");
@@ -41,14 +70,14 @@ BA_D long long ld_acquire_sys(const long long* p) {
 }
 
 // xstate: [0] sequence number of the last exchange this rank published, [1] ticket, [2] error flag
-__global__ void __launch_bounds__(RS_WARPS * 32) k_rows_finish_xchg(Params P, double* __restrict__ xbuf, int cap,
-                                                                    int* __restrict__ xstate) {
+__global__ void __launch_bounds__(RS_WARPS * 32) k_rows_finish_xchg(Params P, double* __restrict__ xbuf, double* const* __restrict__ peers,
+                                                                    int nranks, int rank, int push, int cap, int* __restrict__ xstate) {
     __shared__ int last;
     if (P.st->pcg_done) return;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int c = blockIdx.x * RS_WARPS + wid;
     const long long seq = (long long)xstate[0] + 1;  // only the last CTA changes xstate[0], after everybody has read it
-    double* slot = xbuf + XB_HDR + (size_t)(seq & 1) * cap;
+    const size_t slot = xb_slot(seq, rank, nranks, cap);
     if (c < P.n_cams) {
         const int r0 = __ldg(P.cam_row_off + c), r1 = __ldg(P.cam_row_off + c + 1);
         double a[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
@@ -59,44 +88,43 @@ __global__ void __launch_bounds__(RS_WARPS * 32) k_rows_finish_xchg(Params P, do
         }
 #pragma unroll
         for (int k = 0; k < 6; ++k) a[k] = warp_sum(a[k]);
-        if (lane == 0) {
-            double2* o = reinterpret_cast<double2*>(slot + (size_t)c * 6);
+        // push: lane d stores the camera's sums into rank d's buffer; pull: lane 0 into the own buffer
+        if (lane < (push ? nranks : 1)) {
+            double2* o = reinterpret_cast<double2*>((push ? peers[lane] : xbuf) + slot + (size_t)c * 6);
             o[0] = make_double2(a[0], a[1]); o[1] = make_double2(a[2], a[3]); o[2] = make_double2(a[4], a[5]);
         }
     }
+    __threadfence_system();  // this thread's stores, before the CTA's ticket
     __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence_system();  // this CTA's payload before its ticket
-        last = (atomicAdd(xstate + 1, 1) == (int)gridDim.x - 1);
-    }
+    if (threadIdx.x == 0) last = (atomicAdd(xstate + 1, 1) == (int)gridDim.x - 1);
     __syncthreads();
-    if (last && threadIdx.x == 0) {
-        __threadfence_system();
-        xstate[1] = 0;
-        xstate[0] = (int)seq;
-        st_release_sys(reinterpret_cast<long long*>(xbuf) + (seq & 1), seq);  // publish
+    if (last) {
+        if (threadIdx.x == 0) {
+            __threadfence_system();
+            xstate[1] = 0;
+            xstate[0] = (int)seq;
+        }
+        if (threadIdx.x < (push ? nranks : 1)) {
+            __threadfence_system();
+            st_release_sys(xb_flag(push ? peers[threadIdx.x] : xbuf, seq, rank), seq);  // publish
+        }
     }
 }
 
 // peers[r] = exchange buffer of rank r as mapped into this process (peers[own rank] = the local buffer)
-__global__ void __launch_bounds__(VEC_THREADS) k_pcg_dots_peer(Params P, double* const* __restrict__ peers, int nranks,
-                                                               int cap, int* __restrict__ xstate) {
+__global__ void __launch_bounds__(VEC_THREADS) k_pcg_dots_peer(Params P, double* __restrict__ xbuf, double* const* __restrict__ peers,
+                                                               int nranks, int push, int cap, int* __restrict__ xstate) {
     __shared__ double sm[VEC_THREADS / 32];
     __shared__ int ok;
     if (P.st->pcg_done) return;
     const long long seq = xstate[0];
-    const size_t slot_off = XB_HDR + (size_t)(seq & 1) * cap;
-    if (threadIdx.x == 0) {
-        int good = 1;
-        for (int r = 0; r < nranks && good; ++r) {
-            const long long* flag = reinterpret_cast<const long long*>(peers[r]) + (seq & 1);
-            long long spins = 0;
-            while (ld_acquire_sys(flag) < seq) {
-                if (++spins > XB_SPIN_LIMIT) { good = 0; break; }
-            }
-        }
-        if (!good) atomicExch(xstate + 2, 1);
-        ok = good;
+    if (threadIdx.x == 0) ok = 1;
+    __syncthreads();
+    if (threadIdx.x < nranks) {  // one thread per rank polls that rank's flag
+        const long long* flag = xb_flag(push ? xbuf : peers[threadIdx.x], seq, threadIdx.x);
+        long long spins = 0;
+        while (ld_acquire_sys(flag) < seq)
+            if (++spins > XB_SPIN_LIMIT) { atomicExch(xstate + 2, 1); ok = 0; break; }
     }
     __syncthreads();
     const int c = blockIdx.x * VEC_THREADS + threadIdx.x;
@@ -105,7 +133,7 @@ __global__ void __launch_bounds__(VEC_THREADS) k_pcg_dots_peer(Params P, double*
         const double lam = P.st->lambda;
         double w[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
         for (int r = 0; r < nranks; ++r) {  // rank order: identical bits on every rank
-            const double2* q = reinterpret_cast<const double2*>(peers[r] + slot_off + (size_t)c * 6);
+            const double2* q = reinterpret_cast<const double2*>((push ? xbuf : peers[r]) + xb_slot(seq, r, nranks, cap) + (size_t)c * 6);
             const double2 v0 = __ldcv(q), v1 = __ldcv(q + 1), v2 = __ldcv(q + 2);
             w[0] += v0.x; w[1] += v0.y; w[2] += v1.x; w[3] += v1.y; w[4] += v2.x; w[5] += v2.y;
         }
@@ -149,8 +177,8 @@ __host__ __device__ inline size_t pt_smem_bytes(int n_cams, int cluster) {
 
 template <bool PEER>
 __global__ void __launch_bounds__(PT_THREADS, 1) k_pcg_tail(Params P, double tol, int max_iters, double* __restrict__ xbuf,
-                                                            double* const* __restrict__ peers, int nranks, int cap,
-                                                            int* __restrict__ xstate) {
+                                                            double* const* __restrict__ peers, int nranks, int rank, int push,
+                                                            int cap, int* __restrict__ xstate) {
     extern __shared__ __align__(16) double dsm[];
     __shared__ double part_d[PT_MAX_CLUSTER];  // delta partials of all CTAs (every CTA gets all of them)
     __shared__ double part_g[PT_MAX_CLUSTER];  // gamma partials (CTA 0 only)
@@ -169,7 +197,6 @@ __global__ void __launch_bounds__(PT_THREADS, 1) k_pcg_tail(Params P, double tol
     const double gamma = st->gamma, alpha_prev = st->alpha, gamma_prev = st->gamma_prev, lam = st->lambda;
     const int first = (st->pcg_iter == 0);
     const long long seq = PEER ? (long long)xstate[0] + 1 : 0;
-    const size_t slot_off = PEER ? XB_HDR + (size_t)(seq & 1) * cap : 0;
 
     // ---- per-camera sums of this GPU's rows (camera-major, so a chunk's rows are one contiguous range):
     //      a group of `lpc` lanes per camera, all cameras of the chunk side by side --------------------------
@@ -196,27 +223,47 @@ __global__ void __launch_bounds__(PT_THREADS, 1) k_pcg_tail(Params P, double tol
 #pragma unroll
                 for (int k = 0; k < 6; ++k) a[k] += __shfl_down_sync(0xffffffffu, a[k], d, 32);
             if (li == 0 && valid) {
-                double2* o = reinterpret_cast<double2*>(PEER ? xbuf + slot_off + (size_t)c * 6 : sW + (size_t)(c - c0) * 6);
+                double2* o = reinterpret_cast<double2*>(sW + (size_t)(c - c0) * 6);
                 o[0] = make_double2(a[0], a[1]); o[1] = make_double2(a[2], a[3]); o[2] = make_double2(a[4], a[5]);
             }
         }
     }
     if (PEER) {
-        __threadfence_system();  // this thread's part of the slot, before the cluster says "complete"
-        cl.sync();
-        if (R == 0 && tid == 0) {
-            xstate[0] = (int)seq;
-            st_release_sys(reinterpret_cast<long long*>(xbuf) + (seq & 1), seq);  // publish
-        }
-        if (tid == 0) ok = 1;
         __syncthreads();
-        if (tid < nranks) {  // one thread per rank polls that rank's flag: the NVLink round trips overlap
-            const long long* flag = reinterpret_cast<const long long*>(peers[tid]) + (seq & 1);
-            long long spins = 0;
-            bool good = true;
-            while (ld_acquire_sys(flag) < seq)
-                if (++spins > XB_SPIN_LIMIT) { good = false; break; }
-            if (!good) { atomicExch(xstate + 2, 1); ok = 0; }
+        // the chunk's sums go (coalesced) into this rank's slot of every rank's buffer (push) or of the own buffer (pull)
+        const size_t slot = xb_slot(seq, rank, nranks, cap) + (size_t)c0 * 6;
+        if (push == 2) {
+            // LL: (data, sequence) words straight into every rank's buffer; the readers below spin on the words themselves
+            const unsigned long long f = (unsigned long long)(unsigned)seq << 32;
+            for (int e = tid; e < n_el; e += PT_THREADS) {
+                const unsigned long long bits = (unsigned long long)__double_as_longlong(sW[e]);
+                for (int d = 0; d < nranks; ++d)
+                    st_relaxed_sys_v2(xb_ll_slot(peers[d], seq, rank, nranks, cap) + (size_t)c0 * 6 + e, (bits & 0xffffffffull) | f, (bits >> 32) | f);
+            }
+            if (tid == 0) ok = 1;
+        } else {
+            for (int e = tid; e < n_el; e += PT_THREADS) {
+                const double v = sW[e];
+                if (push) {
+                    for (int d = 0; d < nranks; ++d) peers[d][slot + e] = v;
+                } else {
+                    xbuf[slot + e] = v;
+                }
+            }
+            __threadfence_system();  // this thread's part of the slot(s), before the cluster says "complete"
+            cl.sync();
+            if (R == 0 && tid < (push ? nranks : 1))
+                st_release_sys(xb_flag(push ? peers[tid] : xbuf, seq, rank), seq);  // publish
+            if (tid == 0) ok = 1;
+            __syncthreads();
+            if (tid < nranks) {  // one thread per rank polls that rank's flag (pull: the NVLink round trips overlap)
+                const long long* flag = xb_flag(push ? xbuf : peers[tid], seq, tid);
+                long long spins = 0;
+                bool good = true;
+                while (ld_acquire_sys(flag) < seq)
+                    if (++spins > XB_SPIN_LIMIT) { good = false; break; }
+                if (!good) { atomicExch(xstate + 2, 1); ok = 0; }
+            }
         }
     }
     __syncthreads();
@@ -226,12 +273,31 @@ __global__ void __launch_bounds__(PT_THREADS, 1) k_pcg_tail(Params P, double tol
     for (int e = tid; e < n_el; e += PT_THREADS) {
         const size_t i = (size_t)c0 * 6 + e;
         double w = 0.0;
-        if (PEER) {
+        if (PEER && push == 2) {
+            const unsigned f = (unsigned)seq;
+            for (int r0 = 0; r0 < nranks; r0 += 8) {  // eight loads in flight; a word that has not arrived yet is polled again
+                ulonglong2 v[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    if (r0 + j < nranks) v[j] = ld_relaxed_sys_v2(xb_ll_slot(xbuf, seq, r0 + j, nranks, cap) + i);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    if (r0 + j >= nranks) continue;
+                    long long spins = 0;
+                    while ((unsigned)(v[j].x >> 32) != f || (unsigned)(v[j].y >> 32) != f) {
+                        if (++spins > XB_SPIN_LIMIT) { atomicExch(xstate + 2, 1); break; }
+                        v[j] = ld_relaxed_sys_v2(xb_ll_slot(xbuf, seq, r0 + j, nranks, cap) + i);
+                    }
+                    w += __longlong_as_double((long long)((v[j].x & 0xffffffffull) | (v[j].y << 32)));
+                }
+            }
+        } else if (PEER) {
             if (ok)
-                for (int r0 = 0; r0 < nranks; r0 += 8) {  // eight remote loads in flight, then the adds in rank order
+                for (int r0 = 0; r0 < nranks; r0 += 8) {  // eight loads in flight, then the adds in rank order
                     double v[8];
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) v[j] = (r0 + j < nranks) ? __ldcv(peers[r0 + j] + slot_off + i) : 0.0;
+                    for (int j = 0; j < 8; ++j)
+                        v[j] = (r0 + j < nranks) ? __ldcv((push ? xbuf : peers[r0 + j]) + xb_slot(seq, r0 + j, nranks, cap) + i) : 0.0;
 #pragma unroll
                     for (int j = 0; j < 8; ++j) w += v[j];
                 }
@@ -280,6 +346,7 @@ __global__ void __launch_bounds__(PT_THREADS, 1) k_pcg_tail(Params P, double tol
     if (tid == 0) cl.map_shared_rank(part_g, 0)[R] = gpart;
     cl.sync();
     if (R == 0 && tid == 0) {
+        if (PEER) xstate[0] = (int)seq;  // read by every CTA at the start of the kernel, written after the last cluster barrier
         double g = 0.0;
         for (int r = 0; r < CL; ++r) g += part_g[r];
         st->gamma_prev = gamma;

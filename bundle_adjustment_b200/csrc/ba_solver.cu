@@ -417,6 +417,7 @@ struct ba_handle {
     // peer-memory exchange of the PCG mat-vec partials (ba_peer.cuh); multi-GPU handles only
     bool peer_ok = false;
     int xcap = 0;
+    int xpush = 2;  // exchange by remote loads (0, pull), remote stores + flags (1, push), remote stores of LL words (2)
     DBuf<double> xbuf;
     DBuf<int> xstate;
     DBuf<double*> d_peers;
@@ -807,13 +808,17 @@ static void setup_peer_exchange(ba_handle* h, int n_cams) {
     h->peer_ptr.assign(h->nranks, nullptr);
     h->peer_ok = false;
     h->xbuf.release();
-    h->xbuf.alloc((size_t)XB_HDR + 2 * (size_t)need);
+    h->xbuf.alloc(xb_doubles(h->nranks, need));
     h->xbuf.zero(s);
     h->xstate.alloc(4);
     h->xstate.zero(s);
     h->xcap = need;
     h->d_peers.alloc(h->nranks);
-    int good = getenv("BA_B200_NO_PEER") ? 0 : 1;
+    int good = (getenv("BA_B200_NO_PEER") || h->nranks > XB_MAX_RANKS) ? 0 : 1;
+    {
+        const char* e = getenv("BA_B200_XCHG");  // "pull": peers read this rank's buffer; default: this rank stores into theirs
+        h->xpush = (e && strcmp(e, "pull") == 0) ? 0 : (e && strcmp(e, "push") == 0) ? 1 : 2;  // 2 = push, LL words in the tail
+    }
     struct Card { cudaIpcMemHandle_t mem; char uuid[16]; } mine;
     memset(&mine, 0, sizeof mine);
     if (good && cudaIpcGetMemHandle(&mine.mem, h->xbuf.p) != cudaSuccess) { cudaGetLastError(); good = 0; }
@@ -1244,17 +1249,19 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
                     const size_t bytes = pt_smem_bytes(P.n_cams, h->tail_cluster);
                     if (h->nranks > 1)
                         launch_cluster(h, KN_PCG_TAIL, k_pcg_tail<true>, h->tail_cluster, PT_THREADS, bytes, PA, opt->pcg_tol, opt->pcg_max_iters,
-                                       h->xbuf.p, (double* const*)h->d_peers.p, h->nranks, h->xcap, h->xstate.p);
+                                       h->xbuf.p, (double* const*)h->d_peers.p, h->nranks, h->rank, h->xpush, h->xcap, h->xstate.p);
                     else
                         launch_cluster(h, KN_PCG_TAIL, k_pcg_tail<false>, h->tail_cluster, PT_THREADS, bytes, PA, opt->pcg_tol, opt->pcg_max_iters,
-                                       (double*)nullptr, (double* const*)nullptr, 1, 0, (int*)nullptr);
+                                       (double*)nullptr, (double* const*)nullptr, 1, 0, 0, 0, (int*)nullptr);
                     return;
                 }
                 if (tiles) {
                     launch_tile_matvec(h, PA, acc, h->v_u.p);
                     if (h->nranks > 1 && h->peer_ok) {  // exchange through peer memory, fused into both neighbours
-                        launch(h, KN_ROWS_XCHG, k_rows_finish_xchg, cdiv(P.n_cams, RS_WARPS), RS_WARPS * 32, 0, PA, h->xbuf.p, h->xcap, h->xstate.p);
-                        launch(h, KN_DOTS_PEER, k_pcg_dots_peer, P.vec_ctas, VEC_THREADS, 0, P, (double* const*)h->d_peers.p, h->nranks, h->xcap, h->xstate.p);
+                        launch(h, KN_ROWS_XCHG, k_rows_finish_xchg, cdiv(P.n_cams, RS_WARPS), RS_WARPS * 32, 0, PA, h->xbuf.p,
+                               (double* const*)h->d_peers.p, h->nranks, h->rank, h->xpush, h->xcap, h->xstate.p);
+                        launch(h, KN_DOTS_PEER, k_pcg_dots_peer, P.vec_ctas, VEC_THREADS, 0, P, h->xbuf.p, (double* const*)h->d_peers.p,
+                               h->nranks, h->xpush, h->xcap, h->xstate.p);
                     } else if (h->nranks > 1) {
                         launch(h, KN_ROWS_FIN, k_rows_finish<true>, cdiv(P.n_cams, RS_WARPS), RS_WARPS * 32, 0, PA);
                         allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 6);
