@@ -32,7 +32,7 @@ class Options(C.Structure):
                 ("lambda_min", C.c_double), ("lambda_max", C.c_double), ("precond", C.c_int32),
                 ("pcg_max_iters", C.c_int32), ("pcg_tol", C.c_double), ("pcg_check_every", C.c_int32),
                 ("verbose", C.c_int32), ("schur_path", C.c_int32), ("pcg_tail", C.c_int32),
-                ("reserved", C.c_int32 * 5)]
+                ("device_loop", C.c_int32), ("reserved", C.c_int32 * 4)]
 
 
 class Stats(C.Structure):

@@ -75,6 +75,12 @@ struct LMState {
     int pcg_done, pcg_iter, pcg_total;
     int bad;                 // non-finite seen
 };
+// the last step was rejected: the camera-side linearisation of the current point is still valid
+BA_D bool lin_gated(const LMState* st) { return st->iter > 0 && st->last_accepted == 0; }
+// Device-side loop control (conditional WHILE nodes of the solve graph, see solve()): 0 = no graph, nothing to set.
+BA_D void set_loop(unsigned long long handle, bool go_on) {
+    if (handle) cudaGraphSetConditional((cudaGraphConditionalHandle)handle, go_on ? 1u : 0u);
+}
 
 struct Params {
     Intr K;
@@ -150,6 +156,8 @@ struct Params {
     const int* ep_g0;         // [epochs+1 (+2 slack)] first accumulator slot (= row) of an epoch
     const int* slot_row;      // [slots] row of an accumulator slot (rows are camera-major)
     // partial sums
+    int lin_gate;        // device-side LM loop: the camera-side linearisation kernels return at once after a rejected step
+                         // (the host loop does not launch them then)
     double* cm_partial;  // [cm_tiles*27]
     double* pm_partial;  // [n_partial_rows*NSCAL]
     double* cam_partial; // [n_cams*NSCAL]
@@ -578,6 +586,7 @@ __global__ void __launch_bounds__(CM_THREADS, 2) k_camera_pass(Params P, const d
     __shared__ double red[WARP ? 1 : CM_THREADS / 32 * N];
     __shared__ double tot[WARP ? 1 : N];
     if (KIND == 2 && P.st->pcg_done) return;
+    if (KIND == 0 && P.lin_gate && lin_gated(P.st)) return;
     const int lane = WARP ? (threadIdx.x & 31) : threadIdx.x;
     constexpr int STRIDE = WARP ? 32 : CM_THREADS;
     const int tile_id = WARP ? blockIdx.x * (CM_THREADS / 32) + (threadIdx.x >> 5) : blockIdx.x;
@@ -731,8 +740,10 @@ __global__ void __launch_bounds__(256) k_fp64_peak(double* __restrict__ sink, in
 }
 
 // Sum the tile partials of each camera in tile order: cam_acc[c*n_val + k] (k < n_val).
-__global__ void k_camera_sum(Params P, int n_val, int pcg_gated) {
-    if (pcg_gated && P.st->pcg_done) return;
+// gated: 1 = part of a PCG iteration, 2 = part of the camera-side linearisation (device-side LM loop).
+__global__ void k_camera_sum(Params P, int n_val, int gated) {
+    if (gated == 1 && P.st->pcg_done) return;
+    if (gated == 2 && P.lin_gate && lin_gated(P.st)) return;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= P.n_cams * n_val) return;
     const int c = idx / n_val, k = idx - c * n_val;
@@ -744,6 +755,7 @@ __global__ void k_camera_sum(Params P, int n_val, int pcg_gated) {
 
 // After K-LINC (+ all-reduce): store U, g_c, D_c = clamp(diag U).
 __global__ void k_camera_finish_lin(Params P, double dmin, double dmax) {
+    if (P.lin_gate && lin_gated(P.st)) return;
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= P.n_cams) return;
     const double* a = P.cam_acc + (size_t)c * 27;
@@ -794,7 +806,8 @@ BA_D void minv_apply(const double* __restrict__ Minv, const double* __restrict__
 
 // After K-SCHURC (+ all-reduce): M_c = U_c + lambda D_c - corr_c, Minv_c; b_c = -g_c + (E Vinv g_p)_c;
 // PCG start: x = 0, r = b, u = Minv r, p = s = 0, gamma = r.u.
-__global__ void __launch_bounds__(VEC_THREADS) k_camera_finish_schur(Params P, int with_schur_diag, int* ticket) {
+__global__ void __launch_bounds__(VEC_THREADS) k_camera_finish_schur(Params P, int with_schur_diag, int* ticket,
+                                                                     unsigned long long pcg_loop) {
     __shared__ double sm[VEC_THREADS / 32];
     __shared__ int last;
     const int c = blockIdx.x * VEC_THREADS + threadIdx.x;
@@ -848,6 +861,7 @@ __global__ void __launch_bounds__(VEC_THREADS) k_camera_finish_schur(Params P, i
             st->gamma = g; st->gamma0 = g; st->gamma_prev = g; st->alpha = 0.0; st->beta = 0.0; st->pcg_iter = 0;
             st->pcg_done = !(g > 0.0);  // zero (or non-finite) right-hand side: nothing to solve
             *ticket = 0;
+            set_loop(pcg_loop, g > 0.0);
         }
     }
 }
@@ -1053,6 +1067,7 @@ __global__ void __launch_bounds__(RED_THREADS) k_reduce_scalars(Params P, unsign
 // gmax = max(|g_c|, |g_p|) at the current point; gtol test.
 __global__ void __launch_bounds__(RED_THREADS) k_gradient_check(Params P, double gtol) {
     __shared__ double sm[32];
+    if (P.lin_gate && lin_gated(P.st)) return;
     double v = 0.0;
     for (int i = threadIdx.x; i < P.n_cams * 6; i += RED_THREADS) v = fmax(v, fabs(P.cam_g[i]));
     v = warp_max(v);
@@ -1076,9 +1091,13 @@ __global__ void k_store_cost(Params P, int which) {
 }
 
 // Accept / reject the trial point, update the damping (Nielsen), test ftol / xtol.
-__global__ void k_lm_decide(Params P, double ftol, double xtol, double lam_min, double lam_max, int max_iters) {
+__global__ void k_lm_decide(Params P, double ftol, double xtol, double lam_min, double lam_max, int max_iters,
+                            unsigned long long lm_loop) {
     LMState* st = P.st;
-    if (st->status != 0) return;  // already terminated (gtol at the current point)
+    if (st->status != 0) {  // already terminated (gtol at the current point)
+        set_loop(lm_loop, false);
+        return;
+    }
     const double* s = st->scal;
     const int cur = st->cur, tri = cur ^ 1;
     const double cost_new = s[S_COST], raw_new = s[S_RAW];
@@ -1117,6 +1136,7 @@ __global__ void k_lm_decide(Params P, double ftol, double xtol, double lam_min, 
         if (st->status == 0 && st->lambda > lam_max) st->status = 5;
     }
     if (st->status == 0 && st->iter >= max_iters) st->status = 6;  // iteration limit (reported as 0)
+    set_loop(lm_loop, st->status == 0);
 }
 
 }  // namespace ba

@@ -178,7 +178,7 @@ __host__ __device__ inline size_t pt_smem_bytes(int n_cams, int cluster) {
 template <bool PEER>
 __global__ void __launch_bounds__(PT_THREADS, 1) k_pcg_tail(Params P, double tol, int max_iters, double* __restrict__ xbuf,
                                                             double* const* __restrict__ peers, int nranks, int rank, int push,
-                                                            int cap, int* __restrict__ xstate) {
+                                                            int cap, int* __restrict__ xstate, unsigned long long pcg_loop) {
     extern __shared__ __align__(16) double dsm[];
     __shared__ double part_d[PT_MAX_CLUSTER];  // delta partials of all CTAs (every CTA gets all of them)
     __shared__ double part_g[PT_MAX_CLUSTER];  // gamma partials (CTA 0 only)
@@ -353,7 +353,9 @@ __global__ void __launch_bounds__(PT_THREADS, 1) k_pcg_tail(Params P, double tol
         st->gamma = g; st->alpha = alpha; st->beta = beta;
         const int it = st->pcg_iter + 1;
         st->pcg_iter = it; st->pcg_total += 1;
-        if (!(alpha > 0.0) || !(g > tol * tol * st->gamma0) || it >= max_iters) st->pcg_done = 1;
+        const bool done = !(alpha > 0.0) || !(g > tol * tol * st->gamma0) || it >= max_iters;
+        if (done) st->pcg_done = 1;
+        set_loop(pcg_loop, !done);
     }
 }
 

@@ -1025,7 +1025,9 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     // tiles per SM); otherwise tiles of <= CM_TILE observations, one WARP each (shuffle-tree reductions only)
     h->cm_warp = n_cams > 0 && n_obs_adj / n_cams < 2 * CM_TILE;
     if (const char* e = getenv("BA_B200_CM_WARP")) h->cm_warp = atoi(e) != 0;
-    const int cm_len = h->cm_warp ? CM_TILE
+    // warp tiles: short enough that the device is full of warps (16 per SM) also on a window-sized problem - 4 cameras x 1500
+    // observations as 8 warps of 1024 took 45 us per pass, as 48 warps of 128 a few - but at least four trips of a warp
+    const int cm_len = h->cm_warp ? std::min(CM_TILE, std::max(128, cdiv(cdiv(n_obs_adj, 16 * h->sm_count), 32) * 32))
                                   : std::min(8 * CM_TILE, std::max(CM_TILE, cdiv(cdiv(n_obs_adj, 4 * h->sm_count), CM_THREADS) * CM_THREADS));
     for (int c = 0; c < n_cams; ++c) {
         tile_off[c] = (int)tiles.size();
@@ -1191,12 +1193,13 @@ static void lin_cameras(ba_handle* h, double dmin, double dmax) {
     const Params& P = h->P;
     if (P.n_cams == 0) return;
     launch_camera_pass<0>(h, KN_LIN_CAM, nullptr, 0);
-    launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 27, 256), 256, 0, P, 27, 0);
+    launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 27, 256), 256, 0, P, 27, 2);
     allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 27);
     launch(h, KN_CAM_FIN, k_camera_finish_lin, cdiv(P.n_cams, 128), 128, 0, P, dmin, dmax);
 }
 
 static const double kDiagMin = 1e-6, kDiagMax = 1e32;
+static const int kDeviceLoopMaxObs = 262144;  // largest problem the device-side LM / PCG loops are the default for
 
 static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     need_problem(h);
@@ -1231,8 +1234,11 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
 
     bool need_lin = true;
     int status = opt->max_iters == 0 ? 6 : 0;
-    while (status == 0) {
-        if (need_lin) {
+    unsigned long long pcg_loop = 0, lm_loop = 0;  // conditional handles of the device-side loops (0: host loops)
+
+    // ---- the three parts of one LM iteration ------------------------------------------------------------------
+    auto before_pcg = [&](bool lin) {
+        if (lin) {
             lin_cameras(h, kDiagMin, kDiagMax);
             launch(h, KN_GRAD, k_gradient_check, 1, RED_THREADS, 0, P, opt->gtol);
         }
@@ -1241,48 +1247,140 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
             launch_camera_pass<1>(h, KN_SCHUR_CAM, nullptr, with_schur);
             launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 27, 256), 256, 0, P, 27, 0);
             allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 27);
-            launch(h, KN_CAM_FIN, k_camera_finish_schur, P.vec_ctas, VEC_THREADS, 0, P, with_schur, h->ticket.p);
-            auto pcg_iteration = [&]() {
-                int n_dots = P.vec_ctas;
-                if (tiles && tail) {  // two kernels per iteration: the tile pass, then everything else in one cluster
-                    launch_tile_matvec(h, PA, acc, h->v_u.p);
-                    const size_t bytes = pt_smem_bytes(P.n_cams, h->tail_cluster);
-                    if (h->nranks > 1)
-                        launch_cluster(h, KN_PCG_TAIL, k_pcg_tail<true>, h->tail_cluster, PT_THREADS, bytes, PA, opt->pcg_tol, opt->pcg_max_iters,
-                                       h->xbuf.p, (double* const*)h->d_peers.p, h->nranks, h->rank, h->xpush, h->xcap, h->xstate.p);
-                    else
-                        launch_cluster(h, KN_PCG_TAIL, k_pcg_tail<false>, h->tail_cluster, PT_THREADS, bytes, PA, opt->pcg_tol, opt->pcg_max_iters,
-                                       (double*)nullptr, (double* const*)nullptr, 1, 0, 0, 0, (int*)nullptr);
-                    return;
-                }
-                if (tiles) {
-                    launch_tile_matvec(h, PA, acc, h->v_u.p);
-                    if (h->nranks > 1 && h->peer_ok) {  // exchange through peer memory, fused into both neighbours
-                        launch(h, KN_ROWS_XCHG, k_rows_finish_xchg, cdiv(P.n_cams, RS_WARPS), RS_WARPS * 32, 0, PA, h->xbuf.p,
-                               (double* const*)h->d_peers.p, h->nranks, h->rank, h->xpush, h->xcap, h->xstate.p);
-                        launch(h, KN_DOTS_PEER, k_pcg_dots_peer, P.vec_ctas, VEC_THREADS, 0, P, h->xbuf.p, (double* const*)h->d_peers.p,
-                               h->nranks, h->xpush, h->xcap, h->xstate.p);
-                    } else if (h->nranks > 1) {
-                        launch(h, KN_ROWS_FIN, k_rows_finish<true>, cdiv(P.n_cams, RS_WARPS), RS_WARPS * 32, 0, PA);
-                        allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 6);
-                        launch(h, KN_PCG_DOTS, k_pcg_dots<false>, P.vec_ctas, VEC_THREADS, 0, P);
-                    } else {
-                        n_dots = cdiv(P.n_cams, RS_WARPS);
-                        launch(h, KN_ROWS_FIN, k_rows_finish<false>, n_dots, RS_WARPS * 32, 0, PA);
-                    }
-                } else {
-                    launch(h, KN_PT_PASS, k_point_pass<0>, P.pm_tiles, PM_THREADS, h->smem_pass, P, (const double*)h->v_u.p);
-                    launch_camera_pass<2>(h, KN_MATVEC_CAM, h->v_u.p, 0);
-                    if (h->nranks > 1) {
-                        launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 6, 256), 256, 0, P, 6, 1);
-                        allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 6);
-                        launch(h, KN_PCG_DOTS, k_pcg_dots<false>, P.vec_ctas, VEC_THREADS, 0, P);
-                    } else {
-                        launch(h, KN_PCG_DOTS, k_pcg_dots<true>, P.vec_ctas, VEC_THREADS, 0, P);
-                    }
-                }
-                launch(h, KN_PCG_UPDATE, k_pcg_update, P.vec_ctas, VEC_THREADS, 0, P, opt->pcg_tol, opt->pcg_max_iters, n_dots, h->ticket.p);
-            };
+            launch(h, KN_CAM_FIN, k_camera_finish_schur, P.vec_ctas, VEC_THREADS, 0, P, with_schur, h->ticket.p, pcg_loop);
+        }
+    };
+    auto pcg_iteration = [&]() {
+        int n_dots = P.vec_ctas;
+        if (tiles && tail) {  // two kernels per iteration: the tile pass, then everything else in one cluster
+            launch_tile_matvec(h, PA, acc, h->v_u.p);
+            const size_t bytes = pt_smem_bytes(P.n_cams, h->tail_cluster);
+            if (h->nranks > 1)
+                launch_cluster(h, KN_PCG_TAIL, k_pcg_tail<true>, h->tail_cluster, PT_THREADS, bytes, PA, opt->pcg_tol, opt->pcg_max_iters,
+                               h->xbuf.p, (double* const*)h->d_peers.p, h->nranks, h->rank, h->xpush, h->xcap, h->xstate.p, pcg_loop);
+            else
+                launch_cluster(h, KN_PCG_TAIL, k_pcg_tail<false>, h->tail_cluster, PT_THREADS, bytes, PA, opt->pcg_tol, opt->pcg_max_iters,
+                               (double*)nullptr, (double* const*)nullptr, 1, 0, 0, 0, (int*)nullptr, pcg_loop);
+            return;
+        }
+        if (tiles) {
+            launch_tile_matvec(h, PA, acc, h->v_u.p);
+            if (h->nranks > 1 && h->peer_ok) {  // exchange through peer memory, fused into both neighbours
+                launch(h, KN_ROWS_XCHG, k_rows_finish_xchg, cdiv(P.n_cams, RS_WARPS), RS_WARPS * 32, 0, PA, h->xbuf.p,
+                       (double* const*)h->d_peers.p, h->nranks, h->rank, h->xpush, h->xcap, h->xstate.p);
+                launch(h, KN_DOTS_PEER, k_pcg_dots_peer, P.vec_ctas, VEC_THREADS, 0, P, h->xbuf.p, (double* const*)h->d_peers.p,
+                       h->nranks, h->xpush, h->xcap, h->xstate.p);
+            } else if (h->nranks > 1) {
+                launch(h, KN_ROWS_FIN, k_rows_finish<true>, cdiv(P.n_cams, RS_WARPS), RS_WARPS * 32, 0, PA);
+                allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 6);
+                launch(h, KN_PCG_DOTS, k_pcg_dots<false>, P.vec_ctas, VEC_THREADS, 0, P);
+            } else {
+                n_dots = cdiv(P.n_cams, RS_WARPS);
+                launch(h, KN_ROWS_FIN, k_rows_finish<false>, n_dots, RS_WARPS * 32, 0, PA);
+            }
+        } else {
+            launch(h, KN_PT_PASS, k_point_pass<0>, P.pm_tiles, PM_THREADS, h->smem_pass, P, (const double*)h->v_u.p);
+            launch_camera_pass<2>(h, KN_MATVEC_CAM, h->v_u.p, 0);
+            if (h->nranks > 1) {
+                launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 6, 256), 256, 0, P, 6, 1);
+                allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 6);
+                launch(h, KN_PCG_DOTS, k_pcg_dots<false>, P.vec_ctas, VEC_THREADS, 0, P);
+            } else {
+                launch(h, KN_PCG_DOTS, k_pcg_dots<true>, P.vec_ctas, VEC_THREADS, 0, P);
+            }
+        }
+        launch(h, KN_PCG_UPDATE, k_pcg_update, P.vec_ctas, VEC_THREADS, 0, P, opt->pcg_tol, opt->pcg_max_iters, n_dots, h->ticket.p);
+    };
+    auto after_pcg = [&]() {
+        if (tiles)
+            launch(h, KN_TILE_BACKSUB, k_tile_pass<1>, h->ft_grid, FT_THREADS, ft_smem_bytes(FT_ROWS_MV), P, (const double*)h->v_x.p);
+        else
+            launch(h, KN_BACKSUB, k_point_pass<1>, P.pm_tiles, PM_THREADS, h->smem_pass, P, (const double*)h->v_x.p);
+        launch(h, KN_CAM_UPDATE, k_camera_update, cdiv(nc1, 128), 128, 0, P);
+        lin_points_and_cost(h, 3);
+        reduce_scalars(h, MASK_LIN | MASK_STEP_PM, MASK_STEP_CAM);
+        launch(h, KN_DECIDE, k_lm_decide, 1, 1, 0, P, opt->ftol, opt->xtol, opt->lambda_min, opt->lambda_max, opt->max_iters, lm_loop);
+    };
+
+    // ---- device-side loops: the WHOLE solve is one CUDA graph - a conditional WHILE node over the LM iterations whose body
+    //      holds a second WHILE node over the PCG iterations; k_lm_decide / k_camera_finish_schur / k_pcg_tail set the two
+    //      conditions (cudaGraphSetConditional).  One graph launch and one state read-back per solve: no host round trip per
+    //      LM iteration or per batch of PCG iterations, which is what a window-sized problem spends its time on.
+    //      Single GPU, default kernel path; the host loops below serve everything else (and verbose / per-kernel timing).
+    //      Measured (profiles/r01j_ab_device_loop.txt): a WHILE trip costs about 2.8 us more than the same two kernels replayed
+    //      from a flat graph, so the device loops win only where the host round trips outweigh that - small problems
+    //      (window: 13.3 -> 12.5 ms, 100 k observations: 17.0 -> 16.4 ms; 680 k: 84.7 -> 89.5 ms, 5 M: 337 -> 345 ms).
+    //      device_loop = 1 therefore means "up to kDeviceLoopMaxObs observations", 2 = always.
+    const bool device_loop = status == 0 && (opt->device_loop == 2 || (opt->device_loop == 1 && P.n_obs <= kDeviceLoopMaxObs)) &&
+                             h->nranks == 1 && tiles && tail && P.n_cams > 0 && !h->time_kernels && !(opt->verbose & 1) &&
+                             !getenv("BA_B200_HOST_LOOP");
+    if (device_loop) {
+        long long before[KN_COUNT], per_lm[KN_COUNT], per_pcg[KN_COUNT];
+        memcpy(before, h->launches, sizeof before);
+        cudaGraph_t g = nullptr;
+        cudaGraphExec_t gx = nullptr;
+        CK(cudaGraphCreate(&g, 0));
+        try {
+            cudaGraphConditionalHandle hl = 0, hp = 0;
+            CK(cudaGraphConditionalHandleCreate(&hl, g, 1, cudaGraphCondAssignDefault));
+            cudaGraphNodeParams np = {};
+            np.type = cudaGraphNodeTypeConditional;
+            np.conditional.handle = hl; np.conditional.type = cudaGraphCondTypeWhile; np.conditional.size = 1;
+            cudaGraphNode_t lm_node = nullptr;
+            CK(cudaGraphAddNode(&lm_node, g, nullptr, 0, &np));
+            cudaGraph_t lm_body = np.conditional.phGraph_out[0];
+            CK(cudaGraphConditionalHandleCreate(&hp, lm_body, 0, 0));
+            lm_loop = (unsigned long long)hl; pcg_loop = (unsigned long long)hp;
+            h->P.lin_gate = 1;  // the linearisation kernels are always in the graph and return at once after a rejected step
+            // first part of the body; the PCG loop hangs off its last node
+            CK(cudaStreamBeginCaptureToGraph(s, lm_body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
+            before_pcg(true);
+            cudaStreamCaptureStatus cs;
+            const cudaGraphNode_t* deps = nullptr;
+            size_t n_deps = 0;
+            CK(cudaStreamGetCaptureInfo(s, &cs, nullptr, nullptr, &deps, &n_deps));
+            std::vector<cudaGraphNode_t> last(deps, deps + n_deps);
+            CK(cudaStreamEndCapture(s, nullptr));
+            cudaGraphNodeParams pp = {};
+            pp.type = cudaGraphNodeTypeConditional;
+            pp.conditional.handle = hp; pp.conditional.type = cudaGraphCondTypeWhile; pp.conditional.size = 1;
+            cudaGraphNode_t pcg_node = nullptr;
+            CK(cudaGraphAddNode(&pcg_node, lm_body, last.data(), last.size(), &pp));
+            cudaGraph_t pcg_body = pp.conditional.phGraph_out[0];
+            for (int k = 0; k < KN_COUNT; ++k) per_lm[k] = h->launches[k] - before[k];
+            CK(cudaStreamBeginCaptureToGraph(s, pcg_body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
+            pcg_iteration();
+            CK(cudaStreamEndCapture(s, nullptr));
+            for (int k = 0; k < KN_COUNT; ++k) per_pcg[k] = h->launches[k] - before[k] - per_lm[k];
+            CK(cudaStreamBeginCaptureToGraph(s, lm_body, &pcg_node, nullptr, 1, cudaStreamCaptureModeThreadLocal));
+            after_pcg();
+            CK(cudaStreamEndCapture(s, nullptr));
+            for (int k = 0; k < KN_COUNT; ++k) per_lm[k] = h->launches[k] - before[k] - per_pcg[k];
+            h->P.lin_gate = 0;
+            lm_loop = pcg_loop = 0;
+            CK(cudaGraphInstantiate(&gx, g, 0));
+            CK(cudaGraphLaunch(gx, s));
+            read_state(h);
+        } catch (...) {
+            h->P.lin_gate = 0;
+            cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+            if (cudaStreamIsCapturing(s, &cs) == cudaSuccess && cs != cudaStreamCaptureStatusNone) cudaStreamEndCapture(s, nullptr);
+            cudaGetLastError();
+            if (gx) cudaGraphExecDestroy(gx);
+            cudaGraphDestroy(g);
+            throw;
+        }
+        CK(cudaGraphExecDestroy(gx));
+        CK(cudaGraphDestroy(g));
+        const LMState& st = *h->h_state;
+        status = st.status;
+        // a pass that ended on the gradient test ran its kernels without counting as an iteration
+        const long long passes = st.iter + (st.status == 1 ? 1 : 0);
+        for (int k = 0; k < KN_COUNT; ++k) h->launches[k] = before[k] + per_lm[k] * passes + per_pcg[k] * st.pcg_total;
+    }
+    while (status == 0) {
+        before_pcg(need_lin);
+        if (P.n_cams > 0) {
             auto pcg_converged = [&]() {
                 CK(cudaMemcpyAsync(h->h_flag, &h->st.p->pcg_done, sizeof(int), cudaMemcpyDeviceToHost, s));
                 CK(cudaStreamSynchronize(s));
@@ -1313,14 +1411,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
                 }
             }
         }
-        if (tiles)
-            launch(h, KN_TILE_BACKSUB, k_tile_pass<1>, h->ft_grid, FT_THREADS, ft_smem_bytes(FT_ROWS_MV), P, (const double*)h->v_x.p);
-        else
-            launch(h, KN_BACKSUB, k_point_pass<1>, P.pm_tiles, PM_THREADS, h->smem_pass, P, (const double*)h->v_x.p);
-        launch(h, KN_CAM_UPDATE, k_camera_update, cdiv(nc1, 128), 128, 0, P);
-        lin_points_and_cost(h, 3);
-        reduce_scalars(h, MASK_LIN | MASK_STEP_PM, MASK_STEP_CAM);
-        launch(h, KN_DECIDE, k_lm_decide, 1, 1, 0, P, opt->ftol, opt->xtol, opt->lambda_min, opt->lambda_max, opt->max_iters);
+        after_pcg();
         read_state(h);
         const LMState& st = *h->h_state;
         status = st.status;
@@ -1393,6 +1484,7 @@ void ba_default_options(ba_options* o) {
     o->verbose = 0;
     o->schur_path = BA_PATH_TILES;
     o->pcg_tail = 1;
+    o->device_loop = 1;
 }
 
 int ba_create(int device, ba_handle** out) {

@@ -68,7 +68,11 @@ typedef struct ba_options {
     int32_t schur_path;       /* BA_PATH_*                                                          */
     int32_t pcg_tail;         /* 1 (default): everything between two tile passes of a PCG iteration runs in ONE
                                  thread-block-cluster kernel; 0: row finish / inner products / update kernels */
-    int32_t reserved[5];
+    int32_t device_loop;      /* single-GPU solves on the default kernel path can run as ONE CUDA graph whose conditional WHILE
+                                 nodes loop over the LM and the PCG iterations on the device (one launch and one read-back per
+                                 solve).  1 (default): for problems of up to 262144 observations (where it is faster); 2: always;
+                                 0: the host drives the loops (always the case for verbose / timed / multi-GPU solves) */
+    int32_t reserved[4];
 } ba_options;
 
 typedef struct ba_stats {

@@ -266,6 +266,28 @@ def test_bitwise_reproducible(gpu_solver):
     assert outs[0][1] == outs[1][1] and outs[0][2] == outs[1][2]
 
 
+@pytest.mark.parametrize("lam0", [1e-4, 1e-9])
+def test_device_side_loops_match_host_loops(gpu_solver, lam0):
+    """The solve as ONE graph with conditional WHILE nodes (LM loop, PCG loop inside) runs the same kernels with the same
+    arguments as the host-driven loops: identical bits, iteration counts and launch accounting - also when steps are
+    rejected (tiny initial damping on a rough start) and when the solve stops on a tolerance."""
+    fp = S.make_flat_problem(30, 3000, 14000, seed=11)
+    if lam0 < 1e-6:  # a rough start with next to no damping: the first steps overshoot and are rejected
+        rng = np.random.default_rng(5)
+        fp.tvec = fp.tvec + rng.normal(0, 0.15, fp.tvec.shape)
+        fp.pts = fp.pts + rng.normal(0, 0.3, fp.pts.shape)
+    outs = []
+    for mode in (2, 0, 2):
+        gpu_solver.set_flat(fp)
+        st = gpu_solver.solve(max_iters=25, initial_lambda=lam0, device_loop=mode, ftol=1e-4)
+        outs.append((gpu_solver.get_x(), st))
+    (x_d, st_d), (x_h, st_h), (x_d2, _) = outs
+    assert np.array_equal(x_d, x_h) and np.array_equal(x_d, x_d2)
+    for k in ("status", "iterations", "accepted", "rejected", "pcg_iterations", "final_cost", "final_raw_cost", "gradient_max", "final_lambda"):
+        assert st_d[k] == st_h[k], k
+    assert st_d["launches"] <= st_h["launches"]          # no early-exit launches of a converged PCG batch
+
+
 def test_observation_order_does_not_matter(gpu_solver):
     """The device builds its own point-major / camera-major orders: permuting the input rows only
     permutes the residual vector."""
