@@ -209,6 +209,8 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
     }
     __syncthreads();
 
+    int ep_pos = 0;  // tiles of the current epoch that are behind this one (a counter instead of (t - es[0]) % es[1]: a
+                     // division by a run-time value in every thread and tile was 7 % of the pass's instructions)
     for (unsigned it = 0;; ++it) {
         const int buf = it & 1;
         const int tn = t + 1;
@@ -252,7 +254,7 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
             ft_issue_group1<MODE>(P, S, Tn, b, buf ^ 1, S.bar);
             hs[0] = Tn.p0; hs[1] = Tn.m; hs[2] = Tn.o0; hs[3] = Tn.n; hs[4] = Tn.s0; hs[5] = Tn.ns; hs[6] = Tn.r0; hs[7] = Tn.maxlen;
         }
-        if (ACC && tid >= FT_THREADS - 32 && (t - es[0]) % es[1] == 0) {
+        if (ACC && tid >= FT_THREADS - 32 && ep_pos == 0) {
             // first tile of an epoch: the last warp (idle in phase B) fetches the rows of the epoch's slots; the
             // previous epoch was flushed before the barrier above, this one is flushed after later barriers
             const int ep = es[2] + (t - es[0]) / es[1];
@@ -384,7 +386,8 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
         if (MODE == 0) {
             // No barrier between phase D of this tile and phase A of the next: they use different scratch (sO / sA), and
             // everything the next phase A reads arrived through the TMA.  Only the end of an epoch needs all of phase D.
-            const bool epoch_end = ACC && (!have_next || (t + 1 - es[0]) % es[1] == 0);
+            const bool epoch_end = ACC && (!have_next || ep_pos + 1 == es[1]);
+            ep_pos = epoch_end ? 0 : ep_pos + 1;
             if (epoch_end) { __syncthreads(); flush(); }
             if (!have_next) break;
         }
