@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(RS_WARPS * 32) k_rows_finish_xchg(Params P, do
             a[0] += v0.x; a[1] += v0.y; a[2] += v1.x; a[3] += v1.y; a[4] += v2.x; a[5] += v2.y;
         }
 #pragma unroll
-        for (int k = 0; k < 6; ++k) a[k] = warp_sum(a[k]);
+        for (int k = 0; k < 6; ++k) a[k] = __shfl_sync(0xffffffffu, warp_sum(a[k]), 0);  // the total is lane 0's
         // push: lane d stores the camera's sums into rank d's buffer; pull: lane 0 into the own buffer
         if (lane < (push ? nranks : 1)) {
             double2* o = reinterpret_cast<double2*>((push ? peers[lane] : xbuf) + slot + (size_t)c * 6);

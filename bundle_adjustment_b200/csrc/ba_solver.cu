@@ -1266,10 +1266,12 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
         if (tiles) {
             launch_tile_matvec(h, PA, acc, h->v_u.p);
             if (h->nranks > 1 && h->peer_ok) {  // exchange through peer memory, fused into both neighbours
+                // the separate kernels keep the pull protocol unless BA_B200_XCHG=push asks for remote stores
+                const int xp = h->xpush == 1 ? 1 : 0;
                 launch(h, KN_ROWS_XCHG, k_rows_finish_xchg, cdiv(P.n_cams, RS_WARPS), RS_WARPS * 32, 0, PA, h->xbuf.p,
-                       (double* const*)h->d_peers.p, h->nranks, h->rank, h->xpush, h->xcap, h->xstate.p);
+                       (double* const*)h->d_peers.p, h->nranks, h->rank, xp, h->xcap, h->xstate.p);
                 launch(h, KN_DOTS_PEER, k_pcg_dots_peer, P.vec_ctas, VEC_THREADS, 0, P, h->xbuf.p, (double* const*)h->d_peers.p,
-                       h->nranks, h->xpush, h->xcap, h->xstate.p);
+                       h->nranks, xp, h->xcap, h->xstate.p);
             } else if (h->nranks > 1) {
                 launch(h, KN_ROWS_FIN, k_rows_finish<true>, cdiv(P.n_cams, RS_WARPS), RS_WARPS * 32, 0, PA);
                 allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 6);

@@ -1,0 +1,35 @@
+"""One rank of the multi-GPU test (launched by tests/test_gpu_multi.py through torch.distributed.run)."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from bundle_adjustment_b200 import FlatSolver, sharding, synthetic as S  # noqa: E402
+
+
+def main(out_path, pcg_tail):
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+    if rank == 0:
+        idt = torch.tensor(list(FlatSolver.nccl_unique_id()), dtype=torch.uint8, device="cuda")
+    dist.broadcast(idt, 0)
+    fp = S.make_flat_problem(60, 20000, 100000, seed=21)
+    shard, (lo, hi) = sharding.shard_problem(fp, rank, world)
+    with FlatSolver(local, rank=rank, nranks=world, nccl_id=bytes(idt.cpu().tolist())) as s:
+        s.set_flat(shard)
+        st = s.solve(max_iters=8, pcg_tail=pcg_tail)
+        rvec, tvec, pts = s.get_params()
+    np.savez(f"{out_path}.rank{rank}.npz", rvec=rvec, tvec=tvec, pts=pts, lo=lo, hi=hi, cost=st["final_cost"],
+             pcg=st["pcg_iterations"], iters=st["iterations"], status=st["status"])
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main(sys.argv[1], int(sys.argv[2]))
