@@ -40,6 +40,34 @@ def test_struct_sizes_match_header():
     assert ctypes.sizeof(_capi.Stats) == 6 * 4 + 7 * 8 + 8 * 8
 
 
+def test_struct_layout_against_the_compiled_header(tmp_path):
+    """The ctypes mirrors of ba_options / ba_stats against the header itself, compiled with gcc: size and the offset of
+    every field, and the defaults of the fields added last."""
+    import shutil
+    import subprocess
+    if not shutil.which("gcc"):
+        pytest.skip("no gcc")
+    fields = {"ba_options": [n for n, _ in _capi.Options._fields_], "ba_stats": [n for n, _ in _capi.Stats._fields_]}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "ba_b200.h"', 'int main(void) {']
+    for st, names in fields.items():
+        lines.append(f'printf("{st} %zu\\n", sizeof({st}));')
+        lines += [f'printf("{st}.{n} %zu\\n", offsetof({st}, {n}));' for n in names]
+    lines += ['return 0; }']
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    subprocess.run(["gcc", "-I", os.path.join(root, "include"), "-o", str(exe), str(src)], check=True)
+    out = dict(l.split() for l in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.splitlines())
+    for st, cls in (("ba_options", _capi.Options), ("ba_stats", _capi.Stats)):
+        assert int(out[st]) == ctypes.sizeof(cls), st
+        for n, _ in cls._fields_:
+            assert int(out[f"{st}.{n}"]) == getattr(cls, n).offset, (st, n)
+    o = _capi.Options()
+    _capi.lib().ba_default_options(ctypes.byref(o))
+    assert o.pcg_tail == 1 and o.device_loop == 1 and list(o.reserved) == [0, 0, 0, 0]
+
+
 def test_geometry_matches_oracle():
     rng = np.random.default_rng(1)
     for _ in range(100):
