@@ -34,8 +34,8 @@ constexpr int FT_THREADS = 256;        // threads per CTA = observation capacity
 constexpr int FT_PTS = 128;            // point capacity of a tile
 constexpr int FT_CTAS_PER_SM = 1024 / FT_THREADS;  // register file: 64 registers per thread
 constexpr int FT_SEG_MAX = 16;         // observations per segment (one output row each)
-constexpr int FT_LD = FT_THREADS + 2;  // row stride of the camera-side scratch (phases C/D): 2*FT_LD mod 32 = 4 banks, so the
-                                       // six components of one segment fall on different banks
+constexpr int FT_LD = FT_THREADS + 3;  // row stride of the camera-side scratch (phases C/D), in double2: three rows of value PAIRS
+                                       // (xm0,xm1) (xm2,mm0) (mm1,mm2); 3 mod 8 sixteen-byte bank groups between the pairs of a segment
 constexpr int FT_LDB = FT_THREADS + 4; // row stride of the point-side scratch (phases A/B): 2*FT_LDB mod 32 = 8 banks, so the
                                        // three rows read by the four points of a half-warp are disjoint
 constexpr int FT_ROWS_MV = 6;          // scratch rows of the mat-vec pass
@@ -340,36 +340,35 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
                 const double mm[3] = {j0.x * bx + j1.y * by, j0.y * bx + j2.x * by, j1.x * bx + j2.y * by};
                 double xm[3];
                 cross3(X, mm, xm);
-#pragma unroll
-                for (int k = 0; k < 3; ++k) { S.sO[k * FT_LD + tid] = xm[k]; S.sO[(3 + k) * FT_LD + tid] = mm[k]; }
+                double2* o2 = reinterpret_cast<double2*>(S.sO) + tid;  // three 16-byte stores instead of six 8-byte ones
+                o2[0] = make_double2(xm[0], xm[1]); o2[FT_LD] = make_double2(xm[2], mm[0]); o2[2 * FT_LD] = make_double2(mm[1], mm[2]);
             }
             __syncthreads();
 
-            // ---- phase D: one thread per (segment, component): fixed-order sum -> one row per segment ---
+            // ---- phase D: one thread per (segment, pair of components): fixed-order sum -> one row per segment ---
             const int* seg_i = S.sSeg + buf * FT_SEG_N + (T.s0 & 3);
             const int* seg_r = S.sRow + buf * FT_SEG_N + (T.s0 & 3);
-            for (int w0 = tid & ~31; w0 < T.ns * 6; w0 += FT_THREADS) {  // warp-uniform bounds
+            for (int w0 = tid & ~31; w0 < T.ns * 3; w0 += FT_THREADS) {  // warp-uniform bounds
                 const int w = w0 + (tid & 31);
-                const bool valid = w < T.ns * 6;
-                const int seg = w / 6, k = w - 6 * seg;
+                const bool valid = w < T.ns * 3;
+                const int seg = w / 3, pr = w - 3 * seg;
                 const int info = valid ? seg_i[seg] : 0;  // first tile-camera position | length << 16; longest first
                 const int a = info & 0xffff, len = info >> 16;
                 const int wmax = __reduce_max_sync(0xffffffffu, len);
-                const double* src = S.sO + k * FT_LD + a;
+                const double2* src = reinterpret_cast<const double2*>(S.sO) + pr * FT_LD + a;
                 // a slot occurs at most once per tile; its running sum is fetched ahead of the segment's loop
-                double* slot = ACC ? S.sAcc + (valid ? seg_r[seg] * 6 + k : 0) : nullptr;
-                const double before = (ACC && valid) ? *slot : 0.0;
-                double sum = 0.0;
-                for (int j0 = 0; j0 < wmax; j0 += 4) {
-                    double v[4];
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) v[j] = (j0 + j < len) ? src[j0 + j] : 0.0;
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) sum += v[j];
+                double2* slot = ACC ? reinterpret_cast<double2*>(S.sAcc + (valid ? seg_r[seg] * 6 + 2 * pr : 0)) : nullptr;
+                const double2 before = (ACC && valid) ? *slot : make_double2(0.0, 0.0);
+                double sx = 0.0, sy = 0.0;
+                for (int j0 = 0; j0 < wmax; j0 += 2) {
+                    const double2 z2 = make_double2(0.0, 0.0);
+                    const double2 v0 = (j0 < len) ? src[j0] : z2, v1 = (j0 + 1 < len) ? src[j0 + 1] : z2;
+                    sx += v0.x; sy += v0.y;
+                    sx += v1.x; sy += v1.y;
                 }
                 if (valid) {
-                    if (ACC) *slot = before + sum;
-                    else P.rows[(size_t)seg_r[seg] * 6 + k] = sum;
+                    if (ACC) *slot = make_double2(before.x + sx, before.y + sy);
+                    else *reinterpret_cast<double2*>(P.rows + (size_t)seg_r[seg] * 6 + 2 * pr) = make_double2(sx, sy);
                 }
             }
         }
