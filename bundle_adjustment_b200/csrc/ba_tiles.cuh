@@ -16,8 +16,9 @@
 //   * neighbouring lanes read the SAME camera record -> the camera gather is a broadcast load (a few
 //     L1 wavefronts per warp instead of one per lane);
 //   * a camera's observations form a contiguous run of threads; runs are cut into SEGMENTS of at most
-//     FT_SEG_MAX observations, each segment is summed in index order by one thread per component and
-//     leaves one 6-double (mat-vec) or 27-double (linearisation) ROW in HBM;
+//     FT_SEG_MAX observations, each segment is summed in index order by one thread per PAIR of components
+//     (the per-observation products are parked as three double2) and leaves one 6-double ROW in HBM - or adds
+//     to a shared-memory accumulator slot that becomes a row when its epoch ends;
 //   * rows are laid out camera-major, so the per-camera finish is a contiguous, fixed-order sum.
 // No floating-point atomics: every sum has a fixed order, results are bit-reproducible.
 //
@@ -38,7 +39,7 @@ constexpr int FT_LD = FT_THREADS + 3;  // row stride of the camera-side scratch 
                                        // (xm0,xm1) (xm2,mm0) (mm1,mm2); 3 mod 8 sixteen-byte bank groups between the pairs of a segment
 constexpr int FT_LDB = FT_THREADS + 4; // row stride of the point-side scratch (phases A/B): 2*FT_LDB mod 32 = 8 banks, so the
                                        // three rows read by the four points of a half-warp are disjoint
-constexpr int FT_ROWS_MV = 6;          // scratch rows of the mat-vec pass
+constexpr int FT_ROWS_MV = 6;          // doubles per observation in the camera-side scratch of the mat-vec pass (three double2 rows)
 constexpr int FT_ACC_CAP = 96;         // accumulator slots (6 doubles + row number each) of an epoch; what is left of 228 KB / 4 CTAs
 
 // Tiles of persistent CTA b of a grid of G over T tiles, and the way a CTA cuts its run into EPOCHS of about
@@ -57,7 +58,8 @@ __host__ __device__ inline int ft_epoch_len(int len, int target) {
 constexpr int FT_META_N = FT_THREADS + 2, FT_OFF_N = FT_PTS + 8, FT_SEG_N = FT_THREADS + 8;
 struct FtSmem {
     double* sA;  // [3][FT_LDB] point-side scratch (phases A/B); separate from sO so that phase D of a tile and phase A of the next overlap
-    double* sO; double2* sJ; int2* sMeta; double2* sX01; double* sX2; double2* sZ01; double* sZ2; double* sVi;
+    double* sO;  // [3][FT_LD] double2: (X x m, m) of every observation as three value pairs (phases C/D)
+    double2* sJ; int2* sMeta; double2* sX01; double* sX2; double2* sZ01; double* sZ2; double* sVi;
     int* sOff; int* sRs; int* sSeg; int* sRow;
     unsigned long long* bar;
     double* sAcc;  // [FT_ACC_CAP][6] epoch accumulators (only when the pass is instantiated with them)
