@@ -278,11 +278,22 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
                 const bool valid = q < T.m;
                 // transposed track layout: observation i of point q sits at rs[i] + q, so the lanes of
                 // neighbouring points read neighbouring words; tracks of a warp are (nearly) equally long
-                const int len = (valid && k < 3) ? off[q + 1] - off[q] : 0;
+                // idle lanes (fourth lane of a quad, points past the tile's last) shadow a working lane - same address, a
+                // broadcast - so that the head of the loop, up to the shortest track of the warp (the tracks of a warp are
+                // sorted and nearly equally long), needs no predicates; their sums are never used
+                const int qs = min(q, T.m - 1);
+                const int len_s = off[qs + 1] - off[qs];
+                const int len = (valid && k < 3) ? len_s : 0;
                 const int wmax = __reduce_max_sync(0xffffffffu, len);
-                const double* src = S.sA + k * FT_LDB + q;
+                const int whead = __reduce_min_sync(0xffffffffu, len_s) & ~3;
+                const double* src = S.sA + min(k, 2) * FT_LDB + qs;
                 double sk = 0.0;
-                for (int i0 = 0; i0 < wmax; i0 += 4) {  // loads first, then the (ordered) adds; x + 0.0 is exact
+                for (int i0 = 0; i0 < whead; i0 += 4) {  // loads first, then the (ordered) adds
+                    const int4 r4 = *reinterpret_cast<const int4*>(rsb + i0);  // broadcast
+                    const double v0 = src[r4.x], v1 = src[r4.y], v2 = src[r4.z], v3 = src[r4.w];
+                    sk += v0; sk += v1; sk += v2; sk += v3;
+                }
+                for (int i0 = whead; i0 < wmax; i0 += 4) {  // the tail: x + 0.0 is exact
                     const int4 r4 = *reinterpret_cast<const int4*>(rsb + i0);  // broadcast
                     const int rs[4] = {r4.x, r4.y, r4.z, r4.w};
                     double v[4];
