@@ -197,8 +197,11 @@ class BundleAdjuster:
             kf = gmap.keyframes[kf_id]
             kf.R = rvec_to_matrix(rvecs[i])
             kf.t = tvecs[i].reshape(3, 1).copy()
+        # one (n, 3, 1) block, every position a view of its row: the reference hands out views of res.x as well (:237-240)
+        block = np.ascontiguousarray(pts).reshape(-1, 3, 1).copy()
+        mpd = gmap.map_points
         for i, mp_id in enumerate(local_map_point_ids):
-            gmap.map_points[mp_id].position = pts[i].reshape(3, 1).copy()
+            mpd[mp_id].position = block[i]
 
     # -- the entry point ---------------------------------------------------------------------------
     def run(self, gmap):
@@ -227,8 +230,13 @@ class BundleAdjuster:
 
         rvecs = np.array([matrix_to_rvec(gmap.keyframes[i].R) for i in adjustable_kf_ids]).reshape(-1, 3)
         tvecs = np.array([np.asarray(gmap.keyframes[i].t, dtype=np.float64).ravel() for i in adjustable_kf_ids]).reshape(-1, 3)
-        pts = np.array([np.asarray(gmap.map_points[i].position, dtype=np.float64).ravel()
-                        for i in local_map_point_ids]).reshape(-1, 3)
+        mpd = gmap.map_points
+        try:        # positions are (3, 1) float64 arrays in the pipeline: one concatenate instead of a conversion per point
+            pts = np.concatenate([mpd[i].position for i in local_map_point_ids], dtype=np.float64).reshape(-1, 3)
+            if pts.shape[0] != len(local_map_point_ids):
+                raise ValueError
+        except (ValueError, TypeError):
+            pts = np.array([np.asarray(mpd[i].position, dtype=np.float64).ravel() for i in local_map_point_ids]).reshape(-1, 3)
         fixed_kf = gmap.keyframes[fixed_kf_id]
 
         fx, fy, cx, cy = self._intrinsics()

@@ -68,6 +68,46 @@ def test_struct_layout_against_the_compiled_header(tmp_path):
     assert o.pcg_tail == 1 and o.device_loop == 1 and list(o.reserved) == [0, 0, 0, 0]
 
 
+def test_run_host_path_with_a_stub_solver():
+    """Everything of ``run`` around the device calls (window selection, packing, write-back as (3, 1) arrays, the printed
+    line), with the solver replaced by a stub that shifts every point by one: no GPU needed."""
+    from bundle_adjustment_b200.map_structures import Keyframe, KeyPoint, Map, MapPoint
+    spec = S.make_window_spec(n_kfs=10, n_pts=400)
+    gmap = S.build_map(spec, Map, Keyframe, MapPoint, KeyPoint.from_xy)
+
+    class Stub:
+        def set_problem(self, fx, fy, cx, cy, rvecs, tvecs, frv, ftv, pts, oc, op, ouv):
+            assert pts.dtype == np.float64 and pts.shape[1] == 3 and oc.min() == -1 and op.max() == len(pts) - 1
+            self.n_cams, self.x = len(rvecs), np.concatenate([rvecs.ravel(), tvecs.ravel(), (pts + 1.0).ravel()])
+
+        def solve(self, **kw):
+            return {"initial_raw_cost": 2.0, "final_raw_cost": 1.0}
+
+        def get_x(self):
+            return self.x
+
+    adj = BundleAdjuster(spec["camera_matrix"], window_size=5)
+    stub = Stub()
+    adj._get_solver = lambda: stub
+    before = {k: v.position.copy() for k, v in gmap.map_points.items()}
+    # positions in the forms a caller may hold them: (3, 1) arrays (the pipeline), nested lists, flat arrays
+    ids = sorted(gmap.keyframes)[-6:-1]
+    seen = sorted({mp for kf in ids for mp, _ in gmap.keyframes[kf].observations})
+    gmap.map_points[seen[0]].position = before[seen[0]].tolist()
+    gmap.map_points[seen[1]].position = before[seen[1]].ravel()
+    with redirect_stdout(io.StringIO()) as out:
+        adj.run(gmap)
+    assert "LBA Complete. Initial Cost: 2.00, Final Cost: 1.00, Improvement: 50.00%" in out.getvalue()
+    assert stub.n_cams == 4
+    for k, mp in gmap.map_points.items():
+        assert mp.position.shape == (3, 1) and mp.position.dtype == np.float64
+        want = before[k] + 1.0 if k in seen else before[k]
+        assert np.array_equal(mp.position, want), k
+    # write-back hands out independent rows: an in-place edit of one position leaves its neighbours alone
+    gmap.map_points[seen[2]].position += 5.0
+    assert np.array_equal(gmap.map_points[seen[3]].position, before[seen[3]] + 1.0)
+
+
 def test_geometry_matches_oracle():
     rng = np.random.default_rng(1)
     for _ in range(100):
