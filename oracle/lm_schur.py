@@ -202,3 +202,91 @@ def solve(prob: O.Problem, rvec, tvec, pts, *, mode="irls", huber=True, max_iter
                 status = 5
                 break
     return LMResult(rvec, tvec, pts, lin.cost, lin.raw, it, status, hist)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Preconditioned CG on the reduced camera system, as the device runs it, and the two-level preconditioner planned for
+# round 2.  TEST INFRASTRUCTURE: the CPU statement the device kernels will be checked
+# against; the study behind the choice is scripts/precond_study.py.
+# ------------------------------------------------------------------------------------------------------------------
+class SchurOperator:
+    """Implicit S u = (U + lam D) u - E V^-1 E^T u of one linearisation - what the tile pass (+ lam D u in the tail)
+    computes - and its 6x6 diagonal blocks (the Schur-Jacobi preconditioner)."""
+
+    def __init__(self, prob: O.Problem, lin: Linearization, lam: float, dmin=1e-6, dmax=1e32):
+        adj = prob.obs_cam >= 0
+        self.nc = prob.n_cams
+        self.ca, self.pa = prob.obs_cam[adj], prob.obs_pt[adj]
+        Dp = np.clip(np.einsum("nii->ni", lin.V), dmin, dmax)
+        self.Dc = np.clip(np.einsum("nii->ni", lin.U), dmin, dmax)
+        self.Vinv = np.linalg.inv(lin.V + lam * np.einsum("ni,ij->nij", Dp, np.eye(3)))
+        self.E = np.einsum("nki,nk,nkj->nij", lin.Jc[adj], lin.wH[adj], lin.Jp[adj])
+        self.U, self.lam, self.n_pts = lin.U, lam, prob.n_pts
+        self.rhs = -lin.gc.copy()
+        np.add.at(self.rhs, self.ca, np.einsum("nij,njk,nk->ni", self.E, self.Vinv[self.pa], lin.gp[self.pa]))
+
+    def matvec(self, u):
+        u = u.reshape(self.nc, 6)
+        s = np.zeros((self.n_pts, 3))
+        np.add.at(s, self.pa, np.einsum("nij,ni->nj", self.E, u[self.ca]))
+        z = np.einsum("nij,nj->ni", self.Vinv, s)
+        w = np.einsum("nij,nj->ni", self.U, u) + self.lam * self.Dc * u
+        np.subtract.at(w, self.ca, np.einsum("nij,nj->ni", self.E, z[self.pa]))
+        return w.ravel()
+
+    def jacobi_blocks(self):
+        M = self.U + self.lam * np.einsum("ni,ij->nij", self.Dc, np.eye(6))
+        EV = np.einsum("nij,njk->nik", self.E, self.Vinv[self.pa])
+        np.subtract.at(M, self.ca, np.einsum("nij,nkj->nik", EV, self.E))
+        return np.linalg.inv(M)
+
+
+def coarse_prolongation(n_cams: int, agg: int) -> np.ndarray:
+    """Z (6 n_cams x 6 n_agg): one rigid 6-vector per aggregate of `agg` consecutive cameras (piecewise constant)."""
+    n_agg = (n_cams + agg - 1) // agg
+    Z = np.zeros((6 * n_cams, 6 * n_agg))
+    c = np.arange(n_cams)
+    for d in range(6):
+        Z[6 * c + d, 6 * (c // agg) + d] = 1.0
+    return Z
+
+
+def coarse_matrix_by_probing(matvec, Z: np.ndarray) -> np.ndarray:
+    """Z^T S Z column by column: one mat-vec per coarse unknown (what the device does with its tile pass)."""
+    A0 = np.stack([Z.T @ matvec(Z[:, j]) for j in range(Z.shape[1])], axis=1)
+    return 0.5 * (A0 + A0.T)
+
+
+def pcg(matvec, b, Minv_blocks, *, tol=0.1, max_iters=100, Z=None, A0_inv=None):
+    """CG preconditioned with the 6x6 blocks `Minv_blocks` (n_cams,6,6) and, if Z / A0_inv are given, the additive coarse
+    correction  M^-1 r = blockdiag r + Z A0^-1 Z^T r.  Stops like the device: r^T M^-1 r <= tol^2 r0^T M^-1 r0.
+    -> (x, iterations, final r^T M^-1 r / initial)."""
+    nc = Minv_blocks.shape[0]
+
+    def prec(r):
+        u = np.einsum("nij,nj->ni", Minv_blocks, r.reshape(nc, 6)).ravel()
+        if Z is not None:
+            u = u + Z @ (A0_inv @ (Z.T @ r))
+        return u
+
+    x = np.zeros_like(b)
+    r = b.copy()
+    u = prec(r)
+    p = u.copy()
+    g0 = g = float(r @ u)
+    it = 0
+    if not g0 > 0.0:
+        return x, 0, 0.0
+    for it in range(1, max_iters + 1):
+        Ap = matvec(p)
+        alpha = g / float(p @ Ap)
+        x += alpha * p
+        r -= alpha * Ap
+        u = prec(r)
+        gn = float(r @ u)
+        if not gn > tol * tol * g0:
+            g = gn
+            break
+        p = u + (gn / g) * p
+        g = gn
+    return x, it, g / g0

@@ -145,8 +145,14 @@ for lm_it in range(n_lm):
     res = {}
     sj = cluster_precond(A, nc, 1)
     res["SJ"], x_sj = pcg(A, b, sj, maxit=100 if inexact else 1000, want_x=True)
+    if os.environ.get("STEP", "sj") == "two_level" and lm_it >= 5:
+        # the planned device behaviour: Schur-Jacobi while the damping falls, then the two-level preconditioner with the
+        # coarse matrix of THAT iteration kept to the end; the LM step is this solve's result
+        if "A_step" not in globals():
+            A_step = A.copy()
+        res["step: SJ+C-32 lagged"], x_sj = pcg(A, b, two_level(A, nc, 32, A0_from=A_step), maxit=100, want_x=True)
     if lm_it % every:
-        res = {"SJ": res["SJ"]}
+        res = {k: v for k, v in res.items() if k == "SJ" or k.startswith("step")}
     else:
       if True:
         if os.environ.get("CLUSTERS", "0") == "1":
