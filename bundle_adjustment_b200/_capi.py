@@ -15,7 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libba_b200.so")
 
 ROBUST = {"none": 0, "irls": 1, "triggs": 2}
-PRECOND = {"jacobi": 0, "schur_jacobi": 1}
+PRECOND = {"jacobi": 0, "schur_jacobi": 1, "two_level": 2}
 SCHUR_PATH = {"tiles": 0, "two_pass": 1, "tiles_rows": 2}
 STATUS_TEXT = {0: "iteration limit", 1: "gtol", 2: "ftol", 3: "xtol", 4: "ftol and xtol", 5: "damping limit"}
 

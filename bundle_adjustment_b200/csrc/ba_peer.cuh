@@ -170,15 +170,43 @@ __global__ void __launch_bounds__(VEC_THREADS) k_pcg_dots_peer(Params P, double*
 namespace cg = cooperative_groups;
 constexpr int PT_THREADS = 1024;
 constexpr int PT_MAX_CLUSTER = 16;
-__host__ __device__ inline size_t pt_smem_bytes(int n_cams, int cluster) {
+__host__ __device__ inline size_t pt_smem_bytes(int n_cams, int cluster, int coarse_nz = 0, int coarse_agg = 1) {
     const int chunk = (n_cams + cluster - 1) / cluster;
-    return (size_t)chunk * 6 * 2 * sizeof(double);
+    // two-level preconditioner: + the restricted residual [nz] and the correction of the aggregates that meet a chunk
+    const size_t coarse = coarse_nz ? (size_t)coarse_nz + (size_t)(chunk / coarse_agg + 2) * 6 : 0;
+    return ((size_t)chunk * 6 * 2 + coarse) * sizeof(double);
 }
 
-template <bool PEER>
+// Two-level preconditioner (BA_PRECOND_TWO_LEVEL; DESIGN.md section 8, oracle/lm_schur.py: pcg with Z / A0_inv):
+//     M^-1 r = blockdiag(Minv) r + Z A0^-1 Z^T r,
+// Z = one rigid 6-vector per aggregate of `agg` consecutive cameras, A0 = Z^T S Z (built by probing, solver side).
+struct Coarse {
+    const double* Ainv;  // [nz * nz] inverse of the coarse matrix (symmetric), nz = 6 * number of aggregates
+    int agg, nz;
+};
+// (Z^T r)[j], j < nz, into shared memory: thread j adds its aggregate's residual component in camera order (fixed order ->
+// the same bits in every CTA).  Callers synchronise afterwards.
+BA_D void coarse_restrict(const Coarse& C, const double* __restrict__ r, int n_cams, double* __restrict__ s_rc) {
+    for (int j = threadIdx.x; j < C.nz; j += blockDim.x) {
+        const int a = j / 6, d = j - 6 * a;
+        const int c0 = a * C.agg, c1 = min(c0 + C.agg, n_cams);
+        double rc = 0.0;
+        for (int c = c0; c < c1; ++c) rc += r[(size_t)c * 6 + d];
+        s_rc[j] = rc;
+    }
+}
+// y[row] = sum_j Ainv[row][j] * rc[j] by one warp (lane-strided products, shuffle tree); all lanes return the value.
+BA_D double coarse_row(const Coarse& C, const double* __restrict__ s_rc, int row, int lane) {
+    double acc = 0.0;
+    for (int j = lane; j < C.nz; j += 32) acc += __ldg(C.Ainv + (size_t)row * C.nz + j) * s_rc[j];
+    return __shfl_sync(0xffffffffu, warp_sum(acc), 0);
+}
+
+template <bool PEER, bool COARSE = false>
 __global__ void __launch_bounds__(PT_THREADS, 1) k_pcg_tail(Params P, double tol, int max_iters, double* __restrict__ xbuf,
                                                             double* const* __restrict__ peers, int nranks, int rank, int push,
-                                                            int cap, int* __restrict__ xstate, unsigned long long pcg_loop) {
+                                                            int cap, int* __restrict__ xstate, unsigned long long pcg_loop,
+                                                            Coarse C = Coarse{nullptr, 0, 0}) {
     extern __shared__ __align__(16) double dsm[];
     __shared__ double part_d[PT_MAX_CLUSTER];  // delta partials of all CTAs (every CTA gets all of them)
     __shared__ double part_g[PT_MAX_CLUSTER];  // gamma partials (CTA 0 only)
@@ -330,7 +358,25 @@ __global__ void __launch_bounds__(PT_THREADS, 1) k_pcg_tail(Params P, double tol
         sR[e] = r;
     }
     __syncthreads();
-    // ---- u = Minv r (6x6 block per camera),  gamma = r.u ---------------------------------------------------
+    double* sY = nullptr;  // coarse correction of the aggregates that meet this CTA's chunk, [aggregates][6]
+    int a_first = 0;
+    if (COARSE) {
+        // every CTA's part of the new residual is in global memory (v_r); the cluster barrier makes it visible to all
+        cl.sync();
+        double* sRc = dsm + (size_t)chunk * 12;  // [nz] restricted residual
+        sY = sRc + C.nz;
+        coarse_restrict(C, P.v_r, P.n_cams, sRc);
+        __syncthreads();
+        a_first = c0 / C.agg;
+        const int a_last = (c1 > c0) ? (c1 - 1) / C.agg : a_first - 1;
+        const int rows = (a_last - a_first + 1) * 6;
+        for (int rr = wid; rr < rows; rr += PT_THREADS / 32) {
+            const double y = coarse_row(C, sRc, a_first * 6 + rr, lane);
+            if (lane == 0) sY[rr] = y;
+        }
+        __syncthreads();
+    }
+    // ---- u = Minv r (6x6 block per camera) [+ coarse correction],  gamma = r.u -----------------------------
     part = 0.0;
     for (int e = tid; e < n_el; e += PT_THREADS) {
         const int cl_ = e / 6, k = e - 6 * cl_;
@@ -339,6 +385,7 @@ __global__ void __launch_bounds__(PT_THREADS, 1) k_pcg_tail(Params P, double tol
         double u = 0.0;
 #pragma unroll
         for (int j = 0; j < 6; ++j) u += __ldg(M + j) * r[j];
+        if (COARSE) u += sY[((c0 + cl_) / C.agg - a_first) * 6 + k];
         P.v_u[(size_t)c0 * 6 + e] = u;
         part += sR[e] * u;
     }
@@ -356,6 +403,53 @@ __global__ void __launch_bounds__(PT_THREADS, 1) k_pcg_tail(Params P, double tol
         const bool done = !(alpha > 0.0) || !(g > tol * tol * st->gamma0) || it >= max_iters;
         if (done) st->pcg_done = 1;
         set_loop(pcg_loop, !done);
+    }
+}
+
+// ---- coarse space: probing and the first preconditioned residual of a PCG solve -----------------------------------
+// probe vector of coarse unknown j: 1 in component (j % 6) of every camera of aggregate j / 6, 0 elsewhere
+__global__ void k_coarse_probe(int n_cams, int agg, int j, double* __restrict__ probe) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (n_cams + 1) * 6) return;
+    const int c = i / 6, d = i - 6 * c;
+    probe[i] = (c < n_cams && c / agg == j / 6 && d == j % 6) ? 1.0 : 0.0;
+}
+// column j of A0 = Z^T (S probe_j): per-aggregate sums of w in camera order
+__global__ void k_coarse_column(int n_cams, int agg, int nz, const double* __restrict__ w, double* __restrict__ col) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nz) return;
+    const int a = t / 6, d = t - 6 * a;
+    const int c0 = a * agg, c1 = min(c0 + agg, n_cams);
+    double s = 0.0;
+    for (int c = c0; c < c1; ++c) s += w[(size_t)c * 6 + d];
+    col[t] = s;
+}
+// After k_camera_finish_schur (u = Minv r, gamma = r.u): add the coarse correction to u and redo gamma.  One CTA.
+__global__ void __launch_bounds__(PT_THREADS) k_coarse_first(Params P, Coarse C, unsigned long long pcg_loop) {
+    extern __shared__ __align__(16) double sy[];  // [nz] correction, [nz] restricted residual
+    __shared__ double red[33];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    double* s_rc = sy + C.nz;
+    coarse_restrict(C, P.v_r, P.n_cams, s_rc);
+    __syncthreads();
+    for (int row = wid; row < C.nz; row += PT_THREADS / 32) {
+        const double y = coarse_row(C, s_rc, row, lane);
+        if (lane == 0) sy[row] = y;
+    }
+    __syncthreads();
+    double part = 0.0;
+    for (int i = tid; i < P.n_cams * 6; i += PT_THREADS) {
+        const int c = i / 6, d = i - 6 * c;
+        const double u = P.v_u[i] + sy[(c / C.agg) * 6 + d];
+        P.v_u[i] = u;
+        part += P.v_r[i] * u;
+    }
+    const double g = cta_sum_all(part, red);
+    if (tid == 0) {
+        LMState* st = P.st;
+        st->gamma = g; st->gamma0 = g; st->gamma_prev = g;
+        st->pcg_done = !(g > 0.0);
+        set_loop(pcg_loop, g > 0.0);
     }
 }
 

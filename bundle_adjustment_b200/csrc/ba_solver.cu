@@ -416,6 +416,10 @@ struct ba_handle {
     DBuf<double> rows;
     // peer-memory exchange of the PCG mat-vec partials (ba_peer.cuh); multi-GPU handles only
     bool peer_ok = false;
+    // two-level preconditioner (BA_PRECOND_TWO_LEVEL): coarse matrix of the current solve
+    DBuf<double> coarse_Ainv, coarse_A, coarse_probe, coarse_w;
+    int coarse_agg = 32, coarse_nz = 0;
+    bool coarse_ready = false;
     int xcap = 0;
     int xpush = 2;  // exchange by remote loads (0, pull), remote stores + flags (1, push), remote stores of LL words (2)
     DBuf<double> xbuf;
@@ -1210,7 +1214,8 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     for (int k = 0; k < KN_COUNT; ++k) { h->launches[k] = 0; h->kernel_ms[k] = 0.0; }
     h->time_kernels = opt->verbose >= 2;
     const int check_every = std::max(1, opt->pcg_check_every);
-    const int with_schur = opt->precond == BA_PRECOND_SCHUR_JACOBI ? 1 : 0;
+    const int with_schur = opt->precond >= BA_PRECOND_SCHUR_JACOBI ? 1 : 0;
+    if (opt->precond < BA_PRECOND_JACOBI || opt->precond > BA_PRECOND_TWO_LEVEL) fail(BA_ERR_ARG, "unknown preconditioner %d", opt->precond);
     const int nc1 = P.n_cams + 1;
     if (opt->schur_path < BA_PATH_TILES || opt->schur_path > BA_PATH_TILES_ROWS) fail(BA_ERR_ARG, "unknown schur_path %d", opt->schur_path);
     const bool tiles = opt->schur_path != BA_PATH_TWO_PASS && h->fused_ok;
@@ -1236,6 +1241,75 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     int status = opt->max_iters == 0 ? 6 : 0;
     unsigned long long pcg_loop = 0, lm_loop = 0;  // conditional handles of the device-side loops (0: host loops)
 
+    // ---- two-level preconditioner (EXPERIMENTAL, see BA_PRECOND_TWO_LEVEL): single GPU, default kernel path, host loops.
+    //      The coarse matrix A0 = Z^T S Z is probed with the tile pass once the PCG of an LM iteration has needed more than
+    //      15 iterations (the damping has reached its floor by then and S changes little), inverted on the host and kept to the
+    //      end of the solve.
+    bool two_level = opt->precond == BA_PRECOND_TWO_LEVEL && h->nranks == 1 && tiles && tail && P.n_cams > 0;
+    h->coarse_ready = false;
+    if (two_level) {
+        if (const char* e = getenv("BA_B200_COARSE_AGG")) h->coarse_agg = std::max(1, atoi(e));
+        h->coarse_nz = 6 * cdiv(P.n_cams, h->coarse_agg);
+        const size_t cb = pt_smem_bytes(P.n_cams, h->tail_cluster, h->coarse_nz, h->coarse_agg);
+        if (cudaFuncSetAttribute(k_pcg_tail<false, true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess ||
+            cudaFuncSetAttribute(k_pcg_tail<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(cb, (size_t)1024)) != cudaSuccess) {
+            cudaGetLastError();
+            two_level = false;  // the coarse tail does not fit this device: plain Schur-Jacobi
+        }
+    }
+    auto build_coarse = [&]() {  // between k_camera_finish_schur and the first PCG iteration: V^-1, lambda and D are current
+        const int nz = h->coarse_nz, agg = h->coarse_agg;
+        h->coarse_A.alloc((size_t)nz * nz); h->coarse_Ainv.alloc((size_t)nz * nz);
+        h->coarse_probe.alloc((size_t)nc1 * 6); h->coarse_w.alloc((size_t)nc1 * 6);
+        Params PQ = PA;  // the row finish reads the probe instead of u and leaves S * probe in a scratch vector
+        PQ.v_u = h->coarse_probe.p; PQ.v_w = h->coarse_w.p;
+        for (int j = 0; j < nz; ++j) {
+            launch(h, KN_SETUP, k_coarse_probe, cdiv(nc1 * 6, 256), 256, 0, P.n_cams, agg, j, h->coarse_probe.p);
+            launch_tile_matvec(h, PA, acc, h->coarse_probe.p);
+            launch(h, KN_ROWS_FIN, k_rows_finish<false>, cdiv(P.n_cams, RS_WARPS), RS_WARPS * 32, 0, PQ);
+            launch(h, KN_SETUP, k_coarse_column, cdiv(nz, 128), 128, 0, P.n_cams, agg, nz, (const double*)h->coarse_w.p,
+                   h->coarse_A.p + (size_t)j * nz);
+        }
+        std::vector<double> A((size_t)nz * nz), Ainv((size_t)nz * nz, 0.0);
+        CK(cudaMemcpyAsync(A.data(), h->coarse_A.p, A.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+        // symmetrise, Cholesky A = L L^T (in place, lower), inverse = L^-T L^-1
+        for (int i = 0; i < nz; ++i)
+            for (int j = 0; j < i; ++j) A[(size_t)i * nz + j] = A[(size_t)j * nz + i] = 0.5 * (A[(size_t)i * nz + j] + A[(size_t)j * nz + i]);
+        for (int j = 0; j < nz; ++j) {
+            double d = A[(size_t)j * nz + j];
+            for (int k = 0; k < j; ++k) d -= A[(size_t)j * nz + k] * A[(size_t)j * nz + k];
+            if (!(d > 0.0)) return false;  // not positive definite (degenerate aggregate): stay with Schur-Jacobi
+            const double l = std::sqrt(d);
+            A[(size_t)j * nz + j] = l;
+            for (int i = j + 1; i < nz; ++i) {
+                double v = A[(size_t)i * nz + j];
+                for (int k = 0; k < j; ++k) v -= A[(size_t)i * nz + k] * A[(size_t)j * nz + k];
+                A[(size_t)i * nz + j] = v / l;
+            }
+        }
+        std::vector<double> Li((size_t)nz * nz, 0.0);  // L^-1 (lower), column by column
+        for (int c = 0; c < nz; ++c) {
+            Li[(size_t)c * nz + c] = 1.0 / A[(size_t)c * nz + c];
+            for (int i = c + 1; i < nz; ++i) {
+                double v = 0.0;
+                for (int k = c; k < i; ++k) v -= A[(size_t)i * nz + k] * Li[(size_t)k * nz + c];
+                Li[(size_t)i * nz + c] = v / A[(size_t)i * nz + i];
+            }
+        }
+        for (int i = 0; i < nz; ++i)
+            for (int j = 0; j <= i; ++j) {
+                double v = 0.0;
+                for (int k = i; k < nz; ++k) v += Li[(size_t)k * nz + i] * Li[(size_t)k * nz + j];
+                Ainv[(size_t)i * nz + j] = Ainv[(size_t)j * nz + i] = v;
+            }
+        CK(cudaMemcpyAsync(h->coarse_Ainv.p, Ainv.data(), Ainv.size() * sizeof(double), cudaMemcpyHostToDevice, s));
+        CK(cudaStreamSynchronize(s));
+        return true;
+    };
+    int last_pcg_iters = 0;
+    bool coarse_failed = false;
+
     // ---- the three parts of one LM iteration ------------------------------------------------------------------
     auto before_pcg = [&](bool lin) {
         if (lin) {
@@ -1248,6 +1322,14 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
             launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 27, 256), 256, 0, P, 27, 0);
             allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 27);
             launch(h, KN_CAM_FIN, k_camera_finish_schur, P.vec_ctas, VEC_THREADS, 0, P, with_schur, h->ticket.p, pcg_loop);
+            if (two_level && !h->coarse_ready && !coarse_failed && last_pcg_iters > 15) {
+                h->coarse_ready = build_coarse();
+                coarse_failed = !h->coarse_ready;
+                if (pcg_graph) { CK(cudaGraphExecDestroy(pcg_graph)); pcg_graph = nullptr; }  // the tail of the graph changes
+            }
+            if (two_level && h->coarse_ready)
+                launch(h, KN_CAM_FIN, k_coarse_first, 1, PT_THREADS, 2 * (size_t)h->coarse_nz * sizeof(double), P,
+                       Coarse{h->coarse_Ainv.p, h->coarse_agg, h->coarse_nz}, pcg_loop);
         }
     };
     auto pcg_iteration = [&]() {
@@ -1255,12 +1337,18 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
         if (tiles && tail) {  // two kernels per iteration: the tile pass, then everything else in one cluster
             launch_tile_matvec(h, PA, acc, h->v_u.p);
             const size_t bytes = pt_smem_bytes(P.n_cams, h->tail_cluster);
+            const Coarse none{nullptr, 1, 0};
             if (h->nranks > 1)
-                launch_cluster(h, KN_PCG_TAIL, k_pcg_tail<true>, h->tail_cluster, PT_THREADS, bytes, PA, opt->pcg_tol, opt->pcg_max_iters,
-                               h->xbuf.p, (double* const*)h->d_peers.p, h->nranks, h->rank, h->xpush, h->xcap, h->xstate.p, pcg_loop);
+                launch_cluster(h, KN_PCG_TAIL, k_pcg_tail<true, false>, h->tail_cluster, PT_THREADS, bytes, PA, opt->pcg_tol, opt->pcg_max_iters,
+                               h->xbuf.p, (double* const*)h->d_peers.p, h->nranks, h->rank, h->xpush, h->xcap, h->xstate.p, pcg_loop, none);
+            else if (two_level && h->coarse_ready)
+                launch_cluster(h, KN_PCG_TAIL, k_pcg_tail<false, true>, h->tail_cluster, PT_THREADS,
+                               pt_smem_bytes(P.n_cams, h->tail_cluster, h->coarse_nz, h->coarse_agg), PA, opt->pcg_tol, opt->pcg_max_iters,
+                               (double*)nullptr, (double* const*)nullptr, 1, 0, 0, 0, (int*)nullptr, pcg_loop,
+                               Coarse{h->coarse_Ainv.p, h->coarse_agg, h->coarse_nz});
             else
-                launch_cluster(h, KN_PCG_TAIL, k_pcg_tail<false>, h->tail_cluster, PT_THREADS, bytes, PA, opt->pcg_tol, opt->pcg_max_iters,
-                               (double*)nullptr, (double* const*)nullptr, 1, 0, 0, 0, (int*)nullptr, pcg_loop);
+                launch_cluster(h, KN_PCG_TAIL, k_pcg_tail<false, false>, h->tail_cluster, PT_THREADS, bytes, PA, opt->pcg_tol, opt->pcg_max_iters,
+                               (double*)nullptr, (double* const*)nullptr, 1, 0, 0, 0, (int*)nullptr, pcg_loop, none);
             return;
         }
         if (tiles) {
@@ -1315,7 +1403,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     //      device_loop = 1 therefore means "up to kDeviceLoopMaxObs observations", 2 = always.
     const bool device_loop = status == 0 && (opt->device_loop == 2 || (opt->device_loop == 1 && P.n_obs <= kDeviceLoopMaxObs)) &&
                              h->nranks == 1 && tiles && tail && P.n_cams > 0 && !h->time_kernels && !(opt->verbose & 1) &&
-                             !getenv("BA_B200_HOST_LOOP");
+                             !two_level && !getenv("BA_B200_HOST_LOOP");
     if (device_loop) {
         long long before[KN_COUNT], per_lm[KN_COUNT], per_pcg[KN_COUNT];
         memcpy(before, h->launches, sizeof before);
@@ -1418,6 +1506,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
         const LMState& st = *h->h_state;
         status = st.status;
         need_lin = st.last_accepted != 0;
+        last_pcg_iters = st.pcg_iter;
         if (opt->verbose & 1)
             fprintf(stderr, "[ba_b200] it %3d %s cost %.9e -> trial %.9e  rho %+.3e  lambda %.3e  pcg %d  |g| %.3e  |dx| %.3e\n",
                     st.iter, st.last_accepted ? "acc" : "REJ", st.cost[st.cur ^ (st.last_accepted ? 1 : 0)], st.scal[S_COST], st.rho,

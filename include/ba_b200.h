@@ -44,6 +44,10 @@ typedef struct ba_handle ba_handle;
 
 #define BA_PRECOND_JACOBI 0       /* camera blocks of J^T J                                    */
 #define BA_PRECOND_SCHUR_JACOBI 1 /* diagonal blocks of the Schur complement          (default) */
+#define BA_PRECOND_TWO_LEVEL 2    /* EXPERIMENTAL (round 2, not yet validated on the device): Schur-Jacobi plus a coarse
+                                     correction, one rigid 6-vector per aggregate of 32 consecutive cameras, coarse matrix
+                                     by probing with the tile pass once the PCG needs more than 15 iterations
+                                     (single GPU, default kernel path, host-driven loops)           */
 
 #define BA_PATH_TILES 0    /* fused point-tile passes: one kernel per Schur mat-vec          (default) */
 #define BA_PATH_TWO_PASS 1 /* point-major pass + camera-major pass (also used when a track is longer

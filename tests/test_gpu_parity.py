@@ -4,6 +4,8 @@ Tolerances are the ones BASELINE.json's north_star states: residuals 1e-9 relati
 relative to the reference's finite-difference Jacobian, converged cost 1e-6 relative, index / sparsity
 construction bit-exact.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -461,3 +463,18 @@ def test_full_size_properties(gpu_solver, name):
     assert abs(O.huber_cost(r) - st["final_cost"]) <= 1e-9 * st["final_cost"]
     assert abs(float((r * r).sum()) - st["final_raw_cost"]) <= 1e-9 * st["final_raw_cost"]
     del prob
+
+
+@pytest.mark.skipif(not os.environ.get("BA_TEST_EXPERIMENTAL"), reason="BA_PRECOND_TWO_LEVEL is not validated on the device yet "
+                    "(written without GPU time left in round 1; set BA_TEST_EXPERIMENTAL=1 to run)")
+def test_two_level_preconditioner_experimental(gpu_solver):
+    """Round-2 entry point: the two-level preconditioner (Schur-Jacobi + coarse space by probing) must reach the cost of the
+    default solve with fewer PCG iterations on a long camera chain (CPU statement: oracle/lm_schur.py::pcg, study:
+    scripts/precond_study.py)."""
+    fp = S.make_flat_problem(600, 40000, 200000, seed=31)
+    gpu_solver.set_flat(fp)
+    st1 = gpu_solver.solve(max_iters=30, device_loop=0)
+    gpu_solver.set_flat(fp)
+    st2 = gpu_solver.solve(max_iters=30, device_loop=0, precond="two_level")
+    assert abs(st2["final_cost"] - st1["final_cost"]) <= 1e-4 * st1["final_cost"]
+    assert st2["pcg_iterations"] < st1["pcg_iterations"]
