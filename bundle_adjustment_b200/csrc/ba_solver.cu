@@ -9,6 +9,7 @@
 #include "ba_kernels.cuh"
 #include "ba_tiles.cuh"
 #include "ba_peer.cuh"
+#include "ba_host_math.h"
 #include "ba_triangulate.cuh"
 
 #include <cub/cub.cuh>
@@ -1270,39 +1271,10 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
             launch(h, KN_SETUP, k_coarse_column, cdiv(nz, 128), 128, 0, P.n_cams, agg, nz, (const double*)h->coarse_w.p,
                    h->coarse_A.p + (size_t)j * nz);
         }
-        std::vector<double> A((size_t)nz * nz), Ainv((size_t)nz * nz, 0.0);
+        std::vector<double> A((size_t)nz * nz), Ainv;
         CK(cudaMemcpyAsync(A.data(), h->coarse_A.p, A.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
         CK(cudaStreamSynchronize(s));
-        // symmetrise, Cholesky A = L L^T (in place, lower), inverse = L^-T L^-1
-        for (int i = 0; i < nz; ++i)
-            for (int j = 0; j < i; ++j) A[(size_t)i * nz + j] = A[(size_t)j * nz + i] = 0.5 * (A[(size_t)i * nz + j] + A[(size_t)j * nz + i]);
-        for (int j = 0; j < nz; ++j) {
-            double d = A[(size_t)j * nz + j];
-            for (int k = 0; k < j; ++k) d -= A[(size_t)j * nz + k] * A[(size_t)j * nz + k];
-            if (!(d > 0.0)) return false;  // not positive definite (degenerate aggregate): stay with Schur-Jacobi
-            const double l = std::sqrt(d);
-            A[(size_t)j * nz + j] = l;
-            for (int i = j + 1; i < nz; ++i) {
-                double v = A[(size_t)i * nz + j];
-                for (int k = 0; k < j; ++k) v -= A[(size_t)i * nz + k] * A[(size_t)j * nz + k];
-                A[(size_t)i * nz + j] = v / l;
-            }
-        }
-        std::vector<double> Li((size_t)nz * nz, 0.0);  // L^-1 (lower), column by column
-        for (int c = 0; c < nz; ++c) {
-            Li[(size_t)c * nz + c] = 1.0 / A[(size_t)c * nz + c];
-            for (int i = c + 1; i < nz; ++i) {
-                double v = 0.0;
-                for (int k = c; k < i; ++k) v -= A[(size_t)i * nz + k] * Li[(size_t)k * nz + c];
-                Li[(size_t)i * nz + c] = v / A[(size_t)i * nz + i];
-            }
-        }
-        for (int i = 0; i < nz; ++i)
-            for (int j = 0; j <= i; ++j) {
-                double v = 0.0;
-                for (int k = i; k < nz; ++k) v += Li[(size_t)k * nz + i] * Li[(size_t)k * nz + j];
-                Ainv[(size_t)i * nz + j] = Ainv[(size_t)j * nz + i] = v;
-            }
+        if (!spd_inverse_host(A, nz, Ainv)) return false;  // not positive definite (degenerate aggregate): stay with Schur-Jacobi
         CK(cudaMemcpyAsync(h->coarse_Ainv.p, Ainv.data(), Ainv.size() * sizeof(double), cudaMemcpyHostToDevice, s));
         CK(cudaStreamSynchronize(s));
         return true;

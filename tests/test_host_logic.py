@@ -108,6 +108,60 @@ def test_run_host_path_with_a_stub_solver():
     assert np.array_equal(gmap.map_points[seen[3]].position, before[seen[3]] + 1.0)
 
 
+def test_host_spd_inverse_against_numpy(tmp_path):
+    """csrc/ba_host_math.h (inverse of the two-level preconditioner's coarse matrix), compiled with g++, against numpy:
+    a well-conditioned and a badly scaled SPD matrix, and the refusal of an indefinite one."""
+    import shutil
+    import subprocess
+    if not shutil.which("g++"):
+        pytest.skip("no g++")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = tmp_path / "inv.cpp"
+    src.write_text('''
+#include "ba_host_math.h"
+#include <cstdio>
+int main(int argc, char** argv) {
+    int n = 0;
+    FILE* f = fopen(argv[1], "rb");
+    if (fread(&n, sizeof n, 1, f) != 1) return 2;
+    std::vector<double> A((size_t)n * n), Ainv;
+    if (fread(A.data(), sizeof(double), A.size(), f) != A.size()) return 2;
+    fclose(f);
+    const bool ok = ba::spd_inverse_host(A, n, Ainv);
+    f = fopen(argv[2], "wb");
+    int flag = ok ? 1 : 0;
+    fwrite(&flag, sizeof flag, 1, f);
+    if (ok) fwrite(Ainv.data(), sizeof(double), Ainv.size(), f);
+    fclose(f);
+    return 0;
+}
+''')
+    exe = tmp_path / "inv"
+    subprocess.run(["g++", "-O2", "-std=c++17", "-I", os.path.join(root, "bundle_adjustment_b200", "csrc"), "-o", str(exe), str(src)], check=True)
+
+    def run(A):
+        n = A.shape[0]
+        (tmp_path / "a.bin").write_bytes(np.int32(n).tobytes() + np.ascontiguousarray(A, dtype=np.float64).tobytes())
+        subprocess.run([str(exe), str(tmp_path / "a.bin"), str(tmp_path / "o.bin")], check=True)
+        raw = (tmp_path / "o.bin").read_bytes()
+        ok = np.frombuffer(raw[:4], dtype=np.int32)[0] == 1
+        return ok, (np.frombuffer(raw[4:], dtype=np.float64).reshape(n, n) if ok else None)
+
+    rng = np.random.default_rng(3)
+    B = rng.normal(size=(90, 90))
+    A = B @ B.T + 90 * np.eye(90)
+    A_noisy = A + 1e-12 * rng.normal(size=A.shape)            # probing leaves rounding-level asymmetry
+    ok, Ai = run(A_noisy)
+    assert ok and np.abs(Ai - np.linalg.inv(A)).max() <= 1e-9 * np.abs(np.linalg.inv(A)).max()
+    assert np.array_equal(Ai, Ai.T)
+    D = np.diag(10.0 ** rng.uniform(-4, 4, 90))                # rotation and translation blocks differ by orders of magnitude
+    ok, Ai = run(D @ A @ D)
+    assert ok and np.abs(Ai @ (D @ A @ D) - np.eye(90)).max() <= 1e-6
+    A[5, 5] = -1.0
+    ok, _ = run(A)
+    assert not ok
+
+
 def test_geometry_matches_oracle():
     rng = np.random.default_rng(1)
     for _ in range(100):
