@@ -15,7 +15,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libba_b200.so")
 
 ROBUST = {"none": 0, "irls": 1, "triggs": 2}
-PRECOND = {"jacobi": 0, "schur_jacobi": 1, "two_level": 2}
+PRECOND = {"jacobi": 0, "schur_jacobi": 1, "two_level": 2, "auto": 3}
+PRECOND_NAME = {v: k for k, v in PRECOND.items()}
 SCHUR_PATH = {"tiles": 0, "two_pass": 1, "tiles_rows": 2}
 STATUS_TEXT = {0: "iteration limit", 1: "gtol", 2: "ftol", 3: "xtol", 4: "ftol and xtol", 5: "damping limit"}
 
@@ -32,7 +33,8 @@ class Options(C.Structure):
                 ("lambda_min", C.c_double), ("lambda_max", C.c_double), ("precond", C.c_int32),
                 ("pcg_max_iters", C.c_int32), ("pcg_tol", C.c_double), ("pcg_check_every", C.c_int32),
                 ("verbose", C.c_int32), ("schur_path", C.c_int32), ("pcg_tail", C.c_int32),
-                ("device_loop", C.c_int32), ("reserved", C.c_int32 * 4)]
+                ("device_loop", C.c_int32), ("coarse_aggregate", C.c_int32), ("coarse_after", C.c_int32),
+                ("reserved", C.c_int32 * 2)]
 
 
 class Stats(C.Structure):
@@ -40,11 +42,13 @@ class Stats(C.Structure):
                 ("pcg_iterations", C.c_int32), ("launches", C.c_int32), ("initial_raw_cost", C.c_double),
                 ("final_raw_cost", C.c_double), ("initial_cost", C.c_double), ("final_cost", C.c_double),
                 ("gradient_max", C.c_double), ("final_lambda", C.c_double), ("solve_ms", C.c_double),
-                ("reserved", C.c_double * 8)]
+                ("precond_used", C.c_int32), ("coarse_builds", C.c_int32), ("coarse_matvecs", C.c_int32),
+                ("coarse_unknowns", C.c_int32), ("reserved", C.c_double * 6)]
 
     def as_dict(self):
         d = {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
         d["status_text"] = STATUS_TEXT.get(self.status, "?")
+        d["precond_text"] = PRECOND_NAME.get(self.precond_used, "?")
         return d
 
 

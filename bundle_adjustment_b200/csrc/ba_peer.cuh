@@ -406,23 +406,128 @@ __global__ void __launch_bounds__(PT_THREADS, 1) k_pcg_tail(Params P, double tol
     }
 }
 
-// ---- coarse space: probing and the first preconditioned residual of a PCG solve -----------------------------------
-// probe vector of coarse unknown j: 1 in component (j % 6) of every camera of aggregate j / 6, 0 elsewhere
-__global__ void k_coarse_probe(int n_cams, int agg, int j, double* __restrict__ probe) {
+// ---- coarse space: coloured probing, the inverse of the coarse matrix, the first preconditioned residual ---------------
+//
+// A0 = Z^T S Z couples two aggregates only if a point is seen from both.  adj[a * n_agg + b] = 1 marks such pairs (bytes,
+// idempotent plain stores: no atomics, no order dependence).  The host colours the aggregates so that no aggregate is
+// coupled to two of one colour (ba_solver.cu: coarse_colouring); one mat-vec then probes a whole colour at once.
+__global__ void k_agg_adjacency(int n_pts, int n_cams, int agg, int n_agg, const int* __restrict__ pt_off,
+                                const int2* __restrict__ pm_idx, unsigned char* __restrict__ adj) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pts) return;
+    const int o0 = pt_off[p], o1 = pt_off[p + 1];
+    for (int i = o0; i < o1; ++i) {
+        const int ci = pm_idx[i].x;
+        if (ci >= n_cams) continue;  // the fixed camera has no unknowns
+        const int ai = ci / agg;
+        for (int j = o0; j < o1; ++j) {
+            const int cj = pm_idx[j].x;
+            if (cj < n_cams) adj[(size_t)ai * n_agg + cj / agg] = 1;
+        }
+    }
+}
+// probe vector of (colour, component d): 1 in component d of every camera whose aggregate has that colour
+__global__ void k_coarse_probe(int n_cams, int agg, const int* __restrict__ colour, int col, int d, double* __restrict__ probe) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (n_cams + 1) * 6) return;
-    const int c = i / 6, d = i - 6 * c;
-    probe[i] = (c < n_cams && c / agg == j / 6 && d == j % 6) ? 1.0 : 0.0;
+    const int c = i / 6, e = i - 6 * c;
+    probe[i] = (c < n_cams && e == d && colour[c / agg] == col) ? 1.0 : 0.0;
 }
-// column j of A0 = Z^T (S probe_j): per-aggregate sums of w in camera order
-__global__ void k_coarse_column(int n_cams, int agg, int nz, const double* __restrict__ w, double* __restrict__ col) {
+// w = S_local * probe(colour, d): the aggregate sums of w (camera order) are the entries A0[6 b + e][6 a + d] of the one
+// aggregate a of that colour that b is coupled to (nb[b]; -1: none).
+__global__ void k_coarse_scatter(int n_cams, int agg, int nz, int d, const int* __restrict__ nb, const double* __restrict__ w,
+                                 double* __restrict__ A) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= nz) return;
-    const int a = t / 6, d = t - 6 * a;
-    const int c0 = a * agg, c1 = min(c0 + agg, n_cams);
+    const int b = t / 6, e = t - 6 * b;
+    const int a = nb[b];
+    if (a < 0) return;
+    const int c0 = b * agg, c1 = min(c0 + agg, n_cams);
     double s = 0.0;
-    for (int c = c0; c < c1; ++c) s += w[(size_t)c * 6 + d];
-    col[t] = s;
+    for (int c = c0; c < c1; ++c) s += w[(size_t)c * 6 + e];
+    A[(size_t)t * nz + 6 * a + d] = s;
+}
+// after the sum over the ranks: + lambda Z^T D Z (diagonal: the aggregates are disjoint) and symmetrise
+__global__ void k_coarse_finish(int n_cams, int agg, int nz, const double* __restrict__ cam_D, const LMState* __restrict__ st,
+                                const double* __restrict__ A, double* __restrict__ out) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= nz * nz) return;
+    const int i = idx / nz, j = idx - i * nz;
+    double v = 0.5 * (A[(size_t)i * nz + j] + A[(size_t)j * nz + i]);
+    if (i == j) {
+        const int a = i / 6, d = i - 6 * a;
+        const int c0 = a * agg, c1 = min(c0 + agg, n_cams);
+        double s = 0.0;
+        for (int c = c0; c < c1; ++c) s += cam_D[(size_t)c * 6 + d];
+        v += st->lambda * s;
+    }
+    out[idx] = v;
+}
+
+// In-place inverse of the symmetric positive definite coarse matrix by Gauss-Jordan elimination without pivoting, on ONE
+// thread-block cluster: CTA r keeps rows [r * rows_per, ...) in shared memory, the scaled pivot row of step k travels through
+// distributed shared memory (two buffers alternate, so one cluster barrier per step suffices).  n^3 multiply-adds spread over
+// the cluster, n barriers: ~0.5 ms for n = 336 against tens of milliseconds for a host factorisation plus two copies and a
+// synchronisation.  flag[0] = 1 when a pivot is not positive (matrix not positive definite; the result is then unusable).
+__host__ __device__ inline size_t spd_smem_bytes(int n, int cluster) {
+    const int rows_per = (n + cluster - 1) / cluster;
+    return ((size_t)rows_per * n + 3 * (size_t)n) * sizeof(double);
+}
+__global__ void __launch_bounds__(PT_THREADS, 1) k_spd_inverse(int n, const double* __restrict__ A, double* __restrict__ Ainv,
+                                                                int* __restrict__ flag) {
+    extern __shared__ __align__(16) double dsm[];
+    __shared__ int s_bad;
+    namespace cgx = cooperative_groups;
+    cgx::cluster_group cl = cgx::this_cluster();
+    const int R = (int)cl.block_rank(), CL = (int)cl.num_blocks();
+    const int tid = threadIdx.x;
+    const int rows_per = (n + CL - 1) / CL;
+    const int r0 = min(R * rows_per, n), r1 = min(r0 + rows_per, n);
+    const int nr = r1 - r0;
+    double* M = dsm;                             // [rows_per][n] my rows
+    double* prow = dsm + (size_t)rows_per * n;   // [2][n] pivot rows published by their owners
+    double* lrow = prow + 2 * (size_t)n;         // [n] local copy of the current pivot row
+    for (int l = tid; l < nr * n; l += PT_THREADS) M[l] = A[(size_t)r0 * n + l];
+    if (tid == 0) s_bad = 0;
+    __syncthreads();
+    for (int k = 0; k < n; ++k) {
+        const int owner = k / rows_per;
+        double* mine = prow + (size_t)(k & 1) * n;
+        if (R == owner) {
+            double* row = M + (size_t)(k - r0) * n;
+            const double piv = row[k];
+            if (!(piv > 0.0) || !isfinite(piv)) { if (tid == 0) s_bad = 1; }
+            const double ip = 1.0 / piv;
+            __syncthreads();
+            for (int j = tid; j < n; j += PT_THREADS) {
+                const double v = (j == k) ? ip : row[j] * ip;
+                row[j] = v;
+                mine[j] = v;
+            }
+        }
+        cl.sync();
+        const double* pr = cl.map_shared_rank(prow, owner) + (size_t)(k & 1) * n;
+        for (int j = tid; j < n; j += PT_THREADS) lrow[j] = pr[j];  // one remote read per element
+        __syncthreads();
+        // every row i != k of mine: f = a_ik; a_ij -= f * p_j (j != k); a_ik = -f * p_k
+        for (int l = tid; l < nr * n; l += PT_THREADS) {
+            const int i = l / n, j = l - i * n;
+            if (r0 + i == k) continue;
+            const double f = M[(size_t)i * n + k];
+            // column k is read by every thread of the row in this step: it is rewritten after the barrier below
+            if (j != k) M[l] -= f * lrow[j];
+        }
+        __syncthreads();
+        {
+            const double pk = lrow[k];
+            for (int i = tid; i < nr; i += PT_THREADS)
+                if (r0 + i != k) M[(size_t)i * n + k] = -M[(size_t)i * n + k] * pk;
+        }
+        __syncthreads();
+    }
+    cl.sync();  // nobody leaves while a peer may still read its pivot buffer
+    for (int l = tid; l < nr * n; l += PT_THREADS) Ainv[(size_t)r0 * n + l] = M[l];
+    if (tid == 0 && s_bad) atomicExch(flag, 1);
 }
 // After k_camera_finish_schur (u = Minv r, gamma = r.u): add the coarse correction to u and redo gamma.  One CTA.
 __global__ void __launch_bounds__(PT_THREADS) k_coarse_first(Params P, Coarse C, unsigned long long pcg_loop) {

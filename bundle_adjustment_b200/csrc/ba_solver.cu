@@ -418,8 +418,11 @@ struct ba_handle {
     // peer-memory exchange of the PCG mat-vec partials (ba_peer.cuh); multi-GPU handles only
     bool peer_ok = false;
     // two-level preconditioner (BA_PRECOND_TWO_LEVEL): coarse matrix of the current solve
-    DBuf<double> coarse_Ainv, coarse_A, coarse_probe, coarse_w;
+    DBuf<double> coarse_Ainv, coarse_A, coarse_A2, coarse_probe, coarse_w;
+    DBuf<unsigned char> coarse_adj;
+    DBuf<int> coarse_colour, coarse_nb, coarse_flag;
     int coarse_agg = 32, coarse_nz = 0;
+    int coarse_colours = 0, coarse_graph_agg = 0;  // colouring of the aggregate graph of the uploaded problem (0: not built)
     bool coarse_ready = false;
     int xcap = 0;
     int xpush = 2;  // exchange by remote loads (0, pull), remote stores + flags (1, push), remote stores of LL words (2)
@@ -799,6 +802,19 @@ static void launch_tile_matvec(ba_handle* h, const Params& Q, bool acc, const do
     else launch(h, KN_TILE_MV, k_tile_pass<0, false>, h->ft_grid, FT_THREADS, ft_smem_bytes(FT_ROWS_MV), Q, vec);
 }
 
+// Unmap the peers' exchange buffers and wait until every rank has done the same: freeing memory that a peer still has
+// mapped through cudaIpc is undefined behaviour.  Collective.
+static void close_peer_maps(ba_handle* h) {
+    bool any = false;
+    for (size_t r = 0; r < h->peer_ptr.size(); ++r)
+        if (h->peer_ptr[r] && (int)r != h->rank) { cudaIpcCloseMemHandle(h->peer_ptr[r]); any = true; }
+    h->peer_ptr.assign(h->nranks, nullptr);
+    if (!any || !h->comm || !h->xstate.p) return;
+    // xstate[3] is a spare word; the all-reduce is only a barrier across the ranks
+    NK(nccl_api().AllReduce(h->xstate.p + 3, h->xstate.p + 3, 1, ncclInt, ncclSum, h->comm, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+}
+
 // Map every rank's exchange buffer into this process (collective: all ranks call it with the same n_cams).
 // Falls back to the NCCL all-reduce (peer_ok = false on EVERY rank) if any rank cannot map a peer.
 static void setup_peer_exchange(ba_handle* h, int n_cams) {
@@ -808,9 +824,7 @@ static void setup_peer_exchange(ba_handle* h, int n_cams) {
     cudaStream_t s = h->stream;
     ScratchScope scratch(s);
     CK(cudaStreamSynchronize(s));
-    for (size_t r = 0; r < h->peer_ptr.size(); ++r)
-        if (h->peer_ptr[r] && (int)r != h->rank) cudaIpcCloseMemHandle(h->peer_ptr[r]);
-    h->peer_ptr.assign(h->nranks, nullptr);
+    close_peer_maps(h);
     h->peer_ok = false;
     h->xbuf.release();
     h->xbuf.alloc(xb_doubles(h->nranks, need));
@@ -875,6 +889,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     cudaStream_t s = h->stream;
     ScratchScope scratch(s);
     h->have_problem = false;
+    h->coarse_colours = 0; h->coarse_graph_agg = 0;  // the aggregate graph belongs to the problem
     const size_t nc1 = (size_t)n_cams + 1;
     StageTimer tm(s);
 
@@ -1216,7 +1231,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     h->time_kernels = opt->verbose >= 2;
     const int check_every = std::max(1, opt->pcg_check_every);
     const int with_schur = opt->precond >= BA_PRECOND_SCHUR_JACOBI ? 1 : 0;
-    if (opt->precond < BA_PRECOND_JACOBI || opt->precond > BA_PRECOND_TWO_LEVEL) fail(BA_ERR_ARG, "unknown preconditioner %d", opt->precond);
+    if (opt->precond < BA_PRECOND_JACOBI || opt->precond > BA_PRECOND_AUTO) fail(BA_ERR_ARG, "unknown preconditioner %d", opt->precond);
     const int nc1 = P.n_cams + 1;
     if (opt->schur_path < BA_PATH_TILES || opt->schur_path > BA_PATH_TILES_ROWS) fail(BA_ERR_ARG, "unknown schur_path %d", opt->schur_path);
     const bool tiles = opt->schur_path != BA_PATH_TWO_PASS && h->fused_ok;
@@ -1229,6 +1244,9 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     long long graph_launches[KN_COUNT] = {0};
 
     CK(cudaEventRecord(h->ev_solve0, s));
+    // the two kernel paths write the per-tile step sums into different rows of pm_partial and k_reduce_scalars adds ALL rows:
+    // leftovers of a solve on the other path must not survive into this one
+    h->pm_partial.zero(s);
     launch(h, KN_SETUP, k_init_state, 1, 1, 0, h->st.p, opt->initial_lambda);
     launch(h, KN_CAM_PREP, k_cam_prepare, cdiv(nc1, 256), 256, 0, P, 2);
     lin_points_and_cost(h, 2);
@@ -1242,44 +1260,111 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     int status = opt->max_iters == 0 ? 6 : 0;
     unsigned long long pcg_loop = 0, lm_loop = 0;  // conditional handles of the device-side loops (0: host loops)
 
-    // ---- two-level preconditioner (EXPERIMENTAL, see BA_PRECOND_TWO_LEVEL): single GPU, default kernel path, host loops.
-    //      The coarse matrix A0 = Z^T S Z is probed with the tile pass once the PCG of an LM iteration has needed more than
-    //      15 iterations (the damping has reached its floor by then and S changes little), inverted on the host and kept to the
-    //      end of the solve.
-    bool two_level = opt->precond == BA_PRECOND_TWO_LEVEL && h->nranks == 1 && tiles && tail && P.n_cams > 0;
+    // ---- two-level preconditioner (BA_PRECOND_TWO_LEVEL / AUTO): default kernel path (tiles + cluster tail, peer exchange on
+    //      N > 1 GPUs), host loops.  The coarse matrix A0 = Z^T S Z is probed with the tile pass once the PCG of an LM iteration
+    //      has needed more than 15 iterations (the damping has reached its floor by then and S changes little), inverted on the
+    //      device and kept; it is rebuilt when the iteration count climbs past 30 again.
+    const bool want_two_level = opt->precond == BA_PRECOND_TWO_LEVEL || (opt->precond == BA_PRECOND_AUTO && P.n_cams >= 128);
+    bool two_level = want_two_level && tiles && tail && P.n_cams > 0;
     h->coarse_ready = false;
+    int coarse_builds = 0, coarse_matvecs = 0, coarse_built_at = -1000;
+    const int coarse_after = opt->coarse_after == 0 ? 15 : opt->coarse_after;
     if (two_level) {
-        if (const char* e = getenv("BA_B200_COARSE_AGG")) h->coarse_agg = std::max(1, atoi(e));
+        h->coarse_agg = opt->coarse_aggregate > 0 ? opt->coarse_aggregate : std::max(32, cdiv(P.n_cams, 64));
         h->coarse_nz = 6 * cdiv(P.n_cams, h->coarse_agg);
         const size_t cb = pt_smem_bytes(P.n_cams, h->tail_cluster, h->coarse_nz, h->coarse_agg);
-        if (cudaFuncSetAttribute(k_pcg_tail<false, true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess ||
-            cudaFuncSetAttribute(k_pcg_tail<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(cb, (size_t)1024)) != cudaSuccess) {
+        const void* fn = h->nranks > 1 ? (const void*)k_pcg_tail<true, true> : (const void*)k_pcg_tail<false, true>;
+        if (cb > 200 * 1024 || cudaFuncSetAttribute(fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess ||
+            cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(cb, (size_t)1024)) != cudaSuccess) {
             cudaGetLastError();
-            two_level = false;  // the coarse tail does not fit this device: plain Schur-Jacobi
+            two_level = false;  // the coarse tail does not fit this device: plain Schur-Jacobi (reported in ba_stats)
         }
     }
+    // Colour the aggregates so that no aggregate is coupled (through a shared point) to two aggregates of one colour: a probe
+    // vector can then carry a whole colour.  Local to this rank's points - every rank probes its own part of S.
+    auto coarse_colouring = [&]() {
+        const int agg = h->coarse_agg, na = h->coarse_nz / 6;
+        if (h->coarse_graph_agg == agg && h->coarse_colours > 0) return;
+        h->coarse_adj.alloc((size_t)na * na);
+        h->coarse_adj.zero(s);
+        launch(h, KN_SETUP, k_agg_adjacency, cdiv(P.n_pts, 128), 128, 0, P.n_pts, P.n_cams, agg, na, P.pt_off, P.pm_idx, h->coarse_adj.p);
+        std::vector<unsigned char> adj((size_t)na * na);
+        CK(cudaMemcpyAsync(adj.data(), h->coarse_adj.p, adj.size(), cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+        for (int a = 0; a < na; ++a) adj[(size_t)a * na + a] = 1;
+        // columns a, b conflict when some row is coupled to both
+        std::vector<int> colour(na, -1);
+        int ncol = 0;
+        std::vector<char> used;
+        for (int a = 0; a < na; ++a) {
+            used.assign(ncol + 1, 0);
+            for (int r = 0; r < na; ++r) {
+                if (!adj[(size_t)r * na + a]) continue;
+                for (int b = 0; b < a; ++b)
+                    if (adj[(size_t)r * na + b]) used[colour[b]] = 1;
+            }
+            int c = 0;
+            while (used[c]) ++c;
+            colour[a] = c;
+            ncol = std::max(ncol, c + 1);
+        }
+        // nb[col][b] = the aggregate of colour col that b is coupled to (at most one), -1 if none
+        std::vector<int> nb((size_t)ncol * na, -1);
+        for (int b = 0; b < na; ++b)
+            for (int a = 0; a < na; ++a)
+                if (adj[(size_t)b * na + a]) nb[(size_t)colour[a] * na + b] = a;
+        h->coarse_colour.alloc(na); h->coarse_nb.alloc(nb.size());
+        CK(cudaMemcpyAsync(h->coarse_colour.p, colour.data(), (size_t)na * sizeof(int), cudaMemcpyHostToDevice, s));
+        CK(cudaMemcpyAsync(h->coarse_nb.p, nb.data(), nb.size() * sizeof(int), cudaMemcpyHostToDevice, s));
+        CK(cudaStreamSynchronize(s));
+        h->coarse_colours = ncol; h->coarse_graph_agg = agg;
+    };
     auto build_coarse = [&]() {  // between k_camera_finish_schur and the first PCG iteration: V^-1, lambda and D are current
-        const int nz = h->coarse_nz, agg = h->coarse_agg;
-        h->coarse_A.alloc((size_t)nz * nz); h->coarse_Ainv.alloc((size_t)nz * nz);
-        h->coarse_probe.alloc((size_t)nc1 * 6); h->coarse_w.alloc((size_t)nc1 * 6);
-        Params PQ = PA;  // the row finish reads the probe instead of u and leaves S * probe in a scratch vector
-        PQ.v_u = h->coarse_probe.p; PQ.v_w = h->coarse_w.p;
-        for (int j = 0; j < nz; ++j) {
-            launch(h, KN_SETUP, k_coarse_probe, cdiv(nc1 * 6, 256), 256, 0, P.n_cams, agg, j, h->coarse_probe.p);
-            launch_tile_matvec(h, PA, acc, h->coarse_probe.p);
-            launch(h, KN_ROWS_FIN, k_rows_finish<false>, cdiv(P.n_cams, RS_WARPS), RS_WARPS * 32, 0, PQ);
-            launch(h, KN_SETUP, k_coarse_column, cdiv(nz, 128), 128, 0, P.n_cams, agg, nz, (const double*)h->coarse_w.p,
-                   h->coarse_A.p + (size_t)j * nz);
+        const int nz = h->coarse_nz, agg = h->coarse_agg, na = nz / 6;
+        coarse_colouring();
+        h->coarse_A.alloc((size_t)nz * nz); h->coarse_A2.alloc((size_t)nz * nz); h->coarse_Ainv.alloc((size_t)nz * nz);
+        h->coarse_probe.alloc((size_t)nc1 * 6); h->coarse_w.alloc((size_t)nc1 * 6); h->coarse_flag.alloc(1);
+        h->coarse_A.zero(s); h->coarse_flag.zero(s);
+        Params PQ = PA;  // the row finish leaves this rank's part of S * probe (without the damping term) in a scratch vector
+        PQ.cam_acc = h->coarse_w.p;
+        for (int col = 0; col < h->coarse_colours; ++col)
+            for (int d = 0; d < 6; ++d) {
+                launch(h, KN_SETUP, k_coarse_probe, cdiv(nc1 * 6, 256), 256, 0, P.n_cams, agg, (const int*)h->coarse_colour.p, col, d,
+                       h->coarse_probe.p);
+                launch_tile_matvec(h, PA, acc, h->coarse_probe.p);
+                launch(h, KN_ROWS_FIN, k_rows_finish<true>, cdiv(P.n_cams, RS_WARPS), RS_WARPS * 32, 0, PQ);
+                launch(h, KN_SETUP, k_coarse_scatter, cdiv(nz, 128), 128, 0, P.n_cams, agg, nz, d,
+                       (const int*)(h->coarse_nb.p + (size_t)col * na), (const double*)h->coarse_w.p, h->coarse_A.p);
+                ++coarse_matvecs;
+            }
+        allreduce_sum(h, h->coarse_A.p, (size_t)nz * nz);
+        launch(h, KN_SETUP, k_coarse_finish, cdiv((long long)nz * nz, 256), 256, 0, P.n_cams, agg, nz, (const double*)P.cam_D,
+               (const LMState*)h->st.p, (const double*)h->coarse_A.p, h->coarse_A2.p);
+        ++coarse_builds;
+        // inverse on the device by the tail's cluster when its rows fit shared memory, else on the host
+        int cl = h->tail_cluster;
+        const size_t sb = spd_smem_bytes(nz, cl);
+        bool on_device = cl >= 1 && sb <= 200 * 1024 && !getenv("BA_B200_HOST_INVERSE") &&
+                         cudaFuncSetAttribute(k_spd_inverse, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess &&
+                         cudaFuncSetAttribute(k_spd_inverse, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb) == cudaSuccess;
+        cudaGetLastError();
+        if (on_device) {
+            launch_cluster(h, KN_SETUP, k_spd_inverse, cl, PT_THREADS, sb, nz, (const double*)h->coarse_A2.p, h->coarse_Ainv.p,
+                           h->coarse_flag.p);
+            int bad = 0;
+            CK(cudaMemcpyAsync(&bad, h->coarse_flag.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+            CK(cudaStreamSynchronize(s));
+            return bad == 0;
         }
         std::vector<double> A((size_t)nz * nz), Ainv;
-        CK(cudaMemcpyAsync(A.data(), h->coarse_A.p, A.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(A.data(), h->coarse_A2.p, A.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
         CK(cudaStreamSynchronize(s));
         if (!spd_inverse_host(A, nz, Ainv)) return false;  // not positive definite (degenerate aggregate): stay with Schur-Jacobi
         CK(cudaMemcpyAsync(h->coarse_Ainv.p, Ainv.data(), Ainv.size() * sizeof(double), cudaMemcpyHostToDevice, s));
         CK(cudaStreamSynchronize(s));
         return true;
     };
-    int last_pcg_iters = 0;
+    int last_pcg_iters = 0, lm_iter_host = 0;
     bool coarse_failed = false;
 
     // ---- the three parts of one LM iteration ------------------------------------------------------------------
@@ -1294,10 +1379,14 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
             launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 27, 256), 256, 0, P, 27, 0);
             allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 27);
             launch(h, KN_CAM_FIN, k_camera_finish_schur, P.vec_ctas, VEC_THREADS, 0, P, with_schur, h->ticket.p, pcg_loop);
-            if (two_level && !h->coarse_ready && !coarse_failed && last_pcg_iters > 15) {
+            const bool first_build = !h->coarse_ready && last_pcg_iters > coarse_after;
+            const bool rebuild = h->coarse_ready && last_pcg_iters > 30 && lm_iter_host - coarse_built_at >= 3;
+            if (two_level && !coarse_failed && (first_build || rebuild)) {
+                const bool was_ready = h->coarse_ready;
                 h->coarse_ready = build_coarse();
                 coarse_failed = !h->coarse_ready;
-                if (pcg_graph) { CK(cudaGraphExecDestroy(pcg_graph)); pcg_graph = nullptr; }  // the tail of the graph changes
+                coarse_built_at = lm_iter_host;
+                if (pcg_graph && was_ready != h->coarse_ready) { CK(cudaGraphExecDestroy(pcg_graph)); pcg_graph = nullptr; }  // the tail of the graph changes
             }
             if (two_level && h->coarse_ready)
                 launch(h, KN_CAM_FIN, k_coarse_first, 1, PT_THREADS, 2 * (size_t)h->coarse_nz * sizeof(double), P,
@@ -1310,7 +1399,12 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
             launch_tile_matvec(h, PA, acc, h->v_u.p);
             const size_t bytes = pt_smem_bytes(P.n_cams, h->tail_cluster);
             const Coarse none{nullptr, 1, 0};
-            if (h->nranks > 1)
+            if (h->nranks > 1 && two_level && h->coarse_ready)
+                launch_cluster(h, KN_PCG_TAIL, k_pcg_tail<true, true>, h->tail_cluster, PT_THREADS,
+                               pt_smem_bytes(P.n_cams, h->tail_cluster, h->coarse_nz, h->coarse_agg), PA, opt->pcg_tol, opt->pcg_max_iters,
+                               h->xbuf.p, (double* const*)h->d_peers.p, h->nranks, h->rank, h->xpush, h->xcap, h->xstate.p, pcg_loop,
+                               Coarse{h->coarse_Ainv.p, h->coarse_agg, h->coarse_nz});
+            else if (h->nranks > 1)
                 launch_cluster(h, KN_PCG_TAIL, k_pcg_tail<true, false>, h->tail_cluster, PT_THREADS, bytes, PA, opt->pcg_tol, opt->pcg_max_iters,
                                h->xbuf.p, (double* const*)h->d_peers.p, h->nranks, h->rank, h->xpush, h->xcap, h->xstate.p, pcg_loop, none);
             else if (two_level && h->coarse_ready)
@@ -1479,6 +1573,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
         status = st.status;
         need_lin = st.last_accepted != 0;
         last_pcg_iters = st.pcg_iter;
+        lm_iter_host = st.iter;
         if (opt->verbose & 1)
             fprintf(stderr, "[ba_b200] it %3d %s cost %.9e -> trial %.9e  rho %+.3e  lambda %.3e  pcg %d  |g| %.3e  |dx| %.3e\n",
                     st.iter, st.last_accepted ? "acc" : "REJ", st.cost[st.cur ^ (st.last_accepted ? 1 : 0)], st.scal[S_COST], st.rho,
@@ -1510,6 +1605,9 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
         out->initial_raw_cost = raw0; out->initial_cost = cost0;
         out->final_raw_cost = st.raw[st.cur]; out->final_cost = st.cost[st.cur];
         out->gradient_max = st.gmax; out->final_lambda = st.lambda; out->solve_ms = ms;
+        out->precond_used = coarse_builds > 0 && !coarse_failed ? BA_PRECOND_TWO_LEVEL : with_schur ? BA_PRECOND_SCHUR_JACOBI : BA_PRECOND_JACOBI;
+        out->coarse_builds = coarse_builds; out->coarse_matvecs = coarse_matvecs;
+        out->coarse_unknowns = coarse_builds > 0 ? h->coarse_nz : 0;
     }
 }
 
@@ -1539,10 +1637,10 @@ void ba_default_options(ba_options* o) {
     if (!o) return;
     memset(o, 0, sizeof *o);
     o->max_iters = 50;
-    o->gtol = 1e-8; o->ftol = 1e-6; o->xtol = 1e-8;
+    o->gtol = 1e-8; o->ftol = 1e-5; o->xtol = 1e-5;  // the reference's call: src/bundle_adjuster.py:172
     o->huber_delta = 1.0; o->robust_mode = BA_ROBUST_IRLS;
     o->initial_lambda = 1e-4; o->lambda_min = 1e-6; o->lambda_max = 1e16;
-    o->precond = BA_PRECOND_SCHUR_JACOBI;
+    o->precond = BA_PRECOND_AUTO;
     o->pcg_max_iters = 100; o->pcg_tol = 0.1; o->pcg_check_every = 8;
     o->verbose = 0;
     o->schur_path = BA_PATH_TILES;
@@ -1601,6 +1699,8 @@ int ba_destroy(ba_handle* h) {
     if (h) {
         cudaSetDevice(h->device);
         cudaStreamSynchronize(h->stream);
+        // distributed handles: collective - the exchange buffer is freed only after every rank has unmapped it
+        try { ba::close_peer_maps(h); } catch (...) { delete h; throw; }
         delete h;
     }
     API_END

@@ -130,13 +130,19 @@ def _track_lengths(rng, n_pts, n_obs, max_len):
 
 
 def make_flat_problem(n_cams: int, n_pts: int, n_obs: int, seed: int, *, outlier_frac: float = 0.05,
-                      pixel_sigma: float = 0.5, keep_truth: bool = True) -> FlatProblem:
+                      pixel_sigma: float = 0.5, keep_truth: bool = True, well_posed: bool = False) -> FlatProblem:
     """Cameras on a smooth trajectory along +x looking at a slab of points (depth 8-20).
 
     ``n_cams`` counts the fixed camera (camera 0), so ``n_cams - 1`` are adjustable.
     Noise model: pixel noise N(0, 0.5^2), 5 % outliers with uniform +-50 px error,
     uv rounded through float32; initial guess = truth + N(0, 0.003^2) rad on rvec, N(0, 0.02^2) on t,
     N(0, 0.05^2) on points; camera 0 fixed at truth.
+
+    ``well_posed``: the same generator, but the outliers (still ``outlier_frac`` of all observations) are drawn so that
+    every point keeps at least TWO inlier observations.  Under the Huber loss a two-view point with a gross outlier can
+    have its optimum at infinite depth (the outlier asks for a negative disparity): the objective then has an infimum
+    but no minimiser, no solver reaches a stationary point, and "converged cost" is undefined.  The converged-cost
+    parity tests therefore use ``well_posed=True``; everything else (and the bench) keeps the default.
     """
     rng = np.random.default_rng(seed)
     dx = 0.42
@@ -180,7 +186,17 @@ def make_flat_problem(n_cams: int, n_pts: int, n_obs: int, seed: int, *, outlier
 
     uv = project(rvec_true[cam], tvec_true[cam], pts_true[obs_pt])
     uv += rng.normal(0, pixel_sigma, uv.shape)
-    out = rng.random(n_obs) < outlier_frac
+    if well_posed:
+        # rank the observations of each point by a random key; the two smallest keys of a point stay inliers
+        key = rng.random(n_obs)
+        rank = np.empty(n_obs, dtype=np.int64)
+        o = np.lexsort((key, obs_pt))
+        rank[o] = np.arange(n_obs) - np.repeat(start, L)
+        eligible = rank >= 2
+        frac = min(1.0, outlier_frac * n_obs / max(int(eligible.sum()), 1))
+        out = eligible & (rng.random(n_obs) < frac)
+    else:
+        out = rng.random(n_obs) < outlier_frac
     uv[out] += rng.uniform(-50.0, 50.0, (int(out.sum()), 2))
     uv = uv.astype(np.float32).astype(np.float64)
 
@@ -199,14 +215,14 @@ def make_flat_problem(n_cams: int, n_pts: int, n_obs: int, seed: int, *, outlier
                        (cam - 1).astype(np.int32), obs_pt.astype(np.int32), np.ascontiguousarray(uv), truth)
 
 
-def make_named_problem(name: str, scale: float = 1.0, keep_truth: bool = True) -> FlatProblem:
+def make_named_problem(name: str, scale: float = 1.0, keep_truth: bool = True, well_posed: bool = False) -> FlatProblem:
     """One of the BASELINE.json shapes (``SHAPES``), optionally scaled down in points/observations."""
     n_cams, n_pts, n_obs = SHAPES[name]
     if scale != 1.0:
         n_pts = max(int(round(n_pts * scale)), 16)
         n_obs = max(int(round(n_obs * scale)), 2 * n_pts)
         n_cams = max(int(round(n_cams * max(scale, 0.05))), 4)
-    return make_flat_problem(n_cams, n_pts, n_obs, SEEDS[name], keep_truth=keep_truth)
+    return make_flat_problem(n_cams, n_pts, n_obs, SEEDS[name], keep_truth=keep_truth, well_posed=well_posed)
 
 
 # ----------------------------------------------------------------------------------------------

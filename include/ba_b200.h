@@ -43,11 +43,15 @@ typedef struct ba_handle ba_handle;
 #define BA_ROBUST_TRIGGS 2 /* SciPy's scale_for_robust_loss_function: max(rho'+2 rho'' r^2, eps) */
 
 #define BA_PRECOND_JACOBI 0       /* camera blocks of J^T J                                    */
-#define BA_PRECOND_SCHUR_JACOBI 1 /* diagonal blocks of the Schur complement          (default) */
-#define BA_PRECOND_TWO_LEVEL 2    /* EXPERIMENTAL (round 2, not yet validated on the device): Schur-Jacobi plus a coarse
-                                     correction, one rigid 6-vector per aggregate of 32 consecutive cameras, coarse matrix
-                                     by probing with the tile pass once the PCG needs more than 15 iterations
-                                     (single GPU, default kernel path, host-driven loops)           */
+#define BA_PRECOND_SCHUR_JACOBI 1 /* diagonal blocks of the Schur complement                    */
+#define BA_PRECOND_TWO_LEVEL 2    /* Schur-Jacobi plus an additive coarse correction  Z (Z^T S Z)^-1 Z^T : one rigid 6-vector per
+                                     aggregate of consecutive cameras; the coarse matrix is probed with the tile pass (one
+                                     mat-vec per colour of the aggregate graph and component) once the PCG of an LM iteration
+                                     has needed more than 15 iterations, inverted on the device and kept (rebuilt when the
+                                     iteration count climbs again).  Needs the default kernel path (tiles + cluster tail; on
+                                     N > 1 GPUs the peer-memory exchange); where that is unavailable the solve runs with
+                                     Schur-Jacobi and says so in ba_stats.precond_used.  Host-driven loops.              */
+#define BA_PRECOND_AUTO 3         /* two-level for >= 128 adjustable cameras, else Schur-Jacobi               (default) */
 
 #define BA_PATH_TILES 0    /* fused point-tile passes: one kernel per Schur mat-vec          (default) */
 #define BA_PATH_TWO_PASS 1 /* point-major pass + camera-major pass (also used when a track is longer
@@ -76,7 +80,10 @@ typedef struct ba_options {
                                  nodes loop over the LM and the PCG iterations on the device (one launch and one read-back per
                                  solve).  1 (default): for problems of up to 262144 observations (where it is faster); 2: always;
                                  0: the host drives the loops (always the case for verbose / timed / multi-GPU solves) */
-    int32_t reserved[4];
+    int32_t coarse_aggregate; /* cameras per aggregate of the two-level preconditioner; 0 (default) = max(32, n_cams / 64)  */
+    int32_t coarse_after;     /* build the coarse matrix once an LM iteration's PCG needed more than this many iterations;
+                                 0 (default) = 15, negative = from the first LM iteration on                              */
+    int32_t reserved[2];
 } ba_options;
 
 typedef struct ba_stats {
@@ -92,11 +99,16 @@ typedef struct ba_stats {
     double gradient_max;      /* max |g| at the returned point (local camera coordinates)           */
     double final_lambda;
     double solve_ms;          /* CUDA-event time of the device LM loop                              */
-    double reserved[8];
+    int32_t precond_used;     /* BA_PRECOND_* the PCG actually ran with (TWO_LEVEL only if a coarse matrix was built)   */
+    int32_t coarse_builds;    /* coarse matrices built during the solve                                                 */
+    int32_t coarse_matvecs;   /* tile-pass mat-vecs spent on probing them (not counted in pcg_iterations)               */
+    int32_t coarse_unknowns;  /* size of the coarse system (6 x aggregates), 0 if none                                  */
+    double reserved[6];
 } ba_stats;
 
-/* Defaults: max_iters 50, gtol 1e-8, ftol 1e-6, xtol 1e-8, huber 1.0, IRLS, lambda 1e-4 (floor 1e-6: keeps the
- * step bounded along the free scale gauge and along low-parallax depth directions), Schur-Jacobi PCG, tol 0.1. */
+/* Defaults: max_iters 50, gtol 1e-8, ftol = xtol = 1e-5 (the reference's call, src/bundle_adjuster.py:172), huber 1.0, IRLS,
+ * lambda 1e-4 (floor 1e-6: keeps the step bounded along the free scale gauge and along low-parallax depth directions),
+ * PCG with BA_PRECOND_AUTO, forcing term 0.1. */
 void ba_default_options(ba_options* opt);
 
 /* One handle = one GPU + one CUDA stream.  `device` is a CUDA ordinal.  Replaces nothing in the
@@ -110,6 +122,8 @@ int ba_create(int device, ba_handle** out);
 int ba_nccl_unique_id(char id_out[128]);
 int ba_create_distributed(int device, int rank, int nranks, const char nccl_id[128], ba_handle** out);
 
+/* Distributed handles: COLLECTIVE - every rank unmaps its peers' exchange buffers, the ranks meet in one NCCL all-reduce, and
+ * only then is the exported buffer freed (the same order is kept when a later ba_set_problem has to grow it). */
 int ba_destroy(ba_handle* h);
 
 /* Upload one problem.  Replaces the flattening at src/bundle_adjuster.py:150-162 on the device side:

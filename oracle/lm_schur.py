@@ -94,6 +94,10 @@ def weights(r, mode: str):
         return np.maximum(rho1 + 2.0 * rho2 * r * r, O.DBL_EPS), rho1
     if mode == "none":
         return np.ones_like(r), np.ones_like(r)
+    if mode.startswith("hybrid:"):
+        # curvature weight kappa * rho' in the linear regime (kappa = 1: IRLS, kappa = 0: the true second derivative)
+        kappa = float(mode.split(":")[1])
+        return np.where(rho2 < 0.0, np.maximum(kappa * rho1, O.DBL_EPS), rho1), rho1
     raise ValueError(mode)
 
 
@@ -112,7 +116,24 @@ def linearize(prob: O.Problem, rvec, tvec, pts, mode="irls", huber=True) -> Line
     Jc = np.einsum("nij,njk->nik", Jp, G)
     adj = prob.obs_cam >= 0
     Jc[~adj] = 0.0
-    wH, wg = weights(r, mode if huber else "none")
+    if huber and mode.startswith("guarded"):
+        # Per-point guarded second-order weights: a point whose TRUE curvature (rows in the quadratic regime only, the
+        # Triggs / SciPy weights) is at least tau times its IRLS curvature in every direction uses the true weights for all
+        # its rows; any other point (too few inlier rows at the current iterate) keeps the IRLS majoriser.
+        tau = float(mode.split(":")[1]) if ":" in mode else 0.1
+        wT, wg = weights(r, "triggs")
+        wI, _ = weights(r, "irls")
+        Vt = np.zeros((prob.n_pts, 3, 3)); Vi = np.zeros((prob.n_pts, 3, 3))
+        np.add.at(Vt, prob.obs_pt, np.einsum("nki,nk,nkj->nij", Jp, wT, Jp))
+        np.add.at(Vi, prob.obs_pt, np.einsum("nki,nk,nkj->nij", Jp, wI, Jp))
+        # min generalised eigenvalue of (Vt, Vi) through the Cholesky factor of Vi
+        Lc = np.linalg.cholesky(Vi + 1e-300 * np.eye(3))
+        Li = np.linalg.inv(Lc)
+        M = np.einsum("nij,njk,nlk->nil", Li, Vt, Li)
+        safe = np.linalg.eigvalsh(M)[:, 0] >= tau
+        wH = np.where(safe[prob.obs_pt][:, None], wT, wI)
+    else:
+        wH, wg = weights(r, mode if huber else "none")
     cost = O.huber_cost(r.ravel()) if huber else 0.5 * float((r * r).sum())
     V = np.zeros((prob.n_pts, 3, 3)); gp = np.zeros((prob.n_pts, 3))
     U = np.zeros((prob.n_cams, 6, 6)); gc = np.zeros((prob.n_cams, 6))

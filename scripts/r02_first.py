@@ -16,9 +16,15 @@ fp = S.make_named_problem(shape, keep_truth=False)
 s = FlatSolver(0)
 s.set_flat(fp)
 out = {}
-for name, kw in (("schur_jacobi", {}), ("two_level", {"precond": "two_level"})):
-    for rep in range(2):
+keys = ("status_text", "precond_text", "iterations", "pcg_iterations", "coarse_builds", "coarse_matvecs", "final_cost", "solve_ms", "launches")
+for name, kw in (("schur_jacobi ftol=0", {"precond": "schur_jacobi", "ftol": 0.0, "xtol": 0.0}), ("default ftol=0", {"ftol": 0.0, "xtol": 0.0}),
+                 ("default", {})):
+    for rep in range(3):
         s.restore_initial()
-        st = s.solve(max_iters=max_iters, device_loop=0, verbose=1 if rep == 1 else 0, **kw)
+        st = s.solve(max_iters=max_iters, verbose=1 if rep == 2 and name == "default" else 0, **kw)
     out[name] = st
-    print(name, json.dumps({k: st[k] for k in ("status_text", "iterations", "pcg_iterations", "final_cost", "solve_ms", "launches")}), flush=True)
+    print(name, json.dumps({k: st[k] for k in keys}), flush=True)
+s.restore_initial()
+st = s.solve(max_iters=max_iters, verbose=2, pcg_check_every=1)
+ks = s.kernel_stats()
+print("per-kernel us:", "  ".join(f"{k} {1e3 * ms_ / n:.1f}x{n}" for k, (n, ms_) in ks.items() if n and ms_ > 0.0), flush=True)

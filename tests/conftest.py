@@ -24,7 +24,7 @@ def _built_library():
 
 def golden_names():
     """Window fixtures (one reference ``run`` each); recordings of whole pipelines are named pipeline_*."""
-    return sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz") and not f.startswith("pipeline_"))
+    return sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz") and not f.startswith(("pipeline_", "converged_")))
 
 
 def recorded_map(g, k, which="before"):

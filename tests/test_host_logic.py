@@ -31,7 +31,9 @@ def test_default_options_without_gpu():
     o = _capi.Options()
     _capi.lib().ba_default_options(ctypes.byref(o))
     assert o.max_iters == 50 and o.huber_delta == 1.0 and o.robust_mode == _capi.ROBUST["irls"]
-    assert o.precond == _capi.PRECOND["schur_jacobi"] and o.pcg_max_iters > 0
+    assert o.precond == _capi.PRECOND["auto"] and o.pcg_max_iters > 0
+    # the reference's own tolerances (src/bundle_adjuster.py:172)
+    assert o.ftol == 1e-5 and o.xtol == 1e-5 and o.gtol == 1e-8
 
 
 def test_struct_sizes_match_header():
@@ -65,7 +67,7 @@ def test_struct_layout_against_the_compiled_header(tmp_path):
             assert int(out[f"{st}.{n}"]) == getattr(cls, n).offset, (st, n)
     o = _capi.Options()
     _capi.lib().ba_default_options(ctypes.byref(o))
-    assert o.pcg_tail == 1 and o.device_loop == 1 and list(o.reserved) == [0, 0, 0, 0]
+    assert o.pcg_tail == 1 and o.device_loop == 1 and o.coarse_aggregate == 0 and o.coarse_after == 0 and list(o.reserved) == [0, 0]
 
 
 def test_run_host_path_with_a_stub_solver():
