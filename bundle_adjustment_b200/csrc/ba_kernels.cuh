@@ -74,7 +74,17 @@ struct LMState {
     int last_accepted;       // 1 if the last decide() accepted
     int pcg_done, pcg_iter, pcg_total;
     int bad;                 // non-finite seen
+    unsigned long long t0;   // %globaltimer (ns) when the solve started: origin of the trace's time stamps
 };
+// One record per LM iteration (entry 0 = the initial point), written by the 1-thread decision kernels: Huber cost and raw sum of
+// squares of the CURRENT point after the decision, device time since the start of the solve, PCG iterations so far.
+constexpr int TRACE_CAP = 1024;
+struct TraceRec { double cost, raw, ms; int pcg_total, accepted; };
+BA_D unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 // the last step was rejected: the camera-side linearisation of the current point is still valid
 BA_D bool lin_gated(const LMState* st) { return st->iter > 0 && st->last_accepted == 0; }
 // Device-side loop control (conditional WHILE nodes of the solve graph, see solve()): 0 = no graph, nothing to set.
@@ -162,6 +172,7 @@ struct Params {
     double* pm_partial;  // [n_partial_rows*NSCAL]
     double* cam_partial; // [n_cams*NSCAL]
     LMState* st;
+    TraceRec* trace;     // [TRACE_CAP]
 };
 
 // position of point p in parameter buffer b
@@ -1088,6 +1099,7 @@ __global__ void k_store_cost(Params P, int which) {
     st->cost[b] = st->scal[S_COST];
     st->raw[b] = st->scal[S_RAW];
     if (st->scal[S_BAD] > 0.0 || !isfinite(st->scal[S_COST])) st->bad = 1;
+    if (P.trace && st->iter == 0) P.trace[0] = TraceRec{st->cost[b], st->raw[b], 1e-6 * (double)(global_ns() - st->t0), 0, 0};
 }
 
 // Accept / reject the trial point, update the damping (Nielsen), test ftol / xtol.
@@ -1136,6 +1148,8 @@ __global__ void k_lm_decide(Params P, double ftol, double xtol, double lam_min, 
         if (st->status == 0 && st->lambda > lam_max) st->status = 5;
     }
     if (st->status == 0 && st->iter >= max_iters) st->status = 6;  // iteration limit (reported as 0)
+    if (P.trace && st->iter < TRACE_CAP)
+        P.trace[st->iter] = TraceRec{st->cost[st->cur], st->raw[st->cur], 1e-6 * (double)(global_ns() - st->t0), st->pcg_total, accept ? 1 : 0};
     set_loop(lm_loop, st->status == 0);
 }
 

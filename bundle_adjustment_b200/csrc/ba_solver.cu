@@ -367,6 +367,7 @@ __global__ void k_init_state(LMState* st, double lambda) {
     z.lambda = lambda;
     z.nu = 2.0;
     z.cur = st->cur;  // the parameter buffer selector survives across solves
+    z.t0 = global_ns();
     *st = z;
 }
 
@@ -433,6 +434,8 @@ struct ba_handle {
     DBuf<int4> cm_tile;
     DBuf<double> cm_partial, pm_partial, cam_partial;
     DBuf<LMState> st;
+    DBuf<TraceRec> trace;  // per-LM-iteration records of the last solve (ba_solve_trace)
+    int trace_n = 0;
     DBuf<double> io;  // staging for parameter upload / download
     LMState* h_state = nullptr;  // pinned
     int* h_flag = nullptr;       // pinned
@@ -563,6 +566,8 @@ static void create_common(ba_handle* h, int device) {
     CK(cudaEventCreate(&h->ev_solve1));
     h->st.alloc(1);
     h->st.zero(h->stream);
+    h->trace.alloc(TRACE_CAP);
+    h->trace.zero(h->stream);
     h->ticket.alloc(1);
     h->ticket.zero(h->stream);
     h->dot_partial.alloc(2 * MAX_VEC_CTAS);
@@ -1115,7 +1120,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     P.o_uv = h->o_uv.p; P.o_idx = h->o_idx.p; P.pm_uv = h->pm_uv.p; P.pm_idx = h->pm_idx.p; P.pt_off = h->pt_off.p;
     P.pm_tile_pt = h->pm_tile_pt.p; P.cm_uv = h->cm_uv.p; P.cm_pt = h->cm_pt.p; P.cm_tile = h->cm_tile.p;
     P.cam_tile_off = h->cam_tile_off.p; P.cm_partial = h->cm_partial.p; P.pm_partial = h->pm_partial.p;
-    P.cam_partial = h->cam_partial.p; P.st = h->st.p;
+    P.cam_partial = h->cam_partial.p; P.st = h->st.p; P.trace = h->trace.p;
     P.ft_tiles = h->ft_tiles; P.n_seg = h->n_seg; P.n_partial_rows = n_partial_rows;
     P.ft_pt = h->ft_pt.p; P.ft_obs = h->ft_obs.p; P.ft_seg = h->ft_seg.p; P.tc_uv = h->tc_uv.p;
     P.ft_hdr = h->ft_hdr.p; P.tc_meta = h->tc_meta.p; P.pm_tc = h->fused_ok ? h->pm_tc.p : nullptr;
@@ -1593,6 +1598,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     CK(cudaEventElapsedTime(&ms, h->ev_solve0, h->ev_solve1));
     if (h->time_kernels) resolve_stamps(h);
     h->time_kernels = false;
+    h->trace_n = std::min(h->h_state->iter + 1, TRACE_CAP);
     if (out) {
         const LMState& st = *h->h_state;
         memset(out, 0, sizeof *out);
@@ -2035,6 +2041,27 @@ int ba_triangulate(ba_handle* h, const double P1[12], const double P2[12], const
     if (xyz) CK(cudaMemcpyAsync(xyz, dx.p, (size_t)n * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
     if (valid) CK(cudaMemcpyAsync(valid, dv.p, (size_t)n, cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
+    API_END
+}
+
+int ba_solve_trace(ba_handle* h, int32_t cap, double* cost, double* raw_cost, double* ms, int32_t* pcg_total, int32_t* accepted,
+                   int32_t* n_out) {
+    API_BEGIN
+    ba::need_problem(h);
+    const int n = std::min<int>(h->trace_n, std::max(cap, 0));
+    std::vector<ba::TraceRec> rec((size_t)std::max(n, 1));
+    if (n > 0) {
+        CK(cudaMemcpyAsync(rec.data(), h->trace.p, (size_t)n * sizeof(ba::TraceRec), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    for (int i = 0; i < n; ++i) {
+        if (cost) cost[i] = rec[i].cost;
+        if (raw_cost) raw_cost[i] = rec[i].raw;
+        if (ms) ms[i] = rec[i].ms;
+        if (pcg_total) pcg_total[i] = rec[i].pcg_total;
+        if (accepted) accepted[i] = rec[i].accepted;
+    }
+    if (n_out) *n_out = h->trace_n;
     API_END
 }
 

@@ -192,6 +192,15 @@ int ba_schur_matvec(ba_handle* h, const ba_options* opt, double lambda, const do
  * replaced by the result.  Replaces the least_squares call at src/bundle_adjuster.py:170-174. */
 int ba_solve(ba_handle* h, const ba_options* opt, ba_stats* stats_out);
 
+/* Trajectory of the last ba_solve, recorded on the device by the 1-thread decision kernel (time stamps from %globaltimer, so
+ * they include everything the solve enqueued and no host time): entry 0 = the initial point, entry i = the state after LM
+ * iteration i.  cost = 0.5 * sum rho and raw_cost = sum r^2 of the CURRENT point (unchanged by a rejected step), ms = device time
+ * since the start of the solve, pcg_total = PCG iterations so far, accepted = 1 if iteration i was accepted.  Up to `cap` entries
+ * are written (any array may be NULL); *n_out = entries available (iterations + 1, at most 1024).  What the reference offers
+ * instead: verbose=2 prints of least_squares (src/bundle_adjuster.py:173 passes verbose=0). */
+int ba_solve_trace(ba_handle* h, int32_t cap, double* cost, double* raw_cost, double* ms, int32_t* pcg_total, int32_t* accepted,
+                   int32_t* n_out);
+
 /* Per-kernel accounting of the last ba_solve: for each of the `n` kernel kinds (ba_kernel_name(k)),
  * number of launches and summed CUDA-event milliseconds.  Times are filled when opt->verbose >= 2:
  * every launch is bracketed by a pair of pooled CUDA events on the solver stream (no synchronisation
