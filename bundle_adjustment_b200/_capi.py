@@ -34,7 +34,7 @@ class Options(C.Structure):
                 ("pcg_max_iters", C.c_int32), ("pcg_tol", C.c_double), ("pcg_check_every", C.c_int32),
                 ("verbose", C.c_int32), ("schur_path", C.c_int32), ("pcg_tail", C.c_int32),
                 ("device_loop", C.c_int32), ("coarse_aggregate", C.c_int32), ("coarse_after", C.c_int32),
-                ("reserved", C.c_int32 * 2)]
+                ("point_linesearch", C.c_int32), ("reserved", C.c_int32 * 1)]
 
 
 class Stats(C.Structure):

@@ -162,13 +162,13 @@ struct TBuf {
 enum Kind {
     KN_SETUP = 0, KN_CAM_PREP, KN_RESID, KN_JAC, KN_LIN_PTS, KN_PT_PREP, KN_PT_PASS, KN_BACKSUB, KN_LIN_CAM,
     KN_SCHUR_CAM, KN_MATVEC_CAM, KN_CAM_SUM, KN_CAM_FIN, KN_PCG_DOTS, KN_PCG_UPDATE, KN_CAM_UPDATE, KN_REDUCE,
-    KN_GRAD, KN_DECIDE, KN_TILE_MV, KN_TILE_BACKSUB, KN_ROWS_FIN, KN_ROWS_XCHG, KN_DOTS_PEER, KN_PCG_TAIL, KN_COUNT
+    KN_GRAD, KN_DECIDE, KN_TILE_MV, KN_TILE_BACKSUB, KN_ROWS_FIN, KN_ROWS_XCHG, KN_DOTS_PEER, KN_PCG_TAIL, KN_LINESEARCH, KN_COUNT
 };
 static const char* kKindNames[KN_COUNT] = {
     "setup", "cam_prepare", "residuals", "jacobian_blocks", "lin_points", "point_prepare", "schur_matvec_points",
     "backsub_points", "lin_cameras", "schur_rhs_cameras", "schur_matvec_cameras", "camera_sum", "camera_finish",
     "pcg_dots", "pcg_update", "camera_update", "reduce_scalars", "gradient_check", "lm_decide",
-    "schur_matvec_tiles", "backsub_tiles", "rows_finish", "rows_finish_xchg", "pcg_dots_peer", "pcg_tail"};
+    "schur_matvec_tiles", "backsub_tiles", "rows_finish", "rows_finish_xchg", "pcg_dots_peer", "pcg_tail", "point_linesearch"};
 
 // ---------------------------------------------------------------------------------------------
 // setup kernels (device-side construction of the two observation orders)
@@ -1458,6 +1458,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
         else
             launch(h, KN_BACKSUB, k_point_pass<1>, P.pm_tiles, PM_THREADS, h->smem_pass, P, (const double*)h->v_x.p);
         launch(h, KN_CAM_UPDATE, k_camera_update, cdiv(nc1, 128), 128, 0, P);
+        if (opt->point_linesearch && h->tile_lin) launch(h, KN_LINESEARCH, k_tile_linesearch, h->ft_grid, FT_THREADS, 0, P);
         lin_points_and_cost(h, 3);
         reduce_scalars(h, MASK_LIN | MASK_STEP_PM, MASK_STEP_CAM);
         launch(h, KN_DECIDE, k_lm_decide, 1, 1, 0, P, opt->ftol, opt->xtol, opt->lambda_min, opt->lambda_max, opt->max_iters, lm_loop);
@@ -1652,6 +1653,7 @@ void ba_default_options(ba_options* o) {
     o->schur_path = BA_PATH_TILES;
     o->pcg_tail = 1;
     o->device_loop = 1;
+    o->point_linesearch = 1;
 }
 
 int ba_create(int device, ba_handle** out) {

@@ -83,7 +83,10 @@ typedef struct ba_options {
     int32_t coarse_aggregate; /* cameras per aggregate of the two-level preconditioner; 0 (default) = max(32, n_cams / 64)  */
     int32_t coarse_after;     /* build the coarse matrix once an LM iteration's PCG needed more than this many iterations;
                                  0 (default) = 15, negative = from the first LM iteration on                              */
-    int32_t reserved[2];
+    int32_t point_linesearch; /* 1 (default): after every LM step each point scales its own update by the factor out of
+                                 {1, 1/2, 2, 4, 8, 16} with the smallest Huber cost over its observations (cameras at the trial
+                                 poses; the total cost can only go down against the plain step).  0: plain LM steps           */
+    int32_t reserved[1];
 } ba_options;
 
 typedef struct ba_stats {

@@ -187,9 +187,40 @@ def retract(rvec, tvec, pts, dc, dp):
     return rv, tv, pts + dp
 
 
+LS_ALPHAS = (0.5, 2.0, 4.0, 8.0, 16.0)   # tried after alpha = 1, in this order (k_tile_linesearch: kLsAlpha)
+
+
+def point_costs(prob: O.Problem, rvec, tvec, pts, huber=True) -> np.ndarray:
+    """0.5 * sum rho over the observations of each point (n_pts,); non-finite -> 1e300 per observation, as on the device."""
+    x = np.concatenate([np.asarray(rvec).ravel(), np.asarray(tvec).ravel(), np.asarray(pts).ravel()])
+    with np.errstate(all="ignore"):
+        r = prob.residuals(x).reshape(-1, 2)
+        c = 0.5 * (O.huber_rho(r * r)[0] if huber else r * r).sum(1)
+    c = np.where(np.isfinite(c), c, 1e300)
+    out = np.zeros(prob.n_pts)
+    np.add.at(out, prob.obs_pt, c)
+    return out
+
+
+def point_linesearch(prob: O.Problem, rvec_new, tvec_new, pts_cur, pts_new, huber=True):
+    """CPU statement of k_tile_linesearch (csrc/ba_tiles.cuh): with the cameras at their trial poses every point scales its
+    own step by the factor out of {1, 1/2, 2, 4, 8, 16} with the smallest cost over its observations; a factor other than 1
+    must win by more than 1e-9 relative.  -> (points, chosen factors)."""
+    dp = pts_new - pts_cur
+    c1 = point_costs(prob, rvec_new, tvec_new, pts_new, huber)
+    thr = c1 - 1e-9 * np.abs(c1)
+    best, alpha = c1.copy(), np.ones(prob.n_pts)
+    for a in LS_ALPHAS:
+        c = point_costs(prob, rvec_new, tvec_new, pts_cur + a * dp, huber)
+        m = (c < thr) & (c < best)
+        best[m] = c[m]
+        alpha[m] = a
+    return pts_cur + alpha[:, None] * dp, alpha
+
+
 def solve(prob: O.Problem, rvec, tvec, pts, *, mode="irls", huber=True, max_iters=100, lam0=1e-4, ftol=1e-12,
-          gtol=1e-10, lam_min=1e-12, lam_max=1e16, verbose=False) -> LMResult:
-    """Levenberg-Marquardt with Nielsen's damping update (the rule the device loop uses)."""
+          gtol=1e-10, lam_min=1e-12, lam_max=1e16, verbose=False, linesearch=True) -> LMResult:
+    """Levenberg-Marquardt with Nielsen's damping update and the per-point line search (the rules the device loop uses)."""
     rvec, tvec, pts = rvec.copy(), tvec.copy(), pts.copy()
     lam, nu = lam0, 2.0
     lin = linearize(prob, rvec, tvec, pts, mode, huber)
@@ -201,6 +232,8 @@ def solve(prob: O.Problem, rvec, tvec, pts, *, mode="irls", huber=True, max_iter
             break
         dc, dp, model, _ = schur_step(prob, lin, lam)
         rv, tv, pn = retract(rvec, tvec, pts, dc, dp)
+        if linesearch:
+            pn, _ = point_linesearch(prob, rv, tv, pts, pn, huber)
         lin_new = linearize(prob, rv, tv, pn, mode, huber)
         rho = (lin.cost - lin_new.cost) / model if model > 0 else -1.0
         accepted = bool(np.isfinite(lin_new.cost) and rho > 0)

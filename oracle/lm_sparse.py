@@ -81,8 +81,9 @@ def gradient_max(lin: L.Linearization) -> float:
 
 
 def solve(prob: O.Problem, rvec, tvec, pts, *, mode="irls", max_iters=200, lam0=1e-4, lam_min=1e-14, lam_max=1e16,
-          gtol=1e-8, ftol=0.0, verbose=False, callback: Optional[Callable] = None) -> L.LMResult:
-    """Exact-step LM (Nielsen damping) until max|g| < gtol (or a relative cost decrease below ftol)."""
+          gtol=1e-8, ftol=0.0, verbose=False, callback: Optional[Callable] = None, linesearch=True) -> L.LMResult:
+    """Exact-step LM (Nielsen damping, per-point line search as on the device) until max|g| < gtol (or a relative cost
+    decrease below ftol)."""
     rvec, tvec, pts = rvec.copy(), tvec.copy(), pts.copy()
     lam, nu = lam0, 2.0
     lin = L.linearize(prob, rvec, tvec, pts, mode, True)
@@ -97,6 +98,8 @@ def solve(prob: O.Problem, rvec, tvec, pts, *, mode="irls", max_iters=200, lam0=
         dc = spl.splu(S).solve(rhs).reshape(prob.n_cams, 6) if prob.n_cams else np.zeros((0, 6))
         dp, model = backsub(dc)
         rv, tv, pn = L.retract(rvec, tvec, pts, dc, dp)
+        if linesearch:
+            pn, _ = L.point_linesearch(prob, rv, tv, pts, pn, True)
         lin_new = L.linearize(prob, rv, tv, pn, mode, True)
         rho = (lin.cost - lin_new.cost) / model if model > 0 else -1.0
         accepted = bool(np.isfinite(lin_new.cost) and rho > 0)

@@ -487,6 +487,7 @@ def test_two_level_preconditioner_against_the_cpu_statement(gpu_solver):
     np.add.at(w, prob.obs_pt[adj], np.einsum("nij,ni->nj", op.E, dc[prob.obs_cam[adj]]))
     dp = -np.einsum("nij,nj->ni", op.Vinv, w)
     rv, tv, pn = L.retract(fp.rvec, fp.tvec, fp.pts, dc, dp)
+    pn, alpha = L.point_linesearch(prob, rv, tv, fp.pts, pn)
 
     gpu_solver.set_flat(fp)
     kw = dict(max_iters=1, initial_lambda=lam0, pcg_tol=tol, pcg_max_iters=400, ftol=0.0, xtol=0.0, gtol=0.0, device_loop=0)
