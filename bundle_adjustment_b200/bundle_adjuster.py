@@ -8,8 +8,9 @@ itself - the reference's ``scipy.optimize.least_squares`` call at ``:170-174`` -
 helpers keep the reference's names and argument lists so they can be called side by side with the
 reference's in tests.
 
-Flat import, like the reference (``from bundle_adjuster import BundleAdjuster`` with
-``bundle_adjustment_b200`` on ``sys.path``) or ``from bundle_adjustment_b200 import BundleAdjuster``.
+Import as ``from bundle_adjustment_b200 import BundleAdjuster``; for the reference's flat
+``from bundle_adjuster import BundleAdjuster`` (``src/pipeline.py:12``) put ``bundle_adjustment_b200/shim`` ahead of the
+reference's ``src/`` on ``sys.path`` (``shim/bundle_adjuster.py`` re-exports this class).
 """
 from __future__ import annotations
 
@@ -25,10 +26,11 @@ from .solver import FlatSolver
 class BundleAdjuster:
     """Local bundle adjustment over the most recent window of keyframes, on a B200."""
 
-    def __init__(self, camera_matrix, window_size=5, *, device: int = 0, max_iters: int = 50, ftol: float = 1e-6,
-                 xtol: float = 1e-8, gtol: float = 1e-8, huber_delta: float = 1.0, robust_mode: str = "irls",
+    def __init__(self, camera_matrix, window_size=5, *, device: int = 0, max_iters: int = 50, ftol: float = 1e-5,
+                 xtol: float = 1e-5, gtol: float = 1e-8, huber_delta: float = 1.0, robust_mode: str = "irls",
                  verbose: int = 0, lba_steps_dir: Optional[str] = None, solver_options: Optional[dict] = None):
-        # public, mutable attributes exactly as in the reference (src/main.py:83-86 mutates window_size)
+        # public, mutable attributes exactly as in the reference (src/main.py:83-86 mutates window_size); the tolerances default
+        # to the reference's call (xtol = ftol = 1e-5, max_nfev = 50: src/bundle_adjuster.py:172), gtol to SciPy's default
         self.camera_matrix = camera_matrix
         self.window_size = window_size
         self.device = device

@@ -162,13 +162,13 @@ struct TBuf {
 enum Kind {
     KN_SETUP = 0, KN_CAM_PREP, KN_RESID, KN_JAC, KN_LIN_PTS, KN_PT_PREP, KN_PT_PASS, KN_BACKSUB, KN_LIN_CAM,
     KN_SCHUR_CAM, KN_MATVEC_CAM, KN_CAM_SUM, KN_CAM_FIN, KN_PCG_DOTS, KN_PCG_UPDATE, KN_CAM_UPDATE, KN_REDUCE,
-    KN_GRAD, KN_DECIDE, KN_TILE_MV, KN_TILE_BACKSUB, KN_ROWS_FIN, KN_ROWS_XCHG, KN_DOTS_PEER, KN_PCG_TAIL, KN_LINESEARCH, KN_COUNT
+    KN_GRAD, KN_DECIDE, KN_TILE_MV, KN_TILE_BACKSUB, KN_ROWS_FIN, KN_ROWS_XCHG, KN_DOTS_PEER, KN_PCG_TAIL, KN_ALLREDUCE, KN_COUNT
 };
 static const char* kKindNames[KN_COUNT] = {
     "setup", "cam_prepare", "residuals", "jacobian_blocks", "lin_points", "point_prepare", "schur_matvec_points",
     "backsub_points", "lin_cameras", "schur_rhs_cameras", "schur_matvec_cameras", "camera_sum", "camera_finish",
     "pcg_dots", "pcg_update", "camera_update", "reduce_scalars", "gradient_check", "lm_decide",
-    "schur_matvec_tiles", "backsub_tiles", "rows_finish", "rows_finish_xchg", "pcg_dots_peer", "pcg_tail", "point_linesearch"};
+    "schur_matvec_tiles", "backsub_tiles", "rows_finish", "rows_finish_xchg", "pcg_dots_peer", "pcg_tail", "peer_allreduce"};
 
 // ---------------------------------------------------------------------------------------------
 // setup kernels (device-side construction of the two observation orders)
@@ -426,6 +426,8 @@ struct ba_handle {
     int coarse_colours = 0, coarse_graph_agg = 0;  // colouring of the aggregate graph of the uploaded problem (0: not built)
     bool coarse_ready = false;
     int xcap = 0;
+    int ar_cap = 0;        // capacity (doubles) of the LL all-reduce region behind the tail's slots; 0 = NCCL only
+    size_t ar_base = 0;    // its offset in xbuf (doubles)
     int xpush = 2;  // exchange by remote loads (0, pull), remote stores + flags (1, push), remote stores of LL words (2)
     DBuf<double> xbuf;
     DBuf<int> xstate;
@@ -528,14 +530,20 @@ static void resolve_stamps(ba_handle* h) {
 
 static inline int cdiv(long long a, int b) { return (int)((a + b - 1) / b); }
 
-static void allreduce_sum(ba_handle* h, double* buf, size_t count) {
+// In place, on the solver stream.  Camera-sized vectors travel through the LL words of the peer-mapped exchange buffer
+// (k_peer_allreduce: rank-order sums, identical bits on every rank); larger ones, and handles without peer access, use NCCL.
+static void allreduce(ba_handle* h, double* buf, size_t count, bool is_max) {
     if (h->nranks <= 1 || count == 0) return;
-    NK(nccl_api().AllReduce(buf, buf, count, ncclDouble, ncclSum, h->comm, h->stream));
+    if (h->peer_ok && h->ar_cap > 0 && count <= (size_t)h->ar_cap) {
+        const int grid = (int)std::min<size_t>((count + AR_THREADS - 1) / AR_THREADS, (size_t)4 * h->sm_count);
+        launch(h, KN_ALLREDUCE, k_peer_allreduce, grid, AR_THREADS, 0, buf, (int)count, is_max ? 1 : 0, h->xbuf.p,
+               (double* const*)h->d_peers.p, h->nranks, h->rank, h->ar_base, h->ar_cap, h->xstate.p);
+        return;
+    }
+    NK(nccl_api().AllReduce(buf, buf, count, ncclDouble, is_max ? ncclMax : ncclSum, h->comm, h->stream));
 }
-static void allreduce_max(ba_handle* h, double* buf, size_t count) {
-    if (h->nranks <= 1 || count == 0) return;
-    NK(nccl_api().AllReduce(buf, buf, count, ncclDouble, ncclMax, h->comm, h->stream));
-}
+static void allreduce_sum(ba_handle* h, double* buf, size_t count) { allreduce(h, buf, count, false); }
+static void allreduce_max(ba_handle* h, double* buf, size_t count) { allreduce(h, buf, count, true); }
 
 static void create_common(ba_handle* h, int device) {
     int ndev = 0;
@@ -832,9 +840,13 @@ static void setup_peer_exchange(ba_handle* h, int n_cams) {
     close_peer_maps(h);
     h->peer_ok = false;
     h->xbuf.release();
-    h->xbuf.alloc(xb_doubles(h->nranks, need));
+    // behind the tail's slots: the LL all-reduce region, [2][nranks][ar_cap] pairs of words
+    const int ar_need = ((std::max(n_cams, 1) * 27 + 15) / 16) * 16;
+    h->ar_cap = (getenv("BA_B200_NCCL_ALLREDUCE") || ar_need > AR_MAX_DOUBLES) ? 16 : ar_need;
+    h->ar_base = (xb_doubles(h->nranks, need) + 1) & ~(size_t)1;
+    h->xbuf.alloc(h->ar_base + 4 * (size_t)h->nranks * h->ar_cap);
     h->xbuf.zero(s);
-    h->xstate.alloc(4);
+    h->xstate.alloc(8);
     h->xstate.zero(s);
     h->xcap = need;
     h->d_peers.alloc(h->nranks);
@@ -1187,9 +1199,11 @@ static void apply_robust(ba_handle* h, const ba_options* opt) {
 }
 
 // linearise the point side at buffer `which` and reduce the cost scalars
-static void lin_points_and_cost(ba_handle* h, int which) {
+// `linesearch`: the trial point (which = 3) with the per-point line search fused into the tile kernel
+static void lin_points_and_cost(ba_handle* h, int which, bool linesearch = false) {
     const Params& P = h->P;
-    if (h->tile_lin) launch(h, KN_LIN_PTS, k_tile_lin, h->ft_grid, FT_THREADS, 0, P, which);
+    if (h->tile_lin && linesearch && which == 3) launch(h, KN_LIN_PTS, k_tile_lin<true>, h->ft_grid, FT_THREADS, 0, P, which);
+    else if (h->tile_lin) launch(h, KN_LIN_PTS, k_tile_lin<false>, h->ft_grid, FT_THREADS, 0, P, which);
     else launch(h, KN_LIN_PTS, k_lin_points, P.pm_tiles, PM_THREADS, h->smem_lin, P, which);
 }
 
@@ -1458,8 +1472,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
         else
             launch(h, KN_BACKSUB, k_point_pass<1>, P.pm_tiles, PM_THREADS, h->smem_pass, P, (const double*)h->v_x.p);
         launch(h, KN_CAM_UPDATE, k_camera_update, cdiv(nc1, 128), 128, 0, P);
-        if (opt->point_linesearch && h->tile_lin) launch(h, KN_LINESEARCH, k_tile_linesearch, h->ft_grid, FT_THREADS, 0, P);
-        lin_points_and_cost(h, 3);
+        lin_points_and_cost(h, 3, opt->point_linesearch != 0);
         reduce_scalars(h, MASK_LIN | MASK_STEP_PM, MASK_STEP_CAM);
         launch(h, KN_DECIDE, k_lm_decide, 1, 1, 0, P, opt->ftol, opt->xtol, opt->lambda_min, opt->lambda_max, opt->max_iters, lm_loop);
     };

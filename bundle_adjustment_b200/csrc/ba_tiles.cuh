@@ -426,12 +426,28 @@ BA_D void cp_async16(void* smem, const void* gmem) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(smem_u32(smem)), "l"(gmem) : "memory");
 }
 
+// Per-point line search on the trial step (LS = true: the linearisation of the TRIAL point, after back-substitution and
+// camera update).  With the trial cameras held fixed the cost is a sum over the points, so every point may scale ITS step
+// dp by its own factor: X = X_cur + alpha dp, alpha in {1, 1/2, 2, 4, 8, 16}, whichever has the smallest Huber cost over the
+// point's observations (alpha = 1 unless another is better by more than 1e-9 relative).  The total cost can only go down
+// against the plain trial point, so the accept / reject logic is unchanged.  Why: under IRLS a point whose observations sit
+// in the linear regime of the Huber loss (an outlier pulling along a poorly constrained depth, a point running to infinity)
+// moves by a small fraction of the distance to its piecewise-linear optimum per LM iteration - gain ratios of 2 for dozens
+// of iterations; the search lets those few points jump (CPU statement: oracle/lm_schur.py::point_linesearch).  The six
+// candidate costs of an observation go through the same transposed track layout as the nine sums of the linearisation
+// (before them, in the same scratch), the chosen position replaces the trial point in HBM and is linearised right away.
+constexpr int LS_K = 6;
+__device__ __constant__ double kLsAlpha[LS_K] = {1.0, 0.5, 2.0, 4.0, 8.0, 16.0};
+
 // Persistent CTAs over contiguous runs of tiles.  Every thread stages the record and the measurement of ITS
 // observation of the next tile with cp.async while the current tile is computed (a thread only reads what it
 // copied itself: cp.async.wait_group, no barrier), and the tile headers are fetched two tiles ahead - the chain
 // header -> record -> pose/point of a tile no longer sits in front of its arithmetic.
+template <bool LS>
 __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_lin(Params P, int which) {
     __shared__ double sA[9 * FT_LDL];
+    __shared__ double sC[LS ? LS_K * FT_PTS : 1];
+    __shared__ double sX[LS ? 3 * FT_PTS : 1];
     __shared__ __align__(16) double2 sUv[2][FT_THREADS];
     __shared__ __align__(16) int2 sMeta[2][FT_THREADS];
     __shared__ int sRs[FT_THREADS];
@@ -471,13 +487,84 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_lin(Params 
         if (t + 1 < t_end) stage(buf ^ 1, han);
         else asm volatile("cp.async.commit_group;\n" ::: "memory");
         asm volatile("cp.async.wait_group 1;\n" ::: "memory");  // this tile's copies (of this thread) have landed
+        if (tid < hb.w) sRs[tid] = rsv;
+        if (tid <= m) sOff[tid] = offv;
+        if constexpr (LS) {
+            const int cur = b ^ 1;
+            if (tid < n) {
+                const int2 meta = sMeta[buf][tid];
+                const double2 uv = sUv[buf][tid];
+                const int pos = (meta.y >> 10) & 1023;
+                double X0[3], X[3], Rt[12];
+                load_cam(camR, meta.x, Rt);
+                load_pt(P, b, p0 + (meta.y & 1023), X);
+                load_pt(P, cur, p0 + (meta.y & 1023), X0);
+                const double d[3] = {X[0] - X0[0], X[1] - X0[1], X[2] - X0[2]};
+                // x_cam(alpha) = (R X0 + t) + alpha R d
+                const double ax = fma(Rt[0], X0[0], fma(Rt[1], X0[1], fma(Rt[2], X0[2], Rt[9])));
+                const double ay = fma(Rt[3], X0[0], fma(Rt[4], X0[1], fma(Rt[5], X0[2], Rt[10])));
+                const double az = fma(Rt[6], X0[0], fma(Rt[7], X0[1], fma(Rt[8], X0[2], Rt[11])));
+                const double dx = fma(Rt[0], d[0], fma(Rt[1], d[1], Rt[2] * d[2]));
+                const double dy = fma(Rt[3], d[0], fma(Rt[4], d[1], Rt[5] * d[2]));
+                const double dz = fma(Rt[6], d[0], fma(Rt[7], d[1], Rt[8] * d[2]));
+#pragma unroll
+                for (int k = 0; k < LS_K; ++k) {
+                    const double al = kLsAlpha[k];
+                    const double iz = 1.0 / fma(al, dz, az);
+                    const double rx = uv.x - fma(P.K.fx, fma(al, dx, ax) * iz, P.K.cx);
+                    const double ry = uv.y - fma(P.K.fy, fma(al, dy, ay) * iz, P.K.cy);
+                    double wH, wg, r0x, r0y;
+                    robust_weights(rx, P.delta, P.mode, wH, wg, r0x);
+                    robust_weights(ry, P.delta, P.mode, wH, wg, r0y);
+                    const double c = 0.5 * (r0x + r0y);
+                    sA[k * FT_LDL + pos] = isfinite(c) ? c : 1e300;
+                }
+            }
+            __syncthreads();
+            for (int w = tid; w < m * LS_K; w += FT_THREADS) {
+                const int q = w / LS_K, k = w - LS_K * q;
+                const int len = sOff[q + 1] - sOff[q];
+                const double* src = sA + k * FT_LDL + q;
+                double sk = 0.0;
+                for (int i = 0; i < len; ++i) sk += src[sRs[i]];
+                sC[k * FT_PTS + q] = sk;
+            }
+            __syncthreads();
+            if (tid < m) {
+                const double c1 = sC[tid];
+                const double thr = c1 - 1e-9 * fabs(c1);
+                double best = c1;
+                int kb = 0;
+#pragma unroll
+                for (int k = 1; k < LS_K; ++k) {
+                    const double c = sC[k * FT_PTS + tid];
+                    if (c < thr && c < best) { best = c; kb = k; }
+                }
+                double X0[3], X1[3];
+                load_pt(P, cur, p0 + tid, X0);
+                load_pt(P, b, p0 + tid, X1);
+                if (kb != 0) {
+                    const double al = kLsAlpha[kb];
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) X1[k] = fma(al, X1[k] - X0[k], X0[k]);
+                    store_pt(P, b, p0 + tid, X1[0], X1[1], X1[2]);
+                }
+                sX[3 * tid] = X1[0]; sX[3 * tid + 1] = X1[1]; sX[3 * tid + 2] = X1[2];
+            }
+            __syncthreads();  // the chosen positions; and the candidate costs in sA have all been read
+        }
         if (tid < n) {
             const int2 meta = sMeta[buf][tid];
             const double2 uv = sUv[buf][tid];
             const int pos = (meta.y >> 10) & 1023;
             double X[3], Rt[12];
-            load_cam(camR, meta.x, Rt);
-            load_pt(P, b, p0 + (meta.y & 1023), X);
+            load_cam(camR, meta.x, Rt);  // (LS: again - from L1 - rather than twelve registers held across three barriers)
+            if constexpr (LS) {
+                const int q = meta.y & 1023;
+                X[0] = sX[3 * q]; X[1] = sX[3 * q + 1]; X[2] = sX[3 * q + 2];
+            } else {
+                load_pt(P, b, p0 + (meta.y & 1023), X);
+            }
             ObsLin o;
             linearize_obs(Rt, X, uv.x, uv.y, P.K, o);
             double wHx, wgx, r0x, wHy, wgy, r0y;
@@ -505,8 +592,6 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_lin(Params 
             dst[7 * FT_LDL] = o.jx[1] * gx + o.jy[1] * gy;
             dst[8 * FT_LDL] = o.jx[2] * gx + o.jy[2] * gy;
         }
-        if (tid < hb.w) sRs[tid] = rsv;
-        if (tid <= m) sOff[tid] = offv;
         __syncthreads();
         double* V = Vb + (size_t)p0 * 6;
         double* G = Gb + (size_t)p0 * 4;
@@ -536,120 +621,6 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_lin(Params 
         for (int i = 0; i < FT_THREADS / 32; ++i) mx = fmax(mx, red[i]);
         double* out = P.pm_partial + (size_t)blockIdx.x * NSCAL;
         out[S_COST] = tot[0]; out[S_RAW] = tot[1]; out[S_BAD] = tot[2]; out[S_GPMAX] = mx;
-    }
-}
-
-// ---------------------------------------------------------------------------------------------
-// Per-point line search on the trial step (between back-substitution / camera update and the linearisation of the trial
-// point).  With the trial cameras held fixed the cost is a sum over the points, so every point may scale ITS step dp by its
-// own factor: X = X_cur + alpha dp, alpha in {1, 1/2, 2, 4, 8, 16}, whichever has the smallest Huber cost over the point's
-// observations (alpha = 1 unless another is better by more than 1e-9 relative).  The total cost can only go down against
-// the plain trial point, so the accept / reject logic is unchanged.  Why: under IRLS a point whose observations sit in the
-// linear regime of the Huber loss (an outlier pulling along a poorly constrained depth, a point running to infinity)
-// moves by a small fraction of the distance to its piecewise-linear optimum per LM iteration - gain ratios of 2 for dozens
-// of iterations; the search lets those few points jump (CPU statement: oracle/lm_schur.py::point_linesearch).
-// Same tile walk and transposed track layout as k_tile_lin; six per-point sums instead of nine, no Jacobian cache.
-// ---------------------------------------------------------------------------------------------
-constexpr int LS_K = 6;
-__device__ __constant__ double kLsAlpha[LS_K] = {1.0, 0.5, 2.0, 4.0, 8.0, 16.0};
-
-__global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_linesearch(Params P) {
-    __shared__ double sA[LS_K * FT_LDL];
-    __shared__ double sC[LS_K * FT_PTS];
-    __shared__ __align__(16) double2 sUv[2][FT_THREADS];
-    __shared__ __align__(16) int2 sMeta[2][FT_THREADS];
-    __shared__ int sRs[FT_THREADS];
-    __shared__ int sOff[FT_PTS + 1];
-    const int cur = P.st->cur, b = cur ^ 1;  // trial buffer
-    const int tid = threadIdx.x;
-    int t = ft_cta_begin(blockIdx.x, P.ft_tiles, gridDim.x);
-    const int t_end = ft_cta_begin(blockIdx.x + 1, P.ft_tiles, gridDim.x);
-    const double* camR = P.cam_R + (size_t)b * (P.n_cams + 1) * 12;
-    auto stage = [&](int buf, const int4& h) {  // h = (p0, m, o0, n)
-        if (tid < h.w) {
-            cp_async16(&sUv[buf][tid], P.tc_uv + h.z + tid);
-            cp_async8(&sMeta[buf][tid], P.tc_meta + h.z + tid);
-        }
-        asm volatile("cp.async.commit_group;\n" ::: "memory");
-    };
-    int4 ha = make_int4(0, 0, 0, 0), han = ha;
-    if (t < t_end) {
-        ha = __ldg(P.ft_hdr + 2 * t);
-        han = t + 1 < t_end ? __ldg(P.ft_hdr + 2 * (t + 1)) : ha;
-        stage(0, ha);
-    }
-    for (int it = 0; t < t_end; ++t, ++it) {
-        const int buf = it & 1;
-        const int4 hann = t + 2 < t_end ? __ldg(P.ft_hdr + 2 * (t + 2)) : han;
-        const int4 hb = __ldg(P.ft_hdr + 2 * t + 1);  // (s0, ns, r0, maxlen)
-        const int p0 = ha.x, m = ha.y, n = ha.w;
-        const int rsv = tid < hb.w ? __ldg(P.ft_rs + hb.z + tid) : 0;
-        const int offv = tid <= m ? __ldg(P.pt_off + p0 + tid) : 0;
-        if (t + 1 < t_end) stage(buf ^ 1, han);
-        else asm volatile("cp.async.commit_group;\n" ::: "memory");
-        asm volatile("cp.async.wait_group 1;\n" ::: "memory");
-        if (tid < n) {
-            const int2 meta = sMeta[buf][tid];
-            const double2 uv = sUv[buf][tid];
-            const int pos = (meta.y >> 10) & 1023;
-            double X0[3], X1[3], Rt[12];
-            load_cam(camR, meta.x, Rt);
-            load_pt(P, cur, p0 + (meta.y & 1023), X0);
-            load_pt(P, b, p0 + (meta.y & 1023), X1);
-            const double d[3] = {X1[0] - X0[0], X1[1] - X0[1], X1[2] - X0[2]};
-            // x_cam(alpha) = (R X0 + t) + alpha R d
-            const double ax = fma(Rt[0], X0[0], fma(Rt[1], X0[1], fma(Rt[2], X0[2], Rt[9])));
-            const double ay = fma(Rt[3], X0[0], fma(Rt[4], X0[1], fma(Rt[5], X0[2], Rt[10])));
-            const double az = fma(Rt[6], X0[0], fma(Rt[7], X0[1], fma(Rt[8], X0[2], Rt[11])));
-            const double dx = fma(Rt[0], d[0], fma(Rt[1], d[1], Rt[2] * d[2]));
-            const double dy = fma(Rt[3], d[0], fma(Rt[4], d[1], Rt[5] * d[2]));
-            const double dz = fma(Rt[6], d[0], fma(Rt[7], d[1], Rt[8] * d[2]));
-#pragma unroll
-            for (int k = 0; k < LS_K; ++k) {
-                const double al = kLsAlpha[k];
-                const double iz = 1.0 / fma(al, dz, az);
-                const double rx = uv.x - fma(P.K.fx, fma(al, dx, ax) * iz, P.K.cx);
-                const double ry = uv.y - fma(P.K.fy, fma(al, dy, ay) * iz, P.K.cy);
-                double wH, wg, r0x, r0y;
-                robust_weights(rx, P.delta, P.mode, wH, wg, r0x);
-                robust_weights(ry, P.delta, P.mode, wH, wg, r0y);
-                const double c = 0.5 * (r0x + r0y);
-                sA[k * FT_LDL + pos] = isfinite(c) ? c : 1e300;
-            }
-        }
-        if (tid < hb.w) sRs[tid] = rsv;
-        if (tid <= m) sOff[tid] = offv;
-        __syncthreads();
-        for (int w = tid; w < m * LS_K; w += FT_THREADS) {
-            const int q = w / LS_K, k = w - LS_K * q;
-            const int len = sOff[q + 1] - sOff[q];
-            const double* src = sA + k * FT_LDL + q;
-            double sk = 0.0;
-            for (int i = 0; i < len; ++i) sk += src[sRs[i]];
-            sC[k * FT_PTS + q] = sk;
-        }
-        __syncthreads();
-        if (tid < m) {
-            const double c1 = sC[tid];
-            double best = c1, thr = c1 - 1e-9 * fabs(c1);
-            int kb = 0;
-#pragma unroll
-            for (int k = 1; k < LS_K; ++k) {
-                const double c = sC[k * FT_PTS + tid];
-                if (c < thr && c < best) { best = c; kb = k; }
-            }
-            if (kb != 0) {
-                double X0[3], X1[3];
-                load_pt(P, cur, p0 + tid, X0);
-                load_pt(P, b, p0 + tid, X1);
-                const double al = kLsAlpha[kb];
-                store_pt(P, b, p0 + tid, fma(al, X1[0] - X0[0], X0[0]), fma(al, X1[1] - X0[1], X0[1]), fma(al, X1[2] - X0[2], X0[2]));
-            }
-        }
-        // sA / sC / the track tables are rewritten by the next tile only after its own barriers: sA by threads that passed
-        // the second barrier above (every reader of sA is past it), sC after the next tile's first barrier
-        __syncthreads();
-        ha = han; han = hann;
     }
 }
 

@@ -23,6 +23,9 @@ for name, kw in (("schur_jacobi ftol=0", {"precond": "schur_jacobi", "ftol": 0.0
         s.restore_initial()
         st = s.solve(max_iters=max_iters, verbose=1 if rep == 2 and name == "default" else 0, **kw)
     out[name] = st
+    tr = s.solve_trace()
+    print("   ms per LM iteration:", " ".join(f"{b - a:.2f}" for a, b in zip(tr["ms"][:-1], tr["ms"][1:])), flush=True)
+    print("   pcg per LM iteration:", " ".join(str(b - a) for a, b in zip(tr["pcg_total"][:-1], tr["pcg_total"][1:])), flush=True)
     print(name, json.dumps({k: st[k] for k in keys}), flush=True)
 s.restore_initial()
 st = s.solve(max_iters=max_iters, verbose=2, pcg_check_every=1)

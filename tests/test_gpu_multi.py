@@ -25,11 +25,11 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _run_two_ranks(tmp_path, tag, env_extra, pcg_tail=1):
+def _run_two_ranks(tmp_path, tag, env_extra, pcg_tail=1, which="chain60"):
     out = str(tmp_path / tag)
     env = dict(os.environ, **env_extra)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
-           "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "_multi_gpu_worker.py"), out, str(pcg_tail)]
+           "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "_multi_gpu_worker.py"), out, str(pcg_tail), which]
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=int(os.environ.get("BA_TEST_RANK_TIMEOUT", "120")))
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
     return [np.load(f"{out}.rank{r}.npz") for r in range(2)]
@@ -79,3 +79,24 @@ def test_two_ranks_match_one_gpu_and_the_protocols_agree_bitwise(tmp_path):
     # NCCL all-reduce per iteration (ring / tree order): same solution up to summation order
     if "nccl" in runs:
         assert abs(float(runs["nccl"][0]["cost"]) - st1["final_cost"]) <= 1e-8 * st1["final_cost"]
+
+
+def test_two_level_preconditioner_on_two_ranks(tmp_path):
+    """The coarse matrix is the sum of the ranks' probed parts (one all-reduce per build); the sharded solve must follow the
+    single-GPU solve: same iteration counts, same cost up to summation order, ranks bit-identical."""
+    if _gpus() < 2:
+        pytest.skip("needs two GPUs")
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from _multi_gpu_worker import PROBLEMS
+    (nc, npt, nobs, seed), kw = PROBLEMS["two_level"]
+    fp = S.make_flat_problem(nc, npt, nobs, seed=seed)
+    with FlatSolver(0) as s:
+        s.set_flat(fp)
+        st1 = s.solve(**kw)
+    assert st1["precond_text"] == "two_level" and st1["coarse_builds"] >= 1
+    r0, r1 = _run_two_ranks(tmp_path, "two_level", {}, 1, "two_level")
+    assert int(r0["precond"]) == 2 and int(r0["coarse_builds"]) == st1["coarse_builds"]
+    assert np.array_equal(r0["rvec"], r1["rvec"]) and float(r0["cost"]) == float(r1["cost"])
+    assert int(r0["iters"]) == st1["iterations"]
+    assert abs(int(r0["pcg"]) - st1["pcg_iterations"]) <= 2
+    assert abs(float(r0["cost"]) - st1["final_cost"]) <= 1e-7 * st1["final_cost"]

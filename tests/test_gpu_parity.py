@@ -516,7 +516,8 @@ def test_two_level_preconditioner_whole_solve(gpu_solver):
     gpu_solver.restore_initial()
     st2 = gpu_solver.solve(max_iters=30, ftol=0.0, xtol=0.0)
     assert st1["precond_text"] == "schur_jacobi" and st2["precond_text"] == "two_level"
-    assert abs(st2["final_cost"] - st1["final_cost"]) <= 1e-4 * st1["final_cost"]
+    # inexact steps + per-point line search: the two trajectories differ in which points jumped when, not in where they go
+    assert abs(st2["final_cost"] - st1["final_cost"]) <= 1e-3 * st1["final_cost"]
     assert st2["pcg_iterations"] * 2 < st1["pcg_iterations"]
     os.environ["BA_B200_HOST_INVERSE"] = "1"
     try:
@@ -556,3 +557,47 @@ def test_default_solve_stops_on_the_reference_tolerances(gpu_solver):
     assert st["iterations"] < 50
     assert st["final_cost"] <= float(g["res_cost"])
 
+
+
+# ------------------------------------------------------------------------------------------------
+# converged cost on BASELINE shapes (north_star: 1e-6 relative)
+# ------------------------------------------------------------------------------------------------
+def _converged_golden(shape):
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", f"converged_{shape}.npz")
+    if not os.path.isfile(path):
+        pytest.skip(f"{path} not generated (oracle/gen_converged_golden.py)")
+    return np.load(path)
+
+
+@pytest.mark.parametrize("shape", ["bal50", "ladybug"])
+def test_converged_cost_on_baseline_shapes(gpu_solver, shape):
+    """Configs 2 and 3 (well-posed variant of the generator: every point keeps two inlier observations, so a minimiser exists):
+    the device solve, run as deep as the exact-step CPU restatement was (oracle/lm_sparse.py: sparse Schur complement +
+    SuperLU, same LM rules), reaches the same converged cost to 1e-6 relative, and the same cameras after the one free gauge
+    (global scale about the fixed camera) is aligned.  On bal50 the golden also carries SciPy's verdict on that point: the
+    reference's own solver, given the analytic Jacobian and tolerances of 1e-12 and started there, finds nothing lower."""
+    g = _converged_golden(shape)
+    fp = S.make_named_problem(shape, keep_truth=False, well_posed=True)
+    assert fp.n_obs == int(g["n_obs"]) and fp.n_pts == int(g["n_pts"])
+    gpu_solver.set_flat(fp)
+    st = gpu_solver.solve(max_iters=int(g["iterations"]) + 40, ftol=0.0, xtol=0.0, gtol=1e-9, lambda_min=1e-10, pcg_tol=1e-4,
+                          pcg_max_iters=3000)
+    cost_ref = float(g["cost"])
+    assert abs(float(g["x0_cost"]) - st["initial_cost"]) <= 1e-9 * st["initial_cost"]
+    assert abs(st["final_cost"] - cost_ref) <= 1e-6 * cost_ref, (st["final_cost"], cost_ref)
+    if float(g["scipy_cost"]) > 0:   # SciPy started at the oracle's point did not get lower than the device did, to 1e-6
+        assert st["final_cost"] <= float(g["scipy_cost"]) * (1 + 1e-6)
+    # cameras: align the scale about the fixed camera's centre (cost-invariant), then compare
+    rvec, tvec, pts = gpu_solver.get_params()
+    Rf = O.rodrigues(fp.fixed_rvec)
+    c_fix = -Rf.T @ fp.fixed_tvec
+
+    def centres(rv, tv):
+        R = O.rodrigues(rv)
+        return -np.einsum("nji,nj->ni", R, tv) - c_fix
+    ca, cb = centres(rvec, tvec), centres(g["rvec"], g["tvec"])
+    s = float((ca * cb).sum() / (ca * ca).sum())
+    assert abs(s - 1.0) < 0.05
+    span = np.linalg.norm(cb, axis=1).max()
+    assert np.abs(s * ca - cb).max() <= 2e-3 * span
+    assert np.abs(rvec - g["rvec"]).max() <= 2e-3

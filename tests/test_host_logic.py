@@ -354,3 +354,16 @@ def test_incremental_flattening_follows_a_growing_map():
     both()
     kf.observations.append((10 ** 6, 0))                         # observation of a map point that is not in the map: dropped
     both()
+
+
+def test_flat_import_through_the_shim():
+    """``from bundle_adjuster import BundleAdjuster`` - the reference's own import line (src/pipeline.py:12) - resolves to the
+    drop-in when bundle_adjustment_b200/shim is ahead on sys.path (run in a fresh interpreter)."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = ("import sys; sys.path.insert(0, %r); from bundle_adjuster import BundleAdjuster; import inspect; "
+            "print(BundleAdjuster.__module__, list(inspect.signature(BundleAdjuster.__init__).parameters)[:3])"
+            % os.path.join(root, "bundle_adjustment_b200", "shim"))
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, check=True, cwd="/").stdout
+    assert "bundle_adjustment_b200.bundle_adjuster" in out and "'camera_matrix', 'window_size'" in out
