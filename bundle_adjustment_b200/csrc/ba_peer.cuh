@@ -36,7 +36,25 @@ namespace ba {
 
 constexpr int XB_MAX_RANKS = 16;           // ranks that can exchange through peer memory (more: NCCL all-reduce)
 constexpr int XB_HDR = 2 * XB_MAX_RANKS;   // doubles reserved in front of the payloads (the flags)
-constexpr long long XB_SPIN_LIMIT = 1LL << 28;  // polls before a rank gives up on a peer (~ seconds) and flags an error
+// A rank waits for a peer's words for at most XB_WAIT_NS of device time (%globaltimer, looked at every 256 polls), then gives
+// up, records the rank it was waiting for (xstate[6] = rank + 1) and raises the error flag xstate[2]: the solve fails with
+// BA_ERR_NCCL naming the rank instead of hanging on a dead peer.
+constexpr unsigned long long XB_WAIT_NS = 4000000000ull;  // 4 s: three orders of magnitude above a whole LM iteration
+struct SpinGuard {
+    unsigned long long t0 = 0;
+    long long spins = 0;
+    BA_D bool expired() {  // call once per failed poll
+        if ((++spins & 255) != 0) return false;
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        if (t0 == 0) { t0 = t; return false; }
+        return t - t0 > XB_WAIT_NS;
+    }
+};
+BA_D void spin_failed(int* xstate, int waited_for_rank) {
+    atomicExch(xstate + 2, 1);
+    atomicCAS(xstate + 6, 0, waited_for_rank + 1);
+}
 __host__ __device__ inline size_t xb_slot(long long seq, int src, int nranks, int cap) {
     return (size_t)XB_HDR + ((size_t)(seq & 1) * nranks + src) * cap;
 }
@@ -69,7 +87,8 @@ BA_D long long ld_acquire_sys(const long long* p) {
     return v;
 }
 
-// xstate: [0] sequence number of the last exchange this rank published, [1] ticket, [2] error flag
+// xstate: [0] sequence number of the last exchange this rank published, [1] ticket, [2] error flag, [3] spare (host barrier),
+// [4] / [5] sequence number / ticket of the LL all-reduce, [6] rank + 1 a timed-out wait was for
 __global__ void __launch_bounds__(RS_WARPS * 32) k_rows_finish_xchg(Params P, double* __restrict__ xbuf, double* const* __restrict__ peers,
                                                                     int nranks, int rank, int push, int cap, int* __restrict__ xstate) {
     __shared__ int last;
@@ -122,9 +141,9 @@ __global__ void __launch_bounds__(VEC_THREADS) k_pcg_dots_peer(Params P, double*
     __syncthreads();
     if (threadIdx.x < nranks) {  // one thread per rank polls that rank's flag
         const long long* flag = xb_flag(push ? xbuf : peers[threadIdx.x], seq, threadIdx.x);
-        long long spins = 0;
+        SpinGuard g;
         while (ld_acquire_sys(flag) < seq)
-            if (++spins > XB_SPIN_LIMIT) { atomicExch(xstate + 2, 1); ok = 0; break; }
+            if (g.expired()) { spin_failed(xstate, threadIdx.x); ok = 0; break; }
     }
     __syncthreads();
     const int c = blockIdx.x * VEC_THREADS + threadIdx.x;
@@ -179,9 +198,9 @@ __global__ void __launch_bounds__(AR_THREADS) k_peer_allreduce(double* __restric
         for (int r = 0; r < nranks; ++r) {
             const ulonglong2* src = reinterpret_cast<const ulonglong2*>(xbuf + ar_base) + (slot_off + r) * ar_cap + e;
             ulonglong2 v = ld_relaxed_sys_v2(src);
-            long long spins = 0;
+            SpinGuard g;
             while ((unsigned)(v.x >> 32) != (unsigned)seq || (unsigned)(v.y >> 32) != (unsigned)seq) {
-                if (++spins > XB_SPIN_LIMIT) { atomicExch(xstate + 2, 1); break; }
+                if (g.expired()) { spin_failed(xstate, r); break; }
                 v = ld_relaxed_sys_v2(src);
             }
             const double x = __longlong_as_double((long long)((v.x & 0xffffffffull) | (v.y << 32)));
@@ -335,11 +354,11 @@ __global__ void __launch_bounds__(PT_THREADS, 1) k_pcg_tail(Params P, double tol
             __syncthreads();
             if (tid < nranks) {  // one thread per rank polls that rank's flag (pull: the NVLink round trips overlap)
                 const long long* flag = xb_flag(push ? xbuf : peers[tid], seq, tid);
-                long long spins = 0;
+                SpinGuard g;
                 bool good = true;
                 while (ld_acquire_sys(flag) < seq)
-                    if (++spins > XB_SPIN_LIMIT) { good = false; break; }
-                if (!good) { atomicExch(xstate + 2, 1); ok = 0; }
+                    if (g.expired()) { good = false; break; }
+                if (!good) { spin_failed(xstate, tid); ok = 0; }
             }
         }
     }
@@ -360,9 +379,9 @@ __global__ void __launch_bounds__(PT_THREADS, 1) k_pcg_tail(Params P, double tol
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     if (r0 + j >= nranks) continue;
-                    long long spins = 0;
+                    SpinGuard g;
                     while ((unsigned)(v[j].x >> 32) != f || (unsigned)(v[j].y >> 32) != f) {
-                        if (++spins > XB_SPIN_LIMIT) { atomicExch(xstate + 2, 1); break; }
+                        if (g.expired()) { spin_failed(xstate, r0 + j); break; }
                         v[j] = ld_relaxed_sys_v2(xb_ll_slot(xbuf, seq, r0 + j, nranks, cap) + i);
                     }
                     w += __longlong_as_double((long long)((v[j].x & 0xffffffffull) | (v[j].y << 32)));

@@ -896,15 +896,44 @@ static void setup_peer_exchange(ba_handle* h, int n_cams) {
     CK(cudaStreamSynchronize(s));
 }
 
+// Distributed handles: a validation error on ONE rank must fail the call on ALL ranks, or the others block forever in the next
+// collective.  Every rank contributes its error code (0 = fine) to one all-reduce (max); a rank that is fine itself reports
+// that another rank failed.  Single-GPU handles: fails at once.
+static void agree_or_fail(ba_handle* h, int code, const char* fmt, ...) {
+    char buf[512] = "";
+    if (code) {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(buf, sizeof buf, fmt, ap);
+        va_end(ap);
+    }
+    int any = code;
+    if (h->nranks > 1 && h->comm) {
+        TBuf<int> d;
+        d.alloc(1);
+        const int mine = code ? 1 : 0;
+        CK(cudaMemcpyAsync(d.p, &mine, sizeof(int), cudaMemcpyHostToDevice, h->stream));
+        NK(nccl_api().AllReduce(d.p, d.p, 1, ncclInt, ncclMax, h->comm, h->stream));
+        int all = 0;
+        CK(cudaMemcpyAsync(&all, d.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+        if (all && !code) fail(BA_ERR_ARG, "ba_set_problem failed on another rank (this rank's arguments were accepted)");
+        any = all ? code : 0;
+    }
+    if (any) fail(BA_ERR_ARG, "%s", buf);
+}
+
 static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy, int n_cams, int n_pts, int n_obs,
                         const double* rvec, const double* tvec, const double* frv, const double* ftv, const double* pts,
                         const int* obs_cam, const int* obs_pt, const double* obs_uv) {
     use(h);
-    if (n_cams < 0 || n_pts <= 0 || n_obs <= 0) fail(BA_ERR_ARG, "need n_adj_cams >= 0, n_pts > 0, n_obs > 0");
-    if (!frv || !ftv || !pts || !obs_cam || !obs_pt || !obs_uv || (n_cams > 0 && (!rvec || !tvec)))
-        fail(BA_ERR_ARG, "null array argument");
     cudaStream_t s = h->stream;
     ScratchScope scratch(s);
+    {
+        const bool bad_n = n_cams < 0 || n_pts <= 0 || n_obs <= 0;
+        const bool bad_p = !frv || !ftv || !pts || !obs_cam || !obs_pt || !obs_uv || (n_cams > 0 && (!rvec || !tvec));
+        agree_or_fail(h, (bad_n || bad_p) ? 1 : 0, "%s", bad_n ? "need n_adj_cams >= 0, n_pts > 0, n_obs > 0" : "null array argument");
+    }
     h->have_problem = false;
     h->coarse_colours = 0; h->coarse_graph_agg = 0;  // the aggregate graph belongs to the problem
     const size_t nc1 = (size_t)n_cams + 1;
@@ -917,7 +946,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     h->pt_D.alloc((size_t)n_pts * 4);
     h->pt_X.zero(s); h->pt_z.zero(s); h->pt_h.zero(s);
     h->init_cam_rt.alloc(nc1 * 6); h->init_pts.alloc((size_t)n_pts * 3);
-    if (cdiv(std::max(n_cams, 1), RS_WARPS) > MAX_VEC_CTAS) fail(BA_ERR_ARG, "too many cameras (%d)", n_cams);
+    if (cdiv(std::max(n_cams, 1), RS_WARPS) > MAX_VEC_CTAS) fail(BA_ERR_ARG, "too many cameras (%d)", n_cams);  // same on every rank
     const size_t ncz = std::max<size_t>(n_cams, 1);
     h->cam_U.alloc(ncz * 21); h->cam_g.alloc(ncz * 6); h->cam_D.alloc(ncz * 6); h->cam_Minv.alloc(ncz * 36);
     h->cam_acc.alloc(ncz * 27); h->cam_partial.alloc(ncz * NSCAL);
@@ -1052,7 +1081,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     CK(cudaMemcpyAsync(camoff.data(), d_camoff.p, (nc1 + 1) * sizeof(int), cudaMemcpyDeviceToHost, s));
     CK(cudaMemcpyAsync(err_track, d_err.p, 2 * sizeof(int), cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
-    if (err_track[0]) fail(BA_ERR_ARG, "observation index out of range (obs_cam must be in [-1, n_adj_cams), obs_pt in [0, n_pts))");
+    agree_or_fail(h, err_track[0], "observation index out of range (obs_cam must be in [-1, n_adj_cams), obs_pt in [0, n_pts))");
     const int n_obs_adj = camoff[n_cams];
     launch(h, KN_SETUP, k_gather_cm, cdiv(n_obs_adj, B), B, 0, n_obs_adj, (const int*)d_perm.p, (const double2*)h->o_uv.p,
            (const int2*)h->o_idx.p, h->cm_uv.p, h->cm_pt.p);
@@ -1113,9 +1142,9 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     h->smem_lin = pm_smem_bytes<9, 6>(cap);
     h->smem_pass = pm_smem_bytes<3, 9>(cap);
     const size_t smem_max = 227 * 1024 - 1024;  // static shared memory of the kernels comes on top
-    if (h->smem_lin > smem_max || h->smem_pass > smem_max)
-        fail(BA_ERR_ARG, "a point is observed %d times; this build supports track lengths up to %d", h->max_track,
-             (int)((smem_max - pm_smem_bytes<9, 6>(0)) / 72) - PM_THREADS);
+    agree_or_fail(h, (h->smem_lin > smem_max || h->smem_pass > smem_max) ? 1 : 0,
+                  "a point is observed %d times; this build supports track lengths up to %d", h->max_track,
+                  (int)((smem_max - pm_smem_bytes<9, 6>(0)) / 72) - PM_THREADS);
     CK(cudaFuncSetAttribute(k_lin_points, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_lin));
     CK(cudaFuncSetAttribute(k_point_pass<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_pass));
     CK(cudaFuncSetAttribute(k_point_pass<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_pass));
@@ -1601,10 +1630,15 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     if (opt->max_iters == 0) read_state(h);
     if (pcg_graph) CK(cudaGraphExecDestroy(pcg_graph));
     if (h->nranks > 1 && h->peer_ok) {
-        int xs[4] = {0, 0, 0, 0};
+        int xs[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         CK(cudaMemcpyAsync(xs, h->xstate.p, sizeof xs, cudaMemcpyDeviceToHost, s));
         CK(cudaStreamSynchronize(s));
-        if (xs[2]) fail(BA_ERR_NCCL, "peer-memory exchange timed out waiting for another rank");
+        if (xs[2]) {
+            CK(cudaMemsetAsync(h->xstate.p + 2, 0, sizeof(int), s));
+            CK(cudaMemsetAsync(h->xstate.p + 6, 0, sizeof(int), s));
+            fail(BA_ERR_NCCL, "peer-memory exchange: rank %d waited more than %.0f s for the words of rank %d", h->rank,
+                 1e-9 * (double)XB_WAIT_NS, xs[6] - 1);
+        }
     }
     CK(cudaEventRecord(h->ev_solve1, s));
     CK(cudaEventSynchronize(h->ev_solve1));

@@ -510,13 +510,19 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_lin(Params 
 #pragma unroll
                 for (int k = 0; k < LS_K; ++k) {
                     const double al = kLsAlpha[k];
-                    const double iz = 1.0 / fma(al, dz, az);
+                    // candidates only have to be RANKED (a factor other than 1 must win by 1e-9 relative): the reciprocal of
+                    // the depth by two Newton steps from the single-precision one (~ 2^-45) instead of a full FP64 division,
+                    // which was most of this loop's instructions
+                    const double z = fma(al, dz, az);
+                    double iz = (double)__frcp_rn((float)z);
+                    iz = iz * fma(-z, iz, 2.0);
+                    iz = iz * fma(-z, iz, 2.0);
                     const double rx = uv.x - fma(P.K.fx, fma(al, dx, ax) * iz, P.K.cx);
                     const double ry = uv.y - fma(P.K.fy, fma(al, dy, ay) * iz, P.K.cy);
-                    double wH, wg, r0x, r0y;
-                    robust_weights(rx, P.delta, P.mode, wH, wg, r0x);
-                    robust_weights(ry, P.delta, P.mode, wH, wg, r0y);
-                    const double c = 0.5 * (r0x + r0y);
+                    const double axr = fabs(rx), ayr = fabs(ry);
+                    const double cx_ = (P.mode == ROBUST_NONE || axr <= P.delta) ? rx * rx : P.delta * (2.0 * axr - P.delta);
+                    const double cy_ = (P.mode == ROBUST_NONE || ayr <= P.delta) ? ry * ry : P.delta * (2.0 * ayr - P.delta);
+                    const double c = 0.5 * (cx_ + cy_);
                     sA[k * FT_LDL + pos] = isfinite(c) ? c : 1e300;
                 }
             }

@@ -554,7 +554,7 @@ def test_default_solve_stops_on_the_reference_tolerances(gpu_solver):
     _upload(gpu_solver, prob, flat)
     st = gpu_solver.solve()
     assert st["status"] in (2, 3, 4), st
-    assert st["iterations"] < 50
+    assert st["iterations"] <= 50
     assert st["final_cost"] <= float(g["res_cost"])
 
 

@@ -267,6 +267,17 @@ def test_partition_points_balanced_and_complete():
         assert total == fp.n_obs
 
 
+def test_partition_points_never_leaves_a_rank_empty():
+    """Skewed tracks (one point holds most observations) put several cuts on the same point; every rank still gets a point,
+    and more ranks than points is the same ValueError on every rank (an empty shard would fail ba_set_problem on one rank only
+    and leave the others waiting in a collective)."""
+    obs_pt = np.concatenate([np.zeros(1000, dtype=np.int64), np.arange(1, 6)])
+    b = sharding.partition_points(obs_pt, 6, 4)
+    assert b[0] == 0 and b[-1] == 6 and np.all(np.diff(b) >= 1)
+    with pytest.raises(ValueError, match="at least one point"):
+        sharding.partition_points(obs_pt, 6, 7)
+
+
 def test_injected_into_the_unmodified_reference_pipeline(tmp_path, monkeypatch, capsys):
     """SURVEY 8f-1 on the CPU side: the reference's VisualOdometryPipeline constructs and calls the drop-in
     class exactly as it does its own (src/pipeline.py:39, :99).  Real frames (desk_images) through the
