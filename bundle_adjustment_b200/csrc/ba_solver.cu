@@ -1412,8 +1412,8 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
         CK(cudaStreamSynchronize(s));
         return true;
     };
-    int last_pcg_iters = 0, lm_iter_host = 0;
-    bool coarse_failed = false;
+    int last_pcg_iters = 0, lm_iter_host = 0, pcg_at_build = 0;
+    bool coarse_failed = false, coarse_rebuild_ok = true;
 
     // ---- the three parts of one LM iteration ------------------------------------------------------------------
     auto before_pcg = [&](bool lin) {
@@ -1428,12 +1428,16 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
             allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 27);
             launch(h, KN_CAM_FIN, k_camera_finish_schur, P.vec_ctas, VEC_THREADS, 0, P, with_schur, h->ticket.p, pcg_loop);
             const bool first_build = !h->coarse_ready && last_pcg_iters > coarse_after;
-            const bool rebuild = h->coarse_ready && last_pcg_iters > 30 && lm_iter_host - coarse_built_at >= 3;
+            // a rebuild has to pay: if the first PCG solve after a (re)build needed more than 3/4 of the iterations that
+            // triggered it, the coarse space is not what this problem lacks - keep the matrix, stop probing
+            if (h->coarse_ready && lm_iter_host == coarse_built_at + 1 && last_pcg_iters * 4 > pcg_at_build * 3) coarse_rebuild_ok = false;
+            const bool rebuild = h->coarse_ready && coarse_rebuild_ok && last_pcg_iters > 30 && lm_iter_host - coarse_built_at >= 3;
             if (two_level && !coarse_failed && (first_build || rebuild)) {
                 const bool was_ready = h->coarse_ready;
                 h->coarse_ready = build_coarse();
                 coarse_failed = !h->coarse_ready;
                 coarse_built_at = lm_iter_host;
+                pcg_at_build = last_pcg_iters;
                 if (pcg_graph && was_ready != h->coarse_ready) { CK(cudaGraphExecDestroy(pcg_graph)); pcg_graph = nullptr; }  // the tail of the graph changes
             }
             if (two_level && h->coarse_ready)
