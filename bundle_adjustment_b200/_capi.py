@@ -18,6 +18,7 @@ ROBUST = {"none": 0, "irls": 1, "triggs": 2}
 PRECOND = {"jacobi": 0, "schur_jacobi": 1, "two_level": 2, "auto": 3}
 PRECOND_NAME = {v: k for k, v in PRECOND.items()}
 SCHUR_PATH = {"tiles": 0, "two_pass": 1, "tiles_rows": 2}
+TRIANGULATE_STATIC_MAX = 16384   # BA_TRIANGULATE_STATIC_MAX in include/ba_b200.h
 STATUS_TEXT = {0: "iteration limit", 1: "gtol", 2: "ftol", 3: "xtol", 4: "ftol and xtol", 5: "damping limit"}
 
 
@@ -87,6 +88,7 @@ SYMBOLS = {
     "ba_layout_info": (C.c_int, [C.c_void_p, _lp]),
     "ba_tile_layout": (C.c_int, [C.c_void_p, _ip, _ip, _ip, _ip, _dp, _ip, _ip, _ip, _ip, _ip]),
     "ba_triangulate": (C.c_int, [C.c_void_p, _dp, _dp, _dp, _dp, C.c_int32, _dp, _dp, _dp, _dp, C.POINTER(C.c_uint8)]),
+    "ba_triangulate_static": (C.c_int, [C.c_void_p, _dp, _dp, _dp, _dp, C.c_int32, _dp, _dp, _dp, _dp, C.POINTER(C.c_uint8)]),
     "ba_last_error": (C.c_char_p, []),
 }
 

@@ -21,6 +21,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -2093,6 +2094,77 @@ int ba_triangulate(ba_handle* h, const double P1[12], const double P2[12], const
     if (hom) CK(cudaMemcpyAsync(hom, dh.p, (size_t)n * 4 * sizeof(double), cudaMemcpyDeviceToHost, s));
     if (xyz) CK(cudaMemcpyAsync(xyz, dx.p, (size_t)n * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
     if (valid) CK(cudaMemcpyAsync(valid, dv.p, (size_t)n, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    API_END
+}
+
+// ---------------------------------------------------------------------------------------------
+// ba_triangulate_static: ba_triangulate without any allocation (requested by the run's operators; no counterpart in the
+// reference).  ba_triangulate stages pts1 / pts2 and the three outputs in scratch buffers from the stream-ordered pool
+// (cudaMallocAsync / cudaFreeAsync); here the same scratch is ONE file-scope __device__ array of fixed size, carved into
+// [pts1 2M | pts2 2M | hom 4M | xyz 3M | valid M bytes], M = BA_TRIANGULATE_STATIC_MAX correspondences (1.46 MB, held by every
+// GPU that loads the library until the process exits).  In host code `g_tri_scratch` is only a stand-in for the symbol, not a
+// device address: the address comes from cudaGetSymbolAddress, once per device with that device current, and is what the
+// kernel is given.  Every call shares the array: it keeps the previous call's contents (the output part is cleared before the
+// kernel runs), and two calls that overlap on the GPU - two handles / streams of one device - race.
+// ---------------------------------------------------------------------------------------------
+namespace ba {
+constexpr size_t TRI_M = BA_TRIANGULATE_STATIC_MAX;
+constexpr size_t TRI_SCRATCH_DOUBLES = 11 * TRI_M + TRI_M / 8;  // valid: M bytes
+static_assert(TRI_M % 32 == 0, "the carve-up keeps every part 256-byte aligned");
+static __device__ __align__(256) double g_tri_scratch[TRI_SCRATCH_DOUBLES];
+
+constexpr int TRI_MAX_DEVICES = 64;
+static double* g_tri_ptr[TRI_MAX_DEVICES] = {nullptr};  // device address of g_tri_scratch on each device (0: not resolved yet)
+static std::mutex g_tri_mutex;
+// set-up, once per device: the caller has made `device` current (ba::use)
+static double* tri_scratch_ptr(int device) {
+    if (device < 0 || device >= TRI_MAX_DEVICES) fail(BA_ERR_ARG, "device ordinal %d beyond %d", device, TRI_MAX_DEVICES - 1);
+    std::lock_guard<std::mutex> lock(g_tri_mutex);
+    if (!g_tri_ptr[device]) {
+        double* ptr = nullptr;
+        CK(cudaGetSymbolAddress((void**)&ptr, g_tri_scratch));
+        if (!ptr) fail(BA_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the triangulation scratch");
+        g_tri_ptr[device] = ptr;
+    }
+    return g_tri_ptr[device];
+}
+}  // namespace ba
+
+int ba_triangulate_static(ba_handle* h, const double P1[12], const double P2[12], const double* R_rel, const double* t_rel,
+                          int32_t n, const double* pts1, const double* pts2, double* hom, double* xyz, uint8_t* valid) {
+    API_BEGIN
+    ba::use(h);
+    if (n < 0 || !P1 || !P2 || (n > 0 && (!pts1 || !pts2))) ba::fail(BA_ERR_ARG, "null or negative argument");
+    if (valid && (!R_rel || !t_rel)) ba::fail(BA_ERR_ARG, "the cheirality test needs R_rel and t_rel");
+    if (n > BA_TRIANGULATE_STATIC_MAX)
+        ba::fail(BA_ERR_ARG, "ba_triangulate_static: %d correspondences exceed the static scratch (BA_TRIANGULATE_STATIC_MAX = %d); "
+                             "split the batch or call ba_triangulate", (int)n, (int)BA_TRIANGULATE_STATIC_MAX);
+    if (n == 0) return BA_OK;
+    cudaStream_t s = h->stream;
+    double* base = ba::tri_scratch_ptr(h->device);
+    const size_t M = ba::TRI_M;
+    double* d1 = base;
+    double* d2 = base + 2 * M;
+    double* dh = base + 4 * M;
+    double* dx = base + 8 * M;
+    unsigned char* dv = reinterpret_cast<unsigned char*>(base + 11 * M);
+    ba::TriParams T;
+    memcpy(T.P1, P1, sizeof T.P1); memcpy(T.P2, P2, sizeof T.P2);
+    for (int k = 0; k < 9; ++k) T.R[k] = R_rel ? R_rel[k] : (k % 4 == 0 ? 1.0 : 0.0);
+    for (int k = 0; k < 3; ++k) T.t[k] = t_rel ? t_rel[k] : 0.0;
+    // the array keeps the last call's results: clear the output part this call will read back
+    CK(cudaMemsetAsync(dh, 0, (size_t)n * 4 * sizeof(double), s));
+    CK(cudaMemsetAsync(dx, 0, (size_t)n * 3 * sizeof(double), s));
+    CK(cudaMemsetAsync(dv, 0, (size_t)n, s));
+    CK(cudaMemcpyAsync(d1, pts1, (size_t)n * 2 * sizeof(double), cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d2, pts2, (size_t)n * 2 * sizeof(double), cudaMemcpyHostToDevice, s));
+    ba::k_triangulate<<<ba::cdiv(n, 128), 128, 0, s>>>(T, (int)n, (const double*)d1, (const double*)d2, hom ? dh : nullptr,
+                                                       xyz ? dx : nullptr, valid ? dv : nullptr);
+    CK(cudaGetLastError());
+    if (hom) CK(cudaMemcpyAsync(hom, dh, (size_t)n * 4 * sizeof(double), cudaMemcpyDeviceToHost, s));
+    if (xyz) CK(cudaMemcpyAsync(xyz, dx, (size_t)n * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
+    if (valid) CK(cudaMemcpyAsync(valid, dv, (size_t)n, cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
     API_END
 }

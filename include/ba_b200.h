@@ -236,6 +236,20 @@ int ba_tile_layout(ba_handle* h, int32_t* ft_pt, int32_t* ft_obs, int32_t* ft_se
 int ba_triangulate(ba_handle* h, const double P1[12], const double P2[12], const double* R_rel, const double* t_rel,
                    int32_t n, const double* pts1, const double* pts2, double* hom, double* xyz, uint8_t* valid);
 
+/* ba_triangulate without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same
+ * arguments, outputs and arithmetic as ba_triangulate (the same kernel), but the device staging of pts1 / pts2 / hom / xyz /
+ * valid - which ba_triangulate takes from the stream-ordered memory pool - lives in ONE file-scope `static __device__` array of
+ * fixed size inside the library: 11.125 doubles per correspondence x BA_TRIANGULATE_STATIC_MAX = 1.46 MB, held by every GPU
+ * that loads the library until the process exits.  n > BA_TRIANGULATE_STATIC_MAX is rejected with BA_ERR_ARG.  The call issues
+ * no cudaMalloc / cudaFree / cudaMallocAsync and no allocating library routine; the first call on a device resolves the array's
+ * device address (cudaGetSymbolAddress) - make one warm-up call before capturing.  All calls on a device share the array: it
+ * keeps the previous call's contents (the part a call reads back is cleared first), and calls that OVERLAP on the GPU (two
+ * handles / streams of one device) race - serialise them. */
+#define BA_TRIANGULATE_STATIC_MAX 16384
+int ba_triangulate_static(ba_handle* h, const double P1[12], const double P2[12], const double* R_rel, const double* t_rel,
+                          int32_t n, const double* pts1, const double* pts2, double* hom, double* xyz, uint8_t* valid);
+
 /* Thread-local text of the last error returned on this thread. */
 const char* ba_last_error(void);
 
