@@ -81,7 +81,7 @@ SYMBOLS = {
     "ba_normal_blocks": (C.c_int, [C.c_void_p, C.POINTER(Options), _dp, _dp, _dp, _dp]),
     "ba_schur_matvec": (C.c_int, [C.c_void_p, C.POINTER(Options), C.c_double, _dp, _dp]),
     "ba_solve": (C.c_int, [C.c_void_p, C.POINTER(Options), C.POINTER(Stats)]),
-    "ba_solve_trace": (C.c_int, [C.c_void_p, C.c_int32, _dp, _dp, _dp, _ip, _ip, _ip]),
+    "ba_solve_trace": (C.c_int, [C.c_void_p, C.c_int32, _dp, _dp, _dp, _ip, _ip, _dp, _ip]),
     "ba_kernel_count": (C.c_int, []),
     "ba_kernel_name": (C.c_char_p, [C.c_int]),
     "ba_kernel_stats": (C.c_int, [C.c_void_p, _lp, _dp]),

@@ -79,7 +79,7 @@ struct LMState {
 // One record per LM iteration (entry 0 = the initial point), written by the 1-thread decision kernels: Huber cost and raw sum of
 // squares of the CURRENT point after the decision, device time since the start of the solve, PCG iterations so far.
 constexpr int TRACE_CAP = 1024;
-struct TraceRec { double cost, raw, ms; int pcg_total, accepted; };
+struct TraceRec { double cost, raw, ms, lambda; int pcg_total, accepted; };
 BA_D unsigned long long global_ns() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -1099,7 +1099,7 @@ __global__ void k_store_cost(Params P, int which) {
     st->cost[b] = st->scal[S_COST];
     st->raw[b] = st->scal[S_RAW];
     if (st->scal[S_BAD] > 0.0 || !isfinite(st->scal[S_COST])) st->bad = 1;
-    if (P.trace && st->iter == 0) P.trace[0] = TraceRec{st->cost[b], st->raw[b], 1e-6 * (double)(global_ns() - st->t0), 0, 0};
+    if (P.trace && st->iter == 0) P.trace[0] = TraceRec{st->cost[b], st->raw[b], 1e-6 * (double)(global_ns() - st->t0), st->lambda, 0, 0};
 }
 
 // Accept / reject the trial point, update the damping (Nielsen), test ftol / xtol.
@@ -1111,6 +1111,7 @@ __global__ void k_lm_decide(Params P, double ftol, double xtol, double lam_min, 
         return;
     }
     const double* s = st->scal;
+    const double lambda_used = st->lambda;  // the damping this iteration's step was computed with (trace)
     const int cur = st->cur, tri = cur ^ 1;
     const double cost_new = s[S_COST], raw_new = s[S_RAW];
     const bool finite_new = isfinite(cost_new) && !(s[S_BAD] > 0.0);
@@ -1149,7 +1150,7 @@ __global__ void k_lm_decide(Params P, double ftol, double xtol, double lam_min, 
     }
     if (st->status == 0 && st->iter >= max_iters) st->status = 6;  // iteration limit (reported as 0)
     if (P.trace && st->iter < TRACE_CAP)
-        P.trace[st->iter] = TraceRec{st->cost[st->cur], st->raw[st->cur], 1e-6 * (double)(global_ns() - st->t0), st->pcg_total, accept ? 1 : 0};
+        P.trace[st->iter] = TraceRec{st->cost[st->cur], st->raw[st->cur], 1e-6 * (double)(global_ns() - st->t0), lambda_used, st->pcg_total, accept ? 1 : 0};
     set_loop(lm_loop, st->status == 0);
 }
 

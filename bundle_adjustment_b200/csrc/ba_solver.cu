@@ -1289,8 +1289,8 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     const bool tail = tiles && h->tail_cluster > 0 && (h->nranks == 1 || h->peer_ok) && opt->pcg_tail != 0;
     // the PCG iterations of a solve are replayed from a CUDA graph (no NCCL call inside, no per-kernel event timing)
     const bool use_graph = (h->nranks == 1 || (h->peer_ok && tiles)) && !h->time_kernels && check_every > 1;
-    cudaGraphExec_t pcg_graph = nullptr;
-    long long graph_launches[KN_COUNT] = {0};
+    cudaGraphExec_t pcg_graph[2] = {nullptr, nullptr};  // [0] Schur-Jacobi tail, [1] tail with the coarse correction
+    long long graph_launches[2][KN_COUNT] = {{0}, {0}};
 
     CK(cudaEventRecord(h->ev_solve0, s));
     // the two kernel paths write the per-tile step sums into different rows of pm_partial and k_reduce_scalars adds ALL rows:
@@ -1317,9 +1317,12 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     bool two_level = want_two_level && tiles && tail && P.n_cams > 0;
     h->coarse_ready = false;
     int coarse_builds = 0, coarse_matvecs = 0, coarse_built_at = -1000;
-    const int coarse_after = opt->coarse_after == 0 ? 15 : opt->coarse_after;
+    // 24: Schur-Jacobi has to be struggling.  On the 50 M-observation problem (10 k cameras) it never needs more than 18 iterations and a
+    // coarse matrix, stale after a few LM iterations of a far-from-converged problem, cost more than it saved (profiles/r02j_*)
+    const int coarse_after = opt->coarse_after == 0 ? 24 : opt->coarse_after;
     if (two_level) {
         h->coarse_agg = opt->coarse_aggregate > 0 ? opt->coarse_aggregate : std::max(32, cdiv(P.n_cams, 64));
+        h->coarse_agg = std::max(h->coarse_agg, cdiv(P.n_cams, 128));  // at most 128 aggregates = 768 coarse unknowns (the inverse is cubic)
         h->coarse_nz = 6 * cdiv(P.n_cams, h->coarse_agg);
         const size_t cb = pt_smem_bytes(P.n_cams, h->tail_cluster, h->coarse_nz, h->coarse_agg);
         const void* fn = h->nranks > 1 ? (const void*)k_pcg_tail<true, true> : (const void*)k_pcg_tail<false, true>;
@@ -1413,8 +1416,9 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
         CK(cudaStreamSynchronize(s));
         return true;
     };
-    int last_pcg_iters = 0, lm_iter_host = 0, pcg_at_build = 0;
-    bool coarse_failed = false, coarse_rebuild_ok = true;
+    int last_pcg_iters = 0, lm_iter_host = 0, pcg_at_build = 0, pcg_after_build = 0;
+    bool coarse_failed = false, use_coarse = false, used_coarse_last = false;
+    double lambda_now = opt->initial_lambda, lambda_at_build = 0.0;
 
     // ---- the three parts of one LM iteration ------------------------------------------------------------------
     auto before_pcg = [&](bool lin) {
@@ -1428,20 +1432,25 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
             launch(h, KN_CAM_SUM, k_camera_sum, cdiv((long long)P.n_cams * 27, 256), 256, 0, P, 27, 0);
             allreduce_sum(h, h->cam_acc.p, (size_t)P.n_cams * 27);
             launch(h, KN_CAM_FIN, k_camera_finish_schur, P.vec_ctas, VEC_THREADS, 0, P, with_schur, h->ticket.p, pcg_loop);
-            const bool first_build = !h->coarse_ready && last_pcg_iters > coarse_after;
-            // a rebuild has to pay: if the first PCG solve after a (re)build needed more than 3/4 of the iterations that
-            // triggered it, the coarse space is not what this problem lacks - keep the matrix, stop probing
-            if (h->coarse_ready && lm_iter_host == coarse_built_at + 1 && last_pcg_iters * 4 > pcg_at_build * 3) coarse_rebuild_ok = false;
-            const bool rebuild = h->coarse_ready && coarse_rebuild_ok && last_pcg_iters > 30 && lm_iter_host - coarse_built_at >= 3;
-            if (two_level && !coarse_failed && (first_build || rebuild)) {
-                const bool was_ready = h->coarse_ready;
-                h->coarse_ready = build_coarse();
-                coarse_failed = !h->coarse_ready;
-                coarse_built_at = lm_iter_host;
-                pcg_at_build = last_pcg_iters;
-                if (pcg_graph && was_ready != h->coarse_ready) { CK(cudaGraphExecDestroy(pcg_graph)); pcg_graph = nullptr; }  // the tail of the graph changes
+            // --- two-level preconditioner: when to build, use, rebuild and give up (all from replicated state: every rank decides alike)
+            if (two_level && !coarse_failed) {
+                if (h->coarse_ready && used_coarse_last && lm_iter_host == coarse_built_at + 1) pcg_after_build = last_pcg_iters;
+                const bool first_build = !h->coarse_ready && last_pcg_iters > coarse_after;
+                const bool rebuild = h->coarse_ready && used_coarse_last && lm_iter_host - coarse_built_at >= 3 &&
+                                     last_pcg_iters > std::max(30, 2 * pcg_after_build);
+                if (first_build || rebuild) {
+                    h->coarse_ready = build_coarse();
+                    coarse_failed = !h->coarse_ready;
+                    coarse_built_at = lm_iter_host;
+                    pcg_at_build = last_pcg_iters;
+                    lambda_at_build = lambda_now;
+                }
             }
-            if (two_level && h->coarse_ready)
+            // the coarse matrix belongs to the damping it was probed with ((V + lambda D)^-1 inside S): after a rejected step has
+            // pushed lambda out of [1/4, 4] x that value the lagged correction does harm - this LM iteration runs Schur-Jacobi
+            use_coarse = two_level && h->coarse_ready && !coarse_failed &&
+                         lambda_now <= 4.0 * lambda_at_build && lambda_now >= 0.25 * lambda_at_build;
+            if (use_coarse)
                 launch(h, KN_CAM_FIN, k_coarse_first, 1, PT_THREADS, 2 * (size_t)h->coarse_nz * sizeof(double), P,
                        Coarse{h->coarse_Ainv.p, h->coarse_agg, h->coarse_nz}, pcg_loop);
         }
@@ -1452,7 +1461,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
             launch_tile_matvec(h, PA, acc, h->v_u.p);
             const size_t bytes = pt_smem_bytes(P.n_cams, h->tail_cluster);
             const Coarse none{nullptr, 1, 0};
-            if (h->nranks > 1 && two_level && h->coarse_ready)
+            if (h->nranks > 1 && use_coarse)
                 launch_cluster(h, KN_PCG_TAIL, k_pcg_tail<true, true>, h->tail_cluster, PT_THREADS,
                                pt_smem_bytes(P.n_cams, h->tail_cluster, h->coarse_nz, h->coarse_agg), PA, opt->pcg_tol, opt->pcg_max_iters,
                                h->xbuf.p, (double* const*)h->d_peers.p, h->nranks, h->rank, h->xpush, h->xcap, h->xstate.p, pcg_loop,
@@ -1460,7 +1469,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
             else if (h->nranks > 1)
                 launch_cluster(h, KN_PCG_TAIL, k_pcg_tail<true, false>, h->tail_cluster, PT_THREADS, bytes, PA, opt->pcg_tol, opt->pcg_max_iters,
                                h->xbuf.p, (double* const*)h->d_peers.p, h->nranks, h->rank, h->xpush, h->xcap, h->xstate.p, pcg_loop, none);
-            else if (two_level && h->coarse_ready)
+            else if (use_coarse)
                 launch_cluster(h, KN_PCG_TAIL, k_pcg_tail<false, true>, h->tail_cluster, PT_THREADS,
                                pt_smem_bytes(P.n_cams, h->tail_cluster, h->coarse_nz, h->coarse_agg), PA, opt->pcg_tol, opt->pcg_max_iters,
                                (double*)nullptr, (double* const*)nullptr, 1, 0, 0, 0, (int*)nullptr, pcg_loop,
@@ -1597,20 +1606,21 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
             };
             if (use_graph) {
                 // `check_every` PCG iterations = one CUDA graph launch (kernels early-exit once the device flag is set)
-                if (!pcg_graph) {
+                const int gi = use_coarse ? 1 : 0;
+                if (!pcg_graph[gi]) {
                     long long before[KN_COUNT];
                     memcpy(before, h->launches, sizeof before);
                     cudaGraph_t g = nullptr;
                     CK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
                     for (int k = 0; k < check_every; ++k) pcg_iteration();
                     CK(cudaStreamEndCapture(s, &g));
-                    CK(cudaGraphInstantiate(&pcg_graph, g, 0));
+                    CK(cudaGraphInstantiate(&pcg_graph[gi], g, 0));
                     CK(cudaGraphDestroy(g));
-                    for (int k = 0; k < KN_COUNT; ++k) { graph_launches[k] = h->launches[k] - before[k]; h->launches[k] = before[k]; }
+                    for (int k = 0; k < KN_COUNT; ++k) { graph_launches[gi][k] = h->launches[k] - before[k]; h->launches[k] = before[k]; }
                 }
                 for (int it = 0; it < opt->pcg_max_iters; it += check_every) {
-                    CK(cudaGraphLaunch(pcg_graph, s));
-                    for (int k = 0; k < KN_COUNT; ++k) h->launches[k] += graph_launches[k];
+                    CK(cudaGraphLaunch(pcg_graph[gi], s));
+                    for (int k = 0; k < KN_COUNT; ++k) h->launches[k] += graph_launches[gi][k];
                     if (it + check_every < opt->pcg_max_iters && pcg_converged()) break;
                 }
             } else {
@@ -1627,13 +1637,16 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
         need_lin = st.last_accepted != 0;
         last_pcg_iters = st.pcg_iter;
         lm_iter_host = st.iter;
+        lambda_now = st.lambda;
+        used_coarse_last = use_coarse;
         if (opt->verbose & 1)
             fprintf(stderr, "[ba_b200] it %3d %s cost %.9e -> trial %.9e  rho %+.3e  lambda %.3e  pcg %d  |g| %.3e  |dx| %.3e\n",
                     st.iter, st.last_accepted ? "acc" : "REJ", st.cost[st.cur ^ (st.last_accepted ? 1 : 0)], st.scal[S_COST], st.rho,
                     st.lambda, st.pcg_iter, st.gmax, st.step_norm);
     }
     if (opt->max_iters == 0) read_state(h);
-    if (pcg_graph) CK(cudaGraphExecDestroy(pcg_graph));
+    for (int gi = 0; gi < 2; ++gi)
+        if (pcg_graph[gi]) CK(cudaGraphExecDestroy(pcg_graph[gi]));
     if (h->nranks > 1 && h->peer_ok) {
         int xs[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         CK(cudaMemcpyAsync(xs, h->xstate.p, sizeof xs, cudaMemcpyDeviceToHost, s));
@@ -2170,7 +2183,7 @@ int ba_triangulate_static(ba_handle* h, const double P1[12], const double P2[12]
 }
 
 int ba_solve_trace(ba_handle* h, int32_t cap, double* cost, double* raw_cost, double* ms, int32_t* pcg_total, int32_t* accepted,
-                   int32_t* n_out) {
+                   double* lambda, int32_t* n_out) {
     API_BEGIN
     ba::need_problem(h);
     const int n = std::min<int>(h->trace_n, std::max(cap, 0));
@@ -2185,6 +2198,7 @@ int ba_solve_trace(ba_handle* h, int32_t cap, double* cost, double* raw_cost, do
         if (ms) ms[i] = rec[i].ms;
         if (pcg_total) pcg_total[i] = rec[i].pcg_total;
         if (accepted) accepted[i] = rec[i].accepted;
+        if (lambda) lambda[i] = rec[i].lambda;
     }
     if (n_out) *n_out = h->trace_n;
     API_END

@@ -191,13 +191,13 @@ class FlatSolver:
     def solve_trace(self) -> Dict[str, np.ndarray]:
         """Per-LM-iteration record of the last solve, stamped on the device (``ba_solve_trace``): entry 0 = initial point."""
         n = C.c_int32()
-        api.check(api.lib().ba_solve_trace(self._h, 0, None, None, None, None, None, C.byref(n)))
+        api.check(api.lib().ba_solve_trace(self._h, 0, None, None, None, None, None, None, C.byref(n)))
         k = n.value
-        cost, raw, ms = np.zeros(k), np.zeros(k), np.zeros(k)
+        cost, raw, ms, lam = np.zeros(k), np.zeros(k), np.zeros(k), np.zeros(k)
         pcg, acc = np.zeros(k, dtype=np.int32), np.zeros(k, dtype=np.int32)
         api.check(api.lib().ba_solve_trace(self._h, k, api.dptr(cost), api.dptr(raw), api.dptr(ms), api.iptr(pcg), api.iptr(acc),
-                                           C.byref(n)))
-        return {"cost": cost, "raw_cost": raw, "ms": ms, "pcg_total": pcg, "accepted": acc}
+                                           api.dptr(lam), C.byref(n)))
+        return {"cost": cost, "raw_cost": raw, "ms": ms, "pcg_total": pcg, "accepted": acc, "lambda": lam}
 
     def layout_info(self) -> Dict[str, int]:
         out = np.zeros(12, dtype=np.int64)

@@ -47,8 +47,9 @@ typedef struct ba_handle ba_handle;
 #define BA_PRECOND_TWO_LEVEL 2    /* Schur-Jacobi plus an additive coarse correction  Z (Z^T S Z)^-1 Z^T : one rigid 6-vector per
                                      aggregate of consecutive cameras; the coarse matrix is probed with the tile pass (one
                                      mat-vec per colour of the aggregate graph and component) once the PCG of an LM iteration
-                                     has needed more than 15 iterations, inverted on the device and kept (rebuilt when the
-                                     iteration count climbs again).  Needs the default kernel path (tiles + cluster tail; on
+                                     has needed more than 24 iterations, inverted on the device and kept (rebuilt when the
+                                     iteration count climbs again; skipped for an LM iteration whose damping is more than 4x away
+                                     from the one it was probed with).  Needs the default kernel path (tiles + cluster tail; on
                                      N > 1 GPUs the peer-memory exchange); where that is unavailable the solve runs with
                                      Schur-Jacobi and says so in ba_stats.precond_used.  Host-driven loops.              */
 #define BA_PRECOND_AUTO 3         /* two-level for >= 128 adjustable cameras, else Schur-Jacobi               (default) */
@@ -82,7 +83,7 @@ typedef struct ba_options {
                                  0: the host drives the loops (always the case for verbose / timed / multi-GPU solves) */
     int32_t coarse_aggregate; /* cameras per aggregate of the two-level preconditioner; 0 (default) = max(32, n_cams / 64)  */
     int32_t coarse_after;     /* build the coarse matrix once an LM iteration's PCG needed more than this many iterations;
-                                 0 (default) = 15, negative = from the first LM iteration on                              */
+                                 0 (default) = 24, negative = from the first LM iteration on                              */
     int32_t point_linesearch; /* 1 (default): after every LM step each point scales its own update by the factor out of
                                  {1, 1/2, 2, 4, 8, 16} with the smallest Huber cost over its observations (cameras at the trial
                                  poses; the total cost can only go down against the plain step).  0: plain LM steps           */
@@ -198,11 +199,12 @@ int ba_solve(ba_handle* h, const ba_options* opt, ba_stats* stats_out);
 /* Trajectory of the last ba_solve, recorded on the device by the 1-thread decision kernel (time stamps from %globaltimer, so
  * they include everything the solve enqueued and no host time): entry 0 = the initial point, entry i = the state after LM
  * iteration i.  cost = 0.5 * sum rho and raw_cost = sum r^2 of the CURRENT point (unchanged by a rejected step), ms = device time
- * since the start of the solve, pcg_total = PCG iterations so far, accepted = 1 if iteration i was accepted.  Up to `cap` entries
+ * since the start of the solve, pcg_total = PCG iterations so far, accepted = 1 if iteration i was accepted, lambda = the damping
+ * iteration i's step was computed with (entry 0: the initial damping).  Up to `cap` entries
  * are written (any array may be NULL); *n_out = entries available (iterations + 1, at most 1024).  What the reference offers
  * instead: verbose=2 prints of least_squares (src/bundle_adjuster.py:173 passes verbose=0). */
 int ba_solve_trace(ba_handle* h, int32_t cap, double* cost, double* raw_cost, double* ms, int32_t* pcg_total, int32_t* accepted,
-                   int32_t* n_out);
+                   double* lambda, int32_t* n_out);
 
 /* Per-kernel accounting of the last ba_solve: for each of the `n` kernel kinds (ba_kernel_name(k)),
  * number of launches and summed CUDA-event milliseconds.  Times are filled when opt->verbose >= 2:

@@ -28,4 +28,5 @@ for var in variants:
     print(f"{var:40s}", json.dumps({k: st[k] for k in keys}), flush=True)
     print("   ms :", " ".join(f"{b - a:.1f}" for a, b in zip(tr["ms"][:-1], tr["ms"][1:])))
     print("   pcg:", " ".join(str(b - a) for a, b in zip(tr["pcg_total"][:-1], tr["pcg_total"][1:])))
+    print("   lam:", " ".join(f"{v:.0e}" for v in tr["lambda"][1:]))
     print("   cost:", " ".join(f"{c:.5e}" for c in tr["cost"][::5]), flush=True)

@@ -12,8 +12,11 @@ from bundle_adjustment_b200 import FlatSolver, sharding, synthetic as S  # noqa:
 
 
 PROBLEMS = {"chain60": ((60, 20000, 100000, 21), dict(max_iters=8)),
-            # long camera chain, two-level preconditioner from the first LM iteration on (coarse matrix summed over the ranks)
-            "two_level": ((300, 12000, 60000, 31), dict(max_iters=12, precond="two_level", coarse_after=-1, ftol=0.0, xtol=0.0))}
+            # long camera chain, two-level preconditioner from the first LM iteration on (coarse matrix summed over the ranks); the
+            # damping starts at its floor and the PCG runs to 1e-8, so that the LM steps are exact and do not hinge on a stopping
+            # threshold crossed one iteration earlier or later
+            "two_level": ((300, 12000, 60000, 31), dict(max_iters=4, precond="two_level", coarse_after=-1, ftol=0.0, xtol=0.0, gtol=0.0,
+                                                        initial_lambda=1e-6, pcg_tol=1e-8, pcg_max_iters=2000))}
 
 
 def main(out_path, pcg_tail, which="chain60"):

@@ -98,5 +98,5 @@ def test_two_level_preconditioner_on_two_ranks(tmp_path):
     assert int(r0["precond"]) == 2 and int(r0["coarse_builds"]) == st1["coarse_builds"]
     assert np.array_equal(r0["rvec"], r1["rvec"]) and float(r0["cost"]) == float(r1["cost"])
     assert int(r0["iters"]) == st1["iterations"]
-    assert abs(int(r0["pcg"]) - st1["pcg_iterations"]) <= 2
-    assert abs(float(r0["cost"]) - st1["final_cost"]) <= 1e-7 * st1["final_cost"]
+    assert abs(float(r0["cost"]) - st1["final_cost"]) <= 1e-9 * st1["final_cost"]
+    assert abs(int(r0["pcg"]) - st1["pcg_iterations"]) <= 0.05 * st1["pcg_iterations"] + 2, (int(r0["pcg"]), st1["pcg_iterations"])
