@@ -35,7 +35,7 @@ class Options(C.Structure):
                 ("pcg_max_iters", C.c_int32), ("pcg_tol", C.c_double), ("pcg_check_every", C.c_int32),
                 ("verbose", C.c_int32), ("schur_path", C.c_int32), ("pcg_tail", C.c_int32),
                 ("device_loop", C.c_int32), ("coarse_aggregate", C.c_int32), ("coarse_after", C.c_int32),
-                ("point_linesearch", C.c_int32), ("reserved", C.c_int32 * 1)]
+                ("point_linesearch", C.c_int32), ("dense_schur", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -44,10 +44,10 @@ class Stats(C.Structure):
                 ("final_raw_cost", C.c_double), ("initial_cost", C.c_double), ("final_cost", C.c_double),
                 ("gradient_max", C.c_double), ("final_lambda", C.c_double), ("solve_ms", C.c_double),
                 ("precond_used", C.c_int32), ("coarse_builds", C.c_int32), ("coarse_matvecs", C.c_int32),
-                ("coarse_unknowns", C.c_int32), ("reserved", C.c_double * 6)]
+                ("coarse_unknowns", C.c_int32), ("dense_solves", C.c_int32), ("reserved_i", C.c_int32), ("reserved", C.c_double * 5)]
 
     def as_dict(self):
-        d = {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
+        d = {k: getattr(self, k) for k, _ in self._fields_ if not k.startswith("reserved")}
         d["status_text"] = STATUS_TEXT.get(self.status, "?")
         d["precond_text"] = PRECOND_NAME.get(self.precond_used, "?")
         return d

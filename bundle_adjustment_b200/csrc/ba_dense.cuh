@@ -1,0 +1,227 @@
+// ba_dense.cuh - the reduced camera system of a SMALL problem (at most DN_MAX_CAMS adjustable cameras: the sliding windows of
+// the reference's pipeline, src/pipeline.py:99 with BA_WINDOW_SIZE = 5, and its final global BA over a handful of keyframes)
+// assembled explicitly and solved by a dense Cholesky factorisation, instead of preconditioned CG:
+//
+//      S = blockdiag(U_c + lambda D_c) - sum_p  E_p (V_p + lambda D_p)^-1 E_p^T          (6 Nc x 6 Nc, Nc <= 16)
+//
+// With 24 .. 96 unknowns a PCG solve is 7 .. 20 iterations of two launch-bound kernels each and leaves an inexact step;
+// ONE kernel here does the whole camera side of an LM iteration and gives the exact step.
+//
+// PAIRS.  Two cameras are coupled through every point both observe.  ba_set_problem lists all ordered pairs (i, j) of
+// observations of adjustable cameras that share a point - i = j included, a camera that lists a point twice included - sorted
+// by bin = camera(i) * Nc + camera(j).  One CTA per bin adds the 6x6 blocks of its pairs,
+//      E_i Vinv E_j^T = C_i^T (Jt_i Vinv Jt_j^T) C_j,     C = Jt [-[X]x | I]  (2x6),   Jt = W^1/2 Jp  (the Jacobian cache),
+// thread-strided with register accumulators, a shuffle tree and a fixed-order sum over the warps: no floating-point atomics,
+// bit-reproducible.
+#pragma once
+#include "ba_tiles.cuh"
+
+namespace ba {
+
+constexpr int DN_MAX_CAMS = 16;           // 96 unknowns: the factorisation runs in one CTA's shared memory
+constexpr int DN_MAX_OBS = 1 << 17;
+constexpr int DN_MAX_PAIRS = 1 << 22;
+constexpr int DN_THREADS = 256;
+
+// number of pairs observation i (point-major index) opens: the adjustable observations of its point
+__global__ void k_dn_pair_count(int n_obs, int n_cams, const int2* __restrict__ pm_idx, const int* __restrict__ pt_off,
+                                int* __restrict__ cnt) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i > n_obs) return;
+    int c = 0;
+    if (i < n_obs && pm_idx[i].x < n_cams) {
+        const int p = pm_idx[i].y;
+        for (int j = pt_off[p]; j < pt_off[p + 1]; ++j) c += pm_idx[j].x < n_cams ? 1 : 0;
+    }
+    cnt[i] = c;  // cnt[n_obs] = 0: the exclusive scan's last entry is the total
+}
+__global__ void k_dn_pair_fill(int n_obs, int n_cams, const int2* __restrict__ pm_idx, const int* __restrict__ pt_off,
+                               const int* __restrict__ pm_tc, const int* __restrict__ off, unsigned* __restrict__ key,
+                               int* __restrict__ idx, int4* __restrict__ pairs) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_obs) return;
+    const int2 me = pm_idx[i];
+    if (me.x >= n_cams) return;
+    int k = off[i];
+    const int ti = pm_tc[i];
+    for (int j = pt_off[me.y]; j < pt_off[me.y + 1]; ++j) {
+        const int cj = pm_idx[j].x;
+        if (cj >= n_cams) continue;
+        key[k] = (unsigned)(me.x * n_cams + cj);
+        idx[k] = k;
+        pairs[k] = make_int4(ti, pm_tc[j], me.y, 0);
+        ++k;
+    }
+}
+__global__ void k_dn_pair_gather(int n, const int* __restrict__ perm, const int4* __restrict__ in, int4* __restrict__ out) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < n) out[k] = in[perm[k]];
+}
+
+// ONE kernel per LM iteration does the whole camera side of a small problem: CTA (c, c') adds its bin
+//      S_cc' = delta_cc' U_c  -  sum over the pairs of C_i^T (Jt_i Vinv Jt_j^T) C_j                (row-major 6x6)
+// and the diagonal CTAs, from their i = j pairs (= the observations of camera c), also diag(U_c), the gradient
+// g_c = sum C_i^T rho_i  (rho = W^-1/2 w_g r, stored beside the Jacobian cache by the tile linearisation) and E h = sum C_i^T Jt_i h_p.
+// That replaces the two camera-major passes, their tile sums and finish kernels.  The CTA that finishes LAST (integer ticket;
+// what it computes does not depend on which one it is) assembles S + lambda D, factorises it (Cholesky in shared memory),
+// solves S x = E h - g_c, and writes x, g_c, D_c, the gradient test.  Fixed summation order everywhere: bit-reproducible.
+constexpr int DN_EXTRA = 18;  // per camera: diag(U) 6, g_c 6, E h 6
+
+__host__ __device__ inline size_t dn_solve_smem(int n_cams) {
+    const size_t n = 6 * (size_t)n_cams;
+    return (n * (n + 1) + 2 * n) * sizeof(double);
+}
+
+__global__ void __launch_bounds__(DN_THREADS) k_dense_schur(Params P, const int4* __restrict__ pairs, const int* __restrict__ bin_off,
+                                                            double* __restrict__ S_bins, double* __restrict__ extra,
+                                                            int* __restrict__ ticket, int* __restrict__ n_solves, double dmin,
+                                                            double dmax, double gtol) {
+    extern __shared__ __align__(16) double dsm[];
+    __shared__ double red[DN_THREADS / 32 * (36 + DN_EXTRA)];
+    __shared__ double tot[36 + DN_EXTRA];
+    __shared__ int last, bad;
+    const int tid = threadIdx.x;
+    const int nc = P.n_cams, bin = blockIdx.x;
+    const int ci = bin / nc, cj = bin - ci * nc;
+    const bool diag = ci == cj;
+    const int b = P.st->cur;
+    const double2* Jb = P.tc_J + (size_t)b * 3 * P.n_obs;
+    const double2* Rb = P.tc_r + (size_t)b * P.n_obs;
+    double acc[36 + DN_EXTRA];
+#pragma unroll
+    for (int k = 0; k < 36 + DN_EXTRA; ++k) acc[k] = 0.0;
+    const int k0 = __ldg(bin_off + bin), k1 = __ldg(bin_off + bin + 1);
+    for (int k = k0 + tid; k < k1; k += DN_THREADS) {
+        const int4 pr = __ldg(pairs + k);
+        double X[3], Vi[6];
+        load_pt(P, b, pr.z, X);
+        {
+            const double2* v = reinterpret_cast<const double2*>(P.pt_Vinv + (size_t)pr.z * 6);
+            const double2 a0 = v[0], a1 = v[1], a2 = v[2];
+            Vi[0] = a0.x; Vi[1] = a0.y; Vi[2] = a1.x; Vi[3] = a1.y; Vi[4] = a2.x; Vi[5] = a2.y;  // 00 01 02 11 12 22
+        }
+        const double2 i0 = Jb[pr.x], i1 = Jb[(size_t)P.n_obs + pr.x], i2 = Jb[2 * (size_t)P.n_obs + pr.x];
+        const double2 j0 = Jb[pr.y], j1 = Jb[(size_t)P.n_obs + pr.y], j2 = Jb[2 * (size_t)P.n_obs + pr.y];
+        const double jxi[3] = {i0.x, i0.y, i1.x}, jyi[3] = {i1.y, i2.x, i2.y};
+        const double jxj[3] = {j0.x, j0.y, j1.x}, jyj[3] = {j1.y, j2.x, j2.y};
+        double tx[3], ty[3];  // Vinv jx_j, Vinv jy_j
+        sym3_mulv(Vi, jxj, tx);
+        sym3_mulv(Vi, jyj, ty);
+        const double K00 = jxi[0] * tx[0] + jxi[1] * tx[1] + jxi[2] * tx[2], K01 = jxi[0] * ty[0] + jxi[1] * ty[1] + jxi[2] * ty[2];
+        const double K10 = jyi[0] * tx[0] + jyi[1] * tx[1] + jyi[2] * tx[2], K11 = jyi[0] * ty[0] + jyi[1] * ty[1] + jyi[2] * ty[2];
+        double cxi[6], cyi[6], cxj[6], cyj[6];  // rows of C = (X x j, j)
+        cross3(X, jxi, cxi); cross3(X, jyi, cyi); cross3(X, jxj, cxj); cross3(X, jyj, cyj);
+#pragma unroll
+        for (int q = 0; q < 3; ++q) { cxi[3 + q] = jxi[q]; cyi[3 + q] = jyi[q]; cxj[3 + q] = jxj[q]; cyj[3 + q] = jyj[q]; }
+        const bool self = diag && pr.x == pr.y;  // the observation itself: its U, g_c and E h terms
+        const double u = self ? 1.0 : 0.0;
+        double Tx[6], Ty[6];  // (delta_ij I - K) C_j
+#pragma unroll
+        for (int q = 0; q < 6; ++q) { Tx[q] = (u - K00) * cxj[q] - K01 * cyj[q]; Ty[q] = -K10 * cxj[q] + (u - K11) * cyj[q]; }
+#pragma unroll
+        for (int a = 0; a < 6; ++a)
+#pragma unroll
+            for (int q = 0; q < 6; ++q) acc[6 * a + q] += cxi[a] * Tx[q] + cyi[a] * Ty[q];
+        if (self) {
+            const double2 rho = Rb[pr.x];
+            double h[3];
+            load_v3(P.pt_h + (size_t)pr.z * 4, h);
+            const double ex = jxi[0] * h[0] + jxi[1] * h[1] + jxi[2] * h[2], ey = jyi[0] * h[0] + jyi[1] * h[1] + jyi[2] * h[2];
+#pragma unroll
+            for (int a = 0; a < 6; ++a) {
+                acc[36 + a] += cxi[a] * cxi[a] + cyi[a] * cyi[a];
+                acc[42 + a] += cxi[a] * rho.x + cyi[a] * rho.y;
+                acc[48 + a] += cxi[a] * ex + cyi[a] * ey;
+            }
+        }
+    }
+    block_sum<36 + DN_EXTRA, DN_THREADS>(acc, red, tot);
+    __syncthreads();
+    if (tid < 36) S_bins[(size_t)bin * 36 + tid] = tot[tid];
+    if (diag && tid < DN_EXTRA) extra[(size_t)ci * DN_EXTRA + tid] = tot[36 + tid];
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) last = (atomicAdd(ticket, 1) == (int)gridDim.x - 1);
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+
+    // ---- the last CTA: S + lambda D, Cholesky, solve -------------------------------------------------------------------
+    const int n = 6 * nc, ld = n + 1;
+    double* A = dsm;                       // [n][ld], lower triangle
+    double* y = dsm + (size_t)n * ld;      // [n] right-hand side -> solution
+    double* D = y + n;                     // [n]
+    LMState* st = P.st;
+    const double lam = st->lambda;
+    if (tid == 0) { bad = 0; *ticket = 0; }
+    for (int l = tid; l < n; l += DN_THREADS) {
+        const int c = l / 6, a = l - 6 * c;
+        const double* e = extra + (size_t)c * DN_EXTRA;
+        const double d = fmin(fmax(__ldcg(e + a), dmin), dmax), g = __ldcg(e + 6 + a), eh = __ldcg(e + 12 + a);
+        D[l] = d;
+        y[l] = eh - g;
+        P.cam_D[l] = d; P.cam_g[l] = g; P.v_b[l] = eh - g;
+    }
+    __syncthreads();
+    for (int l = tid; l < n * n; l += DN_THREADS) {
+        const int r = l / n, c = l - r * n;
+        if (c > r) continue;
+        const int cr = r / 6, a = r - 6 * cr, cc = c / 6, q = c - 6 * cc;
+        double v = __ldcg(S_bins + (size_t)(cr * nc + cc) * 36 + 6 * a + q);
+        if (r == c) v += lam * D[r];
+        A[r * ld + c] = v;
+    }
+    // gradient test at the current point (skipped after a rejected step: the point and its gradient are unchanged)
+    if (tid == 0 && !lin_gated(st)) {
+        double m = st->scal[S_GPMAX];
+        for (int l = 0; l < n; ++l) m = fmax(m, fabs(P.cam_g[l]));
+        st->gmax = m;
+        if (st->status == 0 && m < gtol) st->status = 1;
+    }
+    __syncthreads();
+    for (int k = 0; k < n; ++k) {  // right-looking Cholesky, lower triangle in place
+        const double d = A[k * ld + k];
+        if (!(d > 0.0) || !isfinite(d)) { if (tid == 0) bad = 1; break; }  // same value in every thread: uniform exit
+        const double ljj = sqrt(d);
+        __syncthreads();
+        for (int i = k + tid; i < n; i += DN_THREADS) A[i * ld + k] = (i == k) ? ljj : A[i * ld + k] / ljj;
+        __syncthreads();
+        const int m = n - k - 1;  // trailing block: entries (i, j), k < j <= i < n
+        for (int l = tid; l < m * m; l += DN_THREADS) {
+            const int i = k + 1 + l / m, j = k + 1 + (l - (l / m) * m);
+            if (j <= i) A[i * ld + j] -= A[i * ld + k] * A[j * ld + k];
+        }
+        __syncthreads();
+    }
+    __syncthreads();
+    if (!bad) {
+        for (int k = 0; k < n; ++k) {  // L y = b
+            if (tid == 0) y[k] /= A[k * ld + k];
+            __syncthreads();
+            const double yk = y[k];
+            for (int i = k + 1 + tid; i < n; i += DN_THREADS) y[i] -= A[i * ld + k] * yk;
+            __syncthreads();
+        }
+        for (int k = n - 1; k >= 0; --k) {  // L^T x = y
+            if (tid == 0) y[k] /= A[k * ld + k];
+            __syncthreads();
+            const double xk = y[k];
+            for (int i = tid; i < k; i += DN_THREADS) y[i] -= A[k * ld + i] * xk;
+            __syncthreads();
+        }
+    }
+    // a pivot that is not positive (cannot happen for a damped Schur complement in exact arithmetic) leaves x = 0: the points
+    // alone move, the model decrease stays exact, LM carries on
+    for (int l = tid; l < n; l += DN_THREADS) {
+        const double x = bad ? 0.0 : y[l];
+        P.v_x[l] = isfinite(x) ? x : 0.0;
+        P.v_r[l] = 0.0;  // PCG residual of the step: exact
+    }
+    if (tid == 0) {
+        st->pcg_iter = 0;
+        st->pcg_done = 1;
+        if (n_solves) *n_solves += bad ? 0 : 1;
+    }
+}
+
+}  // namespace ba

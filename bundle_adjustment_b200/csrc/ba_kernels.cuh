@@ -154,6 +154,8 @@ struct Params {
     const int* pm_tc;         // [n_obs] point-major index -> tile-camera index
     double2* tc_J;            // [2][3][n_obs] Jacobian cache W^1/2 Jp of the linearisation at parameter buffer b:
                               // planes (jx0, jx1), (jx2, jy0), (jy1, jy2), tile-camera order
+    double2* tc_r;            // [2][n_obs] rho = W^-1/2 w_g r of the same linearisation (tile-camera order); only allocated for small
+                              // problems (dense reduced system, ba_dense.cuh), nullptr otherwise
     const int* seg_cam;       // [n_seg]
     const int* seg_info;      // [n_seg] first tile-camera position inside the tile | length << 16 (longest first per tile)
     const int* seg_row;       // [n_seg] row slot of a segment (camera-major); accumulator slot inside its epoch when ep_target > 0

@@ -9,6 +9,7 @@
 #include "ba_kernels.cuh"
 #include "ba_tiles.cuh"
 #include "ba_peer.cuh"
+#include "ba_dense.cuh"
 #include "ba_host_math.h"
 #include "ba_triangulate.cuh"
 
@@ -163,13 +164,13 @@ struct TBuf {
 enum Kind {
     KN_SETUP = 0, KN_CAM_PREP, KN_RESID, KN_JAC, KN_LIN_PTS, KN_PT_PREP, KN_PT_PASS, KN_BACKSUB, KN_LIN_CAM,
     KN_SCHUR_CAM, KN_MATVEC_CAM, KN_CAM_SUM, KN_CAM_FIN, KN_PCG_DOTS, KN_PCG_UPDATE, KN_CAM_UPDATE, KN_REDUCE,
-    KN_GRAD, KN_DECIDE, KN_TILE_MV, KN_TILE_BACKSUB, KN_ROWS_FIN, KN_ROWS_XCHG, KN_DOTS_PEER, KN_PCG_TAIL, KN_ALLREDUCE, KN_COUNT
+    KN_GRAD, KN_DECIDE, KN_TILE_MV, KN_TILE_BACKSUB, KN_ROWS_FIN, KN_ROWS_XCHG, KN_DOTS_PEER, KN_PCG_TAIL, KN_ALLREDUCE, KN_DENSE, KN_COUNT
 };
 static const char* kKindNames[KN_COUNT] = {
     "setup", "cam_prepare", "residuals", "jacobian_blocks", "lin_points", "point_prepare", "schur_matvec_points",
     "backsub_points", "lin_cameras", "schur_rhs_cameras", "schur_matvec_cameras", "camera_sum", "camera_finish",
     "pcg_dots", "pcg_update", "camera_update", "reduce_scalars", "gradient_check", "lm_decide",
-    "schur_matvec_tiles", "backsub_tiles", "rows_finish", "rows_finish_xchg", "pcg_dots_peer", "pcg_tail", "peer_allreduce"};
+    "schur_matvec_tiles", "backsub_tiles", "rows_finish", "rows_finish_xchg", "pcg_dots_peer", "pcg_tail", "peer_allreduce", "dense_schur"};
 
 // ---------------------------------------------------------------------------------------------
 // setup kernels (device-side construction of the two observation orders)
@@ -426,6 +427,13 @@ struct ba_handle {
     int coarse_agg = 32, coarse_nz = 0;
     int coarse_colours = 0, coarse_graph_agg = 0;  // colouring of the aggregate graph of the uploaded problem (0: not built)
     bool coarse_ready = false;
+    // dense reduced system of small problems (ba_dense.cuh)
+    bool dense_ok = false;
+    int dn_pairs_n = 0;
+    DBuf<int4> dn_pairs;
+    DBuf<int> dn_off, dn_count;   // dn_count: [0] successful factorisations of the last solve, [1] ticket
+    DBuf<double> dn_S, dn_extra;
+    DBuf<double2> tc_r;
     int xcap = 0;
     int ar_cap = 0;        // capacity (doubles) of the LL all-reduce region behind the tail's slots; 0 = NCCL only
     size_t ar_base = 0;    // its offset in xbuf (doubles)
@@ -897,6 +905,54 @@ static void setup_peer_exchange(ba_handle* h, int n_cams) {
     CK(cudaStreamSynchronize(s));
 }
 
+// Pair lists of the dense reduced system (ba_dense.cuh): only for single-GPU problems with at most DN_MAX_CAMS adjustable cameras
+// and a tile layout (the Jacobian cache is indexed in tile-camera order).
+static void build_dense_pairs(ba_handle* h) {
+    const Params& P = h->P;
+    h->dense_ok = false;
+    h->dn_pairs_n = 0;
+    h->P.tc_r = nullptr;
+    if (h->nranks != 1 || !h->fused_ok || !h->tile_lin || P.n_cams < 1 || P.n_cams > DN_MAX_CAMS || P.n_obs > DN_MAX_OBS || getenv("BA_B200_NO_DENSE")) return;
+    cudaStream_t s = h->stream;
+    ScratchScope scratch(s);
+    const int B = 256, n = P.n_obs, nb = P.n_cams * P.n_cams;
+    TBuf<int> cnt, off;
+    cnt.alloc((size_t)n + 1); off.alloc((size_t)n + 1);
+    launch(h, KN_SETUP, k_dn_pair_count, cdiv(n + 1, B), B, 0, n, P.n_cams, P.pm_idx, P.pt_off, cnt.p);
+    size_t tb = 0, tb2 = 0;
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt.p, off.p, n + 1, s));
+    TBuf<unsigned char> tmp;
+    tmp.alloc(tb);
+    CK(cub::DeviceScan::ExclusiveSum(tmp.p, tb, cnt.p, off.p, n + 1, s));
+    int total = 0;
+    CK(cudaMemcpyAsync(&total, off.p + n, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    if (total <= 0 || total > DN_MAX_PAIRS) return;
+    TBuf<unsigned> key, key_s;
+    TBuf<int> idx, idx_s;
+    TBuf<int4> raw;
+    key.alloc(total); key_s.alloc(total); idx.alloc(total); idx_s.alloc(total); raw.alloc(total);
+    launch(h, KN_SETUP, k_dn_pair_fill, cdiv(n, B), B, 0, n, P.n_cams, P.pm_idx, P.pt_off, P.pm_tc, (const int*)off.p, key.p, idx.p, raw.p);
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, tb2, key.p, key_s.p, idx.p, idx_s.p, total, 0, 8, s));
+    TBuf<unsigned char> tmp2;
+    tmp2.alloc(tb2);
+    CK(cub::DeviceRadixSort::SortPairs(tmp2.p, tb2, key.p, key_s.p, idx.p, idx_s.p, total, 0, 8, s));  // stable: point order inside a bin
+    h->dn_pairs.alloc(total); h->dn_off.alloc((size_t)nb + 1); h->dn_S.alloc((size_t)nb * 36); h->dn_count.alloc(2);
+    h->dn_extra.alloc((size_t)P.n_cams * DN_EXTRA); h->tc_r.alloc(2 * (size_t)n);
+    h->dn_count.zero(s);
+    launch(h, KN_SETUP, k_dn_pair_gather, cdiv(total, B), B, 0, total, (const int*)idx_s.p, (const int4*)raw.p, h->dn_pairs.p);
+    launch(h, KN_SETUP, k_lower_bound_u32, cdiv(nb + 1, B), B, 0, total, (const unsigned*)key_s.p, nb + 1, h->dn_off.p);
+    if (cudaFuncSetAttribute(k_dense_schur, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dn_solve_smem(P.n_cams)) != cudaSuccess) {
+        cudaGetLastError();
+        CK(cudaStreamSynchronize(s));
+        return;
+    }
+    CK(cudaStreamSynchronize(s));  // scratch dies here
+    h->dn_pairs_n = total;
+    h->dense_ok = true;
+    h->P.tc_r = h->tc_r.p;  // from now on the tile linearisation also stores the weighted residuals
+}
+
 // Distributed handles: a validation error on ONE rank must fail the call on ALL ranks, or the others block forever in the next
 // collective.  Every rank contributes its error code (0 = fine) to one all-reduce (max); a rank that is fine itself reports
 // that another rank failed.  Single-GPU handles: fails at once.
@@ -1174,6 +1230,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     h->st.zero(s);
     CK(cudaStreamSynchronize(s));  // the sort scratch buffers die at scope exit
     setup_peer_exchange(h, n_cams);
+    build_dense_pairs(h);
     tm.mark("finish");
     h->have_problem = true;
 }
@@ -1279,7 +1336,9 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     for (int k = 0; k < KN_COUNT; ++k) { h->launches[k] = 0; h->kernel_ms[k] = 0.0; }
     h->time_kernels = opt->verbose >= 2;
     const int check_every = std::max(1, opt->pcg_check_every);
-    const int with_schur = opt->precond >= BA_PRECOND_SCHUR_JACOBI ? 1 : 0;
+    // small problems: explicit reduced system + dense Cholesky instead of PCG (ba_dense.cuh); no preconditioner needed then
+    const bool dense = h->dense_ok && opt->dense_schur != 0 && opt->schur_path == BA_PATH_TILES && h->nranks == 1 && h->P.n_cams > 0;
+    const int with_schur = (opt->precond >= BA_PRECOND_SCHUR_JACOBI && !dense) ? 1 : 0;
     if (opt->precond < BA_PRECOND_JACOBI || opt->precond > BA_PRECOND_AUTO) fail(BA_ERR_ARG, "unknown preconditioner %d", opt->precond);
     const int nc1 = P.n_cams + 1;
     if (opt->schur_path < BA_PATH_TILES || opt->schur_path > BA_PATH_TILES_ROWS) fail(BA_ERR_ARG, "unknown schur_path %d", opt->schur_path);
@@ -1314,7 +1373,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     //      has needed more than 15 iterations (the damping has reached its floor by then and S changes little), inverted on the
     //      device and kept; it is rebuilt when the iteration count climbs past 30 again.
     const bool want_two_level = opt->precond == BA_PRECOND_TWO_LEVEL || (opt->precond == BA_PRECOND_AUTO && P.n_cams >= 128);
-    bool two_level = want_two_level && tiles && tail && P.n_cams > 0;
+    bool two_level = want_two_level && tiles && tail && P.n_cams > 0 && !dense;
     h->coarse_ready = false;
     int coarse_builds = 0, coarse_matvecs = 0, coarse_built_at = -1000;
     // 24: Schur-Jacobi has to be struggling.  On the 50 M-observation problem (10 k cameras) it never needs more than 18 iterations and a
@@ -1509,6 +1568,12 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
         }
         launch(h, KN_PCG_UPDATE, k_pcg_update, P.vec_ctas, VEC_THREADS, 0, P, opt->pcg_tol, opt->pcg_max_iters, n_dots, h->ticket.p);
     };
+    auto dense_solve = [&]() {  // the whole camera side of an LM iteration: bins, gradient, S, Cholesky, exact step
+        launch(h, KN_PT_PREP, k_point_prepare, cdiv(P.n_pts, 256), 256, 0, P, kDiagMin, kDiagMax);
+        launch(h, KN_DENSE, k_dense_schur, P.n_cams * P.n_cams, DN_THREADS, dn_solve_smem(P.n_cams), P, (const int4*)h->dn_pairs.p,
+               (const int*)h->dn_off.p, h->dn_S.p, h->dn_extra.p, h->dn_count.p + 1, h->dn_count.p, kDiagMin, kDiagMax, opt->gtol);
+    };
+    if (dense) CK(cudaMemsetAsync(h->dn_count.p, 0, sizeof(int), s));
     auto after_pcg = [&]() {
         if (tiles)
             launch(h, KN_TILE_BACKSUB, k_tile_pass<1>, h->ft_grid, FT_THREADS, ft_smem_bytes(FT_ROWS_MV), P, (const double*)h->v_x.p);
@@ -1530,7 +1595,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     //      (window: 13.3 -> 12.5 ms, 100 k observations: 17.0 -> 16.4 ms; 680 k: 84.7 -> 89.5 ms, 5 M: 337 -> 345 ms).
     //      device_loop = 1 therefore means "up to kDeviceLoopMaxObs observations", 2 = always.
     const bool device_loop = status == 0 && (opt->device_loop == 2 || (opt->device_loop == 1 && P.n_obs <= kDeviceLoopMaxObs)) &&
-                             h->nranks == 1 && tiles && tail && P.n_cams > 0 && !h->time_kernels && !(opt->verbose & 1) &&
+                             h->nranks == 1 && tiles && (tail || dense) && P.n_cams > 0 && !h->time_kernels && !(opt->verbose & 1) &&
                              !two_level && !getenv("BA_B200_HOST_LOOP");
     if (device_loop) {
         long long before[KN_COUNT], per_lm[KN_COUNT], per_pcg[KN_COUNT];
@@ -1547,9 +1612,18 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
             cudaGraphNode_t lm_node = nullptr;
             CK(cudaGraphAddNode(&lm_node, g, nullptr, 0, &np));
             cudaGraph_t lm_body = np.conditional.phGraph_out[0];
+            h->P.lin_gate = 1;  // the linearisation kernels are always in the graph and return at once after a rejected step
+            if (dense) {
+                // no inner loop: linearisation, pair bins, Cholesky, back-substitution and decision are one straight body
+                lm_loop = (unsigned long long)hl; pcg_loop = 0;
+                CK(cudaStreamBeginCaptureToGraph(s, lm_body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
+                dense_solve();
+                after_pcg();
+                CK(cudaStreamEndCapture(s, nullptr));
+                for (int k = 0; k < KN_COUNT; ++k) { per_lm[k] = h->launches[k] - before[k]; per_pcg[k] = 0; }
+            } else {
             CK(cudaGraphConditionalHandleCreate(&hp, lm_body, 0, 0));
             lm_loop = (unsigned long long)hl; pcg_loop = (unsigned long long)hp;
-            h->P.lin_gate = 1;  // the linearisation kernels are always in the graph and return at once after a rejected step
             // first part of the body; the PCG loop hangs off its last node
             CK(cudaStreamBeginCaptureToGraph(s, lm_body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
             before_pcg(true);
@@ -1574,6 +1648,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
             after_pcg();
             CK(cudaStreamEndCapture(s, nullptr));
             for (int k = 0; k < KN_COUNT; ++k) per_lm[k] = h->launches[k] - before[k] - per_pcg[k];
+            }
             h->P.lin_gate = 0;
             lm_loop = pcg_loop = 0;
             CK(cudaGraphInstantiate(&gx, g, 0));
@@ -1597,6 +1672,9 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
         for (int k = 0; k < KN_COUNT; ++k) h->launches[k] = before[k] + per_lm[k] * passes + per_pcg[k] * st.pcg_total;
     }
     while (status == 0) {
+        if (dense) {
+            dense_solve();
+        } else {
         before_pcg(need_lin);
         if (P.n_cams > 0) {
             auto pcg_converged = [&]() {
@@ -1629,6 +1707,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
                     if ((it + 1) % check_every == 0 && it + 1 < opt->pcg_max_iters && pcg_converged()) break;
                 }
             }
+        }
         }
         after_pcg();
         read_state(h);
@@ -1680,6 +1759,10 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
         out->precond_used = coarse_builds > 0 && !coarse_failed ? BA_PRECOND_TWO_LEVEL : with_schur ? BA_PRECOND_SCHUR_JACOBI : BA_PRECOND_JACOBI;
         out->coarse_builds = coarse_builds; out->coarse_matvecs = coarse_matvecs;
         out->coarse_unknowns = coarse_builds > 0 ? h->coarse_nz : 0;
+        if (dense) {
+            CK(cudaMemcpyAsync(&out->dense_solves, h->dn_count.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+            CK(cudaStreamSynchronize(s));
+        }
     }
 }
 
@@ -1719,6 +1802,7 @@ void ba_default_options(ba_options* o) {
     o->pcg_tail = 1;
     o->device_loop = 1;
     o->point_linesearch = 1;
+    o->dense_schur = 1;
 }
 
 int ba_create(int device, ba_handle** out) {

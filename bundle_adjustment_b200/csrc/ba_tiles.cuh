@@ -594,6 +594,7 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_lin(Params 
             dst[4 * FT_LDL] = bx * o.jx[2] + by * o.jy[2];
             dst[5 * FT_LDL] = cx * o.jx[2] + cy * o.jy[2];
             const double gx = wgx * o.rx, gy = wgy * o.ry;
+            if (P.tc_r) P.tc_r[(size_t)b * P.n_obs + o0 + tid] = make_double2(gx / sx, gy / sy);
             dst[6 * FT_LDL] = o.jx[0] * gx + o.jy[0] * gy;
             dst[7 * FT_LDL] = o.jx[1] * gx + o.jy[1] * gy;
             dst[8 * FT_LDL] = o.jx[2] * gx + o.jy[2] * gy;

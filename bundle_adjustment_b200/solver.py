@@ -28,7 +28,7 @@ def make_options(**kw) -> api.Options:
             v = api.PRECOND[v]
         if k == "schur_path" and isinstance(v, str):
             v = api.SCHUR_PATH[v]
-        if not hasattr(o, k) or k == "reserved":
+        if not hasattr(o, k) or k.startswith("reserved"):
             raise TypeError(f"unknown solver option {k!r}")
         setattr(o, k, v)
     return o

@@ -180,7 +180,7 @@ def test_fused_tiles_match_two_pass(gpu_solver, shape, seed):
     """The fused point-tile mat-vec / back-substitution and the two-pass kernels are the same arithmetic
     in a different summation order: identical LM trajectories to rounding."""
     fp = S.make_flat_problem(*shape, seed=seed)
-    kw = dict(max_iters=5, pcg_tol=1e-10, pcg_max_iters=300, ftol=0.0, xtol=0.0, gtol=0.0)
+    kw = dict(max_iters=5, pcg_tol=1e-10, pcg_max_iters=300, ftol=0.0, xtol=0.0, gtol=0.0, dense_schur=0)   # the PCG kernels
     out = {}
     for path in ("tiles", "tiles_rows", "two_pass", "tiles/kernels"):
         gpu_solver.set_flat(fp)
@@ -557,6 +557,50 @@ def test_default_solve_stops_on_the_reference_tolerances(gpu_solver):
     assert st["iterations"] <= 50
     assert st["final_cost"] <= float(g["res_cost"])
 
+
+
+# ------------------------------------------------------------------------------------------------
+# small problems: explicit reduced system + dense Cholesky (csrc/ba_dense.cuh)
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("shape,seed", [((5, 1400, 3000), 4), ((9, 600, 2400), 12), ((17, 900, 5000), 13)])
+def test_dense_schur_path_takes_exact_steps(gpu_solver, shape, seed):
+    """Up to 16 adjustable cameras: the LM step comes from the explicitly assembled Schur complement and a Cholesky
+    factorisation.  Exact steps -> the iterates of the CPU restatement with exact solves (oracle/lm_schur.py::solve, line search
+    included), and of the PCG path run to 1e-12; identical bits whether the host or the device drives the loop."""
+    fp = S.make_flat_problem(*shape, seed=seed)
+    prob = O.Problem.from_flat(fp)
+    kw = dict(max_iters=6, ftol=0.0, xtol=0.0, gtol=0.0, lambda_min=1e-12)
+    gpu_solver.set_flat(fp)
+    st = gpu_solver.solve(**kw)
+    x = gpu_solver.get_x()
+    assert st["dense_solves"] == st["iterations"] == 6 and st["pcg_iterations"] == 0
+    ks = gpu_solver.kernel_stats()
+    assert ks["dense_schur"][0] == st["iterations"] and ks["schur_matvec_tiles"][0] == 0 and ks["lin_cameras"][0] == 0
+    ref = L.solve(prob, fp.rvec, fp.tvec, fp.pts, max_iters=6, ftol=0.0, gtol=0.0)
+    assert abs(st["final_cost"] - ref.cost) <= 1e-9 * ref.cost, (st["final_cost"], ref.cost)
+    assert np.abs(x - ref.x()).max() <= 1e-7 * np.abs(ref.x()).max()
+    gpu_solver.restore_initial()
+    st_p = gpu_solver.solve(dense_schur=0, pcg_tol=1e-12, pcg_max_iters=600, **kw)
+    assert st_p["dense_solves"] == 0 and st_p["pcg_iterations"] > 0
+    assert abs(st_p["final_cost"] - st["final_cost"]) <= 1e-9 * st["final_cost"]
+    for mode in (0, 2):
+        gpu_solver.restore_initial()
+        st_m = gpu_solver.solve(device_loop=mode, **kw)
+        assert st_m["final_cost"] == st["final_cost"] and np.array_equal(gpu_solver.get_x(), x), mode
+
+
+def test_dense_schur_path_on_the_pipeline_window(gpu_solver):
+    """The reference pipeline's window (golden window_cfg1: 4 adjustable keyframes): default solve = dense path, ends on a
+    tolerance in fewer LM iterations than the inexact PCG steps need, at a cost no higher."""
+    g, spec, flat, prob = _golden_problem("window_cfg1")
+    _upload(gpu_solver, prob, flat)
+    st = gpu_solver.solve()
+    assert st["dense_solves"] == st["iterations"] and st["status"] in (2, 3, 4)
+    _upload(gpu_solver, prob, flat)
+    st_p = gpu_solver.solve(dense_schur=0)
+    assert st["iterations"] <= st_p["iterations"]
+    assert st["final_cost"] <= st_p["final_cost"] * (1 + 1e-4)
+    assert st["final_cost"] <= float(g["res_cost"])
 
 
 # ------------------------------------------------------------------------------------------------

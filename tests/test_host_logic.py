@@ -67,7 +67,7 @@ def test_struct_layout_against_the_compiled_header(tmp_path):
             assert int(out[f"{st}.{n}"]) == getattr(cls, n).offset, (st, n)
     o = _capi.Options()
     _capi.lib().ba_default_options(ctypes.byref(o))
-    assert o.pcg_tail == 1 and o.device_loop == 1 and o.coarse_aggregate == 0 and o.coarse_after == 0 and o.point_linesearch == 1 and list(o.reserved) == [0]
+    assert o.pcg_tail == 1 and o.device_loop == 1 and o.coarse_aggregate == 0 and o.coarse_after == 0 and o.point_linesearch == 1 and o.dense_schur == 1
 
 
 def test_run_host_path_with_a_stub_solver():
