@@ -65,23 +65,67 @@ __global__ void k_dn_pair_gather(int n, const int* __restrict__ perm, const int4
 // That replaces the two camera-major passes, their tile sums and finish kernels.  The CTA that finishes LAST (integer ticket;
 // what it computes does not depend on which one it is) assembles S + lambda D, factorises it (Cholesky in shared memory),
 // solves S x = E h - g_c, and writes x, g_c, D_c, the gradient test.  Fixed summation order everywhere: bit-reproducible.
+constexpr int DN_MAX_SPLIT = 8;  // CTAs that share a bin
 constexpr int DN_EXTRA = 18;  // per camera: diag(U) 6, g_c 6, E h 6
 
 __host__ __device__ inline size_t dn_solve_smem(int n_cams) {
     const size_t n = 6 * (size_t)n_cams;
-    return (n * (n + 1) + 2 * n) * sizeof(double);
+    return (n * (n + 1) + 4 * n) * sizeof(double);
+}
+
+template <bool WARP>
+BA_D void dn_sync() {
+    if (WARP) __syncwarp(); else __syncthreads();
+}
+// A (n x n, leading dimension ld, lower triangle) = L L^T in place (the diagonal ends up holding 1 / L_kk, so that the two
+// triangular solves multiply instead of divide), then y <- A^-1 y, by a group of nt threads (t = index in the
+// group): one warp (WARP) or the whole CTA.  Returns true - in every thread of the group - when a pivot is not positive.
+template <bool WARP>
+BA_D bool dn_cholesky_solve(double* A, double* y, int n, int ld, int t, int nt) {
+    for (int k = 0; k < n; ++k) {  // right-looking Cholesky
+        const double d = A[k * ld + k];
+        if (!(d > 0.0) || !isfinite(d)) return true;  // same value in every thread: uniform exit
+        const double ljj = sqrt(d), ilj = 1.0 / ljj;
+        dn_sync<WARP>();
+        for (int i = k + t; i < n; i += nt) A[i * ld + k] = (i == k) ? ilj : A[i * ld + k] * ilj;  // the diagonal holds 1 / L_kk
+        dn_sync<WARP>();
+        const int m = n - k - 1;  // trailing block: entries (i, j), k < j <= i < n
+        for (int l = t; l < m * m; l += nt) {
+            const int q = l / m;
+            const int i = k + 1 + q, j = k + 1 + (l - q * m);
+            if (j <= i) A[i * ld + j] -= A[i * ld + k] * A[j * ld + k];
+        }
+        dn_sync<WARP>();
+    }
+    for (int k = 0; k < n; ++k) {  // L y = b
+        const double yk = y[k] * A[k * ld + k];  // every thread computes the same value
+        dn_sync<WARP>();
+        if (t == 0) y[k] = yk;
+        for (int i = k + 1 + t; i < n; i += nt) y[i] -= A[i * ld + k] * yk;
+        dn_sync<WARP>();
+    }
+    for (int k = n - 1; k >= 0; --k) {  // L^T x = y
+        const double xk = y[k] * A[k * ld + k];
+        dn_sync<WARP>();
+        if (t == 0) y[k] = xk;
+        for (int i = t; i < k; i += nt) y[i] -= A[k * ld + i] * xk;
+        dn_sync<WARP>();
+    }
+    return false;
 }
 
 __global__ void __launch_bounds__(DN_THREADS) k_dense_schur(Params P, const int4* __restrict__ pairs, const int* __restrict__ bin_off,
                                                             double* __restrict__ S_bins, double* __restrict__ extra,
                                                             int* __restrict__ ticket, int* __restrict__ n_solves, double dmin,
-                                                            double dmax, double gtol) {
+                                                            double dmax, double gtol, int split) {
     extern __shared__ __align__(16) double dsm[];
     __shared__ double red[DN_THREADS / 32 * (36 + DN_EXTRA)];
     __shared__ double tot[36 + DN_EXTRA];
     __shared__ int last, bad;
     const int tid = threadIdx.x;
-    const int nc = P.n_cams, bin = blockIdx.x;
+    // `split` CTAs share a bin (contiguous parts of its pair list): a window has 16 bins of a few thousand pairs, and one CTA
+    // per bin would walk them in a dozen dependent-load round trips; the last CTA adds the parts in order
+    const int nc = P.n_cams, bin = blockIdx.x / split, part = blockIdx.x - bin * split;
     const int ci = bin / nc, cj = bin - ci * nc;
     const bool diag = ci == cj;
     const int b = P.st->cur;
@@ -90,7 +134,8 @@ __global__ void __launch_bounds__(DN_THREADS) k_dense_schur(Params P, const int4
     double acc[36 + DN_EXTRA];
 #pragma unroll
     for (int k = 0; k < 36 + DN_EXTRA; ++k) acc[k] = 0.0;
-    const int k0 = __ldg(bin_off + bin), k1 = __ldg(bin_off + bin + 1);
+    const int b0_ = __ldg(bin_off + bin), b1_ = __ldg(bin_off + bin + 1);
+    const int k0 = b0_ + (int)((long long)(b1_ - b0_) * part / split), k1 = b0_ + (int)((long long)(b1_ - b0_) * (part + 1) / split);
     for (int k = k0 + tid; k < k1; k += DN_THREADS) {
         const int4 pr = __ldg(pairs + k);
         double X[3], Vi[6];
@@ -137,8 +182,8 @@ __global__ void __launch_bounds__(DN_THREADS) k_dense_schur(Params P, const int4
     }
     block_sum<36 + DN_EXTRA, DN_THREADS>(acc, red, tot);
     __syncthreads();
-    if (tid < 36) S_bins[(size_t)bin * 36 + tid] = tot[tid];
-    if (diag && tid < DN_EXTRA) extra[(size_t)ci * DN_EXTRA + tid] = tot[36 + tid];
+    if (tid < 36) S_bins[((size_t)bin * split + part) * 36 + tid] = tot[tid];
+    if (diag && tid < DN_EXTRA) extra[((size_t)ci * split + part) * DN_EXTRA + tid] = tot[36 + tid];
     __threadfence();
     __syncthreads();
     if (tid == 0) last = (atomicAdd(ticket, 1) == (int)gridDim.x - 1);
@@ -151,14 +196,20 @@ __global__ void __launch_bounds__(DN_THREADS) k_dense_schur(Params P, const int4
     double* A = dsm;                       // [n][ld], lower triangle
     double* y = dsm + (size_t)n * ld;      // [n] right-hand side -> solution
     double* D = y + n;                     // [n]
+    double* G = D + n;                     // [n] gradient
     LMState* st = P.st;
     const double lam = st->lambda;
     if (tid == 0) { bad = 0; *ticket = 0; }
     for (int l = tid; l < n; l += DN_THREADS) {
         const int c = l / 6, a = l - 6 * c;
-        const double* e = extra + (size_t)c * DN_EXTRA;
-        const double d = fmin(fmax(__ldcg(e + a), dmin), dmax), g = __ldcg(e + 6 + a), eh = __ldcg(e + 12 + a);
+        double du = 0.0, g = 0.0, eh = 0.0;
+        for (int sp = 0; sp < split; ++sp) {  // the parts in order
+            const double* e = extra + ((size_t)c * split + sp) * DN_EXTRA;
+            du += __ldcg(e + a); g += __ldcg(e + 6 + a); eh += __ldcg(e + 12 + a);
+        }
+        const double d = fmin(fmax(du, dmin), dmax);
         D[l] = d;
+        G[l] = g;
         y[l] = eh - g;
         P.cam_D[l] = d; P.cam_g[l] = g; P.v_b[l] = eh - g;
     }
@@ -167,49 +218,31 @@ __global__ void __launch_bounds__(DN_THREADS) k_dense_schur(Params P, const int4
         const int r = l / n, c = l - r * n;
         if (c > r) continue;
         const int cr = r / 6, a = r - 6 * cr, cc = c / 6, q = c - 6 * cc;
-        double v = __ldcg(S_bins + (size_t)(cr * nc + cc) * 36 + 6 * a + q);
+        const double* src = S_bins + (size_t)(cr * nc + cc) * split * 36 + 6 * a + q;
+        double part[DN_MAX_SPLIT];  // all loads in flight, then the adds in order
+#pragma unroll
+        for (int sp = 0; sp < DN_MAX_SPLIT; ++sp) part[sp] = sp < split ? __ldcg(src + sp * 36) : 0.0;
+        double v = 0.0;
+#pragma unroll
+        for (int sp = 0; sp < DN_MAX_SPLIT; ++sp) v += part[sp];
         if (r == c) v += lam * D[r];
         A[r * ld + c] = v;
     }
     // gradient test at the current point (skipped after a rejected step: the point and its gradient are unchanged)
     if (tid == 0 && !lin_gated(st)) {
         double m = st->scal[S_GPMAX];
-        for (int l = 0; l < n; ++l) m = fmax(m, fabs(P.cam_g[l]));
+        for (int l = 0; l < n; ++l) m = fmax(m, fabs(G[l]));
         st->gmax = m;
         if (st->status == 0 && m < gtol) st->status = 1;
     }
     __syncthreads();
-    for (int k = 0; k < n; ++k) {  // right-looking Cholesky, lower triangle in place
-        const double d = A[k * ld + k];
-        if (!(d > 0.0) || !isfinite(d)) { if (tid == 0) bad = 1; break; }  // same value in every thread: uniform exit
-        const double ljj = sqrt(d);
-        __syncthreads();
-        for (int i = k + tid; i < n; i += DN_THREADS) A[i * ld + k] = (i == k) ? ljj : A[i * ld + k] / ljj;
-        __syncthreads();
-        const int m = n - k - 1;  // trailing block: entries (i, j), k < j <= i < n
-        for (int l = tid; l < m * m; l += DN_THREADS) {
-            const int i = k + 1 + l / m, j = k + 1 + (l - (l / m) * m);
-            if (j <= i) A[i * ld + j] -= A[i * ld + k] * A[j * ld + k];
-        }
-        __syncthreads();
+    {
+        // (one warp with __syncwarp between the steps was tried for n <= 48: slower - the trailing update of a step is a few
+        // hundred entries, worth the CTA barrier)
+        const bool b0 = dn_cholesky_solve<false>(A, y, n, ld, tid, DN_THREADS);
+        if (tid == 0) bad = b0 ? 1 : 0;
     }
     __syncthreads();
-    if (!bad) {
-        for (int k = 0; k < n; ++k) {  // L y = b
-            if (tid == 0) y[k] /= A[k * ld + k];
-            __syncthreads();
-            const double yk = y[k];
-            for (int i = k + 1 + tid; i < n; i += DN_THREADS) y[i] -= A[i * ld + k] * yk;
-            __syncthreads();
-        }
-        for (int k = n - 1; k >= 0; --k) {  // L^T x = y
-            if (tid == 0) y[k] /= A[k * ld + k];
-            __syncthreads();
-            const double xk = y[k];
-            for (int i = tid; i < k; i += DN_THREADS) y[i] -= A[k * ld + i] * xk;
-            __syncthreads();
-        }
-    }
     // a pivot that is not positive (cannot happen for a damped Schur complement in exact arithmetic) leaves x = 0: the points
     // alone move, the model decrease stays exact, LM carries on
     for (int l = tid; l < n; l += DN_THREADS) {
@@ -222,6 +255,8 @@ __global__ void __launch_bounds__(DN_THREADS) k_dense_schur(Params P, const int4
         st->pcg_done = 1;
         if (n_solves) *n_solves += bad ? 0 : 1;
     }
+    __syncthreads();  // x, g_c, D_c are in place (this CTA wrote them): the trial poses and the step's camera-side scalars
+    for (int c = tid; c <= nc; c += DN_THREADS) camera_update_one(P, c);
 }
 
 }  // namespace ba

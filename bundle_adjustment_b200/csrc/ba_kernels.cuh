@@ -475,9 +475,7 @@ __global__ void __launch_bounds__(PM_THREADS) k_lin_points(Params P, int which) 
 }
 
 // K-PTPREP: V_d = V + lambda D_p, D_p = clamp(diag V); Vinv = V_d^-1; h = Vinv g_p.
-__global__ void k_point_prepare(Params P, double dmin, double dmax) {
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= P.n_pts) return;
+BA_D void point_prepare_one(const Params& P, int p, double dmin, double dmax) {
     const int b = P.st->cur;
     const double lam = P.st->lambda;
     double V[6], g[3];
@@ -495,6 +493,10 @@ __global__ void k_point_prepare(Params P, double dmin, double dmax) {
     vo[0] = make_double2(Vi[0], Vi[1]); vo[1] = make_double2(Vi[2], Vi[3]); vo[2] = make_double2(Vi[4], Vi[5]);
     store_v3(P.pt_h + (size_t)p * 4, h[0], h[1], h[2]);
     store_v3(P.pt_D + (size_t)p * 4, d0, d1, d2);
+}
+__global__ void k_point_prepare(Params P, double dmin, double dmax) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < P.n_pts) point_prepare_one(P, p, dmin, dmax);
 }
 
 // K-P1 (MODE 0): z_p = Vinv_p * sum_i Jp_i^T W_i Jc_i vec_c         (first half of the Schur mat-vec)
@@ -977,9 +979,7 @@ __global__ void __launch_bounds__(VEC_THREADS) k_pcg_update(Params P, double tol
 }
 
 // Trial camera poses from the PCG solution x: R <- R Exp(w), t <- t + R v; rvec = Log(R).
-__global__ void k_camera_update(Params P) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c > P.n_cams) return;
+BA_D void camera_update_one(const Params& P, int c) {
     const int b = P.st->cur;
     const size_t nc1 = (size_t)P.n_cams + 1;
     const double* rt = P.cam_rt + (size_t)b * nc1 * 6 + (size_t)c * 6;
@@ -1013,6 +1013,10 @@ __global__ void k_camera_update(Params P) {
     }
     out[S_GDC] = gd; out[S_DDC] = dd; out[S_RDC] = rd; out[S_DC2] = d2; out[S_XC2] = x2;
 }
+__global__ void k_camera_update(Params P) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c <= P.n_cams) camera_update_one(P, c);
+}
 
 // ---------------------------------------------------------------------------------------------
 // single-CTA scalar kernels (once per LM iteration)
@@ -1034,79 +1038,10 @@ BA_D double cta_sum_all(double v, double* sm /* >= 33 */) {  // all threads get 
     return sm[32];
 }
 
-// Reduce per-tile / per-camera scalar partials into st->scal (fixed order).  The masks select slots.
-__global__ void __launch_bounds__(RED_THREADS) k_reduce_scalars(Params P, unsigned pm_mask, unsigned cam_mask) {
-    // One thread-block cluster (1..16 CTAs): CTA r takes the row groups r, r + CL, ...; 16 lanes per partial row (one
-    // 128-byte line): thread t owns slot t & 15.  CTA totals meet in CTA 0's shared memory and are added in rank order.
-    static_assert(NSCAL == 16, "row layout");
-    __shared__ double sm[RED_THREADS];
-    __shared__ double part[16 * 16];  // [rank][slot], CTA 0 only
-    cooperative_groups::cluster_group cl = cooperative_groups::this_cluster();
-    const int R = (int)cl.block_rank(), CL = (int)cl.num_blocks();
-    const int s = threadIdx.x & 15, g = threadIdx.x >> 4;
-    constexpr int G = RED_THREADS / 16;
-    const bool pm = (pm_mask >> s) & 1u, cm = (cam_mask >> s) & 1u, is_max = (s == S_GPMAX);
-    double v = 0.0;
-    if (pm) {
-        for (int t = R * G + g; t < P.n_partial_rows; t += CL * G) {
-            const double x = P.pm_partial[(size_t)t * NSCAL + s];
-            v = is_max ? fmax(v, x) : v + x;
-        }
-    }
-    if (cm) {
-        for (int c = R * G + g; c < P.n_cams; c += CL * G) v += P.cam_partial[(size_t)c * NSCAL + s];
-    }
-    sm[g * 16 + s] = v;
-    __syncthreads();
-    if (threadIdx.x < 16) {  // fixed order over the 64 row groups
-        double tot = 0.0;
-        for (int i = 0; i < G; ++i) {
-            const double x = sm[i * 16 + s];
-            tot = is_max ? fmax(tot, x) : tot + x;
-        }
-        cl.map_shared_rank(part, 0)[R * 16 + s] = tot;
-    }
-    cl.sync();
-    if (R == 0 && threadIdx.x < 16 && (pm || cm)) {
-        double tot = 0.0;
-        for (int r = 0; r < CL; ++r) {
-            const double x = part[r * 16 + s];
-            tot = is_max ? fmax(tot, x) : tot + x;
-        }
-        P.st->scal[s] = tot;
-    }
-}
-
-// gmax = max(|g_c|, |g_p|) at the current point; gtol test.
-__global__ void __launch_bounds__(RED_THREADS) k_gradient_check(Params P, double gtol) {
-    __shared__ double sm[32];
-    if (P.lin_gate && lin_gated(P.st)) return;
-    double v = 0.0;
-    for (int i = threadIdx.x; i < P.n_cams * 6; i += RED_THREADS) v = fmax(v, fabs(P.cam_g[i]));
-    v = warp_max(v);
-    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double m = P.st->scal[S_GPMAX];
-        for (int i = 0; i < RED_THREADS / 32; ++i) m = fmax(m, sm[i]);
-        P.st->gmax = m;
-        if (P.st->status == 0 && m < gtol) P.st->status = 1;
-    }
-}
-
-// Record the cost of buffer `which` from st->scal (after k_lin_points + k_reduce_scalars).
-__global__ void k_store_cost(Params P, int which) {
-    LMState* st = P.st;
-    const int b = resolve_buf(st, which);
-    st->cost[b] = st->scal[S_COST];
-    st->raw[b] = st->scal[S_RAW];
-    if (st->scal[S_BAD] > 0.0 || !isfinite(st->scal[S_COST])) st->bad = 1;
-    if (P.trace && st->iter == 0) P.trace[0] = TraceRec{st->cost[b], st->raw[b], 1e-6 * (double)(global_ns() - st->t0), st->lambda, 0, 0};
-}
-
 // Accept / reject the trial point, update the damping (Nielsen), test ftol / xtol.
-__global__ void k_lm_decide(Params P, double ftol, double xtol, double lam_min, double lam_max, int max_iters,
-                            unsigned long long lm_loop) {
+struct DecideArgs { double ftol, xtol, lam_min, lam_max; int max_iters; unsigned long long lm_loop; };
+BA_D void lm_decide_body(const Params& P, double ftol, double xtol, double lam_min, double lam_max, int max_iters,
+                         unsigned long long lm_loop) {
     LMState* st = P.st;
     if (st->status != 0) {  // already terminated (gtol at the current point)
         set_loop(lm_loop, false);
@@ -1154,6 +1089,93 @@ __global__ void k_lm_decide(Params P, double ftol, double xtol, double lam_min, 
     if (P.trace && st->iter < TRACE_CAP)
         P.trace[st->iter] = TraceRec{st->cost[st->cur], st->raw[st->cur], 1e-6 * (double)(global_ns() - st->t0), lambda_used, st->pcg_total, accept ? 1 : 0};
     set_loop(lm_loop, st->status == 0);
+}
+__global__ void k_lm_decide(Params P, double ftol, double xtol, double lam_min, double lam_max, int max_iters,
+                            unsigned long long lm_loop) {
+    lm_decide_body(P, ftol, xtol, lam_min, lam_max, max_iters, lm_loop);
+}
+
+// Reduce per-tile / per-camera scalar partials into st->scal (fixed order).  The masks select slots.
+// decide != 0 (single GPU, end of an LM iteration): thread 0 goes straight on to the accept / reject decision - one launch less.
+// prep != 0 (small problems): once the decision is made the whole cluster prepares the points (V^-1, h, D at the new damping and
+// the new current point) for the next iteration - another launch less.
+__global__ void __launch_bounds__(RED_THREADS) k_reduce_scalars(Params P, unsigned pm_mask, unsigned cam_mask, int decide, DecideArgs da,
+                                                                int prep, double dmin, double dmax) {
+    // One thread-block cluster (1..16 CTAs): CTA r takes the row groups r, r + CL, ...; 16 lanes per partial row (one
+    // 128-byte line): thread t owns slot t & 15.  CTA totals meet in CTA 0's shared memory and are added in rank order.
+    static_assert(NSCAL == 16, "row layout");
+    __shared__ double sm[RED_THREADS];
+    __shared__ double part[16 * 16];  // [rank][slot], CTA 0 only
+    cooperative_groups::cluster_group cl = cooperative_groups::this_cluster();
+    const int R = (int)cl.block_rank(), CL = (int)cl.num_blocks();
+    const int s = threadIdx.x & 15, g = threadIdx.x >> 4;
+    constexpr int G = RED_THREADS / 16;
+    const bool pm = (pm_mask >> s) & 1u, cm = (cam_mask >> s) & 1u, is_max = (s == S_GPMAX);
+    double v = 0.0;
+    if (pm) {
+        for (int t = R * G + g; t < P.n_partial_rows; t += CL * G) {
+            const double x = P.pm_partial[(size_t)t * NSCAL + s];
+            v = is_max ? fmax(v, x) : v + x;
+        }
+    }
+    if (cm) {
+        for (int c = R * G + g; c < P.n_cams; c += CL * G) v += P.cam_partial[(size_t)c * NSCAL + s];
+    }
+    sm[g * 16 + s] = v;
+    __syncthreads();
+    if (threadIdx.x < 16) {  // fixed order over the 64 row groups
+        double tot = 0.0;
+        for (int i = 0; i < G; ++i) {
+            const double x = sm[i * 16 + s];
+            tot = is_max ? fmax(tot, x) : tot + x;
+        }
+        cl.map_shared_rank(part, 0)[R * 16 + s] = tot;
+    }
+    cl.sync();
+    if (R == 0 && threadIdx.x < 16 && (pm || cm)) {
+        double tot = 0.0;
+        for (int r = 0; r < CL; ++r) {
+            const double x = part[r * 16 + s];
+            tot = is_max ? fmax(tot, x) : tot + x;
+        }
+        P.st->scal[s] = tot;
+    }
+    if (decide && R == 0 && threadIdx.x < 32) {
+        __syncwarp();  // the sixteen totals of warp 0 are in place
+        if (threadIdx.x == 0) lm_decide_body(P, da.ftol, da.xtol, da.lam_min, da.lam_max, da.max_iters, da.lm_loop);
+    }
+    if (prep) {
+        __threadfence();
+        cl.sync();  // the decision (current buffer, damping) is visible to the whole cluster
+        for (int p = R * RED_THREADS + threadIdx.x; p < P.n_pts; p += CL * RED_THREADS) point_prepare_one(P, p, dmin, dmax);
+    }
+}
+
+// gmax = max(|g_c|, |g_p|) at the current point; gtol test.
+__global__ void __launch_bounds__(RED_THREADS) k_gradient_check(Params P, double gtol) {
+    __shared__ double sm[32];
+    if (P.lin_gate && lin_gated(P.st)) return;
+    double v = 0.0;
+    for (int i = threadIdx.x; i < P.n_cams * 6; i += RED_THREADS) v = fmax(v, fabs(P.cam_g[i]));
+    v = warp_max(v);
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double m = P.st->scal[S_GPMAX];
+        for (int i = 0; i < RED_THREADS / 32; ++i) m = fmax(m, sm[i]);
+        P.st->gmax = m;
+        if (P.st->status == 0 && m < gtol) P.st->status = 1;
+    }
+}
+
+// Record the cost of buffer `which` from st->scal (after k_lin_points + k_reduce_scalars).
+__global__ void k_store_cost(Params P, int which) {
+    LMState* st = P.st;
+    const int b = resolve_buf(st, which);
+    st->cost[b] = st->scal[S_COST];
+    st->raw[b] = st->scal[S_RAW];
+    if (st->scal[S_BAD] > 0.0 || !isfinite(st->scal[S_COST])) st->bad = 1;
+    if (P.trace && st->iter == 0) P.trace[0] = TraceRec{st->cost[b], st->raw[b], 1e-6 * (double)(global_ns() - st->t0), st->lambda, 0, 0};
 }
 
 }  // namespace ba

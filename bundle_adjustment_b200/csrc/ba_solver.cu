@@ -429,7 +429,7 @@ struct ba_handle {
     bool coarse_ready = false;
     // dense reduced system of small problems (ba_dense.cuh)
     bool dense_ok = false;
-    int dn_pairs_n = 0;
+    int dn_pairs_n = 0, dn_split = 1;
     DBuf<int4> dn_pairs;
     DBuf<int> dn_off, dn_count;   // dn_count: [0] successful factorisations of the last solve, [1] ticket
     DBuf<double> dn_S, dn_extra;
@@ -937,8 +937,10 @@ static void build_dense_pairs(ba_handle* h) {
     TBuf<unsigned char> tmp2;
     tmp2.alloc(tb2);
     CK(cub::DeviceRadixSort::SortPairs(tmp2.p, tb2, key.p, key_s.p, idx.p, idx_s.p, total, 0, 8, s));  // stable: point order inside a bin
-    h->dn_pairs.alloc(total); h->dn_off.alloc((size_t)nb + 1); h->dn_S.alloc((size_t)nb * 36); h->dn_count.alloc(2);
-    h->dn_extra.alloc((size_t)P.n_cams * DN_EXTRA); h->tc_r.alloc(2 * (size_t)n);
+    // CTAs per bin: fill the device (a window has 16 bins), but no part shorter than one trip of a CTA
+    h->dn_split = std::max(1, std::min(std::min(DN_MAX_SPLIT, h->sm_count / nb), cdiv(cdiv(total, nb), DN_THREADS)));
+    h->dn_pairs.alloc(total); h->dn_off.alloc((size_t)nb + 1); h->dn_S.alloc((size_t)nb * h->dn_split * 36); h->dn_count.alloc(2);
+    h->dn_extra.alloc((size_t)P.n_cams * h->dn_split * DN_EXTRA); h->tc_r.alloc(2 * (size_t)n);
     h->dn_count.zero(s);
     launch(h, KN_SETUP, k_dn_pair_gather, cdiv(total, B), B, 0, total, (const int*)idx_s.p, (const int4*)raw.p, h->dn_pairs.p);
     launch(h, KN_SETUP, k_lower_bound_u32, cdiv(nb + 1, B), B, 0, total, (const unsigned*)key_s.p, nb + 1, h->dn_off.p);
@@ -1305,14 +1307,20 @@ static void launch_camera_pass(ba_handle* h, Kind kind, const double* vec, int w
     else launch(h, kind, k_camera_pass<KIND, false>, P.cm_tiles, CM_THREADS, 0, P, vec, with_schur);
 }
 
-static void reduce_scalars(ba_handle* h, unsigned pm_mask, unsigned cam_mask) {
+static const double kDiagMin = 1e-6, kDiagMax = 1e32;
+
+// `decide`: single-GPU solves fold the accept / reject decision into the reduction kernel (returns true if it did)
+static bool reduce_scalars(ba_handle* h, unsigned pm_mask, unsigned cam_mask, const DecideArgs* decide = nullptr, bool prep = false) {
     const Params& P = h->P;
-    launch_cluster(h, KN_REDUCE, k_reduce_scalars, std::max(1, h->red_cluster), RED_THREADS, 0, P, pm_mask, cam_mask);
+    const bool fused = decide && h->nranks == 1;
+    launch_cluster(h, KN_REDUCE, k_reduce_scalars, std::max(1, h->red_cluster), RED_THREADS, 0, P, pm_mask, cam_mask, fused ? 1 : 0,
+                   fused ? *decide : DecideArgs{0.0, 0.0, 0.0, 0.0, 0, 0ull}, (fused && prep) ? 1 : 0, kDiagMin, kDiagMax);
     if (h->nranks > 1) {
         double* scal = reinterpret_cast<double*>(reinterpret_cast<char*>(h->st.p) + offsetof(LMState, scal));
         allreduce_sum(h, scal, N_PT_SCAL);
         if (pm_mask & (1u << S_GPMAX)) allreduce_max(h, scal + S_GPMAX, 1);
     }
+    return fused;
 }
 
 static void lin_cameras(ba_handle* h, double dmin, double dmax) {
@@ -1324,7 +1332,6 @@ static void lin_cameras(ba_handle* h, double dmin, double dmax) {
     launch(h, KN_CAM_FIN, k_camera_finish_lin, cdiv(P.n_cams, 128), 128, 0, P, dmin, dmax);
 }
 
-static const double kDiagMin = 1e-6, kDiagMax = 1e32;
 static const int kDeviceLoopMaxObs = 262144;  // largest problem the device-side LM / PCG loops are the default for
 
 static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
@@ -1568,10 +1575,13 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
         }
         launch(h, KN_PCG_UPDATE, k_pcg_update, P.vec_ctas, VEC_THREADS, 0, P, opt->pcg_tol, opt->pcg_max_iters, n_dots, h->ticket.p);
     };
-    auto dense_solve = [&]() {  // the whole camera side of an LM iteration: bins, gradient, S, Cholesky, exact step
-        launch(h, KN_PT_PREP, k_point_prepare, cdiv(P.n_pts, 256), 256, 0, P, kDiagMin, kDiagMax);
-        launch(h, KN_DENSE, k_dense_schur, P.n_cams * P.n_cams, DN_THREADS, dn_solve_smem(P.n_cams), P, (const int4*)h->dn_pairs.p,
-               (const int*)h->dn_off.p, h->dn_S.p, h->dn_extra.p, h->dn_count.p + 1, h->dn_count.p, kDiagMin, kDiagMax, opt->gtol);
+    // the whole camera side of an LM iteration: bins, gradient, S, Cholesky, exact step, trial poses.  The points (V^-1, h) are
+    // prepared by the reduction kernel that closed the previous iteration; once here for the first.
+    if (dense && status == 0) launch(h, KN_PT_PREP, k_point_prepare, cdiv(P.n_pts, 256), 256, 0, P, kDiagMin, kDiagMax);
+    auto dense_solve = [&]() {
+        launch(h, KN_DENSE, k_dense_schur, P.n_cams * P.n_cams * h->dn_split, DN_THREADS, dn_solve_smem(P.n_cams), P,
+               (const int4*)h->dn_pairs.p, (const int*)h->dn_off.p, h->dn_S.p, h->dn_extra.p, h->dn_count.p + 1, h->dn_count.p, kDiagMin,
+               kDiagMax, opt->gtol, h->dn_split);
     };
     if (dense) CK(cudaMemsetAsync(h->dn_count.p, 0, sizeof(int), s));
     auto after_pcg = [&]() {
@@ -1579,10 +1589,11 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
             launch(h, KN_TILE_BACKSUB, k_tile_pass<1>, h->ft_grid, FT_THREADS, ft_smem_bytes(FT_ROWS_MV), P, (const double*)h->v_x.p);
         else
             launch(h, KN_BACKSUB, k_point_pass<1>, P.pm_tiles, PM_THREADS, h->smem_pass, P, (const double*)h->v_x.p);
-        launch(h, KN_CAM_UPDATE, k_camera_update, cdiv(nc1, 128), 128, 0, P);
+        if (!dense) launch(h, KN_CAM_UPDATE, k_camera_update, cdiv(nc1, 128), 128, 0, P);  // dense: done by the solve kernel
         lin_points_and_cost(h, 3, opt->point_linesearch != 0);
-        reduce_scalars(h, MASK_LIN | MASK_STEP_PM, MASK_STEP_CAM);
-        launch(h, KN_DECIDE, k_lm_decide, 1, 1, 0, P, opt->ftol, opt->xtol, opt->lambda_min, opt->lambda_max, opt->max_iters, lm_loop);
+        const DecideArgs da{opt->ftol, opt->xtol, opt->lambda_min, opt->lambda_max, opt->max_iters, lm_loop};
+        if (!reduce_scalars(h, MASK_LIN | MASK_STEP_PM, MASK_STEP_CAM, &da, dense))
+            launch(h, KN_DECIDE, k_lm_decide, 1, 1, 0, P, opt->ftol, opt->xtol, opt->lambda_min, opt->lambda_max, opt->max_iters, lm_loop);
     };
 
     // ---- device-side loops: the WHOLE solve is one CUDA graph - a conditional WHILE node over the LM iterations whose body

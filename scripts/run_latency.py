@@ -47,3 +47,9 @@ names = ["gather", "index", "pack", "set_problem", "solve", "get_x", "update_map
 print(f"window: {len(ids)} keyframes, {len(mp_ids)} points, {len(obs)} observations")
 for n, a, b in zip(names, t[:-1], t[1:]):
     print(f"  {n:12s} {1e3 * (b - a):8.3f} ms")
+# per-kernel device times of the same window (host-driven loop, CUDA events around every launch)
+s.set_problem(K[0, 0], K[1, 1], K[0, 2], K[1, 2], rv, tv, matrix_to_rvec(gmap.keyframes[ids[0]].R), gmap.keyframes[ids[0]].t.ravel(), pts, oc, op, ouv)
+st = s.solve(verbose=2, device_loop=0)
+ks = s.kernel_stats()
+print(f"per-kernel (host loop, {st['iterations']} LM iterations, {st['solve_ms']:.2f} ms): " +
+      "  ".join(f"{k} {1e3 * ms_ / n:.1f}us x{n}" for k, (n, ms_) in ks.items() if n and ms_ > 0.0))
