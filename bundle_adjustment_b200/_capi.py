@@ -89,8 +89,17 @@ SYMBOLS = {
     "ba_tile_layout": (C.c_int, [C.c_void_p, _ip, _ip, _ip, _ip, _dp, _ip, _ip, _ip, _ip, _ip]),
     "ba_triangulate": (C.c_int, [C.c_void_p, _dp, _dp, _dp, _dp, C.c_int32, _dp, _dp, _dp, _dp, C.POINTER(C.c_uint8)]),
     "ba_triangulate_static": (C.c_int, [C.c_void_p, _dp, _dp, _dp, _dp, C.c_int32, _dp, _dp, _dp, _dp, C.POINTER(C.c_uint8)]),
+    "ba_map_clear": (C.c_int, [C.c_void_p]),
+    "ba_map_append_observations": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, _ip, _dp]),
+    "ba_map_set_points": (C.c_int, [C.c_void_p, C.c_int32, _ip, _dp]),
+    "ba_map_forget_points": (C.c_int, [C.c_void_p, C.c_int32, _ip]),
+    "ba_map_window": (C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int32, _ip, _dp, _dp, _ip, _ip]),
+    "ba_map_window_points": (C.c_int, [C.c_void_p, _ip]),
+    "ba_map_commit": (C.c_int, [C.c_void_p]),
+    "ba_map_stats": (C.c_int, [C.c_void_p, _lp]),
     "ba_last_error": (C.c_char_p, []),
 }
+MAP_MAX_ID = 1 << 24   # dense id tables of the resident map (include/ba_b200.h)
 
 
 def lib():

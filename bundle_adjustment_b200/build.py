@@ -8,10 +8,8 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "ba_solver.cu")
-DEPS = [SRC, os.path.join(HERE, "csrc", "ba_kernels.cuh"), os.path.join(HERE, "csrc", "ba_math.cuh"),
-        os.path.join(HERE, "csrc", "ba_tiles.cuh"), os.path.join(HERE, "csrc", "ba_peer.cuh"), os.path.join(HERE, "csrc", "ba_triangulate.cuh"),
-        os.path.join(os.path.dirname(HERE), "include", "ba_b200.h"),
-        os.path.join(HERE, "csrc", "ba_host_math.h")]
+DEPS = sorted(os.path.join(HERE, "csrc", f) for f in os.listdir(os.path.join(HERE, "csrc")) if f.endswith((".cu", ".cuh", ".h"))) + \
+    [os.path.join(os.path.dirname(HERE), "include", "ba_b200.h")]
 OUT = os.path.join(HERE, "libba_b200.so")
 
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",

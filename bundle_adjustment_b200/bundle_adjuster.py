@@ -19,8 +19,24 @@ from typing import Dict, List, Optional, Tuple
 
 import numpy as np
 
+from . import _capi as api
 from .geometry import matrix_to_rvec, rvec_to_matrix
 from .solver import FlatSolver
+
+
+class _NotResident(Exception):
+    """The map cannot be mirrored on the device (ids that are no small non-negative integers, an oversized window):
+    this call flattens on the host instead."""
+
+
+class _ResidentMap:
+    """Host-side bookkeeping of the device-resident map (``ba_map_*``): what has been uploaded so far."""
+
+    def __init__(self, mpd):
+        self.mpd = mpd                      # the map_points dict the device copy mirrors
+        self.kfs: Dict[int, tuple] = {}     # kf_id -> (observation list, keypoint list, rows uploaded)
+        self.known: set = set()             # map point ids whose position is on the device
+        self.last_key = None                # last key of mpd when it was scanned (dicts keep insertion order)
 
 
 class BundleAdjuster:
@@ -28,7 +44,8 @@ class BundleAdjuster:
 
     def __init__(self, camera_matrix, window_size=5, *, device: int = 0, max_iters: int = 50, ftol: float = 1e-5,
                  xtol: float = 1e-5, gtol: float = 1e-8, huber_delta: float = 1.0, robust_mode: str = "irls",
-                 verbose: int = 0, lba_steps_dir: Optional[str] = None, solver_options: Optional[dict] = None):
+                 verbose: int = 0, lba_steps_dir: Optional[str] = None, solver_options: Optional[dict] = None,
+                 resident=True):
         # public, mutable attributes exactly as in the reference (src/main.py:83-86 mutates window_size); the tolerances default
         # to the reference's call (xtol = ftol = 1e-5, max_nfev = 50: src/bundle_adjuster.py:172), gtol to SciPy's default
         self.camera_matrix = camera_matrix
@@ -45,6 +62,14 @@ class BundleAdjuster:
         self._solver: Optional[FlatSolver] = None
         # incremental flattening: per keyframe, the arrays of its observation list as last seen
         self._kf_cache: Dict[int, tuple] = {}
+        # device-resident map: observation rows and point positions stay on the GPU between run() calls, a call
+        # uploads what the pipeline appended since the last one and the device builds the window.  True: positions the
+        # device already holds are trusted (only BA rewrites them: the reference assigns `position` at creation and in
+        # _update_map, nowhere else); "verify": they are also compared with the host's every call and re-uploaded where they
+        # differ; False: flatten on the host every call (the round-1 path).
+        self.resident = resident
+        self._res: Optional[_ResidentMap] = None
+        self.last_upload: Optional[dict] = None
 
     # ------------------------------------------------------------------------------------------
     def _get_solver(self) -> FlatSolver:
@@ -151,6 +176,98 @@ class BundleAdjuster:
         obs_pt = np.searchsorted(ids, mp).astype(np.int32)
         return ids.tolist(), cam, obs_pt, np.ascontiguousarray(uv)
 
+    # -- device-resident window (what run() uses when self.resident) ---------------------------------------
+    @staticmethod
+    def _small_ids(ids) -> np.ndarray:
+        a = np.asarray(ids)
+        if a.size and (a.dtype.kind not in "iu" or int(a.min()) < 0 or int(a.max()) >= api.MAP_MAX_ID):
+            raise _NotResident
+        return a.astype(np.int32)
+
+    def _window_resident(self, gmap, local_kf_ids: list):
+        """Upload what is new since the last call and let the device build the window's flat problem (``ba_map_window``):
+        -> sorted map point ids of the window, or None when it holds no observation of a known point.  Equivalent to
+        ``_gather_flat`` + ``set_problem`` (same rows, same order, same point numbering)."""
+        solver = self._get_solver()
+        mpd = gmap.map_points
+        self._small_ids(local_kf_ids)
+        if self._res is None or self._res.mpd is not mpd:
+            solver.map_clear()
+            self._res = _ResidentMap(mpd)
+        for attempt in (0, 1):
+            st, ok = self._res, True
+            for kf_id in local_kf_ids:
+                kf = gmap.keyframes[kf_id]
+                obs, kps = kf.observations, kf.keypoints
+                n, ent = len(obs), st.kfs.get(kf_id)
+                if ent is None:
+                    start = 0
+                elif ent[0] is obs and ent[1] is kps and ent[2] <= n:
+                    start = ent[2]                      # the pipeline only appends (src/pipeline.py:172-173, 306-307)
+                else:
+                    ok = False                          # another list, or a shorter one: rebuild the resident copy
+                    break
+                if start < n:
+                    tail = obs[start:]
+                    mp = self._small_ids(np.fromiter((o[0] for o in tail), dtype=np.int64, count=len(tail)))
+                    uv = np.array([kps[o[1]].pt for o in tail], dtype=np.float64).reshape(-1, 2)
+                    solver.map_append_observations(kf_id, mp, uv)
+                st.kfs[kf_id] = (obs, kps, n)
+            if ok:
+                break
+            solver.map_clear()
+            self._res = _ResidentMap(mpd)
+        st = self._res
+        # new map points: the tail of the dict (insertion order); anything else that changed triggers a full comparison
+        known = st.known
+        last_key = next(reversed(mpd)) if mpd else None
+        if len(mpd) != len(known) or last_key != st.last_key:
+            new = []
+            for mp_id in reversed(mpd):
+                if mp_id in known:
+                    break
+                new.append(mp_id)
+            if len(known) + len(new) != len(mpd):
+                gone = [i for i in known if i not in mpd]
+                if gone:
+                    solver.map_forget_points(np.asarray(gone, dtype=np.int32))
+                    known.difference_update(gone)
+                new = [i for i in mpd if i not in known]
+            if new:
+                ids = self._small_ids(new)
+                xyz = np.array([np.asarray(mpd[i].position, dtype=np.float64).ravel() for i in new]).reshape(-1, 3)
+                solver.map_set_points(ids, xyz)
+                known.update(new)
+            st.last_key = last_key
+        rvecs = np.array([matrix_to_rvec(gmap.keyframes[i].R) for i in local_kf_ids]).reshape(-1, 3)
+        tvecs = np.array([np.asarray(gmap.keyframes[i].t, dtype=np.float64).ravel() for i in local_kf_ids]).reshape(-1, 3)
+        fx, fy, cx, cy = self._intrinsics()
+        for attempt in (0, 1, 2):
+            try:
+                n_pts, n_obs = solver.map_window(fx, fy, cx, cy, local_kf_ids, rvecs, tvecs)
+            except api.BaError as e:
+                if "pair table" in str(e):
+                    raise _NotResident from e
+                raise
+            if n_obs == 0:
+                return None
+            ids = solver.map_window_points().tolist()
+            # `mp_id in gmap.map_points` (:213) for ids that were removed behind our back
+            missing = [i for i in ids if i not in mpd]
+            if missing:
+                solver.map_forget_points(np.asarray(missing, dtype=np.int32))
+                known.difference_update(missing)
+                continue
+            if self.resident == "verify" and attempt < 2:
+                host = np.array([np.asarray(mpd[i].position, dtype=np.float64).ravel() for i in ids]).reshape(-1, 3)
+                dev = solver.get_params()[2]
+                changed = np.flatnonzero((host != dev).any(axis=1))
+                if changed.size:
+                    solver.map_set_points(np.asarray(ids, dtype=np.int32)[changed], host[changed])
+                    continue
+            return ids
+        raise _NotResident
+
     def _cost_function(self, params, fixed_kf_pose, fixed_kf_id, adjustable_kf_ids, map_point_ids, observations,
                        keypoints_2d):
         """Re-projection residuals (observed - projected, x then y per row) for the parameter vector
@@ -223,28 +340,52 @@ class BundleAdjuster:
             print("    -> LBA Skipped: No adjustable keyframes.")
             return
 
-        local_map_point_ids, obs_cam, obs_pt, obs_uv = self._gather_flat(gmap, local_kf_ids, fixed_kf_id)
-        if not local_map_point_ids:
+        # the third skip needs no device (and is decided before one is asked for, as in the reference): is there ANY
+        # observation of a known map point in the window?  Stops at the first one.
+        mpd = gmap.map_points
+        if not any(o[0] in mpd for kf_id in local_kf_ids for o in gmap.keyframes[kf_id].observations):
             print("    -> LBA Skipped: No points in the local window.")
             return
-        for stale in [k for k in self._kf_cache if k not in gmap.keyframes]:
-            del self._kf_cache[stale]
 
-        rvecs = np.array([matrix_to_rvec(gmap.keyframes[i].R) for i in adjustable_kf_ids]).reshape(-1, 3)
-        tvecs = np.array([np.asarray(gmap.keyframes[i].t, dtype=np.float64).ravel() for i in adjustable_kf_ids]).reshape(-1, 3)
-        mpd = gmap.map_points
-        try:        # positions are (3, 1) float64 arrays in the pipeline: one concatenate instead of a conversion per point
-            pts = np.concatenate([mpd[i].position for i in local_map_point_ids], dtype=np.float64).reshape(-1, 3)
-            if pts.shape[0] != len(local_map_point_ids):
-                raise ValueError
-        except (ValueError, TypeError):
-            pts = np.array([np.asarray(mpd[i].position, dtype=np.float64).ravel() for i in local_map_point_ids]).reshape(-1, 3)
-        fixed_kf = gmap.keyframes[fixed_kf_id]
-
-        fx, fy, cx, cy = self._intrinsics()
         solver = self._get_solver()
-        solver.set_problem(fx, fy, cx, cy, rvecs, tvecs, matrix_to_rvec(fixed_kf.R),
-                           np.asarray(fixed_kf.t, dtype=np.float64).ravel(), pts, obs_cam, obs_pt, obs_uv)
+        on_device = False
+        self.last_upload = None
+        if self.resident:
+            before = solver.map_stats()
+            try:
+                local_map_point_ids = self._window_resident(gmap, local_kf_ids)
+                on_device = True
+                after = solver.map_stats()
+                self.last_upload = {k: after[k] - before[k] for k in ("rows_appended", "points_set", "bytes_uploaded")}
+                self.last_upload["resident_rows"] = after["resident_rows"]
+            except _NotResident:
+                self._res = None
+        if on_device:
+            if local_map_point_ids is None:
+                print("    -> LBA Skipped: No points in the local window.")
+                return
+        else:
+            local_map_point_ids, obs_cam, obs_pt, obs_uv = self._gather_flat(gmap, local_kf_ids, fixed_kf_id)
+            if not local_map_point_ids:
+                print("    -> LBA Skipped: No points in the local window.")
+                return
+            for stale in [k for k in self._kf_cache if k not in gmap.keyframes]:
+                del self._kf_cache[stale]
+
+            rvecs = np.array([matrix_to_rvec(gmap.keyframes[i].R) for i in adjustable_kf_ids]).reshape(-1, 3)
+            tvecs = np.array([np.asarray(gmap.keyframes[i].t, dtype=np.float64).ravel() for i in adjustable_kf_ids]).reshape(-1, 3)
+            mpd = gmap.map_points
+            try:    # positions are (3, 1) float64 arrays in the pipeline: one concatenate instead of a conversion per point
+                pts = np.concatenate([mpd[i].position for i in local_map_point_ids], dtype=np.float64).reshape(-1, 3)
+                if pts.shape[0] != len(local_map_point_ids):
+                    raise ValueError
+            except (ValueError, TypeError):
+                pts = np.array([np.asarray(mpd[i].position, dtype=np.float64).ravel() for i in local_map_point_ids]).reshape(-1, 3)
+            fixed_kf = gmap.keyframes[fixed_kf_id]
+
+            fx, fy, cx, cy = self._intrinsics()
+            solver.set_problem(fx, fy, cx, cy, rvecs, tvecs, matrix_to_rvec(fixed_kf.R),
+                               np.asarray(fixed_kf.t, dtype=np.float64).ravel(), pts, obs_cam, obs_pt, obs_uv)
         stats = solver.solve(**self.solver_options)
         self.last_stats = stats
 
@@ -255,6 +396,8 @@ class BundleAdjuster:
             return
 
         self._update_map(gmap, solver.get_x(), adjustable_kf_ids, local_map_point_ids)
+        if on_device:
+            solver.map_commit()      # the resident positions follow the map (a discarded solve leaves them alone)
 
         improvement = 100.0 * (initial_cost - final_cost) / (initial_cost + 1e-8)
         print(f"    -> LBA Complete. Initial Cost: {initial_cost:.2f}, Final Cost: {final_cost:.2f}, "

@@ -114,6 +114,104 @@ BA_D bool dn_cholesky_solve(double* A, double* y, int n, int ld, int t, int nt) 
     return false;
 }
 
+#ifdef BA_DN_STAMPS
+// experiment builds only (scripts/window_stamps.py): %globaltimer at the stage boundaries of the last launch
+__device__ unsigned long long g_dn_stamps[16];
+#define DN_STAMP(i) do { if (threadIdx.x == 0) g_dn_stamps[i] = global_ns(); } while (0)
+#else
+#define DN_STAMP(i) do { } while (0)
+#endif
+
+// n <= 32 unknowns (the pipeline's windows: 4 adjustable keyframes = 24): ONE warp, lane i owning row i, square-root-free
+// (A = L D L^T, L unit lower).  What bounds a factorisation this small is the chain of dependent operations from one pivot to
+// the next, so everything on that chain stays in registers and shuffles: lane i carries its diagonal entry and its entry of
+// the next column; per column the chain is shuffle (pivot) - reciprocal - multiply - shuffle (multiplier of the next
+// column) - FMA, about 200 cycles.  The rest of the trailing update goes through shared memory behind it (loads before
+// stores: the rows alias to the compiler).  Measured on a 24 x 24 system: 3.9 us against 11.4 us for the same loop with
+// the pivot read from shared memory and a library rsqrt per column, and about 8 us for the CTA routine above (168 barriers).
+// y <- A^-1 y; returns true (in every lane) on a non-positive pivot.
+BA_D bool dn_ldlt_solve_warp(double* A, int ld, double* y, int n, int lane) {
+    constexpr unsigned FULL = 0xffffffffu;
+    const bool mine = lane < n;
+    double* row = A + (size_t)min(lane, n - 1) * ld;
+    double dii = mine ? row[lane] : 1.0;     // running diagonal entry a_ii
+    double tcur = (mine && lane > 0) ? row[0] : 0.0;  // a_ik of the current column k (lanes > k)
+    double inv = 0.0;                        // 1 / d_i in lane i
+#ifdef BA_DN_STAMPS
+    long long c_a = 0, c_b = 0, c_c = 0, c_d = 0;
+#define DN_CLK(v) const long long v = clock64()
+#else
+#define DN_CLK(v)
+#endif
+    for (int k = 0; k < n; ++k) {
+        DN_CLK(t0);
+        const double d = __shfl_sync(FULL, dii, k);
+        if (!(d > 0.0) || !isfinite(d)) return true;  // uniform
+        const double r = 1.0 / d;
+#ifdef BA_DN_STAMPS
+        const long long t1 = (r > 0.0) ? clock64() : 0;
+#endif
+        if (lane == k) inv = r;
+        const bool below = mine && lane > k;
+        const double t = below ? tcur : 0.0;
+        const double l = t * r;               // L_ik
+        const double l1 = __shfl_sync(FULL, l, min(k + 1, 31));  // L_{k+1,k}: the multiplier of the next column's entries
+        if (below) {
+            row[k] = l;
+            dii -= t * l;
+        }
+        // entry of the next column (registers), then the other entries of the row (shared memory)
+        const double nxt = (mine && lane > k + 1) ? row[k + 1] - t * l1 : 0.0;
+#ifdef BA_DN_STAMPS
+        const long long t2 = (nxt == 12345.678) ? 0 : clock64();
+#endif
+        __syncwarp();                         // the L_jk are visible
+        if (mine && lane > k + 2) {
+            int j = k + 2;
+            for (; j + 7 < lane; j += 8) {
+                double m[8], q[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) { m[e] = A[(j + e) * ld + k]; q[e] = row[j + e]; }
+#pragma unroll
+                for (int e = 0; e < 8; ++e) row[j + e] = q[e] - t * m[e];
+            }
+            double m[8], q[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const int je = min(j + e, lane - 1);
+                m[e] = A[je * ld + k]; q[e] = row[je];
+            }
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+                if (j + e < lane) row[j + e] = q[e] - t * m[e];
+        }
+        __syncwarp();
+        tcur = nxt;
+#ifdef BA_DN_STAMPS
+        const long long t3 = clock64();
+        c_a += t1 - t0; c_b += t2 - t1; c_c += t3 - t2;
+#endif
+    }
+#ifdef BA_DN_STAMPS
+    if (threadIdx.x == 0) { g_dn_stamps[12] = c_a; g_dn_stamps[13] = c_b; g_dn_stamps[14] = c_c; }
+#endif
+    DN_STAMP(9);
+    double rhs = mine ? y[lane] : 0.0;
+    for (int k = 0; k < n; ++k) {  // L z = b (unit diagonal)
+        const double zk = __shfl_sync(FULL, rhs, k);
+        if (mine && lane > k) rhs -= row[k] * zk;
+    }
+    rhs *= inv;                    // D w = z
+    DN_STAMP(10);
+    for (int k = n - 1; k >= 0; --k) {  // L^T x = w
+        const double xk = __shfl_sync(FULL, rhs, k);
+        if (lane < k) rhs -= A[k * ld + lane] * xk;
+    }
+    DN_STAMP(11);
+    if (mine) y[lane] = rhs;
+    return false;
+}
+
 __global__ void __launch_bounds__(DN_THREADS) k_dense_schur(Params P, const int4* __restrict__ pairs, const int* __restrict__ bin_off,
                                                             double* __restrict__ S_bins, double* __restrict__ extra,
                                                             int* __restrict__ ticket, int* __restrict__ n_solves, double dmin,
@@ -129,6 +227,7 @@ __global__ void __launch_bounds__(DN_THREADS) k_dense_schur(Params P, const int4
     const int ci = bin / nc, cj = bin - ci * nc;
     const bool diag = ci == cj;
     const int b = P.st->cur;
+    if (blockIdx.x == 0) DN_STAMP(0);
     const double2* Jb = P.tc_J + (size_t)b * 3 * P.n_obs;
     const double2* Rb = P.tc_r + (size_t)b * P.n_obs;
     double acc[36 + DN_EXTRA];
@@ -180,8 +279,10 @@ __global__ void __launch_bounds__(DN_THREADS) k_dense_schur(Params P, const int4
             }
         }
     }
+    if (blockIdx.x == 0) DN_STAMP(1);
     block_sum<36 + DN_EXTRA, DN_THREADS>(acc, red, tot);
     __syncthreads();
+    if (blockIdx.x == 0) DN_STAMP(2);
     if (tid < 36) S_bins[((size_t)bin * split + part) * 36 + tid] = tot[tid];
     if (diag && tid < DN_EXTRA) extra[((size_t)ci * split + part) * DN_EXTRA + tid] = tot[36 + tid];
     __threadfence();
@@ -190,6 +291,7 @@ __global__ void __launch_bounds__(DN_THREADS) k_dense_schur(Params P, const int4
     __syncthreads();
     if (!last) return;
     __threadfence();
+    DN_STAMP(3);
 
     // ---- the last CTA: S + lambda D, Cholesky, solve -------------------------------------------------------------------
     const int n = 6 * nc, ld = n + 1;
@@ -214,6 +316,7 @@ __global__ void __launch_bounds__(DN_THREADS) k_dense_schur(Params P, const int4
         P.cam_D[l] = d; P.cam_g[l] = g; P.v_b[l] = eh - g;
     }
     __syncthreads();
+    DN_STAMP(4);
     for (int l = tid; l < n * n; l += DN_THREADS) {
         const int r = l / n, c = l - r * n;
         if (c > r) continue;
@@ -236,13 +339,20 @@ __global__ void __launch_bounds__(DN_THREADS) k_dense_schur(Params P, const int4
         if (st->status == 0 && m < gtol) st->status = 1;
     }
     __syncthreads();
-    {
-        // (one warp with __syncwarp between the steps was tried for n <= 48: slower - the trailing update of a step is a few
-        // hundred entries, worth the CTA barrier)
+    DN_STAMP(5);
+    if (n <= 32) {
+        // up to five adjustable cameras: one warp, a row per lane
+        if (tid < 32) {
+            const bool b0 = dn_ldlt_solve_warp(A, ld, y, n, tid);
+            if (tid == 0) bad = b0 ? 1 : 0;
+        }
+    } else {
+        // (one warp with the CTA routine's element-strided loops was tried for n <= 48: slower than the CTA)
         const bool b0 = dn_cholesky_solve<false>(A, y, n, ld, tid, DN_THREADS);
         if (tid == 0) bad = b0 ? 1 : 0;
     }
     __syncthreads();
+    DN_STAMP(6);
     // a pivot that is not positive (cannot happen for a damped Schur complement in exact arithmetic) leaves x = 0: the points
     // alone move, the model decrease stays exact, LM carries on
     for (int l = tid; l < n; l += DN_THREADS) {
@@ -256,7 +366,9 @@ __global__ void __launch_bounds__(DN_THREADS) k_dense_schur(Params P, const int4
         if (n_solves) *n_solves += bad ? 0 : 1;
     }
     __syncthreads();  // x, g_c, D_c are in place (this CTA wrote them): the trial poses and the step's camera-side scalars
+    DN_STAMP(7);
     for (int c = tid; c <= nc; c += DN_THREADS) camera_update_one(P, c);
+    DN_STAMP(8);
 }
 
 }  // namespace ba

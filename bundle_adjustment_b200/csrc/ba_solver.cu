@@ -12,6 +12,7 @@
 #include "ba_dense.cuh"
 #include "ba_host_math.h"
 #include "ba_triangulate.cuh"
+#include "ba_map.cuh"
 
 #include <cub/cub.cuh>
 #include <dlfcn.h>
@@ -448,6 +449,17 @@ struct ba_handle {
     DBuf<TraceRec> trace;  // per-LM-iteration records of the last solve (ba_solve_trace)
     int trace_n = 0;
     DBuf<double> io;  // staging for parameter upload / download
+    // device-resident map (ba_map.cuh): observation rows of every keyframe seen so far, map point positions by id
+    DBuf<int> ms_kf, ms_mp;
+    DBuf<double2> ms_uv;
+    size_t ms_rows = 0;
+    DBuf<double> mp_xyz;
+    DBuf<unsigned char> mp_known;
+    DBuf<int> kf_slot;
+    DBuf<int> mw_ids;        // map point ids of the last window (sorted), = the caller's point indices of the uploaded problem
+    int mw_n_pts = 0;
+    bool mw_current = false;  // the uploaded problem is the one ba_map_window built
+    long long map_counters[8] = {0};  // see ba_map_stats
     LMState* h_state = nullptr;  // pinned
     int* h_flag = nullptr;       // pinned
 
@@ -994,6 +1006,7 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
         agree_or_fail(h, (bad_n || bad_p) ? 1 : 0, "%s", bad_n ? "need n_adj_cams >= 0, n_pts > 0, n_obs > 0" : "null array argument");
     }
     h->have_problem = false;
+    h->mw_current = false;
     h->coarse_colours = 0; h->coarse_graph_agg = 0;  // the aggregate graph belongs to the problem
     const size_t nc1 = (size_t)n_cams + 1;
     StageTimer tm(s);
@@ -1025,9 +1038,11 @@ static void set_problem(ba_handle* h, double fx, double fy, double cx, double cy
     d_cam.alloc(n_obs); d_pt.alloc(n_obs); d_iota.alloc(n_obs); d_perm.alloc(n_obs); d_err.alloc(2);
     d_kpt.alloc(n_obs); d_kpt_s.alloc(n_obs); d_kcam.alloc(n_obs); d_kcam_s.alloc(n_obs); d_camoff.alloc(nc1 + 1);
     d_err.zero(s);
-    CK(cudaMemcpyAsync(d_cam.p, obs_cam, (size_t)n_obs * sizeof(int), cudaMemcpyHostToDevice, s));
-    CK(cudaMemcpyAsync(d_pt.p, obs_pt, (size_t)n_obs * sizeof(int), cudaMemcpyHostToDevice, s));
-    CK(cudaMemcpyAsync(h->o_uv.p, obs_uv, (size_t)n_obs * sizeof(double2), cudaMemcpyHostToDevice, s));
+    // cudaMemcpyDefault: the observation arrays are the caller's host arrays (ba_set_problem) or device arrays built from the
+    // resident map (ba_map_window)
+    CK(cudaMemcpyAsync(d_cam.p, obs_cam, (size_t)n_obs * sizeof(int), cudaMemcpyDefault, s));
+    CK(cudaMemcpyAsync(d_pt.p, obs_pt, (size_t)n_obs * sizeof(int), cudaMemcpyDefault, s));
+    CK(cudaMemcpyAsync(h->o_uv.p, obs_uv, (size_t)n_obs * sizeof(double2), cudaMemcpyDefault, s));
 
     tm.mark("allocate + upload");
     Params& P = h->P;
@@ -1247,7 +1262,7 @@ static void set_params(ba_handle* h, const double* rvec, const double* tvec, con
     const size_t nc1 = (size_t)P.n_cams + 1;
     CK(cudaMemsetAsync(&h->st.p->cur, 0, sizeof(int), s));
     if (pts) {
-        CK(cudaMemcpyAsync(h->io.p, pts, (size_t)P.n_pts * 3 * sizeof(double), cudaMemcpyHostToDevice, s));
+        CK(cudaMemcpyAsync(h->io.p, pts, (size_t)P.n_pts * 3 * sizeof(double), cudaMemcpyDefault, s));  // host, or device (ba_map_window)
         launch(h, KN_SETUP, k_pack_points, cdiv(P.n_pts, B), B, 0, P.n_pts, P.n_pad, (const int*)h->pt_perm.p, (const double*)h->io.p,
                h->pt_X.p);
         if (save_initial)
@@ -2311,4 +2326,230 @@ int ba_kernel_stats(ba_handle* h, int64_t* launches, double* ms) {
     API_END
 }
 
+// ---- device-resident map (kernels in ba_map.cuh) ---------------------------------------------
 }  // extern "C"
+
+namespace ba {
+
+static const int kMapMaxId = 1 << 24;               // dense tables: ids of keyframes and map points below this
+static const long long kMapMaxPairs = 1LL << 28;    // (window keyframes) x (window points) entries of the pair table
+
+// grow a resident buffer, keeping its first `used` elements; `fill` is the byte value of the new part (-1: leave it)
+template <class T>
+static void map_grow(DBuf<T>& b, size_t used, size_t need, cudaStream_t s, int fill) {
+    if (need <= b.n) return;
+    const size_t cap = std::max(need, std::max<size_t>(2 * b.n, 4096));
+    T* q = nullptr;
+    CK(cudaMalloc(&q, cap * sizeof(T)));
+    if (used) CK(cudaMemcpyAsync(q, b.p, used * sizeof(T), cudaMemcpyDeviceToDevice, s));
+    if (fill >= 0) CK(cudaMemsetAsync(q + used, fill, (cap - used) * sizeof(T), s));
+    CK(cudaStreamSynchronize(s));
+    if (b.p) cudaFree(b.p);
+    b.p = q;
+    b.n = cap;
+}
+
+static void map_need_single(ba_handle* h) {
+    if (!h) fail(BA_ERR_ARG, "null handle");
+    if (h->nranks != 1) fail(BA_ERR_STATE, "the resident map belongs to single-GPU handles (windows are far below one GPU)");
+    use(h);
+}
+
+static void map_window(ba_handle* h, double fx, double fy, double cx, double cy, int n_kfs, const int* kf_id, const double* rvec,
+                       const double* tvec, int* n_pts_out, int* n_obs_out) {
+    map_need_single(h);
+    if (n_kfs < 1 || !kf_id || !rvec || !tvec || !n_pts_out || !n_obs_out) fail(BA_ERR_ARG, "need n_kfs >= 1 and non-null arrays");
+    cudaStream_t s = h->stream;
+    ScratchScope scratch(s);
+    *n_pts_out = 0; *n_obs_out = 0;
+    h->mw_current = false;
+    int max_kf = 0;
+    for (int i = 0; i < n_kfs; ++i) {
+        if (kf_id[i] < 0 || kf_id[i] >= kMapMaxId) fail(BA_ERR_ARG, "keyframe id %d outside [0, %d)", kf_id[i], kMapMaxId);
+        max_kf = std::max(max_kf, kf_id[i]);
+    }
+    const int n_rows = (int)h->ms_rows, mp_cap = (int)h->mp_known.n;
+    if (n_rows == 0 || mp_cap == 0) return;
+    const int B = 256;
+    map_grow(h->kf_slot, 0, (size_t)max_kf + 1, s, -1);
+    const int kf_cap = (int)h->kf_slot.n;
+    CK(cudaMemsetAsync(h->kf_slot.p, 0xff, (size_t)kf_cap * sizeof(int), s));
+    TBuf<int> d_kf, d_val, d_order, d_flag, d_local, d_cnt;
+    TBuf<unsigned> d_key, d_key_s;
+    d_kf.alloc(n_kfs); d_val.alloc(n_rows); d_order.alloc(n_rows); d_key.alloc(n_rows); d_key_s.alloc(n_rows);
+    d_flag.alloc((size_t)mp_cap + 1); d_local.alloc((size_t)mp_cap + 1); d_cnt.alloc(1);
+    d_flag.zero(s); d_cnt.zero(s);
+    CK(cudaMemcpyAsync(d_kf.p, kf_id, (size_t)n_kfs * sizeof(int), cudaMemcpyHostToDevice, s));
+    launch(h, KN_SETUP, k_mw_slots, cdiv(n_kfs, B), B, 0, n_kfs, (const int*)d_kf.p, h->kf_slot.p);
+    launch(h, KN_SETUP, k_mw_keys, cdiv(n_rows, B), B, 0, n_rows, n_kfs, kf_cap, mp_cap, (const int*)h->ms_kf.p, (const int*)h->ms_mp.p,
+           (const int*)h->kf_slot.p, (const unsigned char*)h->mp_known.p, d_key.p, d_val.p, d_flag.p, d_cnt.p);
+    int bits = 1;
+    while ((1LL << bits) < (long long)n_kfs + 1) ++bits;
+    size_t tb1 = 0, tb2 = 0;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, tb1, d_key.p, d_key_s.p, d_val.p, d_order.p, n_rows, 0, bits, s));
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, tb2, d_flag.p, d_local.p, mp_cap + 1, s));
+    TBuf<unsigned char> d_tmp;
+    d_tmp.alloc(std::max(tb1, tb2));
+    tb1 = d_tmp.n;
+    CK(cub::DeviceRadixSort::SortPairs(d_tmp.p, tb1, d_key.p, d_key_s.p, d_val.p, d_order.p, n_rows, 0, bits, s));  // stable
+    tb2 = d_tmp.n;
+    CK(cub::DeviceScan::ExclusiveSum(d_tmp.p, tb2, d_flag.p, d_local.p, mp_cap + 1, s));
+    h->launches[KN_SETUP] += 2;
+    int n_obs = 0, n_pts = 0;
+    CK(cudaMemcpyAsync(&n_obs, d_cnt.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(&n_pts, d_local.p + mp_cap, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    if (n_obs == 0 || n_pts == 0) return;  // "No points in the local window" (src/bundle_adjuster.py:150-152)
+    if ((long long)n_kfs * n_pts > kMapMaxPairs)
+        fail(BA_ERR_ARG, "window of %d keyframes x %d points exceeds the pair table (%lld entries)", n_kfs, n_pts, kMapMaxPairs);
+    TBuf<int> d_last, d_cam, d_pt;
+    TBuf<double2> d_uv;
+    TBuf<double> d_pts;
+    d_last.alloc((size_t)n_kfs * n_pts); d_cam.alloc(n_obs); d_pt.alloc(n_obs); d_uv.alloc(n_obs); d_pts.alloc((size_t)n_pts * 3);
+    h->mw_ids.alloc(n_pts);
+    CK(cudaMemsetAsync(d_last.p, 0xff, (size_t)n_kfs * n_pts * sizeof(int), s));
+    launch(h, KN_SETUP, k_mw_points, cdiv(mp_cap, B), B, 0, mp_cap, (const int*)d_flag.p, (const int*)d_local.p, (const double*)h->mp_xyz.p,
+           h->mw_ids.p, d_pts.p);
+    launch(h, KN_SETUP, k_mw_last, cdiv(n_obs, B), B, 0, n_obs, n_pts, (const unsigned*)d_key_s.p, (const int*)d_order.p,
+           (const int*)h->ms_mp.p, (const int*)d_local.p, d_last.p);
+    launch(h, KN_SETUP, k_mw_fill, cdiv(n_obs, B), B, 0, n_obs, n_pts, (const unsigned*)d_key_s.p, (const int*)d_order.p,
+           (const int*)h->ms_mp.p, (const double2*)h->ms_uv.p, (const int*)d_local.p, (const int*)d_last.p, d_cam.p, d_pt.p, d_uv.p);
+    // slot 0 is the fixed keyframe (src/bundle_adjuster.py:141-142): its pose is rvec[0..3) / tvec[0..3)
+    set_problem(h, fx, fy, cx, cy, n_kfs - 1, n_pts, n_obs, rvec + 3, tvec + 3, rvec, tvec, d_pts.p, d_cam.p, d_pt.p,
+                reinterpret_cast<const double*>(d_uv.p));
+    set_params(h, rvec + 3, tvec + 3, rvec, tvec, d_pts.p, /*save_initial=*/true);
+    h->mw_n_pts = n_pts;
+    h->mw_current = true;
+    *n_pts_out = n_pts; *n_obs_out = n_obs;
+}
+
+}  // namespace ba
+
+extern "C" {
+
+int ba_map_clear(ba_handle* h) {
+    API_BEGIN
+    ba::map_need_single(h);
+    h->ms_rows = 0;
+    h->mw_current = false;
+    if (h->mp_known.p) h->mp_known.zero(h->stream);
+    CK(cudaStreamSynchronize(h->stream));
+    h->map_counters[0] = 0;  // the other counters are cumulative over the handle's life
+    API_END
+}
+
+int ba_map_append_observations(ba_handle* h, int32_t kf_id, int32_t n, const int32_t* mp_id, const double* uv) {
+    API_BEGIN
+    ba::map_need_single(h);
+    if (kf_id < 0 || kf_id >= ba::kMapMaxId) ba::fail(BA_ERR_ARG, "keyframe id %d outside [0, %d)", kf_id, ba::kMapMaxId);
+    if (n < 0 || (n > 0 && (!mp_id || !uv))) ba::fail(BA_ERR_ARG, "need n >= 0 and non-null arrays");
+    if (n == 0) return BA_OK;
+    cudaStream_t s = h->stream;
+    const size_t r0 = h->ms_rows, r1 = r0 + (size_t)n;
+    if (r1 > (size_t)INT32_MAX) ba::fail(BA_ERR_ARG, "more than 2^31 resident observation rows");
+    ba::map_grow(h->ms_kf, r0, r1, s, -1);
+    ba::map_grow(h->ms_mp, r0, r1, s, -1);
+    ba::map_grow(h->ms_uv, r0, r1, s, -1);
+    CK(cudaMemcpyAsync(h->ms_mp.p + r0, mp_id, (size_t)n * sizeof(int), cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(h->ms_uv.p + r0, uv, (size_t)n * sizeof(double2), cudaMemcpyHostToDevice, s));
+    ba::launch(h, ba::KN_SETUP, ba::k_map_fill_rows, ba::cdiv(n, 256), 256, 0, (int)n, (int)kf_id, h->ms_kf.p + r0);
+    CK(cudaStreamSynchronize(s));
+    h->ms_rows = r1;
+    h->map_counters[0] = (long long)r1;
+    h->map_counters[1] += n;
+    h->map_counters[4] += (long long)n * 20;
+    API_END
+}
+
+int ba_map_set_points(ba_handle* h, int32_t n, const int32_t* mp_id, const double* xyz) {
+    API_BEGIN
+    ba::map_need_single(h);
+    if (n < 0 || (n > 0 && (!mp_id || !xyz))) ba::fail(BA_ERR_ARG, "need n >= 0 and non-null arrays");
+    if (n == 0) return BA_OK;
+    int max_id = 0;
+    for (int i = 0; i < n; ++i) {
+        if (mp_id[i] < 0 || mp_id[i] >= ba::kMapMaxId) ba::fail(BA_ERR_ARG, "map point id %d outside [0, %d)", mp_id[i], ba::kMapMaxId);
+        max_id = std::max(max_id, (int)mp_id[i]);
+    }
+    cudaStream_t s = h->stream;
+    ba::ScratchScope scratch(s);
+    const size_t cap0 = h->mp_known.n;
+    ba::map_grow(h->mp_known, cap0, (size_t)max_id + 1, s, 0);
+    ba::map_grow(h->mp_xyz, 3 * cap0, 3 * h->mp_known.n, s, 0);
+    ba::TBuf<int> d_id;
+    ba::TBuf<double> d_xyz;
+    d_id.alloc(n); d_xyz.alloc((size_t)n * 3);
+    CK(cudaMemcpyAsync(d_id.p, mp_id, (size_t)n * sizeof(int), cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_xyz.p, xyz, (size_t)n * 3 * sizeof(double), cudaMemcpyHostToDevice, s));
+    ba::launch(h, ba::KN_SETUP, ba::k_map_set_points, ba::cdiv(n, 256), 256, 0, (int)n, (const int*)d_id.p, (const double*)d_xyz.p,
+               h->mp_xyz.p, h->mp_known.p);
+    CK(cudaStreamSynchronize(s));
+    h->mw_current = false;  // the uploaded window may hold older positions
+    h->map_counters[2] += n;
+    h->map_counters[4] += (long long)n * 28;
+    API_END
+}
+
+int ba_map_forget_points(ba_handle* h, int32_t n, const int32_t* mp_id) {
+    API_BEGIN
+    ba::map_need_single(h);
+    if (n < 0 || (n > 0 && !mp_id)) ba::fail(BA_ERR_ARG, "need n >= 0 and a non-null array");
+    if (n == 0 || h->mp_known.n == 0) return BA_OK;
+    cudaStream_t s = h->stream;
+    ba::ScratchScope scratch(s);
+    ba::TBuf<int> d_id;
+    d_id.alloc(n);
+    CK(cudaMemcpyAsync(d_id.p, mp_id, (size_t)n * sizeof(int), cudaMemcpyHostToDevice, s));
+    ba::launch(h, ba::KN_SETUP, ba::k_map_forget_points, ba::cdiv(n, 256), 256, 0, (int)n, (int)h->mp_known.n, (const int*)d_id.p,
+               h->mp_known.p);
+    CK(cudaStreamSynchronize(s));
+    h->mw_current = false;
+    API_END
+}
+
+int ba_map_window(ba_handle* h, double fx, double fy, double cx, double cy, int32_t n_kfs, const int32_t* kf_id, const double* rvec,
+                  const double* tvec, int32_t* n_pts_out, int32_t* n_obs_out) {
+    API_BEGIN
+    ba::map_window(h, fx, fy, cx, cy, n_kfs, kf_id, rvec, tvec, n_pts_out, n_obs_out);
+    h->map_counters[3] += 1;
+    h->map_counters[4] += (long long)n_kfs * 52;
+    API_END
+}
+
+int ba_map_window_points(ba_handle* h, int32_t* mp_id_out) {
+    API_BEGIN
+    ba::map_need_single(h);
+    if (!h->mw_current || !h->have_problem) ba::fail(BA_ERR_STATE, "the uploaded problem was not built by ba_map_window");
+    if (!mp_id_out) ba::fail(BA_ERR_ARG, "null array argument");
+    CK(cudaMemcpyAsync(mp_id_out, h->mw_ids.p, (size_t)h->mw_n_pts * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    API_END
+}
+
+int ba_map_commit(ba_handle* h) {
+    API_BEGIN
+    ba::map_need_single(h);
+    if (!h->mw_current || !h->have_problem) ba::fail(BA_ERR_STATE, "the uploaded problem was not built by ba_map_window");
+    const ba::Params& P = h->P;
+    ba::read_state(h);
+    const int b = h->h_state->cur;
+    ba::launch(h, ba::KN_SETUP, ba::k_map_commit, ba::cdiv(P.n_pts, 256), 256, 0, P.n_pts, P.n_pad, (const int*)h->pt_perm.p,
+               (const double*)(h->pt_X.p + (size_t)b * P.pt_stride), (const int*)h->mw_ids.p, h->mp_xyz.p);
+    CK(cudaStreamSynchronize(h->stream));
+    API_END
+}
+
+int ba_map_stats(ba_handle* h, int64_t out[8]) {
+    API_BEGIN
+    if (!h || !out) ba::fail(BA_ERR_ARG, "null argument");
+    for (int k = 0; k < 8; ++k) out[k] = h->map_counters[k];
+    API_END
+}
+
+}  // extern "C"
+
+#ifdef BA_DN_STAMPS
+extern "C" int ba_dn_stamps(unsigned long long out[16]) {
+    return cudaMemcpyFromSymbol(out, ba::g_dn_stamps, 16 * sizeof(unsigned long long)) == cudaSuccess ? 0 : -2;
+}
+#endif

@@ -90,6 +90,57 @@ class FlatSolver:
         self.set_problem(fp.fx, fp.fy, fp.cx, fp.cy, fp.rvec, fp.tvec, fp.fixed_rvec, fp.fixed_tvec, fp.pts,
                          fp.obs_cam, fp.obs_pt, fp.obs_uv)
 
+    # -- device-resident map (``ba_map_*``) --------------------------------------------------
+    def map_clear(self):
+        api.check(api.lib().ba_map_clear(self._h))
+
+    def map_append_observations(self, kf_id: int, mp_ids, uv):
+        """Rows of ONE keyframe, in the order of its observation list."""
+        mp_ids, uv = api.i32(mp_ids).ravel(), api.f64(uv).reshape(-1, 2)
+        if uv.shape[0] != mp_ids.shape[0]:
+            raise ValueError("inconsistent array shapes")
+        api.check(api.lib().ba_map_append_observations(self._h, int(kf_id), mp_ids.shape[0], api.iptr(mp_ids), api.dptr(uv)))
+
+    def map_set_points(self, mp_ids, xyz):
+        mp_ids, xyz = api.i32(mp_ids).ravel(), api.f64(xyz).reshape(-1, 3)
+        if xyz.shape[0] != mp_ids.shape[0]:
+            raise ValueError("inconsistent array shapes")
+        api.check(api.lib().ba_map_set_points(self._h, mp_ids.shape[0], api.iptr(mp_ids), api.dptr(xyz)))
+
+    def map_forget_points(self, mp_ids):
+        mp_ids = api.i32(mp_ids).ravel()
+        api.check(api.lib().ba_map_forget_points(self._h, mp_ids.shape[0], api.iptr(mp_ids)))
+
+    def map_window(self, fx, fy, cx, cy, kf_ids, rvec, tvec) -> Tuple[int, int]:
+        """Build and upload the flat problem of a window from the resident rows: ``kf_ids[0]`` is the fixed keyframe.
+        -> (n_pts, n_obs); (0, 0) and no problem when the window is empty."""
+        kf_ids = api.i32(kf_ids).ravel()
+        n = kf_ids.shape[0]
+        rvec, tvec = api.f64(rvec).reshape(n, 3), api.f64(tvec).reshape(n, 3)
+        n_pts, n_obs = C.c_int32(), C.c_int32()
+        self._shape = None
+        api.check(api.lib().ba_map_window(self._h, float(fx), float(fy), float(cx), float(cy), n, api.iptr(kf_ids), api.dptr(rvec),
+                                          api.dptr(tvec), C.byref(n_pts), C.byref(n_obs)))
+        if n_obs.value > 0:
+            self._shape = (n - 1, n_pts.value, n_obs.value)
+        return n_pts.value, n_obs.value
+
+    def map_window_points(self) -> np.ndarray:
+        _, npt, _ = self._need()
+        ids = np.empty(npt, dtype=np.int32)
+        api.check(api.lib().ba_map_window_points(self._h, api.iptr(ids)))
+        return ids
+
+    def map_commit(self):
+        self._need()
+        api.check(api.lib().ba_map_commit(self._h))
+
+    def map_stats(self) -> Dict[str, int]:
+        out = np.zeros(8, dtype=np.int64)
+        api.check(api.lib().ba_map_stats(self._h, api.lptr(out)))
+        keys = ("resident_rows", "rows_appended", "points_set", "windows", "bytes_uploaded")
+        return {k: int(v) for k, v in zip(keys, out)}
+
     def _need(self):
         if self._shape is None:
             raise api.BaError(-4, "no problem uploaded")

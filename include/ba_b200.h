@@ -256,6 +256,38 @@ int ba_triangulate(ba_handle* h, const double P1[12], const double P2[12], const
 int ba_triangulate_static(ba_handle* h, const double P1[12], const double P2[12], const double* R_rel, const double* t_rel,
                           int32_t n, const double* pts1, const double* pts2, double* hom, double* xyz, uint8_t* valid);
 
+/* ---- device-resident map of successive windows ----------------------------------------------------
+ * Replaces, for a caller that runs local BA window after window on a growing map, the per-call flattening of the
+ * reference: _gather_local_data (src/bundle_adjuster.py:195-218: keyframe-major (kf, mp) rows of the window, sorted unique
+ * map point ids, the (kf, mp) -> keypoint dict) and the packing of x0 (:157-162).  The observation rows of every keyframe
+ * and the positions of the map points stay in HBM between calls; a call uploads only what is new - the reference pipeline
+ * only ever appends (src/pipeline.py:172-173, 215-217, 277-278, 306-308) - and ba_map_window builds on the device the
+ * same flat problem ba_set_problem would have received: same row order, same point numbering (rank of the id among the
+ * window's ids), the last keypoint of a (kf, mp) pair that is listed twice (:216), rows of unknown map points dropped
+ * (:213).  Ids are dense table indices: 0 <= id < 2^24.  Single-GPU handles only.
+ *
+ *   ba_map_clear                 forget every resident row and point (the counters of ba_map_stats keep counting)
+ *   ba_map_append_observations   rows (mp_id[i], uv[2i..2i+1]) of ONE keyframe, appended in the order of its observation list
+ *   ba_map_set_points            insert or overwrite positions ([n][3]); the ids become "in the map"
+ *   ba_map_forget_points         the ids are no longer in the map (`mp_id in gmap.map_points` false)
+ *   ba_map_window                kf_id[0] is the fixed keyframe (:141), kf_id[1..] the adjustable ones in camera order;
+ *                                rvec/tvec [n_kfs][3] are their CURRENT poses (240 bytes: uploaded every call).  Uploads the
+ *                                problem as ba_set_problem does (so every other entry point works on it) and returns its
+ *                                sizes; both 0 (and no problem) when the window holds no observation of a known point
+ *   ba_map_window_points         ids of the window's points in problem order (= sorted), [n_pts]
+ *   ba_map_commit                after an accepted solve: the solver's current points -> the resident positions
+ *   ba_map_stats                 [0] resident rows, [1] rows appended so far, [2] positions set so far, [3] windows built,
+ *                                [4] bytes uploaded by the ba_map_* calls so far, [5..7] 0 */
+int ba_map_clear(ba_handle* h);
+int ba_map_append_observations(ba_handle* h, int32_t kf_id, int32_t n, const int32_t* mp_id, const double* uv);
+int ba_map_set_points(ba_handle* h, int32_t n, const int32_t* mp_id, const double* xyz);
+int ba_map_forget_points(ba_handle* h, int32_t n, const int32_t* mp_id);
+int ba_map_window(ba_handle* h, double fx, double fy, double cx, double cy, int32_t n_kfs, const int32_t* kf_id,
+                  const double* rvec, const double* tvec, int32_t* n_pts_out, int32_t* n_obs_out);
+int ba_map_window_points(ba_handle* h, int32_t* mp_id_out);
+int ba_map_commit(ba_handle* h);
+int ba_map_stats(ba_handle* h, int64_t out[8]);
+
 /* Thread-local text of the last error returned on this thread. */
 const char* ba_last_error(void);
 

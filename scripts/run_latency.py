@@ -25,8 +25,45 @@ for rep in range(4):
         adj.run(gmap)
     dt = time.perf_counter() - t0
     st = adj.last_stats
-    print(f"run {rep}: {1e3 * dt:7.2f} ms total | device solve {st['solve_ms']:6.2f} ms, {st['iterations']} LM / {st['pcg_iterations']} PCG iterations, "
-          f"launches {st['launches']} | {out.getvalue().strip().splitlines()[-1].strip()}")
+    print(f"run {rep} (a NEW map every call: everything is uploaded): {1e3 * dt:7.2f} ms total | device solve {st['solve_ms']:6.2f} ms, "
+          f"{st['iterations']} LM / {st['pcg_iterations']} PCG iterations, launches {st['launches']} | {out.getvalue().strip().splitlines()[-1].strip()}")
+
+
+# the pipeline's pattern: ONE map that gains a keyframe (and the points it brings) between calls
+def growing(resident, n_total=14):
+    import cProfile, pstats
+    sp = S.make_window_spec(n_kfs=n_total, n_pts=n_pts * n_total // 10)
+    full = S.build_map(sp, Map, Keyframe, MapPoint, KeyPoint.from_xy)
+    gm, a, out_ms = Map(), BundleAdjuster(sp["camera_matrix"], window_size=5, resident=resident), []
+    prof = cProfile.Profile()
+    for step, kf_id in enumerate(sorted(full.keyframes)):
+        kf = full.keyframes[kf_id]
+        for mp_id, _ in kf.observations:
+            if mp_id not in gm.map_points:
+                gm.add_map_point(full.map_points[mp_id])
+        gm.add_keyframe(kf)
+        if step < 5:
+            continue
+        t0 = time.perf_counter()
+        if step == n_total - 1:
+            prof.enable()
+        with redirect_stdout(io.StringIO()):
+            a.run(gm)
+        prof.disable()
+        out_ms.append((1e3 * (time.perf_counter() - t0), a.last_stats["solve_ms"], a.last_stats["iterations"], a.last_upload))
+    return out_ms, prof
+
+
+for resident in (True, False):
+    ms, prof = growing(resident)
+    print(f"growing map, resident={resident}: per call " + "  ".join(f"{m:.2f}" for m, *_ in ms) + " ms")
+    tail = ms[2:-1]
+    print(f"  median of calls 3.. : {np.median([m for m, *_ in tail]):.2f} ms total, device solve {np.median([m[1] for m in tail]):.2f} ms "
+          f"({tail[-1][2]} LM iterations), last upload {tail[-1][3]}")
+    if resident:
+        import pstats
+        st_ = pstats.Stats(prof, stream=sys.stdout).sort_stats("cumulative")
+        st_.print_stats(14)
 # stage by stage
 gmap = S.build_map(spec, Map, Keyframe, MapPoint, KeyPoint.from_xy)
 ids = sorted(gmap.keyframes)[-6:-1]

@@ -153,3 +153,117 @@ def test_replay_of_the_reference_pipeline_calls():
         assert mine_huber <= ref_huber * (1.0 + 1e-6), (k, mine_huber, ref_huber)
         n_solved += 1
     assert n_solved >= 3
+
+
+# ---- device-resident map (ba_map_*) -------------------------------------------------------------------
+def _device_problem(solver):
+    """What the device holds of the uploaded problem, through the C ABI: residual vector (row order + keypoints + poses +
+    points), the Jacobian's CSR structure (camera / point of every row) and the parameter vector."""
+    indptr, indices, shape = solver.sparsity_csr()
+    return solver.residuals(), indptr, indices, shape, solver.get_x()
+
+
+def test_resident_window_is_the_host_flattened_problem_and_uploads_only_the_delta():
+    """``ba_map_window`` (device-built window from the resident rows) against the host flattening (``_gather_flat`` +
+    ``ba_set_problem``) AND against the CPU statement (oracle/map_window.py), on a map that grows between calls as the
+    pipeline grows it: residual vectors bit-identical, same Jacobian structure, same x0; a call uploads exactly what was
+    appended since the previous one."""
+    from bundle_adjustment_b200 import FlatSolver, synthetic as S
+    from bundle_adjustment_b200.geometry import matrix_to_rvec
+    from bundle_adjustment_b200.map_structures import KeyPoint, MapPoint
+    from oracle.map_window import MapStore
+    spec = S.make_window_spec(n_kfs=8, n_pts=600, seed=23, duplicates=4, dangling=3, kf_id_stride=3)
+    gmap = mirror_map(spec)
+    K = spec["camera_matrix"]
+    adj = BundleAdjuster(K, window_size=5)
+    local = sorted(gmap.keyframes)[-6:-1]
+
+    def check():
+        dev = adj._get_solver()
+        before = dev.map_stats()
+        ids = adj._window_resident(gmap, local)
+        after = dev.map_stats()
+        got = _device_problem(dev)
+        ids_h, oc, op, ouv = adj._gather_flat(gmap, local, local[0])
+        assert ids == ids_h
+        rv = np.array([matrix_to_rvec(gmap.keyframes[i].R) for i in local])
+        tv = np.array([gmap.keyframes[i].t.ravel() for i in local])
+        pts = np.array([gmap.map_points[i].position.ravel() for i in ids_h])
+        with FlatSolver(0) as host:
+            host.set_problem(K[0, 0], K[1, 1], K[0, 2], K[1, 2], rv[1:], tv[1:], rv[0], tv[0], pts, oc, op, ouv)
+            want = _device_problem(host)
+        for a, b in zip(got, want):
+            assert np.array_equal(a, b)
+        # the CPU statement builds the same rows from the same keyframe lists
+        cpu = MapStore()
+        for k in sorted(gmap.keyframes):
+            obs, kps = gmap.keyframes[k].observations, gmap.keyframes[k].keypoints
+            cpu.map_append_observations(k, [o[0] for o in obs], [kps[o[1]].pt for o in obs])
+        cpu.xyz = {i: mp.position.ravel().copy() for i, mp in gmap.map_points.items()}
+        cpu.map_window(K[0, 0], K[1, 1], K[0, 2], K[1, 2], local, rv, tv)
+        f = cpu.flat
+        assert f["ids"].tolist() == ids and np.array_equal(f["obs_cam"], oc) and np.array_equal(f["obs_pt"], op)
+        assert np.array_equal(f["obs_uv"], ouv) and np.array_equal(f["pts"], pts)
+        return after["rows_appended"] - before["rows_appended"], after["points_set"] - before["points_set"]
+
+    n_rows = sum(len(gmap.keyframes[k].observations) for k in local)
+    assert check() == (n_rows, len(gmap.map_points))
+    assert check() == (0, 0)
+    kf = gmap.keyframes[local[2]]
+    new_id = int(spec["mp_ids"].max()) + 100
+    gmap.add_map_point(MapPoint(id=new_id, position=np.array([[0.1], [0.2], [9.0]])))
+    kf.keypoints.append(KeyPoint.from_xy(321.5, 222.25))
+    kf.observations.append((new_id, len(kf.keypoints) - 1))
+    kf.observations.append((kf.observations[0][0], len(kf.keypoints) - 1))     # duplicate pair: the last keypoint for both rows
+    kf.observations.append((10 ** 6, 0))                                       # not in the map: dropped
+    assert check() == (3, 1)
+    local[:] = sorted(gmap.keyframes)[-5:]                                     # the window slides by one keyframe
+    assert check() == (len(gmap.keyframes[local[-1]].observations), 0)
+    gone = kf.observations[1][0]
+    del gmap.map_points[gone]                                                  # a point leaves the map: its rows go
+    assert check() == (0, 0)
+
+
+def test_resident_runs_equal_host_runs_on_a_growing_map():
+    """Successive ``run`` calls while keyframes and points are appended (what the pipeline does between calls): the resident
+    path and the host-flattening path leave bit-identical maps, the resident one uploading only the new rows / points -
+    positions of old points never travel again because ``ba_map_commit`` keeps the device's copy in step."""
+    from bundle_adjustment_b200 import synthetic as S
+    from bundle_adjustment_b200.map_structures import Keyframe, KeyPoint, Map, MapPoint
+    spec = S.make_window_spec(n_kfs=10, n_pts=1200, seed=5, duplicates=2)
+    full = [mirror_map(spec), mirror_map(spec)]
+    maps = [Map(), Map()]
+    adjs = [BundleAdjuster(spec["camera_matrix"], window_size=5, resident=True),
+            BundleAdjuster(spec["camera_matrix"], window_size=5, resident=False)]
+    kf_ids = sorted(full[0].keyframes)
+    uploads = []
+    for step, kf_id in enumerate(kf_ids):
+        for gm, src in zip(maps, full):
+            kf = src.keyframes[kf_id]
+            for mp_id, _ in kf.observations:                    # the points this keyframe brings (first sighting)
+                if mp_id in src.map_points and mp_id not in gm.map_points:
+                    gm.add_map_point(src.map_points[mp_id])
+            gm.add_keyframe(kf)
+        if step < 5:
+            continue
+        texts = []
+        for adj, gm in zip(adjs, maps):
+            with redirect_stdout(io.StringIO()) as out:
+                adj.run(gm)
+            texts.append(out.getvalue())
+        assert texts[0] == texts[1] and "LBA Complete" in texts[0]
+        uploads.append(dict(adjs[0].last_upload))
+        for k in maps[0].keyframes:
+            assert np.array_equal(maps[0].keyframes[k].R, maps[1].keyframes[k].R)
+            assert np.array_equal(maps[0].keyframes[k].t, maps[1].keyframes[k].t)
+        for k in maps[0].map_points:
+            assert np.array_equal(maps[0].map_points[k].position, maps[1].map_points[k].position)
+    assert adjs[1].last_upload is None
+    # first window: five keyframes; afterwards only the keyframe that entered the window (the newest one is not optimised,
+    # so the one uploaded is the previous call's newest) and the points it brought
+    assert uploads[0]["rows_appended"] == sum(len(maps[0].keyframes[k].observations) for k in kf_ids[:5])
+    for step, up in enumerate(uploads[1:], start=1):
+        entered = kf_ids[4 + step]
+        assert up["rows_appended"] == len(maps[0].keyframes[entered].observations)
+        assert 0 <= up["points_set"] <= len(maps[0].keyframes[entered].observations) + len(maps[0].keyframes[kf_ids[5 + step]].observations)
+    assert sum(u["points_set"] for u in uploads) == len(maps[0].map_points)

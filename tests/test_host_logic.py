@@ -9,6 +9,8 @@ import numpy as np
 import pytest
 
 from conftest import ROOT, golden_names, load_golden, mirror_map
+import bundle_adjustment_b200.bundle_adjuster
+import bundle_adjustment_b200
 from bundle_adjustment_b200 import BundleAdjuster, _capi, geometry, sharding, synthetic as S
 from bundle_adjustment_b200.map_structures import Keyframe, KeyPoint, Map, MapPoint
 from oracle import ba_oracle as O
@@ -88,7 +90,7 @@ def test_run_host_path_with_a_stub_solver():
         def get_x(self):
             return self.x
 
-    adj = BundleAdjuster(spec["camera_matrix"], window_size=5)
+    adj = BundleAdjuster(spec["camera_matrix"], window_size=5, resident=False)
     stub = Stub()
     adj._get_solver = lambda: stub
     before = {k: v.position.copy() for k, v in gmap.map_points.items()}
@@ -365,6 +367,117 @@ def test_incremental_flattening_follows_a_growing_map():
     both()
     kf.observations.append((10 ** 6, 0))                         # observation of a map point that is not in the map: dropped
     both()
+
+
+class _ResidentStub:
+    """Stands in for FlatSolver in the CPU tests of the resident path: the map calls are the CPU statement of ``ba_map_*``
+    (oracle/map_window.py); "solving" shifts every point by one."""
+
+    def __new__(cls):
+        from oracle.map_window import MapStore
+
+        class Stub(MapStore):
+            def solve(self, **kw):
+                return {"initial_raw_cost": 2.0, "final_raw_cost": 1.0}
+
+            def get_params(self):
+                return self.flat["rvec"], self.flat["tvec"], self.flat["pts"]
+
+            def get_x(self):
+                f = self.flat
+                return np.concatenate([f["rvec"].ravel(), f["tvec"].ravel(), (f["pts"] + 1.0).ravel()])
+
+            def map_commit(self):
+                MapStore.map_commit(self, self.flat["pts"] + 1.0)
+        return Stub()
+
+
+def test_resident_window_equals_the_host_flattening_and_uploads_only_the_delta():
+    """SURVEY 8f-2, host logic of the device-resident map (no GPU: the device calls go to their CPU statement): on a map that
+    grows between calls the window the resident path builds equals what the host flattening builds (ids, rows, order,
+    duplicate pairs with the last keypoint, dangling observations dropped, positions, poses), and every call uploads
+    exactly what was appended since the last one."""
+    from bundle_adjustment_b200.geometry import matrix_to_rvec
+    spec = S.make_window_spec(n_kfs=7, n_pts=200, seed=11, duplicates=3, dangling=2)
+    gmap = mirror_map(spec)
+    adj = BundleAdjuster(spec["camera_matrix"], window_size=5)
+    stub = _ResidentStub()
+    adj._get_solver = lambda: stub
+    local = sorted(gmap.keyframes)[-6:-1]
+
+    def both():
+        before = stub.map_stats()
+        ids = adj._window_resident(gmap, local)
+        after = stub.map_stats()
+        ids_h, oc, op, ouv = adj._gather_flat(gmap, local, local[0])
+        f = stub.flat
+        assert ids == ids_h and f["ids"].tolist() == ids_h
+        assert np.array_equal(f["obs_cam"], oc) and np.array_equal(f["obs_pt"], op) and np.array_equal(f["obs_uv"], ouv)
+        assert np.array_equal(f["pts"], np.array([gmap.map_points[i].position.ravel() for i in ids]))
+        assert np.array_equal(f["fixed_rvec"], matrix_to_rvec(gmap.keyframes[local[0]].R))
+        assert np.array_equal(f["tvec"], np.array([gmap.keyframes[i].t.ravel() for i in local[1:]]))
+        return after["rows_appended"] - before["rows_appended"], after["points_set"] - before["points_set"]
+
+    n_rows = sum(len(gmap.keyframes[k].observations) for k in local)
+    # the first call uploads the window's keyframes and every point of the map
+    assert both() == (n_rows, len(gmap.map_points))
+    assert both() == (0, 0)                                      # nothing changed: nothing uploaded
+    kf = gmap.keyframes[local[2]]
+    new_id = gmap.next_map_point_id
+    gmap.add_map_point(MapPoint(id=new_id, position=np.array([[0.1], [0.2], [9.0]])))
+    kf.keypoints.append(KeyPoint.from_xy(321.5, 222.25))
+    kf.observations.append((new_id, len(kf.keypoints) - 1))
+    kf.observations.append((kf.observations[0][0], len(kf.keypoints) - 1))   # duplicate pair: last keypoint wins for both rows
+    assert both() == (2, 1)                                      # two appended rows, one new point
+    kf.observations.append((10 ** 6, 0))                         # observation of a map point that is not in the map: dropped
+    assert both() == (1, 0)
+    kf2 = gmap.keyframes[local[3]]
+    kf2.observations = list(reversed(kf2.observations))          # another list object: the resident copy is rebuilt
+    rows, pts = both()
+    assert rows == sum(len(gmap.keyframes[k].observations) for k in local) and pts == len(gmap.map_points)
+    kf2.observations.pop()                                       # shorter: rebuilt again
+    assert both()[0] == sum(len(gmap.keyframes[k].observations) for k in local)
+    # a point leaves the map (`mp_id in gmap.map_points`, src/bundle_adjuster.py:213): its rows go
+    gone = kf.observations[1][0]
+    del gmap.map_points[gone]
+    assert both() == (0, 0) and gone not in stub.flat["ids"].tolist()
+    # the window slides: only the keyframe that enters is uploaded
+    local[:] = sorted(gmap.keyframes)[-5:]
+    assert both() == (len(gmap.keyframes[local[-1]].observations), 0)
+    # ids that cannot index a dense table: the call says so and run() flattens on the host
+    with pytest.raises(bundle_adjustment_b200.bundle_adjuster._NotResident):
+        adj._small_ids([3, 1 << 30])
+
+
+def test_resident_run_keeps_the_device_positions_in_step_with_the_map():
+    """run() on the resident path with the stub: the write-back reaches the map AND the resident positions (ba_map_commit),
+    so the next window starts from what the last one produced without any position upload; "verify" re-uploads a position
+    that somebody else replaced."""
+    from bundle_adjustment_b200.map_structures import Keyframe, KeyPoint as KP, Map, MapPoint as MP
+    spec = S.make_window_spec(n_kfs=10, n_pts=400)
+    gmap = S.build_map(spec, Map, Keyframe, MP, KP.from_xy)
+    adj = BundleAdjuster(spec["camera_matrix"], window_size=5, resident="verify")
+    stub = _ResidentStub()
+    adj._get_solver = lambda: stub
+    before = {k: v.position.copy() for k, v in gmap.map_points.items()}
+    with redirect_stdout(io.StringIO()) as out:
+        adj.run(gmap)
+    assert "LBA Complete. Initial Cost: 2.00, Final Cost: 1.00, Improvement: 50.00%" in out.getvalue()
+    ids = stub.flat["ids"].tolist()
+    assert adj.last_upload["points_set"] == len(gmap.map_points) and adj.last_upload["rows_appended"] == stub.flat["obs_cam"].shape[0]
+    for k, mp in gmap.map_points.items():
+        assert mp.position.shape == (3, 1)
+        assert np.array_equal(mp.position, before[k] + 1.0 if k in ids else before[k])
+        assert np.array_equal(stub.xyz[k], mp.position.ravel())
+    with redirect_stdout(io.StringIO()):
+        adj.run(gmap)
+    assert adj.last_upload["points_set"] == 0 and adj.last_upload["rows_appended"] == 0
+    assert np.array_equal(gmap.map_points[ids[0]].position, before[ids[0]] + 2.0)
+    gmap.map_points[ids[0]].position = np.array([[1.0], [2.0], [3.0]])          # replaced behind the adjuster's back
+    with redirect_stdout(io.StringIO()):
+        adj.run(gmap)
+    assert adj.last_upload["points_set"] == 1
+    assert np.array_equal(gmap.map_points[ids[0]].position, np.array([[2.0], [3.0], [4.0]]))
 
 
 def test_flat_import_through_the_shim():
