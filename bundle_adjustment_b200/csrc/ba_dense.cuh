@@ -123,78 +123,58 @@ __device__ unsigned long long g_dn_stamps[16];
 #endif
 
 // n <= 32 unknowns (the pipeline's windows: 4 adjustable keyframes = 24): ONE warp, lane i owning row i, square-root-free
-// (A = L D L^T, L unit lower).  What bounds a factorisation this small is the chain of dependent operations from one pivot to
-// the next, so everything on that chain stays in registers and shuffles: lane i carries its diagonal entry and its entry of
-// the next column; per column the chain is shuffle (pivot) - reciprocal - multiply - shuffle (multiplier of the next
-// column) - FMA, about 200 cycles.  The rest of the trailing update goes through shared memory behind it (loads before
-// stores: the rows alias to the compiler).  Measured on a 24 x 24 system: 3.9 us against 11.4 us for the same loop with
-// the pivot read from shared memory and a library rsqrt per column, and about 8 us for the CTA routine above (168 barriers).
+// (A = L D L^T, L unit lower), left-looking.  What bounds a factorisation this small is the chain of dependent operations
+// from one pivot to the next, so that chain stays in registers and shuffles - pivot by shuffle, reciprocal, L_ik = s_i / d_k,
+// one FMA for the last term of the next column - while the rest of the next column's inner products (terms of the columns
+// before k, which do not depend on this pivot) issue in the shadow of the reciprocal: loads only, uniform trip counts.
+// The lower triangle receives L; the upper triangle (free) keeps the undivided entries t_km = L_km d_m that the inner
+// products of row k's column need, so every operand is a conflict-free row read or a broadcast.
+// Measured at n = 24 (scripts/window_stamps.py): 8.4 us for factorisation + both solves (0.28 us per column: two shuffles, the
+// reciprocal and three dependent FP64 operations at about 40 cycles each; 33 ns per row of a solve), against 11.4-14.4 us for
+// right-looking variants with the pivot in shared memory and a library rsqrt, and 11.9 us for rows held in registers (unrolled).
 // y <- A^-1 y; returns true (in every lane) on a non-positive pivot.
 BA_D bool dn_ldlt_solve_warp(double* A, int ld, double* y, int n, int lane) {
     constexpr unsigned FULL = 0xffffffffu;
     const bool mine = lane < n;
     double* row = A + (size_t)min(lane, n - 1) * ld;
-    double dii = mine ? row[lane] : 1.0;     // running diagonal entry a_ii
-    double tcur = (mine && lane > 0) ? row[0] : 0.0;  // a_ik of the current column k (lanes > k)
-    double inv = 0.0;                        // 1 / d_i in lane i
-#ifdef BA_DN_STAMPS
-    long long c_a = 0, c_b = 0, c_c = 0, c_d = 0;
-#define DN_CLK(v) const long long v = clock64()
-#else
-#define DN_CLK(v)
-#endif
+    double s = mine ? row[0] : 0.0;  // entry (i, k) of the current column with every earlier column's term subtracted
+    double inv = 0.0;                // 1 / d_i in lane i
+    bool bad = false;                // same in every lane: the pivots are broadcast
     for (int k = 0; k < n; ++k) {
-        DN_CLK(t0);
-        const double d = __shfl_sync(FULL, dii, k);
-        if (!(d > 0.0) || !isfinite(d)) return true;  // uniform
-        const double r = 1.0 / d;
-#ifdef BA_DN_STAMPS
-        const long long t1 = (r > 0.0) ? clock64() : 0;
-#endif
+        const double d = __shfl_sync(FULL, s, k);
+        const double tk1 = __shfl_sync(FULL, s, min(k + 1, 31));  // t_{k+1,k}
+        // branch-free: the library division is a call with a slow path, which the scheduler does not overlap with the inner
+        // products below.  Hardware seed (rcp.approx.ftz.f64: about 20 bits) and two Newton steps give 1 / d to an ulp or
+        // two for the pivots that pass the test (checked after the loop: a bad pivot only poisons numbers nobody uses).
+        bad |= !(d > 1e-280) || !(d < 1e280);
+        double r;
+        asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+        r = fma(r, fma(-d, r, 1.0), r);
+        r = fma(r, fma(-d, r, 1.0), r);
+        // entry (i, k + 1) minus the terms of the columns m < k (independent of r)
+        const int k1 = min(k + 1, n - 1);
+        const double* col = A + k1;
+        double p0 = 0.0, p1 = 0.0, p2 = 0.0, p3 = 0.0;
+        int m = 0;
+        for (; m + 3 < k; m += 4) {
+            p0 += row[m] * col[m * ld];
+            p1 += row[m + 1] * col[(m + 1) * ld];
+            p2 += row[m + 2] * col[(m + 2) * ld];
+            p3 += row[m + 3] * col[(m + 3) * ld];
+        }
+        for (; m < k; ++m) p0 += row[m] * col[m * ld];
+        const double part = row[k1] - ((p0 + p1) + (p2 + p3));
         if (lane == k) inv = r;
         const bool below = mine && lane > k;
-        const double t = below ? tcur : 0.0;
-        const double l = t * r;               // L_ik
-        const double l1 = __shfl_sync(FULL, l, min(k + 1, 31));  // L_{k+1,k}: the multiplier of the next column's entries
+        const double l = below ? s * r : 0.0;  // L_ik
         if (below) {
             row[k] = l;
-            dii -= t * l;
+            A[k * ld + lane] = s;              // t_ik, read as the multiplier of row i's columns later
         }
-        // entry of the next column (registers), then the other entries of the row (shared memory)
-        const double nxt = (mine && lane > k + 1) ? row[k + 1] - t * l1 : 0.0;
-#ifdef BA_DN_STAMPS
-        const long long t2 = (nxt == 12345.678) ? 0 : clock64();
-#endif
-        __syncwarp();                         // the L_jk are visible
-        if (mine && lane > k + 2) {
-            int j = k + 2;
-            for (; j + 7 < lane; j += 8) {
-                double m[8], q[8];
-#pragma unroll
-                for (int e = 0; e < 8; ++e) { m[e] = A[(j + e) * ld + k]; q[e] = row[j + e]; }
-#pragma unroll
-                for (int e = 0; e < 8; ++e) row[j + e] = q[e] - t * m[e];
-            }
-            double m[8], q[8];
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                const int je = min(j + e, lane - 1);
-                m[e] = A[je * ld + k]; q[e] = row[je];
-            }
-#pragma unroll
-            for (int e = 0; e < 8; ++e)
-                if (j + e < lane) row[j + e] = q[e] - t * m[e];
-        }
+        s = part - l * tk1;
         __syncwarp();
-        tcur = nxt;
-#ifdef BA_DN_STAMPS
-        const long long t3 = clock64();
-        c_a += t1 - t0; c_b += t2 - t1; c_c += t3 - t2;
-#endif
     }
-#ifdef BA_DN_STAMPS
-    if (threadIdx.x == 0) { g_dn_stamps[12] = c_a; g_dn_stamps[13] = c_b; g_dn_stamps[14] = c_c; }
-#endif
+    if (bad) return true;
     DN_STAMP(9);
     double rhs = mine ? y[lane] : 0.0;
     for (int k = 0; k < n; ++k) {  // L z = b (unit diagonal)
@@ -365,9 +345,8 @@ __global__ void __launch_bounds__(DN_THREADS) k_dense_schur(Params P, const int4
         st->pcg_done = 1;
         if (n_solves) *n_solves += bad ? 0 : 1;
     }
-    __syncthreads();  // x, g_c, D_c are in place (this CTA wrote them): the trial poses and the step's camera-side scalars
+    // the trial poses and the step's camera-side scalars follow in the back-substitution launch (its extra CTA, ba_tiles.cuh)
     DN_STAMP(7);
-    for (int c = tid; c <= nc; c += DN_THREADS) camera_update_one(P, c);
     DN_STAMP(8);
 }
 

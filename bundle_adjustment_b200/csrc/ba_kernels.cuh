@@ -168,6 +168,7 @@ struct Params {
     const int* ep_g0;         // [epochs+1 (+2 slack)] first accumulator slot (= row) of an epoch
     const int* slot_row;      // [slots] row of an accumulator slot (rows are camera-major)
     // partial sums
+    int cam_in_backsub;  // dense path: the back-substitution pass carries one extra CTA that moves the cameras (k_tile_pass<1>)
     int lin_gate;        // device-side LM loop: the camera-side linearisation kernels return at once after a rejected step
                          // (the host loop does not launch them then)
     double* cm_partial;  // [cm_tiles*27]

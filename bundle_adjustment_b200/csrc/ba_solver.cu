@@ -1360,6 +1360,11 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     const int check_every = std::max(1, opt->pcg_check_every);
     // small problems: explicit reduced system + dense Cholesky instead of PCG (ba_dense.cuh); no preconditioner needed then
     const bool dense = h->dense_ok && opt->dense_schur != 0 && opt->schur_path == BA_PATH_TILES && h->nranks == 1 && h->P.n_cams > 0;
+    struct FlagScope {  // the flag rides in the kernel parameters of this solve only (also when it throws)
+        int& f;
+        FlagScope(int& flag, int v) : f(flag) { f = v; }
+        ~FlagScope() { f = 0; }
+    } cam_flag(h->P.cam_in_backsub, dense ? 1 : 0);
     const int with_schur = (opt->precond >= BA_PRECOND_SCHUR_JACOBI && !dense) ? 1 : 0;
     if (opt->precond < BA_PRECOND_JACOBI || opt->precond > BA_PRECOND_AUTO) fail(BA_ERR_ARG, "unknown preconditioner %d", opt->precond);
     const int nc1 = P.n_cams + 1;
@@ -1600,11 +1605,12 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
     };
     if (dense) CK(cudaMemsetAsync(h->dn_count.p, 0, sizeof(int), s));
     auto after_pcg = [&]() {
-        if (tiles)
-            launch(h, KN_TILE_BACKSUB, k_tile_pass<1>, h->ft_grid, FT_THREADS, ft_smem_bytes(FT_ROWS_MV), P, (const double*)h->v_x.p);
+        if (tiles)  // dense: one more CTA, which moves the cameras
+            launch(h, KN_TILE_BACKSUB, k_tile_pass<1>, h->ft_grid + (dense ? 1 : 0), FT_THREADS, ft_smem_bytes(FT_ROWS_MV), P,
+                   (const double*)h->v_x.p);
         else
             launch(h, KN_BACKSUB, k_point_pass<1>, P.pm_tiles, PM_THREADS, h->smem_pass, P, (const double*)h->v_x.p);
-        if (!dense) launch(h, KN_CAM_UPDATE, k_camera_update, cdiv(nc1, 128), 128, 0, P);  // dense: done by the solve kernel
+        if (!dense) launch(h, KN_CAM_UPDATE, k_camera_update, cdiv(nc1, 128), 128, 0, P);
         lin_points_and_cost(h, 3, opt->point_linesearch != 0);
         const DecideArgs da{opt->ftol, opt->xtol, opt->lambda_min, opt->lambda_max, opt->max_iters, lm_loop};
         if (!reduce_scalars(h, MASK_LIN | MASK_STEP_PM, MASK_STEP_CAM, &da, dense))

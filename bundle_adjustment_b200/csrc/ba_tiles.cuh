@@ -189,9 +189,19 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
     __shared__ int hs[8];
     __shared__ int es[4];  // [0] first tile of the CTA, [1] epoch length, [2] first epoch, [3] 6 x slots of the current epoch
     if (MODE == 0 && P.st->pcg_done) return;
+    int G = gridDim.x;
+    if (MODE == 1 && P.cam_in_backsub) {
+        // small problems (dense reduced system): the trial poses R <- R Exp(w), t <- t + R v are a 4 us chain of FP64 trigonometry
+        // in one thread per camera; the last CTA of this launch runs it beside the point update instead of after the solve
+        G -= 1;
+        if ((int)blockIdx.x == G) {
+            for (int c = threadIdx.x; c <= P.n_cams; c += FT_THREADS) camera_update_one(P, c);
+            return;
+        }
+    }
     // contiguous run of tiles per CTA: neighbouring tiles share cameras, so the camera vectors stay in L1
-    int t = ft_cta_begin(blockIdx.x, P.ft_tiles, gridDim.x);
-    const int t_end = ft_cta_begin(blockIdx.x + 1, P.ft_tiles, gridDim.x);
+    int t = ft_cta_begin(blockIdx.x, P.ft_tiles, G);
+    const int t_end = ft_cta_begin(blockIdx.x + 1, P.ft_tiles, G);
     if (t >= t_end) return;
     const FtSmem S = ft_carve(sm, FT_ROWS_MV);
     const int b = P.st->cur;
