@@ -595,44 +595,62 @@ __host__ __device__ constexpr size_t cm_smem_bytes() {
 // WARP = true : one warp per tile (<= CM_TILE observations): the N sums of a tile are a shuffle tree, no shared memory,
 //               no barrier - faster when a camera has only a few hundred observations (many cameras, or a rank of a
 //               multi-GPU run that holds 1/N of every camera's observations).
-template <int KIND, bool WARP>
-__global__ void __launch_bounds__(CM_THREADS, 2) k_camera_pass(Params P, const double* __restrict__ vec, int with_schur_diag) {
+template <int KIND, bool WARP, int PRE = 1, int THREADS = CM_THREADS>
+__global__ void __launch_bounds__(THREADS, 2) k_camera_pass(Params P, const double* __restrict__ vec, int with_schur_diag) {
     constexpr int N = CmN<KIND>::value;
-    constexpr int NCH = CmCh<KIND>::value;
-    __shared__ double red[WARP ? 1 : CM_THREADS / 32 * N];
+    constexpr int NPRE = (KIND == 0) ? 3 : ((KIND == 1 && PRE == 2) ? 12 : 6);  // doubles gathered one trip ahead: X [+ z | h] [+ Vinv]
+    __shared__ double red[WARP ? 1 : THREADS / 32 * N];
     __shared__ double tot[WARP ? 1 : N];
+    // the camera's pose in shared memory (broadcast reads), not in 24 registers of every thread: with the 27 accumulators and
+    // the gathers of two trips in flight the kernel otherwise spills at its 128 registers (round 1: STACK 80, LDL 22 / STL 24)
+    __shared__ double sRt[(WARP ? THREADS / 32 : 1) * 12];
     if (KIND == 2 && P.st->pcg_done) return;
     if (KIND == 0 && P.lin_gate && lin_gated(P.st)) return;
     const int lane = WARP ? (threadIdx.x & 31) : threadIdx.x;
-    constexpr int STRIDE = WARP ? 32 : CM_THREADS;
-    const int tile_id = WARP ? blockIdx.x * (CM_THREADS / 32) + (threadIdx.x >> 5) : blockIdx.x;
+    constexpr int STRIDE = WARP ? 32 : THREADS;
+    const int tile_id = WARP ? blockIdx.x * (THREADS / 32) + (threadIdx.x >> 5) : blockIdx.x;
     if (WARP && tile_id >= P.cm_tiles) return;
     const int b = P.st->cur;
     const int4 tile = __ldg(P.cm_tile + tile_id);
     const int cam = tile.x, o0 = tile.y, n = tile.z;
-    double Rt[12], x[6];
-    load_cam(P.cam_R + (size_t)b * (P.n_cams + 1) * 12, cam, Rt);
+    // the records are fetched ahead: the point index two trips ahead, because it is the address of the gathers, and the
+    // gathers themselves (point, and z or h) one trip ahead - a trip is about 200 FP64 instructions, a gather a round trip to L2
+    int p_cur = 0, p_next = 0;
+    if (lane < n) p_cur = __ldg(P.cm_pt + o0 + lane);
+    if (lane + STRIDE < n) p_next = __ldg(P.cm_pt + o0 + lane + STRIDE);
+    double* Rt = sRt + (WARP ? (threadIdx.x >> 5) * 12 : 0);
+    if (lane < 12) Rt[lane] = __ldg(P.cam_R + (size_t)b * (P.n_cams + 1) * 12 + (size_t)cam * 12 + lane);
+    double x[6];
     if (KIND == 2) load_vec6(vec, cam, x);
     double acc[N];
 #pragma unroll
     for (int k = 0; k < N; ++k) acc[k] = 0.0;
-    // the record of the NEXT observation is fetched one trip ahead: its point index is the address of the gathers
+    auto gather = [&](int p, double* rec) {
+        load_pt(P, b, p, rec);
+        if constexpr (KIND == 2) load_v3(P.pt_z + (size_t)p * 4, rec + 3);
+        if constexpr (KIND == 1) load_v3(P.pt_h + (size_t)p * 4, rec + 3);
+        if constexpr (KIND == 1 && PRE == 2) load_sym3(P.pt_Vinv, p, rec + 6);
+    };
     double2 uv_next = make_double2(0.0, 0.0);
-    int p_next = 0;
-    if (lane < n) { uv_next = __ldg(P.cm_uv + o0 + lane); p_next = __ldg(P.cm_pt + o0 + lane); }
+    double rec_next[NPRE];
+#pragma unroll
+    for (int k = 0; k < NPRE; ++k) rec_next[k] = 0.0;
+    if (lane < n) { uv_next = __ldg(P.cm_uv + o0 + lane); gather(p_cur, rec_next); }
+    if (WARP) __syncwarp(); else __syncthreads();
     for (int i = lane; i < n; i += STRIDE) {
         const double2 uvr = uv_next;
-        const int p = p_next;
-        if (i + STRIDE < n) { uv_next = __ldg(P.cm_uv + o0 + i + STRIDE); p_next = __ldg(P.cm_pt + o0 + i + STRIDE); }
-        double rec[2 * NCH];
-        {
-            load_pt(P, b, p, rec);
-            if constexpr (KIND == 2) load_v3(P.pt_z + (size_t)p * 4, rec + 4);
-            if constexpr (KIND == 1) {
-                load_v3(P.pt_h + (size_t)p * 4, rec + 4);
-                load_sym3(P.pt_Vinv, p, rec + 8);
-            }
+        double rec[NPRE];
+#pragma unroll
+        for (int k = 0; k < NPRE; ++k) rec[k] = rec_next[k];
+        double Vi[6];
+        if constexpr (KIND == 1 && PRE != 2) load_sym3(P.pt_Vinv, p_cur, Vi);  // needed late in the trip
+        if constexpr (KIND == 1 && PRE == 2) {
+#pragma unroll
+            for (int k = 0; k < 6; ++k) Vi[k] = rec[6 + k];
         }
+        p_cur = p_next;
+        if (i + 2 * STRIDE < n) p_next = __ldg(P.cm_pt + o0 + i + 2 * STRIDE);
+        if (i + STRIDE < n) { uv_next = __ldg(P.cm_uv + o0 + i + STRIDE); gather(p_cur, rec_next); }
         double2 uv[1] = {uvr};
         constexpr int r = 0;
         const double* X = rec;
@@ -663,7 +681,7 @@ __global__ void __launch_bounds__(CM_THREADS, 2) k_camera_pass(Params P, const d
                 W[0] = ax * o.jx[0] + ay * o.jy[0]; W[1] = ax * o.jx[1] + ay * o.jy[1]; W[2] = ax * o.jx[2] + ay * o.jy[2];
                 W[3] = bx * o.jx[1] + by * o.jy[1]; W[4] = bx * o.jx[2] + by * o.jy[2]; W[5] = cx * o.jx[2] + cy * o.jy[2];
             }
-            const double* h = rec + 4;
+            const double* h = rec + 3;
             double m[3], xm[3];
             sym3_mulv(W, h, m);  // E h = G^T (W h)
             cross3(X, m, xm);
@@ -671,7 +689,6 @@ __global__ void __launch_bounds__(CM_THREADS, 2) k_camera_pass(Params P, const d
             for (int k = 0; k < 3; ++k) { acc[21 + k] += xm[k]; acc[24 + k] += m[k]; }
             if (with_schur_diag) {
                 // T = W Vinv W (sym), correction = G^T T G with G = [-[X]x | I]
-                const double* Vi = rec + 8;
                 const double Wf[9] = {W[0], W[1], W[2], W[1], W[3], W[4], W[2], W[4], W[5]};
                 double A[9];  // A = Vinv W
 #pragma unroll
@@ -711,7 +728,7 @@ __global__ void __launch_bounds__(CM_THREADS, 2) k_camera_pass(Params P, const d
                     for (int c = a; c < 3; ++c) acc[sym6(3 + a, 3 + c)] += Tm[3 * a + c];
             }
         } else {
-            const double* z = rec + 4;
+            const double* z = rec + 3;
             const double d0 = fma(x[1], X[2], fma(-x[2], X[1], x[3])) - z[0];
             const double d1 = fma(x[2], X[0], fma(-x[0], X[2], x[4])) - z[1];
             const double d2 = fma(x[0], X[1], fma(-x[1], X[0], x[5])) - z[2];
@@ -733,7 +750,7 @@ __global__ void __launch_bounds__(CM_THREADS, 2) k_camera_pass(Params P, const d
             if (lane == 0) out[k] = tsum;
         }
     } else {
-        block_sum<N, CM_THREADS>(acc, red, tot);
+        block_sum<N, THREADS>(acc, red, tot);
         __syncthreads();
         if (threadIdx.x < N) out[threadIdx.x] = tot[threadIdx.x];
     }

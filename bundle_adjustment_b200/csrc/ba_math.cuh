@@ -86,13 +86,29 @@ BA_HD void mat3_mul(const double A[9], const double B[9], double C[9]) {
 // ---------------------------------------------------------------------------------------------
 enum { ROBUST_NONE = 0, ROBUST_IRLS = 1, ROBUST_TRIGGS = 2 };
 
+// 1 / d in the hot loops (device): hardware seed (rcp.approx.ftz.f64, about 20 bits) and two Newton steps - five instructions
+// without a branch, accurate to an ulp or two for normal d, against the library division's call with a slow path (three of
+// those per observation were a third of the camera-major passes' FP64 instructions).  d = 0, inf, nan give nan (the division
+// gives inf / 0 / nan): every caller treats non-finite results alike.
+BA_HD double fast_rcp(double d) {
+#ifdef __CUDA_ARCH__
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+    r = fma(r, fma(-d, r, 1.0), r);
+    r = fma(r, fma(-d, r, 1.0), r);
+    return r;
+#else
+    return 1.0 / d;
+#endif
+}
+
 // rho0 = delta^2 * rho((f/delta)^2); wg = rho' (gradient weight); wH = curvature weight.
 BA_HD void robust_weights(double f, double delta, int mode, double& wH, double& wg, double& rho0) {
     const double a = fabs(f);
     if (mode == ROBUST_NONE || a <= delta) {
         wH = 1.0; wg = 1.0; rho0 = f * f;
     } else {
-        wg = delta / a;
+        wg = delta * fast_rcp(a);
         rho0 = delta * (2.0 * a - delta);
         wH = (mode == ROBUST_IRLS) ? wg : DBL_EPSILON;
     }
@@ -123,7 +139,7 @@ BA_D void linearize_obs(const double* Rt, const double X[3], double u, double v,
     const double xc = fma(Rt[0], X[0], fma(Rt[1], X[1], fma(Rt[2], X[2], Rt[9])));
     const double yc = fma(Rt[3], X[0], fma(Rt[4], X[1], fma(Rt[5], X[2], Rt[10])));
     const double zc = fma(Rt[6], X[0], fma(Rt[7], X[1], fma(Rt[8], X[2], Rt[11])));
-    const double iz = 1.0 / zc;
+    const double iz = fast_rcp(zc);
     const double un = xc * iz, vn = yc * iz;
     o.zc = zc;
     o.rx = u - fma(K.fx, un, K.cx);
@@ -141,7 +157,7 @@ BA_D void point_jacobian(const double* Rt, const double X[3], const Intr& K, dou
     const double xc = fma(Rt[0], X[0], fma(Rt[1], X[1], fma(Rt[2], X[2], Rt[9])));
     const double yc = fma(Rt[3], X[0], fma(Rt[4], X[1], fma(Rt[5], X[2], Rt[10])));
     const double zc = fma(Rt[6], X[0], fma(Rt[7], X[1], fma(Rt[8], X[2], Rt[11])));
-    const double iz = 1.0 / zc;
+    const double iz = fast_rcp(zc);
     const double un = xc * iz, vn = yc * iz;
     const double sx = -K.fx * iz, sy = -K.fy * iz;
 #pragma unroll
@@ -172,15 +188,17 @@ BA_HD void sym3_mulv(const double S[6], const double x[3], double y[3]) {
 BA_HD bool sym3_inverse(const double A[6], double Ai[6]) {
     const double d0 = A[0];
     if (!(d0 > 0.0)) return false;
-    const double l10 = A[1] / d0, l20 = A[2] / d0;
+    const double i0 = fast_rcp(d0);
+    const double l10 = A[1] * i0, l20 = A[2] * i0;
     const double d1 = A[3] - l10 * A[1];
     if (!(d1 > 0.0)) return false;
-    const double l21 = (A[4] - l20 * A[1]) / d1;
+    const double i1 = fast_rcp(d1);
+    const double l21 = (A[4] - l20 * A[1]) * i1;
     const double d2 = A[5] - l20 * A[2] - l21 * l21 * d1;
     if (!(d2 > 0.0)) return false;
+    const double i2 = fast_rcp(d2);
     // L^-1 = [[1,0,0],[-l10,1,0],[l10*l21-l20,-l21,1]]
     const double m10 = -l10, m20 = l10 * l21 - l20, m21 = -l21;
-    const double i0 = 1.0 / d0, i1 = 1.0 / d1, i2 = 1.0 / d2;
     Ai[0] = i0 + m10 * m10 * i1 + m20 * m20 * i2;
     Ai[1] = m10 * i1 + m20 * m21 * i2;
     Ai[2] = m20 * i2;

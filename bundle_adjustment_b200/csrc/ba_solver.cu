@@ -1318,8 +1318,17 @@ static const unsigned MASK_STEP_CAM = (1u << S_GDC) | (1u << S_DDC) | (1u << S_R
 template <int KIND>
 static void launch_camera_pass(ba_handle* h, Kind kind, const double* vec, int with_schur) {
     const Params& P = h->P;
-    if (h->cm_warp) launch(h, kind, k_camera_pass<KIND, true>, cdiv(P.cm_tiles, CM_THREADS / 32), CM_THREADS, 0, P, vec, with_schur);
-    else launch(h, kind, k_camera_pass<KIND, false>, P.cm_tiles, CM_THREADS, 0, P, vec, with_schur);
+    if constexpr (KIND == 1) {
+        // the Schur-assembly pass holds 27 accumulators, the point record of two trips and a dozen 3x3 temporaries: 192-thread
+        // CTAs leave it 170 registers (no spills; at 256 threads / 128 registers it spilled 56-88 bytes and ran 160-180 us on
+        // the venice shape against 121 us), gathers of the next trip - X, h and V^-1 - in flight
+        constexpr int T1 = 192;
+        if (h->cm_warp) launch(h, kind, k_camera_pass<KIND, true, 2, T1>, cdiv(P.cm_tiles, T1 / 32), T1, 0, P, vec, with_schur);
+        else launch(h, kind, k_camera_pass<KIND, false, 2, T1>, P.cm_tiles, T1, 0, P, vec, with_schur);
+    } else {
+        if (h->cm_warp) launch(h, kind, k_camera_pass<KIND, true>, cdiv(P.cm_tiles, CM_THREADS / 32), CM_THREADS, 0, P, vec, with_schur);
+        else launch(h, kind, k_camera_pass<KIND, false>, P.cm_tiles, CM_THREADS, 0, P, vec, with_schur);
+    }
 }
 
 static const double kDiagMin = 1e-6, kDiagMax = 1e32;
