@@ -462,7 +462,36 @@ def test_full_size_properties(gpu_solver, name):
     r = gpu_solver.residuals()
     assert abs(O.huber_cost(r) - st["final_cost"]) <= 1e-9 * st["final_cost"]
     assert abs(float((r * r).sum()) - st["final_raw_cost"]) <= 1e-9 * st["final_raw_cost"]
-    del prob
+    # (4) at the point the solve reached, the WHOLE linearisation against the oracle's (analytic blocks over all observations,
+    #     oracle/lm_schur.py::linearize): camera and point gradients, U and V blocks, and the gradient maximum the stopping
+    #     rule tests.  Tolerance 1e-9 of each block set's norm (float64 sums over up to 5 M terms in different orders).
+    rvec, tvec, pts = gpu_solver.get_params()
+    nb = gpu_solver.normal_blocks()
+    lin = L.linearize(prob, rvec, tvec, pts)
+    for key, ref in (("gc", lin.gc), ("gp", lin.gp), ("U", lin.U), ("V", lin.V)):
+        assert np.linalg.norm(nb[key] - ref) <= 1e-9 * np.linalg.norm(ref), key
+    gmax = max(np.abs(lin.gc).max(), np.abs(lin.gp).max())
+    assert abs(max(np.abs(nb["gc"]).max(), np.abs(nb["gp"]).max()) - gmax) <= 1e-9 * gmax
+    if name == "ladybug":
+        # (5) one application of the damped Schur complement at that point against the oracle's implicit product
+        lam = 1e-4
+        rng = np.random.default_rng(5)
+        u = rng.normal(size=(fp.n_cams, 6))
+        w_dev = gpu_solver.schur_matvec(u, lam)
+        adj = prob.obs_cam >= 0
+        ca, pa = prob.obs_cam[adj], prob.obs_pt[adj]
+        Dp = np.clip(np.einsum("nii->ni", lin.V), 1e-6, 1e32)
+        Dc = np.clip(np.einsum("nii->ni", lin.U), 1e-6, 1e32)
+        Vd = lin.V.copy()
+        Vd[:, [0, 1, 2], [0, 1, 2]] += lam * Dp
+        E = np.einsum("nki,nk,nkj->nij", lin.Jc[adj], lin.wH[adj], lin.Jp[adj])
+        t = np.zeros((fp.n_pts, 3))
+        np.add.at(t, pa, np.einsum("nij,ni->nj", E, u[ca]))
+        z = np.einsum("nij,nj->ni", np.linalg.inv(Vd), t)
+        w = np.einsum("nij,nj->ni", lin.U, u) + lam * Dc * u
+        np.subtract.at(w, ca, np.einsum("nij,nj->ni", E, z[pa]))
+        assert np.linalg.norm(w_dev - w) <= 1e-9 * np.linalg.norm(w)
+    del prob, lin
 
 
 def test_two_level_preconditioner_against_the_cpu_statement(gpu_solver):
