@@ -2564,6 +2564,11 @@ int ba_map_stats(ba_handle* h, int64_t out[8]) {
 }  // extern "C"
 
 #ifdef BA_DN_STAMPS
+extern "C" int ba_ls_moved(unsigned long long out[8]) {  // reads and clears (scripts/ls_moved.py)
+    unsigned long long z[8] = {0};
+    if (cudaMemcpyFromSymbol(out, ba::g_ls_moved, sizeof z) != cudaSuccess) return -2;
+    return cudaMemcpyToSymbol(ba::g_ls_moved, z, sizeof z) == cudaSuccess ? 0 : -2;
+}
 extern "C" int ba_dn_stamps(unsigned long long out[16]) {
     return cudaMemcpyFromSymbol(out, ba::g_dn_stamps, 16 * sizeof(unsigned long long)) == cudaSuccess ? 0 : -2;
 }

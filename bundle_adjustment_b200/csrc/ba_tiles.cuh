@@ -446,6 +446,9 @@ BA_D void cp_async16(void* smem, const void* gmem) {
 // of iterations; the search lets those few points jump (CPU statement: oracle/lm_schur.py::point_linesearch).  The six
 // candidate costs of an observation go through the same transposed track layout as the nine sums of the linearisation
 // (before them, in the same scratch), the chosen position replaces the trial point in HBM and is linearised right away.
+#ifdef BA_DN_STAMPS
+__device__ unsigned long long g_ls_moved[8];  // experiment builds: points whose line search chose candidate k
+#endif
 constexpr int LS_K = 6;
 __device__ __constant__ double kLsAlpha[LS_K] = {1.0, 0.5, 2.0, 4.0, 8.0, 16.0};
 
@@ -559,6 +562,9 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_lin(Params 
                 double X0[3], X1[3];
                 load_pt(P, cur, p0 + tid, X0);
                 load_pt(P, b, p0 + tid, X1);
+#ifdef BA_DN_STAMPS
+                atomicAdd(&g_ls_moved[kb], 1ull);
+#endif
                 if (kb != 0) {
                     const double al = kLsAlpha[kb];
 #pragma unroll
