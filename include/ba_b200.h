@@ -88,7 +88,7 @@ typedef struct ba_options {
                                  {1, 1/2, 2, 4, 8, 16} with the smallest Huber cost over its observations (cameras at the trial
                                  poses; the total cost can only go down against the plain step).  0: plain LM steps           */
     int32_t dense_schur;      /* 1 (default): single-GPU problems with at most 16 adjustable cameras (the pipeline's windows) assemble the
-                                 reduced camera system explicitly and solve it by a dense Cholesky factorisation - the exact LM step in
+                                 reduced camera system explicitly and solve it by a dense factorisation (L D L^T by one warp up to 32 unknowns, else Cholesky) - the exact LM step in
                                  two kernels - instead of PCG (csrc/ba_dense.cuh).  0: PCG always                              */
 } ba_options;
 
@@ -109,7 +109,7 @@ typedef struct ba_stats {
     int32_t coarse_builds;    /* coarse matrices built during the solve                                                 */
     int32_t coarse_matvecs;   /* tile-pass mat-vecs spent on probing them (not counted in pcg_iterations)               */
     int32_t coarse_unknowns;  /* size of the coarse system (6 x aggregates), 0 if none                                  */
-    int32_t dense_solves;     /* LM iterations whose step came from the dense Cholesky path (0: PCG was used)           */
+    int32_t dense_solves;     /* LM iterations whose step came from the dense factorisation (0: PCG was used)         */
     int32_t reserved_i;
     double reserved[5];
 } ba_stats;
