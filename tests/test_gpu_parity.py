@@ -440,8 +440,11 @@ def test_error_reporting(gpu_solver):
 # ------------------------------------------------------------------------------------------------
 # full-size, size-independent properties (configs 3 and 4)
 # ------------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("name", ["ladybug", "venice"])
+@pytest.mark.parametrize("name", ["ladybug", "venice", "shard50m"])
 def test_full_size_properties(gpu_solver, name):
+    """BASELINE configs 3, 4 and 5 at full size.  The 50 M-observation problem (config 5) takes about a minute to generate
+    and skips the whole-problem linearisation check of step (4) (the oracle's dense blocks of 50 M observations do not fit a
+    test); its residual rows and costs are checked like the others'."""
     fp = S.make_named_problem(name, keep_truth=False)
     gpu_solver.set_flat(fp)
     # (1) the device's reduced cost equals the cost of the residual vector it returns
@@ -462,6 +465,9 @@ def test_full_size_properties(gpu_solver, name):
     r = gpu_solver.residuals()
     assert abs(O.huber_cost(r) - st["final_cost"]) <= 1e-9 * st["final_cost"]
     assert abs(float((r * r).sum()) - st["final_raw_cost"]) <= 1e-9 * st["final_raw_cost"]
+    if name == "shard50m":
+        del prob
+        return
     # (4) at the point the solve reached, the WHOLE linearisation against the oracle's (analytic blocks over all observations,
     #     oracle/lm_schur.py::linearize): camera and point gradients, U and V blocks, and the gradient maximum the stopping
     #     rule tests.  Tolerance 1e-9 of each block set's norm (float64 sums over up to 5 M terms in different orders).
