@@ -260,9 +260,10 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
         }
         mbar_wait(S.bar + 1, it & 1);  // every thread sees group 2 complete BEFORE the barrier, so re-arming is safe after it
         __syncthreads();
-        if (MODE == 0 && have_next && issuer) {
+        if (have_next && issuer) {
             // phase A has its operands in registers: observation records, Jacobian cache, points and the segment table of
-            // the next tile may land.  The next header goes to shared memory here; everybody reads it after later barriers.
+            // the next tile may land (MODE 1 reads the points of phase B from HBM for that reason).  The next header goes to
+            // shared memory here; everybody reads it after later barriers.
             ft_issue_group1<MODE>(P, S, Tn, b, buf ^ 1, S.bar);
             hs[0] = Tn.p0; hs[1] = Tn.m; hs[2] = Tn.o0; hs[3] = Tn.n; hs[4] = Tn.s0; hs[5] = Tn.ns; hs[6] = Tn.r0; hs[7] = Tn.maxlen;
         }
@@ -326,7 +327,7 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
                     if (valid && k == 2) S.sZ2[q] = zk;
                 } else if (valid && k < 3) {
                     const size_t p = (size_t)(T.p0 + q), p4 = p * 4 + k;
-                    const double Xk = k < 2 ? reinterpret_cast<const double*>(S.sX01)[2 * q + k] : S.sX2[(T.p0 & 1) + q];
+                    const double Xk = __ldg(pt_base(P, b) + (k < 2 ? 2 * p + k : 2 * (size_t)P.n_pad + p));
                     const double dp = -__ldg(P.pt_h + p4) - zk;
                     const double gk = __ldg(P.pt_g + (size_t)b * P.n_pts * 4 + p4), Dk = __ldg(P.pt_D + p4);
                     double* out = P.pt_X + (size_t)(b ^ 1) * P.pt_stride;
@@ -342,11 +343,7 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
                 double* out = P.pm_partial + (size_t)t * NSCAL;
                 out[S_GDP] = tot[0]; out[S_DDP] = tot[1]; out[S_DP2] = tot[2]; out[S_XP2] = tot[3];
             }
-            if (have_next && issuer) {  // phase B has read the points: everything may be refilled now
-                ft_issue_group1<MODE>(P, S, Tn, b, buf ^ 1, S.bar);
-                ft_issue_group2(P, S, Tn, S.bar + 1);
-                hs[0] = Tn.p0; hs[1] = Tn.m; hs[2] = Tn.o0; hs[3] = Tn.n; hs[4] = Tn.s0; hs[5] = Tn.ns; hs[6] = Tn.r0; hs[7] = Tn.maxlen;
-            }
+            if (have_next && issuer) ft_issue_group2(P, S, Tn, S.bar + 1);  // phase B is over: V^-1 and the track tables may be refilled
             if (!have_next) break;
             __syncthreads();
         } else {
