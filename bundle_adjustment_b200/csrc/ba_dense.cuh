@@ -245,7 +245,7 @@ __global__ void __launch_bounds__(DN_THREADS) k_dense_schur(Params P, const int4
 #pragma unroll
         for (int a = 0; a < 6; ++a)
 #pragma unroll
-            for (int q = 0; q < 6; ++q) acc[6 * a + q] += cxi[a] * Tx[q] + cyi[a] * Ty[q];
+            for (int q = 0; q < 6; ++q) acc[6 * a + q] = fma(cxi[a], Tx[q], fma(cyi[a], Ty[q], acc[6 * a + q]));
         if (self) {
             const double2 rho = Rb[pr.x];
             double h[3];
@@ -253,9 +253,9 @@ __global__ void __launch_bounds__(DN_THREADS) k_dense_schur(Params P, const int4
             const double ex = jxi[0] * h[0] + jxi[1] * h[1] + jxi[2] * h[2], ey = jyi[0] * h[0] + jyi[1] * h[1] + jyi[2] * h[2];
 #pragma unroll
             for (int a = 0; a < 6; ++a) {
-                acc[36 + a] += cxi[a] * cxi[a] + cyi[a] * cyi[a];
-                acc[42 + a] += cxi[a] * rho.x + cyi[a] * rho.y;
-                acc[48 + a] += cxi[a] * ex + cyi[a] * ey;
+                acc[36 + a] = fma(cxi[a], cxi[a], fma(cyi[a], cyi[a], acc[36 + a]));
+                acc[42 + a] = fma(cxi[a], rho.x, fma(cyi[a], rho.y, acc[42 + a]));
+                acc[48 + a] = fma(cxi[a], ex, fma(cyi[a], ey, acc[48 + a]));
             }
         }
     }

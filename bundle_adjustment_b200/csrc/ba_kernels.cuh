@@ -670,8 +670,8 @@ __global__ void __launch_bounds__(THREADS, 2) k_camera_pass(Params P, const doub
             for (int a = 0; a < 6; ++a) {
                 const double sx = wHx * jcx[a], sy = wHy * jcy[a];
 #pragma unroll
-                for (int c = a; c < 6; ++c) { acc[q] += sx * jcx[c] + sy * jcy[c]; ++q; }
-                acc[21 + a] += jcx[a] * gx + jcy[a] * gy;
+                for (int c = a; c < 6; ++c) { acc[q] = fma(sx, jcx[c], fma(sy, jcy[c], acc[q])); ++q; }  // two FMAs, not mul + fma + add
+                acc[21 + a] = fma(jcx[a], gx, fma(jcy[a], gy, acc[21 + a]));
             }
         } else if constexpr (KIND == 1) {
             double W[6];  // W = Jp^T diag(wH) Jp (sym 3x3)

@@ -2,7 +2,7 @@
 FP64 arithmetic (DFMA/DADD/DMUL), bulk asynchronous copies (UBLKCP = cp.async.bulk, SYNCS = mbarrier), no
 floating-point atomics (ATOM/RED absent), shuffles, barriers.
 
-    python scripts/sass_summary.py [out_dir]        -> <out_dir>/r01j_sass_summary.txt, r01j_sass_tile_pass.txt
+    python scripts/sass_summary.py [out_dir] [tag]   -> <out_dir>/<tag>_sass_summary.txt, <tag>_sass_tile_pass.txt  (tag: r02t)
 """
 import collections
 import os
@@ -12,6 +12,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 out_dir = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "profiles")
+tag = sys.argv[2] if len(sys.argv) > 2 else "r02t"
 so = os.path.join(ROOT, "bundle_adjustment_b200", "libba_b200.so")
 sass = subprocess.run(["cuobjdump", "-sass", so], capture_output=True, text=True, check=True).stdout
 res = subprocess.run(["cuobjdump", "-res-usage", so], capture_output=True, text=True, check=True).stdout
@@ -44,10 +45,10 @@ for f in funcs:
     lines.append(f"    floating-point atomics: {len(fp_atomics)}")
     lines.append("")
 os.makedirs(out_dir, exist_ok=True)
-with open(os.path.join(out_dir, "r01j_sass_summary.txt"), "w") as fh:
+with open(os.path.join(out_dir, tag + "_sass_summary.txt"), "w") as fh:
     fh.write("\n".join(lines))
 if tile:
-    with open(os.path.join(out_dir, "r01j_sass_tile_pass.txt"), "w") as fh:
+    with open(os.path.join(out_dir, tag + "_sass_tile_pass.txt"), "w") as fh:
         body = tile[1].split("\n", 1)[1]
         keep = [re.sub(r"\s*/\* 0x[0-9a-f]{16} \*/\s*$", "", ln).rstrip() for ln in body.splitlines()]
         fh.write(f"Function : {tile[0]}\n" + "\n".join(ln for ln in keep if ln.strip()) + "\n")
