@@ -411,6 +411,9 @@ struct ba_handle {
     size_t tail_cached_bytes = 0;
     int ep_target = 0, n_epochs = 0, n_slots = 0, max_ep_slots = 0;
     DBuf<int> seg_slot, slot_row, ep_g0, cta_ep0, cam_row_off2;
+    DBuf<int> seg_item;      // packed phase-D work items of the accumulator pass (k_ft_item_fill), 8 per quarter-warp
+    DBuf<int4> ft_hdr_acc;   // tile headers of the accumulator pass: (first item, item slots) instead of (first segment, segments)
+    long long n_item_slots = 0;
     int ft_tiles = 0, n_seg = 0, ft_grid = 0, sm_count = 0;
     std::vector<int> ft_pt_h, ft_obs_h, ft_maxlen_h;  // host copy of the tile cuts and longest tracks (empty: no tiles)
     DBuf<int> ft_pt, ft_obs, ft_seg, ft_rs, seg_cam, seg_info, seg_row, cam_row_off;
@@ -777,6 +780,28 @@ static void build_tiles(ba_handle* h, int n_cams, int n_pts, int n_obs) {
             launch(h, KN_SETUP, k_lower_bound_u32, cdiv(n_cams + 2, B), B, 0, R, (const unsigned*)scam_s.p, n_cams + 2, h->cam_row_off2.p);
             h->acc_ok = true;
         }
+        if (h->acc_ok) {
+            // phase-D work items, dealt so that the lanes of a quarter-warp start in different shared-memory bank groups
+            TBuf<int> nq, q_off;
+            nq.alloc((size_t)T + 1); q_off.alloc((size_t)T + 1);
+            nq.zero(s);
+            size_t tbq = 0;
+            CK(cub::DeviceScan::ExclusiveSum(nullptr, tbq, nq.p, q_off.p, T + 1, s));
+            if (tbq > tmp.n) { CK(cudaStreamSynchronize(s)); tmp.alloc(tbq); }
+            launch(h, KN_SETUP, k_ft_item_count, cdiv(T, B), B, 0, T, (const int*)h->ft_seg.p, (const int*)h->seg_info.p, nq.p);
+            tb = tmp.n;
+            CK(cub::DeviceScan::ExclusiveSum(tmp.p, tb, nq.p, q_off.p, T + 1, s));
+            h->launches[KN_SETUP] += 1;
+            int Q = 0;
+            CK(cudaMemcpyAsync(&Q, q_off.p + T, sizeof(int), cudaMemcpyDeviceToHost, s));
+            CK(cudaStreamSynchronize(s));
+            h->n_item_slots = 8LL * Q;
+            h->seg_item.alloc((size_t)8 * Q + 8);  // + TMA window slack
+            h->seg_item.zero(s);
+            h->ft_hdr_acc.alloc(2 * (size_t)T);
+            launch(h, KN_SETUP, k_ft_item_fill, cdiv(T, B), B, 0, T, (const int*)h->ft_seg.p, (const int*)h->seg_info.p,
+                   (const int*)h->seg_slot.p, (const int*)q_off.p, (const int4*)h->ft_hdr.p, h->seg_item.p, h->ft_hdr_acc.p);
+        }
     }
     CK(cudaStreamSynchronize(s));  // scratch dies here
     h->fused_ok = true;
@@ -827,6 +852,7 @@ static Params matvec_params(const ba_handle* h, bool acc) {
     Params Q = h->P;
     if (acc) {
         Q.seg_row = h->seg_slot.p; Q.cam_row_off = h->cam_row_off2.p; Q.ep_target = h->ep_target;
+        Q.seg_info = h->seg_item.p; Q.ft_hdr = h->ft_hdr_acc.p;  // packed work items instead of the segment table
         Q.cta_ep0 = h->cta_ep0.p; Q.ep_g0 = h->ep_g0.p; Q.slot_row = h->slot_row.p;
     }
     return Q;

@@ -56,6 +56,9 @@ __host__ __device__ inline int ft_epoch_len(int len, int target) {
 // Vinv x2 ... | track offsets x2 | track-row starts x2 | segment table x2 | segment rows x2 | two mbarriers.  The x2 regions are double-buffered
 // by tile parity; everything else is refilled by the TMA as soon as its last reader has passed a barrier.
 constexpr int FT_META_N = FT_THREADS + 2, FT_OFF_N = FT_PTS + 8, FT_SEG_N = FT_THREADS + 8;
+// With epoch accumulators the segment table and the row table (2 x 2 x FT_SEG_N ints) hold the tile's packed WORK ITEMS of
+// phase D instead (k_ft_item_fill): two buffers of FT_ITEM_N ints, i.e. at most FT_ITEM_QMAX quarter-warps of eight items.
+constexpr int FT_ITEM_N = 2 * FT_SEG_N, FT_ITEM_QMAX = FT_ITEM_N / 8;
 struct FtSmem {
     double* sA;  // [3][FT_LDB] point-side scratch (phases A/B); separate from sO so that phase D of a tile and phase A of the next overlap
     double* sO;  // [3][FT_LD] double2: (X x m, m) of every observation as three value pairs (phases C/D)
@@ -142,17 +145,18 @@ struct TileCopy {  // 16-byte aligned source windows of one tile
     int meta_lo, off_lo, seg_lo;  // first element copied (<= the tile's first) of tc_meta / pt_off / seg arrays
 };
 
-template <int MODE>
+template <int MODE, bool ACC = false>
 BA_D void ft_issue_group1(const Params& P, const FtSmem& S, const TileHdr& T, int b, int buf, unsigned long long* bar) {
     const int meta_lo = T.o0 & ~1, seg_lo = T.s0 & ~3;
     const unsigned meta_b = (unsigned)(((T.o0 + T.n - meta_lo) * 8 + 15) & ~15);
     const unsigned j_b = (unsigned)T.n * 16u, x01_b = (unsigned)T.m * 16u;
     const int x2_lo = T.p0 & ~1;
     const unsigned x2_b = (unsigned)(((T.p0 + T.m - x2_lo) * 8 + 15) & ~15);
+    // ACC: (s0, ns) of the header = (first work item, work item slots) of the tile, both multiples of 8
     const unsigned seg_b = (unsigned)(((T.s0 + T.ns - seg_lo) * 4 + 15) & ~15);
     unsigned total = x01_b + x2_b;
     if (T.n > 0) total += meta_b + 3 * j_b;
-    if (MODE == 0 && seg_b) total += 2 * seg_b;
+    if (MODE == 0 && seg_b) total += ACC ? seg_b : 2 * seg_b;
     mbar_expect_tx(bar, total);
     if (T.n > 0) {
         tma_load(S.sMeta, P.tc_meta + meta_lo, meta_b, bar);
@@ -163,8 +167,12 @@ BA_D void ft_issue_group1(const Params& P, const FtSmem& S, const TileHdr& T, in
     tma_load(S.sX01, reinterpret_cast<const double2*>(pt_base(P, b)) + T.p0, x01_b, bar);
     tma_load(S.sX2, pt_base(P, b) + 2 * (size_t)P.n_pad + x2_lo, x2_b, bar);
     if (MODE == 0 && seg_b) {
-        tma_load(S.sSeg + buf * FT_SEG_N, P.seg_info + seg_lo, seg_b, bar);
-        tma_load(S.sRow + buf * FT_SEG_N, P.seg_row + seg_lo, seg_b, bar);
+        if (ACC) {
+            tma_load(S.sSeg + buf * FT_ITEM_N, P.seg_info + seg_lo, seg_b, bar);
+        } else {
+            tma_load(S.sSeg + buf * FT_SEG_N, P.seg_info + seg_lo, seg_b, bar);
+            tma_load(S.sRow + buf * FT_SEG_N, P.seg_row + seg_lo, seg_b, bar);
+        }
     }
 }
 BA_D void ft_issue_group2(const Params& P, const FtSmem& S, const TileHdr& T, unsigned long long* bar) {
@@ -216,7 +224,7 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
         mbar_init(S.bar + 1, 1);
         asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
-        ft_issue_group1<MODE>(P, S, T, b, 0, S.bar);
+        ft_issue_group1<MODE, ACC>(P, S, T, b, 0, S.bar);
         ft_issue_group2(P, S, T, S.bar + 1);
     }
     __syncthreads();
@@ -264,7 +272,7 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
             // phase A has its operands in registers: observation records, Jacobian cache, points and the segment table of
             // the next tile may land (MODE 1 reads the points of phase B from HBM for that reason).  The next header goes to
             // shared memory here; everybody reads it after later barriers.
-            ft_issue_group1<MODE>(P, S, Tn, b, buf ^ 1, S.bar);
+            ft_issue_group1<MODE, ACC>(P, S, Tn, b, buf ^ 1, S.bar);
             hs[0] = Tn.p0; hs[1] = Tn.m; hs[2] = Tn.o0; hs[3] = Tn.n; hs[4] = Tn.s0; hs[5] = Tn.ns; hs[6] = Tn.r0; hs[7] = Tn.maxlen;
         }
         if (ACC && tid >= FT_THREADS - 32 && ep_pos == 0) {
@@ -366,29 +374,49 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_pass(Params
             __syncthreads();
 
             // ---- phase D: one thread per (segment, pair of components): fixed-order sum -> one row per segment ---
-            const int* seg_i = S.sSeg + buf * FT_SEG_N + (T.s0 & 3);
-            const int* seg_r = S.sRow + buf * FT_SEG_N + (T.s0 & 3);
-            for (int w0 = tid & ~31; w0 < T.ns * 3; w0 += FT_THREADS) {  // warp-uniform bounds
-                const int w = w0 + (tid & 31);
-                const bool valid = w < T.ns * 3;
-                const int seg = w / 3, pr = w - 3 * seg;
-                const int info = valid ? seg_i[seg] : 0;  // first tile-camera position | length << 16; longest first
-                const int a = info & 0xffff, len = info >> 16;
-                const int wmax = __reduce_max_sync(0xffffffffu, len);
-                const double2* src = reinterpret_cast<const double2*>(S.sO) + pr * FT_LD + a;
-                // a slot occurs at most once per tile; its running sum is fetched ahead of the segment's loop
-                double2* slot = ACC ? reinterpret_cast<double2*>(S.sAcc + (valid ? seg_r[seg] * 6 + 2 * pr : 0)) : nullptr;
-                const double2 before = (ACC && valid) ? *slot : make_double2(0.0, 0.0);
-                double sx = 0.0, sy = 0.0;
-                for (int j0 = 0; j0 < wmax; j0 += 2) {
-                    const double2 z2 = make_double2(0.0, 0.0);
-                    const double2 v0 = (j0 < len) ? src[j0] : z2, v1 = (j0 + 1 < len) ? src[j0 + 1] : z2;
-                    sx += v0.x; sy += v0.y;
-                    sx += v1.x; sy += v1.y;
+            if constexpr (ACC) {
+                // Work items (segment, pair) packed by k_ft_item_fill: the eight lanes of a quarter-warp start in eight
+                // different 16-byte bank groups, so every step of the loop below is one conflict-free wavefront per
+                // quarter-warp (lanes side by side in the segment-major numbering collide 2.3-fold on average).
+                // item = first position | length << 8 | pair << 13 | accumulator slot << 15; 0 = empty lane.
+                const int* items = S.sSeg + buf * FT_ITEM_N;
+                for (int w0 = tid & ~31; w0 < T.ns; w0 += FT_THREADS) {  // warp-uniform bounds
+                    const int w = w0 + (tid & 31);
+                    const int item = w < T.ns ? items[w] : 0;
+                    const int a = item & 255, len = (item >> 8) & 31, pr = (item >> 13) & 3;
+                    const int wmax = __reduce_max_sync(0xffffffffu, len);
+                    const double2* src = reinterpret_cast<const double2*>(S.sO) + pr * FT_LD + a;
+                    // a slot occurs at most once per tile; its running sum is fetched ahead of the segment's loop
+                    double2* slot = reinterpret_cast<double2*>(S.sAcc + (item >> 15) * 6 + 2 * pr);
+                    const double2 before = len ? *slot : make_double2(0.0, 0.0);
+                    double sx = 0.0, sy = 0.0;
+                    for (int j0 = 0; j0 < wmax; j0 += 2) {
+                        const double2 z2 = make_double2(0.0, 0.0);
+                        const double2 v0 = (j0 < len) ? src[j0] : z2, v1 = (j0 + 1 < len) ? src[j0 + 1] : z2;
+                        sx += v0.x; sy += v0.y;
+                        sx += v1.x; sy += v1.y;
+                    }
+                    if (len) *slot = make_double2(before.x + sx, before.y + sy);
                 }
-                if (valid) {
-                    if (ACC) *slot = make_double2(before.x + sx, before.y + sy);
-                    else *reinterpret_cast<double2*>(P.rows + (size_t)seg_r[seg] * 6 + 2 * pr) = make_double2(sx, sy);
+            } else {
+                const int* seg_i = S.sSeg + buf * FT_SEG_N + (T.s0 & 3);
+                const int* seg_r = S.sRow + buf * FT_SEG_N + (T.s0 & 3);
+                for (int w0 = tid & ~31; w0 < T.ns * 3; w0 += FT_THREADS) {  // warp-uniform bounds
+                    const int w = w0 + (tid & 31);
+                    const bool valid = w < T.ns * 3;
+                    const int seg = w / 3, pr = w - 3 * seg;
+                    const int info = valid ? seg_i[seg] : 0;  // first tile-camera position | length << 16; longest first
+                    const int a = info & 0xffff, len = info >> 16;
+                    const int wmax = __reduce_max_sync(0xffffffffu, len);
+                    const double2* src = reinterpret_cast<const double2*>(S.sO) + pr * FT_LD + a;
+                    double sx = 0.0, sy = 0.0;
+                    for (int j0 = 0; j0 < wmax; j0 += 2) {
+                        const double2 z2 = make_double2(0.0, 0.0);
+                        const double2 v0 = (j0 < len) ? src[j0] : z2, v1 = (j0 + 1 < len) ? src[j0 + 1] : z2;
+                        sx += v0.x; sy += v0.y;
+                        sx += v1.x; sy += v1.y;
+                    }
+                    if (valid) *reinterpret_cast<double2*>(P.rows + (size_t)seg_r[seg] * 6 + 2 * pr) = make_double2(sx, sy);
                 }
             }
         }
@@ -866,6 +894,63 @@ __global__ void k_ft_slot_assign(int n_seg, int n_ep, const unsigned long long* 
     seg_slot[order[i]] = g - ep_g0[lo];
     if (i == 0 || key_s[i] != key_s[i - 1]) { slot_cam[g] = (unsigned)((key_s[i] >> 8) & 0xffffffffu); iota[g] = g; }
 }
+// ---- packed work items of phase D (mat-vec pass with epoch accumulators) ----------------------------------------------
+// A work item = (segment, pair of components): one lane adds the segment's double2 values at positions a .. a+len-1 of plane
+// `pair` (plane stride FT_LD = 3 mod 8 sixteen-byte bank groups).  All lanes of a quarter-warp read element j of their item
+// in the same LDS.128, so the quarter-warp is conflict-free iff its eight items START in eight different bank groups,
+// g = (a + 3 pair) mod 8.  The items of a tile (segments longest first) are therefore dealt into eight queues by g;
+// quarter-warp k takes the k-th item of every queue (lane = g; an exhausted queue leaves an empty lane).  The k-th items
+// are about equally long, so the lanes of a warp still run equally long loops.  A tile whose longest queue would not fit
+// the shared-memory table falls back to the dense numbering (eight consecutive items per quarter-warp).
+// item = a | len << 8 | pair << 13 | accumulator slot << 15 (a < 256, len <= 16, slot < 128); 0 = empty lane.
+BA_D int ft_item_quarters(int s0, int s1, const int* __restrict__ seg_info, bool& dense) {
+    unsigned long long cnt = 0;  // eight 8-bit counters
+    for (int s = s0; s < s1; ++s) {
+        const int a = __ldg(seg_info + s) & 0xffff;
+#pragma unroll
+        for (int pr = 0; pr < 3; ++pr) cnt += 1ull << (8 * ((a + 3 * pr) & 7));
+    }
+    int q = 0;
+#pragma unroll
+    for (int g = 0; g < 8; ++g) q = max(q, (int)((cnt >> (8 * g)) & 255));
+    dense = q > FT_ITEM_QMAX || (s1 - s0) > 84;  // (a counter may not overflow: 3 x 84 < 256)
+    return dense ? (3 * (s1 - s0) + 7) / 8 : q;
+}
+__global__ void k_ft_item_count(int n_tiles, const int* __restrict__ ft_seg, const int* __restrict__ seg_info, int* __restrict__ nq) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_tiles) return;
+    bool dense;
+    nq[t] = ft_item_quarters(__ldg(ft_seg + t), __ldg(ft_seg + t + 1), seg_info, dense);
+}
+// q_off = exclusive sum of nq; `items` is zeroed by the caller.  Also writes the tile headers of the accumulator pass:
+// the second int4 = (first item, item slots, first track row, longest track).
+__global__ void k_ft_item_fill(int n_tiles, const int* __restrict__ ft_seg, const int* __restrict__ seg_info,
+                               const int* __restrict__ seg_slot, const int* __restrict__ q_off, const int4* __restrict__ hdr,
+                               int* __restrict__ items, int4* __restrict__ hdr_acc) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_tiles) return;
+    const int s0 = __ldg(ft_seg + t), s1 = __ldg(ft_seg + t + 1);
+    bool dense;
+    const int nq = ft_item_quarters(s0, s1, seg_info, dense);
+    int* out = items + 8 * (size_t)q_off[t];
+    unsigned long long cnt = 0;
+    int n = 0;
+    for (int s = s0; s < s1; ++s) {
+        const int info = __ldg(seg_info + s), a = info & 0xffff, len = info >> 16;
+        const int base = a | (len << 8) | (__ldg(seg_slot + s) << 15);
+#pragma unroll
+        for (int pr = 0; pr < 3; ++pr) {
+            const int g = (a + 3 * pr) & 7;
+            const int k = (int)((cnt >> (8 * g)) & 255);
+            cnt += 1ull << (8 * g);
+            out[dense ? n++ : 8 * k + g] = base | (pr << 13);
+        }
+    }
+    const int4 h0 = hdr[2 * t], h1 = hdr[2 * t + 1];
+    hdr_acc[2 * t] = h0;
+    hdr_acc[2 * t + 1] = make_int4(8 * q_off[t], 8 * nq, h1.z, h1.w);
+}
+
 __global__ void k_iota(int n, int* __restrict__ out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = i;
