@@ -695,6 +695,9 @@ static void build_tiles(ba_handle* h, int n_cams, int n_pts, int n_obs) {
            (const int*)ia.p, (const int*)ic.p, (const int*)h->ft_pt.p, (const int*)h->pt_off.p, (const int*)d_rs0.p,
            (const int*)h->ft_rs.p, (const double2*)h->pm_uv.p, (const int2*)h->pm_idx.p, h->tc_uv.p, h->tc_meta.p, h->pm_tc.p,
            seg_cam0.p, seg_start.p, (const int*)id.p, seg_split0.p);
+    if (!getenv("BA_B200_NO_SLOT_BALANCE"))  // (A/B hook) which observation takes which slot of its point's track: by bank load
+        launch(h, KN_SETUP, k_ft_slot_balance, T, 32, 0, (const int*)h->ft_pt.p, (const int*)h->ft_obs.p, (const int*)h->pt_off.p,
+               (const int*)d_rs0.p, (const int*)h->ft_rs.p, h->tc_meta.p);
     launch(h, KN_SETUP, k_ft_headers, cdiv(T, B), B, 0, T, (const int*)h->ft_pt.p, (const int*)h->ft_obs.p, (const int*)h->ft_seg.p,
            (const int*)d_rs0.p, (const int*)d_maxlen.p, h->ft_hdr.p);
     // segments longest first inside each tile, then rows camera-major (stable sort of the segments by camera)

@@ -894,6 +894,68 @@ __global__ void k_ft_slot_assign(int n_seg, int n_ep, const unsigned long long* 
     seg_slot[order[i]] = g - ep_g0[lo];
     if (i == 0 || key_s[i] != key_s[i - 1]) { slot_cam[g] = (unsigned)((key_s[i] >> 8) & 0xffffffffu); iota[g] = g; }
 }
+// Which observation of a point takes which slot of its track is free (the sums run over the slots in order, any fixed
+// assignment is deterministic), and it decides the shared-memory banks of the per-observation scatter of phases A (three
+// stores in the mat-vec pass, nine to fifteen in the linearisation): a half-warp of camera-ordered observations writes to
+// banks (rs[i] + q) mod 16.  With i = the observation's index in the point-major order the sixteen writes collide 2.8-fold
+// on average.  This pass re-deals the slots, one warp per tile: half-warp by half-warp, the observation whose point has
+// the fewest free slots first, each taking the free slot of its point whose bank is least loaded so far in the half-warp.
+__global__ void __launch_bounds__(32) k_ft_slot_balance(const int* __restrict__ ft_pt, const int* __restrict__ ft_obs,
+                                                        const int* __restrict__ pt_off, const int* __restrict__ rs0,
+                                                        const int* __restrict__ rs, int2* __restrict__ tc_meta) {
+    __shared__ unsigned s_free[FT_PTS][FT_THREADS / 32];  // free slots of every point of the tile
+    __shared__ int s_left[FT_PTS];
+    __shared__ int s_rs[FT_THREADS];
+    const int t = blockIdx.x, lane = threadIdx.x;
+    const int p0 = ft_pt[t], m = ft_pt[t + 1] - p0, o0 = ft_obs[t], n = ft_obs[t + 1] - o0;
+    if (m <= 0 || n <= 0) return;
+    const int maxlen = pt_off[p0 + 1] - pt_off[p0];  // longest track first
+    for (int q = lane; q < m; q += 32) {
+        const int len = pt_off[p0 + q + 1] - pt_off[p0 + q];
+        s_left[q] = len;
+#pragma unroll
+        for (int w = 0; w < FT_THREADS / 32; ++w) {
+            const int k = len - 32 * w;
+            s_free[q][w] = k >= 32 ? 0xffffffffu : (k > 0 ? (1u << k) - 1u : 0u);
+        }
+    }
+    for (int i = lane; i < maxlen; i += 32) s_rs[i] = rs[rs0[t] + i];
+    __syncwarp();
+    const int words = (maxlen + 31) >> 5;
+    for (int h = 0; h < n; h += 16) {
+        int load = 0;  // lane b < 16: writes of this half-warp that fall on bank b so far
+        int2 meta = make_int2(0, 0);
+        int myq = 0, mykey = 0x7fffffff, mypos = 0;
+        const bool mine = lane < 16 && h + lane < n;
+        if (mine) {
+            meta = tc_meta[o0 + h + lane];
+            myq = meta.y & 1023;
+            mykey = s_left[myq] * 16 + lane;
+        }
+        for (int step = 0; step < 16; ++step) {
+            const int kmin = __reduce_min_sync(0xffffffffu, mykey);
+            if (kmin == 0x7fffffff) break;
+            const int l = kmin & 15;
+            const int q = __shfl_sync(0xffffffffu, myq, l);
+            int best = 0x7fffffff;
+            for (int w = 0; w < words; ++w) {
+                const bool cand = (s_free[q][w] >> lane) & 1u;
+                const int i = 32 * w + lane;
+                const int bank = cand ? (s_rs[i] + q) & 15 : 0;
+                const int ld = __shfl_sync(0xffffffffu, load, bank);
+                if (cand) best = min(best, ld * 256 + i);
+            }
+            best = __reduce_min_sync(0xffffffffu, best);
+            const int i = best & 255, pos = s_rs[i] + q;
+            if (lane == (pos & 15)) ++load;
+            if (lane == 0) { s_free[q][i >> 5] &= ~(1u << (i & 31)); --s_left[q]; }
+            if (lane == l) { mypos = pos; mykey = 0x7fffffff; }
+            __syncwarp();
+        }
+        if (mine) tc_meta[o0 + h + lane] = make_int2(meta.x, (meta.y & 1023) | (mypos << 10));
+    }
+}
+
 // ---- packed work items of phase D (mat-vec pass with epoch accumulators) ----------------------------------------------
 // A work item = (segment, pair of components): one lane adds the segment's double2 values at positions a .. a+len-1 of plane
 // `pair` (plane stride FT_LD = 3 mod 8 sixteen-byte bank groups).  All lanes of a quarter-warp read element j of their item

@@ -470,12 +470,21 @@ def test_full_size_properties(gpu_solver, name):
         return
     # (4) at the point the solve reached, the WHOLE linearisation against the oracle's (analytic blocks over all observations,
     #     oracle/lm_schur.py::linearize): camera and point gradients, U and V blocks, and the gradient maximum the stopping
-    #     rule tests.  Tolerance 1e-9 of each block set's norm (float64 sums over up to 5 M terms in different orders).
+    #     rule tests.  Tolerance 1e-9 of each block set's norm (float64 sums over up to 5 M terms in different orders).  The
+    #     gradients are CANCELLING sums this close to the optimum (|g_c| is 1e-4 .. 1e-5 of the sum of the absolute values of its
+    #     terms after 12 iterations on venice, where the plain bound was met by 0.76e-9 or missed by 1.05e-9 depending on the
+    #     order in which a track is added up), so they also get the rounding allowance of their terms: 1e-12 of sum |J^T w r|.
     rvec, tvec, pts = gpu_solver.get_params()
     nb = gpu_solver.normal_blocks()
     lin = L.linearize(prob, rvec, tvec, pts)
+    adj = prob.obs_cam >= 0
+    wr = np.abs(lin.wg * lin.r)
+    abs_gc = np.zeros((fp.n_cams, 6)); abs_gp = np.zeros((fp.n_pts, 3))
+    np.add.at(abs_gc, prob.obs_cam[adj], np.einsum("nki,nk->ni", np.abs(lin.Jc[adj]), wr[adj]))
+    np.add.at(abs_gp, prob.obs_pt, np.einsum("nki,nk->ni", np.abs(lin.Jp), wr))
+    slack = {"gc": 1e-12 * np.linalg.norm(abs_gc), "gp": 1e-12 * np.linalg.norm(abs_gp), "U": 0.0, "V": 0.0}
     for key, ref in (("gc", lin.gc), ("gp", lin.gp), ("U", lin.U), ("V", lin.V)):
-        assert np.linalg.norm(nb[key] - ref) <= 1e-9 * np.linalg.norm(ref), key
+        assert np.linalg.norm(nb[key] - ref) <= 1e-9 * np.linalg.norm(ref) + slack[key], key
     gmax = max(np.abs(lin.gc).max(), np.abs(lin.gp).max())
     assert abs(max(np.abs(nb["gc"]).max(), np.abs(nb["gp"]).max()) - gmax) <= 1e-9 * gmax
     if name == "ladybug":
