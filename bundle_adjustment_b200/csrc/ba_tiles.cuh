@@ -477,21 +477,30 @@ __device__ unsigned long long g_ls_moved[8];  // experiment builds: points whose
 constexpr int LS_K = 6;
 __device__ __constant__ double kLsAlpha[LS_K] = {1.0, 0.5, 2.0, 4.0, 8.0, 16.0};
 
-// Persistent CTAs over contiguous runs of tiles.  Every thread stages the record and the measurement of ITS
-// observation of the next tile with cp.async while the current tile is computed (a thread only reads what it
-// copied itself: cp.async.wait_group, no barrier), and the tile headers are fetched two tiles ahead - the chain
-// header -> record -> pose/point of a tile no longer sits in front of its arithmetic.
+// Persistent CTAs over contiguous runs of tiles.  Everything a tile reads from HBM except the camera poses - the records and
+// measurements of its observations, its points (LS: the current points too), its track offsets and track rows - is staged
+// for the NEXT tile with cp.async while the current tile is computed; a tile ends with cp.async.wait_group 0 and the CTA
+// barrier it needs anyway, which publishes the next tile's data to all threads.  The tile headers are fetched two tiles
+// ahead.  (Before the points were staged, the first use of a point gathered from HBM / L2 and the track-table loads were
+// 14-18 % of the stall samples of this kernel, profiles/r02z.)
+BA_D void cp_async4(void* smem, const void* gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(smem_u32(smem)), "l"(gmem) : "memory");
+}
 template <bool LS>
 __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_lin(Params P, int which) {
-    __shared__ double sA[9 * FT_LDL];
-    __shared__ double sC[LS ? LS_K * FT_PTS : 1];
-    __shared__ double sX[LS ? 3 * FT_PTS : 1];
+    __shared__ double sA[9 * FT_LDL];  // LS: planes 0-5 hold the candidate costs, planes 6-8 their per-point sums (sC)
     __shared__ __align__(16) double2 sUv[2][FT_THREADS];
     __shared__ __align__(16) int2 sMeta[2][FT_THREADS];
-    __shared__ int sRs[FT_THREADS];
-    __shared__ int sOff[FT_PTS + 1];
+    __shared__ __align__(16) double2 sP01[2][FT_PTS];  // the tile's points in parameter buffer b (LS: replaced by the chosen positions)
+    __shared__ double sP2[2][FT_PTS];
+    __shared__ __align__(16) double2 sQ01[LS ? 2 : 1][LS ? FT_PTS : 1];  // LS: the current points (buffer b ^ 1)
+    __shared__ double sQ2[LS ? 2 : 1][LS ? FT_PTS : 1];
+    __shared__ int sRs[2][FT_THREADS];
+    __shared__ int sOff[2][FT_PTS + 1];
     __shared__ double red[FT_THREADS / 32 * 3];
     __shared__ double tot[3];
+    static_assert(LS_K * FT_PTS <= 3 * FT_LDL, "candidate sums alias three planes of the scratch");
+    double* const sC = sA + 6 * FT_LDL;
     const int b = resolve_buf(P.st, which);
     const int tid = threadIdx.x;
     int t = ft_cta_begin(blockIdx.x, P.ft_tiles, gridDim.x);
@@ -502,42 +511,55 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_lin(Params 
     double* const Gb = P.pt_g + (size_t)b * P.n_pts * 4;
     double acc[3] = {0.0, 0.0, 0.0};  // cost, raw, bad
     double gmax = 0.0;
-    auto stage = [&](int buf, const int4& h) {  // h = (p0, m, o0, n)
+    auto hdr_rows = [&](int tile) { return __ldg(reinterpret_cast<const int2*>(P.ft_hdr + 2 * tile + 1) + 1); };
+    auto stage = [&](int buf, const int4& h, const int2& g) {  // h = (p0, m, o0, n), g = (first track row, longest track)
         if (tid < h.w) {
             cp_async16(&sUv[buf][tid], P.tc_uv + h.z + tid);
             cp_async8(&sMeta[buf][tid], P.tc_meta + h.z + tid);
         }
+        if (tid < h.y) {
+            const double* xb = pt_base(P, b);
+            cp_async16(&sP01[buf][tid], reinterpret_cast<const double2*>(xb) + h.x + tid);
+            cp_async8(&sP2[buf][tid], xb + 2 * (size_t)P.n_pad + h.x + tid);
+            if constexpr (LS) {
+                const double* xc = pt_base(P, b ^ 1);
+                cp_async16(&sQ01[buf][tid], reinterpret_cast<const double2*>(xc) + h.x + tid);
+                cp_async8(&sQ2[buf][tid], xc + 2 * (size_t)P.n_pad + h.x + tid);
+            }
+        }
+        if (tid <= h.y) cp_async4(&sOff[buf][tid], P.pt_off + h.x + tid);
+        if (tid < g.y) cp_async4(&sRs[buf][tid], P.ft_rs + g.x + tid);
         asm volatile("cp.async.commit_group;\n" ::: "memory");
     };
     int4 ha = make_int4(0, 0, 0, 0), han = ha;
+    int2 hbn = make_int2(0, 0);
     if (t < t_end) {
         ha = __ldg(P.ft_hdr + 2 * t);
-        han = t + 1 < t_end ? __ldg(P.ft_hdr + 2 * (t + 1)) : ha;
-        stage(0, ha);
+        han = ha;
+        if (t + 1 < t_end) { han = __ldg(P.ft_hdr + 2 * (t + 1)); hbn = hdr_rows(t + 1); }
+        stage(0, ha, hdr_rows(t));
+        asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+        __syncthreads();
     }
     for (int it = 0; t < t_end; ++t, ++it) {
         const int buf = it & 1;
-        const int4 hann = t + 2 < t_end ? __ldg(P.ft_hdr + 2 * (t + 2)) : han;
-        const int4 hb = __ldg(P.ft_hdr + 2 * t + 1);  // (s0, ns, r0, maxlen)
+        int4 hann = han;
+        int2 hbnn = hbn;
+        if (t + 2 < t_end) { hann = __ldg(P.ft_hdr + 2 * (t + 2)); hbnn = hdr_rows(t + 2); }
         const int p0 = ha.x, m = ha.y, o0 = ha.z, n = ha.w;
-        const int rsv = tid < hb.w ? __ldg(P.ft_rs + hb.z + tid) : 0;
-        const int offv = tid <= m ? __ldg(P.pt_off + p0 + tid) : 0;
-        if (t + 1 < t_end) stage(buf ^ 1, han);
-        else asm volatile("cp.async.commit_group;\n" ::: "memory");
-        asm volatile("cp.async.wait_group 1;\n" ::: "memory");  // this tile's copies (of this thread) have landed
-        if (tid < hb.w) sRs[tid] = rsv;
-        if (tid <= m) sOff[tid] = offv;
+        if (t + 1 < t_end) stage(buf ^ 1, han, hbn);  // into the buffers tile t - 1 used: everybody has passed its last barrier
+        const int* const rs = sRs[buf];
+        const int* const off = sOff[buf];
         if constexpr (LS) {
-            const int cur = b ^ 1;
             if (tid < n) {
                 const int2 meta = sMeta[buf][tid];
                 const double2 uv = sUv[buf][tid];
-                const int pos = (meta.y >> 10) & 1023;
-                double X0[3], X[3], Rt[12];
+                const int pos = (meta.y >> 10) & 1023, pl = meta.y & 1023;
+                double Rt[12];
                 load_cam(camR, meta.x, Rt);
-                load_pt(P, b, p0 + (meta.y & 1023), X);
-                load_pt(P, cur, p0 + (meta.y & 1023), X0);
-                const double d[3] = {X[0] - X0[0], X[1] - X0[1], X[2] - X0[2]};
+                const double2 x01 = sP01[buf][pl], q01 = sQ01[buf][pl];
+                const double X0[3] = {q01.x, q01.y, sQ2[buf][pl]};
+                const double d[3] = {x01.x - X0[0], x01.y - X0[1], sP2[buf][pl] - X0[2]};
                 // x_cam(alpha) = (R X0 + t) + alpha R d
                 const double ax = fma(Rt[0], X0[0], fma(Rt[1], X0[1], fma(Rt[2], X0[2], Rt[9])));
                 const double ay = fma(Rt[3], X0[0], fma(Rt[4], X0[1], fma(Rt[5], X0[2], Rt[10])));
@@ -567,10 +589,10 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_lin(Params 
             __syncthreads();
             for (int w = tid; w < m * LS_K; w += FT_THREADS) {
                 const int q = w / LS_K, k = w - LS_K * q;
-                const int len = sOff[q + 1] - sOff[q];
+                const int len = off[q + 1] - off[q];
                 const double* src = sA + k * FT_LDL + q;
                 double sk = 0.0;
-                for (int i = 0; i < len; ++i) sk += src[sRs[i]];
+                for (int i = 0; i < len; ++i) sk += src[rs[i]];
                 sC[k * FT_PTS + q] = sk;
             }
             __syncthreads();
@@ -584,34 +606,31 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_lin(Params 
                     const double c = sC[k * FT_PTS + tid];
                     if (c < thr && c < best) { best = c; kb = k; }
                 }
-                double X0[3], X1[3];
-                load_pt(P, cur, p0 + tid, X0);
-                load_pt(P, b, p0 + tid, X1);
 #ifdef BA_DN_STAMPS
                 atomicAdd(&g_ls_moved[kb], 1ull);
 #endif
                 if (kb != 0) {
                     const double al = kLsAlpha[kb];
+                    const double2 x01 = sP01[buf][tid], q01 = sQ01[buf][tid];
+                    const double X0[3] = {q01.x, q01.y, sQ2[buf][tid]};
+                    double X1[3] = {x01.x, x01.y, sP2[buf][tid]};
 #pragma unroll
                     for (int k = 0; k < 3; ++k) X1[k] = fma(al, X1[k] - X0[k], X0[k]);
                     store_pt(P, b, p0 + tid, X1[0], X1[1], X1[2]);
+                    sP01[buf][tid] = make_double2(X1[0], X1[1]);
+                    sP2[buf][tid] = X1[2];
                 }
-                sX[3 * tid] = X1[0]; sX[3 * tid + 1] = X1[1]; sX[3 * tid + 2] = X1[2];
             }
-            __syncthreads();  // the chosen positions; and the candidate costs in sA have all been read
+            __syncthreads();  // the chosen positions; and the candidate costs and their sums in sA have all been read
         }
         if (tid < n) {
             const int2 meta = sMeta[buf][tid];
             const double2 uv = sUv[buf][tid];
-            const int pos = (meta.y >> 10) & 1023;
-            double X[3], Rt[12];
+            const int pos = (meta.y >> 10) & 1023, pl = meta.y & 1023;
+            double Rt[12];
             load_cam(camR, meta.x, Rt);  // (LS: again - from L1 - rather than twelve registers held across three barriers)
-            if constexpr (LS) {
-                const int q = meta.y & 1023;
-                X[0] = sX[3 * q]; X[1] = sX[3 * q + 1]; X[2] = sX[3 * q + 2];
-            } else {
-                load_pt(P, b, p0 + (meta.y & 1023), X);
-            }
+            const double2 x01 = sP01[buf][pl];
+            const double X[3] = {x01.x, x01.y, sP2[buf][pl]};
             ObsLin o;
             linearize_obs(Rt, X, uv.x, uv.y, P.K, o);
             double wHx, wgx, r0x, wHy, wgy, r0y;
@@ -645,10 +664,10 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_lin(Params 
         double* G = Gb + (size_t)p0 * 4;
         for (int w = tid; w < m * 9; w += FT_THREADS) {
             const int q = w / 9, k = w - 9 * q;
-            const int len = sOff[q + 1] - sOff[q];
+            const int len = off[q + 1] - off[q];
             const double* src = sA + k * FT_LDL + q;
             double sk = 0.0;
-            for (int i = 0; i < len; ++i) sk += src[sRs[i]];
+            for (int i = 0; i < len; ++i) sk += src[rs[i]];
             if (k < 6) {
                 V[q * 6 + k] = sk;
             } else {
@@ -656,8 +675,9 @@ __global__ void __launch_bounds__(FT_THREADS, FT_CTAS_PER_SM) k_tile_lin(Params 
                 gmax = fmax(gmax, fabs(sk));
             }
         }
-        __syncthreads();  // the scratch and the track tables are rewritten by the next tile
-        ha = han; han = hann;
+        asm volatile("cp.async.wait_group 0;\n" ::: "memory");  // the next tile's data (staged at the top of this one)
+        __syncthreads();  // ... becomes visible to everybody; and the scratch is rewritten by the next tile
+        ha = han; han = hann; hbn = hbnn;
     }
     block_sum<3, FT_THREADS>(acc, red, tot);
     __syncthreads();
