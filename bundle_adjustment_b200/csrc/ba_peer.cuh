@@ -516,12 +516,21 @@ __global__ void k_coarse_scatter(int n_cams, int agg, int nz, int d, const int* 
     A[(size_t)t * nz + 6 * a + d] = s;
 }
 // after the sum over the ranks: + lambda Z^T D Z (diagonal: the aggregates are disjoint) and symmetrise
+// cam_U != nullptr (direct build: A holds the point part only): + Z^T U Z, the aggregate sums of the (replicated) camera blocks
 __global__ void k_coarse_finish(int n_cams, int agg, int nz, const double* __restrict__ cam_D, const LMState* __restrict__ st,
-                                const double* __restrict__ A, double* __restrict__ out) {
+                                const double* __restrict__ A, double* __restrict__ out, const double* __restrict__ cam_U = nullptr) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= nz * nz) return;
     const int i = idx / nz, j = idx - i * nz;
     double v = 0.5 * (A[(size_t)i * nz + j] + A[(size_t)j * nz + i]);
+    if (cam_U && i / 6 == j / 6) {
+        const int a = i / 6, di = i - 6 * a, dj = j - 6 * a;
+        const int c0 = a * agg, c1 = min(c0 + agg, n_cams);
+        const int k = di <= dj ? sym6(di, dj) : sym6(dj, di);
+        double s = 0.0;
+        for (int c = c0; c < c1; ++c) s += cam_U[(size_t)c * 21 + k];
+        v += s;
+    }
     if (i == j) {
         const int a = i / 6, d = i - 6 * a;
         const int c0 = a * agg, c1 = min(c0 + agg, n_cams);
@@ -530,6 +539,188 @@ __global__ void k_coarse_finish(int n_cams, int agg, int nz, const double* __res
         v += st->lambda * s;
     }
     out[idx] = v;
+}
+
+// ---- the coarse matrix without probing -----------------------------------------------------------------------------------
+// A0 = Z^T S Z = Z^T U Z + lambda Z^T D Z - sum over the points of F_p^T (V_p + lambda D_p)^-1 F_p, with F_p = the point's E
+// blocks added up per aggregate.  With local camera coordinates the camera block of an observation is Jc = Jp G_p,
+// G_p = [-[X_p]x | I] (3 x 6), so E_cp^T = Jp^T W Jp G_p and the aggregate sum is F_{A,p} = W_{A,p} G_p, W_{A,p} = the sum of
+// Jt^T Jt (Jacobian cache) over the point's observations from cameras of aggregate A: the point part of A0 needs nothing but
+// the cache, the points and V^-1 - one pass over the point-major observation list instead of one mat-vec per probe vector
+// (30 tile passes + 90 small kernels on the venice shape: 3.7 of the 51 ms of a solve).
+//
+// The blocks of all points meet in nz x nz sums.  To keep them bit-reproducible WITHOUT ordering the additions they are
+// accumulated as 64-bit INTEGERS (integer addition is associative: any order, any mix of register, warp and L2 atomic adds
+// gives the same bits): entry (i, j) is scaled by 2^58 / sqrt(d_i d_j), d = diag(Z^T U Z).  The Schur complement of a
+// positive semi-definite matrix bounds every point's term, |t_ij| <= sqrt(u_ii u_jj) with u = the point's share of d, so by
+// Cauchy-Schwarz the absolute sum over the points is at most sqrt(d_i d_j): the scaled sum stays below 2^58, and the
+// rounding of a term is 2^-58 of that bound (18 k terms per entry on venice: 6e-14).
+constexpr int CD_POOL = 64;        // (point, aggregate run) entries a warp holds in shared memory per batch
+constexpr int CD_WARPS = 4;
+constexpr double CD_SCALE = 536870912.0;  // 2^29 per factor: 2^58 per entry
+__global__ void k_coarse_rscale(int n_cams, int agg, int nz, const double* __restrict__ cam_U, double* __restrict__ rscale) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nz) return;
+    const int a = k / 6, i = k - 6 * a;
+    const int c0 = a * agg, c1 = min(c0 + agg, n_cams);
+    double d = 0.0;
+    for (int c = c0; c < c1; ++c) d += cam_U[(size_t)c * 21 + sym6(i, i)];
+    rscale[k] = (d > 0.0 && isfinite(d)) ? CD_SCALE / sqrt(d) : 0.0;
+}
+// A warp walks a contiguous range of points, 32 at a time: every lane turns the runs of equal aggregate in ITS point's track
+// into entries F = W G (18 doubles) of the warp's pool, then the warp forms the 6 x 6 block of every ordered pair of entries
+// of a point, lane = entry of the block (36 over two rounds).  Consecutive points mostly produce the same few aggregate pairs,
+// so each lane keeps the running integer sums of four pairs in registers and sends one to L2 (RED.ADD.64) only when its pair
+// is evicted.  overflow[0] = 1: a point with more than CD_POOL runs (the caller then probes instead).
+__global__ void __launch_bounds__(CD_WARPS * 32) k_coarse_direct(Params P, int agg, int nz, const double* __restrict__ rscale,
+                                                                  unsigned long long* __restrict__ acc, int* __restrict__ overflow) {
+    __shared__ double sF[CD_WARPS][CD_POOL][18];
+    __shared__ int sAgg[CD_WARPS][CD_POOL];
+    __shared__ double sVi[CD_WARPS][32][6];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int b = P.st->cur;
+    const int n_warps = gridDim.x * CD_WARPS, gw = blockIdx.x * CD_WARPS + w;
+    const int per = ((P.n_pts + n_warps - 1) / n_warps + 31) & ~31;
+    const int pa = min(gw * per, P.n_pts), pb = min(pa + per, P.n_pts);
+    const double2* J = P.tc_J + (size_t)b * 3 * P.n_obs;
+    // four cached pairs per lane: key (warp-uniform), two running sums (entries lane and lane + 32)
+    int ckey[4] = {-1, -1, -1, -1};
+    long long c0v[4] = {0, 0, 0, 0}, c1v[4] = {0, 0, 0, 0};
+    int victim = 0;
+    const int i0 = lane / 6, j0 = lane - 6 * i0;               // entry of round 0
+    const int i1 = (lane + 32) / 6, j1 = (lane + 32) - 6 * i1;  // entry of round 1 (lanes 0-3)
+    auto flush = [&](int k) {
+        if (ckey[k] < 0) return;
+        const int A = ckey[k] / (nz / 6), B = ckey[k] - A * (nz / 6);
+        if (c0v[k]) atomicAdd(acc + (size_t)(A * 6 + i0) * nz + B * 6 + j0, (unsigned long long)c0v[k]);
+        if (lane < 4 && c1v[k]) atomicAdd(acc + (size_t)(A * 6 + i1) * nz + B * 6 + j1, (unsigned long long)c1v[k]);
+        ckey[k] = -1; c0v[k] = 0; c1v[k] = 0;
+    };
+    for (int p0 = pa; p0 < pb; p0 += 32) {
+        const int p = p0 + lane;
+        const bool valid = p < pb;
+        const int o0 = valid ? P.pt_off[p] : 0, o1 = valid ? P.pt_off[p + 1] : 0;
+        int runs = 0;
+        {
+            int last = -1;
+            for (int j = o0; j < o1; ++j) {
+                const int cam = P.pm_idx[j].x;
+                if (cam >= P.n_cams) continue;  // the fixed camera has no unknowns
+                const int A = cam / agg;
+                if (A != last) { ++runs; last = A; }
+            }
+        }
+        if (runs > CD_POOL) { *overflow = 1; runs = 0; }
+        bool done = runs == 0;
+        while (__any_sync(0xffffffffu, !done)) {
+            const int need = done ? 0 : runs;
+            int incl = need;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d) incl += t;
+            }
+            const int first = incl - need;
+            const bool take = !done && incl <= CD_POOL;  // a prefix of the lanes that are still waiting
+            if (take) {
+                double X[3], Vi[6];
+                load_pt(P, b, p, X);
+                load_sym3(P.pt_Vinv, p, Vi);
+#pragma unroll
+                for (int k = 0; k < 6; ++k) sVi[w][lane][k] = Vi[k];
+                int e = first - 1, last = -1;
+                double W[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+                auto emit = [&]() {  // F = W [-[X]x | I]: columns 0-2 = W (e_k x X) ... = -W [X]x, columns 3-5 = W
+                    const double Wm[3][3] = {{W[0], W[1], W[2]}, {W[1], W[3], W[4]}, {W[2], W[4], W[5]}};
+                    double* F = sF[w][e];
+#pragma unroll
+                    for (int r = 0; r < 3; ++r) {
+                        // row r of -W [X]x: (-[X]x) = [[0, X2, -X1], [-X2, 0, X0], [X1, -X0, 0]]
+                        F[r * 6 + 0] = -Wm[r][1] * X[2] + Wm[r][2] * X[1];
+                        F[r * 6 + 1] = Wm[r][0] * X[2] - Wm[r][2] * X[0];
+                        F[r * 6 + 2] = -Wm[r][0] * X[1] + Wm[r][1] * X[0];
+                        F[r * 6 + 3] = Wm[r][0]; F[r * 6 + 4] = Wm[r][1]; F[r * 6 + 5] = Wm[r][2];
+                    }
+                    sAgg[w][e] = last;
+                };
+                for (int j = o0; j < o1; ++j) {
+                    const int cam = P.pm_idx[j].x;
+                    if (cam >= P.n_cams) continue;
+                    const int A = cam / agg;
+                    if (A != last) {
+                        if (last >= 0) emit();
+                        ++e; last = A;
+#pragma unroll
+                        for (int k = 0; k < 6; ++k) W[k] = 0.0;
+                    }
+                    const int tc = P.pm_tc[j];
+                    const double2 a0 = J[tc], a1 = J[(size_t)P.n_obs + tc], a2 = J[2 * (size_t)P.n_obs + tc];
+                    const double jx[3] = {a0.x, a0.y, a1.x}, jy[3] = {a1.y, a2.x, a2.y};
+                    W[0] += jx[0] * jx[0] + jy[0] * jy[0]; W[1] += jx[0] * jx[1] + jy[0] * jy[1]; W[2] += jx[0] * jx[2] + jy[0] * jy[2];
+                    W[3] += jx[1] * jx[1] + jy[1] * jy[1]; W[4] += jx[1] * jx[2] + jy[1] * jy[2]; W[5] += jx[2] * jx[2] + jy[2] * jy[2];
+                }
+                if (last >= 0) emit();
+            }
+            __syncwarp();
+            for (int q = 0; q < 32; ++q) {
+                const int rq = __shfl_sync(0xffffffffu, take ? runs : 0, q);
+                if (rq == 0) continue;
+                const int fq = __shfl_sync(0xffffffffu, first, q);
+                const double* Vi = sVi[w][q];
+                const double v00 = Vi[0], v01 = Vi[1], v02 = Vi[2], v11 = Vi[3], v12 = Vi[4], v22 = Vi[5];
+                for (int e = fq; e < fq + rq; ++e) {
+                    const double* Fe = sF[w][e];
+                    const int Ae = sAgg[w][e];
+                    // g = V^-1 Fe[:, i] for the lane's two rows i0, i1
+                    const double f0 = Fe[i0], f1 = Fe[6 + i0], f2 = Fe[12 + i0];
+                    const double g0 = v00 * f0 + v01 * f1 + v02 * f2, g1 = v01 * f0 + v11 * f1 + v12 * f2, g2 = v02 * f0 + v12 * f1 + v22 * f2;
+                    double h0 = 0.0, h1 = 0.0, h2 = 0.0;
+                    if (lane < 4) {
+                        const double e0 = Fe[i1], e1 = Fe[6 + i1], e2 = Fe[12 + i1];
+                        h0 = v00 * e0 + v01 * e1 + v02 * e2; h1 = v01 * e0 + v11 * e1 + v12 * e2; h2 = v02 * e0 + v12 * e1 + v22 * e2;
+                    }
+                    const double se0 = rscale[Ae * 6 + i0], se1 = lane < 4 ? rscale[Ae * 6 + i1] : 0.0;
+                    for (int f = fq; f < fq + rq; ++f) {
+                        const double* Ff = sF[w][f];
+                        const int Af = sAgg[w][f];
+                        const int key = Ae * (nz / 6) + Af;
+                        const double t0 = g0 * Ff[j0] + g1 * Ff[6 + j0] + g2 * Ff[12 + j0];
+                        const long long q0 = __double2ll_rn(t0 * (se0 * rscale[Af * 6 + j0]));
+                        long long q1 = 0;
+                        if (lane < 4) {
+                            const double t1 = h0 * Ff[j1] + h1 * Ff[6 + j1] + h2 * Ff[12 + j1];
+                            q1 = __double2ll_rn(t1 * (se1 * rscale[Af * 6 + j1]));
+                        }
+                        int k = ckey[0] == key ? 0 : (ckey[1] == key ? 1 : (ckey[2] == key ? 2 : (ckey[3] == key ? 3 : -1)));
+                        if (k < 0) {  // warp-uniform: evict round-robin
+                            k = victim;
+                            victim = (victim + 1) & 3;
+#pragma unroll
+                            for (int kk = 0; kk < 4; ++kk)
+                                if (kk == k) { flush(kk); ckey[kk] = key; }
+                        }
+#pragma unroll
+                        for (int kk = 0; kk < 4; ++kk)
+                            if (kk == k) { c0v[kk] += q0; c1v[kk] += q1; }
+                    }
+                }
+            }
+            __syncwarp();
+            done |= take;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) flush(k);
+}
+// point part of this rank's A0 as doubles (negative: it is subtracted), ready for the sum over the ranks
+__global__ void k_coarse_from_acc(int nz, const double* __restrict__ rscale, const unsigned long long* __restrict__ acc,
+                                  double* __restrict__ A, const int* __restrict__ overflow, double* __restrict__ overflow_out) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx == 0) overflow_out[0] = (double)overflow[0];  // as a double: it goes through the all-reduce (max) of a multi-GPU handle
+    if (idx >= nz * nz) return;
+    const int i = idx / nz, j = idx - i * nz;
+    const double r = rscale[i] * rscale[j];
+    A[idx] = r > 0.0 ? -(double)(long long)acc[idx] / r : 0.0;
 }
 
 // In-place inverse of the symmetric positive definite coarse matrix by Gauss-Jordan elimination without pivoting, on ONE

@@ -26,6 +26,7 @@
 #include <mutex>
 #include <stdexcept>
 #include <string>
+#include <functional>
 #include <vector>
 
 namespace ba {
@@ -428,6 +429,8 @@ struct ba_handle {
     DBuf<double> coarse_Ainv, coarse_A, coarse_A2, coarse_probe, coarse_w;
     DBuf<unsigned char> coarse_adj;
     DBuf<int> coarse_colour, coarse_nb, coarse_flag;
+    DBuf<unsigned long long> coarse_acc;  // direct build: integer sums of the point part of the coarse matrix (k_coarse_direct)
+    DBuf<double> coarse_rscale;
     int coarse_agg = 32, coarse_nz = 0;
     int coarse_colours = 0, coarse_graph_agg = 0;  // colouring of the aggregate graph of the uploaded problem (0: not built)
     bool coarse_ready = false;
@@ -1495,12 +1498,31 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
         CK(cudaStreamSynchronize(s));
         h->coarse_colours = ncol; h->coarse_graph_agg = agg;
     };
-    auto build_coarse = [&]() {  // between k_camera_finish_schur and the first PCG iteration: V^-1, lambda and D are current
+    // direct = the point part of A0 in one pass over the point-major observations (k_coarse_direct); otherwise (a point whose
+    // track changes aggregate more than CD_POOL times, or BA_B200_COARSE_PROBE set: the A/B and test hook) by coloured probing
+    std::function<bool(bool)> build_coarse_with = [&](bool direct) -> bool {  // between k_camera_finish_schur and the first PCG iteration: V^-1, lambda and D are current
         const int nz = h->coarse_nz, agg = h->coarse_agg, na = nz / 6;
-        coarse_colouring();
         h->coarse_A.alloc((size_t)nz * nz); h->coarse_A2.alloc((size_t)nz * nz); h->coarse_Ainv.alloc((size_t)nz * nz);
-        h->coarse_probe.alloc((size_t)nc1 * 6); h->coarse_w.alloc((size_t)nc1 * 6); h->coarse_flag.alloc(1);
-        h->coarse_A.zero(s); h->coarse_flag.zero(s);
+        h->coarse_flag.alloc(2);
+        h->coarse_flag.zero(s);
+        if (direct) {
+            h->coarse_acc.alloc((size_t)nz * nz); h->coarse_rscale.alloc((size_t)nz + 1);
+            h->coarse_acc.zero(s);
+            launch(h, KN_SETUP, k_coarse_rscale, cdiv(nz, 128), 128, 0, P.n_cams, agg, nz, (const double*)P.cam_U, h->coarse_rscale.p);
+            launch(h, KN_SETUP, k_coarse_direct, 5 * h->sm_count, CD_WARPS * 32, 0, P, agg, nz, (const double*)h->coarse_rscale.p,
+                   h->coarse_acc.p, h->coarse_flag.p + 1);
+            launch(h, KN_SETUP, k_coarse_from_acc, cdiv((long long)nz * nz, 256), 256, 0, nz, (const double*)h->coarse_rscale.p,
+                   (const unsigned long long*)h->coarse_acc.p, h->coarse_A.p, (const int*)(h->coarse_flag.p + 1), h->coarse_rscale.p + nz);
+            // a track that did not fit the pool on ANY rank sends all ranks to the probing build (same collectives everywhere)
+            if (h->nranks > 1) allreduce_max(h, h->coarse_rscale.p + nz, 1);
+            double ovf = 0.0;
+            CK(cudaMemcpyAsync(&ovf, h->coarse_rscale.p + nz, sizeof(double), cudaMemcpyDeviceToHost, s));
+            CK(cudaStreamSynchronize(s));
+            if (ovf != 0.0) return build_coarse_with(false);
+        } else {
+        coarse_colouring();
+        h->coarse_probe.alloc((size_t)nc1 * 6); h->coarse_w.alloc((size_t)nc1 * 6);
+        h->coarse_A.zero(s);
         Params PQ = PA;  // the row finish leaves this rank's part of S * probe (without the damping term) in a scratch vector
         PQ.cam_acc = h->coarse_w.p;
         for (int col = 0; col < h->coarse_colours; ++col)
@@ -1513,9 +1535,10 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
                        (const int*)(h->coarse_nb.p + (size_t)col * na), (const double*)h->coarse_w.p, h->coarse_A.p);
                 ++coarse_matvecs;
             }
+        }
         allreduce_sum(h, h->coarse_A.p, (size_t)nz * nz);
         launch(h, KN_SETUP, k_coarse_finish, cdiv((long long)nz * nz, 256), 256, 0, P.n_cams, agg, nz, (const double*)P.cam_D,
-               (const LMState*)h->st.p, (const double*)h->coarse_A.p, h->coarse_A2.p);
+               (const LMState*)h->st.p, (const double*)h->coarse_A.p, h->coarse_A2.p, direct ? (const double*)P.cam_U : (const double*)nullptr);
         ++coarse_builds;
         // inverse on the device by the tail's cluster when its rows fit shared memory, else on the host
         int cl = h->tail_cluster;
@@ -1563,7 +1586,7 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
                 const bool rebuild = h->coarse_ready && used_coarse_last && lm_iter_host - coarse_built_at >= 3 &&
                                      last_pcg_iters > std::max(30, 2 * pcg_after_build);
                 if (first_build || rebuild) {
-                    h->coarse_ready = build_coarse();
+                    h->coarse_ready = build_coarse_with(!getenv("BA_B200_COARSE_PROBE"));
                     coarse_failed = !h->coarse_ready;
                     coarse_built_at = lm_iter_host;
                     pcg_at_build = last_pcg_iters;
