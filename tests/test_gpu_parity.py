@@ -510,10 +510,11 @@ def test_full_size_properties(gpu_solver, name):
 
 
 def test_two_level_preconditioner_against_the_cpu_statement(gpu_solver):
-    """The two-level preconditioner (Schur-Jacobi + coarse space; coarse matrix by coloured probing with the tile pass, inverse
-    by the cluster Gauss-Jordan kernel) against its CPU statement (oracle/lm_schur.py::pcg with Z / A0_inv) on ONE linear
-    system: same number of PCG iterations to the same stopping rule, and the same LM step (cameras and points after one
-    iteration) - not only the same final cost."""
+    """The two-level preconditioner (Schur-Jacobi + coarse space; inverse of the coarse matrix by the cluster Gauss-Jordan
+    kernel) against its CPU statement (oracle/lm_schur.py::pcg with Z / A0_inv) on ONE linear system: same number of PCG
+    iterations to the same stopping rule, and the same LM step (cameras and points after one iteration) - not only the same
+    final cost.  Both builds of the coarse matrix: directly from the Jacobian cache (k_coarse_direct, the default: no mat-vec)
+    and by coloured probing with the tile pass (BA_B200_COARSE_PROBE, also the fallback) - and the two against each other."""
     fp = S.make_flat_problem(300, 12000, 60000, seed=31)
     prob = O.Problem.from_flat(fp)
     lam0, agg, tol = 1e-6, 32, 1e-3
@@ -533,17 +534,33 @@ def test_two_level_preconditioner_against_the_cpu_statement(gpu_solver):
     rv, tv, pn = L.retract(fp.rvec, fp.tvec, fp.pts, dc, dp)
     pn, alpha = L.point_linesearch(prob, rv, tv, fp.pts, pn)
 
-    gpu_solver.set_flat(fp)
     kw = dict(max_iters=1, initial_lambda=lam0, pcg_tol=tol, pcg_max_iters=400, ftol=0.0, xtol=0.0, gtol=0.0, device_loop=0)
-    st = gpu_solver.solve(precond="two_level", coarse_after=-1, coarse_aggregate=agg, **kw)
-    assert st["precond_text"] == "two_level" and st["coarse_builds"] == 1 and st["coarse_unknowns"] == Z.shape[1]
-    assert st["coarse_matvecs"] < Z.shape[1]            # coloured probing: far fewer mat-vecs than coarse unknowns
-    assert st["accepted"] == 1
-    assert abs(st["pcg_iterations"] - it_ref) <= 1, (st["pcg_iterations"], it_ref)
-    r1, t1, p1 = gpu_solver.get_params()
     scale = np.abs(tv).max()
-    assert np.abs(r1 - rv).max() <= 1e-7 and np.abs(t1 - tv).max() <= 1e-7 * scale
-    assert np.abs(p1 - pn).max() <= 1e-6 * np.abs(pn).max()
+    got = {}
+    for build in ("direct", "probing"):
+        gpu_solver.set_flat(fp)
+        if build == "probing":
+            os.environ["BA_B200_COARSE_PROBE"] = "1"
+        try:
+            st = gpu_solver.solve(precond="two_level", coarse_after=-1, coarse_aggregate=agg, **kw)
+        finally:
+            os.environ.pop("BA_B200_COARSE_PROBE", None)
+        assert st["precond_text"] == "two_level" and st["coarse_builds"] == 1 and st["coarse_unknowns"] == Z.shape[1]
+        if build == "direct":
+            assert st["coarse_matvecs"] == 0
+        else:
+            assert 0 < st["coarse_matvecs"] < Z.shape[1]    # coloured probing: far fewer mat-vecs than coarse unknowns
+        assert st["accepted"] == 1
+        assert abs(st["pcg_iterations"] - it_ref) <= 1, (build, st["pcg_iterations"], it_ref)
+        r1, t1, p1 = gpu_solver.get_params()
+        assert np.abs(r1 - rv).max() <= 1e-7 and np.abs(t1 - tv).max() <= 1e-7 * scale, build
+        assert np.abs(p1 - pn).max() <= 1e-6 * np.abs(pn).max(), build
+        got[build] = (st["pcg_iterations"], st["final_cost"], r1, t1, p1)
+    # the two coarse matrices are the same matrix (the direct one to 2^-58 of sqrt(d_i d_j) per term): same PCG, same step
+    assert got["direct"][0] == got["probing"][0]
+    assert abs(got["direct"][1] - got["probing"][1]) <= 1e-10 * got["probing"][1]
+    assert np.abs(got["direct"][2] - got["probing"][2]).max() <= 1e-9 and np.abs(got["direct"][3] - got["probing"][3]).max() <= 1e-9 * scale
+    assert np.abs(got["direct"][4] - got["probing"][4]).max() <= 1e-9 * np.abs(pn).max()
     # Schur-Jacobi on the same system: the CPU statement's count again (what the coarse space buys shows over a whole solve,
     # once the damping has fallen and smooth modes dominate the residual: next test)
     gpu_solver.set_flat(fp)
