@@ -45,11 +45,12 @@ typedef struct ba_handle ba_handle;
 #define BA_PRECOND_JACOBI 0       /* camera blocks of J^T J                                    */
 #define BA_PRECOND_SCHUR_JACOBI 1 /* diagonal blocks of the Schur complement                    */
 #define BA_PRECOND_TWO_LEVEL 2    /* Schur-Jacobi plus an additive coarse correction  Z (Z^T S Z)^-1 Z^T : one rigid 6-vector per
-                                     aggregate of consecutive cameras; the coarse matrix is probed with the tile pass (one
-                                     mat-vec per colour of the aggregate graph and component) once the PCG of an LM iteration
+                                     aggregate of consecutive cameras; the coarse matrix is built from the Jacobian cache in one
+                                     pass over the points (fallback: probed with the tile pass, one mat-vec per colour of the
+                                     aggregate graph and component) once the PCG of an LM iteration
                                      has needed more than 24 iterations, inverted on the device and kept (rebuilt when the
                                      iteration count climbs again; skipped for an LM iteration whose damping is more than 4x away
-                                     from the one it was probed with).  Needs the default kernel path (tiles + cluster tail; on
+                                     from the one it was built with).  Needs the default kernel path (tiles + cluster tail; on
                                      N > 1 GPUs the peer-memory exchange); where that is unavailable the solve runs with
                                      Schur-Jacobi and says so in ba_stats.precond_used.  Host-driven loops.              */
 #define BA_PRECOND_AUTO 3         /* two-level for >= 128 adjustable cameras, else Schur-Jacobi               (default) */
@@ -107,7 +108,7 @@ typedef struct ba_stats {
     double solve_ms;          /* CUDA-event time of the device LM loop                              */
     int32_t precond_used;     /* BA_PRECOND_* the PCG actually ran with (TWO_LEVEL only if a coarse matrix was built)   */
     int32_t coarse_builds;    /* coarse matrices built during the solve                                                 */
-    int32_t coarse_matvecs;   /* tile-pass mat-vecs spent on probing them (not counted in pcg_iterations)               */
+    int32_t coarse_matvecs;   /* tile-pass mat-vecs spent on probing them (0 with the direct build; not in pcg_iterations) */
     int32_t coarse_unknowns;  /* size of the coarse system (6 x aggregates), 0 if none                                  */
     int32_t dense_solves;     /* LM iterations whose step came from the dense factorisation (0: PCG was used)         */
     int32_t reserved_i;
