@@ -788,6 +788,101 @@ __global__ void __launch_bounds__(PT_THREADS, 1) k_spd_inverse(int n, const doub
     for (int l = tid; l < nr * n; l += PT_THREADS) Ainv[(size_t)r0 * n + l] = M[l];
     if (tid == 0 && s_bad) atomicExch(flag, 1);
 }
+// The same elimination with 6 x 6 PIVOT BLOCKS (n = 6 x aggregates): one cluster barrier per aggregate instead of one per
+// unknown - the scalar version spends its 1.1 ms (n = 336) on 336 barrier + remote-read round trips, not on arithmetic.
+// Step K: the owner of block row K inverts its 6 x 6 pivot block (scalar Gauss-Jordan by one warp, the same pivots as the
+// scalar elimination, so the positivity test is the same), replaces the block row by P^-1 [row] (P^-1 itself in block column
+// K) and publishes the six rows; every CTA then subtracts F R from its other rows (F = their old block column K), block
+// column K becoming -F P^-1.  Rows are dealt to the CTAs in multiples of 6.
+__host__ __device__ inline int spd6_rows_per(int n, int cluster) { return 6 * ((n / 6 + cluster - 1) / cluster); }
+__host__ __device__ inline size_t spd6_smem_bytes(int n, int cluster) {
+    const int rp = spd6_rows_per(n, cluster);
+    return ((size_t)rp * n + 18 * (size_t)n + (size_t)rp * 6 + 36) * sizeof(double);
+}
+__global__ void __launch_bounds__(PT_THREADS, 1) k_spd_inverse6(int n, const double* __restrict__ A, double* __restrict__ Ainv,
+                                                                 int* __restrict__ flag) {
+    extern __shared__ __align__(16) double dsm[];
+    __shared__ int s_bad;
+    namespace cgx = cooperative_groups;
+    cgx::cluster_group cl = cgx::this_cluster();
+    const int R = (int)cl.block_rank(), CL = (int)cl.num_blocks();
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int rp = spd6_rows_per(n, CL);
+    const int r0 = min(R * rp, n), r1 = min(r0 + rp, n);
+    const int nr = r1 - r0;
+    double* M = dsm;                          // [rp][n] my rows
+    double* prow = M + (size_t)rp * n;        // [2][6][n] pivot rows published by their owners
+    double* lrow = prow + 12 * (size_t)n;     // [6][n] local copy of the current pivot rows
+    double* fcol = lrow + 6 * (size_t)n;      // [rp][6] my rows' old block column K
+    double* sP = fcol + (size_t)rp * 6;       // [36] the pivot block while it is inverted
+    for (int l = tid; l < nr * n; l += PT_THREADS) M[l] = A[(size_t)r0 * n + l];
+    if (tid == 0) s_bad = 0;
+    __syncthreads();
+    for (int K = 0; K < n / 6; ++K) {
+        const int k0 = 6 * K, owner = k0 / rp;
+        double* mine = prow + (size_t)(K & 1) * 6 * n;
+        if (R == owner) {  // CTA-uniform
+            const int lr = k0 - r0;
+            if (tid < 36) sP[tid] = M[(size_t)(lr + tid / 6) * n + k0 + tid % 6];
+            __syncthreads();
+            if (tid < 32) {  // in-place inverse of the 6 x 6 block: lane e holds elements e and (lanes 0-3) e + 32
+                for (int k = 0; k < 6; ++k) {
+                    const double piv = sP[k * 6 + k];
+                    if (lane == 0 && (!(piv > 0.0) || !isfinite(piv))) s_bad = 1;
+                    const double ip = 1.0 / piv;
+                    double nv[2] = {0.0, 0.0};
+#pragma unroll
+                    for (int hh = 0; hh < 2; ++hh) {
+                        const int e = lane + 32 * hh;
+                        if (e < 36) {
+                            const int i = e / 6, j = e - 6 * i;
+                            const double pj = (j == k) ? ip : sP[k * 6 + j] * ip;  // element j of the scaled pivot row
+                            if (i == k) nv[hh] = pj;
+                            else {
+                                const double f = sP[i * 6 + k];
+                                nv[hh] = (j == k) ? -f * ip : sP[e] - f * pj;
+                            }
+                        }
+                    }
+                    __syncwarp();
+                    sP[lane] = nv[0];
+                    if (lane < 4) sP[lane + 32] = nv[1];
+                    __syncwarp();
+                }
+            }
+            __syncthreads();
+            for (int l = tid; l < 6 * n; l += PT_THREADS) {  // the new block row: P^-1 [old rows]; P^-1 in block column K
+                const int r = l / n, j = l - r * n;
+                double v = 0.0;
+                if (j >= k0 && j < k0 + 6) v = sP[r * 6 + (j - k0)];
+                else
+#pragma unroll
+                    for (int c = 0; c < 6; ++c) v += sP[r * 6 + c] * M[(size_t)(lr + c) * n + j];
+                mine[l] = v;
+            }
+            __syncthreads();  // the old rows have all been read
+            for (int l = tid; l < 6 * n; l += PT_THREADS) M[(size_t)lr * n + l] = mine[l];
+        }
+        cl.sync();
+        const double* pr = cl.map_shared_rank(prow, owner) + (size_t)(K & 1) * 6 * n;
+        for (int l = tid; l < 6 * n; l += PT_THREADS) lrow[l] = pr[l];
+        for (int l = tid; l < nr * 6; l += PT_THREADS) fcol[l] = M[(size_t)(l / 6) * n + k0 + (l % 6)];
+        __syncthreads();
+        for (int l = tid; l < nr * n; l += PT_THREADS) {
+            const int i = l / n, j = l - i * n;
+            if (r0 + i >= k0 && r0 + i < k0 + 6) continue;  // the pivot rows are done
+            const double* f = fcol + 6 * i;
+            double sacc = 0.0;
+#pragma unroll
+            for (int r = 0; r < 6; ++r) sacc += f[r] * lrow[(size_t)r * n + j];
+            M[l] = (j >= k0 && j < k0 + 6) ? -sacc : M[l] - sacc;
+        }
+        __syncthreads();
+    }
+    cl.sync();  // nobody leaves while a peer may still read its pivot buffer
+    for (int l = tid; l < nr * n; l += PT_THREADS) Ainv[(size_t)r0 * n + l] = M[l];
+    if (tid == 0 && s_bad) atomicExch(flag, 1);
+}
 // After k_camera_finish_schur (u = Minv r, gamma = r.u): add the coarse correction to u and redo gamma.  One CTA.
 __global__ void __launch_bounds__(PT_THREADS) k_coarse_first(Params P, Coarse C, unsigned long long pcg_loop) {
     extern __shared__ __align__(16) double sy[];  // [nz] correction, [nz] restricted residual

@@ -1542,12 +1542,19 @@ static void solve(ba_handle* h, const ba_options* opt, ba_stats* out) {
         ++coarse_builds;
         // inverse on the device by the tail's cluster when its rows fit shared memory, else on the host
         int cl = h->tail_cluster;
-        const size_t sb = spd_smem_bytes(nz, cl);
+        // 6 x 6 pivot blocks (one cluster barrier per aggregate); the scalar elimination behind BA_B200_SCALAR_INVERSE (A/B hook)
+        const bool blocked = !getenv("BA_B200_SCALAR_INVERSE");
+        const void* inv_fn = blocked ? (const void*)k_spd_inverse6 : (const void*)k_spd_inverse;
+        const size_t sb = blocked ? spd6_smem_bytes(nz, std::max(cl, 1)) : spd_smem_bytes(nz, std::max(cl, 1));
         bool on_device = cl >= 1 && sb <= 200 * 1024 && !getenv("BA_B200_HOST_INVERSE") &&
-                         cudaFuncSetAttribute(k_spd_inverse, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess &&
-                         cudaFuncSetAttribute(k_spd_inverse, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb) == cudaSuccess;
+                         cudaFuncSetAttribute(inv_fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess &&
+                         cudaFuncSetAttribute(inv_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb) == cudaSuccess;
         cudaGetLastError();
         if (on_device) {
+            if (blocked)
+                launch_cluster(h, KN_SETUP, k_spd_inverse6, cl, PT_THREADS, sb, nz, (const double*)h->coarse_A2.p, h->coarse_Ainv.p,
+                               h->coarse_flag.p);
+            else
             launch_cluster(h, KN_SETUP, k_spd_inverse, cl, PT_THREADS, sb, nz, (const double*)h->coarse_A2.p, h->coarse_Ainv.p,
                            h->coarse_flag.p);
             int bad = 0;
