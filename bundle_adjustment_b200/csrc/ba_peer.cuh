@@ -630,16 +630,19 @@ __global__ void __launch_bounds__(CD_WARPS * 32) k_coarse_direct(Params P, int a
                 for (int k = 0; k < 6; ++k) sVi[w][lane][k] = Vi[k];
                 int e = first - 1, last = -1;
                 double W[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-                auto emit = [&]() {  // F = W [-[X]x | I]: columns 0-2 = W (e_k x X) ... = -W [X]x, columns 3-5 = W
+                auto emit = [&]() {  // F = W [-[X]x | I]: columns 0-2 = -W [X]x, columns 3-5 = W; column i scaled by rscale[6 A + i]
                     const double Wm[3][3] = {{W[0], W[1], W[2]}, {W[1], W[3], W[4]}, {W[2], W[4], W[5]}};
                     double* F = sF[w][e];
+                    double rs[6];
+#pragma unroll
+                    for (int k = 0; k < 6; ++k) rs[k] = rscale[last * 6 + k];
 #pragma unroll
                     for (int r = 0; r < 3; ++r) {
                         // row r of -W [X]x: (-[X]x) = [[0, X2, -X1], [-X2, 0, X0], [X1, -X0, 0]]
-                        F[r * 6 + 0] = -Wm[r][1] * X[2] + Wm[r][2] * X[1];
-                        F[r * 6 + 1] = Wm[r][0] * X[2] - Wm[r][2] * X[0];
-                        F[r * 6 + 2] = -Wm[r][0] * X[1] + Wm[r][1] * X[0];
-                        F[r * 6 + 3] = Wm[r][0]; F[r * 6 + 4] = Wm[r][1]; F[r * 6 + 5] = Wm[r][2];
+                        F[r * 6 + 0] = (-Wm[r][1] * X[2] + Wm[r][2] * X[1]) * rs[0];
+                        F[r * 6 + 1] = (Wm[r][0] * X[2] - Wm[r][2] * X[0]) * rs[1];
+                        F[r * 6 + 2] = (-Wm[r][0] * X[1] + Wm[r][1] * X[0]) * rs[2];
+                        F[r * 6 + 3] = Wm[r][0] * rs[3]; F[r * 6 + 4] = Wm[r][1] * rs[4]; F[r * 6 + 5] = Wm[r][2] * rs[5];
                     }
                     sAgg[w][e] = last;
                 };
@@ -668,29 +671,36 @@ __global__ void __launch_bounds__(CD_WARPS * 32) k_coarse_direct(Params P, int a
                 const int fq = __shfl_sync(0xffffffffu, first, q);
                 const double* Vi = sVi[w][q];
                 const double v00 = Vi[0], v01 = Vi[1], v02 = Vi[2], v11 = Vi[3], v12 = Vi[4], v22 = Vi[5];
+                // t(e, f)[i][j] = Fe[:, i] . V^-1 Ff[:, j] (already scaled).  Unordered pairs e <= f: the block of (f, e) is the
+                // transpose.  Equal aggregates go to the diagonal key (the block, plus its transpose when e != f: a track that
+                // returns to an aggregate); A_e < A_f to key (A_e, A_f); A_e > A_f (a track not sorted by camera) to key
+                // (A_f, A_e) transposed.  k_coarse_from_acc mirrors the upper block triangle.
+                auto tval = [&](const double* Fa, const double* Fb, int i, int j) {
+                    const double f0 = Fa[i], f1 = Fa[6 + i], f2 = Fa[12 + i];
+                    const double g0 = v00 * f0 + v01 * f1 + v02 * f2, g1 = v01 * f0 + v11 * f1 + v12 * f2, g2 = v02 * f0 + v12 * f1 + v22 * f2;
+                    return g0 * Fb[j] + g1 * Fb[6 + j] + g2 * Fb[12 + j];
+                };
                 for (int e = fq; e < fq + rq; ++e) {
                     const double* Fe = sF[w][e];
                     const int Ae = sAgg[w][e];
-                    // g = V^-1 Fe[:, i] for the lane's two rows i0, i1
-                    const double f0 = Fe[i0], f1 = Fe[6 + i0], f2 = Fe[12 + i0];
-                    const double g0 = v00 * f0 + v01 * f1 + v02 * f2, g1 = v01 * f0 + v11 * f1 + v12 * f2, g2 = v02 * f0 + v12 * f1 + v22 * f2;
-                    double h0 = 0.0, h1 = 0.0, h2 = 0.0;
-                    if (lane < 4) {
-                        const double e0 = Fe[i1], e1 = Fe[6 + i1], e2 = Fe[12 + i1];
-                        h0 = v00 * e0 + v01 * e1 + v02 * e2; h1 = v01 * e0 + v11 * e1 + v12 * e2; h2 = v02 * e0 + v12 * e1 + v22 * e2;
-                    }
-                    const double se0 = rscale[Ae * 6 + i0], se1 = lane < 4 ? rscale[Ae * 6 + i1] : 0.0;
-                    for (int f = fq; f < fq + rq; ++f) {
+                    for (int f = e; f < fq + rq; ++f) {
                         const double* Ff = sF[w][f];
                         const int Af = sAgg[w][f];
-                        const int key = Ae * (nz / 6) + Af;
-                        const double t0 = g0 * Ff[j0] + g1 * Ff[6 + j0] + g2 * Ff[12 + j0];
-                        const long long q0 = __double2ll_rn(t0 * (se0 * rscale[Af * 6 + j0]));
-                        long long q1 = 0;
-                        if (lane < 4) {
-                            const double t1 = h0 * Ff[j1] + h1 * Ff[6 + j1] + h2 * Ff[12 + j1];
-                            q1 = __double2ll_rn(t1 * (se1 * rscale[Af * 6 + j1]));
+                        double t0, t1 = 0.0;
+                        if (Ae <= Af) {  // warp-uniform
+                            t0 = tval(Fe, Ff, i0, j0);
+                            if (lane < 4) t1 = tval(Fe, Ff, i1, j1);
+                            if (Ae == Af && e != f) {
+                                t0 += tval(Fe, Ff, j0, i0);
+                                if (lane < 4) t1 += tval(Fe, Ff, j1, i1);
+                            }
+                        } else {
+                            t0 = tval(Fe, Ff, j0, i0);
+                            if (lane < 4) t1 = tval(Fe, Ff, j1, i1);
                         }
+                        const int key = min(Ae, Af) * (nz / 6) + max(Ae, Af);
+                        const long long q0 = __double2ll_rn(t0);
+                        const long long q1 = __double2ll_rn(t1);
                         int k = ckey[0] == key ? 0 : (ckey[1] == key ? 1 : (ckey[2] == key ? 2 : (ckey[3] == key ? 3 : -1)));
                         if (k < 0) {  // warp-uniform: evict round-robin
                             k = victim;
@@ -720,7 +730,9 @@ __global__ void k_coarse_from_acc(int nz, const double* __restrict__ rscale, con
     if (idx >= nz * nz) return;
     const int i = idx / nz, j = idx - i * nz;
     const double r = rscale[i] * rscale[j];
-    A[idx] = r > 0.0 ? -(double)(long long)acc[idx] / r : 0.0;
+    // only the upper block triangle (aggregate of the row <= aggregate of the column) was accumulated
+    const size_t src = (i / 6 <= j / 6) ? (size_t)idx : (size_t)j * nz + i;
+    A[idx] = r > 0.0 ? -(double)(long long)acc[src] / r : 0.0;
 }
 
 // In-place inverse of the symmetric positive definite coarse matrix by Gauss-Jordan elimination without pivoting, on ONE
@@ -811,16 +823,19 @@ __global__ void __launch_bounds__(PT_THREADS, 1) k_spd_inverse6(int n, const dou
     const int r0 = min(R * rp, n), r1 = min(r0 + rp, n);
     const int nr = r1 - r0;
     double* M = dsm;                          // [rp][n] my rows
-    double* prow = M + (size_t)rp * n;        // [2][6][n] pivot rows published by their owners
-    double* lrow = prow + 12 * (size_t)n;     // [6][n] local copy of the current pivot rows
-    double* fcol = lrow + 6 * (size_t)n;      // [rp][6] my rows' old block column K
+    double* lrow = M + (size_t)rp * n;        // [2][6][n] the pivot rows of a step, PUSHED into every CTA by their owner (remote
+                                              // stores before the cluster barrier: pulling them afterwards cost a distributed-
+                                              // shared-memory load latency per step, 40 % of the kernel's stall samples)
+    double* tmp = lrow + 12 * (size_t)n;      // [6][n] owner: the new block row before it replaces the old one
+    double* fcol = tmp + 6 * (size_t)n;       // [rp][6] my rows' old block column K
     double* sP = fcol + (size_t)rp * 6;       // [36] the pivot block while it is inverted
     for (int l = tid; l < nr * n; l += PT_THREADS) M[l] = A[(size_t)r0 * n + l];
     if (tid == 0) s_bad = 0;
     __syncthreads();
+    cl.sync();  // every CTA of the cluster is resident before the first remote store
     for (int K = 0; K < n / 6; ++K) {
         const int k0 = 6 * K, owner = k0 / rp;
-        double* mine = prow + (size_t)(K & 1) * 6 * n;
+        const size_t boff = (size_t)(K & 1) * 6 * n;  // a buffer is rewritten two steps later: everybody has passed a barrier since
         if (R == owner) {  // CTA-uniform
             const int lr = k0 - r0;
             if (tid < 36) sP[tid] = M[(size_t)(lr + tid / 6) * n + k0 + tid % 6];
@@ -858,14 +873,17 @@ __global__ void __launch_bounds__(PT_THREADS, 1) k_spd_inverse6(int n, const dou
                 else
 #pragma unroll
                     for (int c = 0; c < 6; ++c) v += sP[r * 6 + c] * M[(size_t)(lr + c) * n + j];
-                mine[l] = v;
+                tmp[l] = v;
             }
             __syncthreads();  // the old rows have all been read
-            for (int l = tid; l < 6 * n; l += PT_THREADS) M[(size_t)lr * n + l] = mine[l];
+            for (int l = tid; l < 6 * n; l += PT_THREADS) {
+                const double v = tmp[l];
+                M[(size_t)lr * n + l] = v;
+                for (int d = 0; d < CL; ++d) cl.map_shared_rank(lrow, d)[boff + l] = v;
+            }
         }
-        cl.sync();
-        const double* pr = cl.map_shared_rank(prow, owner) + (size_t)(K & 1) * 6 * n;
-        for (int l = tid; l < 6 * n; l += PT_THREADS) lrow[l] = pr[l];
+        cl.sync();  // release / acquire: the owner's remote stores are visible
+        const double* pr = lrow + boff;
         for (int l = tid; l < nr * 6; l += PT_THREADS) fcol[l] = M[(size_t)(l / 6) * n + k0 + (l % 6)];
         __syncthreads();
         for (int l = tid; l < nr * n; l += PT_THREADS) {
@@ -874,12 +892,12 @@ __global__ void __launch_bounds__(PT_THREADS, 1) k_spd_inverse6(int n, const dou
             const double* f = fcol + 6 * i;
             double sacc = 0.0;
 #pragma unroll
-            for (int r = 0; r < 6; ++r) sacc += f[r] * lrow[(size_t)r * n + j];
+            for (int r = 0; r < 6; ++r) sacc += f[r] * pr[(size_t)r * n + j];
             M[l] = (j >= k0 && j < k0 + 6) ? -sacc : M[l] - sacc;
         }
         __syncthreads();
     }
-    cl.sync();  // nobody leaves while a peer may still read its pivot buffer
+    cl.sync();  // nobody leaves while a peer may still store into its pivot buffers
     for (int l = tid; l < nr * n; l += PT_THREADS) Ainv[(size_t)r0 * n + l] = M[l];
     if (tid == 0 && s_bad) atomicExch(flag, 1);
 }
