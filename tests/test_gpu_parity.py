@@ -395,6 +395,44 @@ def _dense_visibility_problem(n_cams=300, n_pts=50, track=120, seed=21):
                          X_t + rng.normal(0, 0.03, X_t.shape), (cam - 1).astype(np.int32), pt.astype(np.int32), uv)
 
 
+def _track_slot_stats(layout):
+    """Per tile: the slots the observations of every point were dealt (tc_meta) against the transposed track layout
+    rs[i] + q (i < track length of local point q; rs[i] = number of slots of the shorter rows), and the bank conflicts of
+    the scatter: sum over half-warps of the largest number of writes that fall on one of the 16 eight-byte banks."""
+    meta, ft_obs, ft_pt = layout["tc_meta"], layout["ft_obs"], layout["ft_pt"]
+    wavefronts = ideal = 0
+    for t in range(len(ft_pt) - 1):
+        o0, o1, m = int(ft_obs[t]), int(ft_obs[t + 1]), int(ft_pt[t + 1] - ft_pt[t])
+        if o1 == o0:
+            continue
+        pl = meta[o0:o1, 1] & 1023
+        pos = (meta[o0:o1, 1] >> 10) & 1023
+        lens = np.bincount(pl, minlength=m)
+        assert np.all(np.diff(lens) <= 0), "points of a tile are ordered longest track first"
+        rs = np.concatenate([[0], np.cumsum([(lens > i).sum() for i in range(int(lens.max()))])])
+        for q in range(m):
+            want = {int(rs[i]) + q for i in range(int(lens[q]))}
+            assert set(pos[pl == q].tolist()) == want, (t, q)   # a bijection between the point's observations and its slots
+        for h in range(0, o1 - o0, 16):
+            wavefronts += int(np.bincount(pos[h:h + 16] % 16, minlength=16).max())
+            ideal += 1
+    return wavefronts, ideal
+
+
+def test_track_slots_are_dealt_by_bank_load(gpu_solver, monkeypatch):
+    """k_ft_slot_balance: every observation of a point still owns exactly one slot of the point's track (so the per-point sums
+    see every term once), and the per-observation scatter into those slots collides less than with the point-major dealing."""
+    fp = S.make_flat_problem(60, 5000, 26000, seed=8)
+    gpu_solver.set_flat(fp)
+    balanced, ideal = _track_slot_stats(gpu_solver.tile_layout())
+    monkeypatch.setenv("BA_B200_NO_SLOT_BALANCE", "1")
+    gpu_solver.set_flat(fp)
+    plain, ideal2 = _track_slot_stats(gpu_solver.tile_layout())
+    monkeypatch.delenv("BA_B200_NO_SLOT_BALANCE")
+    assert ideal == ideal2
+    assert balanced < 0.85 * plain, (balanced, plain, ideal)
+
+
 def test_tiles_with_more_cameras_than_accumulator_slots(gpu_solver):
     """When an epoch of even one tile needs more accumulator slots than fit, the tile pass writes one row per segment
     (automatic `tiles_rows`); the mat-vec is still the dense Schur complement's and the solve the two-pass solve."""
