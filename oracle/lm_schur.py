@@ -311,6 +311,70 @@ def coarse_matrix_by_probing(matvec, Z: np.ndarray) -> np.ndarray:
     return 0.5 * (A0 + A0.T)
 
 
+def coarse_matrix_direct(prob: O.Problem, lin: Linearization, pts, lam: float, agg: int, dmin=1e-6, dmax=1e32,
+                         integer_bits=58):
+    """Z^T S Z without a mat-vec - the CPU statement of the device's k_coarse_direct (csrc/ba_peer.cuh).  With local camera
+    coordinates Jc = Jp G_p, G_p = [-[X_p]x | I], so the E blocks of point p summed over the cameras of aggregate A are
+    F_{A,p} = W_{A,p} G_p, W_{A,p} = sum of Jp^T wH Jp over the point's observations from A, and
+        Z^T S Z = Z^T U Z + lam Z^T D Z - sum_p F_p^T (V_p + lam D_p)^-1 F_p.
+    integer_bits: the point part is accumulated like on the device, as integers after scaling entry (i, j) by
+    2^bits / sqrt(d_i d_j), d = diag(Z^T U Z) (python integers: exact; the test checks the bound |sum| <= 2^bits that the
+    device's 64-bit accumulators rely on).  None = plain float64 sums."""
+    nc, n_agg = prob.n_cams, (prob.n_cams + agg - 1) // agg
+    nz = 6 * n_agg
+    adj = prob.obs_cam >= 0
+    ca, pa = prob.obs_cam[adj], prob.obs_pt[adj]
+    aa = ca // agg
+    W = np.einsum("nki,nk,nkj->nij", lin.Jp[adj], lin.wH[adj], lin.Jp[adj])                     # (Na,3,3)
+    Dp = np.clip(np.einsum("nii->ni", lin.V), dmin, dmax)
+    Vinv = np.linalg.inv(lin.V + lam * np.einsum("ni,ij->nij", Dp, np.eye(3)))
+    G = np.concatenate([-skew(pts), np.broadcast_to(np.eye(3), (prob.n_pts, 3, 3))], axis=2)   # (Np,3,6)
+    # one entry per (point, aggregate): F = W_{A,p} G_p
+    key = pa.astype(np.int64) * n_agg + aa
+    uniq, inv = np.unique(key, return_inverse=True)
+    WA = np.zeros((len(uniq), 3, 3))
+    np.add.at(WA, inv, W)
+    ep, ea = uniq // n_agg, uniq % n_agg
+    F = np.einsum("nij,njk->nik", WA, G[ep])                                                   # (Ne,3,6)
+    ZUZ = np.zeros((nz, nz))
+    for c in range(nc):
+        a = c // agg
+        ZUZ[6 * a:6 * a + 6, 6 * a:6 * a + 6] += lin.U[c]
+    d = np.diag(ZUZ).copy()
+    rscale = np.where(d > 0.0, 1.0 / np.sqrt(np.where(d > 0.0, d, 1.0)), 0.0)
+    point_part = np.zeros((nz, nz))
+    acc = np.zeros((nz, nz), dtype=object) if integer_bits is not None else None
+    if acc is not None:
+        acc[:] = 0
+    order = np.argsort(ep, kind="stable")
+    start = np.searchsorted(ep[order], np.arange(prob.n_pts + 1))
+    for p in range(prob.n_pts):
+        es = order[start[p]:start[p + 1]]
+        for e in es:
+            HeT = F[e].T @ Vinv[p]                                                             # (6,3)
+            for f in es:
+                T = HeT @ F[f]                                                                 # block (A_e, A_f)
+                i0, j0 = 6 * ea[e], 6 * ea[f]
+                if acc is None:
+                    point_part[i0:i0 + 6, j0:j0 + 6] += T
+                else:
+                    sc = np.outer(rscale[i0:i0 + 6], rscale[j0:j0 + 6]) * 2.0 ** integer_bits
+                    q = np.rint(T * sc)
+                    for i in range(6):
+                        for j in range(6):
+                            acc[i0 + i, j0 + j] += int(q[i, j])
+    if acc is not None:
+        big = max(abs(int(v)) for v in acc.ravel())
+        assert big <= 2 ** integer_bits, "the Cauchy-Schwarz bound of the scaled sums"
+        sc = np.outer(rscale, rscale) * 2.0 ** integer_bits
+        point_part = np.where(sc > 0.0, acc.astype(float) / np.where(sc > 0.0, sc, 1.0), 0.0)
+    Dc = np.clip(np.einsum("nii->ni", lin.U), dmin, dmax)
+    ZDZ = np.zeros(nz)
+    np.add.at(ZDZ, (6 * (np.arange(nc) // agg))[:, None] + np.arange(6)[None, :], Dc)
+    A0 = ZUZ + lam * np.diag(ZDZ) - point_part
+    return 0.5 * (A0 + A0.T)
+
+
 def pcg(matvec, b, Minv_blocks, *, tol=0.1, max_iters=100, Z=None, A0_inv=None):
     """CG preconditioned with the 6x6 blocks `Minv_blocks` (n_cams,6,6) and, if Z / A0_inv are given, the additive coarse
     correction  M^-1 r = blockdiag r + Z A0^-1 Z^T r.  Stops like the device: r^T M^-1 r <= tol^2 r0^T M^-1 r0.
