@@ -87,6 +87,7 @@ SYMBOLS = {
     "ba_kernel_stats": (C.c_int, [C.c_void_p, _lp, _dp]),
     "ba_layout_info": (C.c_int, [C.c_void_p, _lp]),
     "ba_tile_layout": (C.c_int, [C.c_void_p, _ip, _ip, _ip, _ip, _dp, _ip, _ip, _ip, _ip, _ip]),
+    "ba_tile_items": (C.c_int, [C.c_void_p, _lp, _ip, _ip]),
     "ba_triangulate": (C.c_int, [C.c_void_p, _dp, _dp, _dp, _dp, C.c_int32, _dp, _dp, _dp, _dp, C.POINTER(C.c_uint8)]),
     "ba_triangulate_static": (C.c_int, [C.c_void_p, _dp, _dp, _dp, _dp, C.c_int32, _dp, _dp, _dp, _dp, C.POINTER(C.c_uint8)]),
     "ba_map_clear": (C.c_int, [C.c_void_p]),

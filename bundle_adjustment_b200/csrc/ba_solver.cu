@@ -2246,6 +2246,21 @@ int ba_layout_info(ba_handle* h, int64_t out[12]) {
     API_END
 }
 
+int ba_tile_items(ba_handle* h, int64_t* n_slots, int32_t* items, int32_t* hdr_acc) {
+    API_BEGIN
+    ba::need_problem(h);
+    if (!n_slots) ba::fail(BA_ERR_ARG, "null output");
+    const bool acc = h->fused_ok && h->acc_ok;
+    *n_slots = acc ? h->n_item_slots : 0;
+    if (acc) {
+        cudaStream_t s = h->stream;
+        if (items) CK(cudaMemcpyAsync(items, h->seg_item.p, (size_t)h->n_item_slots * sizeof(int), cudaMemcpyDeviceToHost, s));
+        if (hdr_acc) CK(cudaMemcpyAsync(hdr_acc, h->ft_hdr_acc.p, (size_t)h->ft_tiles * 8 * sizeof(int), cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+    }
+    API_END
+}
+
 int ba_tile_layout(ba_handle* h, int32_t* ft_pt, int32_t* ft_obs, int32_t* ft_seg, int32_t* tc_meta, double* tc_uv,
                    int32_t* seg_cam, int32_t* seg_info, int32_t* seg_row, int32_t* cam_row_off, int32_t* pt_perm) {
     API_BEGIN

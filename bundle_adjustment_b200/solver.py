@@ -271,6 +271,16 @@ class FlatSolver:
             api.iptr(out["seg_info"]), api.iptr(out["seg_row"]), api.iptr(out["cam_row_off"]), api.iptr(out["pt_perm"])))
         return out
 
+    def tile_items(self) -> Dict[str, np.ndarray]:
+        """The packed work items of the accumulator mat-vec pass and its tile headers (test hook, ``ba_tile_items``)."""
+        n = np.zeros(1, dtype=np.int64)
+        api.check(api.lib().ba_tile_items(self._h, api.lptr(n), None, None))
+        T = self.layout_info()["point_tiles"]
+        items, hdr = np.zeros(int(n[0]), dtype=np.int32), np.zeros((T, 8), dtype=np.int32)
+        if n[0] > 0:
+            api.check(api.lib().ba_tile_items(self._h, api.lptr(n), api.iptr(items), api.iptr(hdr)))
+        return {"items": items, "hdr": hdr}
+
     def kernel_stats(self) -> Dict[str, Tuple[int, float]]:
         L = api.lib()
         n = L.ba_kernel_count()

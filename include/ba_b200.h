@@ -234,6 +234,13 @@ int ba_layout_info(ba_handle* h, int64_t out[12]);
 int ba_tile_layout(ba_handle* h, int32_t* ft_pt, int32_t* ft_obs, int32_t* ft_seg, int32_t* tc_meta, double* tc_uv,
                    int32_t* seg_cam, int32_t* seg_info, int32_t* seg_row, int32_t* cam_row_off, int32_t* pt_perm);
 
+/* Test hook: the packed work items of the mat-vec pass with epoch accumulators (csrc/ba_tiles.cuh, k_ft_item_fill; no counterpart in
+ * the reference, whose least_squares call has no such structure).  *n_slots = item slots of all tiles (0 if the accumulators are
+ * not in use); items[*n_slots] (item = first position | length << 8 | pair << 13 | accumulator slot << 15, 0 = empty lane, eight
+ * per quarter-warp); hdr_acc[T * 8] = the pass's tile headers ((p0, points, o0, observations), (first item, item slots, first
+ * track row, longest track)).  items / hdr_acc may be NULL (size query). */
+int ba_tile_items(ba_handle* h, int64_t* n_slots, int32_t* items, int32_t* hdr_acc);
+
 /* Two-view linear triangulation of n correspondences and the cheirality test, on the device: replaces the
  * reference's  cv2.triangulatePoints(P1, P2, pts1.T, pts2.T)  followed by  X = h[:3] / (h[3] + 1e-6), z > 0 in
  * both views  (src/pipeline.py:315-336).  P1, P2: row-major 3x4 projection matrices; R_rel[9] (row-major), t_rel[3]:

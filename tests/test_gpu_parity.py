@@ -433,6 +433,44 @@ def test_track_slots_are_dealt_by_bank_load(gpu_solver, monkeypatch):
     assert balanced < 0.85 * plain, (balanced, plain, ideal)
 
 
+def test_phase_d_work_items_cover_every_segment_once(gpu_solver):
+    """k_ft_item_fill: the packed work items of the accumulator mat-vec pass are exactly the (segment, pair of components)
+    items of every tile - each once, the three of a segment on one accumulator slot, different segments of a tile on
+    different slots - and the eight items of a quarter-warp start in eight different 16-byte bank groups."""
+    fp = S.make_flat_problem(60, 5000, 26000, seed=8)
+    gpu_solver.set_flat(fp)
+    info = gpu_solver.layout_info()
+    assert info["epoch_tiles"] > 0, "this problem is served by the accumulator pass"
+    lay, it = gpu_solver.tile_layout(), gpu_solver.tile_items()
+    items, hdr = it["items"], it["hdr"]
+    assert len(items) > 0 and len(items) % 8 == 0
+    ft_seg, seg_info = lay["ft_seg"], lay["seg_info"]
+    conflict_free = quarters = 0
+    for t in range(info["point_tiles"]):
+        i0, n = int(hdr[t, 4]), int(hdr[t, 5])
+        assert i0 % 8 == 0 and n % 8 == 0
+        assert hdr[t, 0] == lay["ft_pt"][t] and hdr[t, 2] == lay["ft_obs"][t]
+        mine = items[i0:i0 + n]
+        live = mine[mine != 0]
+        a, ln, pr, slot = live & 255, (live >> 8) & 31, (live >> 13) & 3, live >> 15
+        s0, s1 = int(ft_seg[t]), int(ft_seg[t + 1])
+        want = sorted((int(si & 0xffff), int(si >> 16), p) for si in seg_info[s0:s1] for p in range(3))
+        assert sorted(zip(a.tolist(), ln.tolist(), pr.tolist())) == want, t
+        by_seg = {}
+        for ai, si in zip(a.tolist(), slot.tolist()):
+            by_seg.setdefault(ai, set()).add(si)
+        assert all(len(v) == 1 for v in by_seg.values()), t                        # one slot per segment ...
+        assert len({next(iter(v)) for v in by_seg.values()}) == len(by_seg), t     # ... and no two segments share one
+        assert slot.max(initial=0) < 96
+        for q in range(0, n, 8):
+            w = mine[q:q + 8]
+            w = w[w != 0]
+            g = ((w & 255) + 3 * ((w >> 13) & 3)) & 7
+            quarters += 1
+            conflict_free += int(len(set(g.tolist())) == len(g))
+    assert conflict_free == quarters, (conflict_free, quarters)   # (a tile that fell back to the dense numbering would show here)
+
+
 def test_tiles_with_more_cameras_than_accumulator_slots(gpu_solver):
     """When an epoch of even one tile needs more accumulator slots than fit, the tile pass writes one row per segment
     (automatic `tiles_rows`); the mat-vec is still the dense Schur complement's and the solve the two-pass solve."""
